@@ -1,0 +1,407 @@
+"""``mlx.core`` stand-in (NumPy backed; torch-CPU for the dense convolutions).
+
+TEST INFRASTRUCTURE ONLY - see oracle/mlx_shim/mlx/__init__.py.
+"""
+from __future__ import annotations
+
+import builtins
+import numbers
+import types
+
+import numpy as np
+
+float32 = np.dtype("float32")
+int32 = np.dtype("int32")
+int64 = np.dtype("int64")
+bool_ = np.dtype("bool")
+complex64 = np.dtype("complex64")
+float16 = np.dtype("float16")
+pi = float(np.pi)
+
+_DOWN = {np.dtype("float64"): float32, np.dtype("complex128"): complex64, np.dtype("int64"): int32}
+
+
+def _down(a):
+    a = np.asarray(a)
+    t = _DOWN.get(a.dtype)
+    return a.astype(t) if t is not None else a
+
+
+def _wrap(a):
+    if isinstance(a, tuple):
+        return tuple(_wrap(x) for x in a)
+    if isinstance(a, list):
+        return [_wrap(x) for x in a]
+    a = _down(a)
+    return a.view(array)
+
+
+def _raw(x):
+    return x.view(np.ndarray) if isinstance(x, np.ndarray) else x
+
+
+def _kind(x):
+    if isinstance(x, np.ndarray) or isinstance(x, np.generic):
+        return np.asarray(x).dtype.kind
+    if isinstance(x, builtins.bool):
+        return "b"
+    if isinstance(x, numbers.Integral):
+        return "i"
+    if isinstance(x, numbers.Real):
+        return "f"
+    if isinstance(x, numbers.Complex):
+        return "c"
+    return "O"
+
+
+def _promote(inputs, force_float=False):
+    """MLX promotion: python scalars are weak; any float operand => everything float32."""
+    kinds = [_kind(x) for x in inputs]
+    has_c = "c" in kinds
+    has_f = "f" in kinds or force_float
+    out = []
+    for x, k in zip(inputs, kinds):
+        x = _raw(x)
+        if has_c:
+            x = np.asarray(x).astype(np.complex64) if k != "c" or np.asarray(x).dtype != np.complex64 else x
+        elif has_f:
+            if k in "biu" or (k == "f" and np.asarray(x).dtype != np.float32):
+                x = np.asarray(x).astype(np.float32)
+        elif k in "iu":
+            if not isinstance(x, np.ndarray):
+                x = np.asarray(x, dtype=np.int32)
+        out.append(x)
+    return out
+
+
+class _At:
+    def __init__(self, arr, idx=None):
+        self.arr, self.idx = arr, idx
+
+    def __getitem__(self, idx):
+        return _At(self.arr, idx)
+
+    def add(self, vals):
+        out = np.array(_raw(self.arr), copy=True)
+        np.add.at(out, _raw(self.idx), _raw(np.asarray(vals)).astype(out.dtype))
+        return _wrap(out)
+
+
+class array(np.ndarray):
+    """mx.array: ndarray subclass with float32/int32 defaults and MLX-style promotion."""
+
+    def __new__(cls, obj, dtype=None):
+        a = np.asarray(_raw(obj) if isinstance(obj, np.ndarray) else obj)
+        if dtype is not None:
+            a = a.astype(dtype)
+        else:
+            a = _down(a)
+        return np.array(a, copy=True).view(cls)
+
+    def __array_ufunc__(self, ufunc, method, *inputs, out=None, **kwargs):
+        if method == "at":
+            return NotImplemented
+        force_float = ufunc in (np.true_divide, np.sqrt, np.sin, np.cos, np.exp, np.tanh, np.arctan2, np.log,
+                                np.log10)
+        if method == "__call__":
+            ins = _promote(inputs, force_float)
+        else:
+            ins = [_raw(x) for x in inputs]
+        if out is not None:
+            kwargs["out"] = tuple(_raw(o) for o in out)
+        res = getattr(ufunc, method)(*ins, **kwargs)
+        if out is not None:
+            return out[0] if len(out) == 1 else out
+        if isinstance(res, tuple):
+            return tuple(_wrap(r) for r in res)
+        return _wrap(res)
+
+    @property
+    def at(self):
+        return _At(self)
+
+    def moveaxis(self, src, dst):
+        return _wrap(np.moveaxis(_raw(self), src, dst))
+
+    def abs(self):
+        return abs(self)
+
+    def square(self):
+        return self * self
+
+    def log(self):
+        return log(self)
+
+    def log10(self):
+        return _wrap(np.log10(_raw(self)))
+
+    def flatten(self, *a, **k):
+        return _wrap(np.ndarray.flatten(_raw(self)))
+
+    def astype(self, dtype, *a, **k):
+        return _raw(self).astype(dtype).view(array)
+
+    def item(self):
+        return _raw(self).item()
+
+
+def _f(x):
+    """Array-ify an elementwise-function argument (python scalars become float32)."""
+    if isinstance(x, np.ndarray):
+        return _raw(x)
+    return np.asarray(x, dtype=np.float32 if _kind(x) in "bif" else None)
+
+
+def _unary(fn):
+    def g(x, *a, **k):
+        x = _f(x)
+        if x.dtype.kind in "biu" and fn not in (np.abs, np.floor, np.ceil):
+            x = x.astype(np.float32)
+        return _wrap(fn(x, *a, **k))
+    return g
+
+
+sin, cos, exp, tanh, sqrt, log, floor, ceil = (_unary(f) for f in
+                                               (np.sin, np.cos, np.exp, np.tanh, np.sqrt, np.log, np.floor, np.ceil))
+abs = _unary(np.abs)  # noqa: A001
+round = _unary(np.round)  # noqa: A001
+
+
+def sigmoid(x):
+    x = _f(x)
+    return _wrap(1.0 / (1.0 + np.exp(-x)))
+
+
+def arctan2(a, b):
+    a, b = _promote([a, b], True)
+    return _wrap(np.arctan2(a, b))
+
+
+def imag(z):
+    return _wrap(np.imag(_raw(z)))
+
+
+def real(z):
+    return _wrap(np.real(_raw(z)))
+
+
+def _ax(axis):
+    return tuple(axis) if isinstance(axis, list) else axis
+
+
+def sum(x, axis=None, keepdims=False):  # noqa: A001
+    return _wrap(np.sum(_raw(x), axis=_ax(axis), keepdims=keepdims, dtype=_raw(x).dtype))
+
+
+def mean(x, axis=None, keepdims=False):
+    return _wrap(np.mean(_raw(x), axis=_ax(axis), keepdims=keepdims, dtype=_raw(x).dtype))
+
+
+def var(x, axis=None, keepdims=False, ddof=0):
+    return _wrap(np.var(_raw(x), axis=_ax(axis), keepdims=keepdims, ddof=ddof, dtype=_raw(x).dtype))
+
+
+def prod(x, axis=None, keepdims=False):
+    return _wrap(np.prod(_raw(x), axis=_ax(axis), keepdims=keepdims, dtype=_raw(x).dtype))
+
+
+def max(x, axis=None, keepdims=False):  # noqa: A001
+    return _wrap(np.max(_raw(x), axis=_ax(axis), keepdims=keepdims))
+
+
+def cumsum(x, axis=None):
+    x = _raw(x)
+    return _wrap(np.cumsum(x, axis=axis, dtype=x.dtype))  # sequential, in the array dtype
+
+
+def zeros(shape, dtype=float32):
+    return _wrap(np.zeros(shape, dtype))
+
+
+def ones(shape, dtype=float32):
+    return _wrap(np.ones(shape, dtype))
+
+
+def zeros_like(x):
+    return _wrap(np.zeros_like(_raw(x)))
+
+
+def arange(*args, dtype=None):
+    a = np.arange(*args)
+    if dtype is not None:
+        a = a.astype(dtype)
+    return _wrap(a)
+
+
+def linspace(start, stop, num=50, dtype=float32):
+    t = np.arange(num, dtype=np.float32) / np.float32(num - 1)
+    return _wrap((np.float32(start) * (np.float32(1) - t) + np.float32(stop) * t).astype(dtype))
+
+
+def expand_dims(x, axis):
+    return _wrap(np.expand_dims(_raw(x), axis))
+
+
+def squeeze(x, axis=None):
+    return _wrap(np.squeeze(_raw(x), axis))
+
+
+def split(x, n, axis=0):
+    return [_wrap(p) for p in np.split(_raw(x), n, axis=axis)]
+
+
+def concatenate(xs, axis=0):
+    return _wrap(np.concatenate([_raw(np.asarray(x)) for x in xs], axis=axis))
+
+
+def stack(xs, axis=0):
+    return _wrap(np.stack([_raw(np.asarray(x)) for x in xs], axis=axis))
+
+
+def tile(x, reps):
+    return _wrap(np.tile(_raw(x), reps))
+
+
+def repeat(x, n, axis=None):
+    return _wrap(np.repeat(_raw(np.asarray(x)), n, axis=axis))
+
+
+def where(c, a, b):
+    a, b = _promote([a, b])
+    return _wrap(np.where(_raw(np.asarray(c)), a, b))
+
+
+def minimum(a, b):
+    a, b = _promote([a, b])
+    return _wrap(np.minimum(a, b))
+
+
+def maximum(a, b):
+    a, b = _promote([a, b])
+    return _wrap(np.maximum(a, b))
+
+
+def clip(x, a_min=None, a_max=None):
+    return _wrap(np.clip(_raw(x), a_min, a_max))
+
+
+def broadcast_to(x, shape):
+    return _wrap(np.broadcast_to(_raw(x), shape))
+
+
+def roll(x, shifts, axis=None):
+    return _wrap(np.roll(_raw(x), shifts, axis))
+
+
+def reshape(x, shape):
+    return _wrap(np.reshape(_raw(x), shape))
+
+
+def swapaxes(x, a, b):
+    return _wrap(np.swapaxes(_raw(x), a, b))
+
+
+def transpose(x, axes=None):
+    return _wrap(np.transpose(_raw(x), axes))
+
+
+def pad(x, pad_width, constant_values=0):
+    x = _raw(x)
+    if isinstance(pad_width, numbers.Integral):
+        pad_width = [(pad_width, pad_width)] * x.ndim
+    elif isinstance(pad_width, tuple) and len(pad_width) == 2 and all(isinstance(p, numbers.Integral) for p in pad_width):
+        pad_width = [tuple(pad_width)] * x.ndim
+    return _wrap(np.pad(x, pad_width, constant_values=constant_values))
+
+
+def as_strided(x, shape, strides, offset=0):
+    x = np.ascontiguousarray(_raw(x)).ravel()[offset:]
+    it = x.itemsize
+    v = np.lib.stride_tricks.as_strided(x, shape=shape, strides=tuple(s * it for s in strides), writeable=False)
+    return _wrap(np.array(v))
+
+
+def _torch():
+    import torch
+    import torch.nn.functional as F
+    return torch, F
+
+
+def conv1d(x, w, stride=1, padding=0, dilation=1, groups=1):
+    """x (N,L,C_in), w (C_out,K,C_in/groups) -> (N,L_out,C_out); cross-correlation, zero padding."""
+    torch, F = _torch()
+    xt = torch.from_numpy(np.ascontiguousarray(_raw(x))).transpose(1, 2)
+    wt = torch.from_numpy(np.ascontiguousarray(_raw(w))).permute(0, 2, 1)
+    y = F.conv1d(xt, wt, None, int(stride), int(padding), int(dilation), int(groups))
+    return _wrap(y.transpose(1, 2).contiguous().numpy())
+
+
+def conv_transpose1d(x, w, stride=1, padding=0, dilation=1, groups=1):
+    """x (N,L,C_in), w (C_out,K,C_in/groups) -> (N,(L-1)s-2p+d(K-1)+1,C_out)."""
+    torch, F = _torch()
+    xt = torch.from_numpy(np.ascontiguousarray(_raw(x))).transpose(1, 2)
+    wn = torch.from_numpy(np.ascontiguousarray(_raw(w)))
+    groups = int(groups)
+    if groups == 1:
+        wt = wn.permute(2, 0, 1)  # (C_in, C_out, K)
+    else:
+        cout, k, cin_g = wn.shape
+        # torch: (C_in, C_out/groups, K); group g owns C_in/groups inputs and C_out/groups outputs
+        cog = cout // groups
+        wt = wn.reshape(groups, cog, k, cin_g).permute(0, 3, 1, 2).reshape(groups * cin_g, cog, k)
+    y = F.conv_transpose1d(xt, wt, None, int(stride), int(padding), 0, groups, int(dilation))
+    return _wrap(y.transpose(1, 2).contiguous().numpy())
+
+
+class _FFT:
+    @staticmethod
+    def rfft(a, n=None, axis=-1):
+        return _wrap(np.fft.rfft(_raw(a), n=n, axis=axis))
+
+    @staticmethod
+    def irfft(a, n=None, axis=-1):
+        return _wrap(np.fft.irfft(_raw(a), n=n, axis=axis))
+
+
+fft = _FFT()
+
+
+class _Random:
+    """mx.random.normal with an optional replay queue so goldens are reproducible."""
+
+    def __init__(self):
+        self.queue = []
+        self.log = []
+        self.rng = np.random.Generator(np.random.PCG64(0))
+
+    def normal(self, shape=(), dtype=float32, loc=0.0, scale=1.0, key=None):
+        shape = tuple(int(s) for s in shape)
+        if self.queue:
+            a = np.asarray(self.queue.pop(0), np.float32)
+            assert a.shape == shape, (a.shape, shape)
+        else:
+            a = self.rng.standard_normal(shape, dtype=np.float32)
+        self.log.append(shape)
+        return _wrap(a * np.float32(scale) + np.float32(loc))
+
+    def seed(self, s):
+        self.rng = np.random.Generator(np.random.PCG64(s))
+
+
+random = _Random()
+
+
+def eval(*a, **k):  # noqa: A001
+    return None
+
+
+def compile(fn, *a, **k):  # noqa: A001
+    return fn
+
+
+def clear_cache():
+    return None
+
+
+def get_peak_memory():
+    return 0

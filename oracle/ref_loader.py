@@ -1,0 +1,103 @@
+"""Import the reference's own hot-path source files, unmodified, on top of oracle/mlx_shim.
+
+TEST INFRASTRUCTURE ONLY.  Works only where /root/reference exists (the build
+container); never used on the GPU box.  Used by tests/golden/make_golden.py to
+mint golden vectors from the reference's own Python code, and by the CPU tests
+(skipped when the reference tree is absent) to re-check the oracle live.
+"""
+from __future__ import annotations
+
+import importlib.util
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("KK_REFERENCE_ROOT", "/root/reference")
+_SHIM_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "mlx_shim")
+
+
+def reference_available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "mlx_audio", "tts", "models", "kokoro", "istftnet.py"))
+
+
+def _pkg(name: str, path: str):
+    m = types.ModuleType(name)
+    m.__path__ = [path]
+    m.__package__ = name
+    sys.modules[name] = m
+    return m
+
+
+def _load(name: str, path: str):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+_CACHE = {}
+
+
+def load_reference():
+    """Returns a namespace with the reference modules ``utils``, ``interpolate``, ``base``,
+    ``istftnet`` (loaded from REFERENCE_ROOT) plus the shim's ``mx`` / ``nn``."""
+    if "ns" in _CACHE:
+        return _CACHE["ns"]
+    if not reference_available():
+        raise FileNotFoundError(f"reference tree not found under {REFERENCE_ROOT}")
+    real_mlx = None
+    try:  # prefer a real MLX if one is ever importable
+        import mlx.core  # noqa: F401
+        real_mlx = sys.modules["mlx"]
+    except Exception:
+        if _SHIM_DIR not in sys.path:
+            sys.path.insert(0, _SHIM_DIR)
+        for k in [k for k in sys.modules if k == "mlx" or k.startswith("mlx.")]:
+            del sys.modules[k]
+    import mlx.core as mx
+    import mlx.nn as nn
+
+    root = os.path.join(REFERENCE_ROOT, "mlx_audio")
+    # Stub the package chain so the heavy __init__ files (misaki, mlx_lm, ...) are never executed.
+    _pkg("mlx_audio", root)
+    _pkg("mlx_audio.tts", os.path.join(root, "tts"))
+    _pkg("mlx_audio.tts.models", os.path.join(root, "tts", "models"))
+    _pkg("mlx_audio.tts.models.kokoro", os.path.join(root, "tts", "models", "kokoro"))
+    ns = types.SimpleNamespace(mx=mx, nn=nn, shim=real_mlx is None)
+    ns.utils = _load("mlx_audio.utils", os.path.join(root, "utils.py"))
+    ns.base = _load("mlx_audio.tts.models.base", os.path.join(root, "tts", "models", "base.py"))
+    ns.interpolate = _load("mlx_audio.tts.models.interpolate", os.path.join(root, "tts", "models", "interpolate.py"))
+    ns.istftnet = _load("mlx_audio.tts.models.kokoro.istftnet",
+                        os.path.join(root, "tts", "models", "kokoro", "istftnet.py"))
+    _CACHE["ns"] = ns
+    return ns
+
+
+def build_reference_decoder(weights, cfg):
+    """Instantiate the reference ``Decoder`` and load ``weights`` (reference key names, MLX layout)."""
+    ns = load_reference()
+    dec = ns.istftnet.Decoder(**cfg)
+    for k, v in weights.items():
+        assert k.startswith("decoder."), k
+        dec.set_parameter(k[len("decoder."):], v)
+    return dec
+
+
+def run_reference_decoder(weights, cfg, asr, F0_curve, N, s, noise):
+    """Run the reference Decoder.__call__ with ``mx.random.normal`` replaying ``noise``.
+
+    Draw order inside the reference (istftnet.py:563, :620, :679): rand_ini (B,9),
+    noise (B,600T,9), unused (B,600T,1)."""
+    import numpy as np
+    ns = load_reference()
+    mx = ns.mx
+    dec = build_reference_decoder(weights, cfg)
+    B = asr.shape[0]
+    L = noise.shape[1]
+    mx.random.queue = [np.zeros((B, noise.shape[2]), np.float32), np.asarray(noise, np.float32),
+                       np.zeros((B, L, 1), np.float32)]
+    mx.random.log = []
+    out = dec(mx.array(asr), mx.array(F0_curve), mx.array(N), mx.array(s))
+    assert not mx.random.queue, "reference drew fewer random tensors than expected"
+    return np.asarray(out)

@@ -1,0 +1,211 @@
+"""CPU tests: the oracle (oracle/) against the golden vectors minted from the reference's
+own source (tests/golden/make_golden.py), the reference's KATs and independent libraries."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from mlx_audio_b200 import synth
+from oracle import dsp, interp, ref_loader
+from oracle.istftnet import DecoderOracle
+
+
+def _g(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=False)
+
+
+# ---------------------------------------------------------------- interpolate (reference KATs)
+def test_interpolate_kats_from_reference_tests():
+    # mlx_audio/tts/tests/test_interpolate.py:40-84
+    x = np.array([[[1.0, 2.0, 3.0, 4.0]]], np.float32)
+    np.testing.assert_allclose(interp.interpolate1d(x, 8, "nearest"), [[[1, 1, 2, 2, 3, 3, 4, 4]]], rtol=1e-5)
+    np.testing.assert_allclose(interp.interpolate1d(x, 2, "nearest"), [[[1, 3]]], rtol=1e-5)
+    x = np.array([[[1.0, 3.0, 5.0, 7.0]]], np.float32)
+    np.testing.assert_allclose(interp.interpolate1d(x, 7, "linear", True), [[[1, 2, 3, 4, 5, 6, 7]]], rtol=1e-5)
+    assert interp.interpolate1d(x, 7, "linear", False).shape == (1, 1, 7)
+    np.testing.assert_allclose(interp.interpolate1d(np.array([[[5.0]]], np.float32), 4, "linear"), [[[5, 5, 5, 5]]])
+    with pytest.raises(ValueError):
+        interp.interpolate(np.zeros((2, 3)), size=4)
+    with pytest.raises(ValueError):
+        interp.interpolate(np.zeros((2, 3, 4)), size=8, scale_factor=2)
+    with pytest.raises(ValueError):
+        interp.interpolate(np.zeros((2, 3, 4)))
+    with pytest.raises(ValueError):
+        interp.interpolate(np.zeros((2, 3, 4, 5)), size=8)
+    assert interp.interpolate(np.zeros((2, 3, 4), np.float32), size=8).shape == (2, 3, 8)
+    assert interp.interpolate(np.zeros((2, 3, 4), np.float32), scale_factor=2).shape == (2, 3, 8)
+
+
+def test_interpolate_golden(golden_dir):
+    g = _g(golden_dir, "interpolate.npz")
+    eq = np.testing.assert_array_equal
+    eq(interp.interpolate1d(g["x4"], 8, "nearest"), g["nearest_4_to_8"])
+    eq(interp.interpolate1d(g["x4"], 2, "nearest"), g["nearest_4_to_2"])
+    eq(interp.interpolate1d(g["x4b"], 7, "linear", True), g["linear_ac_4_to_7"])
+    eq(interp.interpolate1d(g["x4b"], 7, "linear", False), g["linear_4_to_7"])
+    eq(interp.interpolate(g["xr"], scale_factor=5, mode="linear"), g["linear_up_x5"])
+    eq(interp.interpolate(g["xr"], size=9, mode="linear"), g["linear_down_37_to_9"])
+    eq(interp.interpolate(g["xr"], size=50, mode="nearest"), g["nearest_37_to_50"])
+
+
+def test_interpolate_wraps_negative_index_unlike_torch():
+    # interpolate.py:97-102: floor(x) == -1 is used as a gather index -> last element (SURVEY 8(a) row 7 quirk ii)
+    x = np.arange(1, 9, dtype=np.float32)[None, None, :]
+    ours = interp.interpolate(x, scale_factor=4, mode="linear")[0, 0]
+    ref = torch.nn.functional.interpolate(torch.from_numpy(x), scale_factor=4, mode="linear", align_corners=False)[0, 0].numpy()
+    assert not np.allclose(ours[:2], ref[:2])      # first scale/2 outputs blend in the LAST element
+    np.testing.assert_allclose(ours[2:], ref[2:], rtol=1e-5, atol=1e-6)
+    assert ours[0] == pytest.approx(8 * (1 - 0.625) + 1 * 0.625)
+
+
+# ---------------------------------------------------------------- stft / istft / mel
+STFT_CASES = {
+    "1024_256": dict(n_fft=1024, hop_length=256),
+    "400_160": dict(n_fft=400, hop_length=160),
+    "20_5": dict(n_fft=20, hop_length=5),
+    "800_default": dict(),
+    "512_128_win400_hamming": dict(n_fft=512, hop_length=128, win_length=400, window="hamming"),
+    "256_64_constant": dict(n_fft=256, hop_length=64, pad_mode="constant"),
+    "256_64_nocenter": dict(n_fft=256, hop_length=64, center=False),
+}
+
+
+@pytest.mark.parametrize("tag", list(STFT_CASES))
+def test_stft_golden(golden_dir, tag):
+    g = _g(golden_dir, "dsp.npz")
+    sig = synth.synth_audio(1, int(g["n"]), seed=int(g["seed"]))[0]
+    S = dsp.stft(sig, **STFT_CASES[tag])
+    ref = g[f"stft_{tag}"]
+    assert S.shape == ref.shape
+    np.testing.assert_allclose(S, ref, rtol=0, atol=2e-5 * max(1.0, float(np.abs(ref).max())))
+
+
+@pytest.mark.parametrize("tag,kw", [("1024_256", dict(hop_length=256, win_length=1024)),
+                                    ("400_160", dict(hop_length=160, win_length=400)),
+                                    ("20_5", dict(hop_length=5, win_length=20))])
+def test_istft_golden(golden_dir, tag, kw):
+    g = _g(golden_dir, "dsp.npz")
+    y = dsp.istft(g[f"stft_{tag}"].T, **kw)
+    assert y.shape == g[f"istft_{tag}"].shape
+    np.testing.assert_allclose(y, g[f"istft_{tag}"], atol=2e-6)
+
+
+def test_istft_length_and_explicit_window_golden(golden_dir):
+    g = _g(golden_dir, "dsp.npz")
+    S = g["stft_1024_256"]
+    np.testing.assert_allclose(dsp.istft(S.T, hop_length=256, win_length=1024, length=5000),
+                               g["istft_1024_256_length5000"], atol=2e-6)
+    np.testing.assert_allclose(dsp.istft(S.T, hop_length=256, win_length=1024, window=dsp.hanning(1024)),
+                               g["istft_1024_256_symwin"], atol=2e-6)
+
+
+def test_windows_and_mel_golden(golden_dir):
+    g = _g(golden_dir, "dsp.npz")
+    for name in ("hanning", "hamming", "blackman", "bartlett"):
+        np.testing.assert_array_equal(getattr(dsp, name)(20), g[f"win_{name}_20"])
+    np.testing.assert_allclose(dsp.mel_filters(24000, 1024, 80), g["mel_24000_1024_80_htk"], atol=1e-7)
+    np.testing.assert_allclose(dsp.mel_filters(24000, 1024, 100, norm=None, mel_scale="htk"), g["mel_24000_1024_100_htk"], atol=1e-7)
+    np.testing.assert_allclose(dsp.mel_filters(16000, 400, 80, norm="slaney", mel_scale=None), g["mel_16000_400_80_slaney"], atol=1e-9)
+    np.testing.assert_allclose(dsp.mel_filters(16000, 400, 128, norm="slaney", mel_scale=None), g["mel_16000_400_128_slaney"], atol=1e-9)
+    np.testing.assert_allclose(dsp.mel_filters(22050, 512, 40, f_min=50.0, f_max=8000.0), g["mel_22050_512_40_fmin_fmax"], atol=1e-7)
+
+
+def test_vocos_shape_pin(golden_dir):
+    # codec/tests/test_vocos.py:61-73: 120000 samples -> 469 frames; drop last -> istft -> 119552 samples
+    g = _g(golden_dir, "dsp.npz")
+    S = dsp.stft(np.zeros(120000, np.float32), n_fft=1024, hop_length=256)
+    assert S.shape[0] == 469 == int(g["vocos_frames"])
+    y = dsp.istft(S[:-1].T, hop_length=256, win_length=1024)
+    assert y.shape[0] == 119552 == int(g["vocos_istft_len"])
+
+
+def test_stft_errors():
+    x = np.zeros(100, np.float32)
+    with pytest.raises(ValueError):
+        dsp.stft(x, window="nope")
+    with pytest.raises(ValueError):
+        dsp.stft(x, n_fft=64, pad_mode="edge")
+    with pytest.raises(ValueError):
+        dsp.stft(np.zeros(10, np.float32), n_fft=64, center=False)
+    with pytest.raises(ValueError):
+        dsp.istft(np.zeros((33, 4), np.complex64), window="nope")
+
+
+def test_stft_against_torch_and_istft_sum_w_normaliser():
+    sig = synth.synth_audio(1, 8000, seed=11)[0]
+    S = dsp.stft(sig, n_fft=512, hop_length=128)
+    St = torch.stft(torch.from_numpy(sig), 512, 128, 512, window=torch.hann_window(512, periodic=False),
+                    center=True, pad_mode="reflect", return_complex=True).T.numpy()
+    np.testing.assert_allclose(S, St, atol=2e-4)
+    # the reference divides by sum(w), not sum(w^2): 0.75x torch.istft for periodic Hann, hop=n/4 (utils.py:142-150)
+    y = dsp.istft(S.T, hop_length=128, win_length=512)
+    yt = torch.istft(torch.from_numpy(St.T.copy()), 512, 128, 512, window=torch.hann_window(512, periodic=True),
+                     center=True).numpy()
+    mid = slice(600, 7000)
+    np.testing.assert_allclose(y[mid], 0.75 * yt[mid], atol=2e-5)
+
+
+def test_mel_filters_against_torchaudio():
+    ta = pytest.importorskip("torchaudio")
+    fb = ta.functional.melscale_fbanks(513, 0.0, 12000.0, 80, 24000, norm=None, mel_scale="htk").T.numpy()
+    np.testing.assert_allclose(dsp.mel_filters(24000, 1024, 80), fb, atol=2e-4)
+    fb = ta.functional.melscale_fbanks(201, 0.0, 8000.0, 80, 16000, norm="slaney", mel_scale="slaney").T.numpy()
+    np.testing.assert_allclose(dsp.mel_filters(16000, 400, 80, norm="slaney", mel_scale=None), fb, atol=2e-6)
+
+
+# ---------------------------------------------------------------- decoder
+def test_decoder_golden(golden_dir, synth_weights):
+    g = _g(golden_dir, "decoder_b2_t16.npz")
+    B, T = int(g["batch"]), int(g["frames"])
+    inp = synth.synth_decoder_inputs(B, T, seed=int(g["input_seed"]))
+    o = DecoderOracle(synth_weights)
+    y = o(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"], keep_taps=True)
+    assert y.shape == (B, 1, 600 * T) == g["audio"].shape
+    # harmonic source is reproduced bit for bit (numpy float32, same op order; rand_ini is dead)
+    np.testing.assert_array_equal(o.taps["har_source"], g["har_source"])
+    np.testing.assert_allclose(o.taps["har"][:, :11], g["har_spec"], atol=1e-6)
+    np.testing.assert_allclose(o.taps["har"][:, 11:], g["har_phase"], atol=1e-5)
+    assert np.abs(y - g["audio"]).max() < 2e-5
+
+
+def test_decoder_shapes_and_determinism(synth_weights):
+    inp = synth.synth_decoder_inputs(1, 8, seed=5)
+    o = DecoderOracle(synth_weights)
+    a = o(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+    b = o(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+    assert a.shape == (1, 1, 4800) and np.isfinite(a).all()
+    np.testing.assert_array_equal(a, b)
+
+
+def test_harmonic_source_rand_ini_is_dead(synth_weights):
+    # istftnet.py:563-565 perturbs only sample 0, which the /300 linear resample never reads
+    inp = synth.synth_decoder_inputs(2, 6, seed=9)
+    o = DecoderOracle(synth_weights)
+    a = o.harmonic_source(inp["F0_curve"], inp["noise"])
+    b = o.harmonic_source(inp["F0_curve"], inp["noise"], rand_ini=np.full((2, 9), 0.37, np.float32))
+    np.testing.assert_array_equal(a, b)
+
+
+def test_fp64_shadow_close(synth_weights):
+    inp = synth.synth_decoder_inputs(1, 12, seed=21)
+    a = DecoderOracle(synth_weights)(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+    b = DecoderOracle(synth_weights, dtype=torch.float64)(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+    assert np.abs(a - b).max() < 5e-5
+
+
+@pytest.mark.skipif(not ref_loader.reference_available(), reason="reference tree not present")
+def test_oracle_matches_reference_source_live(synth_weights):
+    inp = synth.synth_decoder_inputs(1, 10, seed=31)
+    y = DecoderOracle(synth_weights)(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+    yr = ref_loader.run_reference_decoder(synth_weights, synth.KOKORO_DECODER, inp["asr"], inp["F0_curve"], inp["N"],
+                                          inp["s"], inp["noise"])
+    assert np.abs(y - yr).max() < 2e-5
+
+
+def test_param_specs_match_survey_counts(synth_weights):
+    n = sum(v.size for v in synth_weights.values())
+    assert abs(n - 53.28e6) < 0.05e6  # decoder ~53.28 M parameters
+    assert synth_weights["decoder.generator.ups.0.weight_v"].shape == (512, 20, 256)
+    assert synth_weights["decoder.generator.ups.0.bias"].shape == (256,)
+    assert synth_weights["decoder.decode.3.pool.weight_v"].shape == (1090, 3, 1)
