@@ -1,0 +1,139 @@
+/* libkokoro_b200 - C ABI of the B200-native Kokoro ISTFTNet decoder + STFT/iSTFT/mel path.
+ *
+ * Every entry point: extern "C", POD arguments only (device pointers, sizes, a cudaStream_t passed as
+ * void*), returns 0 on success or a negative KK_ERR_* code; kk_last_error() gives the thread-local message.
+ * Functions enqueue work on the caller's stream and never synchronise or allocate (CUDA-graph capturable).
+ * The caller owns every buffer.  Activations are channels-last (B, L, pitch) with `pitch` >= channels.
+ *
+ * Each group cites the reference interface it replaces (paths relative to the mlx-audio tree).
+ */
+#ifndef KOKORO_B200_H
+#define KOKORO_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KK_OK 0
+#define KK_ERR_INVALID_ARG (-1)
+#define KK_ERR_UNSUPPORTED (-2)
+#define KK_ERR_CUDA (-3)
+
+#define KK_ACT_NONE 0
+#define KK_ACT_LEAKY 1 /* LeakyReLU(slope)                      istftnet.py:692-693, :831 */
+#define KK_ACT_SNAKE 2 /* x + (1/alpha) sin(alpha x)^2          istftnet.py:382, :389     */
+
+int kk_version(void);
+const char* kk_last_error(void);
+/* 1 when the current device is compute capability 10.x (tcgen05/TMEM/TMA paths usable). */
+int kk_device_is_sm100(void);
+
+/* ---- weights (load time) ------------------------------------------------------------------
+ * weight_norm (istftnet.py:53-93, called from ConvWeighted.__call__ :130 on EVERY forward in the
+ * reference; folded once here): w[o,:] = v[o,:] / (||v[o,:]||_2 + 1e-7) * g[o].  v is (O, KI). */
+int kk_fold_weight_norm(const float* v, const float* g, float* w, int O, int KI, void* stream);
+/* Re-lay a folded conv weight (O,K,I) into the GEMM "B operand" (N, taps*Cp) [K-major], fp32 or bf16.
+ * mode 0: plain conv              out[n][t*Cp+c] = w[n][t][c]                      (mx.conv1d)
+ * mode 1: transposed conv, polyphase (istftnet.py:161-166,:783; mx.conv_transpose1d with w.T):
+ *         w is the folded (C_in_big, K, C_out_small) ConvWeighted tensor, K = 2*up, N = up*C_out,
+ *         out[ph*C_out+co][t*Cp+ci] = w[ci][ph + up*(1-t)][co],  t in {0,1}. */
+int kk_pack_conv_weight(const float* w, void* out, int out_is_bf16, int mode, int O, int K, int I, int up,
+                        int Cp, void* stream);
+
+/* ---- AdaIN style projection (AdaIN1d.fc, istftnet.py:331-336), all layers in one launch:
+ * h[b][r] = sum_k s[b][k] W[r][k] + bias[r];  W is the row-concatenation of every fc.weight (R, S). */
+int kk_style_affine(const float* s, const float* W, const float* bias, float* h, int B, int R, int S, void* stream);
+
+/* ---- instance-norm statistics (InstanceNorm1d, istftnet.py:229-230): accumulates per (b,c) sum and
+ * sum of squares over time into stats (B, C, 2) doubles (caller zeroes them). */
+int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pitch, void* stream);
+
+/* ---- AdaIN apply + activation (istftnet.py:337 then :382/:389 Snake or :876/:889 LeakyReLU):
+ * y = act((1+gamma)*(x-mean)/sqrt(var+1e-5)+beta); gamma = h[b][c], beta = h[b][C+c] (h row stride h_stride).
+ * stats==NULL skips the normalisation (plain activation).  Output fp32 or bf16, pitch out_pitch.
+ * pool != 0: additionally applies AdainResBlk1d's depthwise ConvTranspose1d k3 s2 p1 (+bias) and the
+ * left zero pad (istftnet.py:880-881): output has 2L rows; pool_w is the folded (C,3) weight. */
+int kk_adain_act(const float* x, int x_pitch, const double* stats, const float* h, int h_stride,
+                 const float* alpha, int act, float slope, void* out, int out_is_bf16, int out_pitch,
+                 int B, int L, int C, int pool, const float* pool_w, const float* pool_b, void* stream);
+
+/* ---- Decoder front glue (istftnet.py:949-953,:957): F0_conv / N_conv (k3 s2 p1 on one channel) and the
+ * channels-first -> channels-last transpose of asr, written into out (B, T, out_pitch) at channel offsets
+ * asr_off (512 channels; skipped when asr == NULL), f0_off, n_off.  w3b = {w0,w1,w2,bias} folded. */
+int kk_front_assemble(const float* asr, const float* F0_curve, const float* N, const float* f0_w3b,
+                      const float* n_w3b, float* out, int out_pitch, int asr_off, int f0_off, int n_off,
+                      int B, int C_asr, int T, void* stream);
+/* Strided channel-block copy between channels-last tensors (the concatenations of :957). */
+int kk_copy_channels(const float* src, int src_pitch, int src_off, float* dst, int dst_pitch, int dst_off,
+                     int rows, int C, void* stream);
+/* fp32 -> bf16 (or fp32) channels-last conversion with optional LeakyReLU (shortcut / leaky_relu :777,:798). */
+int kk_convert_act(const float* x, int x_pitch, void* out, int out_is_bf16, int out_pitch, long long rows, int C,
+                   float slope, void* stream);
+
+/* ---- convolution as implicit GEMM (mx.conv1d / mx.conv_transpose1d as used by ConvWeighted.__call__
+ * istftnet.py:128-166 and nn.Conv1d noise_convs :745-758).
+ *   GEMM: acc[b][m][n] = sum_{t<taps} sum_{c<C_in} x[b][m*stride + t*dil - pad_left][c] * W[n][t*Cw + c]
+ *         (rows outside [0,L_in) read as zero: per-utterance zero padding)
+ *   epilogue: ph = n / C_out, c = n % C_out, j = m*up + ph - up_off, out_row = j + left_pad;
+ *         v = (0 <= j < L_true) ? acc + bias[c] : 0;  v += res[b][out_row >> res_shift][c] + res2[b][out_row][c];
+ *         v *= scale; out[b][out_row][c] = v; stats[b][c] += (v, v*v);
+ *         out_act[b][out_row][c] = leaky(v, act_slope) (optional, fp32 or bf16)
+ * A plain conv is up=1, up_off=0, left_pad=0, L_true=L_out=M.  A ConvTranspose1d with kernel 2*up is the
+ * polyphase form taps=2, dil=1, pad_left=1, N = up*C_out (weights from kk_pack_conv_weight mode 1). */
+typedef struct kk_conv_desc {
+  int B, L_in, C_in, x_pitch;      /* input tensor (B, L_in, x_pitch)                                  */
+  int taps, dil, pad_left, stride; /* stride > 1 only in the fp32 kernel                               */
+  int Cw;                          /* channel pitch inside one tap of W (>= C_in)                      */
+  int M, N;                        /* GEMM rows per utterance, GEMM columns                            */
+  int C_out, up, up_off, L_true, left_pad, L_out;
+  const float* bias;
+  const float* res; int res_pitch, res_shift, L_res;
+  const float* res2; int res2_pitch;
+  float scale;
+  float* out; int out_pitch;
+  double* stats;
+  void* out_act; int act_pitch, act_is_bf16; float act_slope;
+} kk_conv_desc;
+
+/* fp32 CUDA-core kernel (strict-fp32 parity path; also the tiny / strided layers). x, w fp32. */
+int kk_conv1d_f32(const float* x, const float* w, const kk_conv_desc* d, void* stream);
+/* tcgen05/TMEM/TMA kernel: x, w bf16 (w from kk_pack_conv_weight(out_is_bf16=1), Cw multiple of 64,
+ * x_pitch multiple of 8), fp32 accumulate in tensor memory.  block_n in {0(auto),32,64,128,256}.
+ * Returns KK_ERR_UNSUPPORTED on a non-sm_100 device. */
+int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int block_n, void* stream);
+
+/* ---- harmonic source (SineGen / SourceModuleHnNSF istftnet.py:531-680, interpolate.py:82-106,
+ * nn.Upsample :718-720) fused with MLXSTFT.transform (:463-495, utils.stft n_fft=20 hop=5):
+ * f0 (B, 2T) -> har_source (B, 600T) -> har (B, 120T+1, har_pitch) = [|X| (11) , angle(X) (11)].
+ * noise (B, 600T, 9) N(0,1) or NULL (then a Philox counter RNG seeded with `seed` is used).
+ * phase_ws: scratch (B, 9, 2T) floats.  lin_w (9), lin_b (1): m_source.l_linear. */
+int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const float* lin_w,
+                   const float* lin_b, float* phase_ws, float* har_source, int B, int T2, int upsample,
+                   void* stream);
+int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream);
+
+/* ---- iSTFT head (Generator tail istftnet.py:804-806, MLXSTFT.inverse :497-523, utils.istft :104-158):
+ * y (B, F, y_pitch) conv_post output -> spec=exp(y[:11]), phase=sin(y[11:]) -> irfft(20) * periodic hann,
+ * overlap-add hop 5, divide by window sum, trim 10 -> audio (B, 5*(F-1)). */
+int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, void* stream);
+
+/* ---- general STFT / iSTFT / log-mel (mlx_audio/utils.py:52-158,164-237), batched over signals.
+ * window: n_fft floats (already zero-extended).  pad_mode: 0 none(center=False) 1 reflect 2 constant.
+ * spec out: (B, frames, n_fft/2+1, 2) float (re, im).  n_fft must factor into {2,3,5} and be <= 4096. */
+int kk_stft_f32(const float* x, const float* window, float* spec, int B, int n, int n_fft, int hop,
+                int pad_mode, int frames, void* stream);
+/* power: 1 -> |X|, 2 -> |X|^2.  mel: fb (n_mels, n_fft/2+1).  log_mode: 0 none, 1 ln(max(.,floor)),
+ * 2 log10(max(.,floor)).  out (B, frames, n_mels).  Spectrogram is never materialised. */
+int kk_logmel_f32(const float* x, const float* window, const float* fb, float* out, int B, int n, int n_fft,
+                  int hop, int pad_mode, int frames, int n_mels, int power, int log_mode, float floor_,
+                  void* stream);
+/* spec (B, frames, n_fft/2+1, 2) [frames-major, i.e. the layout kk_stft_f32 writes] -> signal.
+ * out (B, out_len): out[i] = ola[i + trim] / wsum (where wsum != 0), ola length (frames-1)*hop + n_fft. */
+int kk_istft_f32(const float* spec, const float* window, float* out, int B, int frames, int n_fft, int hop,
+                 int trim, int out_len, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KOKORO_B200_H */

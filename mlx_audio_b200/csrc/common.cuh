@@ -1,0 +1,41 @@
+// Shared helpers for libkokoro_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/kokoro_b200.h"
+
+namespace kk {
+
+// thread-local last-error string (C ABI: kk_last_error)
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define KK_CHECK_ARG(cond, ...)                 \
+  do {                                          \
+    if (!(cond)) {                              \
+      kk::set_error(__VA_ARGS__);               \
+      return KK_ERR_INVALID_ARG;                \
+    }                                           \
+  } while (0)
+
+#define KK_CUDA(expr)                                        \
+  do {                                                       \
+    cudaError_t _e = (expr);                                 \
+    if (_e != cudaSuccess) return kk::cuda_fail(_e, #expr);  \
+  } while (0)
+
+#define KK_LAUNCH_CHECK(name)                                     \
+  do {                                                            \
+    cudaError_t _e = cudaPeekAtLastError();                       \
+    if (_e != cudaSuccess) return kk::cuda_fail(_e, name);        \
+  } while (0)
+
+static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+__device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
+
+}  // namespace kk

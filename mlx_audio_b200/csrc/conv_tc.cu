@@ -1,0 +1,308 @@
+// Implicit-GEMM Conv1d / polyphase ConvTranspose1d on the 5th-gen tensor cores (sm_100a):
+//   TMA (cp.async.bulk.tensor, 128B swizzle) -> shared-memory ring -> tcgen05.mma (bf16 x bf16 -> fp32 in
+//   tensor memory) -> tcgen05.ld epilogue (bias, residuals, scale, instance-norm partial sums, optional
+//   activated bf16 copy).
+// One CTA computes a 128 (positions) x BN (output channels) tile of one utterance.  The K loop walks
+// (tap, 64-channel block): the A tile of a tap is the SAME activation tensor shifted by tap*dil - pad rows;
+// TMA's out-of-bounds zero fill provides the per-utterance conv zero padding for free (tensor map dims are
+// (C, L, B), so a box never bleeds into the neighbouring utterance).
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-5 = epilogue
+// (warp w owns TMEM lanes 32*(w%4)..+31); warp 2 also allocates / frees tensor memory.
+#include "conv_epilogue.cuh"
+#include "ptx_sm100.cuh"
+
+namespace kk {
+
+constexpr int TC_BM = 128;       // UMMA M
+constexpr int TC_BK = 64;        // bf16 elements per K block = one 128-byte swizzle row
+constexpr int TC_THREADS = 192;
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;  // 16 KB
+
+template <int BN>
+struct TcCfg {
+  static constexpr int B_BYTES = BN * TC_BK * 2;
+  static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
+  static constexpr int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 3 : 4);
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 2 * BN * 4 /*stats*/;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS)
+conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const kk_conv_desc d) {
+  using Cfg = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tail = smem + Cfg::STAGES * Cfg::STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  float* s_stats = reinterpret_cast<float*>(tail + 256);  // [2][BN]
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * TC_BM;
+  const int n0 = blockIdx.y * BN;
+  const int b = blockIdx.z;
+  const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
+  const int num_kb = d.taps * cblocks;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    ptx::mbar_init(tmem_full_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<BN>(tmem_slot);
+  if (threadIdx.x >= 64) {
+    for (int i = threadIdx.x - 64; i < 2 * BN; i += 128) s_stats[i] = 0.f;
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % Cfg::STAGES;
+        const uint32_t ph = (kb / Cfg::STAGES) & 1;
+        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+        const int t = kb / cblocks, cb = kb - t * cblocks;
+        uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+        uint8_t* sb = sa + TC_A_BYTES;
+        ptx::mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+        ptx::tma_load_3d(sa, &tmA, &full_bar[s], cb * TC_BK, m0 + t * d.dil - d.pad_left, b);
+        ptx::tma_load_2d(sb, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % Cfg::STAGES;
+        const uint32_t ph = (kb / Cfg::STAGES) & 1;
+        ptx::mbar_wait(&full_bar[s], ph);
+        ptx::tc_fence_after();
+        const uint32_t sa = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t sb = sa + TC_A_BYTES;
+#pragma unroll
+        for (int k = 0; k < TC_BK / 16; ++k) {
+          // K-major, 128B swizzle: rows are 128 B apart, 8-row atoms 1024 B apart; +32 B per 16-element K step
+          const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+          const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+          ptx::umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        ptx::umma_commit(&empty_bar[s]);  // frees the smem slot when these MMAs have read it
+      }
+      ptx::umma_commit(tmem_full_bar);    // accumulator complete
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int lg = warp & 3;                 // TMEM lane group this warp may access
+    const int m = m0 + lg * 32 + lane;       // GEMM row of this thread
+    ptx::mbar_wait(tmem_full_bar, 0);
+    ptx::tc_fence_after();
+    const bool do_stats = d.stats != nullptr;
+#pragma unroll 1
+    for (int ch = 0; ch < BN / 32; ++ch) {
+      float v[32];
+      ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32), v);
+      ptx::tmem_ld_wait();
+      const int nb = n0 + ch * 32;           // first GEMM column of this chunk
+      // phase is constant inside a 32-column chunk (host guarantees C_out % 32 == 0 when up > 1)
+      int ph = 0, cbase = nb;
+      if (d.up > 1) { ph = nb / d.C_out; cbase = nb - ph * d.C_out; }
+      const int j = m * d.up + ph - d.up_off;
+      const bool acc_valid = (j >= 0) && (j < d.L_true);
+      const int out_row = j + d.left_pad;
+      const bool row_ok = (m < d.M) && (out_row >= 0) && (out_row < d.L_out);
+      const size_t orow = (size_t)b * d.L_out + (row_ok ? out_row : 0);
+      const float* resp = d.res ? d.res + ((size_t)b * d.L_res + ((row_ok ? out_row : 0) >> d.res_shift)) * d.res_pitch + cbase : nullptr;
+      const float* res2p = d.res2 ? d.res2 + orow * d.res2_pitch + cbase : nullptr;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const bool col_ok = (nb + i) < d.N;
+        float x = 0.f;
+        if (row_ok && col_ok) {
+          if (acc_valid) x = v[i] + (d.bias ? __ldg(d.bias + cbase + i) : 0.f);
+          if (resp) x += __ldg(resp + i);
+          if (res2p) x += __ldg(res2p + i);
+          x *= d.scale;
+        }
+        v[i] = x;
+      }
+      if (row_ok) {
+        if (d.out) {
+          float* op = d.out + orow * d.out_pitch + cbase;
+          if ((reinterpret_cast<uintptr_t>(op) & 15) == 0 && nb + 32 <= d.N) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(op + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (nb + i < d.N) op[i] = v[i];
+          }
+        }
+        if (d.out_act) {
+          if (d.act_is_bf16) {
+            __nv_bfloat16* ap = (__nv_bfloat16*)d.out_act + orow * d.act_pitch + cbase;
+            if ((reinterpret_cast<uintptr_t>(ap) & 15) == 0 && nb + 32 <= d.N) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8) {
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(leaky(v[i], d.act_slope), leaky(v[i + 1], d.act_slope));
+                __nv_bfloat162 p1 = __floats2bfloat162_rn(leaky(v[i + 2], d.act_slope), leaky(v[i + 3], d.act_slope));
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(leaky(v[i + 4], d.act_slope), leaky(v[i + 5], d.act_slope));
+                __nv_bfloat162 p3 = __floats2bfloat162_rn(leaky(v[i + 6], d.act_slope), leaky(v[i + 7], d.act_slope));
+                uint4 q;
+                q.x = *reinterpret_cast<uint32_t*>(&p0); q.y = *reinterpret_cast<uint32_t*>(&p1);
+                q.z = *reinterpret_cast<uint32_t*>(&p2); q.w = *reinterpret_cast<uint32_t*>(&p3);
+                *reinterpret_cast<uint4*>(ap + i) = q;
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) if (nb + i < d.N) ap[i] = __float2bfloat16(leaky(v[i], d.act_slope));
+            }
+          } else {
+            float* ap = (float*)d.out_act + orow * d.act_pitch + cbase;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (nb + i < d.N) ap[i] = leaky(v[i], d.act_slope);
+          }
+        }
+      }
+      if (do_stats) {
+        // column sums over the warp's 32 rows: halving butterfly, 31 shuffles per quantity; lane i ends
+        // up with column i.  Rows / columns that were not stored hold 0.
+        float q[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) q[i] = v[i] * v[i];
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+          const bool up_half = (lane & off) != 0;
+#pragma unroll
+          for (int i = 0; i < off; ++i) {
+            float send_v = up_half ? v[i] : v[i + off];
+            float send_q = up_half ? q[i] : q[i + off];
+            float keep_v = up_half ? v[i + off] : v[i];
+            float keep_q = up_half ? q[i + off] : q[i];
+            v[i] = keep_v + __shfl_xor_sync(0xffffffffu, send_v, off);
+            q[i] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
+          }
+        }
+        atomicAdd(&s_stats[ch * 32 + lane], v[0]);
+        atomicAdd(&s_stats[BN + ch * 32 + lane], q[0]);
+      }
+    }
+    if (do_stats) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps
+      for (int i = threadIdx.x - 64; i < BN; i += 128) {
+        int n = n0 + i;
+        if (n < d.N) {
+          int c = d.up > 1 ? n % d.C_out : n;
+          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2, (double)s_stats[i]);
+          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2 + 1, (double)s_stats[BN + i]);
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<BN>(tmem_base);
+}
+
+}  // namespace kk
+
+// ================================================================== host side
+namespace kk {
+
+int validate_conv_desc(const kk_conv_desc* d, const char* who);  // conv_f32.cu
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+// bf16 tensor map with 128B swizzle; dims/strides innermost first, strides in bytes for dims 1..rank-1
+static int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t* dims,
+                          const cuuint64_t* strides, const cuuint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) { set_error("cuTensorMapEncodeTiled entry point not available"); return KK_ERR_CUDA; }
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), dims, strides, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return KK_ERR_CUDA; }
+  return KK_OK;
+}
+
+template <int BN>
+static int launch_tc(const void* x, const void* w, const kk_conv_desc* d, cudaStream_t st) {
+  using Cfg = TcCfg<BN>;
+  CUtensorMap tmA, tmB;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)d->C_in, (cuuint64_t)d->L_in, (cuuint64_t)d->B};
+    cuuint64_t strides[2] = {(cuuint64_t)d->x_pitch * 2, (cuuint64_t)d->L_in * d->x_pitch * 2};
+    cuuint32_t box[3] = {TC_BK, TC_BM, 1};
+    int rc = make_tmap_bf16(&tmA, x, 3, dims, strides, box);
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
+    cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * 2};
+    cuuint32_t box[2] = {TC_BK, BN};
+    int rc = make_tmap_bf16(&tmB, w, 2, dims, strides, box);
+    if (rc) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    KK_CUDA(cudaFuncSetAttribute(conv1d_bf16_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  dim3 grid(cdiv(d->M, TC_BM), cdiv(d->N, BN), d->B);
+  conv1d_bf16_tc_kernel<BN><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, *d);
+  KK_LAUNCH_CHECK("conv1d_bf16_tc_kernel");
+  return KK_OK;
+}
+
+}  // namespace kk
+
+extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int block_n, void* stream) {
+  KK_CHECK_ARG(x && w, "kk_conv1d_bf16_tc: null tensor");
+  int rc = kk::validate_conv_desc(d, "kk_conv1d_bf16_tc");
+  if (rc) return rc;
+  if (!kk_device_is_sm100()) {
+    kk::set_error("kk_conv1d_bf16_tc: needs an sm_100 (Blackwell) device");
+    return KK_ERR_UNSUPPORTED;
+  }
+  KK_CHECK_ARG(d->stride == 1, "kk_conv1d_bf16_tc: stride must be 1 (got %d)", d->stride);
+  KK_CHECK_ARG(d->Cw % 64 == 0, "kk_conv1d_bf16_tc: Cw (%d) must be a multiple of 64", d->Cw);
+  KK_CHECK_ARG(d->x_pitch % 8 == 0, "kk_conv1d_bf16_tc: x_pitch (%d) must be a multiple of 8", d->x_pitch);
+  KK_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kk_conv1d_bf16_tc: operands must be 16-byte aligned");
+  KK_CHECK_ARG(d->up == 1 || d->C_out % 32 == 0, "kk_conv1d_bf16_tc: polyphase needs C_out %% 32 == 0");
+  KK_CHECK_ARG(d->B <= 65535, "kk_conv1d_bf16_tc: batch too large");
+  if (block_n == 0) block_n = d->N > 128 ? 256 : (d->N > 64 ? 128 : (d->N > 32 ? 64 : 32));
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (block_n) {
+    case 32: return kk::launch_tc<32>(x, w, d, st);
+    case 64: return kk::launch_tc<64>(x, w, d, st);
+    case 128: return kk::launch_tc<128>(x, w, d, st);
+    case 256: return kk::launch_tc<256>(x, w, d, st);
+    default: kk::set_error("kk_conv1d_bf16_tc: block_n %d not in {32,64,128,256}", block_n); return KK_ERR_INVALID_ARG;
+  }
+}

@@ -1,0 +1,271 @@
+// Coalesced elementwise / reduction kernels: AdaIN style projection, instance-norm statistics,
+// AdaIN-apply + Snake/LeakyReLU (+ depthwise transposed-conv pool), decoder front glue.
+#include "common.cuh"
+
+namespace kk {
+
+// ---------------------------------------------------------------- style projection (AdaIN1d.fc)
+// One warp per output row r; a chunk of <=32 style vectors staged in shared memory.
+__global__ void style_affine_kernel(const float* __restrict__ s, const float* __restrict__ W,
+                                    const float* __restrict__ bias, float* __restrict__ h, int B, int R, int S) {
+  extern __shared__ float sh_s[];  // (nb, S)
+  int b0 = blockIdx.y * 32;
+  int nb = min(32, B - b0);
+  for (int i = threadIdx.x; i < nb * S; i += blockDim.x) sh_s[i] = s[(size_t)b0 * S + i];
+  __syncthreads();
+  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int r = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (r >= R) return;
+  const float* wr = W + (size_t)r * S;
+  float bv = bias ? bias[r] : 0.f;
+  for (int b = 0; b < nb; ++b) {
+    float acc = 0.f;
+    for (int k = lane; k < S; k += 32) acc = fmaf(sh_s[b * S + k], wr[k], acc);
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    if (lane == 0) h[(size_t)(b0 + b) * R + r] = acc + bv;
+  }
+}
+
+// ---------------------------------------------------------------- instance-norm statistics
+// block (32 channels, 8 row lanes); rows [l0, l0+rows_per_block).  fp32 partials -> double atomics.
+__global__ void instnorm_stats_kernel(const float* __restrict__ x, double* __restrict__ stats, int L, int C,
+                                      int pitch, int rows_per_block) {
+  int b = blockIdx.z;
+  int c = blockIdx.x * 32 + threadIdx.x;
+  int l0 = blockIdx.y * rows_per_block;
+  int l1 = min(L, l0 + rows_per_block);
+  float s = 0.f, ss = 0.f;
+  if (c < C) {
+    const float* xb = x + (size_t)b * L * pitch + c;
+    for (int l = l0 + threadIdx.y; l < l1; l += 8) {
+      float v = xb[(size_t)l * pitch];
+      s += v;
+      ss = fmaf(v, v, ss);
+    }
+  }
+  __shared__ float sh[2][8][33];
+  sh[0][threadIdx.y][threadIdx.x] = s;
+  sh[1][threadIdx.y][threadIdx.x] = ss;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    double ds = 0.0, dss = 0.0;
+    for (int i = 0; i < 8; ++i) { ds += sh[0][i][threadIdx.x]; dss += sh[1][i][threadIdx.x]; }
+    atomicAdd(stats + ((size_t)b * C + c) * 2, ds);
+    atomicAdd(stats + ((size_t)b * C + c) * 2 + 1, dss);
+  }
+}
+
+// ---------------------------------------------------------------- AdaIN apply + activation
+template <typename OutT>
+__device__ __forceinline__ void store_out(OutT* p, float v);
+template <>
+__device__ __forceinline__ void store_out<float>(float* p, float v) { *p = v; }
+template <>
+__device__ __forceinline__ void store_out<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16(v); }
+
+struct AdaCoef { float mean, rstd, g1, beta, alpha, inv_alpha; };
+
+__device__ __forceinline__ float ada_act(float x, const AdaCoef& k, bool norm, int act, float slope) {
+  float y = x;
+  if (norm) y = k.g1 * ((x - k.mean) * k.rstd) + k.beta;      // (1+gamma)*xn + beta   istftnet.py:337
+  if (act == KK_ACT_SNAKE) {                                    // x + (1/a) sin(a x)^2  istftnet.py:382
+    float t = sinf(k.alpha * y);
+    y = y + k.inv_alpha * (t * t);
+  } else if (act == KK_ACT_LEAKY) {
+    y = y > 0.f ? y : y * slope;
+  }
+  return y;
+}
+
+template <typename OutT, bool POOL>
+__global__ void adain_act_kernel(const float* __restrict__ x, int x_pitch, const double* __restrict__ stats,
+                                 const float* __restrict__ h, int h_stride, const float* __restrict__ alpha, int act,
+                                 float slope, OutT* __restrict__ out, int out_pitch, int L, int C,
+                                 const float* __restrict__ pool_w, const float* __restrict__ pool_b,
+                                 int rows_per_block) {
+  int b = blockIdx.z;
+  int c = blockIdx.x * 32 + threadIdx.x;
+  if (c >= C) return;
+  AdaCoef k = {0.f, 1.f, 1.f, 0.f, 1.f, 1.f};
+  bool norm = stats != nullptr;
+  if (norm) {
+    double s = stats[((size_t)b * C + c) * 2], ss = stats[((size_t)b * C + c) * 2 + 1];
+    double mean = s / L;
+    double var = ss / L - mean * mean;
+    if (var < 0.0) var = 0.0;
+    k.mean = (float)mean;
+    k.rstd = 1.0f / sqrtf((float)var + 1e-5f);
+    k.g1 = 1.0f + h[(size_t)b * h_stride + c];
+    k.beta = h[(size_t)b * h_stride + C + c];
+  }
+  if (act == KK_ACT_SNAKE) { k.alpha = alpha[c]; k.inv_alpha = 1.0f / k.alpha; }
+  int l0 = blockIdx.y * rows_per_block;
+  int l1 = min(L, l0 + rows_per_block);
+  const float* xb = x + (size_t)b * L * x_pitch + c;
+  if (!POOL) {
+    OutT* ob = out + (size_t)b * L * out_pitch + c;
+    for (int l = l0 + threadIdx.y; l < l1; l += 8)
+      store_out<OutT>(ob + (size_t)l * out_pitch, ada_act(xb[(size_t)l * x_pitch], k, norm, act, slope));
+  } else {
+    // depthwise ConvTranspose1d k3 s2 p1 + bias, then left zero pad (istftnet.py:880-881):
+    // P[0]=0, P[2i+1] = a[i] w1 + b, P[2i+2] = a[i] w2 + a[i+1] w0 + b   (i+1 < L)
+    float w0 = pool_w[c * 3 + 0], w1 = pool_w[c * 3 + 1], w2 = pool_w[c * 3 + 2], pb = pool_b[c];
+    OutT* ob = out + (size_t)b * (2 * L) * out_pitch + c;
+    for (int l = l0 + threadIdx.y; l < l1; l += 8) {
+      float a0 = ada_act(xb[(size_t)l * x_pitch], k, norm, act, slope);
+      if (l == 0) store_out<OutT>(ob, 0.f);
+      store_out<OutT>(ob + (size_t)(2 * l + 1) * out_pitch, a0 * w1 + pb);
+      if (l + 1 < L) {
+        float a1 = ada_act(xb[(size_t)(l + 1) * x_pitch], k, norm, act, slope);
+        store_out<OutT>(ob + (size_t)(2 * l + 2) * out_pitch, a0 * w2 + a1 * w0 + pb);
+      }
+    }
+  }
+}
+
+
+// ---------------------------------------------------------------- decoder front glue
+// asr (B, C, T) channels-first -> out[b][t][off + c]  (32x32 shared-memory transpose)
+__global__ void transpose_cf_to_cl_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int T,
+                                          int dst_pitch, int dst_off) {
+  __shared__ float tile[32][33];
+  int b = blockIdx.z;
+  int t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    int c = c0 + i, t = t0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < C && t < T) ? src[((size_t)b * C + c) * T + t] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    int t = t0 + i, c = c0 + threadIdx.x;
+    if (t < T && c < C) dst[((size_t)b * T + t) * dst_pitch + dst_off + c] = tile[threadIdx.x][i];
+  }
+}
+
+// F0_conv / N_conv: ConvWeighted(1,1,k3,stride 2,padding 1) on a (B, 2T) curve (istftnet.py:933-934, :949-950)
+__global__ void f0n_conv_kernel(const float* __restrict__ f0, const float* __restrict__ nn,
+                                const float* __restrict__ wf, const float* __restrict__ wn, float* __restrict__ out,
+                                int out_pitch, int f0_off, int n_off, int B, int T) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * T) return;
+  int b = idx / T, t = idx - b * T;
+  const float* f = f0 + (size_t)b * 2 * T;
+  const float* g = nn + (size_t)b * 2 * T;
+  float fm = t > 0 ? f[2 * t - 1] : 0.f, gm = t > 0 ? g[2 * t - 1] : 0.f;
+  float vf = fm * wf[0] + f[2 * t] * wf[1] + f[2 * t + 1] * wf[2] + wf[3];
+  float vn = gm * wn[0] + g[2 * t] * wn[1] + g[2 * t + 1] * wn[2] + wn[3];
+  out[(size_t)idx * out_pitch + f0_off] = vf;
+  out[(size_t)idx * out_pitch + n_off] = vn;
+}
+
+__global__ void copy_channels_kernel(const float* __restrict__ src, int src_pitch, int src_off,
+                                     float* __restrict__ dst, int dst_pitch, int dst_off, long long rows, int C) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * C) return;
+  long long r = idx / C;
+  int c = (int)(idx - r * C);
+  dst[r * dst_pitch + dst_off + c] = src[r * src_pitch + src_off + c];
+}
+
+template <typename OutT>
+__global__ void convert_act_kernel(const float* __restrict__ x, int x_pitch, OutT* __restrict__ out, int out_pitch,
+                                   long long rows, int C, float slope) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= rows * C) return;
+  long long r = idx / C;
+  int c = (int)(idx - r * C);
+  float v = x[r * x_pitch + c];
+  store_out<OutT>(out + r * out_pitch + c, v > 0.f ? v : v * slope);
+}
+
+}  // namespace kk
+
+// ================================================================== C ABI
+extern "C" int kk_style_affine(const float* s, const float* W, const float* bias, float* h, int B, int R, int S,
+                               void* stream) {
+  KK_CHECK_ARG(s && W && h && B > 0 && R > 0 && S > 0 && S <= 384, "kk_style_affine: bad arguments B=%d R=%d S=%d", B, R, S);
+  dim3 grid(kk::cdiv(R, 8), kk::cdiv(B, 32));
+  size_t smem = (size_t)32 * S * sizeof(float);
+  kk::style_affine_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(s, W, bias, h, B, R, S);
+  KK_LAUNCH_CHECK("style_affine_kernel");
+  return KK_OK;
+}
+
+static int rows_per_block_for(int L, int B, int cblocks) {
+  // aim for >= ~4 waves of 148 SMs without making blocks tiny
+  int rpb = 512;
+  while (rpb > 64 && (long long)kk::cdiv(L, rpb) * B * cblocks < 148 * 8) rpb >>= 1;
+  return rpb;
+}
+
+extern "C" int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pitch, void* stream) {
+  KK_CHECK_ARG(x && stats && B > 0 && L > 0 && C > 0 && pitch >= C, "kk_instnorm_stats: bad arguments");
+  int cb = kk::cdiv(C, 32);
+  int rpb = rows_per_block_for(L, B, cb);
+  dim3 grid(cb, kk::cdiv(L, rpb), B), block(32, 8);
+  kk::instnorm_stats_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(x, stats, L, C, pitch, rpb);
+  KK_LAUNCH_CHECK("instnorm_stats_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_adain_act(const float* x, int x_pitch, const double* stats, const float* h, int h_stride,
+                            const float* alpha, int act, float slope, void* out, int out_is_bf16, int out_pitch,
+                            int B, int L, int C, int pool, const float* pool_w, const float* pool_b, void* stream) {
+  KK_CHECK_ARG(x && out && B > 0 && L > 0 && C > 0 && x_pitch >= C && out_pitch >= C, "kk_adain_act: bad shape");
+  KK_CHECK_ARG(act == KK_ACT_NONE || act == KK_ACT_LEAKY || act == KK_ACT_SNAKE, "kk_adain_act: act=%d", act);
+  KK_CHECK_ARG(act != KK_ACT_SNAKE || alpha, "kk_adain_act: snake needs alpha");
+  KK_CHECK_ARG(!stats || h, "kk_adain_act: normalisation needs the style projection h");
+  KK_CHECK_ARG(!pool || (pool_w && pool_b), "kk_adain_act: pool needs weights");
+  int cb = kk::cdiv(C, 32);
+  int rpb = rows_per_block_for(L, B, cb);
+  dim3 grid(cb, kk::cdiv(L, rpb), B), block(32, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+#define KK_ADA(T, P) kk::adain_act_kernel<T, P><<<grid, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, \
+    slope, (T*)out, out_pitch, L, C, pool_w, pool_b, rpb)
+  if (out_is_bf16) { if (pool) KK_ADA(__nv_bfloat16, true); else KK_ADA(__nv_bfloat16, false); }
+  else { if (pool) KK_ADA(float, true); else KK_ADA(float, false); }
+#undef KK_ADA
+  KK_LAUNCH_CHECK("adain_act_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_front_assemble(const float* asr, const float* F0_curve, const float* N, const float* f0_w3b,
+                                 const float* n_w3b, float* out, int out_pitch, int asr_off, int f0_off, int n_off,
+                                 int B, int C_asr, int T, void* stream) {
+  KK_CHECK_ARG(F0_curve && N && f0_w3b && n_w3b && out && B > 0 && T > 0, "kk_front_assemble: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (asr) {
+    dim3 grid(kk::cdiv(T, 32), kk::cdiv(C_asr, 32), B), block(32, 8);
+    kk::transpose_cf_to_cl_kernel<<<grid, block, 0, st>>>(asr, out, C_asr, T, out_pitch, asr_off);
+    KK_LAUNCH_CHECK("transpose_cf_to_cl_kernel");
+  }
+  kk::f0n_conv_kernel<<<kk::cdiv((long long)B * T, 256), 256, 0, st>>>(F0_curve, N, f0_w3b, n_w3b, out, out_pitch,
+                                                                      f0_off, n_off, B, T);
+  KK_LAUNCH_CHECK("f0n_conv_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_copy_channels(const float* src, int src_pitch, int src_off, float* dst, int dst_pitch, int dst_off,
+                                int rows, int C, void* stream) {
+  KK_CHECK_ARG(src && dst && rows > 0 && C > 0, "kk_copy_channels: bad arguments");
+  long long total = (long long)rows * C;
+  kk::copy_channels_kernel<<<kk::cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(src, src_pitch, src_off, dst,
+                                                                                   dst_pitch, dst_off, rows, C);
+  KK_LAUNCH_CHECK("copy_channels_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_convert_act(const float* x, int x_pitch, void* out, int out_is_bf16, int out_pitch, long long rows,
+                              int C, float slope, void* stream) {
+  KK_CHECK_ARG(x && out && rows > 0 && C > 0, "kk_convert_act: bad arguments");
+  long long total = rows * C;
+  int blocks = kk::cdiv(total, 256);
+  if (out_is_bf16)
+    kk::convert_act_kernel<__nv_bfloat16><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, x_pitch, (__nv_bfloat16*)out,
+                                                                                     out_pitch, rows, C, slope);
+  else
+    kk::convert_act_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, x_pitch, (float*)out, out_pitch, rows,
+                                                                             C, slope);
+  KK_LAUNCH_CHECK("convert_act_kernel");
+  return KK_OK;
+}

@@ -1,0 +1,178 @@
+// Harmonic-plus-noise source (SineGen / SourceModuleHnNSF) and the n_fft=20 / hop=5 STFT that feeds the
+// generator's noise branch.  The phase chain is bit-faithful to the reference's float32 op order:
+// every multiply / add is an explicit round-to-nearest intrinsic so nvcc cannot contract them into FMAs
+// (the reference materialises each op; phases reach 1e5..1e6 rad where one ulp is ~0.03 rad).
+#include "common.cuh"
+#include <math.h>
+
+namespace kk {
+
+constexpr int NH = 9;  // harmonic_num + 1 (istftnet.py:715, :546)
+
+// ---- per (b, harmonic): r_j = (f0_j*k/24000) mod 1; c_j = cumsum; p_j = ((c_j*2)*pi)*upsample
+// SineGen._f02sine istftnet.py:561-575.  The /300 linear down-sample (:568-572) is the identity on the
+// nearest-upsampled f0 (it reads samples 300j+149 and 300j+150 with weight 0.5 each), and the rand_ini
+// perturbation of sample 0 (:563-565) is never read.
+__global__ void hnsf_phase_kernel(const float* __restrict__ f0, float* __restrict__ phase, int B, int T2,
+                                  float upsample_f) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * NH) return;
+  int b = idx / NH, k = idx - b * NH;
+  const float* f = f0 + (size_t)b * T2;
+  float* p = phase + (size_t)idx * T2;
+  const float harm = (float)(k + 1);
+  const float pi_f = 3.14159265358979323846f;
+  float c = 0.f;
+  for (int j = 0; j < T2; ++j) {
+    float fk = __fmul_rn(f[j], harm);                  // :610
+    float q = __fdiv_rn(fk, 24000.0f);                 // :561
+    float r = __fsub_rn(q, floorf(q));                 // python-sign "% 1"
+    c = __fadd_rn(c, r);                               // sequential float32 cumsum :573
+    p[j] = __fmul_rn(__fmul_rn(__fmul_rn(c, 2.0f), pi_f), upsample_f);  // *2, *pi (:573), *300 (:575)
+  }
+}
+
+// ---- Philox4x32-10 counter RNG + Box-Muller (only used when the caller passes no noise tensor)
+__device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+
+__device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& n0, float& n1) {
+  float u1 = ((float)(a >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  float u2 = ((float)(b >> 8) + 0.5f) * (1.0f / 16777216.0f);
+  float r = sqrtf(-2.0f * logf(u1));
+  float s, c;
+  sincosf(6.28318530717958647692f * u2, &s, &c);
+  n0 = r * c;
+  n1 = r * s;
+}
+
+// ---- per sample: linear up-sample of the phase with the reference's float32 coordinates and its
+// negative-index wrap (interpolate.py:88-106), sin, uv gate, noise, 9->1 linear, tanh.
+__global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
+                                   const float* __restrict__ noise, unsigned long long seed,
+                                   const float* __restrict__ lin_w, const float* __restrict__ lin_b,
+                                   float* __restrict__ out, int B, int T2, int upsample, float inv_up, float half_inv_up) {
+  const long long S = (long long)T2 * upsample;
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * S) return;
+  int b = (int)(idx / S);
+  int i = (int)(idx - (long long)b * S);
+  // x = ((float(i) * fl32(1/300)) + fl32(1/600)) - 0.5
+  float x = __fsub_rn(__fadd_rn(__fmul_rn((float)i, inv_up), half_inv_up), 0.5f);
+  float lo_f = floorf(x);
+  float fr = __fsub_rn(x, lo_f);
+  int lo = (int)lo_f;
+  int hi = min(lo + 1, T2 - 1);
+  if (lo < 0) lo += T2;  // MLX gather wraps index -1 to the last frame
+  float one_m = __fsub_rn(1.0f, fr);
+  float f0v = f0[(size_t)b * T2 + i / upsample];
+  bool voiced = f0v > 10.0f;                          // voiced_threshold 10 (:716, :553)
+  float amp = voiced ? 0.003f : __fdiv_rn(0.1f, 3.0f);  // uv*noise_std + (1-uv)*sine_amp/3 (:619)
+
+  float nz[12];
+  if (noise) {
+    const float* np_ = noise + ((size_t)b * S + i) * NH;
+#pragma unroll
+    for (int k = 0; k < NH; ++k) nz[k] = np_[k];
+  } else {
+    uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+      uint4 r = philox4x32(make_uint4((uint32_t)i, (uint32_t)b, (uint32_t)g, 0x4b4bu), key);
+      box_muller(r.x, r.y, nz[4 * g], nz[4 * g + 1]);
+      box_muller(r.z, r.w, nz[4 * g + 2], nz[4 * g + 3]);
+    }
+  }
+  float acc = 0.f;
+  const float* pb = phase + (size_t)b * NH * T2;
+#pragma unroll
+  for (int k = 0; k < NH; ++k) {
+    const float* p = pb + (size_t)k * T2;
+    float ph = __fadd_rn(__fmul_rn(p[lo], one_m), __fmul_rn(p[hi], fr));  // interpolate.py:106
+    float sine = __fmul_rn(sinf(ph), 0.1f);                                // :579, :613
+    float hk = voiced ? __fadd_rn(sine, __fmul_rn(amp, nz[k])) : __fmul_rn(amp, nz[k]);  // :622
+    acc = fmaf(hk, lin_w[k], acc);
+  }
+  out[idx] = tanhf(acc + lin_b[0]);  // l_linear + tanh (:666, :677)
+}
+
+// ---- STFT n_fft=20, hop=5, symmetric Hann, reflect pad 10, direct 20 -> 11 real DFT per frame.
+struct Dft20Tables { float win[20]; float cs[20]; float sn[20]; };
+
+__global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_pitch, int B, int S,
+                                int F, const Dft20Tables tb) {
+  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long long)B * F) return;
+  int b = (int)(idx / F);
+  int f = (int)(idx - (long long)b * F);
+  const float* x = sig + (size_t)b * S;
+  float v[20];
+#pragma unroll
+  for (int n = 0; n < 20; ++n) {
+    int p = 5 * f + n - 10;
+    if (p < 0) p = -p;                       // reflect without edge repeat (utils.py:81-84)
+    if (p >= S) p = 2 * (S - 1) - p;
+    v[n] = x[p] * tb.win[n];
+  }
+  float* o = har + (size_t)idx * har_pitch;
+#pragma unroll
+  for (int k = 0; k <= 10; ++k) {
+    float re = 0.f, im = 0.f;
+#pragma unroll
+    for (int n = 0; n < 20; ++n) {
+      int j = (k * n) % 20;
+      re = fmaf(v[n], tb.cs[j], re);
+      im = fmaf(-v[n], tb.sn[j], im);
+    }
+    if (k == 0 || k == 10) im = 0.0f;        // r2c: DC / Nyquist imaginary parts are +0
+    o[k] = sqrtf(re * re + im * im);          // mx.abs      istftnet.py:484
+    o[11 + k] = atan2f(im, re);               // mlx_angle   istftnet.py:409
+  }
+  for (int c = 22; c < har_pitch; ++c) o[c] = 0.f;
+}
+
+}  // namespace kk
+
+extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const float* lin_w,
+                              const float* lin_b, float* phase_ws, float* har_source, int B, int T2, int upsample,
+                              void* stream) {
+  KK_CHECK_ARG(f0 && lin_w && lin_b && phase_ws && har_source, "kk_hnsf_source: null pointer");
+  KK_CHECK_ARG(B > 0 && T2 > 1 && upsample > 1, "kk_hnsf_source: bad shape B=%d T2=%d up=%d", B, T2, upsample);
+  KK_CHECK_ARG((long long)T2 * upsample < (1LL << 24), "kk_hnsf_source: utterance too long for float32 sample index");
+  cudaStream_t st = (cudaStream_t)stream;
+  kk::hnsf_phase_kernel<<<kk::cdiv(B * kk::NH, 64), 64, 0, st>>>(f0, phase_ws, B, T2, (float)upsample);
+  KK_LAUNCH_CHECK("hnsf_phase_kernel");
+  // Coordinates as the reference computes them: arange * (in/size) in float32, + 0.5*(in/size) as float32
+  float inv_up = (float)(1.0 / (double)upsample);
+  float half_inv_up = (float)(0.5 * (1.0 / (double)upsample));
+  long long total = (long long)B * T2 * upsample;
+  kk::hnsf_sample_kernel<<<kk::cdiv(total, 256), 256, 0, st>>>(f0, phase_ws, noise, seed, lin_w, lin_b, har_source, B,
+                                                              T2, upsample, inv_up, half_inv_up);
+  KK_LAUNCH_CHECK("hnsf_sample_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream) {
+  KK_CHECK_ARG(har_source && har && B > 0 && S > 10 && har_pitch >= 22 && S % 5 == 0, "kk_stft_n20: bad arguments");
+  kk::Dft20Tables tb;
+  for (int n = 0; n < 20; ++n) {
+    tb.win[n] = (float)(0.5 * (1.0 - cos(2.0 * M_PI * n / 19.0)));  // symmetric hanning(20) utils.py:11-14
+    tb.cs[n] = (float)cos(2.0 * M_PI * n / 20.0);
+    tb.sn[n] = (float)sin(2.0 * M_PI * n / 20.0);
+  }
+  int F = S / 5 + 1;
+  long long total = (long long)B * F;
+  kk::stft_n20_kernel<<<kk::cdiv(total, 128), 128, 0, (cudaStream_t)stream>>>(har_source, har, har_pitch, B, S, F, tb);
+  KK_LAUNCH_CHECK("stft_n20_kernel");
+  return KK_OK;
+}
