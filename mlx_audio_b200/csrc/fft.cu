@@ -1,0 +1,386 @@
+// General STFT / log-mel / iSTFT (mlx_audio/utils.py:52-158) as shared-memory staged mixed-radix FFTs.
+// A real frame of n_fft samples is packed into an n_fft/2-point complex sequence, transformed with an
+// out-of-place Stockham autosort FFT (radices 4, 2, 3, 5; twiddles from a per-block shared-memory table) and
+// unpacked to the n_fft/2+1 half spectrum.  Windowing, centre (reflect / zero) padding, |X| or |X|^2, the
+// mel projection + log, and on the inverse side the periodic window, gather-form overlap-add, window-sum
+// normalisation and trimming are fused into the same kernels: the framed signal and (for log-mel) the
+// spectrogram never touch HBM.
+#include "common.cuh"
+#include <math.h>
+
+namespace kk {
+
+struct FftPlan {
+  int n_fft, nc;       // real size, complex size n_fft/2
+  int nrad;
+  int rad[16];
+};
+
+static int make_fft_plan(int n_fft, FftPlan* p) {
+  if (n_fft < 4 || (n_fft & 1) || n_fft > 4096) return -1;
+  p->n_fft = n_fft;
+  p->nc = n_fft / 2;
+  p->nrad = 0;
+  int n = p->nc;
+  while (n % 4 == 0) { p->rad[p->nrad++] = 4; n /= 4; }
+  while (n % 2 == 0) { p->rad[p->nrad++] = 2; n /= 2; }
+  while (n % 3 == 0) { p->rad[p->nrad++] = 3; n /= 3; }
+  while (n % 5 == 0) { p->rad[p->nrad++] = 5; n /= 5; }
+  return n == 1 ? 0 : -1;
+}
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+  return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cconj(float2 a) { return make_float2(a.x, -a.y); }
+
+// One Stockham stage of radix R over `batch` independent sequences of length nc stored back to back.
+// tw[j] = exp(-2 pi i j / nc).
+template <int R>
+__device__ __forceinline__ void stockham_stage(const float2* __restrict__ in, float2* __restrict__ out,
+                                               const float2* __restrict__ tw, int nc, int ns, int batch) {
+  const int T = nc / R;
+  const int tw_step = nc / (ns * R);
+  for (int it = threadIdx.x; it < batch * T; it += blockDim.x) {
+    const int g = it / T, j = it - g * T;
+    const float2* a = in + g * nc;
+    float2* o = out + g * nc;
+    const int k = j % ns;
+    float2 v[R];
+#pragma unroll
+    for (int t = 0; t < R; ++t) {
+      float2 x = a[j + t * T];
+      v[t] = (t == 0 || k == 0) ? x : cmul(x, tw[(t * k * tw_step) % nc]);
+    }
+    const int j0 = (j / ns) * ns * R + k;
+    if (R == 2) {
+      o[j0] = cadd(v[0], v[1]);
+      o[j0 + ns] = csub(v[0], v[1]);
+    } else if (R == 4) {
+      float2 s0 = cadd(v[0], v[2]), d0 = csub(v[0], v[2]);
+      float2 s1 = cadd(v[1], v[3]), d1 = csub(v[1], v[3]);
+      float2 md1 = make_float2(d1.y, -d1.x);  // -i * d1
+      o[j0] = cadd(s0, s1);
+      o[j0 + ns] = cadd(d0, md1);
+      o[j0 + 2 * ns] = csub(s0, s1);
+      o[j0 + 3 * ns] = csub(d0, md1);
+    } else {
+      const int rs = nc / R;  // tw[q*t*rs] = exp(-2 pi i q t / R)
+#pragma unroll
+      for (int q = 0; q < R; ++q) {
+        float2 acc = v[0];
+#pragma unroll
+        for (int t = 1; t < R; ++t) acc = cadd(acc, cmul(v[t], tw[((q * t) % R) * rs]));
+        o[j0 + q * ns] = acc;
+      }
+    }
+  }
+}
+
+// Runs every stage; returns the buffer holding the result.  All threads of the block must call it.
+__device__ float2* block_fft(float2* a, float2* b, const float2* tw, const FftPlan& p, int batch) {
+  int ns = 1;
+  for (int s = 0; s < p.nrad; ++s) {
+    const int R = p.rad[s];
+    if (R == 4) stockham_stage<4>(a, b, tw, p.nc, ns, batch);
+    else if (R == 2) stockham_stage<2>(a, b, tw, p.nc, ns, batch);
+    else if (R == 3) stockham_stage<3>(a, b, tw, p.nc, ns, batch);
+    else stockham_stage<5>(a, b, tw, p.nc, ns, batch);
+    __syncthreads();
+    ns *= R;
+    float2* t = a; a = b; b = t;
+  }
+  return a;
+}
+
+__device__ __forceinline__ void fill_tables(float2* tw, float2* tw2, int nc, int n_fft) {
+  for (int j = threadIdx.x; j < nc; j += blockDim.x) {
+    float s, c;
+    sincospif(-2.0f * (float)j / (float)nc, &s, &c);
+    tw[j] = make_float2(c, s);
+  }
+  for (int j = threadIdx.x; j <= nc; j += blockDim.x) {
+    float s, c;
+    sincospif(-2.0f * (float)j / (float)n_fft, &s, &c);
+    tw2[j] = make_float2(c, s);
+  }
+}
+
+// ---------------------------------------------------------------- forward: STFT (MODE 0) / log-mel (MODE 1)
+struct StftArgs {
+  const float* x; const float* window; float* out;
+  int n, hop, pad_mode, frames, frames_per_block, group;
+  // log-mel only
+  const float* fb; int n_mels, power, log_mode; float floor_;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPlan p) {
+  extern __shared__ __align__(16) unsigned char smem_[];
+  const int nc = p.nc, n_fft = p.n_fft, bins = nc + 1;
+  float2* tw = reinterpret_cast<float2*>(smem_);
+  float2* tw2 = tw + nc;
+  float* win = reinterpret_cast<float*>(tw2 + bins);
+  float2* buf0 = reinterpret_cast<float2*>(win + n_fft);
+  float2* buf1 = buf0 + a.group * nc;
+  int* mel_lo = reinterpret_cast<int*>(buf1 + a.group * nc);
+  int* mel_hi = mel_lo + (MODE == 1 ? a.n_mels : 0);
+
+  fill_tables(tw, tw2, nc, n_fft);
+  for (int i = threadIdx.x; i < n_fft; i += blockDim.x) win[i] = a.window[i];
+  if (MODE == 1) {
+    for (int m = threadIdx.x; m < a.n_mels; m += blockDim.x) {
+      const float* row = a.fb + (size_t)m * bins;
+      int lo = bins, hi = 0;
+      for (int k = 0; k < bins; ++k)
+        if (row[k] != 0.f) { if (k < lo) lo = k; hi = k + 1; }
+      mel_lo[m] = lo; mel_hi[m] = hi;
+    }
+  }
+  __syncthreads();
+
+  const int b = blockIdx.y;
+  const float* xb = a.x + (size_t)b * a.n;
+  const int pad = a.pad_mode == 0 ? 0 : n_fft / 2;
+  const int f_begin = blockIdx.x * a.frames_per_block;
+  const int f_end = min(a.frames, f_begin + a.frames_per_block);
+  for (int f0 = f_begin; f0 < f_end; f0 += a.group) {
+    const int ng = min(a.group, f_end - f0);
+    // load + window + pack even/odd samples into a complex sequence
+    for (int it = threadIdx.x; it < ng * nc; it += blockDim.x) {
+      const int g = it / nc, i = it - g * nc;
+      const int base = (f0 + g) * a.hop - pad;
+      float v[2];
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        int q = base + 2 * i + e;
+        float s = 0.f;
+        if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
+          if (q < 0) q = -q;
+          if (q >= a.n) q = 2 * (a.n - 1) - q;
+          s = xb[q];
+        } else if (q >= 0 && q < a.n) {
+          s = xb[q];
+        }
+        v[e] = s * win[2 * i + e];
+      }
+      buf0[g * nc + i] = make_float2(v[0], v[1]);
+    }
+    __syncthreads();
+    float2* Z = block_fft(buf0, buf1, tw, p, ng);
+    float2* other = (Z == buf0) ? buf1 : buf0;
+    // unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i)
+    if (MODE == 0) {
+      for (int it = threadIdx.x; it < ng * bins; it += blockDim.x) {
+        const int g = it / bins, k = it - g * bins;
+        float2 zk = Z[g * nc + (k == nc ? 0 : k)];
+        float2 zc = cconj(Z[g * nc + ((nc - k) % nc)]);
+        float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
+        float2 d = csub(zk, zc);
+        float2 o = make_float2(0.5f * d.y, -0.5f * d.x);  // d / (2i)
+        float2 X = cadd(e, cmul(tw2[k], o));
+        if (k == 0 || k == nc) X.y = 0.f;
+        reinterpret_cast<float2*>(a.out)[((size_t)b * a.frames + f0 + g) * bins + k] = X;
+      }
+      __syncthreads();
+    } else {
+      float* P = reinterpret_cast<float*>(other);  // ng * bins floats <= ng * nc float2 (bins <= 2 nc)
+      for (int it = threadIdx.x; it < ng * bins; it += blockDim.x) {
+        const int g = it / bins, k = it - g * bins;
+        float2 zk = Z[g * nc + (k == nc ? 0 : k)];
+        float2 zc = cconj(Z[g * nc + ((nc - k) % nc)]);
+        float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
+        float2 d = csub(zk, zc);
+        float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
+        float2 X = cadd(e, cmul(tw2[k], o));
+        if (k == 0 || k == nc) X.y = 0.f;
+        float m2 = X.x * X.x + X.y * X.y;
+        P[g * bins + k] = a.power == 2 ? m2 : sqrtf(m2);
+      }
+      __syncthreads();
+      for (int it = threadIdx.x; it < ng * a.n_mels; it += blockDim.x) {
+        const int g = it / a.n_mels, m = it - g * a.n_mels;
+        const float* row = a.fb + (size_t)m * bins;
+        float acc = 0.f;
+        for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[g * bins + k], __ldg(row + k), acc);
+        if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
+        else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
+        a.out[((size_t)b * a.frames + f0 + g) * a.n_mels + m] = acc;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+
+// ---------------------------------------------------------------- inverse: iSTFT with gather overlap-add
+struct IstftArgs {
+  const float* spec; const float* window; float* out;
+  int frames, hop, trim, out_len, hops_per_block, group, max_frames;
+};
+
+__global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const FftPlan p) {
+  extern __shared__ __align__(16) unsigned char smem_[];
+  const int nc = p.nc, n_fft = p.n_fft, bins = nc + 1;
+  float2* tw = reinterpret_cast<float2*>(smem_);
+  float2* tw2 = tw + nc;
+  float* win = reinterpret_cast<float*>(tw2 + bins);
+  float2* buf0 = reinterpret_cast<float2*>(win + n_fft);
+  float2* buf1 = buf0 + a.group * nc;
+  float* tf = reinterpret_cast<float*>(buf1 + a.group * nc);   // (max_frames, n_fft) windowed time frames
+
+  fill_tables(tw, tw2, nc, n_fft);
+  for (int i = threadIdx.x; i < n_fft; i += blockDim.x) win[i] = a.window[i];
+  __syncthreads();
+
+  const int b = blockIdx.y;
+  const long long total = (long long)(a.frames - 1) * a.hop + n_fft;   // untrimmed length (utils.py:126)
+  const long long u0 = (long long)blockIdx.x * a.hops_per_block * a.hop;
+  const long long u1 = min(total, u0 + (long long)a.hops_per_block * a.hop);
+  if (u0 >= total) return;
+  const int f_lo = u0 >= n_fft ? (int)((u0 - n_fft) / a.hop) + 1 : 0;
+  const int f_hi = min(a.frames - 1, (int)((u1 - 1) / a.hop));
+  const int nf = f_hi - f_lo + 1;
+  const float2* sb = reinterpret_cast<const float2*>(a.spec) + (size_t)b * a.frames * bins;
+  const float inv_nc = 1.0f / (float)nc;
+
+  for (int g0 = 0; g0 < nf; g0 += a.group) {
+    const int ng = min(a.group, nf - g0);
+    // pack: Z[k] = E[k] + i O[k], E = (X[k]+conj(X[nc-k]))/2, O = (X[k]-conj(X[nc-k]))/2 * e^{+2 pi i k/n};
+    // the inverse transform is conj(FFT(conj(Z)))/nc, so conj(Z) is stored.  irfft ignores Im X[0], Im X[nc].
+    for (int it = threadIdx.x; it < ng * nc; it += blockDim.x) {
+      const int g = it / nc, k = it - g * nc;
+      const float2* X = sb + (size_t)(f_lo + g0 + g) * bins;
+      float2 xk = X[k], xc = X[nc - k];
+      if (k == 0) { xk.y = 0.f; xc.y = 0.f; }
+      xc = cconj(xc);
+      float2 e = make_float2(0.5f * (xk.x + xc.x), 0.5f * (xk.y + xc.y));
+      float2 d = make_float2(0.5f * (xk.x - xc.x), 0.5f * (xk.y - xc.y));
+      float2 o = cmul(d, cconj(tw2[k]));
+      float2 z = make_float2(e.x - o.y, e.y + o.x);   // e + i*o
+      buf0[g * nc + k] = cconj(z);
+    }
+    __syncthreads();
+    float2* Z = block_fft(buf0, buf1, tw, p, ng);
+    for (int it = threadIdx.x; it < ng * nc; it += blockDim.x) {
+      const int g = it / nc, i = it - g * nc;
+      float2 z = Z[g * nc + i];
+      float* dst = tf + (size_t)(g0 + g) * n_fft + 2 * i;
+      // conj and the 1/n normalisation of irfft (1/nc here, the factor 1/2 is already inside E and O)
+      dst[0] = (z.x * inv_nc) * win[2 * i];
+      dst[1] = (-z.y * inv_nc) * win[2 * i + 1];
+    }
+    __syncthreads();
+  }
+  // gather overlap-add in increasing frame order (utils.py:138-150)
+  for (long long u = u0 + threadIdx.x; u < u1; u += blockDim.x) {
+    const long long oi = u - a.trim;
+    if (oi < 0 || oi >= a.out_len) continue;
+    int fa = u >= n_fft ? (int)((u - n_fft) / a.hop) + 1 : 0;
+    int fb_ = min(a.frames - 1, (int)(u / a.hop));
+    float acc = 0.f, ws = 0.f;
+    for (int f = fa; f <= fb_; ++f) {
+      const int n = (int)(u - (long long)f * a.hop);
+      acc += tf[(size_t)(f - f_lo) * n_fft + n];
+      ws += win[n];
+    }
+    a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+  }
+}
+
+}  // namespace kk
+
+// ================================================================== C ABI
+namespace kk {
+static int stft_group(int nc) { int g = 2048 / nc; return g < 1 ? 1 : (g > 8 ? 8 : g); }
+
+template <int MODE>
+static int launch_stft(const StftArgs& a0, const FftPlan& p, int B, cudaStream_t st) {
+  StftArgs a = a0;
+  a.group = stft_group(p.nc);
+  // enough blocks for several waves, but amortise the per-block table setup over >= 4 groups
+  int fpb = a.group * 4;
+  while (fpb < 256 && (long long)cdiv(a.frames, fpb * 2) * B >= 148 * 8) fpb *= 2;
+  a.frames_per_block = fpb;
+  size_t smem = (size_t)p.nc * 8 + (size_t)(p.nc + 1) * 8 + (size_t)p.n_fft * 4 + (size_t)2 * a.group * p.nc * 8 +
+                (MODE == 1 ? (size_t)2 * a.n_mels * 4 : 0) + 16;
+  KK_CUDA(cudaFuncSetAttribute(stft_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  dim3 grid(cdiv(a.frames, fpb), B);
+  stft_kernel<MODE><<<grid, 256, smem, st>>>(a, p);
+  KK_LAUNCH_CHECK("stft_kernel");
+  return KK_OK;
+}
+}  // namespace kk
+
+static int check_stft_args(const char* who, const float* x, const float* window, const void* out, int B, int n,
+                           int n_fft, int hop, int pad_mode, int frames, kk::FftPlan* p) {
+  KK_CHECK_ARG(x && window && out, "%s: null pointer", who);
+  KK_CHECK_ARG(B > 0 && B <= 65535 && n > 0 && hop > 0 && frames > 0, "%s: bad shape", who);
+  KK_CHECK_ARG(pad_mode >= 0 && pad_mode <= 2, "%s: pad_mode %d", who, pad_mode);
+  if (kk::make_fft_plan(n_fft, p) != 0) {
+    kk::set_error("%s: n_fft=%d must be even, <= 4096 and factor into 2, 3, 5", who, n_fft);
+    return KK_ERR_UNSUPPORTED;
+  }
+  int padded = n + (pad_mode ? 2 * (n_fft / 2) : 0);
+  KK_CHECK_ARG(padded >= n_fft && frames <= 1 + (padded - n_fft) / hop, "%s: frames=%d exceeds the signal", who, frames);
+  KK_CHECK_ARG(pad_mode != 1 || n > n_fft / 2, "%s: reflect padding needs n > n_fft/2", who);
+  return KK_OK;
+}
+
+extern "C" int kk_stft_f32(const float* x, const float* window, float* spec, int B, int n, int n_fft, int hop,
+                           int pad_mode, int frames, void* stream) {
+  kk::FftPlan p;
+  int rc = check_stft_args("kk_stft_f32", x, window, spec, B, n, n_fft, hop, pad_mode, frames, &p);
+  if (rc) return rc;
+  kk::StftArgs a = {};
+  a.x = x; a.window = window; a.out = spec; a.n = n; a.hop = hop; a.pad_mode = pad_mode; a.frames = frames;
+  return kk::launch_stft<0>(a, p, B, (cudaStream_t)stream);
+}
+
+extern "C" int kk_logmel_f32(const float* x, const float* window, const float* fb, float* out, int B, int n,
+                             int n_fft, int hop, int pad_mode, int frames, int n_mels, int power, int log_mode,
+                             float floor_, void* stream) {
+  kk::FftPlan p;
+  int rc = check_stft_args("kk_logmel_f32", x, window, out, B, n, n_fft, hop, pad_mode, frames, &p);
+  if (rc) return rc;
+  KK_CHECK_ARG(fb && n_mels > 0 && n_mels <= 1024 && (power == 1 || power == 2) && log_mode >= 0 && log_mode <= 2,
+               "kk_logmel_f32: bad mel arguments");
+  kk::StftArgs a = {};
+  a.x = x; a.window = window; a.out = out; a.n = n; a.hop = hop; a.pad_mode = pad_mode; a.frames = frames;
+  a.fb = fb; a.n_mels = n_mels; a.power = power; a.log_mode = log_mode; a.floor_ = floor_;
+  return kk::launch_stft<1>(a, p, B, (cudaStream_t)stream);
+}
+
+extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, int B, int frames, int n_fft, int hop,
+                            int trim, int out_len, void* stream) {
+  KK_CHECK_ARG(spec && window && out && B > 0 && B <= 65535 && frames > 0 && hop > 0 && trim >= 0 && out_len > 0,
+               "kk_istft_f32: bad arguments");
+  kk::FftPlan p;
+  if (kk::make_fft_plan(n_fft, &p) != 0) {
+    kk::set_error("kk_istft_f32: n_fft=%d must be even, <= 4096 and factor into 2, 3, 5", n_fft);
+    return KK_ERR_UNSUPPORTED;
+  }
+  kk::IstftArgs a = {};
+  a.spec = spec; a.window = window; a.out = out; a.frames = frames; a.hop = hop; a.trim = trim; a.out_len = out_len;
+  a.group = kk::stft_group(p.nc) > 4 ? 4 : kk::stft_group(p.nc);
+  const int overlap = kk::cdiv(n_fft, hop);
+  size_t fixed = (size_t)p.nc * 8 + (size_t)(p.nc + 1) * 8 + (size_t)n_fft * 4 + (size_t)2 * a.group * p.nc * 8 + 16;
+  int hpb = 16;
+  while (hpb > 1 && fixed + (size_t)(hpb + overlap) * n_fft * 4 > 160 * 1024) hpb >>= 1;
+  a.hops_per_block = hpb;
+  a.max_frames = hpb + overlap;
+  size_t smem = fixed + (size_t)a.max_frames * n_fft * 4;
+  if (smem > 200 * 1024) {
+    kk::set_error("kk_istft_f32: hop=%d too small for n_fft=%d (overlap %d frames does not fit shared memory)", hop,
+                  n_fft, overlap);
+    return KK_ERR_UNSUPPORTED;
+  }
+  KK_CUDA(cudaFuncSetAttribute(kk::istft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  long long total = (long long)(frames - 1) * hop + n_fft;
+  dim3 grid(kk::cdiv(total, (long long)hpb * hop), B);
+  kk::istft_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(a, p);
+  KK_LAUNCH_CHECK("istft_kernel");
+  return KK_OK;
+}

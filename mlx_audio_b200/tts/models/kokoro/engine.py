@@ -19,8 +19,8 @@ from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
 
-from ... import _lib as L
-from ..._lib import ConvDesc
+from .... import _lib as L
+from ...._lib import ConvDesc
 
 
 def _ceil(a: int, m: int) -> int:
@@ -72,14 +72,367 @@ class Plan:
         self.buffers: Dict[str, torch.Tensor] = {}
         self.taps: Dict[str, Tuple[torch.Tensor, tuple]] = {}
         self.n_launches = 0
-        self.stats_arena: Optional[torch.Tensor] = None
+        self.arenas: List[torch.Tensor] = []   # instance-norm (sum, sumsq) accumulators, zeroed every forward
+        self._arena_used = 0
+        self.captured: Dict[str, torch.Tensor] = {}
+        self.capture = False
 
     def add(self, fn, *args, launches: int = 1):
         self.ops.append((fn, args))
         self.n_launches += launches
 
     def run(self, stream: int):
+        for a in self.arenas:
+            a.zero_()
         for fn, args in self.ops:
+            if fn is None:  # debug tap
+                if self.capture:
+                    t, view = self.taps[args[0]]
+                    self.captured[args[0]] = (view(t) if view else t).detach().float().clone()
+                continue
             rc = fn(*args, stream)
             if rc != 0:
                 L.check(rc, getattr(fn, "__name__", "kernel"))
+
+
+class DecoderEngine:
+    """Folds/packs the weights once, then builds and runs launch plans.
+
+    ``weights``: flat dict with the reference's parameter names without the ``decoder.`` prefix
+    (e.g. ``generator.resblocks.0.convs1.0.weight_v``), MLX layout (O, K, I), float32 CUDA tensors.
+    ``mode``: "bf16" (tcgen05 tensor-core convolutions, bf16 operands / fp32 accumulate) or
+    "fp32" (CUDA-core float32 convolutions, the strict parity mode).
+    """
+
+    def __init__(self, weights: Dict[str, torch.Tensor], cfg: dict, mode: str = "bf16"):
+        if mode not in ("bf16", "fp32"):
+            raise ValueError(f"mode must be 'bf16' or 'fp32', got {mode!r}")
+        L.require_cuda()
+        self.lib = L.load()
+        self.cfg = cfg
+        self.mode = mode
+        self.tc = mode == "bf16"
+        if self.tc and not self.lib.kk_device_is_sm100():
+            raise L.KokoroB200Error("bf16 tensor-core mode needs an sm_100 (B200) device")
+        self.dev = next(iter(weights.values())).device
+        self.w = weights
+        self.convs: Dict[str, PreparedConv] = {}
+        self.plans: Dict[Tuple[int, int, bool], Plan] = {}
+        self.up_scale = int(math.prod(cfg["upsample_rates"])) * cfg["gen_istft_hop_size"]
+        assert cfg["gen_istft_n_fft"] == 20 and cfg["gen_istft_hop_size"] == 5, "iSTFT head is specialised for 20/5"
+        self._prepare()
+
+    # ------------------------------------------------------------------ weights
+    def _fold(self, prefix: str) -> torch.Tensor:
+        v = self.w[f"{prefix}.weight_v"].contiguous()
+        g = self.w[f"{prefix}.weight_g"].contiguous()
+        out = torch.empty_like(v)
+        O = v.shape[0]
+        L.check(self.lib.kk_fold_weight_norm(L.ptr(v), L.ptr(g), L.ptr(out), O, v.numel() // O, L.stream()),
+                "kk_fold_weight_norm")
+        return out
+
+    def _prep_wn(self, prefix: str, up: int = 0, tc: Optional[bool] = None):
+        tc = self.tc if tc is None else tc
+        self.convs[prefix] = PreparedConv(prefix, self._fold(prefix), self.w.get(f"{prefix}.bias"), up,
+                                          need_bf16=tc, need_f32=not tc)
+
+    def _prepare(self):
+        w, cfg = self.w, self.cfg
+        # AdaIN fc layers: one concatenated (R, style) matrix -> a single projection launch per forward
+        self.ada_off: Dict[str, int] = {}
+        ws, bs, off = [], [], 0
+        for k in sorted(k for k in w if k.endswith(".fc.weight")):
+            p = k[: -len(".fc.weight")]
+            self.ada_off[p] = off
+            ws.append(w[k])
+            bs.append(w[f"{p}.fc.bias"])
+            off += w[k].shape[0]
+        self.ada_W = torch.cat(ws, 0).contiguous()
+        self.ada_b = torch.cat(bs, 0).contiguous()
+        self.ada_R = off
+        # front
+        for blk in ["encode", "decode.0", "decode.1", "decode.2", "decode.3"]:
+            self._prep_wn(f"{blk}.conv1")
+            self._prep_wn(f"{blk}.conv2")
+            if f"{blk}.conv1x1.weight_v" in w:
+                self._prep_wn(f"{blk}.conv1x1")
+        self.pool_w = self._fold("decode.3.pool").reshape(-1, 3).contiguous()
+        self.pool_b = w["decode.3.pool.bias"].contiguous()
+        self._prep_wn("asr_res.0", tc=False)
+        self.f0_w3b = torch.cat([self._fold("F0_conv").reshape(-1), w["F0_conv.bias"].reshape(-1)]).contiguous()
+        self.n_w3b = torch.cat([self._fold("N_conv").reshape(-1), w["N_conv.bias"].reshape(-1)]).contiguous()
+        # generator
+        g = "generator"
+        n_up = len(cfg["upsample_rates"])
+        n_k = len(cfg["resblock_kernel_sizes"])
+        for i, u in enumerate(cfg["upsample_rates"]):
+            assert cfg["upsample_kernel_sizes"][i] == 2 * u, "polyphase path needs kernel == 2*stride"
+            self._prep_wn(f"{g}.ups.{i}", up=u)
+            self.convs[f"{g}.noise_convs.{i}"] = PreparedConv(
+                f"{g}.noise_convs.{i}", w[f"{g}.noise_convs.{i}.weight"].contiguous(), w[f"{g}.noise_convs.{i}.bias"],
+                need_bf16=False, need_f32=True)
+            for blk in [f"{g}.noise_res.{i}"] + [f"{g}.resblocks.{i * n_k + j}" for j in range(n_k)]:
+                for it in range(3):
+                    self._prep_wn(f"{blk}.convs1.{it}")
+                    self._prep_wn(f"{blk}.convs2.{it}")
+        self._prep_wn(f"{g}.conv_post")
+        self.lin_w = w[f"{g}.m_source.l_linear.weight"].reshape(-1).contiguous()
+        self.lin_b = w[f"{g}.m_source.l_linear.bias"].reshape(-1).contiguous()
+        torch.cuda.current_stream().synchronize()
+
+    # ------------------------------------------------------------------ plan helpers
+    @staticmethod
+    def _addr(t: Optional[torch.Tensor], off_elems: int = 0) -> Optional[int]:
+        if t is None:
+            return None
+        return t.data_ptr() + off_elems * t.element_size()
+
+    def _buf(self, plan: Plan, name: str, shape, dtype=torch.float32, zero: bool = False) -> torch.Tensor:
+        t = (torch.zeros if zero else torch.empty)(shape, dtype=dtype, device=self.dev)
+        plan.buffers[name] = t
+        return t
+
+    def _stats(self, plan: Plan, B: int, C: int) -> int:
+        """Carve a zero-initialised (B, C, 2) double slot; returns its device address."""
+        need = B * C * 2
+        arenas = plan.arenas
+        if not arenas or plan._arena_used + need > arenas[-1].numel():
+            arenas.append(torch.zeros(max(need, B * 2 * 8192), dtype=torch.float64, device=self.dev))
+            plan._arena_used = 0
+        a = arenas[-1]
+        addr = a.data_ptr() + plan._arena_used * 8
+        plan._arena_used += need
+        return addr
+
+    def _act_dtype(self):
+        return torch.bfloat16 if self.tc else torch.float32
+
+    def _act_pitch(self, C: int) -> int:
+        return _ceil(C, 64) if self.tc else C
+
+    def _conv(self, plan: Plan, pc: PreparedConv, x_addr: int, B: int, L_in: int, x_pitch: int, M: int, *,
+              dil: int = 1, pad_left: int = 0, stride: int = 1, L_true: Optional[int] = None,
+              L_out: Optional[int] = None, left_pad: int = 0, up_off: int = 0, out_addr: Optional[int] = None,
+              out_pitch: int = 0, use_bias: bool = True, res=None, res2=None, scale: float = 1.0,
+              stats_addr: Optional[int] = None, out_act=None, force_f32: bool = False, block_n: int = 0):
+        """res = (addr, pitch, shift, L_res); res2 = (addr, pitch); out_act = (addr, pitch, is_bf16, slope)."""
+        d = ConvDesc()
+        d.B, d.L_in, d.C_in, d.x_pitch = B, L_in, pc.C_in, x_pitch
+        d.taps, d.dil, d.pad_left, d.stride = pc.taps, dil, pad_left, stride
+        use_tc = self.tc and not force_f32 and pc.w16 is not None
+        d.Cw = pc.Cw16 if use_tc else pc.Cw32
+        d.M, d.N = M, pc.N
+        d.C_out, d.up, d.up_off = pc.C_out, pc.up, up_off
+        d.L_true = M if L_true is None else L_true
+        d.L_out = d.L_true if L_out is None else L_out
+        d.left_pad = left_pad
+        d.bias = self._addr(pc.bias) if (use_bias and pc.bias is not None) else None
+        if res is not None:
+            d.res, d.res_pitch, d.res_shift, d.L_res = res
+        if res2 is not None:
+            d.res2, d.res2_pitch = res2
+        d.scale = scale
+        d.out, d.out_pitch = out_addr, out_pitch
+        d.stats = stats_addr
+        if out_act is not None:
+            d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
+        plan.keep.append(d)
+        if use_tc:
+            plan.add(self.lib.kk_conv1d_bf16_tc, x_addr, self._addr(pc.w16), C.byref(d), block_n)
+        else:
+            assert pc.w32 is not None, pc.name
+            plan.add(self.lib.kk_conv1d_f32, x_addr, self._addr(pc.w32), C.byref(d))
+        return d
+
+    def _ada(self, plan: Plan, x_addr: int, x_pitch: int, stats_addr: Optional[int], ada_prefix: Optional[str],
+             act: int, slope: float, alpha: Optional[torch.Tensor], out: torch.Tensor, out_pitch: int, B: int, L_: int,
+             C_: int, h_all: torch.Tensor, pool: bool = False):
+        h_addr = self._addr(h_all, self.ada_off[ada_prefix]) if ada_prefix is not None else None
+        plan.add(self.lib.kk_adain_act, x_addr, x_pitch, stats_addr, h_addr, self.ada_R,
+                 self._addr(alpha), act, slope, self._addr(out), 1 if out.dtype == torch.bfloat16 else 0, out_pitch,
+                 B, L_, C_, 1 if pool else 0, self._addr(self.pool_w) if pool else None,
+                 self._addr(self.pool_b) if pool else None)
+
+    def _tap(self, plan: Plan, name: str, t: torch.Tensor, view: Optional[Callable] = None):
+        plan.taps[name] = (t, view)
+        plan.ops.append((None, (name,)))
+
+    # ------------------------------------------------------------------ blocks
+    def _adain_resblock1(self, plan: Plan, prefix: str, B: int, L_: int, C_: int, k: int, dils, h_all,
+                         x_in: torch.Tensor, stats_in: int, work: torch.Tensor, act: torch.Tensor, y: torch.Tensor,
+                         final: dict):
+        """AdaINResBlock1 (istftnet.py:341-396).  x_in (B,L,C) fp32 with stats_in known; the running stream lives
+        in ``work`` after the first iteration (work may be x_in itself: fully in place).  ``final`` gives the
+        last conv2 epilogue: dict(out_addr, out_pitch, res2, scale, stats_addr, out_act)."""
+        ap = self._act_pitch(C_)
+        cur, cur_stats = x_in, stats_in
+        for it in range(3):
+            d = dils[it]
+            c1 = self.convs[f"{prefix}.convs1.{it}"]
+            c2 = self.convs[f"{prefix}.convs2.{it}"]
+            self._ada(plan, self._addr(cur), C_, cur_stats, f"{prefix}.adain1.{it}", L.KK_ACT_SNAKE, 0.0,
+                      self.w[f"{prefix}.alpha1.{it}"], act, ap, B, L_, C_, h_all)
+            st_y = self._stats(plan, B, C_)
+            self._conv(plan, c1, self._addr(act), B, L_, ap, L_, dil=d, pad_left=(k * d - d) // 2,
+                       out_addr=self._addr(y), out_pitch=C_, stats_addr=st_y)
+            self._ada(plan, self._addr(y), C_, st_y, f"{prefix}.adain2.{it}", L.KK_ACT_SNAKE, 0.0,
+                      self.w[f"{prefix}.alpha2.{it}"], act, ap, B, L_, C_, h_all)
+            res = (self._addr(cur), C_, 0, L_)
+            if it < 2:
+                st_n = self._stats(plan, B, C_)
+                self._conv(plan, c2, self._addr(act), B, L_, ap, L_, dil=1, pad_left=(k - 1) // 2,
+                           out_addr=self._addr(work), out_pitch=C_, res=res, stats_addr=st_n)
+                cur, cur_stats = work, st_n
+            else:
+                self._conv(plan, c2, self._addr(act), B, L_, ap, L_, dil=1, pad_left=(k - 1) // 2,
+                           out_addr=final.get("out_addr"), out_pitch=final.get("out_pitch", C_), res=res,
+                           res2=final.get("res2"), scale=final.get("scale", 1.0),
+                           stats_addr=final.get("stats_addr"), out_act=final.get("out_act"))
+
+    def _adain_resblk1d(self, plan: Plan, prefix: str, B: int, L_: int, C_in: int, C_out: int, h_all,
+                        x_in_addr: int, x_pitch: int, out_addr: int, out_pitch: int, upsample: bool = False,
+                        out_act=None, name: str = ""):
+        """AdainResBlk1d (istftnet.py:825-899) on a channels-last fp32 input (B, L, x_pitch)."""
+        Lo = 2 * L_ if upsample else L_
+        adt = self._act_dtype()
+        api, apo = self._act_pitch(C_in), self._act_pitch(C_out)
+        st_in = self._stats(plan, B, C_in)
+        plan.add(self.lib.kk_instnorm_stats, x_in_addr, st_in, B, L_, C_in, x_pitch)
+        act1 = self._buf(plan, f"{name}.act1", (B, Lo, api), adt, zero=True)
+        self._ada(plan, x_in_addr, x_pitch, st_in, f"{prefix}.norm1", L.KK_ACT_LEAKY, 0.2, None, act1, api, B, L_, C_in,
+                  h_all, pool=upsample)
+        # shortcut: [nearest x2] -> 1x1 conv without bias; the 1x1 commutes with the repeat, so it runs at L
+        xin_act = self._buf(plan, f"{name}.xin_act", (B, L_, api), adt, zero=True)
+        plan.add(self.lib.kk_convert_act, x_in_addr, x_pitch, self._addr(xin_act), 1 if self.tc else 0, api,
+                 B * L_, C_in, 1.0)
+        sc = self._buf(plan, f"{name}.sc", (B, L_, C_out))
+        self._conv(plan, self.convs[f"{prefix}.conv1x1"], self._addr(xin_act), B, L_, api, L_, use_bias=False,
+                   out_addr=self._addr(sc), out_pitch=C_out)
+        y1 = self._buf(plan, f"{name}.y1", (B, Lo, C_out))
+        st1 = self._stats(plan, B, C_out)
+        self._conv(plan, self.convs[f"{prefix}.conv1"], self._addr(act1), B, Lo, api, Lo, pad_left=1,
+                   out_addr=self._addr(y1), out_pitch=C_out, stats_addr=st1)
+        act2 = self._buf(plan, f"{name}.act2", (B, Lo, apo), adt, zero=True)
+        self._ada(plan, self._addr(y1), C_out, st1, f"{prefix}.norm2", L.KK_ACT_LEAKY, 0.2, None, act2, apo, B, Lo,
+                  C_out, h_all)
+        self._conv(plan, self.convs[f"{prefix}.conv2"], self._addr(act2), B, Lo, apo, Lo, pad_left=1,
+                   out_addr=out_addr, out_pitch=out_pitch, res=(self._addr(sc), C_out, 1 if upsample else 0, L_),
+                   scale=1.0 / math.sqrt(2.0), out_act=out_act)
+
+    # ------------------------------------------------------------------ the whole decoder
+    def build_plan(self, B: int, T: int) -> Plan:
+        """Decoder.__call__ (istftnet.py:947-963) + Generator.__call__ (:769-807) for a fixed (B, T)."""
+        cfg, lib = self.cfg, self.lib
+        plan = Plan()
+        T2, up = 2 * T, self.up_scale
+        S = T2 * up
+        r0, r1 = cfg["upsample_rates"]
+        L20, L3 = T2 * r0, T2 * r0 * r1 + 1
+        C0 = cfg["upsample_initial_channel"]
+        Cs = [C0 // 2, C0 // 4]
+        f32 = torch.float32
+        adt = self._act_dtype()
+        din = cfg["dim_in"]
+        # ---- inputs (persistent so a CUDA graph can replay the plan)
+        asr = self._buf(plan, "in.asr", (B, din, T))
+        f0c = self._buf(plan, "in.F0_curve", (B, T2))
+        nc = self._buf(plan, "in.N", (B, T2))
+        s = self._buf(plan, "in.s", (B, cfg["style_dim"]))
+        noise = self._buf(plan, "in.noise", (B, S, 9)) if False else None
+        plan.noise_buf = noise
+        h_all = self._buf(plan, "h_all", (B, self.ada_R))
+        plan.add(lib.kk_style_affine, self._addr(s), self._addr(self.ada_W), self._addr(self.ada_b), self._addr(h_all),
+                 B, self.ada_R, cfg["style_dim"])
+        # ---- front: x = cat[asr, F0, N] (:951); xcat = cat[x(1024), asr_res(64), F0, N] (:957)
+        c_cat0, c_cat = din + 2, 1024 + 64 + 2
+        xcat0 = self._buf(plan, "xcat0", (B, T, c_cat0))
+        xcat = self._buf(plan, "xcat", (B, T, c_cat))
+        plan.add(lib.kk_front_assemble, self._addr(asr), self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
+                 self._addr(self.n_w3b), self._addr(xcat0), c_cat0, 0, din, din + 1, B, din, T, launches=2)
+        plan.add(lib.kk_front_assemble, None, self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
+                 self._addr(self.n_w3b), self._addr(xcat), c_cat, 0, 1024 + 64, 1024 + 65, B, din, T)
+        self._conv(plan, self.convs["asr_res.0"], self._addr(xcat0), B, T, c_cat0, T,
+                   out_addr=self._addr(xcat, 1024), out_pitch=c_cat, force_f32=True)  # :953
+        self._adain_resblk1d(plan, "encode", B, T, c_cat0, 1024, h_all, self._addr(xcat0), c_cat0, self._addr(xcat),
+                             c_cat, name="encode")
+        self._tap(plan, "encode", xcat, lambda t: t[:, :, :1024].transpose(1, 2))
+        for i in range(3):
+            self._adain_resblk1d(plan, f"decode.{i}", B, T, c_cat, 1024, h_all, self._addr(xcat), c_cat,
+                                 self._addr(xcat), c_cat, name=f"decode{i}")
+            self._tap(plan, f"decode{i}", xcat, lambda t: t[:, :, :1024].transpose(1, 2))
+        x3 = self._buf(plan, "x3", (B, T2, C0))
+        a_prev = self._buf(plan, "a0", (B, T2, self._act_pitch(C0)), adt, zero=True)
+        self._adain_resblk1d(plan, "decode.3", B, T, c_cat, C0, h_all, self._addr(xcat), c_cat, self._addr(x3), C0,
+                             upsample=True, out_act=(self._addr(a_prev), self._act_pitch(C0), int(self.tc), 0.1),
+                             name="decode3")
+        self._tap(plan, "decode3", x3, lambda t: t.transpose(1, 2))
+        # ---- harmonic source + STFT(20,5) (:770-775)
+        phase_ws = self._buf(plan, "phase_ws", (B, 9, T2))
+        har_source = self._buf(plan, "har_source", (B, S))
+        har = self._buf(plan, "har", (B, L3, 24))
+        plan.source_op_index = len(plan.ops)
+        plan.add(lib.kk_hnsf_source, self._addr(f0c), None, 0, self._addr(self.lin_w), self._addr(self.lin_b),
+                 self._addr(phase_ws), self._addr(har_source), B, T2, up, launches=2)
+        plan.add(lib.kk_stft_n20, self._addr(har_source), self._addr(har), 24, B, S)
+        self._tap(plan, "har_source", har_source)
+        self._tap(plan, "har", har, lambda t: t[:, :, :22].transpose(1, 2))
+        # ---- generator stages (:776-796)
+        g = "generator"
+        n_k = len(cfg["resblock_kernel_sizes"])
+        Ls = [L20, L3]
+        L_prev, C_prev = T2, C0
+        for i in range(2):
+            Li, Ci = Ls[i], Cs[i]
+            ap = self._act_pitch(Ci)
+            nconv = self.convs[f"{g}.noise_convs.{i}"]
+            xs = self._buf(plan, f"g{i}.xs", (B, Li, Ci))
+            st_xs = self._stats(plan, B, Ci)
+            if i == 0:
+                stride_f0 = r1
+                self._conv(plan, nconv, self._addr(har), B, L3, 24, Li, stride=stride_f0, pad_left=(stride_f0 + 1) // 2,
+                           out_addr=self._addr(xs), out_pitch=Ci, stats_addr=st_xs, force_f32=True)
+            else:
+                self._conv(plan, nconv, self._addr(har), B, L3, 24, Li, out_addr=self._addr(xs), out_pitch=Ci,
+                           stats_addr=st_xs, force_f32=True)
+            self._tap(plan, f"noise_conv{i}", xs, lambda t: t.transpose(1, 2))
+            act = self._buf(plan, f"g{i}.act", (B, Li, ap), adt, zero=True)
+            y = self._buf(plan, f"g{i}.y", (B, Li, Ci))
+            self._adain_resblock1(plan, f"{g}.noise_res.{i}", B, Li, Ci, 7 if i == 0 else 11, (1, 3, 5), h_all, xs,
+                                  st_xs, xs, act, y, dict(out_addr=self._addr(xs), out_pitch=Ci))
+            self._tap(plan, f"noise_res{i}", xs, lambda t: t.transpose(1, 2))
+            # ups[i]: polyphase transposed conv, + x_source fused as residual (:783-788)
+            u = cfg["upsample_rates"][i]
+            kk_ = cfg["upsample_kernel_sizes"][i]
+            x = self._buf(plan, f"g{i}.x", (B, Li, Ci))
+            st_x = self._stats(plan, B, Ci)
+            last = i == 1
+            self._conv(plan, self.convs[f"{g}.ups.{i}"], self._addr(a_prev), B, L_prev, self._act_pitch(C_prev),
+                       L_prev + 1, pad_left=1, up_off=(kk_ - u) // 2, L_true=L_prev * u, L_out=Li,
+                       left_pad=1 if last else 0, out_addr=self._addr(x), out_pitch=Ci,
+                       res=(self._addr(xs), Ci, 0, Li), stats_addr=st_x)
+            self._tap(plan, f"x_stage{i}", x, lambda t: t.transpose(1, 2))
+            # MRF: mean of three AdaINResBlock1 on the same input (:790-796)
+            work = self._buf(plan, f"g{i}.work", (B, Li, Ci))
+            acc = self._buf(plan, f"g{i}.mrf", (B, Li, Ci))
+            a_next = self._buf(plan, f"a{i + 1}", (B, Li, ap), adt, zero=True)
+            for j in range(n_k):
+                final = dict(out_addr=self._addr(acc), out_pitch=Ci)
+                if j > 0:
+                    final["res2"] = (self._addr(acc), Ci)
+                if j == n_k - 1:
+                    final["scale"] = 1.0 / n_k
+                    final["out_act"] = (self._addr(a_next), ap, int(self.tc), 0.1 if i == 0 else 0.01)
+                self._adain_resblock1(plan, f"{g}.resblocks.{i * n_k + j}", B, Li, Ci, cfg["resblock_kernel_sizes"][j],
+                                      cfg["resblock_dilation_sizes"][j], h_all, x, st_x, work, act, y, final)
+            self._tap(plan, f"mrf{i}", acc, lambda t: t.transpose(1, 2))
+            a_prev, L_prev, C_prev = a_next, Li, Ci
+        # ---- conv_post + iSTFT head (:798-806)
+        ypost = self._buf(plan, "ypost", (B, L3, 24))
+        self._conv(plan, self.convs[f"{g}.conv_post"], self._addr(a_prev), B, L3, self._act_pitch(Cs[1]), L3, pad_left=3,
+                   out_addr=self._addr(ypost), out_pitch=24)
+        self._tap(plan, "conv_post", ypost, lambda t: t[:, :, :22].transpose(1, 2))
+        audio = self._buf(plan, "audio", (B, 1, S))
+        plan.add(lib.kk_istft_head_n20, self._addr(ypost), 24, self._addr(audio), B, L3)
+        plan.shape = (B, T)
+        return plan

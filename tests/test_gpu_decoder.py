@@ -1,0 +1,284 @@
+"""GPU parity tests: source / STFT / iSTFT-head kernels, the general DSP surface and the whole decoder,
+all against the CPU oracle and the golden vectors minted from the reference source."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from mlx_audio_b200 import _lib as L
+from mlx_audio_b200 import synth, utils
+from mlx_audio_b200.tts.models.kokoro import Decoder, build_decoder
+from oracle import dsp
+from oracle.istftnet import DecoderOracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    L.require_cuda()
+    return L.load()
+
+
+@pytest.fixture(scope="module")
+def oracle(synth_weights):
+    return DecoderOracle(synth_weights)
+
+
+@pytest.fixture(scope="module")
+def dec_fp32(synth_weights):
+    return build_decoder(synth_weights, dtype="fp32")
+
+
+@pytest.fixture(scope="module")
+def dec_bf16(synth_weights, lib):
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    return build_decoder(synth_weights, dtype="bf16")
+
+
+def dev(x):
+    return torch.as_tensor(np.asarray(x)).to("cuda", torch.float32).contiguous()
+
+
+# ------------------------------------------------------------------ harmonic source + STFT(20,5)
+def test_hnsf_source_and_stft_n20(lib, oracle, synth_weights):
+    B, T = 3, 24
+    inp = synth.synth_decoder_inputs(B, T, seed=77)
+    ref_src = oracle.harmonic_source(inp["F0_curve"], inp["noise"])
+    lw = dev(synth_weights["decoder.generator.m_source.l_linear.weight"].reshape(-1))
+    lb = dev(synth_weights["decoder.generator.m_source.l_linear.bias"].reshape(-1))
+    ws = torch.empty(B, 9, 2 * T, device="cuda")
+    src = torch.empty(B, 600 * T, device="cuda")
+    L.check(lib.kk_hnsf_source(L.ptr(dev(inp["F0_curve"])), L.ptr(dev(inp["noise"])), 0, L.ptr(lw), L.ptr(lb), L.ptr(ws),
+                               L.ptr(src), B, 2 * T, 300, L.stream()))
+    got = src.cpu().numpy()
+    # the phase chain is bit-faithful; sin / tanh / the 9-term dot product differ by a few ulp
+    assert np.abs(got - ref_src).max() < 2e-6
+    har = torch.empty(B, 120 * T + 1, 24, device="cuda")
+    L.check(lib.kk_stft_n20(L.ptr(dev(ref_src)), L.ptr(har), 24, B, 600 * T, L.stream()))
+    mag, ph = oracle.stft_transform(ref_src)
+    h = har.cpu().numpy()
+    np.testing.assert_allclose(h[:, :, :11].transpose(0, 2, 1), mag, atol=2e-6)
+    # phase: compare on the unit circle (|X| weighted) so that near-zero bins do not dominate
+    dphi = np.angle(np.exp(1j * (h[:, :, 11:22].transpose(0, 2, 1) - ph)))
+    assert (np.abs(dphi) * np.maximum(mag, 1e-3)).max() < 5e-6
+    assert set(np.unique(h[:, :, 11])) <= {np.float32(0.0), np.float32(np.pi)}  # DC phase is exactly 0 or +pi
+
+
+def test_hnsf_source_philox_noise_statistics(lib, synth_weights):
+    B, T = 2, 40
+    f0 = np.zeros((B, 2 * T), np.float32)  # unvoiced: output = tanh(sum_k w_k * (0.1/3) n_k + b)
+    lw = synth_weights["decoder.generator.m_source.l_linear.weight"].reshape(-1)
+    ws = torch.empty(B, 9, 2 * T, device="cuda")
+    src = torch.empty(B, 600 * T, device="cuda")
+    L.check(lib.kk_hnsf_source(L.ptr(dev(f0)), None, 1234, L.ptr(dev(lw)), L.ptr(dev(np.zeros(1, np.float32))), L.ptr(ws),
+                               L.ptr(src), B, 2 * T, 300, L.stream()))
+    x = np.arctanh(src.cpu().numpy().astype(np.float64))
+    sigma = (0.1 / 3) * np.sqrt((lw.astype(np.float64) ** 2).sum())
+    assert abs(x.mean()) < 4 * sigma / np.sqrt(x.size) + 1e-6
+    assert abs(x.std() / sigma - 1) < 0.02
+    assert abs(np.corrcoef(x[0, :-1], x[0, 1:])[0, 1]) < 0.02
+    src2 = torch.empty_like(src)
+    L.check(lib.kk_hnsf_source(L.ptr(dev(f0)), None, 1235, L.ptr(dev(lw)), L.ptr(dev(np.zeros(1, np.float32))), L.ptr(ws),
+                               L.ptr(src2), B, 2 * T, 300, L.stream()))
+    assert not torch.equal(src, src2)
+
+
+def test_istft_head(lib, oracle):
+    r = np.random.Generator(np.random.PCG64(5))
+    B, F_ = 2, 120 * 7 + 1
+    y = r.standard_normal((B, F_, 24), dtype=np.float32)
+    y[:, :, :11] = y[:, :, :11] * 0.5 - 2.0
+    audio = torch.empty(B, 5 * (F_ - 1), device="cuda")
+    L.check(lib.kk_istft_head_n20(L.ptr(dev(y)), 24, L.ptr(audio), B, F_, L.stream()))
+    spec = np.exp(y[:, :, :11]).transpose(0, 2, 1)
+    phase = np.sin(y[:, :, 11:22]).transpose(0, 2, 1)
+    ref = oracle.stft_inverse(spec.astype(np.float32), phase.astype(np.float32))[:, 0]
+    assert audio.shape == ref.shape
+    np.testing.assert_allclose(audio.cpu().numpy(), ref, atol=2e-6)
+
+
+# ------------------------------------------------------------------ general stft / istft / mel surface
+STFT_CASES = {
+    "1024_256": dict(n_fft=1024, hop_length=256),
+    "400_160": dict(n_fft=400, hop_length=160),
+    "20_5": dict(n_fft=20, hop_length=5),
+    "800_default": dict(),
+    "512_128_win400_hamming": dict(n_fft=512, hop_length=128, win_length=400, window="hamming"),
+    "256_64_constant": dict(n_fft=256, hop_length=64, pad_mode="constant"),
+    "256_64_nocenter": dict(n_fft=256, hop_length=64, center=False),
+}
+
+
+@pytest.mark.parametrize("tag", list(STFT_CASES))
+def test_stft_matches_reference_golden(golden_dir, tag):
+    g = np.load(os.path.join(golden_dir, "dsp.npz"))
+    sig = synth.synth_audio(1, int(g["n"]), seed=int(g["seed"]))[0]
+    S = utils.stft(torch.from_numpy(sig), **STFT_CASES[tag])
+    ref = g[f"stft_{tag}"]
+    assert tuple(S.shape) == ref.shape and S.dtype == torch.complex64
+    err = np.abs(S.cpu().numpy() - ref).max()
+    assert err < 1e-4 * max(1.0, float(np.abs(ref).max())), err
+
+
+@pytest.mark.parametrize("tag,kw", [("1024_256", dict(hop_length=256, win_length=1024)),
+                                    ("400_160", dict(hop_length=160, win_length=400)),
+                                    ("20_5", dict(hop_length=5, win_length=20))])
+def test_istft_matches_reference_golden(golden_dir, tag, kw):
+    g = np.load(os.path.join(golden_dir, "dsp.npz"))
+    S = torch.from_numpy(g[f"stft_{tag}"])
+    y = utils.istft(S.T, **kw)
+    ref = g[f"istft_{tag}"]
+    assert tuple(y.shape) == ref.shape
+    np.testing.assert_allclose(y.cpu().numpy(), ref, atol=1e-5)
+    if tag == "1024_256":
+        y2 = utils.istft(S.T, hop_length=256, win_length=1024, length=5000)
+        np.testing.assert_allclose(y2.cpu().numpy(), g["istft_1024_256_length5000"], atol=1e-5)
+        y3 = utils.istft(S.T, hop_length=256, win_length=1024, window=utils.hanning(1024))
+        np.testing.assert_allclose(y3.cpu().numpy(), g["istft_1024_256_symwin"], atol=1e-5)
+
+
+def test_mel_filters_and_windows_golden(golden_dir):
+    g = np.load(os.path.join(golden_dir, "dsp.npz"))
+    np.testing.assert_allclose(utils.mel_filters(24000, 1024, 80).cpu().numpy(), g["mel_24000_1024_80_htk"], atol=1e-7)
+    np.testing.assert_allclose(utils.mel_filters(16000, 400, 80, norm="slaney", mel_scale=None).cpu().numpy(),
+                               g["mel_16000_400_80_slaney"], atol=1e-9)
+    for name in ("hanning", "hamming", "blackman", "bartlett"):
+        np.testing.assert_array_equal(getattr(utils, name)(20).cpu().numpy(), g[f"win_{name}_20"])
+
+
+def test_stft_errors_like_reference():
+    x = torch.zeros(100)
+    with pytest.raises(ValueError):
+        utils.stft(x, window="nope")
+    with pytest.raises(ValueError):
+        utils.stft(x, n_fft=64, pad_mode="edge")
+    with pytest.raises(ValueError):
+        utils.stft(torch.zeros(10), n_fft=64, center=False)
+    with pytest.raises(ValueError):
+        utils.istft(torch.zeros(33, 4, dtype=torch.complex64), window="nope")
+
+
+def test_vocos_shape_pin_and_batched_roundtrip():
+    # codec/tests/test_vocos.py:61-73: 120000 samples -> 469 frames; [:-1] -> istft -> 119552
+    S = utils.stft(torch.zeros(120000), n_fft=1024, hop_length=256)
+    assert tuple(S.shape) == (469, 513)
+    y = utils.istft(S[:-1].T, hop_length=256, win_length=1024)
+    assert tuple(y.shape) == (119552,)
+    x = torch.from_numpy(synth.synth_audio(5, 30000, seed=8)).cuda()
+    Sb = utils.stft(x, n_fft=1024, hop_length=256)
+    yb = utils.istft(Sb.transpose(1, 2), hop_length=256, win_length=1024)
+    # sum(w) normaliser: 0.75 x the signal away from the edges (Hann, hop = n/4)
+    mid = slice(1024, yb.shape[1] - 1024)
+    np.testing.assert_allclose(yb[:, mid].cpu().numpy(), 0.75 * x[:, mid].cpu().numpy(), atol=2e-5)
+
+
+def test_log_mel_recipes():
+    sig = synth.synth_audio(3, 24000, seed=12)
+    got = utils.log_mel_spectrogram(torch.from_numpy(sig), n_fft=1024, hop_length=256, n_mels=80)
+    for b in range(3):
+        ref = dsp.log_mel_vocos(sig[b], n_fft=1024, hop_length=256, n_mels=80)
+        assert tuple(got[b].shape) == ref.shape
+        assert np.abs(got[b].cpu().numpy() - ref).mean() < 1e-4
+        assert np.abs(got[b].cpu().numpy() - ref).max() < 2e-3
+    # whisper-style front end: power spectrum, slaney mel, log10 (stt/models/whisper/audio.py:72-82)
+    w = utils.log_mel_spectrogram(torch.from_numpy(sig[0]), sample_rate=16000, n_fft=400, hop_length=160, n_mels=80,
+                                  power=2, log="log10", floor=1e-10, norm="slaney", mel_scale=None)
+    w = w[:-1]
+    w = torch.maximum(w, w.max() - 8.0)
+    w = (w + 4.0) / 4.0
+    ref = dsp.log_mel_whisper(sig[0])
+    assert np.abs(w.cpu().numpy() - ref).max() < 2e-3
+
+
+# ------------------------------------------------------------------ whole decoder
+def _run(dec, inp, **kw):
+    y = dec(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], noise=inp["noise"], **kw)
+    torch.cuda.synchronize()
+    return y.cpu().numpy()
+
+
+def test_decoder_fp32_matches_reference_golden(golden_dir, dec_fp32):
+    g = np.load(os.path.join(golden_dir, "decoder_b2_t16.npz"))
+    B, T = int(g["batch"]), int(g["frames"])
+    inp = synth.synth_decoder_inputs(B, T, seed=int(g["input_seed"]))
+    y = _run(dec_fp32, inp, capture_taps=True)
+    taps = dec_fp32.taps(B, T)
+    assert np.abs(taps["har_source"].cpu().numpy() - g["har_source"]).max() < 2e-6
+    assert y.shape == g["audio"].shape == (B, 1, 600 * T)
+    err = np.abs(y - g["audio"]).max()
+    assert err <= 1e-3, f"fp32 waveform max-abs error {err} vs golden (north-star gate 1e-3)"
+
+
+def test_decoder_fp32_config1_vs_oracle_waveform_and_mel(dec_fp32, oracle):
+    # BASELINE config 1: B=1, T=200 (5 s).  Gates: waveform max-abs <= 1e-3, log-mel-80 L1 <= 1e-3.
+    inp = synth.synth_decoder_inputs(1, 200, seed=1000)
+    ref = oracle(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"], keep_taps=True)
+    y = _run(dec_fp32, inp, capture_taps=True)
+    taps = dec_fp32.taps(1, 200)
+    report = {k: float(np.abs(taps[k].cpu().numpy() - oracle.taps[k]).max()) for k in oracle.taps if k in taps}
+    print("fp32 tap max-abs errors:", report)
+    err = np.abs(y - ref).max()
+    assert err <= 1e-3, (err, report)
+    mel_ref = dsp.log_mel_vocos(ref[0, 0])
+    mel_got = dsp.log_mel_vocos(y[0, 0])
+    assert np.abs(mel_ref - mel_got).mean() <= 1e-3
+
+
+def test_decoder_bf16_vs_oracle(dec_bf16, oracle):
+    # bf16 operands / fp32 accumulate.  Stated tolerance: waveform max-abs <= 3e-2 (signal peak ~0.3),
+    # relative L2 error <= 5e-2, log-mel-80 L1 <= 5e-2.
+    inp = synth.synth_decoder_inputs(2, 64, seed=2024)
+    ref = oracle(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"], keep_taps=True)
+    y = _run(dec_bf16, inp, capture_taps=True)
+    taps = dec_bf16.taps(2, 64)
+    report = {k: float(np.abs(taps[k].cpu().numpy() - oracle.taps[k]).max()) for k in oracle.taps if k in taps}
+    print("bf16 tap max-abs errors:", report)
+    rel = np.linalg.norm(y - ref) / np.linalg.norm(ref)
+    print("bf16 waveform max-abs", np.abs(y - ref).max(), "rel-l2", rel)
+    assert np.abs(y - ref).max() <= 3e-2 and rel <= 5e-2
+    mel = np.abs(dsp.log_mel_vocos(ref[0, 0]) - dsp.log_mel_vocos(y[0, 0])).mean()
+    print("bf16 log-mel L1", mel)
+    assert mel <= 5e-2
+
+
+def test_decoder_ragged_shapes_and_errors(dec_fp32, oracle):
+    for B, T in ((1, 1), (3, 7), (2, 33)):
+        inp = synth.synth_decoder_inputs(B, T, seed=B * 100 + T)
+        ref = oracle(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+        y = _run(dec_fp32, inp)
+        assert y.shape == (B, 1, 600 * T)
+        assert np.abs(y - ref).max() <= 1e-3
+    inp = synth.synth_decoder_inputs(1, 4, seed=1)
+    with pytest.raises(ValueError):
+        dec_fp32(inp["asr"][:, :100], inp["F0_curve"], inp["N"], inp["s"])
+    with pytest.raises(ValueError):
+        dec_fp32(inp["asr"], inp["F0_curve"][:, :-1], inp["N"], inp["s"])
+
+
+def test_decoder_batch_independence(dec_bf16):
+    # no op mixes utterances: an utterance decodes identically alone and inside a batch
+    inp = synth.synth_decoder_inputs(3, 20, seed=55)
+    full = _run(dec_bf16, inp)
+    one = {k: v[1:2] for k, v in inp.items()}
+    alone = _run(dec_bf16, one)
+    np.testing.assert_allclose(full[1:2], alone, atol=1e-5)
+
+
+def test_decoder_default_noise_and_cuda_graph(dec_bf16):
+    inp = synth.synth_decoder_inputs(2, 16, seed=3)
+    a = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7).clone()
+    b = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7).clone()
+    c = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=8).clone()
+    assert torch.allclose(a, b, atol=1e-5) and not torch.allclose(a, c, atol=1e-3)
+    assert torch.isfinite(a).all()
+    dec_bf16.use_cuda_graph = True
+    try:
+        g1 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7).clone()
+        g2 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7).clone()
+    finally:
+        dec_bf16.use_cuda_graph = False
+    torch.cuda.synchronize()
+    assert torch.allclose(g1, a, atol=1e-5) and torch.allclose(g1, g2, atol=1e-5)

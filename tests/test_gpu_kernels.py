@@ -1,0 +1,250 @@
+"""GPU parity tests of the individual kernels, called through the C ABI, against the CPU oracle."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from mlx_audio_b200 import _lib as L
+from mlx_audio_b200 import synth
+from mlx_audio_b200._lib import ConvDesc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def lib():
+    L.require_cuda()
+    return L.load()
+
+
+def dev(x, dtype=torch.float32):
+    return torch.as_tensor(np.asarray(x)).to("cuda", dtype).contiguous()
+
+
+def rng(seed):
+    return np.random.Generator(np.random.PCG64(seed))
+
+
+# ------------------------------------------------------------------ weights
+def test_fold_weight_norm(lib):
+    r = rng(1)
+    v = r.standard_normal((37, 7, 29), dtype=np.float32)
+    g = r.uniform(0.5, 1.5, (37, 1, 1)).astype(np.float32)
+    out = torch.empty(37, 7, 29, device="cuda")
+    L.check(lib.kk_fold_weight_norm(L.ptr(dev(v)), L.ptr(dev(g)), L.ptr(out), 37, 7 * 29, L.stream()))
+    n = np.sqrt((v.astype(np.float64) ** 2).sum((1, 2), keepdims=True))
+    ref = (v / (n + 1e-7)) * g
+    np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=2e-6, atol=1e-7)
+
+
+def test_pack_conv_weight_modes(lib):
+    r = rng(2)
+    w = r.standard_normal((5, 3, 10), dtype=np.float32)  # (O,K,I)
+    out = torch.empty(5, 3 * 64, device="cuda", dtype=torch.bfloat16)
+    L.check(lib.kk_pack_conv_weight(L.ptr(dev(w)), L.ptr(out), 1, 0, 5, 3, 10, 1, 64, L.stream()))
+    ref = np.zeros((5, 3, 64), np.float32)
+    ref[:, :, :10] = w
+    np.testing.assert_array_equal(out.float().cpu().numpy().reshape(5, 3, 64),
+                                  torch.from_numpy(ref).bfloat16().float().numpy())
+    # transposed / polyphase: w (C_in_big=6, K=2*up=4, C_out_small=3), up=2
+    wt = r.standard_normal((6, 4, 3), dtype=np.float32)
+    out = torch.empty(2 * 3, 2 * 8, device="cuda")
+    L.check(lib.kk_pack_conv_weight(L.ptr(dev(wt)), L.ptr(out), 0, 1, 6, 4, 3, 2, 8, L.stream()))
+    o = out.cpu().numpy().reshape(2, 3, 2, 8)  # (ph, co, t, ci)
+    for ph in range(2):
+        for t in range(2):
+            np.testing.assert_array_equal(o[ph, :, t, :6], wt[:, ph + 2 * (1 - t), :].T)
+    assert (o[..., 6:] == 0).all()
+
+
+# ------------------------------------------------------------------ elementwise
+def test_style_affine(lib):
+    r = rng(3)
+    B, R, S = 37, 301, 128
+    s, W, b = r.standard_normal((B, S), dtype=np.float32), r.standard_normal((R, S), dtype=np.float32), \
+        r.standard_normal(R, dtype=np.float32)
+    h = torch.empty(B, R, device="cuda")
+    L.check(lib.kk_style_affine(L.ptr(dev(s)), L.ptr(dev(W)), L.ptr(dev(b)), L.ptr(h), B, R, S, L.stream()))
+    np.testing.assert_allclose(h.cpu().numpy(), s @ W.T + b, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize("B,Lr,Cc,pitch", [(2, 1000, 70, 72), (3, 77, 1090, 1090), (1, 4801, 128, 128)])
+def test_instnorm_stats_and_adain(lib, B, Lr, Cc, pitch):
+    r = rng(4)
+    x = np.zeros((B, Lr, pitch), np.float32)
+    x[:, :, :Cc] = r.standard_normal((B, Lr, Cc), dtype=np.float32) * 2 + 0.5
+    xd = dev(x)
+    stats = torch.zeros(B, Cc, 2, device="cuda", dtype=torch.float64)
+    L.check(lib.kk_instnorm_stats(L.ptr(xd), L.ptr(stats), B, Lr, Cc, pitch, L.stream()))
+    xs = x[:, :, :Cc].astype(np.float64)
+    np.testing.assert_allclose(stats[..., 0].cpu().numpy(), xs.sum(1), rtol=1e-5, atol=1e-3)
+    np.testing.assert_allclose(stats[..., 1].cpu().numpy(), (xs ** 2).sum(1), rtol=1e-5)
+    h = (r.standard_normal((B, 2 * Cc + 10), dtype=np.float32) * 0.3)
+    alpha = r.uniform(0.5, 2.0, Cc).astype(np.float32)
+    mean, var = xs.mean(1, keepdims=True), xs.var(1, keepdims=True)
+    xn = (xs - mean) / np.sqrt(var + 1e-5)
+    y = (1 + h[:, None, 5:5 + Cc]) * xn + h[:, None, 5 + Cc:5 + 2 * Cc]
+    hd = dev(h)
+    for act, ref in ((L.KK_ACT_SNAKE, y + (1 / alpha) * np.sin(alpha * y) ** 2),
+                     (L.KK_ACT_LEAKY, np.where(y > 0, y, 0.2 * y))):
+        for is_bf16 in (0, 1):
+            out = torch.zeros(B, Lr, pitch, device="cuda", dtype=torch.bfloat16 if is_bf16 else torch.float32)
+            L.check(lib.kk_adain_act(L.ptr(xd), pitch, L.ptr(stats), hd.data_ptr() + 5 * 4, h.shape[1], L.ptr(dev(alpha)),
+                                     act, 0.2, L.ptr(out), is_bf16, pitch, B, Lr, Cc, 0, None, None, L.stream()))
+            got = out.float().cpu().numpy()[:, :, :Cc]
+            tol = 2e-2 if is_bf16 else 2e-5
+            np.testing.assert_allclose(got, ref, rtol=tol, atol=tol)
+
+
+def test_adain_act_pool_matches_depthwise_conv_transpose(lib):
+    r = rng(5)
+    B, Lr, Cc = 2, 33, 50
+    x = r.standard_normal((B, Lr, Cc), dtype=np.float32)
+    pw = r.standard_normal((Cc, 3), dtype=np.float32)
+    pb = r.standard_normal(Cc, dtype=np.float32)
+    out = torch.empty(B, 2 * Lr, Cc, device="cuda")
+    L.check(lib.kk_adain_act(L.ptr(dev(x)), Cc, None, None, 0, None, L.KK_ACT_LEAKY, 0.2, L.ptr(out), 0, Cc, B, Lr, Cc,
+                             1, L.ptr(dev(pw)), L.ptr(dev(pb)), L.stream()))
+    a = torch.from_numpy(np.where(x > 0, x, 0.2 * x)).transpose(1, 2)  # (B,C,L)
+    ref = F.conv_transpose1d(a, torch.from_numpy(pw)[:, None, :], torch.from_numpy(pb), stride=2, padding=1, groups=Cc)
+    ref = F.pad(ref, (1, 0)).transpose(1, 2).numpy()  # left zero pad (istftnet.py:881)
+    assert ref.shape == (B, 2 * Lr, Cc)
+    np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=1e-5, atol=1e-5)
+
+
+def test_front_assemble(lib):
+    r = rng(6)
+    B, Cc, T = 2, 70, 45
+    asr = r.standard_normal((B, Cc, T), dtype=np.float32)
+    f0 = r.standard_normal((B, 2 * T), dtype=np.float32)
+    n = r.standard_normal((B, 2 * T), dtype=np.float32)
+    wf = r.standard_normal(4, dtype=np.float32)
+    wn = r.standard_normal(4, dtype=np.float32)
+    out = torch.zeros(B, T, Cc + 2, device="cuda")
+    L.check(lib.kk_front_assemble(L.ptr(dev(asr)), L.ptr(dev(f0)), L.ptr(dev(n)), L.ptr(dev(wf)), L.ptr(dev(wn)),
+                                  L.ptr(out), Cc + 2, 0, Cc, Cc + 1, B, Cc, T, L.stream()))
+    o = out.cpu().numpy()
+    np.testing.assert_array_equal(o[:, :, :Cc], asr.transpose(0, 2, 1))
+    for src, w, ch in ((f0, wf, Cc), (n, wn, Cc + 1)):
+        ref = F.conv1d(torch.from_numpy(src)[:, None], torch.from_numpy(w[:3])[None, None], torch.from_numpy(w[3:]),
+                       stride=2, padding=1)[:, 0].numpy()
+        np.testing.assert_allclose(o[:, :, ch], ref, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------ convolutions
+def _conv_case(lib, tc, B, Lin, Cin, Cout, k, dil, stride=1, transposed_up=0, with_res=True, left_pad=0, seed=0,
+               block_n=0):
+    r = rng(100 + seed)
+    bf = torch.bfloat16
+    x = r.standard_normal((B, Lin, Cin), dtype=np.float32)
+    bias = r.standard_normal(Cout, dtype=np.float32) * 0.1
+    if transposed_up:
+        u = transposed_up
+        K = 2 * u
+        wfold = r.standard_normal((Cin, K, Cout), dtype=np.float32) / math.sqrt(Cin * 2)  # (C_in_big, K, C_out_small)
+        pad = (K - u) // 2
+        Ltrue = Lin * u
+        Lout = Ltrue + left_pad
+        M, taps, padl, up_off, N, mode = Lin + 1, 2, 1, pad, u * Cout, 1
+    else:
+        wfold = r.standard_normal((Cout, k, Cin), dtype=np.float32) / math.sqrt(Cin * k)
+        padl = (k * dil - dil) // 2
+        Ltrue = (Lin + 2 * padl - dil * (k - 1) - 1) // stride + 1
+        Lout = Ltrue
+        M, taps, up_off, N, mode, u = Ltrue, k, 0, Cout, 0, 1
+    xq = torch.from_numpy(x).to(bf).float() if tc else torch.from_numpy(x)
+    wq = torch.from_numpy(wfold).to(bf).float() if tc else torch.from_numpy(wfold)
+    # reference in float64 on the (rounded) operands
+    if transposed_up:
+        y = F.conv_transpose1d(xq.double().transpose(1, 2), wq.double().permute(0, 2, 1), torch.from_numpy(bias).double(),
+                               stride=u, padding=pad).transpose(1, 2)
+        y = F.pad(y, (0, 0, left_pad, 0))
+    else:
+        y = F.conv1d(xq.double().transpose(1, 2), wq.double().permute(0, 2, 1), torch.from_numpy(bias).double(),
+                     stride=stride, padding=padl, dilation=dil).transpose(1, 2)
+    assert y.shape == (B, Lout, Cout), (y.shape, (B, Lout, Cout))
+    res = r.standard_normal((B, Lout, Cout), dtype=np.float32) if with_res else None
+    res2 = r.standard_normal((B, Lout, Cout), dtype=np.float32) if with_res else None
+    scale = 0.7
+    ref = y.numpy()
+    if with_res:
+        ref = ref + res + res2
+    ref = ref * scale
+    # device side
+    Cp = (Cin + 63) // 64 * 64 if tc else Cin
+    xp = torch.zeros(B, Lin, Cp, dtype=bf if tc else torch.float32, device="cuda")
+    xp[:, :, :Cin] = dev(x).to(xp.dtype)
+    wp = torch.empty(N, taps * Cp, dtype=bf if tc else torch.float32, device="cuda")
+    if transposed_up:
+        L.check(lib.kk_pack_conv_weight(L.ptr(dev(wfold)), L.ptr(wp), int(tc), 1, Cin, 2 * u, Cout, u, Cp, L.stream()))
+    else:
+        L.check(lib.kk_pack_conv_weight(L.ptr(dev(wfold)), L.ptr(wp), int(tc), 0, Cout, k, Cin, 1, Cp, L.stream()))
+    out = torch.full((B, Lout, Cout), float("nan"), device="cuda")
+    act = torch.zeros(B, Lout, Cout, dtype=bf if tc else torch.float32, device="cuda")
+    stats = torch.zeros(B, Cout, 2, dtype=torch.float64, device="cuda")
+    d = ConvDesc()
+    d.B, d.L_in, d.C_in, d.x_pitch = B, Lin, Cin, Cp
+    d.taps, d.dil, d.pad_left, d.stride, d.Cw = taps, dil, padl, stride, Cp
+    d.M, d.N, d.C_out, d.up, d.up_off = M, N, Cout, u, up_off
+    d.L_true, d.left_pad, d.L_out = Ltrue, left_pad, Lout
+    bd, rd, r2d = dev(bias), (dev(res) if with_res else None), (dev(res2) if with_res else None)
+    d.bias = L.ptr(bd)
+    if with_res:
+        d.res, d.res_pitch, d.res_shift, d.L_res = L.ptr(rd), Cout, 0, Lout
+        d.res2, d.res2_pitch = L.ptr(r2d), Cout
+    d.scale = scale
+    d.out, d.out_pitch, d.stats = L.ptr(out), Cout, L.ptr(stats)
+    d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = L.ptr(act), Cout, int(tc), 0.1
+    if tc:
+        L.check(lib.kk_conv1d_bf16_tc(L.ptr(xp), L.ptr(wp), C.byref(d), block_n, L.stream()), "tc")
+    else:
+        L.check(lib.kk_conv1d_f32(L.ptr(xp), L.ptr(wp), C.byref(d), L.stream()), "f32")
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    if left_pad:  # the padded row carries only the residuals
+        exp0 = ((res[:, 0] + res2[:, 0]) * scale) if with_res else np.zeros((B, Cout), np.float32)
+        np.testing.assert_allclose(got[:, 0], exp0, rtol=1e-5, atol=1e-5)
+    tol = 2e-4
+    np.testing.assert_allclose(got, ref, rtol=tol, atol=tol)
+    np.testing.assert_allclose(stats[..., 0].cpu().numpy(), ref.sum(1), rtol=1e-3, atol=2e-2)
+    np.testing.assert_allclose(stats[..., 1].cpu().numpy(), (ref.astype(np.float64) ** 2).sum(1), rtol=1e-3, atol=1e-2)
+    a_ref = np.where(ref > 0, ref, 0.1 * ref)
+    np.testing.assert_allclose(act.float().cpu().numpy(), a_ref, rtol=1e-2 if tc else 1e-4, atol=1e-2 if tc else 1e-4)
+
+
+F32_CASES = [
+    dict(B=2, Lin=200, Cin=22, Cout=48, k=12, dil=1, stride=6),     # noise_convs.0 geometry
+    dict(B=1, Lin=333, Cin=70, Cout=130, k=7, dil=3),
+    dict(B=2, Lin=100, Cin=64, Cout=64, k=1, dil=1, with_res=False),
+    dict(B=2, Lin=50, Cin=40, Cout=32, k=0, dil=1, transposed_up=10),
+    dict(B=1, Lin=61, Cin=32, Cout=32, k=0, dil=1, transposed_up=6, left_pad=1),
+]
+
+
+@pytest.mark.parametrize("case", F32_CASES)
+def test_conv1d_f32(lib, case):
+    _conv_case(lib, False, **case)
+
+
+TC_CASES = [
+    dict(B=2, Lin=300, Cin=128, Cout=128, k=3, dil=1),
+    dict(B=1, Lin=517, Cin=128, Cout=128, k=11, dil=5),
+    dict(B=2, Lin=260, Cin=256, Cout=256, k=7, dil=3),
+    dict(B=2, Lin=130, Cin=256, Cout=256, k=3, dil=1, block_n=128),
+    dict(B=2, Lin=70, Cin=1090, Cout=512, k=3, dil=1, with_res=False),   # K not a multiple of 64
+    dict(B=1, Lin=100, Cin=514, Cout=1024, k=1, dil=1, with_res=False),
+    dict(B=2, Lin=200, Cin=128, Cout=22, k=7, dil=1, with_res=False),    # conv_post geometry (N=22 -> BN=32)
+    dict(B=2, Lin=40, Cin=512, Cout=256, k=0, dil=1, transposed_up=10),  # ups.0 geometry
+    dict(B=1, Lin=150, Cin=256, Cout=128, k=0, dil=1, transposed_up=6, left_pad=1),  # ups.1 geometry
+    dict(B=3, Lin=64, Cin=64, Cout=64, k=3, dil=1, block_n=64),
+]
+
+
+@pytest.mark.parametrize("case", TC_CASES)
+def test_conv1d_bf16_tc(lib, case):
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    _conv_case(lib, True, **case)
