@@ -10,7 +10,7 @@ __global__ void __launch_bounds__(256)
 conv1d_f32_kernel(const float* __restrict__ x, const float* __restrict__ w, const kk_conv_desc d) {
   __shared__ __align__(16) float As[F_BK][F_BM + 4];
   __shared__ __align__(16) float Bs[F_BK][F_BN + 4];
-  __shared__ float s_sum[F_BN], s_sq[F_BN];
+  __shared__ float s_sum[16][F_BN], s_sq[16][F_BN];  // one slot per row group: deterministic combine
 
   const int b = blockIdx.z;
   const int m0 = blockIdx.x * F_BM, n0 = blockIdx.y * F_BN;
@@ -67,10 +67,6 @@ conv1d_f32_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
 
   // ---- epilogue
   const bool do_stats = d.stats != nullptr;
-  if (do_stats) {
-    if (tid < F_BN) { s_sum[tid] = 0.f; s_sq[tid] = 0.f; }
-    __syncthreads();
-  }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     int n = n0 + tx * 4 + j;
@@ -89,8 +85,8 @@ conv1d_f32_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
       }
     }
     if (do_stats) {
-      atomicAdd(&s_sum[tx * 4 + j], cs);
-      atomicAdd(&s_sq[tx * 4 + j], cq);
+      s_sum[ty][tx * 4 + j] = cs;
+      s_sq[ty][tx * 4 + j] = cq;
     }
   }
   if (do_stats) {
@@ -98,8 +94,11 @@ conv1d_f32_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
     if (tid < F_BN && n0 + tid < d.N) {
       int n = n0 + tid;
       int c = d.up > 1 ? n % d.C_out : n;
-      atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2, (double)s_sum[tid]);
-      atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2 + 1, (double)s_sq[tid]);
+      float ts = 0.f, tq = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { ts += s_sum[i][tid]; tq += s_sq[i][tid]; }
+      atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2, (double)ts);
+      atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2 + 1, (double)tq);
     }
   }
 }

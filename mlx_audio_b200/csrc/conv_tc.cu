@@ -23,7 +23,7 @@ struct TcCfg {
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
   static constexpr int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 3 : 4);
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 2 * BN * 4 /*stats*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 8 * BN * 4 /*stats: 4 warps x (sum, sumsq) x BN*/;
 };
 
 template <int BN>
@@ -38,7 +38,7 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   uint64_t* empty_bar = full_bar + Cfg::STAGES;
   uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-  float* s_stats = reinterpret_cast<float*>(tail + 256);  // [2][BN]
+  float* s_stats = reinterpret_cast<float*>(tail + 256);  // [4 warps][2][BN], no atomics: deterministic
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * TC_BM;
@@ -58,9 +58,6 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<BN>(tmem_slot);
-  if (threadIdx.x >= 64) {
-    for (int i = threadIdx.x - 64; i < 2 * BN; i += 128) s_stats[i] = 0.f;
-  }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -194,8 +191,8 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             q[i] = keep_q + __shfl_xor_sync(0xffffffffu, send_q, off);
           }
         }
-        atomicAdd(&s_stats[ch * 32 + lane], v[0]);
-        atomicAdd(&s_stats[BN + ch * 32 + lane], q[0]);
+        s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = v[0];
+        s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = q[0];
       }
     }
     if (do_stats) {
@@ -204,8 +201,11 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         int n = n0 + i;
         if (n < d.N) {
           int c = d.up > 1 ? n % d.C_out : n;
-          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2, (double)s_stats[i]);
-          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2 + 1, (double)s_stats[BN + i]);
+          // fixed-order combine of the four warps, then one double atomic per (tile, column)
+          float ts = (s_stats[0 * BN + i] + s_stats[2 * BN + i]) + (s_stats[4 * BN + i] + s_stats[6 * BN + i]);
+          float tq = (s_stats[1 * BN + i] + s_stats[3 * BN + i]) + (s_stats[5 * BN + i] + s_stats[7 * BN + i]);
+          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2, (double)ts);
+          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2 + 1, (double)tq);
         }
       }
     }

@@ -76,6 +76,7 @@ class Plan:
         self._arena_used = 0
         self.captured: Dict[str, torch.Tensor] = {}
         self.capture = False
+        self.conv_ops: Dict[int, ConvDesc] = {}  # op index -> descriptor (for FLOP accounting)
 
     def add(self, fn, *args, launches: int = 1):
         self.ops.append((fn, args))
@@ -93,6 +94,29 @@ class Plan:
             rc = fn(*args, stream)
             if rc != 0:
                 L.check(rc, getattr(fn, "__name__", "kernel"))
+
+    def run_timed(self, stream: int):
+        """One forward with a CUDA-event pair around every C-ABI call (on the launching stream).
+        Returns [(symbol, op_index, milliseconds)].  Diagnostic only: the gaps serialise the launches."""
+        for a in self.arenas:
+            a.zero_()
+        recs = []
+        for i, (fn, args) in enumerate(self.ops):
+            if fn is None:
+                continue
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*args, stream)
+            e1.record()
+            if rc != 0:
+                L.check(rc, getattr(fn, "__name__", "kernel"))
+            recs.append((fn.__name__, i, e0, e1))
+        torch.cuda.synchronize()
+        return [(n, i, e0.elapsed_time(e1)) for n, i, e0, e1 in recs]
+
+    def conv_flops(self, op_index: int) -> float:
+        d = self.conv_ops[op_index]
+        return 2.0 * d.B * d.M * d.N * d.taps * d.C_in
 
 
 class DecoderEngine:
@@ -238,6 +262,7 @@ class DecoderEngine:
         if out_act is not None:
             d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
         plan.keep.append(d)
+        plan.conv_ops[len(plan.ops)] = d
         if use_tc:
             plan.add(self.lib.kk_conv1d_bf16_tc, x_addr, self._addr(pc.w16), C.byref(d), block_n)
         else:

@@ -38,8 +38,21 @@ def dec_bf16(synth_weights, lib):
     return build_decoder(synth_weights, dtype="bf16")
 
 
+_KEEP = []
+
+
+@pytest.fixture(autouse=True)
+def _release_device_temporaries():
+    yield
+    torch.cuda.synchronize()
+    _KEEP.clear()
+
+
 def dev(x):
-    return torch.as_tensor(np.asarray(x)).to("cuda", torch.float32).contiguous()
+    """Host array -> CUDA tensor that stays alive until the end of the test (raw pointers are passed to C)."""
+    t = torch.as_tensor(np.asarray(x)).to("cuda", torch.float32).contiguous()
+    _KEEP.append(t)
+    return t
 
 
 # ------------------------------------------------------------------ harmonic source + STFT(20,5)
@@ -170,9 +183,12 @@ def test_vocos_shape_pin_and_batched_roundtrip():
     x = torch.from_numpy(synth.synth_audio(5, 30000, seed=8)).cuda()
     Sb = utils.stft(x, n_fft=1024, hop_length=256)
     yb = utils.istft(Sb.transpose(1, 2), hop_length=256, win_length=1024)
-    # sum(w) normaliser: 0.75 x the signal away from the edges (Hann, hop = n/4)
+    # sum(w) normaliser (utils.py:142-150): ~0.75 x the signal away from the edges (Hann, hop = n/4)
     mid = slice(1024, yb.shape[1] - 1024)
-    np.testing.assert_allclose(yb[:, mid].cpu().numpy(), 0.75 * x[:, mid].cpu().numpy(), atol=2e-5)
+    np.testing.assert_allclose(yb[:, mid].cpu().numpy(), 0.75 * x[:, mid].cpu().numpy(), rtol=2e-3, atol=2e-4)
+    for b in (0, 4):
+        ref = dsp.istft(dsp.stft(x[b].cpu().numpy(), n_fft=1024, hop_length=256).T, hop_length=256, win_length=1024)
+        np.testing.assert_allclose(yb[b].cpu().numpy(), ref, atol=1e-5)
 
 
 def test_log_mel_recipes():
@@ -258,13 +274,15 @@ def test_decoder_ragged_shapes_and_errors(dec_fp32, oracle):
         dec_fp32(inp["asr"], inp["F0_curve"][:, :-1], inp["N"], inp["s"])
 
 
-def test_decoder_batch_independence(dec_bf16):
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_decoder_batch_independence(mode, dec_fp32, dec_bf16):
     # no op mixes utterances: an utterance decodes identically alone and inside a batch
+    dec = dec_fp32 if mode == "fp32" else dec_bf16
     inp = synth.synth_decoder_inputs(3, 20, seed=55)
-    full = _run(dec_bf16, inp)
+    full = _run(dec, inp)
     one = {k: v[1:2] for k, v in inp.items()}
-    alone = _run(dec_bf16, one)
-    np.testing.assert_allclose(full[1:2], alone, atol=1e-5)
+    alone = _run(dec, one)
+    np.testing.assert_allclose(full[1:2], alone, atol=2e-5)
 
 
 def test_decoder_default_noise_and_cuda_graph(dec_bf16):

@@ -20,8 +20,21 @@ def lib():
     return L.load()
 
 
+_KEEP = []
+
+
+@pytest.fixture(autouse=True)
+def _release_device_temporaries():
+    yield
+    torch.cuda.synchronize()
+    _KEEP.clear()
+
+
 def dev(x, dtype=torch.float32):
-    return torch.as_tensor(np.asarray(x)).to("cuda", dtype).contiguous()
+    """Host array -> CUDA tensor that stays alive until the end of the test (raw pointers are passed to C)."""
+    t = torch.as_tensor(np.asarray(x)).to("cuda", dtype).contiguous()
+    _KEEP.append(t)
+    return t
 
 
 def rng(seed):
