@@ -196,6 +196,17 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             if name == "kk_conv1d_bf16_tc":
                 tc_ms += ms; tc_flops += plan.conv_flops(idx)
         tot = sum(v[1] for v in by.values())
+        if args.ops_json:
+            ops = []
+            for name, idx, ms in recs:
+                rec = {"op": name, "ms": ms}
+                if idx in plan.conv_ops:
+                    d = plan.conv_ops[idx]
+                    fl = plan.conv_flops(idx)
+                    rec.update(C_in=d.C_in, N=d.N, taps=d.taps, dil=d.dil, M=d.M, B=d.B, gflop=fl / 1e9,
+                               tflops=fl / (ms / 1e3) / 1e12)
+                ops.append(rec)
+            json.dump(ops, open(args.ops_json, "w"), indent=0)
         peaks = load_peaks()
         ms_step = ms_total / args.steps
         value = world * audio_s_per_step / (ms_step / 1e3)
@@ -274,6 +285,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ops-json", default="", help="dump the per-launch event timings of one forward")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
