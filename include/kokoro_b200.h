@@ -23,6 +23,7 @@ extern "C" {
 #define KK_ACT_NONE 0
 #define KK_ACT_LEAKY 1 /* LeakyReLU(slope)                      istftnet.py:692-693, :831 */
 #define KK_ACT_SNAKE 2 /* x + (1/alpha) sin(alpha x)^2          istftnet.py:382, :389     */
+#define KK_ACT_SNAKE_FAST 3 /* Snake with the hardware (MUFU) sine; for bf16-output pipelines */
 
 int kk_version(void);
 const char* kk_last_error(void);

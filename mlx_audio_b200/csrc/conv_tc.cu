@@ -107,6 +107,8 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     ptx::mbar_wait(tmem_full_bar, 0);
     ptx::tc_fence_after();
     const bool do_stats = d.stats != nullptr;
+    // every MMA has completed (tmem_full), so the operand ring is idle: reuse it as epilogue staging
+    float* stage_w = reinterpret_cast<float*>(smem) + lg * 1024;
 #pragma unroll 1
     for (int ch = 0; ch < BN / 32; ++ch) {
       float v[32];
@@ -123,6 +125,95 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const size_t orow = (size_t)b * d.L_out + (row_ok ? out_row : 0);
       const float* resp = d.res ? d.res + ((size_t)b * d.L_res + ((row_ok ? out_row : 0) >> d.res_shift)) * d.res_pitch + cbase : nullptr;
       const float* res2p = d.res2 ? d.res2 + orow * d.res2_pitch + cbase : nullptr;
+      // Fast path: full 32-column chunk, 16-byte aligned rows.  Global traffic goes through a warp-private
+      // 32x32 fp32 staging tile (XOR-swizzled 16-byte chunks) so that every LDG/STG covers whole 128-byte
+      // row segments (lane = column group) while TMEM hands out lane = row.
+      const bool fast = (nb + 32 <= d.N) &&
+                        (!d.out || (((reinterpret_cast<uintptr_t>(d.out) | (size_t)d.out_pitch * 4 | (size_t)cbase * 4) & 15) == 0)) &&
+                        (!d.res || (((reinterpret_cast<uintptr_t>(d.res) | (size_t)d.res_pitch * 4 | (size_t)cbase * 4) & 15) == 0)) &&
+                        (!d.res2 || (((reinterpret_cast<uintptr_t>(d.res2) | (size_t)d.res2_pitch * 4 | (size_t)cbase * 4) & 15) == 0)) &&
+                        (!d.out_act || !d.act_is_bf16 ||
+                         (((reinterpret_cast<uintptr_t>(d.out_act) | (size_t)d.act_pitch * 2 | (size_t)cbase * 2) & 15) == 0)) &&
+                        (!d.out_act || d.act_is_bf16);
+      if (fast) {
+        float* st = stage_w;                       // [32 rows][8 chunks of 4 floats], chunk ^= row & 7
+        const int mw = m0 + lg * 32;               // first GEMM row of this warp
+        if (d.res || d.res2) {
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3), cc = lane & 7;
+            const int jr = (mw + r) * d.up + ph - d.up_off;
+            const int orr = jr + d.left_pad;
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if ((mw + r) < d.M && orr >= 0 && orr < d.L_out) {
+              if (d.res) t = __ldg(reinterpret_cast<const float4*>(
+                             d.res + ((size_t)b * d.L_res + (orr >> d.res_shift)) * d.res_pitch + cbase + cc * 4));
+              if (d.res2) {
+                float4 u = __ldg(reinterpret_cast<const float4*>(
+                    d.res2 + ((size_t)b * d.L_out + orr) * d.res2_pitch + cbase + cc * 4));
+                t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
+              }
+            }
+            *reinterpret_cast<float4*>(st + r * 32 + ((cc ^ (r & 7)) << 2)) = t;
+          }
+          __syncwarp();
+        }
+        {
+          float bsv[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) bsv[i] = d.bias ? __ldg(d.bias + cbase + i) : 0.f;
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (d.res || d.res2) t = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
+            float x0 = acc_valid ? v[c4 * 4 + 0] + bsv[c4 * 4 + 0] : 0.f;
+            float x1 = acc_valid ? v[c4 * 4 + 1] + bsv[c4 * 4 + 1] : 0.f;
+            float x2 = acc_valid ? v[c4 * 4 + 2] + bsv[c4 * 4 + 2] : 0.f;
+            float x3 = acc_valid ? v[c4 * 4 + 3] + bsv[c4 * 4 + 3] : 0.f;
+            x0 = row_ok ? (x0 + t.x) * d.scale : 0.f;
+            x1 = row_ok ? (x1 + t.y) * d.scale : 0.f;
+            x2 = row_ok ? (x2 + t.z) * d.scale : 0.f;
+            x3 = row_ok ? (x3 + t.w) * d.scale : 0.f;
+            v[c4 * 4 + 0] = x0; v[c4 * 4 + 1] = x1; v[c4 * 4 + 2] = x2; v[c4 * 4 + 3] = x3;
+          }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4)
+          *reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2)) =
+              make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+        __syncwarp();
+        if (d.out) {
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3), cc = lane & 7;
+            const int orr = (mw + r) * d.up + ph - d.up_off + d.left_pad;
+            if ((mw + r) < d.M && orr >= 0 && orr < d.L_out)
+              *reinterpret_cast<float4*>(d.out + ((size_t)b * d.L_out + orr) * d.out_pitch + cbase + cc * 4) =
+                  *reinterpret_cast<const float4*>(st + r * 32 + ((cc ^ (r & 7)) << 2));
+          }
+        }
+        if (d.out_act) {
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + (lane >> 2), c8 = lane & 3;
+            const int orr = (mw + r) * d.up + ph - d.up_off + d.left_pad;
+            if ((mw + r) < d.M && orr >= 0 && orr < d.L_out) {
+              float4 t0 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8) ^ (r & 7)) << 2));
+              float4 t1 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8 + 1) ^ (r & 7)) << 2));
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(leaky(t0.x, d.act_slope), leaky(t0.y, d.act_slope));
+              __nv_bfloat162 p1 = __floats2bfloat162_rn(leaky(t0.z, d.act_slope), leaky(t0.w, d.act_slope));
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(leaky(t1.x, d.act_slope), leaky(t1.y, d.act_slope));
+              __nv_bfloat162 p3 = __floats2bfloat162_rn(leaky(t1.z, d.act_slope), leaky(t1.w, d.act_slope));
+              uint4 q4;
+              q4.x = *reinterpret_cast<uint32_t*>(&p0); q4.y = *reinterpret_cast<uint32_t*>(&p1);
+              q4.z = *reinterpret_cast<uint32_t*>(&p2); q4.w = *reinterpret_cast<uint32_t*>(&p3);
+              *reinterpret_cast<uint4*>((__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + orr) * d.act_pitch + cbase + c8 * 8) = q4;
+            }
+          }
+        }
+        __syncwarp();
+      } else {
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         const bool col_ok = (nb + i) < d.N;
@@ -172,6 +263,7 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           }
         }
       }
+      }  // fast / generic
       if (do_stats) {
         // column sums over the warp's 32 rows: halving butterfly, 31 shuffles per quantity; lane i ends
         // up with column i.  Rows / columns that were not stored hold 0.

@@ -71,6 +71,9 @@ __device__ __forceinline__ float ada_act(float x, const AdaCoef& k, bool norm, i
   if (act == KK_ACT_SNAKE) {                                    // x + (1/a) sin(a x)^2  istftnet.py:382
     float t = sinf(k.alpha * y);
     y = y + k.inv_alpha * (t * t);
+  } else if (act == KK_ACT_SNAKE_FAST) {                        // same, MUFU sine (bf16 pipelines)
+    float t = __sinf(k.alpha * y);
+    y = y + k.inv_alpha * (t * t);
   } else if (act == KK_ACT_LEAKY) {
     y = y > 0.f ? y : y * slope;
   }
@@ -98,7 +101,7 @@ __global__ void adain_act_kernel(const float* __restrict__ x, int x_pitch, const
     k.g1 = 1.0f + h[(size_t)b * h_stride + c];
     k.beta = h[(size_t)b * h_stride + C + c];
   }
-  if (act == KK_ACT_SNAKE) { k.alpha = alpha[c]; k.inv_alpha = 1.0f / k.alpha; }
+  if (act == KK_ACT_SNAKE || act == KK_ACT_SNAKE_FAST) { k.alpha = alpha[c]; k.inv_alpha = 1.0f / k.alpha; }
   int l0 = blockIdx.y * rows_per_block;
   int l1 = min(L, l0 + rows_per_block);
   const float* xb = x + (size_t)b * L * x_pitch + c;
@@ -123,6 +126,54 @@ __global__ void adain_act_kernel(const float* __restrict__ x, int x_pitch, const
   }
 }
 
+
+// Vectorised variant: one thread owns 4 consecutive channels (float4 loads, 8/16-byte stores); a warp covers
+// 128 channels = one or more whole 512-byte row segments.  Needs C, pitches % 4 == 0 and aligned bases.
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+adain_act_vec4_kernel(const float* __restrict__ x, int x_pitch, const double* __restrict__ stats,
+                      const float* __restrict__ h, int h_stride, const float* __restrict__ alpha, int act, float slope,
+                      OutT* __restrict__ out, int out_pitch, int L, int C, int rows_per_block) {
+  const int b = blockIdx.z;
+  const int c = (blockIdx.x * 32 + threadIdx.x) * 4;
+  if (c >= C) return;
+  AdaCoef k[4];
+  const bool norm = stats != nullptr;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    k[i] = AdaCoef{0.f, 1.f, 1.f, 0.f, 1.f, 1.f};
+    if (norm) {
+      double s = stats[((size_t)b * C + c + i) * 2], ss = stats[((size_t)b * C + c + i) * 2 + 1];
+      double mean = s / L;
+      double var = ss / L - mean * mean;
+      if (var < 0.0) var = 0.0;
+      k[i].mean = (float)mean;
+      k[i].rstd = 1.0f / sqrtf((float)var + 1e-5f);
+      k[i].g1 = 1.0f + h[(size_t)b * h_stride + c + i];
+      k[i].beta = h[(size_t)b * h_stride + C + c + i];
+    }
+    if (act == KK_ACT_SNAKE || act == KK_ACT_SNAKE_FAST) { k[i].alpha = alpha[c + i]; k[i].inv_alpha = 1.0f / k[i].alpha; }
+  }
+  const int l0 = blockIdx.y * rows_per_block;
+  const int l1 = min(L, l0 + rows_per_block);
+  const float* xb = x + (size_t)b * L * x_pitch + c;
+  OutT* ob = out + (size_t)b * L * out_pitch + c;
+#pragma unroll 4
+  for (int l = l0 + threadIdx.y; l < l1; l += 8) {
+    float4 v = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * x_pitch));
+    float y0 = ada_act(v.x, k[0], norm, act, slope), y1 = ada_act(v.y, k[1], norm, act, slope);
+    float y2 = ada_act(v.z, k[2], norm, act, slope), y3 = ada_act(v.w, k[3], norm, act, slope);
+    if (sizeof(OutT) == 4) {
+      *reinterpret_cast<float4*>(ob + (size_t)l * out_pitch) = make_float4(y0, y1, y2, y3);
+    } else {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(y0, y1), p1 = __floats2bfloat162_rn(y2, y3);
+      uint2 q;
+      q.x = *reinterpret_cast<uint32_t*>(&p0);
+      q.y = *reinterpret_cast<uint32_t*>(&p1);
+      *reinterpret_cast<uint2*>(ob + (size_t)l * out_pitch) = q;
+    }
+  }
+}
 
 // ---------------------------------------------------------------- decoder front glue
 // asr (B, C, T) channels-first -> out[b][t][off + c]  (32x32 shared-memory transpose)
@@ -212,14 +263,29 @@ extern "C" int kk_adain_act(const float* x, int x_pitch, const double* stats, co
                             const float* alpha, int act, float slope, void* out, int out_is_bf16, int out_pitch,
                             int B, int L, int C, int pool, const float* pool_w, const float* pool_b, void* stream) {
   KK_CHECK_ARG(x && out && B > 0 && L > 0 && C > 0 && x_pitch >= C && out_pitch >= C, "kk_adain_act: bad shape");
-  KK_CHECK_ARG(act == KK_ACT_NONE || act == KK_ACT_LEAKY || act == KK_ACT_SNAKE, "kk_adain_act: act=%d", act);
-  KK_CHECK_ARG(act != KK_ACT_SNAKE || alpha, "kk_adain_act: snake needs alpha");
+  KK_CHECK_ARG(act >= KK_ACT_NONE && act <= KK_ACT_SNAKE_FAST, "kk_adain_act: act=%d", act);
+  KK_CHECK_ARG((act != KK_ACT_SNAKE && act != KK_ACT_SNAKE_FAST) || alpha, "kk_adain_act: snake needs alpha");
   KK_CHECK_ARG(!stats || h, "kk_adain_act: normalisation needs the style projection h");
   KK_CHECK_ARG(!pool || (pool_w && pool_b), "kk_adain_act: pool needs weights");
   int cb = kk::cdiv(C, 32);
   int rpb = rows_per_block_for(L, B, cb);
   dim3 grid(cb, kk::cdiv(L, rpb), B), block(32, 8);
   cudaStream_t st = (cudaStream_t)stream;
+  const size_t osz = out_is_bf16 ? 2 : 4;
+  if (!pool && C % 4 == 0 && x_pitch % 4 == 0 && out_pitch % 4 == 0 && ((uintptr_t)x & 15) == 0 &&
+      ((uintptr_t)out & (4 * osz - 1)) == 0) {
+    int cb4 = kk::cdiv(C, 128);
+    int rpb4 = rows_per_block_for(L, B, cb4);
+    dim3 grid4(cb4, kk::cdiv(L, rpb4), B);
+    if (out_is_bf16)
+      kk::adain_act_vec4_kernel<__nv_bfloat16><<<grid4, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, slope,
+                                                                        (__nv_bfloat16*)out, out_pitch, L, C, rpb4);
+    else
+      kk::adain_act_vec4_kernel<float><<<grid4, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, slope,
+                                                                (float*)out, out_pitch, L, C, rpb4);
+    KK_LAUNCH_CHECK("adain_act_vec4_kernel");
+    return KK_OK;
+  }
 #define KK_ADA(T, P) kk::adain_act_kernel<T, P><<<grid, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, \
     slope, (T*)out, out_pitch, L, C, pool_w, pool_b, rpb)
   if (out_is_bf16) { if (pool) KK_ADA(__nv_bfloat16, true); else KK_ADA(__nv_bfloat16, false); }

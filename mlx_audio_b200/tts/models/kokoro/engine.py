@@ -291,17 +291,18 @@ class DecoderEngine:
         in ``work`` after the first iteration (work may be x_in itself: fully in place).  ``final`` gives the
         last conv2 epilogue: dict(out_addr, out_pitch, res2, scale, stats_addr, out_act)."""
         ap = self._act_pitch(C_)
+        snake = L.KK_ACT_SNAKE_FAST if self.tc else L.KK_ACT_SNAKE  # MUFU sine only when the result is rounded to bf16
         cur, cur_stats = x_in, stats_in
         for it in range(3):
             d = dils[it]
             c1 = self.convs[f"{prefix}.convs1.{it}"]
             c2 = self.convs[f"{prefix}.convs2.{it}"]
-            self._ada(plan, self._addr(cur), C_, cur_stats, f"{prefix}.adain1.{it}", L.KK_ACT_SNAKE, 0.0,
+            self._ada(plan, self._addr(cur), C_, cur_stats, f"{prefix}.adain1.{it}", snake, 0.0,
                       self.w[f"{prefix}.alpha1.{it}"], act, ap, B, L_, C_, h_all)
             st_y = self._stats(plan, B, C_)
             self._conv(plan, c1, self._addr(act), B, L_, ap, L_, dil=d, pad_left=(k * d - d) // 2,
                        out_addr=self._addr(y), out_pitch=C_, stats_addr=st_y)
-            self._ada(plan, self._addr(y), C_, st_y, f"{prefix}.adain2.{it}", L.KK_ACT_SNAKE, 0.0,
+            self._ada(plan, self._addr(y), C_, st_y, f"{prefix}.adain2.{it}", snake, 0.0,
                       self.w[f"{prefix}.alpha2.{it}"], act, ap, B, L_, C_, h_all)
             res = (self._addr(cur), C_, 0, L_)
             if it < 2:
