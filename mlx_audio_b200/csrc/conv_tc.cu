@@ -26,91 +26,15 @@ struct TcCfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 8 * BN * 4 /*stats: 4 warps x (sum, sumsq) x BN*/;
 };
 
+// One 32-column chunk of the epilogue for the warp that owns TMEM lane group `lg`: tensor memory -> registers
+// -> (bias, residuals, scale) -> coalesced global stores through the warp-private staging tile; returns the
+// per-column (sum, sum of squares) partials of the warp's 32 rows in lane order via s_stats.
 template <int BN>
-__global__ void __launch_bounds__(TC_THREADS)
-conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const kk_conv_desc d) {
-  using Cfg = TcCfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* tail = smem + Cfg::STAGES * Cfg::STAGE_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
-  uint64_t* empty_bar = full_bar + Cfg::STAGES;
-  uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-  float* s_stats = reinterpret_cast<float*>(tail + 256);  // [4 warps][2][BN], no atomics: deterministic
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * TC_BM;
-  const int n0 = blockIdx.y * BN;
-  const int b = blockIdx.z;
-  const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
-  const int num_kb = d.taps * cblocks;
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tmA);
-    ptx::prefetch_tmap(&tmB);
-    for (int s = 0; s < Cfg::STAGES; ++s) {
-      ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
-    }
-    ptx::mbar_init(tmem_full_bar, 1);
-    ptx::fence_barrier_init();
-  }
-  if (warp == 2) ptx::tmem_alloc<BN>(tmem_slot);
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::STAGES;
-        const uint32_t ph = (kb / Cfg::STAGES) & 1;
-        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
-        const int t = kb / cblocks, cb = kb - t * cblocks;
-        uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
-        uint8_t* sb = sa + TC_A_BYTES;
-        ptx::mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
-        ptx::tma_load_3d(sa, &tmA, &full_bar[s], cb * TC_BK, m0 + t * d.dil - d.pad_left, b);
-        ptx::tma_load_2d(sb, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, BN);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::STAGES;
-        const uint32_t ph = (kb / Cfg::STAGES) & 1;
-        ptx::mbar_wait(&full_bar[s], ph);
-        ptx::tc_fence_after();
-        const uint32_t sa = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES);
-        const uint32_t sb = sa + TC_A_BYTES;
-#pragma unroll
-        for (int k = 0; k < TC_BK / 16; ++k) {
-          // K-major, 128B swizzle: rows are 128 B apart, 8-row atoms 1024 B apart; +32 B per 16-element K step
-          const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-          const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-          ptx::umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
-        }
-        ptx::umma_commit(&empty_bar[s]);  // frees the smem slot when these MMAs have read it
-      }
-      ptx::umma_commit(tmem_full_bar);    // accumulator complete
-    }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int lg = warp & 3;                 // TMEM lane group this warp may access
-    const int m = m0 + lg * 32 + lane;       // GEMM row of this thread
-    ptx::mbar_wait(tmem_full_bar, 0);
-    ptx::tc_fence_after();
-    const bool do_stats = d.stats != nullptr;
-    // every MMA has completed (tmem_full), so the operand ring is idle: reuse it as epilogue staging
-    float* stage_w = reinterpret_cast<float*>(smem) + lg * 1024;
-#pragma unroll 1
-    for (int ch = 0; ch < BN / 32; ++ch) {
+__device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int b, const int m0, const int n0,
+                                               const int ch, const int lg, const int lane, const uint32_t tmem_base,
+                                               float* stage_w, float* s_stats, const bool do_stats) {
+  const int m = m0 + lg * 32 + lane;  // GEMM row of this thread
+  {
       float v[32];
       ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32), v);
       ptx::tmem_ld_wait();
@@ -286,7 +210,94 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = v[0];
         s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = q[0];
       }
+  }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS)
+conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const kk_conv_desc d) {
+  using Cfg = TcCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* tail = smem + Cfg::STAGES * Cfg::STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  float* s_stats = reinterpret_cast<float*>(tail + 256);  // [4 warps][2][BN], no atomics: deterministic
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * TC_BM;
+  const int n0 = blockIdx.y * BN;
+  const int b = blockIdx.z;
+  const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
+  const int num_kb = d.taps * cblocks;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
     }
+    ptx::mbar_init(tmem_full_bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<BN>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % Cfg::STAGES;
+        const uint32_t ph = (kb / Cfg::STAGES) & 1;
+        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+        const int t = kb / cblocks, cb = kb - t * cblocks;
+        uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+        uint8_t* sb = sa + TC_A_BYTES;
+        ptx::mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+        ptx::tma_load_3d(sa, &tmA, &full_bar[s], cb * TC_BK, m0 + t * d.dil - d.pad_left, b);
+        ptx::tma_load_2d(sb, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % Cfg::STAGES;
+        const uint32_t ph = (kb / Cfg::STAGES) & 1;
+        ptx::mbar_wait(&full_bar[s], ph);
+        ptx::tc_fence_after();
+        const uint32_t sa = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES);
+        const uint32_t sb = sa + TC_A_BYTES;
+#pragma unroll
+        for (int k = 0; k < TC_BK / 16; ++k) {
+          // K-major, 128B swizzle: rows are 128 B apart, 8-row atoms 1024 B apart; +32 B per 16-element K step
+          const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+          const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+          ptx::umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        ptx::umma_commit(&empty_bar[s]);  // frees the smem slot when these MMAs have read it
+      }
+      ptx::umma_commit(tmem_full_bar);    // accumulator complete
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int lg = warp & 3;                 // TMEM lane group this warp may access
+    ptx::mbar_wait(tmem_full_bar, 0);
+    ptx::tc_fence_after();
+    const bool do_stats = d.stats != nullptr;
+    // every MMA has completed (tmem_full), so the operand ring is idle: reuse it as epilogue staging
+    float* stage_w = reinterpret_cast<float*>(smem) + lg * 1024;
+#pragma unroll 1
+    for (int ch = 0; ch < BN / 32; ++ch)
+      epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base, stage_w, s_stats, do_stats);
     if (do_stats) {
       asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps
       for (int i = threadIdx.x - 64; i < BN; i += 128) {
@@ -305,6 +316,164 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 2) ptx::tmem_dealloc<BN>(tmem_base);
+}
+
+}  // namespace kk
+
+// ---------------------------------------------------------------------------------------------------------
+// Persistent variant: one CTA per SM loops over output tiles.  Tensor memory holds TWO accumulators so the
+// epilogue of tile i (8 warps) overlaps the TMA/MMA main loop of tile i+1; barrier set-up, TMEM allocation and
+// tensor-map prefetch are paid once per SM instead of once per tile.
+namespace kk {
+
+constexpr int TP_EPI_WARPS = 8;
+constexpr int TP_THREADS = 64 + TP_EPI_WARPS * 32;  // 320
+
+template <int BN>
+struct TpCfg {
+  static constexpr int B_BYTES = BN * TC_BK * 2;
+  static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
+  static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 5 : 6);
+  static constexpr int STAGING_BYTES = TP_EPI_WARPS * 4096;
+  static constexpr int STATS_BYTES = 2 * 8 * BN * 4;  // double-buffered [4 lane groups][sum, sumsq][BN]
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES + 256 + 1024;
+  static constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TP_THREADS, 1)
+conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                              const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles) {
+  using Cfg = TpCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  float* staging = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  float* s_stats_all = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::STAGING_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::STAGING_BYTES +
+                                                   Cfg::STATS_BYTES);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
+  const int num_kb = d.taps * cblocks;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(&tmem_full_bar[a], 1);
+      ptx::mbar_init(&tmem_empty_bar[a], TP_EPI_WARPS * 32);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t kbg = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int nt = tile % n_tiles;
+        const int rest = tile / n_tiles;
+        const int mt = rest % m_tiles, b = rest / m_tiles;
+        const int m0 = mt * TC_BM, n0 = nt * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
+          const int s = kbg % Cfg::STAGES;
+          const uint32_t ph = (kbg / Cfg::STAGES) & 1;
+          ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+          const int t = kb / cblocks, cb = kb - t * cblocks;
+          uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+          ptx::mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+          ptx::tma_load_3d(sa, &tmA, &full_bar[s], cb * TC_BK, m0 + t * d.dil - d.pad_left, b);
+          ptx::tma_load_2d(sa + TC_A_BYTES, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, BN);
+      uint32_t kbg = 0, it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const uint32_t acc = it & 1, aph = (it >> 1) & 1;
+        ptx::mbar_wait(&tmem_empty_bar[acc], aph ^ 1);  // epilogue has drained this accumulator
+        ptx::tc_fence_after();
+        const uint32_t tacc = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
+          const int s = kbg % Cfg::STAGES;
+          const uint32_t ph = (kbg / Cfg::STAGES) & 1;
+          ptx::mbar_wait(&full_bar[s], ph);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES);
+          const uint32_t sb = sa + TC_A_BYTES;
+#pragma unroll
+          for (int k = 0; k < TC_BK / 16; ++k) {
+            const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+            const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+            ptx::umma_bf16(tacc, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[s]);
+        }
+        ptx::umma_commit(&tmem_full_bar[acc]);
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9) =====================
+    const int ew = warp - 2;
+    const int lg = warp & 3;            // TMEM lane group of this warp
+    const int half = ew >> 2;           // which half of the tile's column chunks
+    constexpr int CHUNKS = BN / 32;
+    constexpr int CH_PER = (CHUNKS + 1) / 2;
+    float* stage_w = staging + ew * 1024;
+    const bool do_stats = d.stats != nullptr;
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+      const int nt = tile % n_tiles;
+      const int rest = tile / n_tiles;
+      const int mt = rest % m_tiles, b = rest / m_tiles;
+      const int m0 = mt * TC_BM, n0 = nt * BN;
+      const uint32_t acc = it & 1, aph = (it >> 1) & 1;
+      float* s_stats = s_stats_all + acc * (8 * BN);
+      ptx::mbar_wait(&tmem_full_bar[acc], aph);
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < CH_PER; ++c) {
+        const int ch = half * CH_PER + c;
+        if (ch < CHUNKS)
+          epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, s_stats, do_stats);
+      }
+      // all tcgen05.ld of this thread have completed (wait::ld inside the chunk): hand the accumulator back
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&tmem_empty_bar[acc]);
+      if (do_stats) {
+        asm volatile("bar.sync 1, %0;" ::"n"(TP_EPI_WARPS * 32) : "memory");
+        for (int i = threadIdx.x - 64; i < BN; i += TP_EPI_WARPS * 32) {
+          const int n = n0 + i;
+          if (n < d.N) {
+            const int cc = d.up > 1 ? n % d.C_out : n;
+            float ts = (s_stats[0 * BN + i] + s_stats[2 * BN + i]) + (s_stats[4 * BN + i] + s_stats[6 * BN + i]);
+            float tq = (s_stats[1 * BN + i] + s_stats[3 * BN + i]) + (s_stats[5 * BN + i] + s_stats[7 * BN + i]);
+            atomicAdd(d.stats + ((size_t)b * d.C_out + cc) * 2, (double)ts);
+            atomicAdd(d.stats + ((size_t)b * d.C_out + cc) * 2 + 1, (double)tq);
+          }
+        }
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
 }  // namespace kk
@@ -372,6 +541,49 @@ static int launch_tc(const void* x, const void* w, const kk_conv_desc* d, cudaSt
   return KK_OK;
 }
 
+static int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int BN>
+static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d, cudaStream_t st) {
+  using Cfg = TpCfg<BN>;
+  CUtensorMap tmA, tmB;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)d->C_in, (cuuint64_t)d->L_in, (cuuint64_t)d->B};
+    cuuint64_t strides[2] = {(cuuint64_t)d->x_pitch * 2, (cuuint64_t)d->L_in * d->x_pitch * 2};
+    cuuint32_t box[3] = {TC_BK, TC_BM, 1};
+    int rc = make_tmap_bf16(&tmA, x, 3, dims, strides, box);
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
+    cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * 2};
+    cuuint32_t box[2] = {TC_BK, BN};
+    int rc = make_tmap_bf16(&tmB, w, 2, dims, strides, box);
+    if (rc) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    KK_CUDA(cudaFuncSetAttribute(conv1d_bf16_tc_persist_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int m_tiles = cdiv(d->M, TC_BM), n_tiles = cdiv(d->N, BN);
+  const long long total = (long long)m_tiles * n_tiles * d->B;
+  KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_bf16_tc: too many tiles");
+  const int grid = (int)(total < num_sms() ? total : num_sms());
+  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, *d, m_tiles, n_tiles, (int)total);
+  KK_LAUNCH_CHECK("conv1d_bf16_tc_persist_kernel");
+  return KK_OK;
+}
+
 }  // namespace kk
 
 extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int block_n, void* stream) {
@@ -388,8 +600,20 @@ extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_des
   KK_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kk_conv1d_bf16_tc: operands must be 16-byte aligned");
   KK_CHECK_ARG(d->up == 1 || d->C_out % 32 == 0, "kk_conv1d_bf16_tc: polyphase needs C_out %% 32 == 0");
   KK_CHECK_ARG(d->B <= 65535, "kk_conv1d_bf16_tc: batch too large");
-  if (block_n == 0) block_n = d->N > 128 ? 256 : (d->N > 64 ? 128 : (d->N > 32 ? 64 : 32));
+  // bit 12 of block_n selects the one-tile-per-CTA kernel (kept for A/B comparison); default is persistent
+  const bool legacy = (block_n & 0x1000) != 0;
+  block_n &= 0xfff;
+  if (block_n == 0) block_n = d->N > 64 ? 128 : (d->N > 32 ? 64 : 32);
   cudaStream_t st = (cudaStream_t)stream;
+  if (!legacy) {
+    switch (block_n) {
+      case 32: return kk::launch_tc_persist<32>(x, w, d, st);
+      case 64: return kk::launch_tc_persist<64>(x, w, d, st);
+      case 128: return kk::launch_tc_persist<128>(x, w, d, st);
+      case 256: return kk::launch_tc_persist<256>(x, w, d, st);
+      default: kk::set_error("kk_conv1d_bf16_tc: block_n %d not in {32,64,128,256}", block_n); return KK_ERR_INVALID_ARG;
+    }
+  }
   switch (block_n) {
     case 32: return kk::launch_tc<32>(x, w, d, st);
     case 64: return kk::launch_tc<64>(x, w, d, st);

@@ -264,11 +264,25 @@ class DecoderEngine:
         plan.keep.append(d)
         plan.conv_ops[len(plan.ops)] = d
         if use_tc:
+            if block_n == 0:
+                block_n = self._auto_block_n(pc)
             plan.add(self.lib.kk_conv1d_bf16_tc, x_addr, self._addr(pc.w16), C.byref(d), block_n)
         else:
             assert pc.w32 is not None, pc.name
             plan.add(self.lib.kk_conv1d_f32, x_addr, self._addr(pc.w32), C.byref(d))
         return d
+
+    def _auto_block_n(self, pc: PreparedConv) -> int:
+        """N tile of the tensor-core kernel (0 = library default: 128 for N > 64).  Experiment knobs:
+        KK_TC_BN=<n> forces the tile, KK_TC_LEGACY=1 selects the one-tile-per-CTA kernel."""
+        import os
+        bn = 0
+        env = os.environ.get("KK_TC_BN")
+        if env and pc.N >= int(env):
+            bn = int(env)
+        if os.environ.get("KK_TC_LEGACY") == "1":
+            bn |= 0x1000
+        return bn
 
     def _ada(self, plan: Plan, x_addr: int, x_pitch: int, stats_addr: Optional[int], ada_prefix: Optional[str],
              act: int, slope: float, alpha: Optional[torch.Tensor], out: torch.Tensor, out_pitch: int, B: int, L_: int,
