@@ -1,0 +1,102 @@
+"""Utterance sharding across the GPUs of one box and the final waveform gather.
+
+The decoder has no cross-utterance dependence (instance norm reduces over time only, istftnet.py:221-230; the
+style is per utterance, :334-337), so the path is partitioned by utterance: every rank owns the full decoder
+and a subset of the utterances; the ONLY exchange is the gather of the finished waveforms on rank 0.
+
+Host logic only (torch.distributed plumbing); works with the ``nccl`` backend on GPUs and with ``gloo`` on CPU
+tensors (the world-size-2 tests).  Nothing here computes audio.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+SAMPLES_PER_FRAME = 600
+
+
+def lpt_assign(frames: Sequence[int], world: int) -> List[List[int]]:
+    """Longest-processing-time-first assignment of utterances (cost = frame count T) to ``world`` ranks.
+    Deterministic: ties broken by utterance index, then by rank.  Returns per-rank utterance indices sorted
+    ascending (so that a rank's outputs keep the caller's relative order)."""
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    load = [0] * world
+    out: List[List[int]] = [[] for _ in range(world)]
+    for i in sorted(range(len(frames)), key=lambda i: (-int(frames[i]), i)):
+        r = min(range(world), key=lambda r: (load[r], r))
+        out[r].append(i)
+        load[r] += int(frames[i])
+    return [sorted(a) for a in out]
+
+
+def bucket_by_length(indices: Sequence[int], frames: Sequence[int], max_batch: int) -> List[Tuple[int, List[int]]]:
+    """Group a rank's utterances into same-T batches of at most ``max_batch`` (one launch plan / CUDA graph per
+    (B, T) shape).  Returns [(T, [utterance indices])] ordered by decreasing T."""
+    if max_batch < 1:
+        raise ValueError("max_batch must be >= 1")
+    by_t: Dict[int, List[int]] = {}
+    for i in indices:
+        by_t.setdefault(int(frames[i]), []).append(i)
+    out = []
+    for t in sorted(by_t, reverse=True):
+        ids = by_t[t]
+        for k in range(0, len(ids), max_batch):
+            out.append((t, ids[k:k + max_batch]))
+    return out
+
+
+def gather_waveforms(local: Dict[int, torch.Tensor], frames: Sequence[int], assignment: List[List[int]],
+                     dst: int = 0, group=None) -> Optional[List[torch.Tensor]]:
+    """gather(v) of ragged waveforms to ``dst``.  ``local``: {utterance index: (600*T,) float32 tensor} for the
+    utterances this rank decoded.  Every rank packs its waveforms into ONE flat buffer (order = its assignment
+    list) and rank ``dst`` receives each peer's buffer with a single point-to-point transfer (sizes are known
+    everywhere from ``frames`` + ``assignment``: no size exchange, no padding).  Returns the utterance-ordered
+    list on ``dst``, None elsewhere."""
+    rank = dist.get_rank(group)
+    world = dist.get_world_size(group)
+    mine = assignment[rank]
+    dev = next(iter(local.values())).device if local else torch.device("cpu")
+    sizes = [[int(frames[i]) * SAMPLES_PER_FRAME for i in assignment[r]] for r in range(world)]
+    flat = torch.cat([local[i].reshape(-1) for i in mine]) if mine else torch.empty(0, dtype=torch.float32, device=dev)
+    if flat.numel() != sum(sizes[rank]):
+        raise ValueError(f"rank {rank}: packed {flat.numel()} samples, expected {sum(sizes[rank])}")
+    if rank != dst:
+        if flat.numel():
+            dist.send(flat, dst=dst, group=group)
+        return None
+    out: List[Optional[torch.Tensor]] = [None] * len(frames)
+    for r in range(world):
+        if r == dst:
+            buf = flat
+        else:
+            buf = torch.empty(sum(sizes[r]), dtype=torch.float32, device=dev)
+            if buf.numel():
+                dist.recv(buf, src=r, group=group)
+        off = 0
+        for i, n in zip(assignment[r], sizes[r]):
+            out[i] = buf[off:off + n]
+            off += n
+    return out  # type: ignore[return-value]
+
+
+def decode_sharded(decode_batch: Callable[[int, List[int]], torch.Tensor], frames: Sequence[int], max_batch: int = 64,
+                   dst: int = 0, group=None) -> Optional[List[torch.Tensor]]:
+    """Decode ``len(frames)`` utterances over all ranks.  ``decode_batch(T, ids)`` must return the (len(ids), 1,
+    600*T) waveforms of utterances ``ids`` (all of length T) - on the GPU path it is ``Decoder.__call__`` on
+    the rank's own inputs.  Returns the utterance-ordered waveform list on ``dst``."""
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    assignment = lpt_assign(frames, world)
+    local: Dict[int, torch.Tensor] = {}
+    for t, ids in bucket_by_length(assignment[rank], frames, max_batch):
+        y = decode_batch(t, ids)
+        if y.shape[0] != len(ids) or y.shape[-1] != t * SAMPLES_PER_FRAME:
+            raise ValueError(f"decode_batch returned {tuple(y.shape)} for {len(ids)} utterances of T={t}")
+        for k, i in enumerate(ids):
+            local[i] = y[k].reshape(-1).clone()   # the decoder reuses its output buffer
+    if world == 1:
+        return [local[i] for i in range(len(frames))]
+    return gather_waveforms(local, frames, assignment, dst=dst, group=group)

@@ -1,0 +1,100 @@
+"""Host-side multi-GPU logic (utterance sharding + waveform gather) on CPU: world_size 2, gloo backend."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from mlx_audio_b200 import sharding
+
+
+def test_lpt_assign_balances_and_is_deterministic():
+    rng = np.random.default_rng(4001)
+    frames = rng.integers(240, 401, size=4096).tolist()
+    for world in (1, 2, 4, 8):
+        a = sharding.lpt_assign(frames, world)
+        assert sorted(i for r in a for i in r) == list(range(4096))
+        loads = [sum(frames[i] for i in r) for r in a]
+        assert max(loads) - min(loads) <= max(frames)  # LPT bound
+        assert a == sharding.lpt_assign(frames, world)
+    assert sharding.lpt_assign([], 2) == [[], []]
+    assert sharding.lpt_assign([5], 2) == [[0], []]
+    with pytest.raises(ValueError):
+        sharding.lpt_assign([1], 0)
+
+
+def test_bucket_by_length():
+    frames = [3, 5, 3, 3, 5, 7]
+    b = sharding.bucket_by_length([0, 1, 2, 3, 4, 5], frames, 2)
+    assert b == [(7, [5]), (5, [1, 4]), (3, [0, 2]), (3, [3])]
+    with pytest.raises(ValueError):
+        sharding.bucket_by_length([0], frames, 0)
+
+
+def _fake_wave(i, t):
+    """Deterministic stand-in for the decoder output of utterance i (T = t)."""
+    n = t * sharding.SAMPLES_PER_FRAME
+    return (torch.arange(n, dtype=torch.float32) * 1e-3 + float(i)).reshape(1, 1, n)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, frames, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        calls = []
+
+        def decode_batch(t, ids):
+            calls.append((t, list(ids)))
+            return torch.cat([_fake_wave(i, t) for i in ids], 0)
+
+        out = sharding.decode_sharded(decode_batch, frames, max_batch=2)
+        if rank == 0:
+            ok = all(torch.equal(out[i].reshape(-1), _fake_wave(i, frames[i]).reshape(-1)) for i in range(len(frames)))
+            q.put(("gather", ok, len(out)))
+        else:
+            assert out is None
+        q.put(("calls", rank, calls))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(120)
+def test_decode_sharded_world2_gloo():
+    frames = [4, 2, 7, 2, 4, 3, 1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, frames, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    msgs = [q.get(timeout=100) for _ in range(3)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    gather = [m for m in msgs if m[0] == "gather"][0]
+    assert gather[1] is True and gather[2] == len(frames)
+    calls = {m[1]: m[2] for m in msgs if m[0] == "calls"}
+    assign = sharding.lpt_assign(frames, 2)
+    for r in (0, 1):
+        seen = sorted(i for _, ids in calls[r] for i in ids)
+        assert seen == assign[r]                      # every rank decodes exactly its shard
+        assert all(len(ids) <= 2 for _, ids in calls[r])
+        assert all(frames[i] == t for t, ids in calls[r] for i in ids)
+
+
+def test_decode_sharded_single_process():
+    frames = [2, 3, 2]
+    out = sharding.decode_sharded(lambda t, ids: torch.cat([_fake_wave(i, t) for i in ids], 0), frames, max_batch=8)
+    assert [o.numel() for o in out] == [1200, 1800, 1200]
+    assert torch.equal(out[1], _fake_wave(1, 3).reshape(-1))
