@@ -104,6 +104,24 @@ int kk_conv1d_f32(const float* x, const float* w, const kk_conv_desc* d, void* s
  * Returns KK_ERR_UNSUPPORTED on a non-sm_100 device. */
 int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int block_n, void* stream);
 
+/* ---- fused AdaIN + activation + convolution (AdaINResBlock1's `conv(snake(adain(x, s)))` pairs,
+ * istftnet.py:377-396, and AdainResBlk1d's `conv(leaky(norm(x, s)))`, :874-894) on the tensor cores.
+ * The raw (pre-normalisation) tensor x is read ONCE per output tile (tile + dilation halo); the instance-norm
+ * affine and the activation are applied in registers while the bf16 A operand is written to shared memory
+ * (128B-swizzled), and every tap reads that tile through a row-shifted UMMA descriptor - the activated tensor
+ * never exists in HBM.  Epilogue identical to kk_conv1d_bf16_tc (bias, residuals, scale, stats, out / out_act).
+ *   A[b][l][c] = act(a_c * x[b][l][c] + b_c),  a_c = (1+gamma_c) / sqrt(var_c + 1e-5),  b_c = beta_c - a_c mean_c
+ *   (rows outside [0, L_in) are zero AFTER the activation: the conv's own zero padding)
+ * Restrictions: stride 1, up 1, C_in in {128, 256} with N == C_in, (taps-1)*dil <= 56. */
+typedef struct kk_adain_in {
+  const void* x; int x_is_bf16; int x_pitch; /* raw input (B, L_in, x_pitch), fp32 or bf16                   */
+  const double* stats;                       /* (B, C_in, 2) sum / sum of squares over time; NULL: no norm  */
+  const float* h; int h_stride;              /* gamma = h[b*h_stride + c], beta = h[b*h_stride + C_in + c]  */
+  const float* alpha;                        /* Snake alpha (C_in), KK_ACT_SNAKE* only                      */
+  int act; float slope;                      /* KK_ACT_*; Snake always uses the hardware sine here          */
+} kk_adain_in;
+int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, const kk_conv_desc* d, void* stream);
+
 /* ---- harmonic source (SineGen / SourceModuleHnNSF istftnet.py:531-680, interpolate.py:82-106,
  * nn.Upsample :718-720) fused with MLXSTFT.transform (:463-495, utils.stft n_fft=20 hop=5):
  * f0 (B, 2T) -> har_source (B, 600T) -> har (B, 120T+1, har_pitch) = [|X| (11) , angle(X) (11)].

@@ -40,6 +40,17 @@ class ConvDesc(C.Structure):
     ]
 
 
+class AdainIn(C.Structure):
+    """Mirror of ``kk_adain_in`` (include/kokoro_b200.h)."""
+    _fields_ = [
+        ("x", C.c_void_p), ("x_is_bf16", C.c_int), ("x_pitch", C.c_int),
+        ("stats", C.c_void_p),
+        ("h", C.c_void_p), ("h_stride", C.c_int),
+        ("alpha", C.c_void_p),
+        ("act", C.c_int), ("slope", C.c_float),
+    ]
+
+
 _I, _F, _P, _LL, _ULL = C.c_int, C.c_float, C.c_void_p, C.c_longlong, C.c_ulonglong
 
 # name -> argtypes; every function returns int except kk_last_error
@@ -56,6 +67,7 @@ PROTOTYPES = {
     "kk_convert_act": [_P, _I, _P, _I, _I, _LL, _I, _F, _P],
     "kk_conv1d_f32": [_P, _P, C.POINTER(ConvDesc), _P],
     "kk_conv1d_bf16_tc": [_P, _P, C.POINTER(ConvDesc), _I, _P],
+    "kk_conv1d_adain_bf16_tc": [C.POINTER(AdainIn), _P, C.POINTER(ConvDesc), _P],
     "kk_hnsf_source": [_P, _P, _ULL, _P, _P, _P, _P, _I, _I, _I, _P],
     "kk_stft_n20": [_P, _P, _I, _I, _I, _P],
     "kk_istft_head_n20": [_P, _I, _P, _I, _I, _P],

@@ -20,7 +20,7 @@ from typing import Callable, Dict, List, Optional, Tuple
 import torch
 
 from .... import _lib as L
-from ...._lib import ConvDesc
+from ...._lib import AdainIn, ConvDesc
 
 
 def _ceil(a: int, m: int) -> int:
@@ -136,6 +136,8 @@ class DecoderEngine:
         self.cfg = cfg
         self.mode = mode
         self.tc = mode == "bf16"
+        import os as _os
+        self.fused = self.tc and _os.environ.get("KK_FUSED", "1") != "0"   # A/B knob: 0 = separate AdaIN kernels
         if self.tc and not self.lib.kk_device_is_sm100():
             raise L.KokoroB200Error("bf16 tensor-core mode needs an sm_100 (B200) device")
         self.dev = next(iter(weights.values())).device
@@ -284,6 +286,41 @@ class DecoderEngine:
             bn |= 0x1000
         return bn
 
+    def _conv_fused(self, plan: Plan, pc: PreparedConv, x: torch.Tensor, x_pitch: int, stats_addr: Optional[int],
+                    ada_prefix: Optional[str], act: int, slope: float, alpha: Optional[torch.Tensor], h_all, B: int,
+                    L_: int, *, dil: int = 1, pad_left: int = 0, out_addr: Optional[int] = None, out_pitch: int = 0,
+                    res=None, res2=None, scale: float = 1.0, out_stats: Optional[int] = None, out_act=None):
+        """AdaIN + activation + conv in one tensor-core launch (kk_conv1d_adain_bf16_tc)."""
+        a = AdainIn()
+        a.x, a.x_is_bf16, a.x_pitch = self._addr(x), int(x.dtype == torch.bfloat16), x_pitch
+        a.stats = stats_addr
+        a.h = self._addr(h_all, self.ada_off[ada_prefix]) if ada_prefix is not None else None
+        a.h_stride = self.ada_R
+        a.alpha = self._addr(alpha)
+        a.act, a.slope = act, slope
+        d = ConvDesc()
+        d.B, d.L_in, d.C_in, d.x_pitch = B, L_, pc.C_in, x_pitch
+        d.taps, d.dil, d.pad_left, d.stride = pc.taps, dil, pad_left, 1
+        d.Cw = pc.Cw16
+        d.M, d.N = L_, pc.N
+        d.C_out, d.up, d.up_off = pc.C_out, 1, 0
+        d.L_true = d.L_out = L_
+        d.left_pad = 0
+        d.bias = self._addr(pc.bias) if pc.bias is not None else None
+        if res is not None:
+            d.res, d.res_pitch, d.res_shift, d.L_res = res
+        if res2 is not None:
+            d.res2, d.res2_pitch = res2
+        d.scale = scale
+        d.out, d.out_pitch = out_addr, out_pitch
+        d.stats = out_stats
+        if out_act is not None:
+            d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
+        plan.keep.extend([a, d])
+        plan.conv_ops[len(plan.ops)] = d
+        plan.add(self.lib.kk_conv1d_adain_bf16_tc, C.byref(a), self._addr(pc.w16), C.byref(d))
+        return d
+
     def _ada(self, plan: Plan, x_addr: int, x_pitch: int, stats_addr: Optional[int], ada_prefix: Optional[str],
              act: int, slope: float, alpha: Optional[torch.Tensor], out: torch.Tensor, out_pitch: int, B: int, L_: int,
              C_: int, h_all: torch.Tensor, pool: bool = False):
@@ -307,6 +344,34 @@ class DecoderEngine:
         ap = self._act_pitch(C_)
         snake = L.KK_ACT_SNAKE_FAST if self.tc else L.KK_ACT_SNAKE  # MUFU sine only when the result is rounded to bf16
         cur, cur_stats = x_in, stats_in
+        if self.fused and C_ in (128, 256):
+            # tensor-core mode: AdaIN + Snake run inside the conv (A-operand transform); the conv1 output y is kept
+            # in bf16 (it is only ever normalised, activated and rounded to bf16 again), the residual stream in fp32
+            ybf = plan.buffers.get(f"ybf.{B}.{L_}.{C_}")
+            if ybf is None:
+                ybf = self._buf(plan, f"ybf.{B}.{L_}.{C_}", (B, L_, C_), torch.bfloat16)
+            for it in range(3):
+                d = dils[it]
+                c1 = self.convs[f"{prefix}.convs1.{it}"]
+                c2 = self.convs[f"{prefix}.convs2.{it}"]
+                st_y = self._stats(plan, B, C_)
+                self._conv_fused(plan, c1, cur, C_, cur_stats, f"{prefix}.adain1.{it}", snake, 0.0,
+                                 self.w[f"{prefix}.alpha1.{it}"], h_all, B, L_, dil=d, pad_left=(k * d - d) // 2,
+                                 out_stats=st_y, out_act=(self._addr(ybf), C_, 1, 1.0))
+                res = (self._addr(cur), C_, 0, L_)
+                if it < 2:
+                    st_n = self._stats(plan, B, C_)
+                    self._conv_fused(plan, c2, ybf, C_, st_y, f"{prefix}.adain2.{it}", snake, 0.0,
+                                     self.w[f"{prefix}.alpha2.{it}"], h_all, B, L_, pad_left=(k - 1) // 2,
+                                     out_addr=self._addr(work), out_pitch=C_, res=res, out_stats=st_n)
+                    cur, cur_stats = work, st_n
+                else:
+                    self._conv_fused(plan, c2, ybf, C_, st_y, f"{prefix}.adain2.{it}", snake, 0.0,
+                                     self.w[f"{prefix}.alpha2.{it}"], h_all, B, L_, pad_left=(k - 1) // 2,
+                                     out_addr=final.get("out_addr"), out_pitch=final.get("out_pitch", C_), res=res,
+                                     res2=final.get("res2"), scale=final.get("scale", 1.0),
+                                     out_stats=final.get("stats_addr"), out_act=final.get("out_act"))
+            return
         for it in range(3):
             d = dils[it]
             c1 = self.convs[f"{prefix}.convs1.{it}"]

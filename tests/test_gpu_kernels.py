@@ -261,3 +261,99 @@ def test_conv1d_bf16_tc(lib, case):
     if not lib.kk_device_is_sm100():
         pytest.skip("needs sm_100")
     _conv_case(lib, True, **case)
+
+
+# ------------------------------------------------------------------ fused AdaIN + Snake + conv (tensor cores)
+def _fused_case(lib, B, Lin, Cch, k, dil, x_bf16=False, act="snake", with_res=True, with_norm=True, seed=0):
+    from mlx_audio_b200._lib import AdainIn
+    r = rng(300 + seed)
+    bf = torch.bfloat16
+    x = (r.standard_normal((B, Lin, Cch), dtype=np.float32) * 1.7 + 0.4).astype(np.float32)
+    if x_bf16:
+        x = torch.from_numpy(x).to(bf).float().numpy()
+    S_ = 2 * Cch
+    h = (r.standard_normal((B, 2 * S_), dtype=np.float32) * 0.3).astype(np.float32)   # rows wider than 2C: h_stride
+    alpha = r.uniform(0.5, 2.0, Cch).astype(np.float32)
+    wfold = r.standard_normal((Cch, k, Cch), dtype=np.float32) / math.sqrt(Cch * k)
+    bias = r.standard_normal(Cch, dtype=np.float32) * 0.1
+    padl = (k * dil - dil) // 2
+    # reference: AdaIN (population variance, eps 1e-5) -> activation -> bf16 operand rounding -> conv in float64
+    xd = torch.from_numpy(x).double()
+    if with_norm:
+        mean, var = xd.mean(1, keepdim=True), xd.var(1, unbiased=False, keepdim=True)
+        g = torch.from_numpy(h[:, None, :Cch]).double()
+        bt = torch.from_numpy(h[:, None, Cch:2 * Cch]).double()
+        y = (1 + g) * (xd - mean) / torch.sqrt(var + 1e-5) + bt
+    else:
+        y = xd
+    if act == "snake":
+        al = torch.from_numpy(alpha).double()
+        y = y + (1 / al) * torch.sin(al * y) ** 2
+    elif act == "leaky":
+        y = torch.where(y > 0, y, 0.2 * y)
+    a_ref = y.float()
+    aq = a_ref.to(bf).double()
+    wq = torch.from_numpy(wfold).to(bf).double()
+    out_ref = F.conv1d(aq.transpose(1, 2), wq.permute(0, 2, 1), torch.from_numpy(bias).double(), padding=padl,
+                       dilation=dil).transpose(1, 2).numpy()
+    res = r.standard_normal((B, Lin, Cch), dtype=np.float32) if with_res else None
+    scale = 0.5
+    ref = (out_ref + (res if with_res else 0.0)) * scale
+    # device
+    xdev = dev(x).to(bf).contiguous() if x_bf16 else dev(x)
+    stats = torch.stack([xd.sum(1), (xd * xd).sum(1)], -1).to("cuda").contiguous()      # (B, C, 2) float64
+    wp = torch.empty(Cch, k * Cch, dtype=bf, device="cuda")
+    L.check(lib.kk_pack_conv_weight(L.ptr(dev(wfold)), L.ptr(wp), 1, 0, Cch, k, Cch, 1, Cch, L.stream()))
+    out = torch.full((B, Lin, Cch), float("nan"), device="cuda")
+    oact = torch.zeros(B, Lin, Cch, dtype=bf, device="cuda")
+    ostats = torch.zeros(B, Cch, 2, dtype=torch.float64, device="cuda")
+    hd, ad, bd = dev(h), dev(alpha), dev(bias)
+    rd = dev(res) if with_res else None
+    a = AdainIn()
+    a.x, a.x_is_bf16, a.x_pitch = L.ptr(xdev), int(x_bf16), Cch
+    a.stats = L.ptr(stats) if with_norm else None
+    a.h, a.h_stride = L.ptr(hd), 2 * S_
+    a.alpha = L.ptr(ad)
+    a.act = {"snake": L.KK_ACT_SNAKE_FAST, "leaky": L.KK_ACT_LEAKY, "none": L.KK_ACT_NONE}[act]
+    a.slope = 0.2
+    d = ConvDesc()
+    d.B, d.L_in, d.C_in, d.x_pitch = B, Lin, Cch, Cch
+    d.taps, d.dil, d.pad_left, d.stride, d.Cw = k, dil, padl, 1, Cch
+    d.M, d.N, d.C_out, d.up, d.up_off = Lin, Cch, Cch, 1, 0
+    d.L_true, d.left_pad, d.L_out = Lin, 0, Lin
+    d.bias = L.ptr(bd)
+    if with_res:
+        d.res, d.res_pitch, d.res_shift, d.L_res = L.ptr(rd), Cch, 0, Lin
+    d.scale = scale
+    d.out, d.out_pitch, d.stats = L.ptr(out), Cch, L.ptr(ostats)
+    d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = L.ptr(oact), Cch, 1, 1.0
+    L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused")
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    # tolerance: the kernel's fp32 affine / MUFU sine may round an operand to the neighbouring bf16 value
+    err = np.abs(got - ref)
+    assert np.isfinite(got).all()
+    assert err.max() < 3e-2 and err.mean() < 2e-3, (err.max(), err.mean())
+    np.testing.assert_allclose(ostats[..., 0].cpu().numpy(), got.astype(np.float64).sum(1), rtol=1e-4, atol=1e-2)
+    np.testing.assert_allclose(ostats[..., 1].cpu().numpy(), (got.astype(np.float64) ** 2).sum(1), rtol=1e-4, atol=1e-2)
+    np.testing.assert_allclose(oact.float().cpu().numpy(), got, rtol=1e-2, atol=1e-2)
+
+
+FUSED_CASES = [
+    dict(B=2, Lin=700, Cch=128, k=11, dil=5),
+    dict(B=1, Lin=1000, Cch=128, k=3, dil=1, x_bf16=True),
+    dict(B=3, Lin=257, Cch=128, k=7, dil=3, with_res=False),
+    dict(B=2, Lin=300, Cch=256, k=11, dil=5),
+    dict(B=2, Lin=129, Cch=256, k=7, dil=1, x_bf16=True, with_res=False),
+    dict(B=1, Lin=40, Cch=256, k=3, dil=3),
+    dict(B=2, Lin=200, Cch=128, k=3, dil=1, act="leaky"),
+    dict(B=1, Lin=200, Cch=128, k=1, dil=1, act="none", with_norm=False),
+    dict(B=150, Lin=300, Cch=128, k=7, dil=1),     # > 148 tiles: persistent loop, utterance changes per CTA
+]
+
+
+@pytest.mark.parametrize("case", FUSED_CASES)
+def test_conv1d_adain_bf16_tc(lib, case):
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    _fused_case(lib, **case)
