@@ -16,6 +16,7 @@
 // Warp roles: 0 = TMA (weights), 1 = MMA issuer, 2..7 = transform (warp 2 owns the TMEM allocation),
 // 8..15 = epilogue.  Persistent: one CTA per SM walks the (utterance, row-tile) list.
 #include "tc_epilogue.cuh"
+#include <stdlib.h>
 
 namespace kk {
 
@@ -115,7 +116,7 @@ __device__ __forceinline__ void xf_block(const kk_adain_in& a, const float4* __r
 template <int MT, int BN, int CB>
 __global__ void __launch_bounds__(FU_THREADS, 1)
 conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const kk_conv_desc d, const kk_adain_in a,
-                       const int m_tiles, const int total_tiles) {
+                       const int m_tiles, const int total_tiles, const int flags) {
   using Cfg = FuCfg<MT, BN, CB>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -160,7 +161,28 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const kk_conv_de
     // ===================== TMA producer: weight slabs, order (tile, channel block, tap) =====================
     if (lane == 0) {
       uint32_t g = 0;
+      const size_t xesz = a.x_is_bf16 ? 2 : 4;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        // pull the NEXT tile's input rows and residual rows into L2 while this tile is being computed: the
+        // transform / epilogue warps' loads then see L2-hit latency instead of HBM latency
+        const int ntile = tile + gridDim.x;
+        if ((flags & 1) && ntile < total_tiles) {
+          const int nb_ = ntile / m_tiles, nm0 = (ntile - nb_ * m_tiles) * (128 * MT);
+          int l0 = nm0 - d.pad_left, l1 = l0 + R;
+          l0 = l0 < 0 ? 0 : l0;
+          l1 = l1 > d.L_in ? d.L_in : l1;
+          if (l1 > l0)
+            ptx::prefetch_l2_bulk(reinterpret_cast<const char*>(a.x) + ((size_t)nb_ * d.L_in + l0) * a.x_pitch * xesz,
+                                  (uint32_t)((size_t)(l1 - l0) * a.x_pitch * xesz));
+          int r1 = nm0 + 128 * MT;
+          r1 = r1 > d.M ? d.M : r1;
+          if (d.res && d.res_shift == 0)
+            ptx::prefetch_l2_bulk(d.res + ((size_t)nb_ * d.L_res + nm0) * d.res_pitch,
+                                  (uint32_t)((size_t)(r1 - nm0) * d.res_pitch * 4));
+          if (d.res2)
+            ptx::prefetch_l2_bulk(d.res2 + ((size_t)nb_ * d.L_out + nm0) * d.res2_pitch,
+                                  (uint32_t)((size_t)(r1 - nm0) * d.res2_pitch * 4));
+        }
         for (int cb = 0; cb < CB; ++cb) {
           for (int t = 0; t < d.taps; ++t, ++g) {
             const uint32_t s = g % Cfg::STAGES, ph = (g / Cfg::STAGES) & 1;
@@ -267,8 +289,16 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const kk_conv_de
     float* stage_w = staging + ew * 1024;
     const bool do_stats = d.stats != nullptr;
     uint32_t it = 0;
+    float4 tres[8];
+    if ((int)blockIdx.x < total_tiles) {
+      const int b0 = blockIdx.x / m_tiles;
+      epi_prefetch_chunk(d, b0, (blockIdx.x - b0 * m_tiles) * (128 * MT) + mt * 128, 0, chunk0, lg, lane, tres);
+    }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT);
+      const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128;
+      const int ntile = tile + gridDim.x;
+      const bool more = ntile < total_tiles;
+      const int nx_b = ntile / m_tiles, nx_m0 = (ntile - nx_b * m_tiles) * (128 * MT) + mt * 128;
       const uint32_t buf = it & 1, aph = (it >> 1) & 1;
       ptx::mbar_wait(&tmem_full[buf], aph);
       ptx::tc_fence_after();
@@ -277,7 +307,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const kk_conv_de
 #pragma unroll
       for (int c = 0; c < NCH; ++c) {
         ps[c] = pq[c] = 0.f;
-        epilogue_chunk<BN>(d, b, m0 + mt * 128, 0, chunk0 + c, lg, lane, tacc, stage_w, do_stats, ps[c], pq[c]);
+        const bool last = c + 1 == NCH;
+        epilogue_chunk<BN>(d, b, m0, 0, chunk0 + c, lg, lane, tacc, stage_w, do_stats, ps[c], pq[c], tres,
+                           last ? more : true, last ? nx_b : b, last ? nx_m0 : m0, 0, last ? chunk0 : chunk0 + c + 1);
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(&tmem_empty[buf]);     // all tcgen05.ld of this thread have completed
@@ -337,7 +369,8 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   const int grid = (int)(total < num_sms() ? total : num_sms());
-  conv1d_adain_tc_kernel<MT, BN, CB><<<grid, FU_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, *d, *a, m_tiles, (int)total);
+  static const int flags = getenv("KK_NO_L2PF") ? 0 : 1;   // experiment knob: disable the next-tile L2 prefetch
+  conv1d_adain_tc_kernel<MT, BN, CB><<<grid, FU_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, *d, *a, m_tiles, (int)total, flags);
   KK_LAUNCH_CHECK("conv1d_adain_tc_kernel");
   return KK_OK;
 }

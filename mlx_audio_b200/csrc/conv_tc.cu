@@ -103,16 +103,18 @@ conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int lg = warp & 3;                 // TMEM lane group this warp may access
-    ptx::mbar_wait(tmem_full_bar, 0);
-    ptx::tc_fence_after();
     const bool do_stats = d.stats != nullptr;
     // every MMA has completed (tmem_full), so the operand ring is idle: reuse it as epilogue staging
     float* stage_w = reinterpret_cast<float*>(smem) + lg * 1024;
+    float4 tres[8];
+    epi_prefetch_chunk(d, b, m0, n0, 0, lg, lane, tres);   // residual loads fly while the accumulator completes
+    ptx::mbar_wait(tmem_full_bar, 0);
+    ptx::tc_fence_after();
 #pragma unroll 1
-    for (int ch = 0; ch < BN / 32; ++ch)
-    {
+    for (int ch = 0; ch < BN / 32; ++ch) {
       float cs = 0.f, cq = 0.f;
-      epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base, stage_w, do_stats, cs, cq);
+      epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base, stage_w, do_stats, cs, cq, tres, ch + 1 < BN / 32, b, m0,
+                         n0, ch + 1);
       if (do_stats) { s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = cs; s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = cq; }
     }
     if (do_stats) {
@@ -255,24 +257,35 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
     float* stage_w = staging + ew * 1024;
     const bool do_stats = d.stats != nullptr;
     uint32_t it = 0;
+    const int ch_first = half * CH_PER;
+    const int n_mine = (CHUNKS - ch_first) < CH_PER ? (CHUNKS - ch_first) : CH_PER;   // chunks of this warp (may be <= 0)
+    float4 tres[8];
+    if (n_mine > 0 && (int)blockIdx.x < total_tiles) {
+      const int rest = blockIdx.x / n_tiles;
+      epi_prefetch_chunk(d, rest / m_tiles, (rest % m_tiles) * TC_BM, (blockIdx.x % n_tiles) * BN, ch_first, lg, lane, tres);
+    }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int nt = tile % n_tiles;
       const int rest = tile / n_tiles;
       const int mt = rest % m_tiles, b = rest / m_tiles;
       const int m0 = mt * TC_BM, n0 = nt * BN;
+      const int ntile = tile + gridDim.x;
+      const bool more = ntile < total_tiles;
+      const int nrest = ntile / n_tiles;
+      const int nx_b = nrest / m_tiles, nx_m0 = (nrest % m_tiles) * TC_BM, nx_n0 = (ntile % n_tiles) * BN;
       const uint32_t acc = it & 1, aph = (it >> 1) & 1;
       float* s_stats = s_stats_all + acc * (8 * BN);
       ptx::mbar_wait(&tmem_full_bar[acc], aph);
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < CH_PER; ++c) {
-        const int ch = half * CH_PER + c;
-        if (ch < CHUNKS)
-        {
-          float cs = 0.f, cq = 0.f;
-          epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, do_stats, cs, cq);
-          if (do_stats) { s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = cs; s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = cq; }
-        }
+      for (int c = 0; c < n_mine; ++c) {
+        const int ch = ch_first + c;
+        const bool last = c + 1 == n_mine;
+        float cs = 0.f, cq = 0.f;
+        epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, do_stats, cs, cq, tres,
+                           last ? more : true, last ? nx_b : b, last ? nx_m0 : m0, last ? nx_n0 : n0,
+                           last ? ch_first : ch + 1);
+        if (do_stats) { s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = cs; s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = cq; }
       }
       // all tcgen05.ld of this thread have completed (wait::ld inside the chunk): hand the accumulator back
       ptx::tc_fence_before();

@@ -80,6 +80,12 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* m, uin
       : "memory");
 }
 
+// Asynchronous L2 prefetch of a contiguous global range (16-byte aligned, size a multiple of 16): no registers, no
+// shared memory - turns the later demand loads of that range into L2 hits.
+__device__ __forceinline__ void prefetch_l2_bulk(const void* gptr, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gptr), "r"(bytes) : "memory");
+}
+
 // ---- tensor memory
 template <uint32_t COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem) {

@@ -6,22 +6,88 @@
 
 namespace kk {
 
+// Geometry of one 32-column chunk: first GEMM column, polyphase index, first output channel, and whether the
+// vectorised staging path applies (full chunk, 16-byte aligned rows everywhere).
+struct EpiGeom { int nb, ph, cbase; bool fast; };
+
+__device__ __forceinline__ EpiGeom epi_geom(const kk_conv_desc& d, const int n0, const int ch) {
+  EpiGeom g;
+  g.nb = n0 + ch * 32;
+  g.ph = 0; g.cbase = g.nb;
+  // phase is constant inside a 32-column chunk (host guarantees C_out % 32 == 0 when up > 1)
+  if (d.up > 1) { g.ph = g.nb / d.C_out; g.cbase = g.nb - g.ph * d.C_out; }
+  const size_t cb4 = (size_t)g.cbase * 4;
+  g.fast = (g.nb + 32 <= d.N) &&
+           (!d.out || (((reinterpret_cast<uintptr_t>(d.out) | (size_t)d.out_pitch * 4 | cb4) & 15) == 0)) &&
+           (!d.res || (((reinterpret_cast<uintptr_t>(d.res) | (size_t)d.res_pitch * 4 | cb4) & 15) == 0)) &&
+           (!d.res2 || (((reinterpret_cast<uintptr_t>(d.res2) | (size_t)d.res2_pitch * 4 | cb4) & 15) == 0)) &&
+           (!d.bias || (((reinterpret_cast<uintptr_t>(d.bias) | cb4) & 15) == 0)) &&
+           (!d.out_act || !d.act_is_bf16 ||
+            (((reinterpret_cast<uintptr_t>(d.out_act) | (size_t)d.act_pitch * 2 | (size_t)g.cbase * 2) & 15) == 0)) &&
+           (!d.out_act || d.act_is_bf16);
+  return g;
+}
+
+// Residual prefetch for one chunk of the warp whose first GEMM row is mw: lane (r = it*4 + lane/8, cc = lane%8)
+// loads 16 bytes of row r; t[] stays in flight while the previous chunk is being processed.
+__device__ __forceinline__ void epi_prefetch_res(const kk_conv_desc& d, const EpiGeom& g, const int b, const int mw,
+                                                 const int lane, float4 (&t)[8]) {
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int r = it * 4 + (lane >> 3), cc = lane & 7;
+    const int orr = (mw + r) * d.up + g.ph - d.up_off + d.left_pad;
+    t[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((mw + r) < d.M && orr >= 0 && orr < d.L_out) {
+      if (d.res) t[it] = __ldg(reinterpret_cast<const float4*>(
+                     d.res + ((size_t)b * d.L_res + (orr >> d.res_shift)) * d.res_pitch + g.cbase + cc * 4));
+      if (d.res2) {
+        const float4 u = __ldg(reinterpret_cast<const float4*>(
+            d.res2 + ((size_t)b * d.L_out + orr) * d.res2_pitch + g.cbase + cc * 4));
+        t[it].x += u.x; t[it].y += u.y; t[it].z += u.z; t[it].w += u.w;
+      }
+    }
+  }
+}
+
+// Issue the residual prefetch of chunk `ch` (first GEMM row of the tile m0, column origin n0) when that chunk will
+// take the fast path and has a residual.  Call it for the first chunk of a tile BEFORE waiting on the accumulator.
+__device__ __forceinline__ void epi_prefetch_chunk(const kk_conv_desc& d, const int b, const int m0, const int n0,
+                                                   const int ch, const int lg, const int lane, float4 (&t)[8]) {
+  if (!d.res && !d.res2) return;
+  const EpiGeom g = epi_geom(d, n0, ch);
+  if (g.fast) epi_prefetch_res(d, g, b, m0 + lg * 32, lane, t);
+}
+
 // One 32-column chunk of the epilogue for the warp that owns TMEM lane group `lg`: tensor memory -> registers
 // -> (bias, residuals, scale) -> coalesced global stores through the warp-private staging tile; returns the
 // per-column (sum, sum of squares) partials of the warp's 32 rows (lane i = column i of the chunk).
+// t[] holds this chunk's prefetched residual (epi_prefetch_chunk); once it has been parked in the staging tile
+// the prefetch of the NEXT chunk (has_next: tile origin (nx_m0, nx_n0) of utterance nx_b, chunk nx_ch) is issued so
+// that its latency hides behind this chunk's TMEM read, arithmetic and stores.
 template <int BN>
 __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int b, const int m0, const int n0,
                                                const int ch, const int lg, const int lane, const uint32_t tmem_base,
-                                               float* stage_w, const bool do_stats, float& col_sum, float& col_sq) {
+                                               float* stage_w, const bool do_stats, float& col_sum, float& col_sq,
+                                               float4 (&t)[8], const bool has_next, const int nx_b, const int nx_m0,
+                                               const int nx_n0, const int nx_ch) {
   const int m = m0 + lg * 32 + lane;  // GEMM row of this thread
   {
+      const EpiGeom g = epi_geom(d, n0, ch);
+      const int nb = g.nb, ph = g.ph, cbase = g.cbase;
+      const bool fast = g.fast;
+      float* st = stage_w;                       // [32 rows][8 chunks of 4 floats], chunk ^= row & 7
+      if (fast && (d.res || d.res2)) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int r = it * 4 + (lane >> 3), cc = lane & 7;
+          *reinterpret_cast<float4*>(st + r * 32 + ((cc ^ (r & 7)) << 2)) = t[it];
+        }
+        __syncwarp();
+      }
+      if (has_next) epi_prefetch_chunk(d, nx_b, nx_m0, nx_n0, nx_ch, lg, lane, t);
       float v[32];
       ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32), v);
       ptx::tmem_ld_wait();
-      const int nb = n0 + ch * 32;           // first GEMM column of this chunk
-      // phase is constant inside a 32-column chunk (host guarantees C_out % 32 == 0 when up > 1)
-      int ph = 0, cbase = nb;
-      if (d.up > 1) { ph = nb / d.C_out; cbase = nb - ph * d.C_out; }
       const int j = m * d.up + ph - d.up_off;
       const bool acc_valid = (j >= 0) && (j < d.L_true);
       const int out_row = j + d.left_pad;
@@ -32,52 +98,23 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
       // Fast path: full 32-column chunk, 16-byte aligned rows.  Global traffic goes through a warp-private
       // 32x32 fp32 staging tile (XOR-swizzled 16-byte chunks) so that every LDG/STG covers whole 128-byte
       // row segments (lane = column group) while TMEM hands out lane = row.
-      const bool fast = (nb + 32 <= d.N) &&
-                        (!d.out || (((reinterpret_cast<uintptr_t>(d.out) | (size_t)d.out_pitch * 4 | (size_t)cbase * 4) & 15) == 0)) &&
-                        (!d.res || (((reinterpret_cast<uintptr_t>(d.res) | (size_t)d.res_pitch * 4 | (size_t)cbase * 4) & 15) == 0)) &&
-                        (!d.res2 || (((reinterpret_cast<uintptr_t>(d.res2) | (size_t)d.res2_pitch * 4 | (size_t)cbase * 4) & 15) == 0)) &&
-                        (!d.out_act || !d.act_is_bf16 ||
-                         (((reinterpret_cast<uintptr_t>(d.out_act) | (size_t)d.act_pitch * 2 | (size_t)cbase * 2) & 15) == 0)) &&
-                        (!d.out_act || d.act_is_bf16);
       if (fast) {
-        float* st = stage_w;                       // [32 rows][8 chunks of 4 floats], chunk ^= row & 7
         const int mw = m0 + lg * 32;               // first GEMM row of this warp
-        if (d.res || d.res2) {
-#pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int r = it * 4 + (lane >> 3), cc = lane & 7;
-            const int jr = (mw + r) * d.up + ph - d.up_off;
-            const int orr = jr + d.left_pad;
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if ((mw + r) < d.M && orr >= 0 && orr < d.L_out) {
-              if (d.res) t = __ldg(reinterpret_cast<const float4*>(
-                             d.res + ((size_t)b * d.L_res + (orr >> d.res_shift)) * d.res_pitch + cbase + cc * 4));
-              if (d.res2) {
-                float4 u = __ldg(reinterpret_cast<const float4*>(
-                    d.res2 + ((size_t)b * d.L_out + orr) * d.res2_pitch + cbase + cc * 4));
-                t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w;
-              }
-            }
-            *reinterpret_cast<float4*>(st + r * 32 + ((cc ^ (r & 7)) << 2)) = t;
-          }
-          __syncwarp();
-        }
         {
-          float bsv[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) bsv[i] = d.bias ? __ldg(d.bias + cbase + i) : 0.f;
 #pragma unroll
           for (int c4 = 0; c4 < 8; ++c4) {
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (d.res || d.res2) t = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
-            float x0 = acc_valid ? v[c4 * 4 + 0] + bsv[c4 * 4 + 0] : 0.f;
-            float x1 = acc_valid ? v[c4 * 4 + 1] + bsv[c4 * 4 + 1] : 0.f;
-            float x2 = acc_valid ? v[c4 * 4 + 2] + bsv[c4 * 4 + 2] : 0.f;
-            float x3 = acc_valid ? v[c4 * 4 + 3] + bsv[c4 * 4 + 3] : 0.f;
-            x0 = row_ok ? (x0 + t.x) * d.scale : 0.f;
-            x1 = row_ok ? (x1 + t.y) * d.scale : 0.f;
-            x2 = row_ok ? (x2 + t.z) * d.scale : 0.f;
-            x3 = row_ok ? (x3 + t.w) * d.scale : 0.f;
+            float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (d.res || d.res2) rr = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
+            float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
+            float x0 = acc_valid ? v[c4 * 4 + 0] + bs.x : 0.f;
+            float x1 = acc_valid ? v[c4 * 4 + 1] + bs.y : 0.f;
+            float x2 = acc_valid ? v[c4 * 4 + 2] + bs.z : 0.f;
+            float x3 = acc_valid ? v[c4 * 4 + 3] + bs.w : 0.f;
+            x0 = row_ok ? (x0 + rr.x) * d.scale : 0.f;
+            x1 = row_ok ? (x1 + rr.y) * d.scale : 0.f;
+            x2 = row_ok ? (x2 + rr.z) * d.scale : 0.f;
+            x3 = row_ok ? (x3 + rr.w) * d.scale : 0.f;
             v[c4 * 4 + 0] = x0; v[c4 * 4 + 1] = x1; v[c4 * 4 + 2] = x2; v[c4 * 4 + 3] = x3;
           }
         }
@@ -171,7 +208,6 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
       if (do_stats) {
         // column sums over the warp's 32 rows, read back from the staging tile (lane i = column i; the XOR
         // swizzle keeps every row read conflict-free).  Rows / columns that were not stored hold 0.
-        float* st = stage_w;
         if (!fast) {
           __syncwarp();
 #pragma unroll
