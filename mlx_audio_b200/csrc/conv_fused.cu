@@ -1,0 +1,578 @@
+// Fused AdaIN + Snake/LeakyReLU + Conv1d on the 5th-gen tensor cores (sm_100a), TMA-fed end to end.
+//
+// Reference ops replaced (mlx_audio/tts/models/kokoro/istftnet.py): AdaINResBlock1's
+//   xt = adain(x, s); xt = x + (1/a) sin(a xt)^2; xt = conv(xt) [; x = xt + x]      (:379-395, AdaIN1d :327-338)
+// i.e. per reference call: instance-norm apply, style affine, Snake, swapaxes, conv, residual add - six
+// materialised tensors.  Here the raw tensor x (B, L, C) crosses HBM once per output tile:
+//   * an "X producer" thread streams tile + dilation-halo rows of one 64-channel block with TMA:
+//       - bf16 input: straight into the A-operand slot (128B swizzle), transformed IN PLACE;
+//       - fp32 input: through a ring of 32-row raw stages, transformed into the slot;
+//     (register loads cannot keep enough bytes in flight - profiles/r01_inflight_bw_probe.txt);
+//   * "transform" warps apply a_c x + b_c and the activation and leave bf16 in the canonical K-major
+//     128B-swizzle layout (row = 128 B, 16-byte chunk index XOR (row & 7));
+//   * one thread issues tcgen05.mma: for tap t the A operand is the SAME slot read through a descriptor whose
+//     start address is shifted by t*dil rows (the swizzle is a function of the absolute smem address, so a row
+//     shift that is not a multiple of the 8-row atom is legal - profiles/r01_umma_rowshift_probe.txt);
+//   * the weights (B operand) stream through a second TMA ring, one (channel-block, tap) slab per stage;
+//   * MT (1 or 2) 128-row sub-tiles share every B stage; accumulators are double-buffered in tensor memory
+//     (2 x MT x BN = 512 columns) so the epilogue of tile i overlaps the main loop of tile i+1;
+//   * epilogue warps own 32x32 fp32 staging tiles: the residual arrives in them by TMA (two tiles ahead), the
+//     result is written back in place and leaves by TMA store; instance-norm sums are read off the same tile
+//     and accumulated in fp64 registers across the CTA's contiguous run of tiles (one atomic flush per
+//     utterance change instead of one per tile).
+// Warp roles: 0 = TMA weights, 1 = MMA issuer, 2 = TMA input (+ TMEM allocation), 3 = spare, 4..7 = transform,
+// 8..15 = epilogue.  Persistent: CTA i walks a contiguous range of the (utterance, row-tile) list.
+#include "conv_epilogue.cuh"
+#include "ptx_sm100.cuh"
+#include <stdlib.h>
+
+namespace kk {
+
+constexpr int FV_XF_WARPS = 4;
+constexpr int FV_EPI_WARPS = 8;
+constexpr int FV_XF_THREADS = FV_XF_WARPS * 32;
+constexpr int FV_EPI_THREADS = FV_EPI_WARPS * 32;
+constexpr int FV_XF_WARP0 = 4;
+constexpr int FV_EPI_WARP0 = 8;
+constexpr int FV_THREADS = (FV_EPI_WARP0 + FV_EPI_WARPS) * 32;  // 512
+constexpr int FV_HALO_MAX = 56;
+constexpr int FV_BOX_ROWS = 32;            // rows per input TMA box
+constexpr int FV_RAW_BYTES = 32 * 256;     // fp32 raw stage: 32 rows x 64 channels
+constexpr int FV_XBOX_BYTES = 32 * 128;    // bf16 in-place box: 32 rows x 64 channels
+constexpr int FV_MAX_RAW = 8;
+
+template <int MT, int BN, int CB>
+struct FvCfg {
+  static constexpr int SLOT_ROWS = MT == 2 ? 320 : 192;          // >= 128*MT + halo, multiple of 32
+  static constexpr int SLOT_BYTES = SLOT_ROWS * 128;
+  static constexpr int NSLOT = MT == 2 ? 2 : 3;
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int STAGES = BN >= 256 ? 2 : 3;
+  static constexpr int STG_HALF = FV_EPI_WARPS * 4096;           // one 32x32 fp32 tile per epilogue warp
+  static constexpr int RAW_MIN = MT == 2 ? 3 : 2;                // raw stages when the residual needs both halves
+  static constexpr int COEF_BYTES = CB * 64 * 16;
+  static constexpr int OFF_B = NSLOT * SLOT_BYTES;
+  static constexpr int OFF_STG = OFF_B + STAGES * B_BYTES;       // [half 0][half 1][raw min] contiguous
+  static constexpr int OFF_RAW = OFF_STG + 2 * STG_HALF;
+  static constexpr int OFF_COEF = OFF_RAW + RAW_MIN * FV_RAW_BYTES;
+  static constexpr int OFF_BAR = OFF_COEF + COEF_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 512 + 1024;
+  static constexpr uint32_t TMEM_COLS = 512;
+  static_assert(SLOT_ROWS >= 128 * MT + FV_HALO_MAX && SLOT_ROWS % 32 == 0, "slot too small");
+  static_assert(2 * MT * BN <= 512, "accumulators exceed tensor memory");
+  static_assert(4 + RAW_MIN <= FV_MAX_RAW, "raw ring barrier array");
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget");
+};
+
+__device__ __forceinline__ uint32_t fv_pack(float lo, float hi) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+
+// coef = (a, b, alpha, 1/alpha)
+template <int ACT>
+__device__ __forceinline__ float fv_apply(float x, const float4& k, float slope) {
+  float y = fmaf(k.x, x, k.y);
+  if (ACT == KK_ACT_SNAKE) {
+    float t = __sinf(k.z * y);
+    y = fmaf(k.w, t * t, y);
+  } else if (ACT == KK_ACT_LEAKY) {
+    y = y > 0.f ? y : y * slope;
+  }
+  return y;
+}
+
+// bf16 input, in place: the slot holds rows [0, nrows) as TMA wrote them (128B swizzle).  Lane = (row%4, logical
+// 16-byte chunk q): 8 channels cb*64 + 8q.., coefficients in registers; physical chunk = q ^ (row & 7).
+template <int ACT>
+__device__ __forceinline__ void fv_xf_inplace(uint32_t slot, const float4* __restrict__ coef, float slope, int cb,
+                                              int nrows, int l_base, int L_in, int xw, int lane) {
+  const int q = lane & 7, sub = lane >> 3;
+  float4 k[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) k[i] = coef[cb * 64 + q * 8 + i];
+  const int nsteps = (nrows + 3) >> 2;
+#pragma unroll 2
+  for (int s = xw; s < nsteps; s += FV_XF_WARPS) {
+    const int r = 4 * s + sub;
+    const int l = l_base + r;
+    const uint32_t p = slot + (uint32_t)r * 128u + (uint32_t)((q ^ (r & 7)) << 4);
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);   // rows outside the utterance: the conv's zero padding (post-activation)
+    if (r < nrows && l >= 0 && l < L_in) {
+      uint4 t;
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(p));
+      o.x = fv_pack(fv_apply<ACT>(__uint_as_float(t.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(t.x & 0xffff0000u), k[1], slope));
+      o.y = fv_pack(fv_apply<ACT>(__uint_as_float(t.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(t.y & 0xffff0000u), k[3], slope));
+      o.z = fv_pack(fv_apply<ACT>(__uint_as_float(t.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(t.z & 0xffff0000u), k[5], slope));
+      o.w = fv_pack(fv_apply<ACT>(__uint_as_float(t.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(t.w & 0xffff0000u), k[7], slope));
+    }
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(p), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+  }
+}
+
+// fp32 input: one raw stage (32 rows x 64 channels, row-major 256 B) -> slot rows [row0, row0 + 32).
+// Lane = (row%2, 4-channel group q).
+template <int ACT>
+__device__ __forceinline__ void fv_xf_raw(uint32_t raw, uint32_t slot, const float4 (&k)[4], float slope, int row0,
+                                          int nrows, int l_base, int L_in, int xw, int lane) {
+  const int q = lane & 15, half = lane >> 4;
+  const uint32_t chunk = (uint32_t)(q >> 1), sub8 = (uint32_t)(q & 1) * 8u;
+#pragma unroll
+  for (int i = 0; i < 16 / FV_XF_WARPS; ++i) {
+    const int rr = 2 * (xw + FV_XF_WARPS * i) + half;
+    const int r = row0 + rr;
+    const int l = l_base + r;
+    uint2 o = make_uint2(0u, 0u);
+    if (r < nrows && l >= 0 && l < L_in) {
+      float4 v;
+      asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                   : "r"(raw + (uint32_t)(rr * 256 + q * 16)));
+      o.x = fv_pack(fv_apply<ACT>(v.x, k[0], slope), fv_apply<ACT>(v.y, k[1], slope));
+      o.y = fv_pack(fv_apply<ACT>(v.z, k[2], slope), fv_apply<ACT>(v.w, k[3], slope));
+    }
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(slot + (uint32_t)r * 128u + ((chunk ^ ((uint32_t)r & 7u)) << 4) + sub8),
+                 "r"(o.x), "r"(o.y) : "memory");
+  }
+}
+
+// contiguous share of the tile list for CTA `cta` of `ncta`
+__device__ __forceinline__ void fv_tile_range(int total, int cta, int ncta, int& start, int& count) {
+  const int base = total / ncta, rem = total - base * ncta;
+  count = base + (cta < rem ? 1 : 0);
+  start = cta * base + (cta < rem ? cta : rem);
+}
+
+template <int MT, int BN, int CB>
+__global__ void __launch_bounds__(FV_THREADS, 1)
+conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmX,
+                       const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
+                       const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles) {
+  using Cfg = FvCfg<MT, BN, CB>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sB = smem + Cfg::OFF_B;
+  float4* coef = reinterpret_cast<float4*>(smem + Cfg::OFF_COEF);
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);   // [3] slot transformed, MMA may read
+  uint64_t* a_empty = a_full + 3;                                        // [3] MMAs on the slot completed
+  uint64_t* x_full = a_empty + 3;                                        // [3] bf16 input landed in the slot
+  uint64_t* raw_full = x_full + 3;                                       // [FV_MAX_RAW]
+  uint64_t* raw_empty = raw_full + FV_MAX_RAW;                           // [FV_MAX_RAW]
+  uint64_t* b_full = raw_empty + FV_MAX_RAW;                             // [3]
+  uint64_t* b_empty = b_full + 3;                                        // [3]
+  uint64_t* tmem_full = b_empty + 3;                                     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;                                  // [2]
+  uint64_t* res_full = tmem_empty + 2;                                   // [FV_EPI_WARPS * 2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + FV_EPI_WARPS * 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int halo = (d.taps - 1) * d.dil;
+  const int R = 128 * MT + halo;                         // slot rows a tile needs
+  const int nbox = (R + FV_BOX_ROWS - 1) / FV_BOX_ROWS;  // 32-row TMA boxes per block
+  const bool has_res = d.res != nullptr;
+  // without a residual the second staging half is free: the fp32 raw ring grows over it
+  const int nraw = has_res ? Cfg::RAW_MIN : Cfg::RAW_MIN + 4;
+  uint8_t* sRaw = smem + (has_res ? Cfg::OFF_RAW : Cfg::OFF_STG + Cfg::STG_HALF);
+  int t_start, t_count;
+  fv_tile_range(total_tiles, blockIdx.x, gridDim.x, t_start, t_count);
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmB);
+    ptx::prefetch_tmap(&tmX);
+    if (has_res) ptx::prefetch_tmap(&tmRes);
+    if (d.out) ptx::prefetch_tmap(&tmOut);
+    for (int s = 0; s < 3; ++s) {
+      ptx::mbar_init(&a_full[s], FV_XF_THREADS);
+      ptx::mbar_init(&a_empty[s], 1);
+      ptx::mbar_init(&x_full[s], 1);
+      ptx::mbar_init(&b_full[s], 1);
+      ptx::mbar_init(&b_empty[s], 1);
+    }
+    for (int s = 0; s < FV_MAX_RAW; ++s) {
+      ptx::mbar_init(&raw_full[s], 1);
+      ptx::mbar_init(&raw_empty[s], FV_XF_THREADS);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tmem_full[i], 1);
+      ptx::mbar_init(&tmem_empty[i], FV_EPI_THREADS);
+    }
+    for (int i = 0; i < FV_EPI_WARPS * 2; ++i) ptx::mbar_init(&res_full[i], 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer: weight slabs, order (tile, channel block, tap) =====================
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int j = 0; j < t_count; ++j) {
+        for (int cb = 0; cb < CB; ++cb) {
+          for (int t = 0; t < d.taps; ++t, ++g) {
+            const uint32_t s = g % Cfg::STAGES, ph = (g / Cfg::STAGES) & 1;
+            ptx::mbar_wait(&b_empty[s], ph ^ 1);
+            ptx::mbar_expect_tx(&b_full[s], Cfg::B_BYTES);
+            ptx::tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &b_full[s], t * d.Cw + cb * 64, 0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, BN);
+      uint32_t gb = 0, ga = 0;
+      for (int j = 0; j < t_count; ++j) {
+        const uint32_t buf = j & 1, aph = (j >> 1) & 1;
+        ptx::mbar_wait(&tmem_empty[buf], aph ^ 1);   // epilogue has drained this accumulator set
+        ptx::tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * (MT * BN);
+        for (int cb = 0; cb < CB; ++cb, ++ga) {
+          const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
+          ptx::mbar_wait(&a_full[slot], sph);
+          ptx::tc_fence_after();
+          const uint32_t sa0 = ptx::smem_u32(smem + slot * Cfg::SLOT_BYTES);
+          for (int t = 0; t < d.taps; ++t, ++gb) {
+            const uint32_t s = gb % Cfg::STAGES, ph = (gb / Cfg::STAGES) & 1;
+            ptx::mbar_wait(&b_full[s], ph);
+            ptx::tc_fence_after();
+            const uint32_t sb = ptx::smem_u32(sB + s * Cfg::B_BYTES);
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+              const uint32_t sa = sa0 + (uint32_t)(mt * 128 + t * d.dil) * 128u;   // row-shifted view of the slot
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                ptx::umma_bf16(tacc + mt * BN, ad, bd, idesc, (cb | t | k) != 0 ? 1u : 0u);
+              }
+            }
+            ptx::umma_commit(&b_empty[s]);
+          }
+          ptx::umma_commit(&a_empty[slot]);
+        }
+        ptx::umma_commit(&tmem_full[buf]);
+      }
+    }
+  } else if (warp == 2) {
+    // ===================== TMA producer: input rows (tile + halo), one 64-channel block at a time ============
+    if (lane == 0) {
+      uint32_t ga = 0, gr = 0;
+      for (int j = 0; j < t_count; ++j) {
+        const int tile = t_start + j;
+        const int b = tile / m_tiles, l_base = (tile - b * m_tiles) * (128 * MT) - d.pad_left;
+        for (int cb = 0; cb < CB; ++cb, ++ga) {
+          const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
+          if (a.x_is_bf16) {
+            ptx::mbar_wait(&a_empty[slot], sph ^ 1);       // the MMAs that read this slot have completed
+            ptx::mbar_expect_tx(&x_full[slot], nbox * FV_XBOX_BYTES);
+            for (int i = 0; i < nbox; ++i)
+              ptx::tma_load_3d(smem + slot * Cfg::SLOT_BYTES + i * FV_XBOX_BYTES, &tmX, &x_full[slot], cb * 64,
+                               l_base + i * FV_BOX_ROWS, b);
+          } else {
+            for (int i = 0; i < nbox; ++i, ++gr) {
+              const uint32_t s = gr % nraw, ph = (gr / nraw) & 1;
+              ptx::mbar_wait(&raw_empty[s], ph ^ 1);
+              ptx::mbar_expect_tx(&raw_full[s], FV_RAW_BYTES);
+              ptx::tma_load_3d(sRaw + s * FV_RAW_BYTES, &tmX, &raw_full[s], cb * 64, l_base + i * FV_BOX_ROWS, b);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= FV_XF_WARP0 && warp < FV_XF_WARP0 + FV_XF_WARPS) {
+    // ===================== transform warps: x -> act(a x + b) -> bf16 swizzled slot =====================
+    const int xw = warp - FV_XF_WARP0;
+    const int xt = threadIdx.x - FV_XF_WARP0 * 32;
+    const bool snake = a.act == KK_ACT_SNAKE || a.act == KK_ACT_SNAKE_FAST;
+    int cur_b = -1;
+    uint32_t ga = 0, gr = 0;
+    for (int j = 0; j < t_count; ++j) {
+      const int tile = t_start + j;
+      const int b = tile / m_tiles, l_base = (tile - b * m_tiles) * (128 * MT) - d.pad_left;
+      if (b != cur_b) {
+        asm volatile("bar.sync 2, %0;" ::"n"(FV_XF_THREADS) : "memory");   // everyone is done with the old table
+        for (int c = xt; c < CB * 64; c += FV_XF_THREADS) {
+          float4 k = make_float4(1.f, 0.f, 1.f, 1.f);
+          if (a.stats) {
+            const double s = a.stats[((size_t)b * d.C_in + c) * 2], ss = a.stats[((size_t)b * d.C_in + c) * 2 + 1];
+            const double mean = s / d.L_in;
+            double var = ss / d.L_in - mean * mean;
+            if (var < 0.0) var = 0.0;
+            const float rstd = 1.0f / sqrtf((float)var + 1e-5f);
+            const float g1 = 1.0f + a.h[(size_t)b * a.h_stride + c];
+            k.x = g1 * rstd;
+            k.y = a.h[(size_t)b * a.h_stride + d.C_in + c] - k.x * (float)mean;
+          }
+          if (snake) { k.z = a.alpha[c]; k.w = 1.0f / k.z; }
+          coef[c] = k;
+        }
+        asm volatile("bar.sync 2, %0;" ::"n"(FV_XF_THREADS) : "memory");
+        cur_b = b;
+      }
+      for (int cb = 0; cb < CB; ++cb, ++ga) {
+        const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
+        const uint32_t sp = ptx::smem_u32(smem + slot * Cfg::SLOT_BYTES);
+        if (a.x_is_bf16) {
+          ptx::mbar_wait(&x_full[slot], sph);
+          if (snake) fv_xf_inplace<KK_ACT_SNAKE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
+          else if (a.act == KK_ACT_LEAKY) fv_xf_inplace<KK_ACT_LEAKY>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
+          else fv_xf_inplace<KK_ACT_NONE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
+        } else {
+          float4 k[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) k[i] = coef[cb * 64 + (lane & 15) * 4 + i];
+          ptx::mbar_wait(&a_empty[slot], sph ^ 1);     // the MMAs that read this slot have completed
+          for (int i = 0; i < nbox; ++i, ++gr) {
+            const uint32_t s = gr % nraw, ph = (gr / nraw) & 1;
+            ptx::mbar_wait(&raw_full[s], ph);
+            const uint32_t rp = ptx::smem_u32(sRaw + s * FV_RAW_BYTES);
+            if (snake) fv_xf_raw<KK_ACT_SNAKE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
+            else if (a.act == KK_ACT_LEAKY) fv_xf_raw<KK_ACT_LEAKY>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
+            else fv_xf_raw<KK_ACT_NONE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
+            ptx::mbar_arrive(&raw_empty[s]);           // this thread's reads of the stage are complete
+          }
+        }
+        ptx::fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core
+        ptx::mbar_arrive(&a_full[slot]);
+      }
+    }
+  } else if (warp >= FV_EPI_WARP0) {
+    // ===================== epilogue warps =====================
+    // Work item n = (tile j, chunk c) of this warp: 32 rows (TMEM lane group lg of sub-tile mt) x 32 columns.
+    const int ew = warp - FV_EPI_WARP0;
+    const int lg = warp & 3;                 // TMEM lane group this warp may access
+    const int half = ew >> 2;
+    const int mt = MT == 2 ? half : 0;
+    constexpr int NCH = MT == 2 ? BN / 32 : BN / 64;   // chunks per warp and tile
+    const int chunk0 = MT == 2 ? 0 : half * NCH;
+    uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // staging tile p at stg0 + p * STG_HALF (1024-aligned)
+    uint64_t* rbar = res_full + ew * 2;
+    const bool do_stats = d.stats != nullptr;
+    const bool out_aligned_act = d.out_act != nullptr;
+    const int n_items = t_count * NCH;
+
+    auto issue_res = [&](int n) {   // lane 0: TMA the residual tile of item n into staging buffer n & 1
+      if (n >= n_items) return;
+      const int tile = t_start + n / NCH, c = n % NCH;
+      const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128 + lg * 32;
+      ptx::mbar_expect_tx(&rbar[n & 1], 4096);
+      ptx::tma_load_3d(stg0 + (n & 1) * Cfg::STG_HALF, &tmRes, &rbar[n & 1], (chunk0 + c) * 32, m0, b);
+    };
+    if (has_res && lane == 0) { issue_res(0); issue_res(1); }
+
+    double acc_s[NCH], acc_q[NCH];   // fp64 running instance-norm sums of column `lane` of each chunk
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) acc_s[c] = acc_q[c] = 0.0;
+    int stat_b = -1;
+    auto flush_stats = [&](int b) {
+      if (b < 0) return;
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        const int col = (chunk0 + c) * 32 + lane;
+        atomicAdd(d.stats + ((size_t)b * d.C_out + col) * 2, acc_s[c]);
+        atomicAdd(d.stats + ((size_t)b * d.C_out + col) * 2 + 1, acc_q[c]);
+        acc_s[c] = acc_q[c] = 0.0;
+      }
+    };
+
+    for (int j = 0; j < t_count; ++j) {
+      const int tile = t_start + j;
+      const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128 + lg * 32;   // first row of the warp
+      if (do_stats && b != stat_b) { flush_stats(stat_b); stat_b = b; }
+      const uint32_t buf = j & 1, aph = (j >> 1) & 1;
+      ptx::mbar_wait(&tmem_full[buf], aph);
+      ptx::tc_fence_after();
+      const uint32_t tacc = tmem_base + buf * (MT * BN) + mt * BN + ((uint32_t)(lg * 32) << 16);
+      const int m = m0 + lane;
+      const bool row_ok = m < d.M;
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        const int n = j * NCH + c;
+        const int p = has_res ? (n & 1) : 0;
+        float* st = reinterpret_cast<float*>(stg0 + p * Cfg::STG_HALF);   // [32 rows][8 chunks of 4 floats], chunk ^= row & 7
+        const int cbase = (chunk0 + c) * 32;
+        float v[32];
+        ptx::tmem_ld_32x32(tacc + (uint32_t)cbase, v);
+        if (has_res) ptx::mbar_wait(&rbar[p], (uint32_t)(n >> 1) & 1);
+        else if (d.out) {
+          if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
+          __syncwarp();
+        }
+        ptx::tmem_ld_wait();
+        if (c == NCH - 1) {                              // last TMEM read of this tile: hand the accumulators back
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(&tmem_empty[buf]);
+        }
+#pragma unroll
+        for (int c4 = 0; c4 < 8; ++c4) {
+          float4* sp = reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
+          float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (has_res) rr = *sp;
+          if (d.res2 && row_ok) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(d.res2 + ((size_t)b * d.L_out + m) * d.res2_pitch + cbase + c4 * 4));
+            rr.x += u.x; rr.y += u.y; rr.z += u.z; rr.w += u.w;
+          }
+          float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
+          float4 o;
+          o.x = row_ok ? (v[c4 * 4 + 0] + bs.x + rr.x) * d.scale : 0.f;
+          o.y = row_ok ? (v[c4 * 4 + 1] + bs.y + rr.y) * d.scale : 0.f;
+          o.z = row_ok ? (v[c4 * 4 + 2] + bs.z + rr.z) * d.scale : 0.f;
+          o.w = row_ok ? (v[c4 * 4 + 3] + bs.w + rr.w) * d.scale : 0.f;
+          *sp = o;
+        }
+        if (d.out) ptx::fence_proxy_async();             // staging writes -> visible to the TMA store
+        __syncwarp();
+        if (d.out && lane == 0) {
+          ptx::tma_store_3d(&tmOut, st, cbase, m0, b);   // rows >= L_out are clipped by the tensor map
+          ptx::bulk_commit();
+        }
+        if (out_aligned_act) {
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + (lane >> 2), c8 = lane & 3;
+            if (m0 + r < d.M) {
+              const float4 t0 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8) ^ (r & 7)) << 2));
+              const float4 t1 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8 + 1) ^ (r & 7)) << 2));
+              uint4 q4;
+              q4.x = fv_pack(leaky(t0.x, d.act_slope), leaky(t0.y, d.act_slope));
+              q4.y = fv_pack(leaky(t0.z, d.act_slope), leaky(t0.w, d.act_slope));
+              q4.z = fv_pack(leaky(t1.x, d.act_slope), leaky(t1.y, d.act_slope));
+              q4.w = fv_pack(leaky(t1.z, d.act_slope), leaky(t1.w, d.act_slope));
+              *reinterpret_cast<uint4*>((__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + m0 + r) * d.act_pitch + cbase + c8 * 8) = q4;
+            }
+          }
+        }
+        if (do_stats) {
+          // column sums over the warp's 32 rows (lane i = column i; the swizzle keeps every read conflict-free)
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+          const int cc = lane >> 2, ci = lane & 3;
+#pragma unroll
+          for (int r = 0; r < 32; r += 2) {
+            const float a0 = st[r * 32 + ((cc ^ (r & 7)) << 2) + ci];
+            const float a1 = st[(r + 1) * 32 + ((cc ^ ((r + 1) & 7)) << 2) + ci];
+            s0 += a0; q0 = fmaf(a0, a0, q0);
+            s1 += a1; q1 = fmaf(a1, a1, q1);
+          }
+          acc_s[c] += (double)(s0 + s1);
+          acc_q[c] += (double)(q0 + q1);
+        }
+        __syncwarp();                                    // everyone is done reading this staging tile
+        if (has_res && lane == 0) {
+          if (d.out) ptx::bulk_wait_read<0>();           // ... and so is the TMA store
+          issue_res(n + 2);
+        }
+      }
+    }
+    if (do_stats) flush_stats(stat_b);
+    if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) ptx::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+}  // namespace kk
+
+// ================================================================== host side
+namespace kk {
+
+int validate_conv_desc(const kk_conv_desc* d, const char* who);                            // conv_f32.cu
+int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank, const cuuint64_t* dims,
+              const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle swz);   // conv_tc.cu
+int num_sms();                                                                             // conv_tc.cu
+
+template <int MT, int BN, int CB>
+static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc* d, cudaStream_t st) {
+  using Cfg = FvCfg<MT, BN, CB>;
+  CUtensorMap tmB, tmX, tmRes, tmOut;
+  int rc;
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
+    cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * 2};
+    cuuint32_t box[2] = {64, BN};
+    if ((rc = make_tmap(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, w, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  }
+  {
+    const cuuint64_t esz = a->x_is_bf16 ? 2 : 4;
+    cuuint64_t dims[3] = {(cuuint64_t)d->C_in, (cuuint64_t)d->L_in, (cuuint64_t)d->B};
+    cuuint64_t strides[2] = {(cuuint64_t)a->x_pitch * esz, (cuuint64_t)d->L_in * a->x_pitch * esz};
+    cuuint32_t box[3] = {64, FV_BOX_ROWS, 1};
+    rc = a->x_is_bf16
+             ? make_tmap(&tmX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, a->x, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)
+             : make_tmap(&tmX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, a->x, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+  }
+  tmRes = tmB;
+  tmOut = tmB;
+  if (d->res) {
+    cuuint64_t dims[3] = {(cuuint64_t)d->C_out, (cuuint64_t)d->L_res, (cuuint64_t)d->B};
+    cuuint64_t strides[2] = {(cuuint64_t)d->res_pitch * 4, (cuuint64_t)d->L_res * d->res_pitch * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    if ((rc = make_tmap(&tmRes, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->res, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  }
+  if (d->out) {
+    cuuint64_t dims[3] = {(cuuint64_t)d->C_out, (cuuint64_t)d->L_out, (cuuint64_t)d->B};
+    cuuint64_t strides[2] = {(cuuint64_t)d->out_pitch * 4, (cuuint64_t)d->L_out * d->out_pitch * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    if ((rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->out, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    KK_CUDA(cudaFuncSetAttribute(conv1d_adain_tc_kernel<MT, BN, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 Cfg::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int m_tiles = cdiv(d->M, 128 * MT);
+  const long long total = (long long)m_tiles * d->B;
+  KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
+  const int grid = (int)(total < num_sms() ? total : num_sms());
+  conv1d_adain_tc_kernel<MT, BN, CB><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, *d, *a, m_tiles,
+                                                                              (int)total);
+  KK_LAUNCH_CHECK("conv1d_adain_tc_kernel");
+  return KK_OK;
+}
+
+}  // namespace kk
+
+extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, const kk_conv_desc* d, void* stream) {
+  KK_CHECK_ARG(a && a->x && w, "kk_conv1d_adain_bf16_tc: null tensor");
+  int rc = kk::validate_conv_desc(d, "kk_conv1d_adain_bf16_tc");
+  if (rc) return rc;
+  if (!kk_device_is_sm100()) {
+    kk::set_error("kk_conv1d_adain_bf16_tc: needs an sm_100 (Blackwell) device");
+    return KK_ERR_UNSUPPORTED;
+  }
+  KK_CHECK_ARG(d->stride == 1 && d->up == 1 && d->up_off == 0 && d->left_pad == 0,
+               "kk_conv1d_adain_bf16_tc: plain stride-1 convolutions only");
+  KK_CHECK_ARG(d->M == d->L_true && d->M == d->L_out, "kk_conv1d_adain_bf16_tc: M must equal L_true and L_out");
+  KK_CHECK_ARG(d->x_pitch == a->x_pitch, "kk_conv1d_adain_bf16_tc: x_pitch mismatch between the descriptors");
+  KK_CHECK_ARG((d->taps - 1) * d->dil <= kk::FV_HALO_MAX, "kk_conv1d_adain_bf16_tc: (taps-1)*dil = %d exceeds %d",
+               (d->taps - 1) * d->dil, kk::FV_HALO_MAX);
+  KK_CHECK_ARG(d->Cw == d->C_in, "kk_conv1d_adain_bf16_tc: Cw (%d) must equal C_in (%d)", d->Cw, d->C_in);
+  const int xesz = a->x_is_bf16 ? 2 : 4;
+  KK_CHECK_ARG((a->x_pitch * xesz) % 16 == 0 && ((uintptr_t)a->x & 15) == 0 && ((uintptr_t)w & 15) == 0,
+               "kk_conv1d_adain_bf16_tc: x and w must be 16-byte aligned with 16-byte row pitch");
+  KK_CHECK_ARG(!d->out || (((uintptr_t)d->out & 15) == 0 && d->out_pitch % 4 == 0),
+               "kk_conv1d_adain_bf16_tc: out must be 16-byte aligned with a pitch multiple of 4");
+  KK_CHECK_ARG(!d->res || (((uintptr_t)d->res & 15) == 0 && d->res_pitch % 4 == 0 && d->res_shift == 0 &&
+                           d->L_res == d->L_out),
+               "kk_conv1d_adain_bf16_tc: residual must be 16-byte aligned, same length as the output, no shift");
+  KK_CHECK_ARG(!d->res2 || (((uintptr_t)d->res2 & 15) == 0 && d->res2_pitch % 4 == 0),
+               "kk_conv1d_adain_bf16_tc: second residual must be 16-byte aligned with a pitch multiple of 4");
+  KK_CHECK_ARG(!d->bias || ((uintptr_t)d->bias & 15) == 0, "kk_conv1d_adain_bf16_tc: bias must be 16-byte aligned");
+  KK_CHECK_ARG(!d->out_act || (d->act_is_bf16 && ((uintptr_t)d->out_act & 15) == 0 && d->act_pitch % 8 == 0),
+               "kk_conv1d_adain_bf16_tc: out_act must be bf16, 16-byte aligned, pitch multiple of 8");
+  KK_CHECK_ARG(a->act >= KK_ACT_NONE && a->act <= KK_ACT_SNAKE_FAST, "kk_conv1d_adain_bf16_tc: act=%d", a->act);
+  KK_CHECK_ARG((a->act != KK_ACT_SNAKE && a->act != KK_ACT_SNAKE_FAST) || a->alpha,
+               "kk_conv1d_adain_bf16_tc: snake needs alpha");
+  KK_CHECK_ARG(!a->stats || a->h, "kk_conv1d_adain_bf16_tc: normalisation needs the style projection h");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->C_in == 128 && d->N == 128) return kk::launch_fused<2, 128, 2>(a, w, d, st);
+  if (d->C_in == 256 && d->N == 256) return kk::launch_fused<1, 256, 4>(a, w, d, st);
+  kk::set_error("kk_conv1d_adain_bf16_tc: unsupported shape C_in=%d N=%d (128->128 and 256->256 only)", d->C_in, d->N);
+  return KK_ERR_UNSUPPORTED;
+}
