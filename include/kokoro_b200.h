@@ -131,6 +131,11 @@ int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed,
                    const float* lin_b, float* phase_ws, float* har_source, int B, int T2, int upsample,
                    void* stream);
 int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream);
+/* Same transform, additionally (or only, har == NULL) written as bf16 into (B, bf_rows, bf_pitch) with
+ * bf_rows >= 120T+1: the tensor-core noise_convs (istftnet.py:778) read it as (B, bf_rows/6, 6*bf_pitch) rows
+ * of six frames (stride-6 conv) or as is (1x1 conv).  Rows >= 120T+1 are not touched (caller keeps them zero). */
+int kk_stft_n20_bf16(const float* har_source, float* har, int har_pitch, void* har_bf16, int bf_pitch, int bf_rows,
+                     int B, int S, void* stream);
 
 /* ---- iSTFT head (Generator tail istftnet.py:804-806, MLXSTFT.inverse :497-523, utils.istft :104-158):
  * y (B, F, y_pitch) conv_post output -> spec=exp(y[:11]), phase=sin(y[11:]) -> irfft(20) * periodic hann,

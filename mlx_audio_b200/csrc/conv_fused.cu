@@ -181,7 +181,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (has_res) ptx::prefetch_tmap(&tmRes);
     if (d.out) ptx::prefetch_tmap(&tmOut);
     for (int s = 0; s < 3; ++s) {
-      ptx::mbar_init(&a_full[s], FV_XF_THREADS);
+      ptx::mbar_init(&a_full[s], FV_XF_WARPS);
       ptx::mbar_init(&a_empty[s], 1);
       ptx::mbar_init(&x_full[s], 1);
       ptx::mbar_init(&b_full[s], 1);
@@ -189,11 +189,11 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     }
     for (int s = 0; s < FV_MAX_RAW; ++s) {
       ptx::mbar_init(&raw_full[s], 1);
-      ptx::mbar_init(&raw_empty[s], FV_XF_THREADS);
+      ptx::mbar_init(&raw_empty[s], FV_XF_WARPS);
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tmem_full[i], 1);
-      ptx::mbar_init(&tmem_empty[i], FV_EPI_THREADS);
+      ptx::mbar_init(&tmem_empty[i], FV_EPI_WARPS);
     }
     for (int i = 0; i < FV_EPI_WARPS * 2; ++i) ptx::mbar_init(&res_full[i], 1);
     ptx::fence_barrier_init();
@@ -332,11 +332,13 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             if (snake) fv_xf_raw<KK_ACT_SNAKE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
             else if (a.act == KK_ACT_LEAKY) fv_xf_raw<KK_ACT_LEAKY>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
             else fv_xf_raw<KK_ACT_NONE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
-            ptx::mbar_arrive(&raw_empty[s]);           // this thread's reads of the stage are complete
+            __syncwarp();                              // the warp's reads of the stage are complete
+            if (lane == 0) ptx::mbar_arrive(&raw_empty[s]);
           }
         }
         ptx::fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core
-        ptx::mbar_arrive(&a_full[slot]);
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&a_full[slot]);
       }
     }
   } else if (warp >= FV_EPI_WARP0) {
@@ -404,7 +406,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         ptx::tmem_ld_wait();
         if (c == NCH - 1) {                              // last TMEM read of this tile: hand the accumulators back
           ptx::tc_fence_before();
-          ptx::mbar_arrive(&tmem_empty[buf]);
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
         }
 #pragma unroll
         for (int c4 = 0; c4 < 8; ++c4) {

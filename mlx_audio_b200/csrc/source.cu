@@ -109,8 +109,9 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
 // ---- STFT n_fft=20, hop=5, symmetric Hann, reflect pad 10, direct 20 -> 11 real DFT per frame.
 struct Dft20Tables { float win[20]; float cs[20]; float sn[20]; };
 
-__global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_pitch, int B, int S,
-                                int F, const Dft20Tables tb) {
+__global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_pitch,
+                                __nv_bfloat16* __restrict__ har16, int pitch16, int rows16, int B, int S, int F,
+                                const Dft20Tables tb) {
   long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * F) return;
   int b = (int)(idx / F);
@@ -124,7 +125,8 @@ __global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict
     if (p >= S) p = 2 * (S - 1) - p;
     v[n] = x[p] * tb.win[n];
   }
-  float* o = har + (size_t)idx * har_pitch;
+  float* o = har ? har + (size_t)idx * har_pitch : nullptr;
+  __nv_bfloat16* o16 = har16 ? har16 + ((size_t)b * rows16 + f) * pitch16 : nullptr;
 #pragma unroll
   for (int k = 0; k <= 10; ++k) {
     float re = 0.f, im = 0.f;
@@ -135,10 +137,13 @@ __global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict
       im = fmaf(-v[n], tb.sn[j], im);
     }
     if (k == 0 || k == 10) im = 0.0f;        // r2c: DC / Nyquist imaginary parts are +0
-    o[k] = sqrtf(re * re + im * im);          // mx.abs      istftnet.py:484
-    o[11 + k] = atan2f(im, re);               // mlx_angle   istftnet.py:409
+    const float mag = sqrtf(re * re + im * im);   // mx.abs      istftnet.py:484
+    const float ang = atan2f(im, re);             // mlx_angle   istftnet.py:409
+    if (o) { o[k] = mag; o[11 + k] = ang; }
+    if (o16) { o16[k] = __float2bfloat16(mag); o16[11 + k] = __float2bfloat16(ang); }
   }
-  for (int c = 22; c < har_pitch; ++c) o[c] = 0.f;
+  if (o) for (int c = 22; c < har_pitch; ++c) o[c] = 0.f;
+  if (o16) for (int c = 22; c < pitch16; ++c) o16[c] = __float2bfloat16(0.f);
 }
 
 }  // namespace kk
@@ -162,8 +167,8 @@ extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long
   return KK_OK;
 }
 
-extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream) {
-  KK_CHECK_ARG(har_source && har && B > 0 && S > 10 && har_pitch >= 22 && S % 5 == 0, "kk_stft_n20: bad arguments");
+static int stft_n20_launch(const float* har_source, float* har, int har_pitch, void* har16, int pitch16, int rows16,
+                           int B, int S, void* stream) {
   kk::Dft20Tables tb;
   for (int n = 0; n < 20; ++n) {
     tb.win[n] = (float)(0.5 * (1.0 - cos(2.0 * M_PI * n / 19.0)));  // symmetric hanning(20) utils.py:11-14
@@ -172,7 +177,21 @@ extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, i
   }
   int F = S / 5 + 1;
   long long total = (long long)B * F;
-  kk::stft_n20_kernel<<<kk::cdiv(total, 128), 128, 0, (cudaStream_t)stream>>>(har_source, har, har_pitch, B, S, F, tb);
+  kk::stft_n20_kernel<<<kk::cdiv(total, 128), 128, 0, (cudaStream_t)stream>>>(
+      har_source, har, har_pitch, (__nv_bfloat16*)har16, pitch16, rows16, B, S, F, tb);
   KK_LAUNCH_CHECK("stft_n20_kernel");
   return KK_OK;
+}
+
+extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream) {
+  KK_CHECK_ARG(har_source && har && B > 0 && S > 10 && har_pitch >= 22 && S % 5 == 0, "kk_stft_n20: bad arguments");
+  return stft_n20_launch(har_source, har, har_pitch, nullptr, 0, 0, B, S, stream);
+}
+
+extern "C" int kk_stft_n20_bf16(const float* har_source, float* har, int har_pitch, void* har_bf16, int bf_pitch,
+                                int bf_rows, int B, int S, void* stream) {
+  KK_CHECK_ARG(har_source && har_bf16 && B > 0 && S > 10 && S % 5 == 0, "kk_stft_n20_bf16: bad arguments");
+  KK_CHECK_ARG((!har || har_pitch >= 22) && bf_pitch >= 22 && bf_rows >= S / 5 + 1,
+               "kk_stft_n20_bf16: pitch / rows too small (bf_rows %d < frames %d)", bf_rows, S / 5 + 1);
+  return stft_n20_launch(har_source, har, har_pitch, har_bf16, bf_pitch, bf_rows, B, S, stream);
 }

@@ -195,9 +195,30 @@ class DecoderEngine:
         for i, u in enumerate(cfg["upsample_rates"]):
             assert cfg["upsample_kernel_sizes"][i] == 2 * u, "polyphase path needs kernel == 2*stride"
             self._prep_wn(f"{g}.ups.{i}", up=u)
-            self.convs[f"{g}.noise_convs.{i}"] = PreparedConv(
-                f"{g}.noise_convs.{i}", w[f"{g}.noise_convs.{i}.weight"].contiguous(), w[f"{g}.noise_convs.{i}.bias"],
-                need_bf16=False, need_f32=True)
+            nw, nbias = w[f"{g}.noise_convs.{i}.weight"].contiguous(), w[f"{g}.noise_convs.{i}.bias"]
+            self.convs[f"{g}.noise_convs.{i}"] = PreparedConv(f"{g}.noise_convs.{i}", nw, nbias, need_bf16=False,
+                                                              need_f32=not self.tc)
+            if self.tc:
+                # tensor-core form over the bf16 `har` tensor (B, rows, 24): a stride-s conv with kernel 2s and
+                # padding p becomes a 3-tap stride-1 conv over rows of s frames (s*24 channels):
+                #   frame = s*(m-1+t') + j  <->  tap t = s*t' + j - s + p   (zero weight when t is out of range)
+                O, K, I = nw.shape
+                s_ = int(math.prod(cfg["upsample_rates"][i + 1:]))
+                if K == 1:
+                    v = torch.zeros(O, 1, 24, device=nw.device)
+                    v[:, 0, :I] = nw[:, 0]
+                else:
+                    assert K == 2 * s_, "tensor-core noise conv needs kernel == 2*stride"
+                    p_ = (s_ + 1) // 2
+                    v = torch.zeros(O, 3, s_, 24, device=nw.device)
+                    for tp in range(3):
+                        for j in range(s_):
+                            t = s_ * tp + j - s_ + p_
+                            if 0 <= t < K:
+                                v[:, tp, j, :I] = nw[:, t]
+                    v = v.reshape(O, 3, s_ * 24)
+                self.convs[f"{g}.noise_convs.{i}.tc"] = PreparedConv(f"{g}.noise_convs.{i}.tc", v.contiguous(), nbias,
+                                                                     need_bf16=True, need_f32=False)
             for blk in [f"{g}.noise_res.{i}"] + [f"{g}.resblocks.{i * n_k + j}" for j in range(n_k)]:
                 for it in range(3):
                     self._prep_wn(f"{blk}.convs1.{it}")
@@ -479,7 +500,14 @@ class DecoderEngine:
         plan.source_op_index = len(plan.ops)
         plan.add(lib.kk_hnsf_source, self._addr(f0c), None, 0, self._addr(self.lin_w), self._addr(self.lin_b),
                  self._addr(phase_ws), self._addr(har_source), B, T2, up, launches=2)
-        plan.add(lib.kk_stft_n20, self._addr(har_source), self._addr(har), 24, B, S)
+        har16 = None
+        har_rows = r1 * (L20 + 1)       # rows of the bf16 copy: whole 6-frame rows for the stride-6 noise conv
+        if self.tc:
+            har16 = self._buf(plan, "har16", (B, har_rows, 24), torch.bfloat16, zero=True)
+            plan.add(lib.kk_stft_n20_bf16, self._addr(har_source), self._addr(har), 24, self._addr(har16), 24, har_rows,
+                     B, S)
+        else:
+            plan.add(lib.kk_stft_n20, self._addr(har_source), self._addr(har), 24, B, S)
         self._tap(plan, "har_source", har_source)
         self._tap(plan, "har", har, lambda t: t[:, :, :22].transpose(1, 2))
         # ---- generator stages (:776-796)
@@ -493,7 +521,15 @@ class DecoderEngine:
             nconv = self.convs[f"{g}.noise_convs.{i}"]
             xs = self._buf(plan, f"g{i}.xs", (B, Li, Ci))
             st_xs = self._stats(plan, B, Ci)
-            if i == 0:
+            if self.tc:
+                ntc = self.convs[f"{g}.noise_convs.{i}.tc"]
+                if i == 0:   # (B, L20+1 rows of r1 frames, r1*24 channels), 3 taps, left pad 1
+                    self._conv(plan, ntc, self._addr(har16), B, L20 + 1, r1 * 24, Li, pad_left=1,
+                               out_addr=self._addr(xs), out_pitch=Ci, stats_addr=st_xs)
+                else:        # 1x1 over the frames; rows >= L3 of har16 are never read (M = L3)
+                    self._conv(plan, ntc, self._addr(har16), B, har_rows, 24, Li, out_addr=self._addr(xs),
+                               out_pitch=Ci, stats_addr=st_xs)
+            elif i == 0:
                 stride_f0 = r1
                 self._conv(plan, nconv, self._addr(har), B, L3, 24, Li, stride=stride_f0, pad_left=(stride_f0 + 1) // 2,
                            out_addr=self._addr(xs), out_pitch=Ci, stats_addr=st_xs, force_f32=True)
@@ -501,8 +537,9 @@ class DecoderEngine:
                 self._conv(plan, nconv, self._addr(har), B, L3, 24, Li, out_addr=self._addr(xs), out_pitch=Ci,
                            stats_addr=st_xs, force_f32=True)
             self._tap(plan, f"noise_conv{i}", xs, lambda t: t.transpose(1, 2))
-            act = self._buf(plan, f"g{i}.act", (B, Li, ap), adt, zero=True)
-            y = self._buf(plan, f"g{i}.y", (B, Li, Ci))
+            fused_i = self.fused and Ci in (128, 256)
+            act = None if fused_i else self._buf(plan, f"g{i}.act", (B, Li, ap), adt, zero=True)
+            y = None if fused_i else self._buf(plan, f"g{i}.y", (B, Li, Ci))
             self._adain_resblock1(plan, f"{g}.noise_res.{i}", B, Li, Ci, 7 if i == 0 else 11, (1, 3, 5), h_all, xs,
                                   st_xs, xs, act, y, dict(out_addr=self._addr(xs), out_pitch=Ci))
             self._tap(plan, f"noise_res{i}", xs, lambda t: t.transpose(1, 2))
