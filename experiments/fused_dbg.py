@@ -1,0 +1,55 @@
+"""Debug driver: where does conv1d_adain_tc_kernel wait?  Runs single fused convs at bench size on a
+-DKK_FUSED_DBG build (experiments/build_dbg.sh) and prints per-role barrier wait time as a share of kernel time."""
+import ctypes as C, os, sys
+import numpy as np, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from mlx_audio_b200 import _lib as L
+L.LIB_PATH = os.path.join(ROOT, "experiments", "libkokoro_b200_dbg.so")
+from mlx_audio_b200._lib import AdainIn, ConvDesc
+lib = L.load()
+lib.kk_debug_fused_buffer.argtypes = [C.c_void_p]; lib.kk_debug_fused_buffer.restype = C.c_int
+NAMES = ["Bprod:b_empty", "MMA:tmem_empty", "MMA:a_full", "MMA:b_full", "Xprod:empty", "XF:data", "XF:slot_empty",
+         "EPI:tmem_full", "EPI:res_full", "-", "MMA:total"]
+
+def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
+    dev = "cuda"
+    x = torch.randn(B, Lr, Cc, device=dev)
+    xd = x.to(torch.bfloat16).contiguous() if x_bf16 else x
+    stats = torch.stack([x.double().sum(1), (x.double() ** 2).sum(1)], -1).contiguous()
+    h = torch.randn(B, 2 * Cc, device=dev) * 0.1
+    alpha = torch.rand(Cc, device=dev) + 0.5
+    w = (torch.randn(Cc, k * Cc, device=dev) / (Cc * k) ** 0.5).to(torch.bfloat16)
+    bias = torch.zeros(Cc, device=dev)
+    res = torch.randn(B, Lr, Cc, device=dev) if with_res else None
+    out = torch.empty(B, Lr, Cc, device=dev) if with_out else None
+    oact = None if with_out else torch.empty(B, Lr, Cc, device=dev, dtype=torch.bfloat16)
+    ostats = torch.zeros(B, Cc, 2, dtype=torch.float64, device=dev)
+    dbg = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
+    L.check(lib.kk_debug_fused_buffer(dbg.data_ptr()))
+    a = AdainIn(); a.x, a.x_is_bf16, a.x_pitch = xd.data_ptr(), int(x_bf16), Cc
+    a.stats, a.h, a.h_stride, a.alpha, a.act, a.slope = stats.data_ptr(), h.data_ptr(), 2 * Cc, alpha.data_ptr(), 3, 0.0
+    d = ConvDesc(); d.B, d.L_in, d.C_in, d.x_pitch = B, Lr, Cc, Cc
+    d.taps, d.dil, d.pad_left, d.stride, d.Cw = k, dil, (k * dil - dil) // 2, 1, Cc
+    d.M, d.N, d.C_out, d.up, d.up_off, d.L_true, d.left_pad, d.L_out = Lr, Cc, Cc, 1, 0, Lr, 0, Lr
+    d.bias = bias.data_ptr()
+    if with_res: d.res, d.res_pitch, d.res_shift, d.L_res = res.data_ptr(), Cc, 0, Lr
+    d.scale = 1.0
+    if with_out: d.out, d.out_pitch = out.data_ptr(), Cc
+    else: d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = oact.data_ptr(), Cc, 1, 1.0
+    d.stats = ostats.data_ptr()
+    for _ in range(2):
+        L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), w.data_ptr(), C.byref(d), L.stream()))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), w.data_ptr(), C.byref(d), L.stream())); e1.record()
+    torch.cuda.synchronize()
+    v = dbg.view(148, 16).double().mean(0).cpu().numpy()
+    tot = v[10]
+    print(f"C={Cc} k={k} d={dil} x_bf16={x_bf16} res={with_res} out={'f32' if with_out else 'bf16'}: {e0.elapsed_time(e1):.3f} ms; "
+          + "  ".join(f"{n}={v[i] / tot * 100:.0f}%" for i, n in enumerate(NAMES) if n != "-" and i != 10))
+
+for k in (3, 11):
+    run(64, 38401, 128, k, 1, False, False, False)   # conv1-type
+    run(64, 38401, 128, k, 1, True, True, True)      # conv2-type
+run(64, 6400, 256, 7, 1, False, False, False)
+run(64, 6400, 256, 7, 1, True, True, True)

@@ -45,22 +45,22 @@ template <int MT, int BN, int CB>
 struct FvCfg {
   static constexpr int SLOT_ROWS = MT == 2 ? 320 : 192;          // >= 128*MT + halo, multiple of 32
   static constexpr int SLOT_BYTES = SLOT_ROWS * 128;
-  static constexpr int NSLOT = MT == 2 ? 2 : 3;
+  static constexpr int NSLOT = 2;
   static constexpr int B_BYTES = BN * 128;
-  static constexpr int STAGES = BN >= 256 ? 2 : 3;
+  static constexpr int STAGES = BN >= 256 ? 3 : 4;
   static constexpr int STG_HALF = FV_EPI_WARPS * 4096;           // one 32x32 fp32 tile per epilogue warp
-  static constexpr int RAW_MIN = MT == 2 ? 3 : 2;                // raw stages when the residual needs both halves
+  static constexpr int NRAW = STG_HALF / FV_RAW_BYTES;           // fp32 raw ring = staging half 1 (no residual then)
   static constexpr int COEF_BYTES = CB * 64 * 16;
   static constexpr int OFF_B = NSLOT * SLOT_BYTES;
-  static constexpr int OFF_STG = OFF_B + STAGES * B_BYTES;       // [half 0][half 1][raw min] contiguous
-  static constexpr int OFF_RAW = OFF_STG + 2 * STG_HALF;
-  static constexpr int OFF_COEF = OFF_RAW + RAW_MIN * FV_RAW_BYTES;
+  static constexpr int OFF_STG = OFF_B + STAGES * B_BYTES;       // [half 0][half 1]
+  static constexpr int OFF_RAW = OFF_STG + STG_HALF;             // aliases staging half 1
+  static constexpr int OFF_COEF = OFF_STG + 2 * STG_HALF;
   static constexpr int OFF_BAR = OFF_COEF + COEF_BYTES;
   static constexpr int SMEM_BYTES = OFF_BAR + 512 + 1024;
   static constexpr uint32_t TMEM_COLS = 512;
   static_assert(SLOT_ROWS >= 128 * MT + FV_HALO_MAX && SLOT_ROWS % 32 == 0, "slot too small");
   static_assert(2 * MT * BN <= 512, "accumulators exceed tensor memory");
-  static_assert(4 + RAW_MIN <= FV_MAX_RAW, "raw ring barrier array");
+  static_assert(NRAW <= FV_MAX_RAW && STAGES <= 4, "barrier arrays");
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
 
@@ -84,56 +84,97 @@ __device__ __forceinline__ float fv_apply(float x, const float4& k, float slope)
 
 // bf16 input, in place: the slot holds rows [0, nrows) as TMA wrote them (128B swizzle).  Lane = (row%4, logical
 // 16-byte chunk q): 8 channels cb*64 + 8q.., coefficients in registers; physical chunk = q ^ (row & 7).
+// Batches of XB steps: all loads, then all arithmetic, then all stores (the shared-memory accesses are volatile
+// asm, which the compiler will not reorder - the batching is what exposes the instruction-level parallelism).
 template <int ACT>
 __device__ __forceinline__ void fv_xf_inplace(uint32_t slot, const float4* __restrict__ coef, float slope, int cb,
                                               int nrows, int l_base, int L_in, int xw, int lane) {
+  constexpr int XB = 4;
   const int q = lane & 7, sub = lane >> 3;
   float4 k[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) k[i] = coef[cb * 64 + q * 8 + i];
   const int nsteps = (nrows + 3) >> 2;
-#pragma unroll 2
-  for (int s = xw; s < nsteps; s += FV_XF_WARPS) {
-    const int r = 4 * s + sub;
-    const int l = l_base + r;
-    const uint32_t p = slot + (uint32_t)r * 128u + (uint32_t)((q ^ (r & 7)) << 4);
-    uint4 o = make_uint4(0u, 0u, 0u, 0u);   // rows outside the utterance: the conv's zero padding (post-activation)
-    if (r < nrows && l >= 0 && l < L_in) {
-      uint4 t;
-      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(p));
-      o.x = fv_pack(fv_apply<ACT>(__uint_as_float(t.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(t.x & 0xffff0000u), k[1], slope));
-      o.y = fv_pack(fv_apply<ACT>(__uint_as_float(t.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(t.y & 0xffff0000u), k[3], slope));
-      o.z = fv_pack(fv_apply<ACT>(__uint_as_float(t.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(t.z & 0xffff0000u), k[5], slope));
-      o.w = fv_pack(fv_apply<ACT>(__uint_as_float(t.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(t.w & 0xffff0000u), k[7], slope));
+  for (int s0 = xw; s0 < nsteps; s0 += FV_XF_WARPS * XB) {
+    uint4 t[XB];
+    uint32_t p[XB];
+    bool ok[XB];
+#pragma unroll
+    for (int u = 0; u < XB; ++u) {
+      const int r = 4 * (s0 + u * FV_XF_WARPS) + sub;
+      const int l = l_base + r;
+      p[u] = slot + (uint32_t)r * 128u + (uint32_t)((q ^ (r & 7)) << 4);
+      ok[u] = r < nrows && l >= 0 && l < L_in;
+      t[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (ok[u]) asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t[u].x), "=r"(t[u].y), "=r"(t[u].z), "=r"(t[u].w) : "r"(p[u]));
     }
-    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(p), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+#pragma unroll
+    for (int u = 0; u < XB; ++u) {
+      if (ok[u]) {   // rows outside the utterance stay zero: the conv's zero padding (post-activation)
+        const uint4 v = t[u];
+        t[u].x = fv_pack(fv_apply<ACT>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
+        t[u].y = fv_pack(fv_apply<ACT>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
+        t[u].z = fv_pack(fv_apply<ACT>(__uint_as_float(v.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(v.z & 0xffff0000u), k[5], slope));
+        t[u].w = fv_pack(fv_apply<ACT>(__uint_as_float(v.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(v.w & 0xffff0000u), k[7], slope));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < XB; ++u) {
+      if (s0 + u * FV_XF_WARPS < nsteps)
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(p[u]), "r"(t[u].x), "r"(t[u].y), "r"(t[u].z), "r"(t[u].w) : "memory");
+    }
   }
 }
 
 // fp32 input: one raw stage (32 rows x 64 channels, row-major 256 B) -> slot rows [row0, row0 + 32).
-// Lane = (row%2, 4-channel group q).
+// Lane = (row%2, 4-channel group q).  Loads, arithmetic and stores batched as above.
 template <int ACT>
 __device__ __forceinline__ void fv_xf_raw(uint32_t raw, uint32_t slot, const float4 (&k)[4], float slope, int row0,
                                           int nrows, int l_base, int L_in, int xw, int lane) {
+  constexpr int NS = 16 / FV_XF_WARPS;
   const int q = lane & 15, half = lane >> 4;
   const uint32_t chunk = (uint32_t)(q >> 1), sub8 = (uint32_t)(q & 1) * 8u;
+  float4 v[NS];
+  bool ok[NS];
 #pragma unroll
-  for (int i = 0; i < 16 / FV_XF_WARPS; ++i) {
+  for (int i = 0; i < NS; ++i) {
     const int rr = 2 * (xw + FV_XF_WARPS * i) + half;
     const int r = row0 + rr;
     const int l = l_base + r;
-    uint2 o = make_uint2(0u, 0u);
-    if (r < nrows && l >= 0 && l < L_in) {
-      float4 v;
-      asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+    ok[i] = r < nrows && l >= 0 && l < L_in;
+    v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ok[i])
+      asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[i].x), "=f"(v[i].y), "=f"(v[i].z), "=f"(v[i].w)
                    : "r"(raw + (uint32_t)(rr * 256 + q * 16)));
-      o.x = fv_pack(fv_apply<ACT>(v.x, k[0], slope), fv_apply<ACT>(v.y, k[1], slope));
-      o.y = fv_pack(fv_apply<ACT>(v.z, k[2], slope), fv_apply<ACT>(v.w, k[3], slope));
+  }
+  uint2 o[NS];
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    o[i] = make_uint2(0u, 0u);
+    if (ok[i]) {
+      o[i].x = fv_pack(fv_apply<ACT>(v[i].x, k[0], slope), fv_apply<ACT>(v[i].y, k[1], slope));
+      o[i].y = fv_pack(fv_apply<ACT>(v[i].z, k[2], slope), fv_apply<ACT>(v[i].w, k[3], slope));
     }
-    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(slot + (uint32_t)r * 128u + ((chunk ^ ((uint32_t)r & 7u)) << 4) + sub8),
-                 "r"(o.x), "r"(o.y) : "memory");
+  }
+#pragma unroll
+  for (int i = 0; i < NS; ++i) {
+    const uint32_t r = (uint32_t)(row0 + 2 * (xw + FV_XF_WARPS * i) + half);
+    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(slot + r * 128u + ((chunk ^ (r & 7u)) << 4) + sub8), "r"(o[i].x),
+                 "r"(o[i].y) : "memory");
   }
 }
+
+// Debug instrumentation (KK_FUSED_DBG builds only): cycles spent waiting on each barrier class, per CTA.
+#ifdef KK_FUSED_DBG
+__device__ unsigned long long* g_fv_dbg = nullptr;
+#define FV_WAIT(bar, par, acc) do { long long _t = clock64(); ptx::mbar_wait(bar, par); (acc) += clock64() - _t; } while (0)
+#define FV_DBG_DECL(name) long long name = 0
+#define FV_DBG_OUT(idx, v) do { if (g_fv_dbg) g_fv_dbg[(size_t)blockIdx.x * 16 + (idx)] = (unsigned long long)(v); } while (0)
+#else
+#define FV_WAIT(bar, par, acc) ptx::mbar_wait(bar, par)
+#define FV_DBG_DECL(name)
+#define FV_DBG_OUT(idx, v)
+#endif
 
 // contiguous share of the tile list for CTA `cta` of `ncta`
 __device__ __forceinline__ void fv_tile_range(int total, int cta, int ncta, int& start, int& count) {
@@ -146,7 +187,8 @@ template <int MT, int BN, int CB>
 __global__ void __launch_bounds__(FV_THREADS, 1)
 conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                       const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles) {
+                       const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles,
+                       const int flags) {
   using Cfg = FvCfg<MT, BN, CB>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -157,9 +199,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   uint64_t* x_full = a_empty + 3;                                        // [3] bf16 input landed in the slot
   uint64_t* raw_full = x_full + 3;                                       // [FV_MAX_RAW]
   uint64_t* raw_empty = raw_full + FV_MAX_RAW;                           // [FV_MAX_RAW]
-  uint64_t* b_full = raw_empty + FV_MAX_RAW;                             // [3]
-  uint64_t* b_empty = b_full + 3;                                        // [3]
-  uint64_t* tmem_full = b_empty + 3;                                     // [2]
+  uint64_t* b_full = raw_empty + FV_MAX_RAW;                             // [4]
+  uint64_t* b_empty = b_full + 4;                                        // [4]
+  uint64_t* tmem_full = b_empty + 4;                                     // [2]
   uint64_t* tmem_empty = tmem_full + 2;                                  // [2]
   uint64_t* res_full = tmem_empty + 2;                                   // [FV_EPI_WARPS * 2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + FV_EPI_WARPS * 2);
@@ -169,9 +211,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const int R = 128 * MT + halo;                         // slot rows a tile needs
   const int nbox = (R + FV_BOX_ROWS - 1) / FV_BOX_ROWS;  // 32-row TMA boxes per block
   const bool has_res = d.res != nullptr;
-  // without a residual the second staging half is free: the fp32 raw ring grows over it
-  const int nraw = has_res ? Cfg::RAW_MIN : Cfg::RAW_MIN + 4;
-  uint8_t* sRaw = smem + (has_res ? Cfg::OFF_RAW : Cfg::OFF_STG + Cfg::STG_HALF);
+  // fp32 input comes without a residual (host-checked): the raw ring lives in the second staging half
+  constexpr int nraw = Cfg::NRAW;
+  uint8_t* sRaw = smem + Cfg::OFF_RAW;
   int t_start, t_count;
   fv_tile_range(total_tiles, blockIdx.x, gridDim.x, t_start, t_count);
 
@@ -184,6 +226,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       ptx::mbar_init(&a_full[s], FV_XF_WARPS);
       ptx::mbar_init(&a_empty[s], 1);
       ptx::mbar_init(&x_full[s], 1);
+    }
+    for (int s = 0; s < 4; ++s) {
       ptx::mbar_init(&b_full[s], 1);
       ptx::mbar_init(&b_empty[s], 1);
     }
@@ -208,35 +252,41 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     // ===================== TMA producer: weight slabs, order (tile, channel block, tap) =====================
     if (lane == 0) {
       uint32_t g = 0;
+      FV_DBG_DECL(w_bempty);
       for (int j = 0; j < t_count; ++j) {
         for (int cb = 0; cb < CB; ++cb) {
           for (int t = 0; t < d.taps; ++t, ++g) {
             const uint32_t s = g % Cfg::STAGES, ph = (g / Cfg::STAGES) & 1;
-            ptx::mbar_wait(&b_empty[s], ph ^ 1);
+            FV_WAIT(&b_empty[s], ph ^ 1, w_bempty);
             ptx::mbar_expect_tx(&b_full[s], Cfg::B_BYTES);
             ptx::tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &b_full[s], t * d.Cw + cb * 64, 0);
           }
         }
       }
+      FV_DBG_OUT(0, w_bempty);
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, BN);
       uint32_t gb = 0, ga = 0;
+      FV_DBG_DECL(w_tempty); FV_DBG_DECL(w_afull); FV_DBG_DECL(w_bfull);
+#ifdef KK_FUSED_DBG
+      const long long t_begin = clock64();
+#endif
       for (int j = 0; j < t_count; ++j) {
         const uint32_t buf = j & 1, aph = (j >> 1) & 1;
-        ptx::mbar_wait(&tmem_empty[buf], aph ^ 1);   // epilogue has drained this accumulator set
+        FV_WAIT(&tmem_empty[buf], aph ^ 1, w_tempty);   // epilogue has drained this accumulator set
         ptx::tc_fence_after();
         const uint32_t tacc = tmem_base + buf * (MT * BN);
         for (int cb = 0; cb < CB; ++cb, ++ga) {
           const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
-          ptx::mbar_wait(&a_full[slot], sph);
+          FV_WAIT(&a_full[slot], sph, w_afull);
           ptx::tc_fence_after();
           const uint32_t sa0 = ptx::smem_u32(smem + slot * Cfg::SLOT_BYTES);
           for (int t = 0; t < d.taps; ++t, ++gb) {
             const uint32_t s = gb % Cfg::STAGES, ph = (gb / Cfg::STAGES) & 1;
-            ptx::mbar_wait(&b_full[s], ph);
+            FV_WAIT(&b_full[s], ph, w_bfull);
             ptx::tc_fence_after();
             const uint32_t sb = ptx::smem_u32(sB + s * Cfg::B_BYTES);
 #pragma unroll
@@ -255,18 +305,40 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         }
         ptx::umma_commit(&tmem_full[buf]);
       }
+      FV_DBG_OUT(1, w_tempty); FV_DBG_OUT(2, w_afull); FV_DBG_OUT(3, w_bfull);
+#ifdef KK_FUSED_DBG
+      FV_DBG_OUT(10, clock64() - t_begin);
+#endif
     }
   } else if (warp == 2) {
     // ===================== TMA producer: input rows (tile + halo), one 64-channel block at a time ============
     if (lane == 0) {
       uint32_t ga = 0, gr = 0;
+      FV_DBG_DECL(w_xprod);
       for (int j = 0; j < t_count; ++j) {
         const int tile = t_start + j;
         const int b = tile / m_tiles, l_base = (tile - b * m_tiles) * (128 * MT) - d.pad_left;
+        if ((flags & 1) && j + 1 < t_count) {
+          // pull the NEXT tile's rows (input and residual) into L2 now: the TMA loads one tile later then see
+          // L2-hit latency instead of HBM latency
+          const int nt = tile + 1, nb_ = nt / m_tiles, nm0 = (nt - nb_ * m_tiles) * (128 * MT);
+          const size_t xesz = a.x_is_bf16 ? 2 : 4;
+          int l0 = nm0 - d.pad_left + (nb_ == b ? R - halo : 0), l1 = nm0 - d.pad_left + R;   // rows not already fetched
+          l0 = l0 < 0 ? 0 : l0;
+          l1 = l1 > d.L_in ? d.L_in : l1;
+          if (l1 > l0)
+            ptx::prefetch_l2_bulk(reinterpret_cast<const char*>(a.x) + ((size_t)nb_ * d.L_in + l0) * a.x_pitch * xesz,
+                                  (uint32_t)((size_t)(l1 - l0) * a.x_pitch * xesz));
+          int r1 = nm0 + 128 * MT;
+          r1 = r1 > d.M ? d.M : r1;
+          if (has_res)
+            ptx::prefetch_l2_bulk(d.res + ((size_t)nb_ * d.L_res + nm0) * d.res_pitch,
+                                  (uint32_t)((size_t)(r1 - nm0) * d.res_pitch * 4));
+        }
         for (int cb = 0; cb < CB; ++cb, ++ga) {
           const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
           if (a.x_is_bf16) {
-            ptx::mbar_wait(&a_empty[slot], sph ^ 1);       // the MMAs that read this slot have completed
+            FV_WAIT(&a_empty[slot], sph ^ 1, w_xprod);     // the MMAs that read this slot have completed
             ptx::mbar_expect_tx(&x_full[slot], nbox * FV_XBOX_BYTES);
             for (int i = 0; i < nbox; ++i)
               ptx::tma_load_3d(smem + slot * Cfg::SLOT_BYTES + i * FV_XBOX_BYTES, &tmX, &x_full[slot], cb * 64,
@@ -274,13 +346,14 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           } else {
             for (int i = 0; i < nbox; ++i, ++gr) {
               const uint32_t s = gr % nraw, ph = (gr / nraw) & 1;
-              ptx::mbar_wait(&raw_empty[s], ph ^ 1);
+              FV_WAIT(&raw_empty[s], ph ^ 1, w_xprod);
               ptx::mbar_expect_tx(&raw_full[s], FV_RAW_BYTES);
               ptx::tma_load_3d(sRaw + s * FV_RAW_BYTES, &tmX, &raw_full[s], cb * 64, l_base + i * FV_BOX_ROWS, b);
             }
           }
         }
       }
+      FV_DBG_OUT(4, w_xprod);
     }
   } else if (warp >= FV_XF_WARP0 && warp < FV_XF_WARP0 + FV_XF_WARPS) {
     // ===================== transform warps: x -> act(a x + b) -> bf16 swizzled slot =====================
@@ -289,6 +362,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const bool snake = a.act == KK_ACT_SNAKE || a.act == KK_ACT_SNAKE_FAST;
     int cur_b = -1;
     uint32_t ga = 0, gr = 0;
+    FV_DBG_DECL(w_xdata); FV_DBG_DECL(w_xslot);
     for (int j = 0; j < t_count; ++j) {
       const int tile = t_start + j;
       const int b = tile / m_tiles, l_base = (tile - b * m_tiles) * (128 * MT) - d.pad_left;
@@ -316,7 +390,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
         const uint32_t sp = ptx::smem_u32(smem + slot * Cfg::SLOT_BYTES);
         if (a.x_is_bf16) {
-          ptx::mbar_wait(&x_full[slot], sph);
+          FV_WAIT(&x_full[slot], sph, w_xdata);
           if (snake) fv_xf_inplace<KK_ACT_SNAKE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
           else if (a.act == KK_ACT_LEAKY) fv_xf_inplace<KK_ACT_LEAKY>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
           else fv_xf_inplace<KK_ACT_NONE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
@@ -324,10 +398,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           float4 k[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) k[i] = coef[cb * 64 + (lane & 15) * 4 + i];
-          ptx::mbar_wait(&a_empty[slot], sph ^ 1);     // the MMAs that read this slot have completed
+          FV_WAIT(&a_empty[slot], sph ^ 1, w_xslot);   // the MMAs that read this slot have completed
           for (int i = 0; i < nbox; ++i, ++gr) {
             const uint32_t s = gr % nraw, ph = (gr / nraw) & 1;
-            ptx::mbar_wait(&raw_full[s], ph);
+            FV_WAIT(&raw_full[s], ph, w_xdata);
             const uint32_t rp = ptx::smem_u32(sRaw + s * FV_RAW_BYTES);
             if (snake) fv_xf_raw<KK_ACT_SNAKE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
             else if (a.act == KK_ACT_LEAKY) fv_xf_raw<KK_ACT_LEAKY>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw, lane);
@@ -341,6 +415,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         if (lane == 0) ptx::mbar_arrive(&a_full[slot]);
       }
     }
+    if (warp == FV_XF_WARP0 && lane == 0) { FV_DBG_OUT(5, w_xdata); FV_DBG_OUT(6, w_xslot); }
   } else if (warp >= FV_EPI_WARP0) {
     // ===================== epilogue warps =====================
     // Work item n = (tile j, chunk c) of this warp: 32 rows (TMEM lane group lg of sub-tile mt) x 32 columns.
@@ -369,6 +444,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
 #pragma unroll
     for (int c = 0; c < NCH; ++c) acc_s[c] = acc_q[c] = 0.0;
     int stat_b = -1;
+    FV_DBG_DECL(w_tfull); FV_DBG_DECL(w_res);
     auto flush_stats = [&](int b) {
       if (b < 0) return;
 #pragma unroll
@@ -385,7 +461,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128 + lg * 32;   // first row of the warp
       if (do_stats && b != stat_b) { flush_stats(stat_b); stat_b = b; }
       const uint32_t buf = j & 1, aph = (j >> 1) & 1;
-      ptx::mbar_wait(&tmem_full[buf], aph);
+      FV_WAIT(&tmem_full[buf], aph, w_tfull);
       ptx::tc_fence_after();
       const uint32_t tacc = tmem_base + buf * (MT * BN) + mt * BN + ((uint32_t)(lg * 32) << 16);
       const int m = m0 + lane;
@@ -398,7 +474,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const int cbase = (chunk0 + c) * 32;
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)cbase, v);
-        if (has_res) ptx::mbar_wait(&rbar[p], (uint32_t)(n >> 1) & 1);
+        if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
         else if (d.out) {
           if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
           __syncwarp();
@@ -471,6 +547,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       }
     }
     if (do_stats) flush_stats(stat_b);
+    if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
     if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
   }
   ptx::tc_fence_before();
@@ -533,13 +610,21 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   const int grid = (int)(total < num_sms() ? total : num_sms());
+  static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;   // experiment knob: next-tile L2 prefetch
   conv1d_adain_tc_kernel<MT, BN, CB><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, *d, *a, m_tiles,
-                                                                              (int)total);
+                                                                              (int)total, flags);
   KK_LAUNCH_CHECK("conv1d_adain_tc_kernel");
   return KK_OK;
 }
 
 }  // namespace kk
+
+#ifdef KK_FUSED_DBG
+extern "C" int kk_debug_fused_buffer(unsigned long long* buf) {
+  KK_CUDA(cudaMemcpyToSymbol(kk::g_fv_dbg, &buf, sizeof(buf)));
+  return KK_OK;
+}
+#endif
 
 extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, const kk_conv_desc* d, void* stream) {
   KK_CHECK_ARG(a && a->x && w, "kk_conv1d_adain_bf16_tc: null tensor");
@@ -573,6 +658,11 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
   KK_CHECK_ARG((a->act != KK_ACT_SNAKE && a->act != KK_ACT_SNAKE_FAST) || a->alpha,
                "kk_conv1d_adain_bf16_tc: snake needs alpha");
   KK_CHECK_ARG(!a->stats || a->h, "kk_conv1d_adain_bf16_tc: normalisation needs the style projection h");
+  if (!a->x_is_bf16 && d->res) {
+    kk::set_error("kk_conv1d_adain_bf16_tc: fp32 input with a residual is not supported (the raw-input ring and the "
+                  "residual staging share shared memory)");
+    return KK_ERR_UNSUPPORTED;
+  }
   cudaStream_t st = (cudaStream_t)stream;
   if (d->C_in == 128 && d->N == 128) return kk::launch_fused<2, 128, 2>(a, w, d, st);
   if (d->C_in == 256 && d->N == 256) return kk::launch_fused<1, 256, 4>(a, w, d, st);

@@ -340,16 +340,25 @@ def _fused_case(lib, B, Lin, Cch, k, dil, x_bf16=False, act="snake", with_res=Tr
 
 
 FUSED_CASES = [
-    dict(B=2, Lin=700, Cch=128, k=11, dil=5),
+    # fp32 input (conv1 of an AdaINResBlock1 iteration: no residual) / bf16 input (conv2: residual + fp32 output)
+    dict(B=2, Lin=700, Cch=128, k=11, dil=5, with_res=False),
     dict(B=1, Lin=1000, Cch=128, k=3, dil=1, x_bf16=True),
     dict(B=3, Lin=257, Cch=128, k=7, dil=3, with_res=False),
-    dict(B=2, Lin=300, Cch=256, k=11, dil=5),
+    dict(B=2, Lin=300, Cch=256, k=11, dil=5, x_bf16=True),
     dict(B=2, Lin=129, Cch=256, k=7, dil=1, x_bf16=True, with_res=False),
-    dict(B=1, Lin=40, Cch=256, k=3, dil=3),
-    dict(B=2, Lin=200, Cch=128, k=3, dil=1, act="leaky"),
-    dict(B=1, Lin=200, Cch=128, k=1, dil=1, act="none", with_norm=False),
-    dict(B=150, Lin=300, Cch=128, k=7, dil=1),     # > 148 tiles: persistent loop, utterance changes per CTA
+    dict(B=1, Lin=40, Cch=256, k=3, dil=3, with_res=False),
+    dict(B=2, Lin=200, Cch=128, k=3, dil=1, act="leaky", with_res=False),
+    dict(B=1, Lin=200, Cch=128, k=1, dil=1, act="none", with_norm=False, x_bf16=True),
+    dict(B=150, Lin=300, Cch=128, k=7, dil=1, x_bf16=True),   # > 148 tiles: persistent loop, utterance changes per CTA
+    dict(B=3, Lin=700, Cch=256, k=7, dil=5, with_res=False),
 ]
+
+
+def test_conv1d_adain_rejects_fp32_input_with_residual(lib):
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    with pytest.raises(L.KokoroB200Error, match="unsupported"):
+        _fused_case(lib, B=1, Lin=64, Cch=128, k=3, dil=1, x_bf16=False, with_res=True)
 
 
 @pytest.mark.parametrize("case", FUSED_CASES)
