@@ -183,7 +183,10 @@ __device__ __forceinline__ void fv_tile_range(int total, int cta, int ncta, int&
   start = cta * base + (cta < rem ? cta : rem);
 }
 
-template <int MT, int BN, int CB>
+// SWAP (MT == 2, BN == 128 only): the MMA runs "transposed" - weights as the M = 128 operand, the 256 tile rows
+// as N = 256 - so one 128x256x16 MMA replaces two 128x128x16 ones (12 KB instead of 16 KB of shared-memory
+// operand reads per 128 tensor cycles).  The accumulator is then [channel lanes][row columns].
+template <int MT, int BN, int CB, bool SWAP>
 __global__ void __launch_bounds__(FV_THREADS, 1)
 conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
@@ -268,7 +271,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, BN);
+      constexpr uint32_t idesc = SWAP ? ptx::umma_idesc_bf16(128, 256) : ptx::umma_idesc_bf16(128, BN);
+      static_assert(!SWAP || (MT == 2 && BN == 128), "SWAP is the 256-row x 128-channel configuration");
       uint32_t gb = 0, ga = 0;
       FV_DBG_DECL(w_tempty); FV_DBG_DECL(w_afull); FV_DBG_DECL(w_bfull);
 #ifdef KK_FUSED_DBG
@@ -289,14 +293,24 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             FV_WAIT(&b_full[s], ph, w_bfull);
             ptx::tc_fence_after();
             const uint32_t sb = ptx::smem_u32(sB + s * Cfg::B_BYTES);
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt) {
-              const uint32_t sa = sa0 + (uint32_t)(mt * 128 + t * d.dil) * 128u;   // row-shifted view of the slot
+            if (SWAP) {
+              const uint32_t sx = sa0 + (uint32_t)(t * d.dil) * 128u;                // rows t*dil .. +255 of the slot
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-                const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-                ptx::umma_bf16(tacc + mt * BN, ad, bd, idesc, (cb | t | k) != 0 ? 1u : 0u);
+                const uint64_t wd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                const uint64_t xd = ptx::umma_desc(sx + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                ptx::umma_bf16(tacc, wd, xd, idesc, (cb | t | k) != 0 ? 1u : 0u);
+              }
+            } else {
+#pragma unroll
+              for (int mt = 0; mt < MT; ++mt) {
+                const uint32_t sa = sa0 + (uint32_t)(mt * 128 + t * d.dil) * 128u;   // row-shifted view of the slot
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                  const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                  ptx::umma_bf16(tacc + mt * BN, ad, bd, idesc, (cb | t | k) != 0 ? 1u : 0u);
+                }
               }
             }
             ptx::umma_commit(&b_empty[s]);
