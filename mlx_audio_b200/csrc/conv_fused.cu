@@ -432,6 +432,124 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (warp == FV_XF_WARP0 && lane == 0) { FV_DBG_OUT(5, w_xdata); FV_DBG_OUT(6, w_xslot); }
   } else if (warp >= FV_EPI_WARP0) {
     // ===================== epilogue warps =====================
+    if constexpr (SWAP) {
+    // Transposed accumulator: TMEM lane = output channel, column = tile row.  Work item n = (tile j, 32-row chunk
+    // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.
+    const int ew = warp - FV_EPI_WARP0;
+    const int lg = warp & 3;
+    const int half = ew >> 2;
+    constexpr int NRC = 4;
+    uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // [32 rows][32 channels] fp32, 16-byte chunk ^= row & 7
+    uint64_t* rbar = res_full + ew * 2;
+    const bool do_stats = d.stats != nullptr;
+    const int ch0 = lg * 32, chan = ch0 + lane;
+    const float bias_c = d.bias ? __ldg(d.bias + chan) : 0.f;
+    const int n_items = t_count * NRC;
+    auto issue_res = [&](int n) {   // lane 0: TMA the residual tile of item n into staging buffer n & 1
+      if (n >= n_items) return;
+      const int tile = t_start + n / NRC, rc = n % NRC;
+      const int b = tile / m_tiles, row0 = (tile - b * m_tiles) * 256 + half * 128 + rc * 32;
+      ptx::mbar_expect_tx(&rbar[n & 1], 4096);
+      ptx::tma_load_3d(stg0 + (n & 1) * Cfg::STG_HALF, &tmRes, &rbar[n & 1], ch0, row0, b);
+    };
+    if (has_res && lane == 0) { issue_res(0); issue_res(1); }
+    double acc_s = 0.0, acc_q = 0.0;   // fp64 running instance-norm sums of this thread's channel
+    int stat_b = -1;
+    FV_DBG_DECL(w_tfull); FV_DBG_DECL(w_res);
+    auto flush_stats = [&](int b) {
+      if (b < 0) return;
+      atomicAdd(d.stats + ((size_t)b * d.C_out + chan) * 2, acc_s);
+      atomicAdd(d.stats + ((size_t)b * d.C_out + chan) * 2 + 1, acc_q);
+      acc_s = acc_q = 0.0;
+    };
+    for (int j = 0; j < t_count; ++j) {
+      const int tile = t_start + j;
+      const int b = tile / m_tiles, tm0 = (tile - b * m_tiles) * 256 + half * 128;
+      if (do_stats && b != stat_b) { flush_stats(stat_b); stat_b = b; }
+      const uint32_t buf = j & 1, aph = (j >> 1) & 1;
+      FV_WAIT(&tmem_full[buf], aph, w_tfull);
+      ptx::tc_fence_after();
+      const uint32_t tacc = tmem_base + buf * 256 + (uint32_t)(half * 128) + ((uint32_t)(lg * 32) << 16);
+#pragma unroll 1
+      for (int rc = 0; rc < NRC; ++rc) {
+        const int n = j * NRC + rc;
+        const int p = has_res ? (n & 1) : 0;
+        float* st = reinterpret_cast<float*>(stg0 + p * Cfg::STG_HALF);
+        const int row0 = tm0 + rc * 32;
+        const int nvalid = d.M - row0;           // rows of this chunk inside the utterance (may be <= 0 or >= 32)
+        float v[32];
+        ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
+        if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
+        else if (d.out) {
+          if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
+          __syncwarp();
+        }
+        ptx::tmem_ld_wait();
+        if (rc == NRC - 1) {                             // last TMEM read of this tile: hand the accumulator back
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
+        }
+        float s_ = 0.f, q_ = 0.f;
+        // lane = channel: element (row jj, channel) of the swizzled tile; conflict-free for every jj.  Loads are
+        // batched ahead of the stores (the compiler cannot prove the swizzled addresses distinct).
+        const uint32_t sbase = ptx::smem_u32(st) + (uint32_t)(lane & 3) * 4u;
+        const uint32_t lchunk = (uint32_t)(lane >> 2);
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2) {
+          float rr[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int jj = h2 * 16 + i;
+            rr[i] = 0.f;
+            if (has_res)
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(rr[i]) : "r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)));
+            if (d.res2 && jj < nvalid) rr[i] += __ldg(d.res2 + ((size_t)b * d.L_out + row0 + jj) * d.res2_pitch + chan);
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int jj = h2 * 16 + i;
+            const float o = jj < nvalid ? (v[jj] + bias_c + rr[i]) * d.scale : 0.f;
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)), "f"(o) : "memory");
+            s_ += o;
+            q_ = fmaf(o, o, q_);
+          }
+        }
+        acc_s += (double)s_;
+        acc_q += (double)q_;
+        if (d.out) ptx::fence_proxy_async();             // staging writes -> visible to the TMA store
+        __syncwarp();
+        if (d.out && lane == 0) {
+          ptx::tma_store_3d(&tmOut, st, ch0, row0, b);   // rows >= L_out are clipped by the tensor map
+          ptx::bulk_commit();
+        }
+        if (d.out_act) {
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + (lane >> 2), c8 = lane & 3;
+            if (r < nvalid) {
+              const float4 t0 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8) ^ (r & 7)) << 2));
+              const float4 t1 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8 + 1) ^ (r & 7)) << 2));
+              uint4 q4;
+              q4.x = fv_pack(leaky(t0.x, d.act_slope), leaky(t0.y, d.act_slope));
+              q4.y = fv_pack(leaky(t0.z, d.act_slope), leaky(t0.w, d.act_slope));
+              q4.z = fv_pack(leaky(t1.x, d.act_slope), leaky(t1.y, d.act_slope));
+              q4.w = fv_pack(leaky(t1.z, d.act_slope), leaky(t1.w, d.act_slope));
+              *reinterpret_cast<uint4*>((__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0 + r) * d.act_pitch + ch0 + c8 * 8) = q4;
+            }
+          }
+        }
+        __syncwarp();                                    // everyone is done reading this staging tile
+        if (has_res && lane == 0) {
+          if (d.out) ptx::bulk_wait_read<0>();           // ... and so is the TMA store
+          issue_res(n + 2);
+        }
+      }
+    }
+    if (do_stats) flush_stats(stat_b);
+    if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
+    if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
+    } else {
     // Work item n = (tile j, chunk c) of this warp: 32 rows (TMEM lane group lg of sub-tile mt) x 32 columns.
     const int ew = warp - FV_EPI_WARP0;
     const int lg = warp & 3;                 // TMEM lane group this warp may access
@@ -563,6 +681,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (do_stats) flush_stats(stat_b);
     if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
     if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
+    }  // !SWAP
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -579,7 +698,7 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank
               const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle swz);   // conv_tc.cu
 int num_sms();                                                                             // conv_tc.cu
 
-template <int MT, int BN, int CB>
+template <int MT, int BN, int CB, bool SWAP>
 static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc* d, cudaStream_t st) {
   using Cfg = FvCfg<MT, BN, CB>;
   CUtensorMap tmB, tmX, tmRes, tmOut;
@@ -616,7 +735,7 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   }
   static bool attr_set = false;
   if (!attr_set) {
-    KK_CUDA(cudaFuncSetAttribute(conv1d_adain_tc_kernel<MT, BN, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    KK_CUDA(cudaFuncSetAttribute(conv1d_adain_tc_kernel<MT, BN, CB, SWAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  Cfg::SMEM_BYTES));
     attr_set = true;
   }
@@ -625,7 +744,7 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   const int grid = (int)(total < num_sms() ? total : num_sms());
   static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;   // experiment knob: next-tile L2 prefetch
-  conv1d_adain_tc_kernel<MT, BN, CB><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, *d, *a, m_tiles,
+  conv1d_adain_tc_kernel<MT, BN, CB, SWAP><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, *d, *a, m_tiles,
                                                                               (int)total, flags);
   KK_LAUNCH_CHECK("conv1d_adain_tc_kernel");
   return KK_OK;
@@ -678,8 +797,10 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
     return KK_ERR_UNSUPPORTED;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (d->C_in == 128 && d->N == 128) return kk::launch_fused<2, 128, 2>(a, w, d, st);
-  if (d->C_in == 256 && d->N == 256) return kk::launch_fused<1, 256, 4>(a, w, d, st);
+  static const bool swap128 = !(getenv("KK_FUSED_SWAP") && atoi(getenv("KK_FUSED_SWAP")) == 0);   // A/B knob
+  if (d->C_in == 128 && d->N == 128)
+    return swap128 ? kk::launch_fused<2, 128, 2, true>(a, w, d, st) : kk::launch_fused<2, 128, 2, false>(a, w, d, st);
+  if (d->C_in == 256 && d->N == 256) return kk::launch_fused<1, 256, 4, false>(a, w, d, st);
   kk::set_error("kk_conv1d_adain_bf16_tc: unsupported shape C_in=%d N=%d (128->128 and 256->256 only)", d->C_in, d->N);
   return KK_ERR_UNSUPPORTED;
 }
