@@ -20,21 +20,24 @@
 //     result is written back in place and leaves by TMA store; instance-norm sums are read off the same tile
 //     and accumulated in fp64 registers across the CTA's contiguous run of tiles (one atomic flush per
 //     utterance change instead of one per tile).
-// Warp roles: 0 = TMA weights, 1 = MMA issuer, 2 = TMA input (+ TMEM allocation), 3 = spare, 4..7 = transform,
-// 8..15 = epilogue.  Persistent: CTA i walks a contiguous range of the (utterance, row-tile) list.
+// Warp roles: 0 = TMA weights, 1 = MMA issuer, 2 = TMA input (+ TMEM allocation), 3 = spare, 4..11 = transform,
+// 12..19 = epilogue; registers are re-balanced per warpgroup with setmaxnreg (control 40, transform 72, epilogue 144)
+// as the first statement of every role branch (ptxas then allocates each branch against its own budget).  Persistent: CTA i walks a contiguous range of the (utterance, row-tile) list.
 #include "conv_epilogue.cuh"
 #include "ptx_sm100.cuh"
 #include <stdlib.h>
 
 namespace kk {
 
-constexpr int FV_XF_WARPS = 4;
+constexpr int FV_XF_WARPS = 8;
 constexpr int FV_EPI_WARPS = 8;
 constexpr int FV_XF_THREADS = FV_XF_WARPS * 32;
 constexpr int FV_EPI_THREADS = FV_EPI_WARPS * 32;
 constexpr int FV_XF_WARP0 = 4;
-constexpr int FV_EPI_WARP0 = 8;
-constexpr int FV_THREADS = (FV_EPI_WARP0 + FV_EPI_WARPS) * 32;  // 512
+constexpr int FV_EPI_WARP0 = 12;
+constexpr int FV_THREADS = (FV_EPI_WARP0 + FV_EPI_WARPS) * 32;  // 640 = 5 warpgroups, launched with 96 registers
+// per-warpgroup register reallocation (setmaxnreg): freed by dec 128*(56 + 2*24) = 13312 >= needed by inc 256*48
+constexpr int FV_REGS_CTRL = 40, FV_REGS_XF = 72, FV_REGS_EPI = 144;
 constexpr int FV_HALO_MAX = 56;
 constexpr int FV_BOX_ROWS = 32;            // rows per input TMA box
 constexpr int FV_RAW_BYTES = 32 * 256;     // fp32 raw stage: 32 rows x 64 channels
@@ -109,14 +112,14 @@ __device__ __forceinline__ void fv_xf_inplace(uint32_t slot, const float4* __res
       if (ok[u]) asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t[u].x), "=r"(t[u].y), "=r"(t[u].z), "=r"(t[u].w) : "r"(p[u]));
     }
 #pragma unroll
-    for (int u = 0; u < XB; ++u) {
-      if (ok[u]) {   // rows outside the utterance stay zero: the conv's zero padding (post-activation)
-        const uint4 v = t[u];
-        t[u].x = fv_pack(fv_apply<ACT>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
-        t[u].y = fv_pack(fv_apply<ACT>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
-        t[u].z = fv_pack(fv_apply<ACT>(__uint_as_float(v.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(v.z & 0xffff0000u), k[5], slope));
-        t[u].w = fv_pack(fv_apply<ACT>(__uint_as_float(v.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(v.w & 0xffff0000u), k[7], slope));
-      }
+    for (int u = 0; u < XB; ++u) {   // branch-free so that the XB sine chains interleave
+      const uint4 v = t[u];
+      const uint32_t x0 = fv_pack(fv_apply<ACT>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
+      const uint32_t x1 = fv_pack(fv_apply<ACT>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
+      const uint32_t x2 = fv_pack(fv_apply<ACT>(__uint_as_float(v.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(v.z & 0xffff0000u), k[5], slope));
+      const uint32_t x3 = fv_pack(fv_apply<ACT>(__uint_as_float(v.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(v.w & 0xffff0000u), k[7], slope));
+      // rows outside the utterance are zero: the conv's zero padding (post-activation)
+      t[u].x = ok[u] ? x0 : 0u; t[u].y = ok[u] ? x1 : 0u; t[u].z = ok[u] ? x2 : 0u; t[u].w = ok[u] ? x3 : 0u;
     }
 #pragma unroll
     for (int u = 0; u < XB; ++u) {
@@ -150,11 +153,10 @@ __device__ __forceinline__ void fv_xf_raw(uint32_t raw, uint32_t slot, const flo
   uint2 o[NS];
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
-    o[i] = make_uint2(0u, 0u);
-    if (ok[i]) {
-      o[i].x = fv_pack(fv_apply<ACT>(v[i].x, k[0], slope), fv_apply<ACT>(v[i].y, k[1], slope));
-      o[i].y = fv_pack(fv_apply<ACT>(v[i].z, k[2], slope), fv_apply<ACT>(v[i].w, k[3], slope));
-    }
+    const uint32_t x0 = fv_pack(fv_apply<ACT>(v[i].x, k[0], slope), fv_apply<ACT>(v[i].y, k[1], slope));
+    const uint32_t x1 = fv_pack(fv_apply<ACT>(v[i].z, k[2], slope), fv_apply<ACT>(v[i].w, k[3], slope));
+    o[i].x = ok[i] ? x0 : 0u;   // branch-free so that the sine chains of the NS steps interleave
+    o[i].y = ok[i] ? x1 : 0u;
   }
 #pragma unroll
   for (int i = 0; i < NS; ++i) {
@@ -253,6 +255,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
 
   if (warp == 0) {
     // ===================== TMA producer: weight slabs, order (tile, channel block, tap) =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));
     if (lane == 0) {
       uint32_t g = 0;
       FV_DBG_DECL(w_bempty);
@@ -270,6 +273,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));
     if (lane == 0) {
       constexpr uint32_t idesc = SWAP ? ptx::umma_idesc_bf16(128, 256) : ptx::umma_idesc_bf16(128, BN);
       static_assert(!SWAP || (MT == 2 && BN == 128), "SWAP is the 256-row x 128-channel configuration");
@@ -326,6 +330,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     }
   } else if (warp == 2) {
     // ===================== TMA producer: input rows (tile + halo), one 64-channel block at a time ============
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));
     if (lane == 0) {
       uint32_t ga = 0, gr = 0;
       FV_DBG_DECL(w_xprod);
@@ -371,6 +376,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     }
   } else if (warp >= FV_XF_WARP0 && warp < FV_XF_WARP0 + FV_XF_WARPS) {
     // ===================== transform warps: x -> act(a x + b) -> bf16 swizzled slot =====================
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_XF));
     const int xw = warp - FV_XF_WARP0;
     const int xt = threadIdx.x - FV_XF_WARP0 * 32;
     const bool snake = a.act == KK_ACT_SNAKE || a.act == KK_ACT_SNAKE_FAST;
@@ -432,6 +438,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (warp == FV_XF_WARP0 && lane == 0) { FV_DBG_OUT(5, w_xdata); FV_DBG_OUT(6, w_xslot); }
   } else if (warp >= FV_EPI_WARP0) {
     // ===================== epilogue warps =====================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FV_REGS_EPI));
     if constexpr (SWAP) {
     // Transposed accumulator: TMEM lane = output channel, column = tile row.  Work item n = (tile j, 32-row chunk
     // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.
@@ -618,22 +625,33 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
         }
 #pragma unroll
-        for (int c4 = 0; c4 < 8; ++c4) {
-          float4* sp = reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
-          float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (has_res) rr = *sp;
-          if (d.res2 && row_ok) {
-            const float4 u = __ldg(reinterpret_cast<const float4*>(d.res2 + ((size_t)b * d.L_out + m) * d.res2_pitch + cbase + c4 * 4));
-            rr.x += u.x; rr.y += u.y; rr.z += u.z; rr.w += u.w;
+        for (int h2 = 0; h2 < 2; ++h2) {   // loads batched ahead of the stores, four 16-byte chunks at a time
+          float4 rr[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int c4 = h2 * 4 + i;
+            rr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (has_res) rr[i] = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
           }
-          float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
-          float4 o;
-          o.x = row_ok ? (v[c4 * 4 + 0] + bs.x + rr.x) * d.scale : 0.f;
-          o.y = row_ok ? (v[c4 * 4 + 1] + bs.y + rr.y) * d.scale : 0.f;
-          o.z = row_ok ? (v[c4 * 4 + 2] + bs.z + rr.z) * d.scale : 0.f;
-          o.w = row_ok ? (v[c4 * 4 + 3] + bs.w + rr.w) * d.scale : 0.f;
-          *sp = o;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int c4 = h2 * 4 + i;
+            if (d.res2 && row_ok) {
+              const float4 u = __ldg(reinterpret_cast<const float4*>(d.res2 + ((size_t)b * d.L_out + m) * d.res2_pitch + cbase + c4 * 4));
+              rr[i].x += u.x; rr[i].y += u.y; rr[i].z += u.z; rr[i].w += u.w;
+            }
+            float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
+            rr[i].x = row_ok ? (v[c4 * 4 + 0] + bs.x + rr[i].x) * d.scale : 0.f;
+            rr[i].y = row_ok ? (v[c4 * 4 + 1] + bs.y + rr[i].y) * d.scale : 0.f;
+            rr[i].z = row_ok ? (v[c4 * 4 + 2] + bs.z + rr[i].z) * d.scale : 0.f;
+            rr[i].w = row_ok ? (v[c4 * 4 + 3] + bs.w + rr[i].w) * d.scale : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int c4 = h2 * 4 + i;
+            *reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2)) = rr[i];
+          }
         }
         if (d.out) ptx::fence_proxy_async();             // staging writes -> visible to the TMA store
         __syncwarp();
@@ -682,6 +700,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
     if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
     }  // !SWAP
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));   // spare warp of warpgroup 0
   }
   ptx::tc_fence_before();
   __syncthreads();
