@@ -502,6 +502,19 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         // batched ahead of the stores (the compiler cannot prove the swizzled addresses distinct).
         const uint32_t sbase = ptx::smem_u32(st) + (uint32_t)(lane & 3) * 4u;
         const uint32_t lchunk = (uint32_t)(lane >> 2);
+        const bool has_res2 = d.res2 != nullptr;
+        if (has_res2) {   // rare (MRF accumulation): fold the second residual into the staging tile first
+          const float* r2 = d.res2 + ((size_t)b * d.L_out + row0) * d.res2_pitch + chan;
+#pragma unroll 8
+          for (int jj = 0; jj < 32; ++jj) {
+            const uint32_t ad = sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4);
+            float t = 0.f;
+            if (has_res) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(t) : "r"(ad));
+            if (jj < nvalid) t += __ldg(r2 + (size_t)jj * d.res2_pitch);
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(ad), "f"(t) : "memory");
+          }
+        }
+        const bool rd = has_res || has_res2;
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {
           float rr[16];
@@ -509,9 +522,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           for (int i = 0; i < 16; ++i) {
             const int jj = h2 * 16 + i;
             rr[i] = 0.f;
-            if (has_res)
+            if (rd)
               asm volatile("ld.shared.f32 %0, [%1];" : "=f"(rr[i]) : "r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)));
-            if (d.res2 && jj < nvalid) rr[i] += __ldg(d.res2 + ((size_t)b * d.L_out + row0 + jj) * d.res2_pitch + chan);
           }
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
@@ -624,6 +636,19 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
         }
+        const bool has_res2 = d.res2 != nullptr;
+        if (has_res2) {   // rare (MRF accumulation): fold the second residual into the staging tile first
+          const float4* r2 = reinterpret_cast<const float4*>(d.res2 + ((size_t)b * d.L_out + (row_ok ? m : 0)) * d.res2_pitch + cbase);
+#pragma unroll
+          for (int c4 = 0; c4 < 8; ++c4) {
+            float4* sp = reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (has_res) t = *sp;
+            if (row_ok) { const float4 u = __ldg(r2 + c4); t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+            *sp = t;
+          }
+        }
+        const bool rd = has_res || has_res2;
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {   // loads batched ahead of the stores, four 16-byte chunks at a time
           float4 rr[4];
@@ -631,15 +656,11 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           for (int i = 0; i < 4; ++i) {
             const int c4 = h2 * 4 + i;
             rr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (has_res) rr[i] = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
+            if (rd) rr[i] = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
           }
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int c4 = h2 * 4 + i;
-            if (d.res2 && row_ok) {
-              const float4 u = __ldg(reinterpret_cast<const float4*>(d.res2 + ((size_t)b * d.L_out + m) * d.res2_pitch + cbase + c4 * 4));
-              rr[i].x += u.x; rr[i].y += u.y; rr[i].z += u.z; rr[i].w += u.w;
-            }
             float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
             if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
             rr[i].x = row_ok ? (v[c4 * 4 + 0] + bs.x + rr[i].x) * d.scale : 0.f;
