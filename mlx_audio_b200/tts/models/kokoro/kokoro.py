@@ -1,0 +1,119 @@
+"""Boundary shim for mlx_audio/tts/models/kokoro/kokoro.py: ``ModelConfig`` and ``Model`` with the reference's call
+surface, wrapping the B200 ``Decoder`` (the hot path).
+
+Scope: the text front end of the reference ``Model`` - ALBERT, TextEncoder, ProsodyPredictor
+(kokoro.py:70-106, modules.py) - is NOT part of the rebuilt path; it only produces the decoder inputs
+``asr (B,512,T), F0_pred (B,2T), N_pred (B,2T)`` (kokoro.py:142-162).  ``Model`` therefore takes that producer as a
+pluggable ``frontend`` callable; everything from ``decoder(asr, F0_pred, N_pred, ref_s[:, :128])`` (kokoro.py:164-165)
+on runs here.  ``SyntheticFrontend`` stands in for tests / benchmarks (seeded features of the right shapes).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field, fields
+from numbers import Number
+from typing import Any, Callable, Dict, Optional, Tuple
+
+import numpy as np
+
+from ....synth import KOKORO_DECODER, synth_f0
+from .istftnet import Decoder
+
+
+@dataclass
+class ModelConfig:
+    """kokoro.py:47-63 (only the fields the decoder needs are interpreted; the rest are carried)."""
+    istftnet: dict = field(default_factory=lambda: {k: v for k, v in KOKORO_DECODER.items()
+                                                    if k not in ("dim_in", "style_dim", "dim_out")})
+    dim_in: int = 64
+    dropout: float = 0.2
+    hidden_dim: int = 512
+    max_conv_dim: int = 512
+    max_dur: int = 50
+    multispeaker: bool = True
+    n_layer: int = 3
+    n_mels: int = 80
+    n_token: int = 178
+    style_dim: int = 128
+    text_encoder_kernel_size: int = 5
+    plbert: dict = field(default_factory=dict)
+    vocab: Dict[str, int] = field(default_factory=dict)
+    sample_rate: int = 24000
+    model_type: str = "kokoro"
+
+    @classmethod
+    def from_dict(cls, params: dict) -> "ModelConfig":
+        """BaseModelArgs.from_dict (base.py:9-18): unknown keys are ignored."""
+        names = {f.name for f in fields(cls)}
+        return cls(**{k: v for k, v in params.items() if k in names})
+
+
+Frontend = Callable[[str, Any, Number], Tuple[Any, Any, Any, Any]]
+
+
+class SyntheticFrontend:
+    """Seeded stand-in for the text front end: every phoneme gets ``frames_per_phoneme`` asr frames; returns
+    (asr (1,512,T), F0 (1,2T), N (1,2T), pred_dur (n_phonemes+2,))."""
+
+    def __init__(self, hidden_dim: int = 512, frames_per_phoneme: int = 3, seed: int = 0):
+        self.hidden_dim, self.fpp, self.seed = hidden_dim, frames_per_phoneme, seed
+
+    def __call__(self, phonemes: str, ref_s, speed: Number = 1):
+        n = len(phonemes) + 2                                     # [0, *ids, 0] (kokoro.py:135)
+        dur = np.maximum(np.round(np.full(n, self.fpp) / float(speed)), 1).astype(np.int32)   # kokoro.py:148-150
+        T = int(dur.sum())
+        rng = np.random.Generator(np.random.PCG64(self.seed + len(phonemes)))
+        asr = rng.standard_normal((1, self.hidden_dim, T), dtype=np.float32)
+        F0 = synth_f0(1, 2 * T, seed=self.seed + 4)
+        N = rng.standard_normal((1, 2 * T), dtype=np.float32)
+        return asr, F0, N, dur
+
+
+class Model:
+    """Reference surface: ``Model(config)``; ``model(phonemes, ref_s, speed=1, return_output=False, decoder=None)``
+    (kokoro.py:120-170); ``model.decoder`` is the B200 Decoder; ``sanitize`` keeps only what the decoder consumes."""
+
+    @dataclass
+    class Output:                      # kokoro.py:115-118
+        audio: Any
+        pred_dur: Optional[Any] = None
+
+    def __init__(self, config: ModelConfig, repo_id: Optional[str] = None, frontend: Optional[Frontend] = None,
+                 dtype: str = "bf16", device: Optional[str] = None):
+        self.config = config
+        self.repo_id = repo_id
+        self.vocab = config.vocab
+        self.context_length = int(config.plbert.get("max_position_embeddings", 512)) if config.plbert else 512
+        self.frontend = frontend
+        self.decoder = Decoder(dim_in=config.hidden_dim, style_dim=config.style_dim, dim_out=config.n_mels,
+                               **config.istftnet, dtype=dtype, device=device)    # kokoro.py:107-112
+        self.sample_rate = config.sample_rate
+
+    # ---- weights
+    def sanitize(self, weights: Dict[str, Any]) -> Dict[str, Any]:
+        """kokoro.py:172-252 restricted to the decoder: ``decoder.*`` keys go through Decoder.sanitize
+        (istftnet.py:965-979), every other sub-module's weights belong to the out-of-scope front end."""
+        out = {}
+        for k, v in weights.items():
+            if k.startswith("decoder."):
+                out[k] = self.decoder.sanitize(k, np.asarray(v))
+        return out
+
+    def load_weights(self, weights, strict: bool = True):
+        items = list(weights.items() if isinstance(weights, dict) else weights)
+        self.decoder.load_weights([(k, v) for k, v in items if k.startswith("decoder.")], strict=strict)
+        return self
+
+    # ---- forward
+    def __call__(self, phonemes: str, ref_s, speed: Number = 1, return_output: bool = False, decoder=None):
+        n_ids = len(phonemes) if not self.vocab else sum(1 for p in phonemes if self.vocab.get(p) is not None)
+        assert n_ids + 2 <= self.context_length, (n_ids + 2, self.context_length)      # kokoro.py:131-134
+        if self.frontend is None:
+            raise NotImplementedError(
+                "Model.__call__ needs a `frontend` (phonemes, ref_s, speed) -> (asr, F0_pred, N_pred, pred_dur): the "
+                "reference's text front end (ALBERT / TextEncoder / ProsodyPredictor, kokoro.py:142-162) is outside "
+                "the rebuilt hot path; pass your own or mlx_audio_b200...kokoro.SyntheticFrontend for testing")
+        ref_s = np.asarray(ref_s, dtype=np.float32) if not hasattr(ref_s, "shape") else ref_s
+        asr, F0_pred, N_pred, pred_dur = self.frontend(phonemes, ref_s, speed)
+        dec = decoder if decoder is not None else self.decoder
+        audio = dec(asr, F0_pred, N_pred, ref_s[:, :128])[0]                            # kokoro.py:165
+        return self.Output(audio=audio, pred_dur=pred_dur) if return_output else audio
