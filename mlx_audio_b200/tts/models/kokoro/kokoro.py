@@ -116,4 +116,6 @@ class Model:
         asr, F0_pred, N_pred, pred_dur = self.frontend(phonemes, ref_s, speed)
         dec = decoder if decoder is not None else self.decoder
         audio = dec(asr, F0_pred, N_pred, ref_s[:, :128])[0]                            # kokoro.py:165
+        if hasattr(audio, "clone"):
+            audio = audio.clone()       # the Decoder returns a view of its persistent output buffer
         return self.Output(audio=audio, pred_dur=pred_dur) if return_output else audio
