@@ -110,7 +110,8 @@ int validate_conv_desc(const kk_conv_desc* d, const char* who) {
   KK_CHECK_ARG(d->M > 0 && d->N > 0 && d->C_out > 0 && d->up > 0 && d->N == d->C_out * d->up,
                "%s: N (%d) must equal C_out*up (%d*%d)", who, d->N, d->C_out, d->up);
   KK_CHECK_ARG(d->L_out > 0 && d->L_true > 0, "%s: bad output length", who);
-  KK_CHECK_ARG(d->out || d->out_act, "%s: no output buffer", who);
+  KK_CHECK_ARG(d->out || d->out_act || d->out_add, "%s: no output buffer", who);
+  KK_CHECK_ARG(!d->out_add || d->add_pitch >= d->C_out, "%s: add_pitch < C_out", who);
   KK_CHECK_ARG(!d->out || d->out_pitch >= d->C_out, "%s: out_pitch < C_out", who);
   KK_CHECK_ARG(!d->out_act || d->act_pitch >= d->C_out, "%s: act_pitch < C_out", who);
   KK_CHECK_ARG(!d->res || (d->res_pitch >= d->C_out && d->L_res > 0 && d->res_shift >= 0), "%s: bad residual", who);
@@ -124,6 +125,10 @@ extern "C" int kk_conv1d_f32(const float* x, const float* w, const kk_conv_desc*
   KK_CHECK_ARG(x && w, "kk_conv1d_f32: null tensor");
   int rc = kk::validate_conv_desc(d, "kk_conv1d_f32");
   if (rc) return rc;
+  if (d->out_add) {
+    kk::set_error("kk_conv1d_f32: out_add is implemented by kk_conv1d_adain_bf16_tc only");
+    return KK_ERR_UNSUPPORTED;
+  }
   dim3 grid(kk::cdiv(d->M, kk::F_BM), kk::cdiv(d->N, kk::F_BN), d->B);
   KK_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "kk_conv1d_f32: grid too large");
   kk::conv1d_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, w, *d);

@@ -192,7 +192,7 @@ template <int MT, int BN, int CB, bool SWAP>
 __global__ void __launch_bounds__(FV_THREADS, 1)
 conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                       const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles,
+                       const __grid_constant__ CUtensorMap tmAdd, const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles,
                        const int flags) {
   using Cfg = FvCfg<MT, BN, CB>;
   extern __shared__ uint8_t smem_raw[];
@@ -216,6 +216,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const int R = 128 * MT + halo;                         // slot rows a tile needs
   const int nbox = (R + FV_BOX_ROWS - 1) / FV_BOX_ROWS;  // 32-row TMA boxes per block
   const bool has_res = d.res != nullptr;
+  const bool has_st = d.out != nullptr || d.out_add != nullptr;   // the staging tile leaves by TMA (store and/or reduce-add)
   // fp32 input comes without a residual (host-checked): the raw ring lives in the second staging half
   constexpr int nraw = Cfg::NRAW;
   uint8_t* sRaw = smem + Cfg::OFF_RAW;
@@ -227,6 +228,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     ptx::prefetch_tmap(&tmX);
     if (has_res) ptx::prefetch_tmap(&tmRes);
     if (d.out) ptx::prefetch_tmap(&tmOut);
+    if (d.out_add) ptx::prefetch_tmap(&tmAdd);
     for (int s = 0; s < 3; ++s) {
       ptx::mbar_init(&a_full[s], FV_XF_WARPS);
       ptx::mbar_init(&a_empty[s], 1);
@@ -487,7 +489,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
         if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
-        else if (d.out) {
+        else if (has_st) {
           if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
           __syncwarp();
         }
@@ -536,10 +538,11 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         }
         acc_s += (double)s_;
         acc_q += (double)q_;
-        if (d.out) ptx::fence_proxy_async();             // staging writes -> visible to the TMA store
+        if (has_st) ptx::fence_proxy_async();            // staging writes -> visible to the TMA store
         __syncwarp();
-        if (d.out && lane == 0) {
-          ptx::tma_store_3d(&tmOut, st, ch0, row0, b);   // rows >= L_out are clipped by the tensor map
+        if (has_st && lane == 0) {
+          if (d.out) ptx::tma_store_3d(&tmOut, st, ch0, row0, b);   // rows >= L_out are clipped by the tensor map
+          if (d.out_add) ptx::tma_reduce_add_3d(&tmAdd, st, ch0, row0, b);
           ptx::bulk_commit();
         }
         if (d.out_act) {
@@ -560,14 +563,14 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         }
         __syncwarp();                                    // everyone is done reading this staging tile
         if (has_res && lane == 0) {
-          if (d.out) ptx::bulk_wait_read<0>();           // ... and so is the TMA store
+          if (has_st) ptx::bulk_wait_read<0>();          // ... and so is the TMA store
           issue_res(n + 2);
         }
       }
     }
     if (do_stats) flush_stats(stat_b);
     if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
-    if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
+    if (has_st && lane == 0) ptx::bulk_wait<0>();        // all TMA stores have completed before the CTA retires
     } else {
     // Work item n = (tile j, chunk c) of this warp: 32 rows (TMEM lane group lg of sub-tile mt) x 32 columns.
     const int ew = warp - FV_EPI_WARP0;
@@ -626,7 +629,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)cbase, v);
         if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
-        else if (d.out) {
+        else if (has_st) {
           if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
           __syncwarp();
         }
@@ -674,10 +677,11 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             *reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2)) = rr[i];
           }
         }
-        if (d.out) ptx::fence_proxy_async();             // staging writes -> visible to the TMA store
+        if (has_st) ptx::fence_proxy_async();            // staging writes -> visible to the TMA store
         __syncwarp();
-        if (d.out && lane == 0) {
-          ptx::tma_store_3d(&tmOut, st, cbase, m0, b);   // rows >= L_out are clipped by the tensor map
+        if (has_st && lane == 0) {
+          if (d.out) ptx::tma_store_3d(&tmOut, st, cbase, m0, b);   // rows >= L_out are clipped by the tensor map
+          if (d.out_add) ptx::tma_reduce_add_3d(&tmAdd, st, cbase, m0, b);
           ptx::bulk_commit();
         }
         if (out_aligned_act) {
@@ -712,14 +716,14 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         }
         __syncwarp();                                    // everyone is done reading this staging tile
         if (has_res && lane == 0) {
-          if (d.out) ptx::bulk_wait_read<0>();           // ... and so is the TMA store
+          if (has_st) ptx::bulk_wait_read<0>();          // ... and so is the TMA store
           issue_res(n + 2);
         }
       }
     }
     if (do_stats) flush_stats(stat_b);
     if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
-    if (d.out && lane == 0) ptx::bulk_wait<0>();         // all TMA stores have completed before the CTA retires
+    if (has_st && lane == 0) ptx::bulk_wait<0>();        // all TMA stores have completed before the CTA retires
     }  // !SWAP
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));   // spare warp of warpgroup 0
@@ -742,7 +746,7 @@ int num_sms();                                                                  
 template <int MT, int BN, int CB, bool SWAP>
 static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc* d, cudaStream_t st) {
   using Cfg = FvCfg<MT, BN, CB>;
-  CUtensorMap tmB, tmX, tmRes, tmOut;
+  CUtensorMap tmB, tmX, tmRes, tmOut, tmAdd;
   int rc;
   {
     cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
@@ -774,6 +778,13 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
     cuuint32_t box[3] = {32, 32, 1};
     if ((rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->out, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   }
+  tmAdd = tmB;
+  if (d->out_add) {
+    cuuint64_t dims[3] = {(cuuint64_t)d->C_out, (cuuint64_t)d->L_out, (cuuint64_t)d->B};
+    cuuint64_t strides[2] = {(cuuint64_t)d->add_pitch * 4, (cuuint64_t)d->L_out * d->add_pitch * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    if ((rc = make_tmap(&tmAdd, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->out_add, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     KK_CUDA(cudaFuncSetAttribute(conv1d_adain_tc_kernel<MT, BN, CB, SWAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -785,7 +796,7 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   const int grid = (int)(total < num_sms() ? total : num_sms());
   static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;   // experiment knob: next-tile L2 prefetch
-  conv1d_adain_tc_kernel<MT, BN, CB, SWAP><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, *d, *a, m_tiles,
+  conv1d_adain_tc_kernel<MT, BN, CB, SWAP><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, tmAdd, *d, *a, m_tiles,
                                                                               (int)total, flags);
   KK_LAUNCH_CHECK("conv1d_adain_tc_kernel");
   return KK_OK;
@@ -820,6 +831,8 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
                "kk_conv1d_adain_bf16_tc: x and w must be 16-byte aligned with 16-byte row pitch");
   KK_CHECK_ARG(!d->out || (((uintptr_t)d->out & 15) == 0 && d->out_pitch % 4 == 0),
                "kk_conv1d_adain_bf16_tc: out must be 16-byte aligned with a pitch multiple of 4");
+  KK_CHECK_ARG(!d->out_add || (((uintptr_t)d->out_add & 15) == 0 && d->add_pitch % 4 == 0),
+               "kk_conv1d_adain_bf16_tc: out_add must be 16-byte aligned with a pitch multiple of 4");
   KK_CHECK_ARG(!d->res || (((uintptr_t)d->res & 15) == 0 && d->res_pitch % 4 == 0 && d->res_shift == 0 &&
                            d->L_res == d->L_out),
                "kk_conv1d_adain_bf16_tc: residual must be 16-byte aligned, same length as the output, no shift");

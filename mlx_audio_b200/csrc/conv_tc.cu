@@ -434,6 +434,10 @@ extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_des
     kk::set_error("kk_conv1d_bf16_tc: needs an sm_100 (Blackwell) device");
     return KK_ERR_UNSUPPORTED;
   }
+  if (d->out_add) {
+    kk::set_error("kk_conv1d_bf16_tc: out_add is implemented by kk_conv1d_adain_bf16_tc only");
+    return KK_ERR_UNSUPPORTED;
+  }
   KK_CHECK_ARG(d->stride == 1, "kk_conv1d_bf16_tc: stride must be 1 (got %d)", d->stride);
   KK_CHECK_ARG(d->Cw % 64 == 0, "kk_conv1d_bf16_tc: Cw (%d) must be a multiple of 64", d->Cw);
   KK_CHECK_ARG(d->x_pitch % 8 == 0, "kk_conv1d_bf16_tc: x_pitch (%d) must be a multiple of 8", d->x_pitch);

@@ -310,8 +310,10 @@ class DecoderEngine:
     def _conv_fused(self, plan: Plan, pc: PreparedConv, x: torch.Tensor, x_pitch: int, stats_addr: Optional[int],
                     ada_prefix: Optional[str], act: int, slope: float, alpha: Optional[torch.Tensor], h_all, B: int,
                     L_: int, *, dil: int = 1, pad_left: int = 0, out_addr: Optional[int] = None, out_pitch: int = 0,
-                    res=None, res2=None, scale: float = 1.0, out_stats: Optional[int] = None, out_act=None):
-        """AdaIN + activation + conv in one tensor-core launch (kk_conv1d_adain_bf16_tc)."""
+                    res=None, res2=None, scale: float = 1.0, out_stats: Optional[int] = None, out_act=None,
+                    out_add=None):
+        """AdaIN + activation + conv in one tensor-core launch (kk_conv1d_adain_bf16_tc).  out_add = (addr, pitch):
+        the result is also accumulated into that tensor (TMA reduce-add)."""
         a = AdainIn()
         a.x, a.x_is_bf16, a.x_pitch = self._addr(x), int(x.dtype == torch.bfloat16), x_pitch
         a.stats = stats_addr
@@ -337,6 +339,8 @@ class DecoderEngine:
         d.stats = out_stats
         if out_act is not None:
             d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
+        if out_add is not None:
+            d.out_add, d.add_pitch = out_add
         plan.keep.extend([a, d])
         plan.conv_ops[len(plan.ops)] = d
         plan.add(self.lib.kk_conv1d_adain_bf16_tc, C.byref(a), self._addr(pc.w16), C.byref(d))
@@ -361,7 +365,11 @@ class DecoderEngine:
                          final: dict):
         """AdaINResBlock1 (istftnet.py:341-396).  x_in (B,L,C) fp32 with stats_in known; the running stream lives
         in ``work`` after the first iteration (work may be x_in itself: fully in place).  ``final`` gives the
-        last conv2 epilogue: dict(out_addr, out_pitch, res2, scale, stats_addr, out_act)."""
+        last conv2 epilogue: dict(out_addr, out_pitch, res2, scale, stats_addr, out_act).  Fused path only:
+        ``out_add`` = (addr, pitch) accumulates the block's output into the MRF sum instead of reading it back as
+        a second residual; ``fold_into`` = (addr, pitch) of the running MRF sum S for the LAST block of the sum:
+        its stream x2 is reduce-added into S by the epilogue that produces it (S' = S + x2), and the final conv
+        then takes S' as its one residual: out = (S' + conv) * scale  ==  (S + x3) * scale."""
         ap = self._act_pitch(C_)
         snake = L.KK_ACT_SNAKE_FAST if self.tc else L.KK_ACT_SNAKE  # MUFU sine only when the result is rounded to bf16
         cur, cur_stats = x_in, stats_in
@@ -380,18 +388,23 @@ class DecoderEngine:
                                  self.w[f"{prefix}.alpha1.{it}"], h_all, B, L_, dil=d, pad_left=(k * d - d) // 2,
                                  out_stats=st_y, out_act=(self._addr(ybf), C_, 1, 1.0))
                 res = (self._addr(cur), C_, 0, L_)
+                fold = final.get("fold_into")
                 if it < 2:
                     st_n = self._stats(plan, B, C_)
                     self._conv_fused(plan, c2, ybf, C_, st_y, f"{prefix}.adain2.{it}", snake, 0.0,
                                      self.w[f"{prefix}.alpha2.{it}"], h_all, B, L_, pad_left=(k - 1) // 2,
-                                     out_addr=self._addr(work), out_pitch=C_, res=res, out_stats=st_n)
+                                     out_addr=self._addr(work), out_pitch=C_, res=res, out_stats=st_n,
+                                     out_add=fold if it == 1 else None)
                     cur, cur_stats = work, st_n
                 else:
+                    if fold is not None:
+                        res = (fold[0], fold[1], 0, L_)
                     self._conv_fused(plan, c2, ybf, C_, st_y, f"{prefix}.adain2.{it}", snake, 0.0,
                                      self.w[f"{prefix}.alpha2.{it}"], h_all, B, L_, pad_left=(k - 1) // 2,
                                      out_addr=final.get("out_addr"), out_pitch=final.get("out_pitch", C_), res=res,
                                      res2=final.get("res2"), scale=final.get("scale", 1.0),
-                                     out_stats=final.get("stats_addr"), out_act=final.get("out_act"))
+                                     out_stats=final.get("stats_addr"), out_act=final.get("out_act"),
+                                     out_add=final.get("out_add"))
             return
         for it in range(3):
             d = dils[it]
@@ -560,7 +573,12 @@ class DecoderEngine:
             a_next = self._buf(plan, f"a{i + 1}", (B, Li, ap), adt, zero=True)
             for j in range(n_k):
                 final = dict(out_addr=self._addr(acc), out_pitch=Ci)
-                if j > 0:
+                if j > 0 and fused_i:       # the sum over resblocks is carried by TMA reduce-adds
+                    if j < n_k - 1:
+                        final = dict(out_add=(self._addr(acc), Ci))
+                    else:
+                        final["fold_into"] = (self._addr(acc), Ci)
+                elif j > 0:
                     final["res2"] = (self._addr(acc), Ci)
                 if j == n_k - 1:
                     final["scale"] = 1.0 / n_k

@@ -327,9 +327,23 @@ def _fused_case(lib, B, Lin, Cch, k, dil, x_bf16=False, act="snake", with_res=Tr
     d.scale = scale
     d.out, d.out_pitch, d.stats = L.ptr(out), Cch, L.ptr(ostats)
     d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = L.ptr(oact), Cch, 1, 1.0
+    # out_add: the result tile is also accumulated (TMA reduce-add) into a wider, pre-filled tensor
+    add0 = r.standard_normal((B, Lin, Cch + 4), dtype=np.float32)
+    addd = dev(add0)
+    d.out_add, d.add_pitch = L.ptr(addd), Cch + 4
     L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused")
     torch.cuda.synchronize()
     got = out.cpu().numpy()
+    addg = addd.cpu().numpy()
+    np.testing.assert_allclose(addg[..., :Cch], add0[..., :Cch] + got, rtol=0, atol=1e-5)
+    np.testing.assert_array_equal(addg[..., Cch:], add0[..., Cch:])
+    # ... and alone (no `out`): same values
+    addd2 = dev(add0)
+    d.out, d.out_add = None, L.ptr(addd2)
+    ostats.zero_()
+    L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused/out_add only")
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(addd2.cpu().numpy(), addg)
     # tolerance: the kernel's fp32 affine / MUFU sine may round an operand to the neighbouring bf16 value
     err = np.abs(got - ref)
     assert np.isfinite(got).all()
