@@ -114,7 +114,7 @@ int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int b
  * never exists in HBM.  Epilogue identical to kk_conv1d_bf16_tc (bias, residuals, scale, stats, out / out_act).
  *   A[b][l][c] = act(a_c * x[b][l][c] + b_c),  a_c = (1+gamma_c) / sqrt(var_c + 1e-5),  b_c = beta_c - a_c mean_c
  *   (rows outside [0, L_in) are zero AFTER the activation: the conv's own zero padding)
- * Restrictions: stride 1, up 1, C_in in {128, 256} with N == C_in, (taps-1)*dil <= 56. */
+ * Restrictions: stride 1, up 1, C_in in {128, 256} with N == C_in, (taps-1)*dil <= 56, no res2 (use out_add). */
 typedef struct kk_adain_in {
   const void* x; int x_is_bf16; int x_pitch; /* raw input (B, L_in, x_pitch), fp32 or bf16                   */
   const double* stats;                       /* (B, C_in, 2) sum / sum of squares over time; NULL: no norm  */

@@ -451,7 +451,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FV_REGS_EPI));
     if constexpr (SWAP) {
     // Transposed accumulator: TMEM lane = output channel, column = tile row.  Work item n = (tile j, 32-row chunk
-    // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.
+    // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.  The result leaves
+    // STRAIGHT FROM REGISTERS (one 128-byte fp32 / 64-byte bf16 row segment per store instruction): the shared
+    // memory pipe is the kernel's bottleneck (UMMA operand reads + TMA fills), so the epilogue stays off it.
+    // Only a reduce-add (out_add) goes through the staging tile, because that is a TMA operation.
     const int ew = warp - FV_EPI_WARP0;
     const int lg = warp & 3;
     const int half = ew >> 2;
@@ -459,6 +462,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // [32 rows][32 channels] fp32, 16-byte chunk ^= row & 7
     uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
+    const bool via_smem = d.out_add != nullptr;
     const int ch0 = lg * 32, chan = ch0 + lane;
     const float bias_c = d.bias ? __ldg(d.bias + chan) : 0.f;
     const int n_items = t_count * NRC;
@@ -479,6 +483,27 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       atomicAdd(d.stats + ((size_t)b * d.C_out + chan) * 2 + 1, acc_q);
       acc_s = acc_q = 0.0;
     };
+    // row-strided stores of the thread's channel; `pitch` is a literal on the hot path (immediate offsets)
+    auto store_f32 = [&](float* op, const int pitch, const float (&o)[32], int nvalid) {
+      if (nvalid >= 32) {
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) op[jj * pitch] = o[jj];
+      } else {
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj)
+          if (jj < nvalid) op[jj * pitch] = o[jj];
+      }
+    };
+    auto store_bf16 = [&](__nv_bfloat16* ap, const int pitch, const float (&o)[32], int nvalid) {
+      if (nvalid >= 32) {
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) ap[jj * pitch] = __float2bfloat16_rn(act_id ? o[jj] : leaky(o[jj], d.act_slope));
+      } else {
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj)
+          if (jj < nvalid) ap[jj * pitch] = __float2bfloat16_rn(act_id ? o[jj] : leaky(o[jj], d.act_slope));
+      }
+    };
     for (int j = 0; j < t_count; ++j) {
       const int tile = t_start + j;
       const int b = tile / m_tiles, tm0 = (tile - b * m_tiles) * 256 + half * 128;
@@ -497,8 +522,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
         if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
-        else if (has_st) {
-          if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
+        else if (via_smem) {
+          if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA operation has finished reading this tile
           __syncwarp();
         }
         ptx::tmem_ld_wait();
@@ -507,83 +532,59 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
         }
-        float s_ = 0.f, q_ = 0.f;
-        // lane = channel: element (row jj, channel) of the swizzled tile; conflict-free for every jj.  Loads are
-        // batched ahead of the stores (the compiler cannot prove the swizzled addresses distinct).
+        // lane = channel: element (row jj, channel) of the swizzled tile; conflict-free for every jj.
         const uint32_t sbase = ptx::smem_u32(st) + (uint32_t)(lane & 3) * 4u;
         const uint32_t lchunk = (uint32_t)(lane >> 2);
-        const bool has_res2 = d.res2 != nullptr;
-        if (has_res2) {   // rare (MRF accumulation): fold the second residual into the staging tile first
-          const float* r2 = d.res2 + ((size_t)b * d.L_out + row0) * d.res2_pitch + chan;
-#pragma unroll 8
+        if (has_res) {
+#pragma unroll
           for (int jj = 0; jj < 32; ++jj) {
-            const uint32_t ad = sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4);
-            float t = 0.f;
-            if (has_res) asm volatile("ld.shared.f32 %0, [%1];" : "=f"(t) : "r"(ad));
-            if (jj < nvalid) t += __ldg(r2 + (size_t)jj * d.res2_pitch);
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(ad), "f"(t) : "memory");
+            float r;
+            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)));
+            v[jj] += r;
           }
         }
-        const bool rd = has_res || has_res2;
+        float s_ = 0.f, q_ = 0.f;
 #pragma unroll
-        for (int h2 = 0; h2 < 2; ++h2) {
-          float rr[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int jj = h2 * 16 + i;
-            rr[i] = 0.f;
-            if (rd)
-              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(rr[i]) : "r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)));
-          }
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int jj = h2 * 16 + i;
-            const float o = jj < nvalid ? (v[jj] + bias_c + rr[i]) * d.scale : 0.f;
-            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)), "f"(o) : "memory");
-            s_ += o;
-            q_ = fmaf(o, o, q_);
-          }
+        for (int jj = 0; jj < 32; ++jj) {
+          v[jj] = jj < nvalid ? (v[jj] + bias_c) * d.scale : 0.f;
+          s_ += v[jj];
+          q_ = fmaf(v[jj], v[jj], q_);
         }
         acc_s += (double)s_;
         acc_q += (double)q_;
-        if (has_st) ptx::fence_proxy_async();            // staging writes -> visible to the TMA store
-        __syncwarp();
-        if (has_st && lane == 0) {
-          if (d.out) ptx::tma_store_3d(&tmOut, st, ch0, row0, b);   // rows >= L_out are clipped by the tensor map
-          if (d.out_add) ptx::tma_reduce_add_3d(&tmAdd, st, ch0, row0, b);
-          ptx::bulk_commit();
-        }
-        if (d.out_act) {
+        if (via_smem) {
 #pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int r = it * 8 + (lane >> 2), c8 = lane & 3;
-            if (r < nvalid) {
-              const float4 t0 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8) ^ (r & 7)) << 2));
-              const float4 t1 = *reinterpret_cast<const float4*>(st + r * 32 + (((2 * c8 + 1) ^ (r & 7)) << 2));
-              uint4 q4;
-              if (act_id) {
-                q4.x = fv_pack(t0.x, t0.y); q4.y = fv_pack(t0.z, t0.w);
-                q4.z = fv_pack(t1.x, t1.y); q4.w = fv_pack(t1.z, t1.w);
-              } else {
-                q4.x = fv_pack(leaky(t0.x, d.act_slope), leaky(t0.y, d.act_slope));
-                q4.y = fv_pack(leaky(t0.z, d.act_slope), leaky(t0.w, d.act_slope));
-                q4.z = fv_pack(leaky(t1.x, d.act_slope), leaky(t1.y, d.act_slope));
-                q4.w = fv_pack(leaky(t1.z, d.act_slope), leaky(t1.w, d.act_slope));
-              }
-              *reinterpret_cast<uint4*>((__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0 + r) * d.act_pitch + ch0 + c8 * 8) = q4;
-            }
+          for (int jj = 0; jj < 32; ++jj)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbase + (uint32_t)jj * 128u + ((lchunk ^ (uint32_t)(jj & 7)) << 4)), "f"(v[jj]) : "memory");
+          ptx::fence_proxy_async();                      // staging writes -> visible to the TMA engine
+          __syncwarp();
+          if (lane == 0) {
+            if (d.out) ptx::tma_store_3d(&tmOut, st, ch0, row0, b);   // rows >= L_out are clipped by the tensor map
+            ptx::tma_reduce_add_3d(&tmAdd, st, ch0, row0, b);
+            ptx::bulk_commit();
           }
+        } else if (d.out && nvalid > 0) {
+          float* op = d.out + ((size_t)b * d.L_out + row0) * d.out_pitch + chan;
+          if (d.out_pitch == 128) store_f32(op, 128, v, nvalid);
+          else store_f32(op, d.out_pitch, v, nvalid);
         }
-        __syncwarp();                                    // everyone is done reading this staging tile
-        if (has_res && lane == 0) {
-          if (has_st) ptx::bulk_wait_read<0>();          // ... and so is the TMA store
-          issue_res(n + 2);
+        if (d.out_act && nvalid > 0) {
+          __nv_bfloat16* ap = (__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0) * d.act_pitch + chan;
+          if (d.act_pitch == 128) store_bf16(ap, 128, v, nvalid);
+          else store_bf16(ap, d.act_pitch, v, nvalid);
+        }
+        if (has_res) {
+          __syncwarp();                                  // everyone is done reading this staging tile
+          if (lane == 0) {
+            if (via_smem) ptx::bulk_wait_read<0>();      // ... and so is the TMA engine
+            issue_res(n + 2);
+          }
         }
       }
     }
     if (do_stats) flush_stats(stat_b);
     if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
-    if (has_st && lane == 0) ptx::bulk_wait<0>();        // all TMA stores have completed before the CTA retires
+    if (via_smem && lane == 0) ptx::bulk_wait<0>();      // all TMA stores have completed before the CTA retires
     } else {
     // Work item n = (tile j, chunk c) of this warp: 32 rows (TMEM lane group lg of sub-tile mt) x 32 columns.
     const int ew = warp - FV_EPI_WARP0;
@@ -652,19 +653,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
         }
-        const bool has_res2 = d.res2 != nullptr;
-        if (has_res2) {   // rare (MRF accumulation): fold the second residual into the staging tile first
-          const float4* r2 = reinterpret_cast<const float4*>(d.res2 + ((size_t)b * d.L_out + (row_ok ? m : 0)) * d.res2_pitch + cbase);
-#pragma unroll
-          for (int c4 = 0; c4 < 8; ++c4) {
-            float4* sp = reinterpret_cast<float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (has_res) t = *sp;
-            if (row_ok) { const float4 u = __ldg(r2 + c4); t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
-            *sp = t;
-          }
-        }
-        const bool rd = has_res || has_res2;
+        const bool rd = has_res;
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {   // loads batched ahead of the stores, four 16-byte chunks at a time
           float4 rr[4];
@@ -854,8 +843,10 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
   KK_CHECK_ARG(!d->res || (((uintptr_t)d->res & 15) == 0 && d->res_pitch % 4 == 0 && d->res_shift == 0 &&
                            d->L_res == d->L_out),
                "kk_conv1d_adain_bf16_tc: residual must be 16-byte aligned, same length as the output, no shift");
-  KK_CHECK_ARG(!d->res2 || (((uintptr_t)d->res2 & 15) == 0 && d->res2_pitch % 4 == 0),
-               "kk_conv1d_adain_bf16_tc: second residual must be 16-byte aligned with a pitch multiple of 4");
+  if (d->res2) {
+    kk::set_error("kk_conv1d_adain_bf16_tc: a second residual is not supported here; accumulate with out_add instead");
+    return KK_ERR_UNSUPPORTED;
+  }
   KK_CHECK_ARG(!d->bias || ((uintptr_t)d->bias & 15) == 0, "kk_conv1d_adain_bf16_tc: bias must be 16-byte aligned");
   KK_CHECK_ARG(!d->out_act || (d->act_is_bf16 && ((uintptr_t)d->out_act & 15) == 0 && d->act_pitch % 8 == 0),
                "kk_conv1d_adain_bf16_tc: out_act must be bf16, 16-byte aligned, pitch multiple of 8");
