@@ -59,11 +59,11 @@ struct FvCfg {
   static constexpr int OFF_RAW = OFF_STG + STG_HALF;             // aliases staging half 1
   static constexpr int OFF_COEF = OFF_STG + 2 * STG_HALF;
   static constexpr int OFF_BAR = OFF_COEF + COEF_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + 512 + 1024;
+  static constexpr int SMEM_BYTES = OFF_BAR + 640 + 1024;
   static constexpr uint32_t TMEM_COLS = 512;
   static_assert(SLOT_ROWS >= 128 * MT + FV_HALO_MAX && SLOT_ROWS % 32 == 0, "slot too small");
   static_assert(2 * MT * BN <= 512, "accumulators exceed tensor memory");
-  static_assert(NRAW <= FV_MAX_RAW && STAGES <= 4, "barrier arrays");
+  static_assert(NRAW <= FV_MAX_RAW && STAGES + STG_HALF / B_BYTES <= 8, "barrier arrays");
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
 
@@ -210,9 +210,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   uint64_t* x_full = a_empty + 3;                                        // [3] bf16 input landed in the slot
   uint64_t* raw_full = x_full + 3;                                       // [FV_MAX_RAW]
   uint64_t* raw_empty = raw_full + FV_MAX_RAW;                           // [FV_MAX_RAW]
-  uint64_t* b_full = raw_empty + FV_MAX_RAW;                             // [4]
-  uint64_t* b_empty = b_full + 4;                                        // [4]
-  uint64_t* tmem_full = b_empty + 4;                                     // [2]
+  uint64_t* b_full = raw_empty + FV_MAX_RAW;                             // [8]
+  uint64_t* b_empty = b_full + 8;                                        // [8]
+  uint64_t* tmem_full = b_empty + 8;                                     // [2]
   uint64_t* tmem_empty = tmem_full + 2;                                  // [2]
   uint64_t* res_full = tmem_empty + 2;                                   // [FV_EPI_WARPS * 2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + FV_EPI_WARPS * 2);
@@ -223,6 +223,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const int nbox = (R + FV_BOX_ROWS - 1) / FV_BOX_ROWS;  // 32-row TMA boxes per block
   const bool has_res = d.res != nullptr;
   const bool act_id = d.act_slope == 1.0f;   // out_act is a plain bf16 copy
+  // weight ring depth: when the epilogue does not use staging half 0 (SWAP, no residual, no reduce-add) the ring
+  // grows into it (the two regions are adjacent)
+  const uint32_t nst = (SWAP && d.res == nullptr && d.out_add == nullptr) ? Cfg::STAGES + Cfg::STG_HALF / Cfg::B_BYTES : Cfg::STAGES;
   const bool has_st = d.out != nullptr || d.out_add != nullptr;   // the staging tile leaves by TMA (store and/or reduce-add)
   // fp32 input comes without a residual (host-checked): the raw ring lives in the second staging half
   constexpr int nraw = Cfg::NRAW;
@@ -241,7 +244,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       ptx::mbar_init(&a_empty[s], 1);
       ptx::mbar_init(&x_full[s], 1);
     }
-    for (int s = 0; s < 4; ++s) {
+    for (int s = 0; s < 8; ++s) {
       ptx::mbar_init(&b_full[s], 1);
       ptx::mbar_init(&b_empty[s], 1);
     }
@@ -271,7 +274,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       for (int j = 0; j < t_count; ++j) {
         for (int cb = 0; cb < CB; ++cb) {
           for (int t = 0; t < d.taps; ++t, ++g) {
-            const uint32_t s = g % Cfg::STAGES, ph = (g / Cfg::STAGES) & 1;
+            const uint32_t s = g % nst, ph = (g / nst) & 1;
             FV_WAIT(&b_empty[s], ph ^ 1, w_bempty);
             ptx::mbar_expect_tx(&b_full[s], Cfg::B_BYTES);
             ptx::tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &b_full[s], t * d.Cw + cb * 64, 0);
@@ -302,7 +305,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           ptx::tc_fence_after();
           const uint32_t sa0 = ptx::smem_u32(smem + slot * Cfg::SLOT_BYTES);
           for (int t = 0; t < d.taps; ++t, ++gb) {
-            const uint32_t s = gb % Cfg::STAGES, ph = (gb / Cfg::STAGES) & 1;
+            const uint32_t s = gb % nst, ph = (gb / nst) & 1;
             FV_WAIT(&b_full[s], ph, w_bfull);
             ptx::tc_fence_after();
             const uint32_t sb = ptx::smem_u32(sB + s * Cfg::B_BYTES);

@@ -9,6 +9,7 @@
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-5 = epilogue
 // (warp w owns TMEM lanes 32*(w%4)..+31); warp 2 also allocates / frees tensor memory.
 #include "tc_epilogue.cuh"
+#include <stdlib.h>
 
 namespace kk {
 
@@ -152,17 +153,20 @@ template <int BN>
 struct TpCfg {
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
-  static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 5 : 6);
-  static constexpr int STAGING_BYTES = TP_EPI_WARPS * 4096;
+  static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 4 : 6);
+  static constexpr int NBUF = BN >= 256 ? 1 : 2;             // residual staging tiles per epilogue warp
+  static constexpr int STAGING_BYTES = TP_EPI_WARPS * NBUF * EPI_TILE_BYTES;
   static constexpr int STATS_BYTES = 2 * 8 * BN * 4;  // double-buffered [4 lane groups][sum, sumsq][BN]
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES + 256 + 1024;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES + 384 + 1024;
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget");
   static constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
 };
 
 template <int BN>
 __global__ void __launch_bounds__(TP_THREADS, 1)
 conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                              const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles) {
+                              const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles,
+                              const int direct_epi) {
   using Cfg = TpCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -173,7 +177,8 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
   uint64_t* empty_bar = full_bar + Cfg::STAGES;
   uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  uint64_t* res_bar = tmem_empty_bar + 2;              // [TP_EPI_WARPS * NBUF]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + TP_EPI_WARPS * Cfg::NBUF);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
@@ -190,6 +195,7 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
       ptx::mbar_init(&tmem_full_bar[a], 1);
       ptx::mbar_init(&tmem_empty_bar[a], TP_EPI_WARPS * 32);
     }
+    for (int i = 0; i < TP_EPI_WARPS * Cfg::NBUF; ++i) ptx::mbar_init(&res_bar[i], 1);
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -260,7 +266,23 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
     const int ch_first = half * CH_PER;
     const int n_mine = (CHUNKS - ch_first) < CH_PER ? (CHUNKS - ch_first) : CH_PER;   // chunks of this warp (may be <= 0)
     float4 tres[8];
-    if (n_mine > 0 && (int)blockIdx.x < total_tiles) {
+    // direct epilogue: item n = (n / n_mine)-th tile of this CTA, chunk ch_first + n % n_mine
+    constexpr int NBUF = Cfg::NBUF;
+    uint8_t* stg = reinterpret_cast<uint8_t*>(staging) + ew * (NBUF * EPI_TILE_BYTES);
+    uint64_t* rbar = res_bar + ew * NBUF;
+    uint32_t item = 0;
+    auto issue_res = [&](uint32_t n) {
+      const int tl = blockIdx.x + (int)(n / (uint32_t)n_mine) * gridDim.x;
+      if (tl >= total_tiles) return;
+      const int rest = tl / n_tiles;
+      epi_issue_res(d, rest / m_tiles, (rest % m_tiles) * TC_BM + lg * 32,
+                    (tl % n_tiles) * BN + (ch_first + (int)(n % (uint32_t)n_mine)) * 32, lane,
+                    stg + (n % NBUF) * EPI_TILE_BYTES, &rbar[n % NBUF]);
+    };
+    if (direct_epi) {
+      if (d.res && n_mine > 0)
+        for (int i = 0; i < NBUF; ++i) issue_res(i);
+    } else if (n_mine > 0 && (int)blockIdx.x < total_tiles) {
       const int rest = blockIdx.x / n_tiles;
       epi_prefetch_chunk(d, rest / m_tiles, (rest % m_tiles) * TC_BM, (blockIdx.x % n_tiles) * BN, ch_first, lg, lane, tres);
     }
@@ -282,9 +304,23 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
         const int ch = ch_first + c;
         const bool last = c + 1 == n_mine;
         float cs = 0.f, cq = 0.f;
-        epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, do_stats, cs, cq, tres,
-                           last ? more : true, last ? nx_b : b, last ? nx_m0 : m0, last ? nx_n0 : n0,
-                           last ? ch_first : ch + 1);
+        if (direct_epi) {
+          const uint32_t bufi = item % NBUF;
+          epilogue_chunk_direct(d, b, m0 + lg * 32, n0 + ch * 32, lane,
+                                tmem_base + acc * BN + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32),
+                                stg + bufi * EPI_TILE_BYTES, &rbar[bufi], (item / NBUF) & 1, do_stats, cs, cq);
+          if (d.res) {
+            if (d.out) ptx::bulk_wait_read<0>();      // the lane's row store has read the tile
+            ptx::fence_proxy_async();                 // generic accesses to the tile precede the next TMA write
+            __syncwarp();
+            issue_res(item + NBUF);
+          }
+          ++item;
+        } else {
+          epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, do_stats, cs, cq, tres,
+                             last ? more : true, last ? nx_b : b, last ? nx_m0 : m0, last ? nx_n0 : n0,
+                             last ? ch_first : ch + 1);
+        }
         if (do_stats) { s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = cs; s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = cq; }
       }
       // all tcgen05.ld of this thread have completed (wait::ld inside the chunk): hand the accumulator back
@@ -304,6 +340,7 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
         }
       }
     }
+    if (direct_epi) ptx::bulk_wait<0>();   // every TMA store of this lane has completed before the CTA retires
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -419,7 +456,15 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
   const long long total = (long long)m_tiles * n_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_bf16_tc: too many tiles");
   const int grid = (int)(total < num_sms() ? total : num_sms());
-  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, *d, m_tiles, n_tiles, (int)total);
+  // direct epilogue (tc_epilogue.cuh): every 32-column chunk full, 16-byte aligned rows, one residual at most
+  auto al16 = [](const void* p, long long pitch_bytes) { return (((uintptr_t)p | (uintptr_t)pitch_bytes) & 15) == 0; };
+  static const bool allow_direct = !(getenv("KK_TC_DIRECT") && atoi(getenv("KK_TC_DIRECT")) == 0);   // A/B knob
+  const int direct = allow_direct && d->N % 32 == 0 && (d->up == 1 || d->C_out % 32 == 0) && !d->res2 &&
+                     (!d->out || al16(d->out, (long long)d->out_pitch * 4)) &&
+                     (!d->res || al16(d->res, (long long)d->res_pitch * 4)) && (!d->bias || al16(d->bias, 0)) &&
+                     (!d->out_act || (d->act_is_bf16 && al16(d->out_act, (long long)d->act_pitch * 2)));
+  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, *d, m_tiles, n_tiles, (int)total,
+                                                                               direct);
   KK_LAUNCH_CHECK("conv1d_bf16_tc_persist_kernel");
   return KK_OK;
 }

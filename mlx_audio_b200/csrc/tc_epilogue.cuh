@@ -232,4 +232,113 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// "Direct" epilogue (every chunk full and 16-byte aligned, no second residual - decided on the host):
+//   * the residual rows arrive in a warp-private staging tile by TMA linear copies, one 128-byte row segment per
+//     lane, issued EPI_NBUF chunks ahead (register loads cannot keep enough bytes in flight per warp:
+//     profiles/r01_inflight_bw_probe.txt); a row-wise copy handles the polyphase row mapping, the shortcut's
+//     row shift and the utterance edges by per-lane predication, with no tensor map;
+//   * TMEM hands out lane = row, so every lane owns 32 consecutive channels = one 128-byte segment of its
+//     output row: it is written into the lane's staging row and leaves by a TMA linear store (STG from registers
+//     measured slower: 1.2-1.6 TB/s); the bf16 activation copy (64-byte segments) goes straight from registers;
+//   * the same staging tile transposes the result for the per-channel instance-norm sums.
+// Staging rows are padded to 144 bytes: lane = row float4 accesses and lane = column scalar reads are both
+// bank-conflict free.
+constexpr int EPI_ROW_BYTES = 144;
+constexpr int EPI_TILE_BYTES = 32 * EPI_ROW_BYTES;
+constexpr int EPI_NBUF_MAX = 2;   // staging tiles per warp (a warp with one tile waits a little earlier than needed: harmless)
+
+struct EpiRow { int ph, cbase, out_row; bool acc_valid, row_ok; };
+
+__device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const int m, const int nb) {
+  EpiRow e;
+  e.ph = 0; e.cbase = nb;
+  if (d.up > 1) { e.ph = nb / d.C_out; e.cbase = nb - e.ph * d.C_out; }
+  const int j = m * d.up + e.ph - d.up_off;
+  e.acc_valid = (j >= 0) && (j < d.L_true);
+  e.out_row = j + d.left_pad;
+  e.row_ok = (m < d.M) && (e.out_row >= 0) && (e.out_row < d.L_out);
+  return e;
+}
+
+// all lanes: start the residual copy of the chunk whose first column is nb, rows m0w..m0w+31 (lane = row)
+__device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const int b, const int m0w, const int nb,
+                                              const int lane, uint8_t* st, uint64_t* bar) {
+  const EpiRow e = epi_row(d, m0w + lane, nb);
+  const unsigned mask = __ballot_sync(0xffffffffu, e.row_ok);
+  if (lane == 0) ptx::mbar_expect_tx(bar, (uint32_t)__popc(mask) * 128u);
+  __syncwarp();
+  if (e.row_ok)
+    ptx::bulk_load_g2s(st + lane * EPI_ROW_BYTES,
+                       d.res + ((size_t)b * d.L_res + (e.out_row >> d.res_shift)) * d.res_pitch + e.cbase, 128u, bar);
+}
+
+__device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, const int b, const int m0w, const int nb,
+                                                      const int lane, const uint32_t tmem_addr, uint8_t* st,
+                                                      uint64_t* rbar, const uint32_t rparity, const bool do_stats,
+                                                      float& col_sum, float& col_sq) {
+  const EpiRow e = epi_row(d, m0w + lane, nb);
+  float v[32];
+  ptx::tmem_ld_32x32(tmem_addr, v);
+  if (d.res) ptx::mbar_wait(rbar, rparity);
+  ptx::tmem_ld_wait();
+  const float4* rrow = reinterpret_cast<const float4*>(st + lane * EPI_ROW_BYTES);
+#pragma unroll
+  for (int c4 = 0; c4 < 8; ++c4) {
+    float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (d.res && e.row_ok) rr = rrow[c4];
+    float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + e.cbase + c4 * 4));
+    const float x0 = e.acc_valid ? v[c4 * 4 + 0] + bs.x : 0.f;
+    const float x1 = e.acc_valid ? v[c4 * 4 + 1] + bs.y : 0.f;
+    const float x2 = e.acc_valid ? v[c4 * 4 + 2] + bs.z : 0.f;
+    const float x3 = e.acc_valid ? v[c4 * 4 + 3] + bs.w : 0.f;
+    v[c4 * 4 + 0] = e.row_ok ? (x0 + rr.x) * d.scale : 0.f;
+    v[c4 * 4 + 1] = e.row_ok ? (x1 + rr.y) * d.scale : 0.f;
+    v[c4 * 4 + 2] = e.row_ok ? (x2 + rr.z) * d.scale : 0.f;
+    v[c4 * 4 + 3] = e.row_ok ? (x3 + rr.w) * d.scale : 0.f;
+  }
+  const size_t orow = (size_t)b * d.L_out + (e.row_ok ? e.out_row : 0);
+  if (e.row_ok && d.out_act) {
+    uint4* ap = reinterpret_cast<uint4*>((__nv_bfloat16*)d.out_act + orow * d.act_pitch + e.cbase);
+#pragma unroll
+    for (int c8 = 0; c8 < 4; ++c8) {
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(leaky(v[c8 * 8 + 0], d.act_slope), leaky(v[c8 * 8 + 1], d.act_slope));
+      __nv_bfloat162 p1 = __floats2bfloat162_rn(leaky(v[c8 * 8 + 2], d.act_slope), leaky(v[c8 * 8 + 3], d.act_slope));
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(leaky(v[c8 * 8 + 4], d.act_slope), leaky(v[c8 * 8 + 5], d.act_slope));
+      __nv_bfloat162 p3 = __floats2bfloat162_rn(leaky(v[c8 * 8 + 6], d.act_slope), leaky(v[c8 * 8 + 7], d.act_slope));
+      uint4 q;
+      q.x = *reinterpret_cast<uint32_t*>(&p0); q.y = *reinterpret_cast<uint32_t*>(&p1);
+      q.z = *reinterpret_cast<uint32_t*>(&p2); q.w = *reinterpret_cast<uint32_t*>(&p3);
+      ap[c8] = q;
+    }
+  }
+  if (d.out || do_stats) {
+    if (!d.res) ptx::bulk_wait_read<EPI_NBUF_MAX - 1>();   // this lane's store out of the tile (NBUF items ago) has read it
+    __syncwarp();                                  // every lane has taken its residual row out of the tile
+    float4* wrow = reinterpret_cast<float4*>(st + lane * EPI_ROW_BYTES);
+#pragma unroll
+    for (int c4 = 0; c4 < 8; ++c4) wrow[c4] = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+    if (d.out) {
+      ptx::fence_proxy_async();                    // the lane's own row: generic writes -> visible to the TMA engine
+      if (e.row_ok) ptx::bulk_store_s2g(d.out + orow * d.out_pitch + e.cbase, wrow, 128u);
+      ptx::bulk_commit();
+    }
+  }
+  if (do_stats) {
+    __syncwarp();
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;   // lane = column: sums over the warp's 32 rows
+#pragma unroll
+    for (int r = 0; r < 32; r += 2) {
+      const float a0 = *reinterpret_cast<const float*>(st + r * EPI_ROW_BYTES + lane * 4);
+      const float a1 = *reinterpret_cast<const float*>(st + (r + 1) * EPI_ROW_BYTES + lane * 4);
+      s0 += a0; q0 = fmaf(a0, a0, q0);
+      s1 += a1; q1 = fmaf(a1, a1, q1);
+    }
+    col_sum = s0 + s1;
+    col_sq = q0 + q1;
+  }
+  __syncwarp();                                    // the tile may be overwritten by the next residual copy
+}
+
 }  // namespace kk
