@@ -154,7 +154,7 @@ struct TpCfg {
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
   static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 4 : 6);
-  static constexpr int NBUF = BN >= 256 ? 1 : 2;             // residual staging tiles per epilogue warp
+  static constexpr int NBUF = EPI_NBUF;                      // residual staging tiles per epilogue warp
   static constexpr int STAGING_BYTES = TP_EPI_WARPS * NBUF * EPI_TILE_BYTES;
   static constexpr int STATS_BYTES = 2 * 8 * BN * 4;  // double-buffered [4 lane groups][sum, sumsq][BN]
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES + 384 + 1024;
@@ -165,6 +165,7 @@ struct TpCfg {
 template <int BN>
 __global__ void __launch_bounds__(TP_THREADS, 1)
 conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                              const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
                               const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles,
                               const int direct_epi) {
   using Cfg = TpCfg<BN>;
@@ -275,7 +276,7 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
       const int tl = blockIdx.x + (int)(n / (uint32_t)n_mine) * gridDim.x;
       if (tl >= total_tiles) return;
       const int rest = tl / n_tiles;
-      epi_issue_res(d, rest / m_tiles, (rest % m_tiles) * TC_BM + lg * 32,
+      epi_issue_res(d, &tmRes, rest / m_tiles, (rest % m_tiles) * TC_BM + lg * 32,
                     (tl % n_tiles) * BN + (ch_first + (int)(n % (uint32_t)n_mine)) * 32, lane,
                     stg + (n % NBUF) * EPI_TILE_BYTES, &rbar[n % NBUF]);
     };
@@ -306,7 +307,7 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
         float cs = 0.f, cq = 0.f;
         if (direct_epi) {
           const uint32_t bufi = item % NBUF;
-          epilogue_chunk_direct(d, b, m0 + lg * 32, n0 + ch * 32, lane,
+          epilogue_chunk_direct(d, &tmOut, b, m0 + lg * 32, n0 + ch * 32, lane,
                                 tmem_base + acc * BN + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32),
                                 stg + bufi * EPI_TILE_BYTES, &rbar[bufi], (item / NBUF) & 1, do_stats, cs, cq);
           if (d.res) {
@@ -463,8 +464,31 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
                      (!d->out || al16(d->out, (long long)d->out_pitch * 4)) &&
                      (!d->res || al16(d->res, (long long)d->res_pitch * 4)) && (!d->bias || al16(d->bias, 0)) &&
                      (!d->out_act || (d->act_is_bf16 && al16(d->out_act, (long long)d->act_pitch * 2)));
-  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, *d, m_tiles, n_tiles, (int)total,
-                                                                               direct);
+  // rank-4 polyphase views (tc_epilogue.cuh) of the residual and output tensors; only coordinates whose rows lie
+  // inside the utterance are ever issued, so the (possibly negative) row offset folded into the base is harmless
+  CUtensorMap tmRes = tmB, tmOut = tmB;
+  if (direct) {
+    const long long off = (long long)d->left_pad - d->up_off;
+    cuuint32_t box[4] = {32, 1, 32, 1};
+    if (d->res && d->res_shift == 0) {
+      cuuint64_t dims[4] = {(cuuint64_t)d->C_out, (cuuint64_t)d->up, (cuuint64_t)d->M, (cuuint64_t)d->B};
+      cuuint64_t strides[3] = {(cuuint64_t)d->res_pitch * 4, (cuuint64_t)d->up * d->res_pitch * 4,
+                               (cuuint64_t)d->L_res * d->res_pitch * 4};
+      int rc = make_tmap(&tmRes, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->res + off * d->res_pitch, 4, dims, strides, box,
+                         CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
+    if (d->out) {
+      cuuint64_t dims[4] = {(cuuint64_t)d->C_out, (cuuint64_t)d->up, (cuuint64_t)d->M, (cuuint64_t)d->B};
+      cuuint64_t strides[3] = {(cuuint64_t)d->out_pitch * 4, (cuuint64_t)d->up * d->out_pitch * 4,
+                               (cuuint64_t)d->L_out * d->out_pitch * 4};
+      int rc = make_tmap(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->out + off * d->out_pitch, 4, dims, strides, box,
+                         CU_TENSOR_MAP_SWIZZLE_128B);
+      if (rc) return rc;
+    }
+  }
+  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, tmRes, tmOut, *d, m_tiles, n_tiles,
+                                                                               (int)total, direct);
   KK_LAUNCH_CHECK("conv1d_bf16_tc_persist_kernel");
   return KK_OK;
 }

@@ -233,20 +233,20 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// "Direct" epilogue (every chunk full and 16-byte aligned, no second residual - decided on the host):
-//   * the residual rows arrive in a warp-private staging tile by TMA linear copies, one 128-byte row segment per
-//     lane, issued EPI_NBUF chunks ahead (register loads cannot keep enough bytes in flight per warp:
-//     profiles/r01_inflight_bw_probe.txt); a row-wise copy handles the polyphase row mapping, the shortcut's
-//     row shift and the utterance edges by per-lane predication, with no tensor map;
-//   * TMEM hands out lane = row, so every lane owns 32 consecutive channels = one 128-byte segment of its
-//     output row: it is written into the lane's staging row and leaves by a TMA linear store (STG from registers
-//     measured slower: 1.2-1.6 TB/s); the bf16 activation copy (64-byte segments) goes straight from registers;
-//   * the same staging tile transposes the result for the per-channel instance-norm sums.
-// Staging rows are padded to 144 bytes: lane = row float4 accesses and lane = column scalar reads are both
-// bank-conflict free.
-constexpr int EPI_ROW_BYTES = 144;
-constexpr int EPI_TILE_BYTES = 32 * EPI_ROW_BYTES;
-constexpr int EPI_NBUF_MAX = 2;   // staging tiles per warp (a warp with one tile waits a little earlier than needed: harmless)
+// TMA epilogue (every chunk full and 16-byte aligned, no second residual - decided on the host).  Register
+// loads / stores cannot keep enough bytes in flight per warp (profiles/r01_inflight_bw_probe.txt), so both the
+// residual and the result travel through a warp-private 32x32 fp32 staging tile by TMA:
+//   * interior chunks (all 32 rows of the warp map to rows inside the utterance): ONE 4 KB tensor-map box per
+//     transfer.  The tensor map is the rank-4 view  V[b][m][phase][c] = T[b][m*up + phase - up_off + left_pad][c]
+//     of the (B, L_out, pitch) tensor, so that the polyphase (transposed-conv) row interleave is just a
+//     coordinate; the box is written with the 128-byte swizzle (16-byte chunk ^= row & 7), which makes the
+//     lane = row float4 accesses and the lane = column scalar reads (instance-norm sums) bank-conflict free;
+//   * edge chunks (first / last rows of an utterance, or a row-shifted shortcut): one 128-byte linear copy per
+//     valid row, unswizzled (rare, so the bank conflicts do not matter).  A 128-byte request costs the TMA unit
+//     about as much as a 4 KB one (~20 clk), which is why this is the fallback and not the rule.
+// The bf16 activation copy (64-byte row segments) goes straight from registers.
+constexpr int EPI_TILE_BYTES = 4096;
+constexpr int EPI_NBUF = 2;        // staging tiles per epilogue warp = residual prefetch distance
 
 struct EpiRow { int ph, cbase, out_row; bool acc_valid, row_ok; };
 
@@ -261,32 +261,50 @@ __device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const int m, co
   return e;
 }
 
-// all lanes: start the residual copy of the chunk whose first column is nb, rows m0w..m0w+31 (lane = row)
-__device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const int b, const int m0w, const int nb,
-                                              const int lane, uint8_t* st, uint64_t* bar) {
+// warp-uniform: do rows m0w .. m0w+31 of the chunk starting at column nb all land inside the utterance?
+__device__ __forceinline__ bool epi_interior(const kk_conv_desc& d, const int m0w, const int nb) {
+  const int ph = d.up > 1 ? nb / d.C_out : 0;
+  const int r0 = m0w * d.up + ph - d.up_off + d.left_pad;
+  return m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < d.L_out;
+}
+
+// all lanes: start the residual transfer of the chunk whose first column is nb, rows m0w..m0w+31 (lane = row)
+__device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const CUtensorMap* tmRes, const int b, const int m0w,
+                                              const int nb, const int lane, uint8_t* st, uint64_t* bar) {
   const EpiRow e = epi_row(d, m0w + lane, nb);
+  if (d.res_shift == 0 && epi_interior(d, m0w, nb)) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(bar, EPI_TILE_BYTES);
+      ptx::tma_load_4d(st, tmRes, bar, e.cbase, e.ph, m0w, b);
+    }
+    return;
+  }
   const unsigned mask = __ballot_sync(0xffffffffu, e.row_ok);
   if (lane == 0) ptx::mbar_expect_tx(bar, (uint32_t)__popc(mask) * 128u);
   __syncwarp();
   if (e.row_ok)
-    ptx::bulk_load_g2s(st + lane * EPI_ROW_BYTES,
-                       d.res + ((size_t)b * d.L_res + (e.out_row >> d.res_shift)) * d.res_pitch + e.cbase, 128u, bar);
+    ptx::bulk_load_g2s(st + lane * 128, d.res + ((size_t)b * d.L_res + (e.out_row >> d.res_shift)) * d.res_pitch + e.cbase,
+                       128u, bar);
 }
 
-__device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, const int b, const int m0w, const int nb,
-                                                      const int lane, const uint32_t tmem_addr, uint8_t* st,
-                                                      uint64_t* rbar, const uint32_t rparity, const bool do_stats,
-                                                      float& col_sum, float& col_sq) {
+__device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, const CUtensorMap* tmOut, const int b,
+                                                      const int m0w, const int nb, const int lane,
+                                                      const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
+                                                      const uint32_t rparity, const bool do_stats, float& col_sum,
+                                                      float& col_sq) {
   const EpiRow e = epi_row(d, m0w + lane, nb);
+  const bool interior = epi_interior(d, m0w, nb);
+  const int rsw = (d.res_shift == 0 && interior) ? 7 : 0;   // swizzle mask of the tile as the residual was written
+  const int wsw = interior ? 7 : 0;                         // ... and as the result is written
   float v[32];
   ptx::tmem_ld_32x32(tmem_addr, v);
   if (d.res) ptx::mbar_wait(rbar, rparity);
   ptx::tmem_ld_wait();
-  const float4* rrow = reinterpret_cast<const float4*>(st + lane * EPI_ROW_BYTES);
+  float* row = reinterpret_cast<float*>(st) + lane * 32;
 #pragma unroll
   for (int c4 = 0; c4 < 8; ++c4) {
     float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (d.res && e.row_ok) rr = rrow[c4];
+    if (d.res && e.row_ok) rr = *reinterpret_cast<const float4*>(row + ((c4 ^ (lane & rsw)) << 2));
     float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
     if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + e.cbase + c4 * 4));
     const float x0 = e.acc_valid ? v[c4 * 4 + 0] + bs.x : 0.f;
@@ -314,24 +332,30 @@ __device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, con
     }
   }
   if (d.out || do_stats) {
-    if (!d.res) ptx::bulk_wait_read<EPI_NBUF_MAX - 1>();   // this lane's store out of the tile (NBUF items ago) has read it
-    __syncwarp();                                  // every lane has taken its residual row out of the tile
-    float4* wrow = reinterpret_cast<float4*>(st + lane * EPI_ROW_BYTES);
+    if (!d.res) ptx::bulk_wait_read<EPI_NBUF - 1>();   // the store that left this tile EPI_NBUF items ago has read it
+    __syncwarp();                                      // ... for every lane; and every lane holds its residual row
 #pragma unroll
-    for (int c4 = 0; c4 < 8; ++c4) wrow[c4] = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+    for (int c4 = 0; c4 < 8; ++c4)
+      *reinterpret_cast<float4*>(row + ((c4 ^ (lane & wsw)) << 2)) = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
     if (d.out) {
-      ptx::fence_proxy_async();                    // the lane's own row: generic writes -> visible to the TMA engine
-      if (e.row_ok) ptx::bulk_store_s2g(d.out + orow * d.out_pitch + e.cbase, wrow, 128u);
+      ptx::fence_proxy_async();                        // generic writes -> visible to the TMA engine
+      if (interior) {
+        __syncwarp();
+        if (lane == 0) ptx::tma_store_4d(tmOut, st, e.cbase, e.ph, m0w, b);
+      } else if (e.row_ok) {
+        ptx::bulk_store_s2g(d.out + orow * d.out_pitch + e.cbase, row, 128u);
+      }
       ptx::bulk_commit();
     }
   }
   if (do_stats) {
     __syncwarp();
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;   // lane = column: sums over the warp's 32 rows
+    const int cc = lane >> 2, ci = lane & 3;
 #pragma unroll
     for (int r = 0; r < 32; r += 2) {
-      const float a0 = *reinterpret_cast<const float*>(st + r * EPI_ROW_BYTES + lane * 4);
-      const float a1 = *reinterpret_cast<const float*>(st + (r + 1) * EPI_ROW_BYTES + lane * 4);
+      const float a0 = reinterpret_cast<const float*>(st)[r * 32 + ((cc ^ (r & wsw)) << 2) + ci];
+      const float a1 = reinterpret_cast<const float*>(st)[(r + 1) * 32 + ((cc ^ ((r + 1) & wsw)) << 2) + ci];
       s0 += a0; q0 = fmaf(a0, a0, q0);
       s1 += a1; q1 = fmaf(a1, a1, q1);
     }
