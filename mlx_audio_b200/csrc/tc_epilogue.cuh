@@ -261,11 +261,12 @@ __device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const int m, co
   return e;
 }
 
-// warp-uniform: do rows m0w .. m0w+31 of the chunk starting at column nb all land inside the utterance?
+// warp-uniform: do rows m0w .. m0w+31 of the chunk starting at column nb all land inside the utterance (and inside
+// the true convolution output, so that no element needs masking)?
 __device__ __forceinline__ bool epi_interior(const kk_conv_desc& d, const int m0w, const int nb) {
   const int ph = d.up > 1 ? nb / d.C_out : 0;
-  const int r0 = m0w * d.up + ph - d.up_off + d.left_pad;
-  return m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < d.L_out;
+  const int j0 = m0w * d.up + ph - d.up_off, r0 = j0 + d.left_pad;
+  return m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < d.L_out && j0 >= 0 && j0 + 31 * d.up < d.L_true;
 }
 
 // all lanes: start the residual transfer of the chunk whose first column is nb, rows m0w..m0w+31 (lane = row)
@@ -287,37 +288,57 @@ __device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const CUten
                        128u, bar);
 }
 
-__device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, const CUtensorMap* tmOut, const int b,
-                                                      const int m0w, const int nb, const int lane,
-                                                      const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
-                                                      const uint32_t rparity, const bool do_stats, float& col_sum,
-                                                      float& col_sq) {
+// INTERIOR: no masking anywhere, swizzled tile, box transfers.  Otherwise: per-element masks, plain tile, row copies.
+template <bool INTERIOR>
+__device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, const CUtensorMap* tmOut, const int b,
+                                                        const int m0w, const int nb, const int lane,
+                                                        const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
+                                                        const uint32_t rparity, const bool do_stats, float& col_sum,
+                                                        float& col_sq) {
   const EpiRow e = epi_row(d, m0w + lane, nb);
-  const bool interior = epi_interior(d, m0w, nb);
-  const int rsw = (d.res_shift == 0 && interior) ? 7 : 0;   // swizzle mask of the tile as the residual was written
-  const int wsw = interior ? 7 : 0;                         // ... and as the result is written
+  constexpr int WSW = INTERIOR ? 7 : 0;                                  // swizzle mask of the result tile
+  const int rsw = (INTERIOR && d.res_shift == 0) ? 7 : 0;               // ... and of the tile as the residual arrived
+  const bool acc_valid = INTERIOR || e.acc_valid, row_ok = INTERIOR || e.row_ok;
   float v[32];
   ptx::tmem_ld_32x32(tmem_addr, v);
   if (d.res) ptx::mbar_wait(rbar, rparity);
   ptx::tmem_ld_wait();
   float* row = reinterpret_cast<float*>(st) + lane * 32;
+  if (d.res) {
 #pragma unroll
-  for (int c4 = 0; c4 < 8; ++c4) {
-    float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (d.res && e.row_ok) rr = *reinterpret_cast<const float4*>(row + ((c4 ^ (lane & rsw)) << 2));
-    float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + e.cbase + c4 * 4));
-    const float x0 = e.acc_valid ? v[c4 * 4 + 0] + bs.x : 0.f;
-    const float x1 = e.acc_valid ? v[c4 * 4 + 1] + bs.y : 0.f;
-    const float x2 = e.acc_valid ? v[c4 * 4 + 2] + bs.z : 0.f;
-    const float x3 = e.acc_valid ? v[c4 * 4 + 3] + bs.w : 0.f;
-    v[c4 * 4 + 0] = e.row_ok ? (x0 + rr.x) * d.scale : 0.f;
-    v[c4 * 4 + 1] = e.row_ok ? (x1 + rr.y) * d.scale : 0.f;
-    v[c4 * 4 + 2] = e.row_ok ? (x2 + rr.z) * d.scale : 0.f;
-    v[c4 * 4 + 3] = e.row_ok ? (x3 + rr.w) * d.scale : 0.f;
+    for (int c4 = 0; c4 < 8; ++c4) {
+      float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row_ok) rr = *reinterpret_cast<const float4*>(row + ((c4 ^ (lane & rsw)) << 2));
+      v[c4 * 4 + 0] += rr.x; v[c4 * 4 + 1] += rr.y; v[c4 * 4 + 2] += rr.z; v[c4 * 4 + 3] += rr.w;
+    }
   }
-  const size_t orow = (size_t)b * d.L_out + (e.row_ok ? e.out_row : 0);
-  if (e.row_ok && d.out_act) {
+  if (d.bias) {
+#pragma unroll
+    for (int c4 = 0; c4 < 8; ++c4) {
+      const float4 bs = __ldg(reinterpret_cast<const float4*>(d.bias + e.cbase + c4 * 4));
+      v[c4 * 4 + 0] += bs.x; v[c4 * 4 + 1] += bs.y; v[c4 * 4 + 2] += bs.z; v[c4 * 4 + 3] += bs.w;
+    }
+  }
+  if (!INTERIOR) {
+    // accumulator rows outside the true output contribute nothing (the residual still does); rows outside the
+    // utterance are zero
+    const float4* rrow = reinterpret_cast<const float4*>(row);
+#pragma unroll
+    for (int c4 = 0; c4 < 8; ++c4) {
+      if (!acc_valid) {
+        float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (d.res && row_ok) rr = rrow[c4];
+        v[c4 * 4 + 0] = rr.x; v[c4 * 4 + 1] = rr.y; v[c4 * 4 + 2] = rr.z; v[c4 * 4 + 3] = rr.w;
+      }
+      if (!row_ok) v[c4 * 4 + 0] = v[c4 * 4 + 1] = v[c4 * 4 + 2] = v[c4 * 4 + 3] = 0.f;
+    }
+  }
+  if (d.scale != 1.0f) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] *= d.scale;
+  }
+  const size_t orow = (size_t)b * d.L_out + (row_ok ? e.out_row : 0);
+  if (row_ok && d.out_act) {
     uint4* ap = reinterpret_cast<uint4*>((__nv_bfloat16*)d.out_act + orow * d.act_pitch + e.cbase);
 #pragma unroll
     for (int c8 = 0; c8 < 4; ++c8) {
@@ -336,13 +357,13 @@ __device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, con
     __syncwarp();                                      // ... for every lane; and every lane holds its residual row
 #pragma unroll
     for (int c4 = 0; c4 < 8; ++c4)
-      *reinterpret_cast<float4*>(row + ((c4 ^ (lane & wsw)) << 2)) = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
+      *reinterpret_cast<float4*>(row + ((c4 ^ (lane & WSW)) << 2)) = make_float4(v[c4 * 4], v[c4 * 4 + 1], v[c4 * 4 + 2], v[c4 * 4 + 3]);
     if (d.out) {
       ptx::fence_proxy_async();                        // generic writes -> visible to the TMA engine
-      if (interior) {
+      if (INTERIOR) {
         __syncwarp();
         if (lane == 0) ptx::tma_store_4d(tmOut, st, e.cbase, e.ph, m0w, b);
-      } else if (e.row_ok) {
+      } else if (row_ok) {
         ptx::bulk_store_s2g(d.out + orow * d.out_pitch + e.cbase, row, 128u);
       }
       ptx::bulk_commit();
@@ -354,8 +375,8 @@ __device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, con
     const int cc = lane >> 2, ci = lane & 3;
 #pragma unroll
     for (int r = 0; r < 32; r += 2) {
-      const float a0 = reinterpret_cast<const float*>(st)[r * 32 + ((cc ^ (r & wsw)) << 2) + ci];
-      const float a1 = reinterpret_cast<const float*>(st)[(r + 1) * 32 + ((cc ^ ((r + 1) & wsw)) << 2) + ci];
+      const float a0 = reinterpret_cast<const float*>(st)[r * 32 + ((cc ^ (r & WSW)) << 2) + ci];
+      const float a1 = reinterpret_cast<const float*>(st)[(r + 1) * 32 + ((cc ^ ((r + 1) & WSW)) << 2) + ci];
       s0 += a0; q0 = fmaf(a0, a0, q0);
       s1 += a1; q1 = fmaf(a1, a1, q1);
     }
@@ -363,6 +384,17 @@ __device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, con
     col_sq = q0 + q1;
   }
   __syncwarp();                                    // the tile may be overwritten by the next residual copy
+}
+
+__device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, const CUtensorMap* tmOut, const int b,
+                                                      const int m0w, const int nb, const int lane,
+                                                      const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
+                                                      const uint32_t rparity, const bool do_stats, float& col_sum,
+                                                      float& col_sq) {
+  if (epi_interior(d, m0w, nb))
+    epilogue_chunk_direct_t<true>(d, tmOut, b, m0w, nb, lane, tmem_addr, st, rbar, rparity, do_stats, col_sum, col_sq);
+  else
+    epilogue_chunk_direct_t<false>(d, tmOut, b, m0w, nb, lane, tmem_addr, st, rbar, rparity, do_stats, col_sum, col_sq);
 }
 
 }  // namespace kk
