@@ -37,7 +37,10 @@ constexpr int FV_XF_WARP0 = 4;
 constexpr int FV_EPI_WARP0 = 12;
 constexpr int FV_THREADS = (FV_EPI_WARP0 + FV_EPI_WARPS) * 32;  // 640 = 5 warpgroups, launched with 96 registers
 // per-warpgroup register reallocation (setmaxnreg): freed by dec 128*(56 + 2*24) = 13312 >= needed by inc 256*48
-constexpr int FV_REGS_CTRL = 40, FV_REGS_XF = 72, FV_REGS_EPI = 144;
+constexpr int FV_REGS_CTRL = 40;
+// transform / epilogue budgets: <SWAP> 96 / 120 (lean register-store epilogue, the transform is the critical path);
+// otherwise 72 / 144.  Freed by dec: 128*56 (+ 256*24) >= needed by inc: 256*24 (256*48).
+template <bool SWAP> struct FvRegs { static constexpr int XF = SWAP ? 96 : 72, EPI = SWAP ? 120 : 144; };
 constexpr int FV_HALO_MAX = 56;
 constexpr int FV_BOX_ROWS = 32;            // rows per input TMA box
 constexpr int FV_RAW_BYTES = 32 * 256;     // fp32 raw stage: 32 rows x 64 channels
@@ -91,6 +94,50 @@ __device__ __forceinline__ float fv_apply(float x, const float4& k, float slope)
 // 16-byte chunk q): 8 channels cb*64 + 8q.., coefficients in registers; physical chunk = q ^ (row & 7).
 // Batches of XB steps: all loads, then all arithmetic, then all stores (the shared-memory accesses are volatile
 // asm, which the compiler will not reorder - the batching is what exposes the instruction-level parallelism).
+__device__ __forceinline__ float4 fv_lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+
+// NB steps (4 rows each, FV_XF_WARPS steps apart) of the in-place transform: all loads, then all arithmetic, then all
+// stores (the shared-memory accesses are volatile asm, which the compiler will not reorder - the batching is what
+// exposes the instruction-level parallelism).
+template <int ACT, int NB>
+__device__ __forceinline__ void fv_xf_steps(uint32_t slot, const float4 (&k)[8], float slope, int s0, int nrows,
+                                            int l_base, int L_in, int q, int sub) {
+  uint4 t[NB];
+  uint32_t p[NB];
+  bool ok[NB];
+#pragma unroll
+  for (int u = 0; u < NB; ++u) {
+    const int r = 4 * (s0 + u * FV_XF_WARPS) + sub;
+    const int l = l_base + r;
+    p[u] = slot + (uint32_t)r * 128u + (uint32_t)((q ^ (r & 7)) << 4);
+    ok[u] = r < nrows && l >= 0 && l < L_in;
+    t[u] = make_uint4(0u, 0u, 0u, 0u);
+    if (ok[u]) asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t[u].x), "=r"(t[u].y), "=r"(t[u].z), "=r"(t[u].w) : "r"(p[u]));
+  }
+#pragma unroll
+  for (int u = 0; u < NB; ++u) {   // branch-free so that the NB cosine chains interleave
+    const uint4 v = t[u];
+    const uint32_t x0 = fv_pack(fv_apply<ACT>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
+    const uint32_t x1 = fv_pack(fv_apply<ACT>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
+    const uint32_t x2 = fv_pack(fv_apply<ACT>(__uint_as_float(v.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(v.z & 0xffff0000u), k[5], slope));
+    const uint32_t x3 = fv_pack(fv_apply<ACT>(__uint_as_float(v.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(v.w & 0xffff0000u), k[7], slope));
+    // rows outside the utterance are zero: the conv's zero padding (post-activation)
+    t[u].x = ok[u] ? x0 : 0u; t[u].y = ok[u] ? x1 : 0u; t[u].z = ok[u] ? x2 : 0u; t[u].w = ok[u] ? x3 : 0u;
+  }
+#pragma unroll
+  for (int u = 0; u < NB; ++u)
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(p[u]), "r"(t[u].x), "r"(t[u].y), "r"(t[u].z), "r"(t[u].w) : "memory");
+}
+
+// bf16 input, in place: the slot holds rows [0, nrows) as TMA wrote them (128B swizzle).  Lane = (row%4, logical
+// 16-byte chunk q): 8 channels cb*64 + 8q.., coefficients in registers; physical chunk = q ^ (row & 7).
+// Full batches of XB steps per warp, then single steps for the ragged tail (tile + halo is not a multiple of the
+// batch).  Slot rows beyond nrows (up to the next multiple of 4) are written too: they are inside the slot and no
+// MMA reads them.
 template <int ACT>
 __device__ __forceinline__ void fv_xf_inplace(uint32_t slot, const float4* __restrict__ coef, float slope, int cb,
                                               int nrows, int l_base, int L_in, int xw, int lane) {
@@ -98,37 +145,12 @@ __device__ __forceinline__ void fv_xf_inplace(uint32_t slot, const float4* __res
   const int q = lane & 7, sub = lane >> 3;
   float4 k[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) k[i] = coef[cb * 64 + q * 8 + i];
+  for (int i = 0; i < 8; ++i) k[i] = fv_lds128(ptx::smem_u32(coef + cb * 64 + q * 8 + i));
   const int nsteps = (nrows + 3) >> 2;
-  for (int s0 = xw; s0 < nsteps; s0 += FV_XF_WARPS * XB) {
-    uint4 t[XB];
-    uint32_t p[XB];
-    bool ok[XB];
-#pragma unroll
-    for (int u = 0; u < XB; ++u) {
-      const int r = 4 * (s0 + u * FV_XF_WARPS) + sub;
-      const int l = l_base + r;
-      p[u] = slot + (uint32_t)r * 128u + (uint32_t)((q ^ (r & 7)) << 4);
-      ok[u] = r < nrows && l >= 0 && l < L_in;
-      t[u] = make_uint4(0u, 0u, 0u, 0u);
-      if (ok[u]) asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(t[u].x), "=r"(t[u].y), "=r"(t[u].z), "=r"(t[u].w) : "r"(p[u]));
-    }
-#pragma unroll
-    for (int u = 0; u < XB; ++u) {   // branch-free so that the XB sine chains interleave
-      const uint4 v = t[u];
-      const uint32_t x0 = fv_pack(fv_apply<ACT>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
-      const uint32_t x1 = fv_pack(fv_apply<ACT>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
-      const uint32_t x2 = fv_pack(fv_apply<ACT>(__uint_as_float(v.z << 16), k[4], slope), fv_apply<ACT>(__uint_as_float(v.z & 0xffff0000u), k[5], slope));
-      const uint32_t x3 = fv_pack(fv_apply<ACT>(__uint_as_float(v.w << 16), k[6], slope), fv_apply<ACT>(__uint_as_float(v.w & 0xffff0000u), k[7], slope));
-      // rows outside the utterance are zero: the conv's zero padding (post-activation)
-      t[u].x = ok[u] ? x0 : 0u; t[u].y = ok[u] ? x1 : 0u; t[u].z = ok[u] ? x2 : 0u; t[u].w = ok[u] ? x3 : 0u;
-    }
-#pragma unroll
-    for (int u = 0; u < XB; ++u) {
-      if (s0 + u * FV_XF_WARPS < nsteps)
-        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(p[u]), "r"(t[u].x), "r"(t[u].y), "r"(t[u].z), "r"(t[u].w) : "memory");
-    }
-  }
+  int s0 = xw;
+  for (; s0 + (XB - 1) * FV_XF_WARPS < nsteps; s0 += FV_XF_WARPS * XB)
+    fv_xf_steps<ACT, XB>(slot, k, slope, s0, nrows, l_base, L_in, q, sub);
+  for (; s0 < nsteps; s0 += FV_XF_WARPS) fv_xf_steps<ACT, 1>(slot, k, slope, s0, nrows, l_base, L_in, q, sub);
 }
 
 // fp32 input: one raw stage (32 rows x 64 channels, row-major 256 B) -> slot rows [row0, row0 + 32).  A stage is
@@ -225,7 +247,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const bool act_id = d.act_slope == 1.0f;   // out_act is a plain bf16 copy
   // weight ring depth: when the epilogue does not use staging half 0 (SWAP, no residual, no reduce-add) the ring
   // grows into it (the two regions are adjacent)
-  const uint32_t nst = (SWAP && d.res == nullptr && d.out_add == nullptr) ? Cfg::STAGES + Cfg::STG_HALF / Cfg::B_BYTES : Cfg::STAGES;
+  const uint32_t nst = (SWAP && d.res == nullptr && d.out_add == nullptr && d.out == nullptr) ? Cfg::STAGES + Cfg::STG_HALF / Cfg::B_BYTES : Cfg::STAGES;
   const bool has_st = d.out != nullptr || d.out_add != nullptr;   // the staging tile leaves by TMA (store and/or reduce-add)
   // fp32 input comes without a residual (host-checked): the raw ring lives in the second staging half
   constexpr int nraw = Cfg::NRAW;
@@ -388,7 +410,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     }
   } else if (warp >= FV_XF_WARP0 && warp < FV_XF_WARP0 + FV_XF_WARPS) {
     // ===================== transform warps: x -> act(a x + b) -> bf16 swizzled slot =====================
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_XF));
+    if constexpr (FvRegs<SWAP>::XF < 96) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FvRegs<SWAP>::XF));
     const int xw = warp - FV_XF_WARP0;
     const int xt = threadIdx.x - FV_XF_WARP0 * 32;
     const bool snake = a.act == KK_ACT_SNAKE || a.act == KK_ACT_SNAKE_FAST;
@@ -429,7 +451,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         } else {
           float4 k[4];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) k[i] = coef[cb * 64 + (lane & 15) * 4 + i];
+          for (int i = 0; i < 4; ++i) k[i] = fv_lds128(ptx::smem_u32(coef + cb * 64 + (lane & 15) * 4 + i));
           FV_WAIT(&a_empty[slot], sph ^ 1, w_xslot);   // the MMAs that read this slot have completed
           for (int i = 0; i < nbox; ++i, ++gr) {
             if ((int)(gr & 3u) != (xw >> 1)) continue;   // raw stage gr belongs to warp pair gr % 4
@@ -451,13 +473,12 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (warp == FV_XF_WARP0 && lane == 0) { FV_DBG_OUT(5, w_xdata); FV_DBG_OUT(6, w_xslot); }
   } else if (warp >= FV_EPI_WARP0) {
     // ===================== epilogue warps =====================
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FV_REGS_EPI));
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FvRegs<SWAP>::EPI));
     if constexpr (SWAP) {
     // Transposed accumulator: TMEM lane = output channel, column = tile row.  Work item n = (tile j, 32-row chunk
-    // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.  The result leaves
-    // STRAIGHT FROM REGISTERS (one 128-byte fp32 / 64-byte bf16 row segment per store instruction): the shared
-    // memory pipe is the kernel's bottleneck (UMMA operand reads + TMA fills), so the epilogue stays off it.
-    // Only a reduce-add (out_add) goes through the staging tile, because that is a TMA operation.
+    // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.  fp32 results are
+    // written into the staging tile (in place over the residual) and leave by TMA (store / reduce-add; register
+    // stores measured slower); the bf16 copy goes straight from registers, one 64-byte row segment per store.
     const int ew = warp - FV_EPI_WARP0;
     const int lg = warp & 3;
     const int half = ew >> 2;
@@ -465,7 +486,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // [32 rows][32 channels] fp32, 16-byte chunk ^= row & 7
     uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
-    const bool via_smem = d.out_add != nullptr;
+    const bool via_smem = has_st;   // fp32 results leave by TMA (store and/or reduce-add) from the staging tile
     const int ch0 = lg * 32, chan = ch0 + lane;
     const float bias_c = d.bias ? __ldg(d.bias + chan) : 0.f;
     const int n_items = t_count * NRC;
@@ -486,17 +507,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       atomicAdd(d.stats + ((size_t)b * d.C_out + chan) * 2 + 1, acc_q);
       acc_s = acc_q = 0.0;
     };
-    // row-strided stores of the thread's channel; `pitch` is a literal on the hot path (immediate offsets)
-    auto store_f32 = [&](float* op, const int pitch, const float (&o)[32], int nvalid) {
-      if (nvalid >= 32) {
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) op[jj * pitch] = o[jj];
-      } else {
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj)
-          if (jj < nvalid) op[jj * pitch] = o[jj];
-      }
-    };
+    // row-strided bf16 stores of the thread's channel; `pitch` is a literal on the hot path (immediate offsets)
     auto store_bf16 = [&](__nv_bfloat16* ap, const int pitch, const float (&o)[32], int nvalid) {
       if (nvalid >= 32) {
 #pragma unroll
@@ -563,13 +574,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           __syncwarp();
           if (lane == 0) {
             if (d.out) ptx::tma_store_3d(&tmOut, st, ch0, row0, b);   // rows >= L_out are clipped by the tensor map
-            ptx::tma_reduce_add_3d(&tmAdd, st, ch0, row0, b);
+            if (d.out_add) ptx::tma_reduce_add_3d(&tmAdd, st, ch0, row0, b);
             ptx::bulk_commit();
           }
-        } else if (d.out && nvalid > 0) {
-          float* op = d.out + ((size_t)b * d.L_out + row0) * d.out_pitch + chan;
-          if (d.out_pitch == 128) store_f32(op, 128, v, nvalid);
-          else store_f32(op, d.out_pitch, v, nvalid);
         }
         if (d.out_act && nvalid > 0) {
           __nv_bfloat16* ap = (__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0) * d.act_pitch + chan;
