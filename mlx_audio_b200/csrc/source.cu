@@ -23,12 +23,29 @@ __global__ void hnsf_phase_kernel(const float* __restrict__ f0, float* __restric
   const float harm = (float)(k + 1);
   const float pi_f = 3.14159265358979323846f;
   float c = 0.f;
-  for (int j = 0; j < T2; ++j) {
-    float fk = __fmul_rn(f[j], harm);                  // :610
-    float q = __fdiv_rn(fk, 24000.0f);                 // :561
-    float r = __fsub_rn(q, floorf(q));                 // python-sign "% 1"
-    c = __fadd_rn(c, r);                               // sequential float32 cumsum :573
-    p[j] = __fmul_rn(__fmul_rn(__fmul_rn(c, 2.0f), pi_f), upsample_f);  // *2, *pi (:573), *300 (:575)
+  // the cumulative sum is sequential by definition; the per-step fractions are not: compute them eight at a time so
+  // that the loads and the divisions overlap instead of sitting on the add chain
+  int j = 0;
+  for (; j + 8 <= T2; j += 8) {
+    float r[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      float fk = __fmul_rn(f[j + u], harm);              // :610
+      float q = __fdiv_rn(fk, 24000.0f);                 // :561
+      r[u] = __fsub_rn(q, floorf(q));                    // python-sign "% 1"
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      c = __fadd_rn(c, r[u]);                            // sequential float32 cumsum :573
+      p[j + u] = __fmul_rn(__fmul_rn(__fmul_rn(c, 2.0f), pi_f), upsample_f);  // *2, *pi (:573), *300 (:575)
+    }
+  }
+  for (; j < T2; ++j) {
+    float fk = __fmul_rn(f[j], harm);
+    float q = __fdiv_rn(fk, 24000.0f);
+    float r = __fsub_rn(q, floorf(q));
+    c = __fadd_rn(c, r);
+    p[j] = __fmul_rn(__fmul_rn(__fmul_rn(c, 2.0f), pi_f), upsample_f);
   }
 }
 
@@ -49,11 +66,21 @@ __device__ __forceinline__ uint4 philox4x32(uint4 ctr, uint2 key) {
 __device__ __forceinline__ void box_muller(uint32_t a, uint32_t b, float& n0, float& n1) {
   float u1 = ((float)(a >> 8) + 0.5f) * (1.0f / 16777216.0f);
   float u2 = ((float)(b >> 8) + 0.5f) * (1.0f / 16777216.0f);
-  float r = sqrtf(-2.0f * logf(u1));
+  float r = sqrtf(-2.0f * __logf(u1));      // internal generator only: hardware log / sin / cos are ample
   float s, c;
-  sincosf(6.28318530717958647692f * u2, &s, &c);
+  __sincosf(6.28318530717958647692f * u2, &s, &c);
   n0 = r * c;
   n1 = r * s;
+}
+
+// sin of a float32 phase of up to ~1e6 rad, correctly rounded to within an ulp like the reference's libm: the
+// argument is reduced modulo 2 pi in double precision (B200 runs fp64 at half the fp32 rate), which keeps sinf on its
+// short polynomial path instead of the Payne-Hanek one it takes above 105615 rad.
+__device__ __forceinline__ float sin_large(float ph) {
+  const double x = (double)ph;
+  const double n = rint(x * 0.15915494309189533577);
+  const double r = fma(n, -6.283185307179586232, x);      // |r| <= pi; 2 pi split error ~2.4e-16 * n: negligible
+  return sinf((float)fma(n, -2.449293598294706414e-16, r));
 }
 
 // ---- per sample: linear up-sample of the phase with the reference's float32 coordinates and its
@@ -99,7 +126,7 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
   for (int k = 0; k < NH; ++k) {
     const float* p = pb + (size_t)k * T2;
     float ph = __fadd_rn(__fmul_rn(p[lo], one_m), __fmul_rn(p[hi], fr));  // interpolate.py:106
-    float sine = __fmul_rn(sinf(ph), 0.1f);                                // :579, :613
+    float sine = __fmul_rn(sin_large(ph), 0.1f);                           // :579, :613
     float hk = voiced ? __fadd_rn(sine, __fmul_rn(amp, nz[k])) : __fmul_rn(amp, nz[k]);  // :622
     acc = fmaf(hk, lin_w[k], acc);
   }
@@ -109,24 +136,36 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
 // ---- STFT n_fft=20, hop=5, symmetric Hann, reflect pad 10, direct 20 -> 11 real DFT per frame.
 struct Dft20Tables { float win[20]; float cs[20]; float sn[20]; };
 
-__global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_pitch,
-                                __nv_bfloat16* __restrict__ har16, int pitch16, int rows16, int B, int S, int F,
-                                const Dft20Tables tb) {
-  long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)B * F) return;
-  int b = (int)(idx / F);
-  int f = (int)(idx - (long long)b * F);
+constexpr int ST_FR = 128;   // frames per block (= threads)
+
+__global__ void __launch_bounds__(ST_FR)
+stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_pitch,
+                __nv_bfloat16* __restrict__ har16, int pitch16, int rows16, int B, int S, int F,
+                const Dft20Tables tb) {
+  // block = 128 consecutive frames of one utterance: the 655 samples they cover are staged in shared memory
+  // (coalesced reads) and, when the bf16 rows are 24 wide, so is the output (128 x 48 B = 6 KB contiguous)
+  __shared__ float s_in[ST_FR * 5 + 16];
+  __shared__ __align__(16) __nv_bfloat16 s_out[ST_FR * 24];
+  const int blocks_per_b = (F + ST_FR - 1) / ST_FR;
+  const int b = blockIdx.x / blocks_per_b;
+  const int f0 = (blockIdx.x - b * blocks_per_b) * ST_FR;
+  const int f = f0 + threadIdx.x;
   const float* x = sig + (size_t)b * S;
-  float v[20];
-#pragma unroll
-  for (int n = 0; n < 20; ++n) {
-    int p = 5 * f + n - 10;
+  for (int i = threadIdx.x; i < ST_FR * 5 + 15; i += ST_FR) {
+    int p = 5 * f0 + i - 10;
     if (p < 0) p = -p;                       // reflect without edge repeat (utils.py:81-84)
     if (p >= S) p = 2 * (S - 1) - p;
-    v[n] = x[p] * tb.win[n];
+    s_in[i] = (p >= 0 && p < S) ? x[p] : 0.f;   // (frames past F are not stored)
   }
-  float* o = har ? har + (size_t)idx * har_pitch : nullptr;
-  __nv_bfloat16* o16 = har16 ? har16 + ((size_t)b * rows16 + f) * pitch16 : nullptr;
+  __syncthreads();
+  const bool live = f < F;
+  float v[20];
+#pragma unroll
+  for (int n = 0; n < 20; ++n) v[n] = s_in[5 * threadIdx.x + n] * tb.win[n];
+  const bool staged = har16 && pitch16 == 24;
+  float* o = (har && live) ? har + ((size_t)b * F + f) * har_pitch : nullptr;
+  __nv_bfloat16* o16 = (har16 && live && !staged) ? har16 + ((size_t)b * rows16 + f) * pitch16 : nullptr;
+  __nv_bfloat16* os = s_out + threadIdx.x * 24;
 #pragma unroll
   for (int k = 0; k <= 10; ++k) {
     float re = 0.f, im = 0.f;
@@ -141,9 +180,19 @@ __global__ void stft_n20_kernel(const float* __restrict__ sig, float* __restrict
     const float ang = atan2f(im, re);             // mlx_angle   istftnet.py:409
     if (o) { o[k] = mag; o[11 + k] = ang; }
     if (o16) { o16[k] = __float2bfloat16(mag); o16[11 + k] = __float2bfloat16(ang); }
+    if (staged) { os[k] = __float2bfloat16(mag); os[11 + k] = __float2bfloat16(ang); }
   }
   if (o) for (int c = 22; c < har_pitch; ++c) o[c] = 0.f;
   if (o16) for (int c = 22; c < pitch16; ++c) o16[c] = __float2bfloat16(0.f);
+  if (staged) {
+    os[22] = os[23] = __float2bfloat16(0.f);
+    __syncthreads();
+    const int nf = min(ST_FR, F - f0);               // live frames of this block
+    const int n16 = nf * 3;                          // 16-byte chunks (48 B per frame)
+    uint4* dst = reinterpret_cast<uint4*>(har16 + ((size_t)b * rows16 + f0) * 24);   // 16-byte aligned: f0 % 128 == 0
+    const uint4* src = reinterpret_cast<const uint4*>(s_out);
+    for (int i = threadIdx.x; i < n16; i += ST_FR) dst[i] = src[i];
+  }
 }
 
 }  // namespace kk
@@ -177,7 +226,9 @@ static int stft_n20_launch(const float* har_source, float* har, int har_pitch, v
   }
   int F = S / 5 + 1;
   long long total = (long long)B * F;
-  kk::stft_n20_kernel<<<kk::cdiv(total, 128), 128, 0, (cudaStream_t)stream>>>(
+  (void)total;
+  const int blocks = B * ((F + kk::ST_FR - 1) / kk::ST_FR);
+  kk::stft_n20_kernel<<<blocks, kk::ST_FR, 0, (cudaStream_t)stream>>>(
       har_source, har, har_pitch, (__nv_bfloat16*)har16, pitch16, rows16, B, S, F, tb);
   KK_LAUNCH_CHECK("stft_n20_kernel");
   return KK_OK;
@@ -191,6 +242,7 @@ extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, i
 extern "C" int kk_stft_n20_bf16(const float* har_source, float* har, int har_pitch, void* har_bf16, int bf_pitch,
                                 int bf_rows, int B, int S, void* stream) {
   KK_CHECK_ARG(har_source && har_bf16 && B > 0 && S > 10 && S % 5 == 0, "kk_stft_n20_bf16: bad arguments");
+  KK_CHECK_ARG(bf_pitch != 24 || ((uintptr_t)har_bf16 & 15) == 0, "kk_stft_n20_bf16: har_bf16 must be 16-byte aligned");
   KK_CHECK_ARG((!har || har_pitch >= 22) && bf_pitch >= 22 && bf_rows >= S / 5 + 1,
                "kk_stft_n20_bf16: pitch / rows too small (bf_rows %d < frames %d)", bf_rows, S / 5 + 1);
   return stft_n20_launch(har_source, har, har_pitch, har_bf16, bf_pitch, bf_rows, B, S, stream);
