@@ -114,7 +114,9 @@ int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int b
  * never exists in HBM.  Epilogue identical to kk_conv1d_bf16_tc (bias, residuals, scale, stats, out / out_act).
  *   A[b][l][c] = act(a_c * x[b][l][c] + b_c),  a_c = (1+gamma_c) / sqrt(var_c + 1e-5),  b_c = beta_c - a_c mean_c
  *   (rows outside [0, L_in) are zero AFTER the activation: the conv's own zero padding)
- * Restrictions: stride 1, up 1, C_in in {128, 256} with N == C_in, (taps-1)*dil <= 56, no res2 (use out_add). */
+ * Restrictions: stride 1, up 1, (C_in, N) in {(128,128), (256,256), (128, <=32: `out` only)}, (taps-1)*dil <= 56,
+ * no res2 (use out_add).  Outputs leave by TMA in 16-byte units: pad columns of `out` between C_out and the next
+ * multiple of 4 are overwritten with zeros. */
 typedef struct kk_adain_in {
   const void* x; int x_is_bf16; int x_pitch; /* raw input (B, L_in, x_pitch), fp32 or bf16                   */
   const double* stats;                       /* (B, C_in, 2) sum / sum of squares over time; NULL: no norm  */

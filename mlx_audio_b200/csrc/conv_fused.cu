@@ -66,7 +66,7 @@ struct FvCfg {
   static constexpr uint32_t TMEM_COLS = 512;
   static_assert(SLOT_ROWS >= 128 * MT + FV_HALO_MAX && SLOT_ROWS % 32 == 0, "slot too small");
   static_assert(2 * MT * BN <= 512, "accumulators exceed tensor memory");
-  static_assert(NRAW <= FV_MAX_RAW && STAGES + STG_HALF / B_BYTES <= 8, "barrier arrays");
+  static_assert(NRAW <= FV_MAX_RAW && STAGES + (BN == 128 ? STG_HALF / B_BYTES : 0) <= 8, "barrier arrays");
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
 };
 
@@ -447,7 +447,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           FV_WAIT(&x_full[slot], sph, w_xdata);
           if (snake) fv_xf_inplace<KK_ACT_SNAKE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
           else if (a.act == KK_ACT_LEAKY) fv_xf_inplace<KK_ACT_LEAKY>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
-          else fv_xf_inplace<KK_ACT_NONE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
+          else if (a.stats) fv_xf_inplace<KK_ACT_NONE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
+          // else: no normalisation and no activation - the operand is exactly what TMA wrote (rows outside the
+          // utterance were zero-filled by the tensor map), so the slot is handed to the MMA as is
         } else {
           float4 k[4];
 #pragma unroll
@@ -677,7 +679,14 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           for (int i = 0; i < 4; ++i) {
             const int c4 = h2 * 4 + i;
             float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (d.bias) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
+            if (d.bias) {
+              if (cbase + c4 * 4 + 4 <= d.C_out) bs = __ldg(reinterpret_cast<const float4*>(d.bias + cbase + c4 * 4));
+              else {   // ragged last channels (C_out not a multiple of 4 / 32)
+                if (cbase + c4 * 4 + 0 < d.C_out) bs.x = __ldg(d.bias + cbase + c4 * 4 + 0);
+                if (cbase + c4 * 4 + 1 < d.C_out) bs.y = __ldg(d.bias + cbase + c4 * 4 + 1);
+                if (cbase + c4 * 4 + 2 < d.C_out) bs.z = __ldg(d.bias + cbase + c4 * 4 + 2);
+              }
+            }
             rr[i].x = row_ok ? (v[c4 * 4 + 0] + bs.x + rr[i].x) * d.scale : 0.f;
             rr[i].y = row_ok ? (v[c4 * 4 + 1] + bs.y + rr[i].y) * d.scale : 0.f;
             rr[i].z = row_ok ? (v[c4 * 4 + 2] + bs.z + rr[i].z) * d.scale : 0.f;
@@ -874,6 +883,11 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
   if (d->C_in == 128 && d->N == 128)
     return swap128 ? kk::launch_fused<2, 128, 2, true>(a, w, d, st) : kk::launch_fused<2, 128, 2, false>(a, w, d, st);
   if (d->C_in == 256 && d->N == 256) return kk::launch_fused<1, 256, 4, false>(a, w, d, st);
-  kk::set_error("kk_conv1d_adain_bf16_tc: unsupported shape C_in=%d N=%d (128->128 and 256->256 only)", d->C_in, d->N);
+  if (d->C_in == 128 && d->N <= 32) {   // narrow head (conv_post, istftnet.py:798-803): no stats / bf16 copy / residual
+    KK_CHECK_ARG(!d->stats && !d->out_act && !d->res && !d->out_add && d->out,
+                 "kk_conv1d_adain_bf16_tc: the N <= 32 configuration writes `out` only");
+    return kk::launch_fused<2, 32, 2, false>(a, w, d, st);
+  }
+  kk::set_error("kk_conv1d_adain_bf16_tc: unsupported shape C_in=%d N=%d (128->128, 256->256 and 128-><=32 only)", d->C_in, d->N);
   return KK_ERR_UNSUPPORTED;
 }

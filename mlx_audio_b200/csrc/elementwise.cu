@@ -5,24 +5,46 @@
 namespace kk {
 
 // ---------------------------------------------------------------- style projection (AdaIN1d.fc)
-// One warp per output row r; a chunk of <=32 style vectors staged in shared memory.
-__global__ void style_affine_kernel(const float* __restrict__ s, const float* __restrict__ W,
-                                    const float* __restrict__ bias, float* __restrict__ h, int B, int R, int S) {
-  extern __shared__ float sh_s[];  // (nb, S)
-  int b0 = blockIdx.y * 32;
-  int nb = min(32, B - b0);
-  for (int i = threadIdx.x; i < nb * S; i += blockDim.x) sh_s[i] = s[(size_t)b0 * S + i];
+// h (B, R) = s (B, S) W^T (R, S) + bias: block = 32 output rows x 32 style vectors, both staged in shared memory;
+// warp = 4 rows, lane = style vector (no cross-lane reduction; W is read as broadcast float4).
+constexpr int SA_ROWS = 32;
+__global__ void __launch_bounds__(256)
+style_affine_kernel(const float* __restrict__ s, const float* __restrict__ W, const float* __restrict__ bias,
+                    float* __restrict__ h, int B, int R, int S) {
+  extern __shared__ __align__(16) float sh[];
+  float* sh_w = sh;                       // [SA_ROWS][S]
+  float* sh_s = sh + SA_ROWS * S;         // [S][33] (transposed, padded)
+  const int b0 = blockIdx.y * 32, r0 = blockIdx.x * SA_ROWS;
+  const int nb = min(32, B - b0), nr = min(SA_ROWS, R - r0);
+  for (int i = threadIdx.x; i < nr * S; i += blockDim.x) sh_w[i] = W[(size_t)r0 * S + i];
+  for (int i = threadIdx.x; i < 32 * S; i += blockDim.x) {
+    const int b = i / S, k = i - b * S;
+    sh_s[k * 33 + b] = b < nb ? s[(size_t)(b0 + b) * S + k] : 0.f;
+  }
   __syncthreads();
-  int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int r = blockIdx.x * (blockDim.x >> 5) + warp;
-  if (r >= R) return;
-  const float* wr = W + (size_t)r * S;
-  float bv = bias ? bias[r] : 0.f;
-  for (int b = 0; b < nb; ++b) {
-    float acc = 0.f;
-    for (int k = lane; k < S; k += 32) acc = fmaf(sh_s[b * S + k], wr[k], acc);
-    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-    if (lane == 0) h[(size_t)(b0 + b) * R + r] = acc + bv;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rw = warp * 4;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int k = 0; k + 4 <= S; k += 4) {
+    const float s0 = sh_s[(k + 0) * 33 + lane], s1 = sh_s[(k + 1) * 33 + lane];
+    const float s2 = sh_s[(k + 2) * 33 + lane], s3 = sh_s[(k + 3) * 33 + lane];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float4 w = *reinterpret_cast<const float4*>(sh_w + (rw + i) * S + k);
+      acc[i] = fmaf(s0, w.x, fmaf(s1, w.y, fmaf(s2, w.z, fmaf(s3, w.w, acc[i]))));
+    }
+  }
+  for (int k = S & ~3; k < S; ++k) {
+    const float sv = sh_s[k * 33 + lane];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i] = fmaf(sv, sh_w[(rw + i) * S + k], acc[i]);
+  }
+  if (lane < nb) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = r0 + rw + i;
+      if (r < R) h[(size_t)(b0 + lane) * R + r] = acc[i] + (bias ? bias[r] : 0.f);
+    }
   }
 }
 
@@ -235,8 +257,9 @@ __global__ void convert_act_kernel(const float* __restrict__ x, int x_pitch, Out
 extern "C" int kk_style_affine(const float* s, const float* W, const float* bias, float* h, int B, int R, int S,
                                void* stream) {
   KK_CHECK_ARG(s && W && h && B > 0 && R > 0 && S > 0 && S <= 384, "kk_style_affine: bad arguments B=%d R=%d S=%d", B, R, S);
-  dim3 grid(kk::cdiv(R, 8), kk::cdiv(B, 32));
-  size_t smem = (size_t)32 * S * sizeof(float);
+  KK_CHECK_ARG(S % 4 == 0 && ((uintptr_t)W & 15) == 0, "kk_style_affine: S must be a multiple of 4 and W 16-byte aligned");
+  dim3 grid(kk::cdiv(R, kk::SA_ROWS), kk::cdiv(B, 32));
+  size_t smem = ((size_t)kk::SA_ROWS * S + (size_t)S * 33) * sizeof(float);
   kk::style_affine_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(s, W, bias, h, B, R, S);
   KK_LAUNCH_CHECK("style_affine_kernel");
   return KK_OK;

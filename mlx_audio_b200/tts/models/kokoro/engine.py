@@ -589,8 +589,14 @@ class DecoderEngine:
             a_prev, L_prev, C_prev = a_next, Li, Ci
         # ---- conv_post + iSTFT head (:798-806)
         ypost = self._buf(plan, "ypost", (B, L3, 24))
-        self._conv(plan, self.convs[f"{g}.conv_post"], self._addr(a_prev), B, L3, self._act_pitch(Cs[1]), L3, pad_left=3,
-                   out_addr=self._addr(ypost), out_pitch=24)
+        pc_post = self.convs[f"{g}.conv_post"]
+        if self.fused and Cs[1] == 128 and pc_post.N <= 32 and self._act_pitch(Cs[1]) == 128:
+            # row-shifted-descriptor kernel: the input tile + halo is read once instead of once per tap
+            self._conv_fused(plan, pc_post, a_prev, 128, None, None, L.KK_ACT_NONE, 0.0, None, h_all, B, L3, pad_left=3,
+                             out_addr=self._addr(ypost), out_pitch=24)
+        else:
+            self._conv(plan, self.convs[f"{g}.conv_post"], self._addr(a_prev), B, L3, self._act_pitch(Cs[1]), L3, pad_left=3,
+                       out_addr=self._addr(ypost), out_pitch=24)
         self._tap(plan, "conv_post", ypost, lambda t: t[:, :, :22].transpose(1, 2))
         audio = self._buf(plan, "audio", (B, 1, S))
         plan.add(lib.kk_istft_head_n20, self._addr(ypost), 24, self._addr(audio), B, L3)

@@ -380,3 +380,43 @@ def test_conv1d_adain_bf16_tc(lib, case):
     if not lib.kk_device_is_sm100():
         pytest.skip("needs sm_100")
     _fused_case(lib, **case)
+
+
+@pytest.mark.parametrize("B,Lin", [(2, 700), (1, 257)])
+def test_conv1d_adain_narrow_head(lib, B, Lin):
+    """(C_in, N) = (128, 22): conv_post through the row-shifted-descriptor kernel, no normalisation / activation
+    (the transform warps pass the TMA-written operand through), `out` rows 24 floats wide, 22 written."""
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    from mlx_audio_b200._lib import AdainIn
+    r = rng(77 + Lin)
+    bf = torch.bfloat16
+    Cch, N, k = 128, 22, 7
+    x = torch.from_numpy(r.standard_normal((B, Lin, Cch), dtype=np.float32)).to(bf)
+    wfold = r.standard_normal((N, k, Cch), dtype=np.float32) / math.sqrt(Cch * k)
+    bias = r.standard_normal(N, dtype=np.float32) * 0.1
+    wq = torch.from_numpy(wfold).to(bf).double()
+    ref = F.conv1d(x.double().transpose(1, 2), wq.permute(0, 2, 1), torch.from_numpy(bias).double(),
+                   padding=3).transpose(1, 2).numpy()
+    xdev = x.cuda().contiguous()
+    wp = torch.empty(N, k * Cch, dtype=bf, device="cuda")
+    L.check(lib.kk_pack_conv_weight(L.ptr(dev(wfold)), L.ptr(wp), 1, 0, N, k, Cch, 1, Cch, L.stream()))
+    out = torch.full((B, Lin, 24), 7.0, device="cuda")
+    bd = dev(bias)
+    a = AdainIn()
+    a.x, a.x_is_bf16, a.x_pitch = L.ptr(xdev), 1, Cch
+    a.act = L.KK_ACT_NONE
+    d = ConvDesc()
+    d.B, d.L_in, d.C_in, d.x_pitch = B, Lin, Cch, Cch
+    d.taps, d.dil, d.pad_left, d.stride, d.Cw = k, 1, 3, 1, Cch
+    d.M, d.N, d.C_out, d.up, d.up_off = Lin, N, N, 1, 0
+    d.L_true, d.left_pad, d.L_out = Lin, 0, Lin
+    d.bias = L.ptr(bd)
+    d.scale = 1.0
+    d.out, d.out_pitch = L.ptr(out), 24
+    L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused narrow")
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    np.testing.assert_allclose(got[..., :N], ref, rtol=0, atol=2e-4)
+    # pad columns: untouched, or zero where TMA's 16-byte store granularity reaches past channel 21
+    assert np.isin(got[..., N:], (0.0, 7.0)).all()
