@@ -216,7 +216,10 @@ __device__ __forceinline__ void fv_tile_range(int total, int cta, int ncta, int&
 // SWAP (MT == 2, BN == 128 only): the MMA runs "transposed" - weights as the M = 128 operand, the 256 tile rows
 // as N = 256 - so one 128x256x16 MMA replaces two 128x128x16 ones (12 KB instead of 16 KB of shared-memory
 // operand reads per 128 tensor cycles).  The accumulator is then [channel lanes][row columns].
-template <int MT, int BN, int CB, bool SWAP>
+// CL = 2: CTAs run as cluster pairs that share the weight stream - each loads half of every weight slab and
+// TMA-multicasts it into both shared memories (the slab sequence is the same for every tile), halving the L2 -> SM
+// weight traffic, which is what bounds the 256-channel configuration (32 KB per 128 x 256 x 64 MMA block).
+template <int MT, int BN, int CB, bool SWAP, int CL>
 __global__ void __launch_bounds__(FV_THREADS, 1)
 conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
@@ -254,6 +257,15 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   uint8_t* sRaw = smem + Cfg::OFF_RAW;
   int t_start, t_count;
   fv_tile_range(total_tiles, blockIdx.x, gridDim.x, t_start, t_count);
+  // the weight pipeline of a pair runs for the longer of the two tile lists (the other CTA passes phantom slabs)
+  int t_pair = t_count;
+  uint32_t crank = 0;
+  if constexpr (CL > 1) {
+    int s2, c2;
+    fv_tile_range(total_tiles, blockIdx.x ^ 1, gridDim.x, s2, c2);
+    t_pair = c2 > t_count ? c2 : t_count;
+    crank = ptx::cluster_ctarank();
+  }
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmB);
@@ -268,7 +280,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     }
     for (int s = 0; s < 8; ++s) {
       ptx::mbar_init(&b_full[s], 1);
-      ptx::mbar_init(&b_empty[s], 1);
+      ptx::mbar_init(&b_empty[s], CL);   // every CTA of the pair has finished reading the stage
     }
     for (int s = 0; s < FV_MAX_RAW; ++s) {
       ptx::mbar_init(&raw_full[s], 1);
@@ -283,6 +295,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
   ptx::tc_fence_before();
+  if constexpr (CL > 1) ptx::cluster_sync();   // the peer's barriers exist before anything is multicast at them
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
@@ -293,13 +306,17 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (lane == 0) {
       uint32_t g = 0;
       FV_DBG_DECL(w_bempty);
-      for (int j = 0; j < t_count; ++j) {
+      for (int j = 0; j < t_pair; ++j) {
         for (int cb = 0; cb < CB; ++cb) {
           for (int t = 0; t < d.taps; ++t, ++g) {
             const uint32_t s = g % nst, ph = (g / nst) & 1;
             FV_WAIT(&b_empty[s], ph ^ 1, w_bempty);
             ptx::mbar_expect_tx(&b_full[s], Cfg::B_BYTES);
-            ptx::tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &b_full[s], t * d.Cw + cb * 64, 0);
+            if constexpr (CL > 1)   // my half of the slab (output channels crank*BN/2 ..), delivered to both CTAs
+              ptx::tma_load_2d_mc(sB + s * Cfg::B_BYTES + crank * (Cfg::B_BYTES / CL), &tmB, &b_full[s],
+                                  t * d.Cw + cb * 64, (int)crank * (BN / CL), (uint16_t)((1u << CL) - 1));
+            else
+              ptx::tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &b_full[s], t * d.Cw + cb * 64, 0);
           }
         }
       }
@@ -316,7 +333,15 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
 #ifdef KK_FUSED_DBG
       const long long t_begin = clock64();
 #endif
-      for (int j = 0; j < t_count; ++j) {
+      for (int j = 0; j < t_pair; ++j) {
+        if (CL > 1 && j >= t_count) {   // phantom tile: keep the pair's weight ring turning, no MMAs
+          for (int i = 0; i < CB * d.taps; ++i, ++gb) {
+            const uint32_t s = gb % nst, ph = (gb / nst) & 1;
+            FV_WAIT(&b_full[s], ph, w_bfull);
+            ptx::umma_commit_mc(&b_empty[s], (uint16_t)((1u << CL) - 1));
+          }
+          continue;
+        }
         const uint32_t buf = j & 1, aph = (j >> 1) & 1;
         FV_WAIT(&tmem_empty[buf], aph ^ 1, w_tempty);   // epilogue has drained this accumulator set
         ptx::tc_fence_after();
@@ -351,7 +376,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
                 }
               }
             }
-            ptx::umma_commit(&b_empty[s]);
+            if constexpr (CL > 1) ptx::umma_commit_mc(&b_empty[s], (uint16_t)((1u << CL) - 1));
+            else ptx::umma_commit(&b_empty[s]);
           }
           ptx::umma_commit(&a_empty[slot]);
         }
@@ -755,6 +781,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));   // spare warp of warpgroup 0
   }
   ptx::tc_fence_before();
+  if constexpr (CL > 1) ptx::cluster_sync();   // nothing of the peer's is still in flight towards this CTA
   __syncthreads();
   if (warp == 2) ptx::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
@@ -769,7 +796,7 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank
               const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle swz);   // conv_tc.cu
 int num_sms();                                                                             // conv_tc.cu
 
-template <int MT, int BN, int CB, bool SWAP>
+template <int MT, int BN, int CB, bool SWAP, int CL = 1>
 static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc* d, cudaStream_t st) {
   using Cfg = FvCfg<MT, BN, CB>;
   CUtensorMap tmB, tmX, tmRes, tmOut, tmAdd;
@@ -777,7 +804,7 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   {
     cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
     cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * 2};
-    cuuint32_t box[2] = {64, BN};
+    cuuint32_t box[2] = {64, BN / CL};   // CL > 1: every CTA of the pair loads (and multicasts) its share of a slab
     if ((rc = make_tmap(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, w, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   }
   {
@@ -813,17 +840,32 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   }
   static bool attr_set = false;
   if (!attr_set) {
-    KK_CUDA(cudaFuncSetAttribute(conv1d_adain_tc_kernel<MT, BN, CB, SWAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    KK_CUDA(cudaFuncSetAttribute(conv1d_adain_tc_kernel<MT, BN, CB, SWAP, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  Cfg::SMEM_BYTES));
     attr_set = true;
   }
   const int m_tiles = cdiv(d->M, 128 * MT);
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
-  const int grid = (int)(total < num_sms() ? total : num_sms());
+  int grid = (int)(total < num_sms() ? total : num_sms());
   static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;   // experiment knob: next-tile L2 prefetch
-  conv1d_adain_tc_kernel<MT, BN, CB, SWAP><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, tmAdd, *d, *a, m_tiles,
-                                                                              (int)total, flags);
+  if constexpr (CL > 1) {
+    grid -= grid % CL;                        // whole clusters (callers fall back to CL = 1 for tiny problems)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(FV_THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    KK_CUDA(cudaLaunchKernelEx(&cfg, conv1d_adain_tc_kernel<MT, BN, CB, SWAP, CL>, tmB, tmX, tmRes, tmOut, tmAdd, *d, *a,
+                               m_tiles, (int)total, flags));
+  } else {
+    conv1d_adain_tc_kernel<MT, BN, CB, SWAP, CL><<<grid, FV_THREADS, Cfg::SMEM_BYTES, st>>>(tmB, tmX, tmRes, tmOut, tmAdd, *d, *a,
+                                                                                    m_tiles, (int)total, flags);
+  }
   KK_LAUNCH_CHECK("conv1d_adain_tc_kernel");
   return KK_OK;
 }
@@ -880,9 +922,19 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
   }
   cudaStream_t st = (cudaStream_t)stream;
   static const bool swap128 = !(getenv("KK_FUSED_SWAP") && atoi(getenv("KK_FUSED_SWAP")) == 0);   // A/B knob
-  if (d->C_in == 128 && d->N == 128)
-    return swap128 ? kk::launch_fused<2, 128, 2, true>(a, w, d, st) : kk::launch_fused<2, 128, 2, false>(a, w, d, st);
-  if (d->C_in == 256 && d->N == 256) return kk::launch_fused<1, 256, 4, false>(a, w, d, st);
+  // cluster pairs (shared weight stream): KK_FUSED_CL bit 0 = 256-channel configuration, bit 1 = 128.  Default
+  // off: measured neutral to slightly negative (C=256 k=7: 5.05 -> 5.20 ms per 12 launches), i.e. the weight stalls
+  // are a latency / ring-depth effect, not L2 bandwidth.  Kept as an A/B knob.
+  static const int cl_mask = getenv("KK_FUSED_CL") ? atoi(getenv("KK_FUSED_CL")) : 0;
+  const long long tiles128 = (long long)kk::cdiv(d->M, 256) * d->B, tiles256 = (long long)kk::cdiv(d->M, 128) * d->B;
+  if (d->C_in == 128 && d->N == 128) {
+    if (!swap128) return kk::launch_fused<2, 128, 2, false>(a, w, d, st);
+    return ((cl_mask & 2) && tiles128 >= 4) ? kk::launch_fused<2, 128, 2, true, 2>(a, w, d, st)
+                                            : kk::launch_fused<2, 128, 2, true>(a, w, d, st);
+  }
+  if (d->C_in == 256 && d->N == 256)
+    return ((cl_mask & 1) && tiles256 >= 4) ? kk::launch_fused<1, 256, 4, false, 2>(a, w, d, st)
+                                            : kk::launch_fused<1, 256, 4, false>(a, w, d, st);
   if (d->C_in == 128 && d->N <= 32) {   // narrow head (conv_post, istftnet.py:798-803): no stats / bf16 copy / residual
     KK_CHECK_ARG(!d->stats && !d->out_act && !d->res && !d->out_add && d->out,
                  "kk_conv1d_adain_bf16_tc: the N <= 32 configuration writes `out` only");
