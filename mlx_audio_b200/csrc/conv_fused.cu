@@ -248,13 +248,16 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const int nbox = (R + FV_BOX_ROWS - 1) / FV_BOX_ROWS;  // 32-row TMA boxes per block
   const bool has_res = d.res != nullptr;
   const bool act_id = d.act_slope == 1.0f;   // out_act is a plain bf16 copy
-  // weight ring depth: when the epilogue does not use staging half 0 (SWAP, no residual, no reduce-add) the ring
-  // grows into it (the two regions are adjacent)
-  const uint32_t nst = (SWAP && d.res == nullptr && d.out_add == nullptr && d.out == nullptr) ? Cfg::STAGES + Cfg::STG_HALF / Cfg::B_BYTES : Cfg::STAGES;
   const bool has_st = d.out != nullptr || d.out_add != nullptr;   // the staging tile leaves by TMA (store and/or reduce-add)
   // fp32 input comes without a residual (host-checked): the raw ring lives in the second staging half
-  constexpr int nraw = Cfg::NRAW;
-  uint8_t* sRaw = smem + Cfg::OFF_RAW;
+  // Staging half 0 is free when nothing leaves through it (no residual, no fp32 output: the "conv1" launches).  Short
+  // kernels (taps <= 7) are bound by the input stream: the raw ring takes it (8 stages, two per warp pair, so that
+  // one loads while the other is transformed); long kernels are bound by the MMA: the weight ring takes it.
+  const bool half0_free = SWAP && d.res == nullptr && d.out == nullptr && d.out_add == nullptr;   // (the non-SWAP epilogue always stages)
+  const bool deep_raw = half0_free && !a.x_is_bf16 && d.taps <= 7 && !(flags & 2);   // flags bit 1: A/B knob (off)
+  const uint32_t nraw = deep_raw ? 2 * Cfg::NRAW : Cfg::NRAW;
+  uint8_t* sRaw = smem + (deep_raw ? Cfg::OFF_STG : Cfg::OFF_RAW);
+  const uint32_t nst = (half0_free && !deep_raw) ? Cfg::STAGES + Cfg::STG_HALF / Cfg::B_BYTES : Cfg::STAGES;
   int t_start, t_count;
   fv_tile_range(total_tiles, blockIdx.x, gridDim.x, t_start, t_count);
   // the weight pipeline of a pair runs for the longer of the two tile lists (the other CTA passes phantom slabs)
@@ -848,7 +851,8 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   int grid = (int)(total < num_sms() ? total : num_sms());
-  static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;   // experiment knob: next-tile L2 prefetch
+  // experiment knobs: bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring
+  static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;
   if constexpr (CL > 1) {
     grid -= grid % CL;                        // whole clusters (callers fall back to CL = 1 for tiny problems)
     cudaLaunchConfig_t cfg = {};

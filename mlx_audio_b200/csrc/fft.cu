@@ -6,6 +6,7 @@
 // normalisation and trimming are fused into the same kernels: the framed signal and (for log-mel) the
 // spectrogram never touch HBM.
 #include "common.cuh"
+#include "fft_fast.cuh"
 #include <math.h>
 
 namespace kk {
@@ -290,6 +291,214 @@ __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const Fft
   }
 }
 
+
+// ================================================================== n_fft = 1024 fast path (fft_fast.cuh)
+// Four frames per block iteration, 64 threads each.  Forward: pass 1 reads the windowed samples straight from
+// global memory (float2, coalesced; reflect / zero padding only on the edge frames), the half spectrum is unpacked
+// from the last exchange buffer.  MODE 1 (log-mel) keeps |X|^p in shared memory and projects it there.
+template <int MODE>
+__global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_[];
+  constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1;
+  float2* tw = reinterpret_cast<float2*>(smem_);
+  float2* tw2 = tw + NC;
+  float2* win = tw2 + bins + 1;                       // n_fft floats as NC float2
+  float2* bufs = win + NC;
+  int* mel_lo = reinterpret_cast<int*>(bufs + 2 * ff::GROUPS * ff::BUF);
+  int* mel_hi = mel_lo + (MODE == 1 ? a.n_mels : 0);
+  const int g = threadIdx.x / NT, j = threadIdx.x % NT;
+  float2* A = bufs + (2 * g) * ff::BUF;
+  float2* Bf = A + ff::BUF;
+
+  ff::fill_tables(tw, tw2);
+  for (int i = threadIdx.x; i < NC; i += blockDim.x) win[i] = make_float2(a.window[2 * i], a.window[2 * i + 1]);
+  if (MODE == 1) {   // non-zero span of every mel filter: one warp per row
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int m = warp; m < a.n_mels; m += ff::THREADS / 32) {
+      const float* row = a.fb + (size_t)m * bins;
+      int lo = bins, hi = 0;
+      for (int k = lane; k < bins; k += 32)
+        if (row[k] != 0.f) { lo = min(lo, k); hi = max(hi, k + 1); }
+      for (int off = 16; off > 0; off >>= 1) {
+        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, off));
+        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, off));
+      }
+      if (lane == 0) { mel_lo[m] = lo; mel_hi[m] = hi; }
+    }
+  }
+  __syncthreads();
+
+  const int b = blockIdx.y;
+  const float* xb = a.x + (size_t)b * a.n;
+  const int pad = a.pad_mode == 0 ? 0 : NC;
+  const bool vec_ok = ((a.hop | pad) & 1) == 0 && ((reinterpret_cast<uintptr_t>(xb) & 7) == 0);
+  const int f_begin = blockIdx.x * a.frames_per_block;
+  const int f_end = min(a.frames, f_begin + a.frames_per_block);
+  for (int f0 = f_begin; f0 < f_end; f0 += ff::GROUPS) {
+    const int f = f0 + g;
+    const bool live = f < f_end;
+    // ---- pass 1: samples 2(j + 64 t), +1 of the frame, windowed, packed as one complex point
+    {
+      float2 v[8];
+      const int base = f * a.hop - pad;
+      if (live && vec_ok && base >= 0 && base + n_fft <= a.n) {
+        const float2* src = reinterpret_cast<const float2*>(xb + base);
+#pragma unroll
+        for (int t = 0; t < 8; ++t) v[t] = __ldg(src + j + NT * t);
+      } else {
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          float sv[2] = {0.f, 0.f};
+          if (live) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              int q = base + 2 * (j + NT * t) + e;
+              if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
+                if (q < 0) q = -q;
+                if (q >= a.n) q = 2 * (a.n - 1) - q;
+                sv[e] = xb[q];
+              } else if (q >= 0 && q < a.n) {
+                sv[e] = xb[q];
+              }
+            }
+          }
+          v[t] = make_float2(sv[0], sv[1]);
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 8; ++t) { const float2 w = win[j + NT * t]; v[t].x *= w.x; v[t].y *= w.y; }
+      ff::pass1_store(v, A, j);
+    }
+    __syncthreads();
+    ff::pass2(A, Bf, tw, j);
+    __syncthreads();
+    {
+      float2 v[8];
+      ff::pass3(Bf, tw, j, v);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) A[ff::pad(j + NT * q)] = v[q];
+    }
+    __syncthreads();
+    // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i)
+    float* P = reinterpret_cast<float*>(Bf);   // MODE 1: |X|^p of this frame (513 floats <= BUF float2)
+    for (int k = j; k < bins; k += NT) {
+      const float2 zk = A[ff::pad(k & (NC - 1))];
+      float2 zc = A[ff::pad((NC - k) & (NC - 1))];
+      zc.y = -zc.y;
+      const float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
+      const float2 d = ff::cs(zk, zc);
+      const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);  // d / (2i)
+      float2 X = ff::ca(e, ff::cm(tw2[k], o));
+      if (k == 0 || k == NC) X.y = 0.f;
+      if (MODE == 0) {
+        if (live) reinterpret_cast<float2*>(a.out)[((size_t)b * a.frames + f) * bins + k] = X;
+      } else {
+        const float m2 = X.x * X.x + X.y * X.y;
+        P[k] = a.power == 2 ? m2 : sqrtf(m2);
+      }
+    }
+    __syncthreads();
+    if (MODE == 1) {
+      for (int m = j; m < a.n_mels; m += NT) {
+        const float* row = a.fb + (size_t)m * bins;
+        float acc = 0.f;
+        for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[k], __ldg(row + k), acc);
+        if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
+        else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
+        if (live) a.out[((size_t)b * a.frames + f) * a.n_mels + m] = acc;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// Inverse: the block's frames are inverse-transformed four at a time straight from the global half spectrum into the
+// windowed time-frame store `tf`, then overlap-added in gather form exactly like the general kernel.
+__global__ void __launch_bounds__(ff::THREADS) istft_fast_kernel(const IstftArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_[];
+  constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1;
+  float2* tw = reinterpret_cast<float2*>(smem_);
+  float2* tw2 = tw + NC;
+  float* win = reinterpret_cast<float*>(tw2 + bins + 1);
+  float2* bufs = reinterpret_cast<float2*>(win + n_fft);
+  float* tf = reinterpret_cast<float*>(bufs + 2 * ff::GROUPS * ff::BUF);   // (max_frames, n_fft) windowed time frames
+  const int g = threadIdx.x / NT, j = threadIdx.x % NT;
+  float2* A = bufs + (2 * g) * ff::BUF;
+  float2* Bf = A + ff::BUF;
+
+  ff::fill_tables(tw, tw2);
+  for (int i = threadIdx.x; i < n_fft; i += blockDim.x) win[i] = a.window[i];
+  __syncthreads();
+
+  const int b = blockIdx.y;
+  const long long total = (long long)(a.frames - 1) * a.hop + n_fft;   // untrimmed length (utils.py:126)
+  const long long u0 = (long long)blockIdx.x * a.hops_per_block * a.hop;
+  const long long u1 = min(total, u0 + (long long)a.hops_per_block * a.hop);
+  if (u0 >= total) return;
+  const int f_lo = u0 >= n_fft ? (int)((u0 - n_fft) / a.hop) + 1 : 0;
+  const int f_hi = min(a.frames - 1, (int)((u1 - 1) / a.hop));
+  const int nf = f_hi - f_lo + 1;
+  const float2* sb = reinterpret_cast<const float2*>(a.spec) + (size_t)b * a.frames * bins;
+  const float inv_nc = 1.0f / (float)NC;
+
+  for (int g0 = 0; g0 < nf; g0 += ff::GROUPS) {
+    const bool live = g0 + g < nf;
+    {
+      // pack: Z[k] = E[k] + i O[k], E = (X[k]+conj(X[nc-k]))/2, O = (X[k]-conj(X[nc-k]))/2 * e^{+2 pi i k/n};
+      // the inverse transform is conj(FFT(conj(Z)))/nc, so conj(Z) goes in.  irfft ignores Im X[0], Im X[nc].
+      float2 v[8];
+      const float2* X = sb + (size_t)(f_lo + g0 + (live ? g : 0)) * bins;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int k = j + NT * t;
+        float2 xk = __ldg(X + k), xc = __ldg(X + NC - k);
+        if (k == 0) { xk.y = 0.f; xc.y = 0.f; }
+        xc.y = -xc.y;
+        const float2 e = make_float2(0.5f * (xk.x + xc.x), 0.5f * (xk.y + xc.y));
+        const float2 dd = make_float2(0.5f * (xk.x - xc.x), 0.5f * (xk.y - xc.y));
+        float2 w2 = tw2[k];
+        w2.y = -w2.y;
+        const float2 o = ff::cm(dd, w2);
+        v[t] = make_float2(e.x - o.y, -(e.y + o.x));   // conj(e + i*o)
+      }
+      ff::pass1_store(v, A, j);
+    }
+    __syncthreads();
+    ff::pass2(A, Bf, tw, j);
+    __syncthreads();
+    {
+      float2 v[8];
+      ff::pass3(Bf, tw, j, v);
+      if (live) {
+        float2* dst = reinterpret_cast<float2*>(tf + (size_t)(g0 + g) * n_fft);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int i = j + NT * q;
+          // conj and the 1/n normalisation of irfft (1/nc here, the factor 1/2 is already inside E and O)
+          dst[i] = make_float2((v[q].x * inv_nc) * win[2 * i], (-v[q].y * inv_nc) * win[2 * i + 1]);
+        }
+      }
+    }
+    // (the next iteration's first exchange-buffer write is to A, last read two barriers ago; B is rewritten only
+    // after the barrier that follows pass 1)
+  }
+  __syncthreads();
+  // gather overlap-add in increasing frame order (utils.py:138-150)
+  for (long long u = u0 + threadIdx.x; u < u1; u += blockDim.x) {
+    const long long oi = u - a.trim;
+    if (oi < 0 || oi >= a.out_len) continue;
+    int fa = u >= n_fft ? (int)((u - n_fft) / a.hop) + 1 : 0;
+    int fb_ = min(a.frames - 1, (int)(u / a.hop));
+    float acc = 0.f, ws = 0.f;
+    for (int f = fa; f <= fb_; ++f) {
+      const int n = (int)(u - (long long)f * a.hop);
+      acc += tf[(size_t)(f - f_lo) * n_fft + n];
+      ws += win[n];
+    }
+    a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+  }
+}
+
 }  // namespace kk
 
 // ================================================================== C ABI
@@ -299,6 +508,18 @@ static int stft_group(int nc) { int g = 2048 / nc; return g < 1 ? 1 : (g > 8 ? 8
 template <int MODE>
 static int launch_stft(const StftArgs& a0, const FftPlan& p, int B, cudaStream_t st) {
   StftArgs a = a0;
+  if (p.n_fft == 2 * ff::NC) {   // register-resident radix-8 path
+    int fpb = 32;
+    while (fpb < 256 && (long long)cdiv(a.frames, fpb * 2) * B >= 148 * 16) fpb *= 2;
+    a.frames_per_block = fpb;
+    size_t smem = (size_t)ff::NC * 8 + (size_t)(ff::NC + 2) * 8 + (size_t)ff::NC * 8 +
+                  (size_t)2 * ff::GROUPS * ff::BUF * 8 + (MODE == 1 ? (size_t)2 * a.n_mels * 4 : 0) + 16;
+    KK_CUDA(cudaFuncSetAttribute(stft_fast_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    dim3 grid(cdiv(a.frames, fpb), B);
+    stft_fast_kernel<MODE><<<grid, ff::THREADS, smem, st>>>(a);
+    KK_LAUNCH_CHECK("stft_fast_kernel");
+    return KK_OK;
+  }
   a.group = stft_group(p.nc);
   // enough blocks for several waves, but amortise the per-block table setup over >= 4 groups
   int fpb = a.group * 4;
@@ -366,6 +587,23 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
   a.spec = spec; a.window = window; a.out = out; a.frames = frames; a.hop = hop; a.trim = trim; a.out_len = out_len;
   a.group = kk::stft_group(p.nc) > 4 ? 4 : kk::stft_group(p.nc);
   const int overlap = kk::cdiv(n_fft, hop);
+  if (n_fft == 2 * kk::ff::NC) {   // register-resident radix-8 path
+    size_t fixed = (size_t)kk::ff::NC * 8 + (size_t)(kk::ff::NC + 2) * 8 + (size_t)n_fft * 4 +
+                   (size_t)2 * kk::ff::GROUPS * kk::ff::BUF * 8 + 16;
+    int hpb = 32;
+    while (hpb > 1 && fixed + (size_t)(hpb + overlap) * n_fft * 4 > 160 * 1024) hpb >>= 1;
+    a.hops_per_block = hpb;
+    a.max_frames = hpb + overlap;
+    size_t smem = fixed + (size_t)a.max_frames * n_fft * 4;
+    if (smem <= 200 * 1024) {
+      KK_CUDA(cudaFuncSetAttribute(kk::istft_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      long long total = (long long)(frames - 1) * hop + n_fft;
+      dim3 grid(kk::cdiv(total, (long long)hpb * hop), B);
+      kk::istft_fast_kernel<<<grid, kk::ff::THREADS, smem, (cudaStream_t)stream>>>(a);
+      KK_LAUNCH_CHECK("istft_fast_kernel");
+      return KK_OK;
+    }
+  }
   size_t fixed = (size_t)p.nc * 8 + (size_t)(p.nc + 1) * 8 + (size_t)n_fft * 4 + (size_t)2 * a.group * p.nc * 8 + 16;
   int hpb = 16;
   while (hpb > 1 && fixed + (size_t)(hpb + overlap) * n_fft * 4 > 160 * 1024) hpb >>= 1;

@@ -1,0 +1,87 @@
+// Register-resident 512-point complex FFT (= 1024-point real transform, the n_fft of the reference's 24 kHz mel / Vocos
+// front ends: indextts/mel.py:20-37, codec/models/vocos/mel.py:22-33) for the general STFT / log-mel / iSTFT kernels.
+// One transform = 64 threads x 8 points: three radix-8 Stockham passes, butterflies in registers, two exchanges
+// through shared memory (padded by one element per eight: every exchange is bank-conflict free); a block runs four
+// transforms side by side.  The first pass reads global memory directly (windowed samples / packed half spectrum).
+#pragma once
+#include "common.cuh"
+
+namespace kk {
+namespace ff {
+
+constexpr int NC = 512;            // complex points
+constexpr int NT = NC / 8;         // threads per transform
+constexpr int GROUPS = 4;          // transforms per block
+constexpr int THREADS = NT * GROUPS;
+constexpr int BUF = NC + NC / 8;   // padded exchange buffer (float2 elements)
+
+__device__ __forceinline__ int pad(int i) { return i + (i >> 3); }
+__device__ __forceinline__ float2 cm(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ float2 ca(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 cs(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 mi(float2 a) { return make_float2(a.y, -a.x); }   // -i * a
+
+// forward 8-point DFT (e^{-2 pi i t q / 8}), natural order in and out
+__device__ __forceinline__ void fft8(float2 (&v)[8]) {
+  const float h = 0.70710678118654752440f;
+  const float2 a0 = ca(v[0], v[4]), a4 = cs(v[0], v[4]);
+  const float2 a2 = ca(v[2], v[6]), a6 = mi(cs(v[2], v[6]));
+  const float2 a1 = ca(v[1], v[5]), a5 = cs(v[1], v[5]);
+  const float2 a3 = ca(v[3], v[7]), a7 = mi(cs(v[3], v[7]));
+  const float2 b0 = ca(a0, a2), b2 = cs(a0, a2), b4 = ca(a4, a6), b6 = cs(a4, a6);
+  const float2 b1 = ca(a1, a3), b3 = mi(cs(a1, a3));
+  const float2 s5 = ca(a5, a7), d7 = cs(a5, a7);
+  const float2 b5 = make_float2(h * (s5.x + s5.y), h * (s5.y - s5.x));     // * (1 - i)/sqrt 2
+  const float2 b7 = make_float2(h * (d7.y - d7.x), -h * (d7.x + d7.y));    // * (-1 - i)/sqrt 2
+  v[0] = ca(b0, b1); v[4] = cs(b0, b1);
+  v[2] = ca(b2, b3); v[6] = cs(b2, b3);
+  v[1] = ca(b4, b5); v[5] = cs(b4, b5);
+  v[3] = ca(b6, b7); v[7] = cs(b6, b7);
+}
+
+// tw[j] = exp(-2 pi i j / 512), tw2[k] = exp(-2 pi i k / 1024) (k <= 512)
+__device__ __forceinline__ void fill_tables(float2* tw, float2* tw2) {
+  for (int j = threadIdx.x; j < NC; j += blockDim.x) {
+    float s, c;
+    sincospif(-2.0f * (float)j / (float)NC, &s, &c);
+    tw[j] = make_float2(c, s);
+  }
+  for (int j = threadIdx.x; j <= NC; j += blockDim.x) {
+    float s, c;
+    sincospif(-(float)j / (float)NC, &s, &c);
+    tw2[j] = make_float2(c, s);
+  }
+}
+
+// pass 1 (ns = 1): v holds points j + 64 t; result to A
+__device__ __forceinline__ void pass1_store(float2 (&v)[8], float2* A, int j) {
+  fft8(v);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) A[pad(8 * j + q)] = v[q];
+}
+// pass 2 (ns = 8): A -> B
+__device__ __forceinline__ void pass2(const float2* A, float2* B, const float2* tw, int j) {
+  float2 v[8];
+  const int k = j & 7;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    v[t] = A[pad(j + NT * t)];
+    if (t) v[t] = cm(v[t], tw[t * k * 8]);
+  }
+  fft8(v);
+  const int o = (j >> 3) * 64 + k;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) B[pad(o + 8 * q)] = v[q];
+}
+// pass 3 (ns = 64): B -> registers; v[q] = point j + 64 q of the transform
+__device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, float2 (&v)[8]) {
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    v[t] = B[pad(j + NT * t)];
+    if (t) v[t] = cm(v[t], tw[t * j]);
+  }
+  fft8(v);
+}
+
+}  // namespace ff
+}  // namespace kk
