@@ -43,11 +43,11 @@ def main():
                           x.numel() * 4 + mel.numel() * 4),
     }
     for name, (fn, nbytes) in calls.items():
-        for _ in range(3):
+        for _ in range(int(os.environ.get("WARM", "3"))):
             L.check(fn(), name)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 10
+        reps = int(os.environ.get("REPS", "10"))
         e0.record()
         for _ in range(reps):
             L.check(fn(), name)

@@ -296,16 +296,26 @@ __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const Fft
 // Four frames per block iteration, 64 threads each.  Forward: pass 1 reads the windowed samples straight from
 // global memory (float2, coalesced; reflect / zero padding only on the edge frames), the half spectrum is unpacked
 // from the last exchange buffer.  MODE 1 (log-mel) keeps |X|^p in shared memory and projects it there.
+constexpr int MEL_ITEMS = 384;   // <= 8-bin pieces of the filterbank's non-zero spans (80 htk mels at 1024: ~170)
+constexpr int MEL_MAX = 128;     // mel rows with a shared-memory accumulator
+
 template <int MODE>
 __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a) {
   extern __shared__ __align__(16) unsigned char smem_[];
   constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1;
   float2* tw = reinterpret_cast<float2*>(smem_);
-  float2* tw2 = tw + NC;
+  float2* tw2 = tw + ff::TW;
   float2* win = tw2 + bins + 1;                       // n_fft floats as NC float2
   float2* bufs = win + NC;
   int* mel_lo = reinterpret_cast<int*>(bufs + 2 * ff::GROUPS * ff::BUF);
-  int* mel_hi = mel_lo + (MODE == 1 ? a.n_mels : 0);
+  const int nm2 = (a.n_mels + 3) & ~3;                      // keeps the float4 table below 16-byte aligned
+  int* mel_hi = mel_lo + (MODE == 1 ? nm2 : 0);
+  // balanced sparse mel projection: the filterbank's non-zero spans cut into items of <= 8 bins
+  int* it_m = mel_hi + (MODE == 1 ? nm2 : 0);               // [MEL_ITEMS] mel row of the item
+  int* it_k = it_m + (MODE == 1 ? MEL_ITEMS : 0);           // [MEL_ITEMS] first bin
+  float* fbc = reinterpret_cast<float*>(it_k + (MODE == 1 ? MEL_ITEMS : 0));   // [MEL_ITEMS][8] weights, zero padded
+  float* melacc = fbc + (MODE == 1 ? MEL_ITEMS * 8 : 0);    // [GROUPS][MEL_MAX]
+  int* n_items_s = reinterpret_cast<int*>(melacc + (MODE == 1 ? ff::GROUPS * MEL_MAX : 0));
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
@@ -325,8 +335,26 @@ __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a
       }
       if (lane == 0) { mel_lo[m] = lo; mel_hi[m] = hi; }
     }
+    __syncthreads();
+    if (threadIdx.x == 0) {   // item list (serial over the rows: a few hundred cheap steps, once per block)
+      int n = 0;
+      for (int m = 0; m < a.n_mels && n >= 0; ++m)
+        for (int k0 = mel_lo[m]; k0 < mel_hi[m]; k0 += 8) {
+          if (n >= MEL_ITEMS) { n = -1; break; }   // too dense for the table: row-loop fallback
+          it_m[n] = m; it_k[n] = k0; ++n;
+        }
+      if (a.n_mels > MEL_MAX) n = -1;
+      *n_items_s = n;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < max(*n_items_s, 0) * 8; i += blockDim.x) {
+      const int it = i >> 3, k = it_k[it] + (i & 7);
+      fbc[i] = k < mel_hi[it_m[it]] ? a.fb[(size_t)it_m[it] * bins + k] : 0.f;
+    }
+    for (int i = threadIdx.x; i < ff::GROUPS * MEL_MAX; i += blockDim.x) melacc[i] = 0.f;
   }
   __syncthreads();
+  const int n_items = MODE == 1 ? *n_items_s : 0;
 
   const int b = blockIdx.y;
   const float* xb = a.x + (size_t)b * a.n;
@@ -334,51 +362,59 @@ __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a
   const bool vec_ok = ((a.hop | pad) & 1) == 0 && ((reinterpret_cast<uintptr_t>(xb) & 7) == 0);
   const int f_begin = blockIdx.x * a.frames_per_block;
   const int f_end = min(a.frames, f_begin + a.frames_per_block);
+  // samples 2(j + 64 t), +1 of frame f (zero for a frame past the block's range)
+  auto load_frame = [&](int f, float2 (&v)[8]) {
+    const int base = f * a.hop - pad;
+    if (f < f_end && vec_ok && base >= 0 && base + n_fft <= a.n) {
+      const float2* src = reinterpret_cast<const float2*>(xb + base);
+#pragma unroll
+      for (int t = 0; t < 8; ++t) v[t] = __ldg(src + j + NT * t);
+    } else {
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        float sv[2] = {0.f, 0.f};
+        if (f < f_end) {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            int q = base + 2 * (j + NT * t) + e;
+            if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
+              if (q < 0) q = -q;
+              if (q >= a.n) q = 2 * (a.n - 1) - q;
+              sv[e] = xb[q];
+            } else if (q >= 0 && q < a.n) {
+              sv[e] = xb[q];
+            }
+          }
+        }
+        v[t] = make_float2(sv[0], sv[1]);
+      }
+    }
+  };
+  // the four transforms of a block are independent: each pair of warps synchronises on its own named barrier
+  auto gsync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(NT) : "memory"); };
+  float2 nx[8];
+  load_frame(f_begin + g, nx);
   for (int f0 = f_begin; f0 < f_end; f0 += ff::GROUPS) {
     const int f = f0 + g;
     const bool live = f < f_end;
-    // ---- pass 1: samples 2(j + 64 t), +1 of the frame, windowed, packed as one complex point
+    // ---- pass 1: windowed samples packed as complex points; the next frame's samples are requested first
     {
       float2 v[8];
-      const int base = f * a.hop - pad;
-      if (live && vec_ok && base >= 0 && base + n_fft <= a.n) {
-        const float2* src = reinterpret_cast<const float2*>(xb + base);
 #pragma unroll
-        for (int t = 0; t < 8; ++t) v[t] = __ldg(src + j + NT * t);
-      } else {
-#pragma unroll
-        for (int t = 0; t < 8; ++t) {
-          float sv[2] = {0.f, 0.f};
-          if (live) {
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              int q = base + 2 * (j + NT * t) + e;
-              if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
-                if (q < 0) q = -q;
-                if (q >= a.n) q = 2 * (a.n - 1) - q;
-                sv[e] = xb[q];
-              } else if (q >= 0 && q < a.n) {
-                sv[e] = xb[q];
-              }
-            }
-          }
-          v[t] = make_float2(sv[0], sv[1]);
-        }
-      }
-#pragma unroll
-      for (int t = 0; t < 8; ++t) { const float2 w = win[j + NT * t]; v[t].x *= w.x; v[t].y *= w.y; }
+      for (int t = 0; t < 8; ++t) { const float2 w = win[j + NT * t]; v[t] = make_float2(nx[t].x * w.x, nx[t].y * w.y); }
+      load_frame(f + ff::GROUPS, nx);
       ff::pass1_store(v, A, j);
     }
-    __syncthreads();
+    gsync();
     ff::pass2(A, Bf, tw, j);
-    __syncthreads();
+    gsync();
     {
       float2 v[8];
       ff::pass3(Bf, tw, j, v);
 #pragma unroll
       for (int q = 0; q < 8; ++q) A[ff::pad(j + NT * q)] = v[q];
     }
-    __syncthreads();
+    gsync();
     // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i)
     float* P = reinterpret_cast<float*>(Bf);   // MODE 1: |X|^p of this frame (513 floats <= BUF float2)
     for (int k = j; k < bins; k += NT) {
@@ -397,57 +433,87 @@ __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a
         P[k] = a.power == 2 ? m2 : sqrtf(m2);
       }
     }
-    __syncthreads();
+    gsync();
     if (MODE == 1) {
+      float* macc = melacc + g * MEL_MAX;
+      if (n_items >= 0) {
+        for (int it = j; it < n_items; it += NT) {
+          const float* pk = P + it_k[it];                 // (bins past 512 read exchange-buffer leftovers x 0)
+          const float4 w0 = *reinterpret_cast<const float4*>(fbc + it * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(fbc + it * 8 + 4);
+          float acc = pk[0] * w0.x;
+          acc = fmaf(pk[1], w0.y, acc); acc = fmaf(pk[2], w0.z, acc); acc = fmaf(pk[3], w0.w, acc);
+          acc = fmaf(pk[4], w1.x, acc); acc = fmaf(pk[5], w1.y, acc); acc = fmaf(pk[6], w1.z, acc);
+          acc = fmaf(pk[7], w1.w, acc);
+          atomicAdd(macc + it_m[it], acc);
+        }
+        gsync();
+      }
       for (int m = j; m < a.n_mels; m += NT) {
-        const float* row = a.fb + (size_t)m * bins;
-        float acc = 0.f;
-        for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[k], __ldg(row + k), acc);
+        float acc;
+        if (n_items >= 0) {
+          acc = macc[m];
+          macc[m] = 0.f;
+        } else {
+          const float* row = a.fb + (size_t)m * bins;
+          acc = 0.f;
+          for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[k], __ldg(row + k), acc);
+        }
         if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
         else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
         if (live) a.out[((size_t)b * a.frames + f) * a.n_mels + m] = acc;
       }
-      __syncthreads();
+      gsync();
     }
   }
 }
 
-// Inverse: the block's frames are inverse-transformed four at a time straight from the global half spectrum into the
-// windowed time-frame store `tf`, then overlap-added in gather form exactly like the general kernel.
-__global__ void __launch_bounds__(ff::THREADS) istft_fast_kernel(const IstftArgs a) {
+// Inverse, streaming form (hop divides n_fft, R = n_fft / hop <= 4): a block walks its frames four at a time; every
+// group inverse-transforms one frame straight from the global half spectrum into its windowed time frame, the block
+// adds the four frames into a ring of running overlap-add sums (gather form: no atomics), emits the four hops that
+// are now complete (divided by the window sum, utils.py:138-150) and moves on.  A block first replays the R - 1
+// frames before its range (warm-up, nothing emitted), the last block drains the tail.
+struct IstftStreamArgs {
+  const float* spec; const float* window; float* out;
+  int frames, hop, trim, out_len, frames_per_block, R;
+};
+
+__global__ void __launch_bounds__(ff::THREADS) istft_stream_kernel(const IstftStreamArgs a) {
   extern __shared__ __align__(16) unsigned char smem_[];
-  constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1;
+  constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1, G = ff::GROUPS;
   float2* tw = reinterpret_cast<float2*>(smem_);
-  float2* tw2 = tw + NC;
+  float2* tw2 = tw + ff::TW;
   float* win = reinterpret_cast<float*>(tw2 + bins + 1);
   float2* bufs = reinterpret_cast<float2*>(win + n_fft);
-  float* tf = reinterpret_cast<float*>(bufs + 2 * ff::GROUPS * ff::BUF);   // (max_frames, n_fft) windowed time frames
+  float* ring = reinterpret_cast<float*>(bufs + 2 * G * ff::BUF);   // (G + R) hops of running sums
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
+  const int hop = a.hop, R = a.R;
+  const int ring_len = (G + R) * hop;
 
   ff::fill_tables(tw, tw2);
   for (int i = threadIdx.x; i < n_fft; i += blockDim.x) win[i] = a.window[i];
+  for (int i = threadIdx.x; i < ring_len; i += blockDim.x) ring[i] = 0.f;
   __syncthreads();
 
   const int b = blockIdx.y;
-  const long long total = (long long)(a.frames - 1) * a.hop + n_fft;   // untrimmed length (utils.py:126)
-  const long long u0 = (long long)blockIdx.x * a.hops_per_block * a.hop;
-  const long long u1 = min(total, u0 + (long long)a.hops_per_block * a.hop);
-  if (u0 >= total) return;
-  const int f_lo = u0 >= n_fft ? (int)((u0 - n_fft) / a.hop) + 1 : 0;
-  const int f_hi = min(a.frames - 1, (int)((u1 - 1) / a.hop));
-  const int nf = f_hi - f_lo + 1;
+  const long long total = (long long)(a.frames - 1) * hop + n_fft;   // untrimmed length (utils.py:126)
+  const int hops_total = (int)((total + hop - 1) / hop);
+  const int H0 = blockIdx.x * a.frames_per_block;
+  const int H1 = (blockIdx.x == gridDim.x - 1) ? hops_total : min(hops_total, H0 + a.frames_per_block);
   const float2* sb = reinterpret_cast<const float2*>(a.spec) + (size_t)b * a.frames * bins;
   const float inv_nc = 1.0f / (float)NC;
+  auto gsync = [&]() { asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "n"(NT) : "memory"); };
 
-  for (int g0 = 0; g0 < nf; g0 += ff::GROUPS) {
-    const bool live = g0 + g < nf;
+  for (int fi = H0 >= G ? H0 - G : 0; fi < H1; fi += G) {
+    const int f = fi + g;
+    const bool live = f < a.frames;
     {
       // pack: Z[k] = E[k] + i O[k], E = (X[k]+conj(X[nc-k]))/2, O = (X[k]-conj(X[nc-k]))/2 * e^{+2 pi i k/n};
       // the inverse transform is conj(FFT(conj(Z)))/nc, so conj(Z) goes in.  irfft ignores Im X[0], Im X[nc].
       float2 v[8];
-      const float2* X = sb + (size_t)(f_lo + g0 + (live ? g : 0)) * bins;
+      const float2* X = sb + (size_t)(live ? f : 0) * bins;
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         const int k = j + NT * t;
@@ -463,39 +529,50 @@ __global__ void __launch_bounds__(ff::THREADS) istft_fast_kernel(const IstftArgs
       }
       ff::pass1_store(v, A, j);
     }
-    __syncthreads();
+    gsync();
     ff::pass2(A, Bf, tw, j);
-    __syncthreads();
+    gsync();
     {
       float2 v[8];
       ff::pass3(Bf, tw, j, v);
-      if (live) {
-        float2* dst = reinterpret_cast<float2*>(tf + (size_t)(g0 + g) * n_fft);
+      float2* tfg = A;   // the group's windowed time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const int i = j + NT * q;
-          // conj and the 1/n normalisation of irfft (1/nc here, the factor 1/2 is already inside E and O)
-          dst[i] = make_float2((v[q].x * inv_nc) * win[2 * i], (-v[q].y * inv_nc) * win[2 * i + 1]);
-        }
+      for (int q = 0; q < 8; ++q) {
+        const int i = j + NT * q;
+        // conj and the 1/n normalisation of irfft (1/nc here, the factor 1/2 is already inside E and O)
+        tfg[i] = live ? make_float2((v[q].x * inv_nc) * win[2 * i], (-v[q].y * inv_nc) * win[2 * i + 1])
+                      : make_float2(0.f, 0.f);
       }
     }
-    // (the next iteration's first exchange-buffer write is to A, last read two barriers ago; B is rewritten only
-    // after the barrier that follows pass 1)
-  }
-  __syncthreads();
-  // gather overlap-add in increasing frame order (utils.py:138-150)
-  for (long long u = u0 + threadIdx.x; u < u1; u += blockDim.x) {
-    const long long oi = u - a.trim;
-    if (oi < 0 || oi >= a.out_len) continue;
-    int fa = u >= n_fft ? (int)((u - n_fft) / a.hop) + 1 : 0;
-    int fb_ = min(a.frames - 1, (int)(u / a.hop));
-    float acc = 0.f, ws = 0.f;
-    for (int f = fa; f <= fb_; ++f) {
-      const int n = (int)(u - (long long)f * a.hop);
-      acc += tf[(size_t)(f - f_lo) * n_fft + n];
-      ws += win[n];
+    __syncthreads();
+    // add the four frames into the ring; the first G hops of the span are complete afterwards
+    const int span = (G - 1) * hop + n_fft;
+    for (int p = threadIdx.x; p < span; p += blockDim.x) {
+      float sum = 0.f;
+#pragma unroll
+      for (int gg = 0; gg < G; ++gg) {
+        const int n = p - gg * hop;
+        if (n >= 0 && n < n_fft) sum += reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[n];
+      }
+      const long long u = (long long)fi * hop + p;
+      const int ri = (int)(u % ring_len);
+      const float acc = ring[ri] + sum;
+      if (p < G * hop) {
+        ring[ri] = 0.f;
+        const int h = fi + p / hop;
+        const long long oi = u - a.trim;
+        if (h >= H0 && h < H1 && u < total && oi >= 0 && oi < a.out_len) {
+          const int fa = u >= n_fft ? (int)((u - n_fft) / hop) + 1 : 0;
+          const int fb_ = min(a.frames - 1, (int)(u / hop));
+          float ws = 0.f;
+          for (int ff_ = fa; ff_ <= fb_; ++ff_) ws += win[(int)(u - (long long)ff_ * hop)];
+          a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+        }
+      } else {
+        ring[ri] = acc;
+      }
     }
-    a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+    __syncthreads();
   }
 }
 
@@ -512,8 +589,9 @@ static int launch_stft(const StftArgs& a0, const FftPlan& p, int B, cudaStream_t
     int fpb = 32;
     while (fpb < 256 && (long long)cdiv(a.frames, fpb * 2) * B >= 148 * 16) fpb *= 2;
     a.frames_per_block = fpb;
-    size_t smem = (size_t)ff::NC * 8 + (size_t)(ff::NC + 2) * 8 + (size_t)ff::NC * 8 +
-                  (size_t)2 * ff::GROUPS * ff::BUF * 8 + (MODE == 1 ? (size_t)2 * a.n_mels * 4 : 0) + 16;
+    size_t smem = (size_t)ff::TW * 8 + (size_t)(ff::NC + 2) * 8 + (size_t)ff::NC * 8 +
+                  (size_t)2 * ff::GROUPS * ff::BUF * 8 +
+                  (MODE == 1 ? (size_t)2 * (a.n_mels + 4) * 4 + (size_t)MEL_ITEMS * (8 + 32) + (size_t)ff::GROUPS * MEL_MAX * 4 + 16 : 0) + 16;
     KK_CUDA(cudaFuncSetAttribute(stft_fast_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     dim3 grid(cdiv(a.frames, fpb), B);
     stft_fast_kernel<MODE><<<grid, ff::THREADS, smem, st>>>(a);
@@ -587,22 +665,22 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
   a.spec = spec; a.window = window; a.out = out; a.frames = frames; a.hop = hop; a.trim = trim; a.out_len = out_len;
   a.group = kk::stft_group(p.nc) > 4 ? 4 : kk::stft_group(p.nc);
   const int overlap = kk::cdiv(n_fft, hop);
-  if (n_fft == 2 * kk::ff::NC) {   // register-resident radix-8 path
-    size_t fixed = (size_t)kk::ff::NC * 8 + (size_t)(kk::ff::NC + 2) * 8 + (size_t)n_fft * 4 +
-                   (size_t)2 * kk::ff::GROUPS * kk::ff::BUF * 8 + 16;
-    int hpb = 32;
-    while (hpb > 1 && fixed + (size_t)(hpb + overlap) * n_fft * 4 > 160 * 1024) hpb >>= 1;
-    a.hops_per_block = hpb;
-    a.max_frames = hpb + overlap;
-    size_t smem = fixed + (size_t)a.max_frames * n_fft * 4;
-    if (smem <= 200 * 1024) {
-      KK_CUDA(cudaFuncSetAttribute(kk::istft_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      long long total = (long long)(frames - 1) * hop + n_fft;
-      dim3 grid(kk::cdiv(total, (long long)hpb * hop), B);
-      kk::istft_fast_kernel<<<grid, kk::ff::THREADS, smem, (cudaStream_t)stream>>>(a);
-      KK_LAUNCH_CHECK("istft_fast_kernel");
-      return KK_OK;
-    }
+  if (n_fft == 2 * kk::ff::NC && n_fft % hop == 0 && n_fft / hop <= 4) {   // register-resident radix-8, streaming OLA
+    kk::IstftStreamArgs sa = {};
+    sa.spec = spec; sa.window = window; sa.out = out; sa.frames = frames; sa.hop = hop; sa.trim = trim;
+    sa.out_len = out_len; sa.R = n_fft / hop;
+    long long total = (long long)(frames - 1) * hop + n_fft;
+    const int hops_total = (int)((total + hop - 1) / hop);
+    int fpb = 32;   // multiple of GROUPS; the R - 1 warm-up frames cost (GROUPS / fpb) extra
+    while (fpb < 256 && (long long)kk::cdiv(hops_total, fpb * 2) * B >= 148 * 16) fpb *= 2;
+    sa.frames_per_block = fpb;
+    size_t smem = (size_t)kk::ff::TW * 8 + (size_t)(kk::ff::NC + 2) * 8 + (size_t)n_fft * 4 +
+                  (size_t)2 * kk::ff::GROUPS * kk::ff::BUF * 8 + (size_t)(kk::ff::GROUPS + sa.R) * hop * 4 + 16;
+    KK_CUDA(cudaFuncSetAttribute(kk::istft_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    dim3 grid(kk::cdiv(hops_total, fpb), B);
+    kk::istft_stream_kernel<<<grid, kk::ff::THREADS, smem, (cudaStream_t)stream>>>(sa);
+    KK_LAUNCH_CHECK("istft_stream_kernel");
+    return KK_OK;
   }
   size_t fixed = (size_t)p.nc * 8 + (size_t)(p.nc + 1) * 8 + (size_t)n_fft * 4 + (size_t)2 * a.group * p.nc * 8 + 16;
   int hpb = 16;

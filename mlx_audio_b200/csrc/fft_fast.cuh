@@ -39,12 +39,18 @@ __device__ __forceinline__ void fft8(float2 (&v)[8]) {
   v[3] = ca(b6, b7); v[7] = cs(b6, b7);
 }
 
-// tw[j] = exp(-2 pi i j / 512), tw2[k] = exp(-2 pi i k / 1024) (k <= 512)
+// Twiddle tables laid out per pass so that a warp reads consecutive addresses (a single exp(-2 pi i j/512) table
+// indexed t*k*8 / t*j puts 8 distinct addresses on one bank):
+//   tw[t*8 + k]        = exp(-2 pi i t k / 64)    pass 2 (t, k < 8)           - 64 entries
+//   tw[64 + t*64 + j]  = exp(-2 pi i t j / 512)   pass 3 (t < 8, j < 64)      - 512 entries
+//   tw2[k]             = exp(-2 pi i k / 1024)    real-transform unpack, k <= 512
+constexpr int TW = 64 + NC;
 __device__ __forceinline__ void fill_tables(float2* tw, float2* tw2) {
-  for (int j = threadIdx.x; j < NC; j += blockDim.x) {
+  for (int i = threadIdx.x; i < TW; i += blockDim.x) {
     float s, c;
-    sincospif(-2.0f * (float)j / (float)NC, &s, &c);
-    tw[j] = make_float2(c, s);
+    if (i < 64) sincospif(-2.0f * (float)((i >> 3) * (i & 7)) / 64.0f, &s, &c);
+    else sincospif(-2.0f * (float)(((i - 64) >> 6) * ((i - 64) & 63)) / (float)NC, &s, &c);
+    tw[i] = make_float2(c, s);
   }
   for (int j = threadIdx.x; j <= NC; j += blockDim.x) {
     float s, c;
@@ -66,7 +72,7 @@ __device__ __forceinline__ void pass2(const float2* A, float2* B, const float2* 
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = A[pad(j + NT * t)];
-    if (t) v[t] = cm(v[t], tw[t * k * 8]);
+    if (t) v[t] = cm(v[t], tw[t * 8 + k]);
   }
   fft8(v);
   const int o = (j >> 3) * 64 + k;
@@ -78,7 +84,7 @@ __device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, 
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = B[pad(j + NT * t)];
-    if (t) v[t] = cm(v[t], tw[t * j]);
+    if (t) v[t] = cm(v[t], tw[64 + t * 64 + j]);
   }
   fft8(v);
 }
