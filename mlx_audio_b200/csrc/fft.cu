@@ -545,31 +545,37 @@ __global__ void __launch_bounds__(ff::THREADS) istft_stream_kernel(const IstftSt
       }
     }
     __syncthreads();
-    // add the four frames into the ring; the first G hops of the span are complete afterwards
-    const int span = (G - 1) * hop + n_fft;
-    for (int p = threadIdx.x; p < span; p += blockDim.x) {
-      float sum = 0.f;
+    // add the four frames into the ring; the first G hops of the span are complete afterwards.  Position = (hop
+    // hh of the span, offset off inside it): no divisions, frame / window indices follow from hh alone.
+    const int rb = (fi % (G + R)) * hop;                 // ring position of sample fi * hop
+    for (int hh = 0; hh < G - 1 + R; ++hh) {
+      const int hcur = fi + hh;                          // absolute hop index
+      const bool emit = hh < G && hcur >= H0 && hcur < H1;
+      for (int off = threadIdx.x; off < hop; off += blockDim.x) {
+        float sum = 0.f;
 #pragma unroll
-      for (int gg = 0; gg < G; ++gg) {
-        const int n = p - gg * hop;
-        if (n >= 0 && n < n_fft) sum += reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[n];
-      }
-      const long long u = (long long)fi * hop + p;
-      const int ri = (int)(u % ring_len);
-      const float acc = ring[ri] + sum;
-      if (p < G * hop) {
-        ring[ri] = 0.f;
-        const int h = fi + p / hop;
-        const long long oi = u - a.trim;
-        if (h >= H0 && h < H1 && u < total && oi >= 0 && oi < a.out_len) {
-          const int fa = u >= n_fft ? (int)((u - n_fft) / hop) + 1 : 0;
-          const int fb_ = min(a.frames - 1, (int)(u / hop));
-          float ws = 0.f;
-          for (int ff_ = fa; ff_ <= fb_; ++ff_) ws += win[(int)(u - (long long)ff_ * hop)];
-          a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+        for (int gg = 0; gg < G; ++gg) {
+          const int r = hh - gg;                         // frame fi + gg covers this hop with its r-th hop
+          if (r >= 0 && r < R) sum += reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[r * hop + off];
         }
-      } else {
-        ring[ri] = acc;
+        int ri = rb + hh * hop + off;
+        if (ri >= ring_len) ri -= ring_len;
+        const float acc = ring[ri] + sum;
+        if (hh < G) {
+          ring[ri] = 0.f;
+          const long long u = (long long)hcur * hop + off;
+          const long long oi = u - a.trim;
+          if (emit && u < total && oi >= 0 && oi < a.out_len) {
+            float ws = 0.f;
+            for (int r = R - 1; r >= 0; --r) {           // increasing frame order, like the reference's loop
+              const int fr = hcur - r;                   // frames covering this sample
+              if (fr >= 0 && fr < a.frames) ws += win[r * hop + off];
+            }
+            a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+          }
+        } else {
+          ring[ri] = acc;
+        }
       }
     }
     __syncthreads();
