@@ -48,8 +48,19 @@ def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
     print(f"C={Cc} k={k} d={dil} x_bf16={x_bf16} res={with_res} out={'f32' if with_out else 'bf16'}: {e0.elapsed_time(e1):.3f} ms; "
           + "  ".join(f"{n}={v[i] / tot * 100:.0f}%" for i, n in enumerate(NAMES) if n != "-" and i != 10))
 
+import os
+if os.environ.get("DBG_SET") == "c256":
+    run(64, 6400, 256, 11, 1, False, False, False)   # fp32 in, bf16 out
+    run(64, 6400, 256, 11, 1, True, False, False)    # bf16 in, bf16 out
+    run(64, 6400, 256, 11, 1, True, False, True)     # bf16 in, f32 out (TMA store), no residual
+    run(64, 6400, 256, 11, 1, True, True, True)      # bf16 in, residual, f32 out
+    run(64, 6400, 256, 11, 1, False, False, True)    # fp32 in, f32 out
+    sys.exit(0)
 for k in (3, 11):
     run(64, 38401, 128, k, 1, False, False, False)   # conv1-type
     run(64, 38401, 128, k, 1, True, True, True)      # conv2-type
-run(64, 6400, 256, 7, 1, False, False, False)
-run(64, 6400, 256, 7, 1, True, True, True)
+for k in (3, 7, 11):
+    run(64, 6400, 256, k, 1, False, False, False)
+    run(64, 6400, 256, k, 1, True, True, True)
+run(64, 38401, 128, 7, 1, False, False, False)
+run(64, 38401, 128, 7, 1, True, True, True)

@@ -206,6 +206,27 @@ __device__ unsigned long long* g_fv_dbg = nullptr;
 #define FV_DBG_OUT(idx, v)
 #endif
 
+// Residual tile (32 rows x 32 fp32 channels at utterance b, row row0, channel ch0) -> staging tile in the 128B-swizzle
+// layout, by 16-byte cp.async from all 32 lanes (8 lanes = one 128-byte row segment); completion = one deferred
+// arrive per lane on `bar` (initialised with count 32).  Deliberately NOT a TMA load: residual boxes in the TMA queue
+// delayed the weight and input loads behind them (C=256 k=11: weight-ring stalls 18 % -> 47 % of the issuer's time).
+__device__ __forceinline__ void fv_issue_res(const kk_conv_desc& d, int b, int row0, int ch0, uint8_t* tile, uint64_t* bar,
+                                             int lane) {
+  const uint32_t t = ptx::smem_u32(tile);
+  const int c = lane & 7;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = i * 4 + (lane >> 3);
+    const int row = row0 + r;
+    const bool ok = row < d.L_res;
+    const float* src = d.res + ((size_t)b * d.L_res + (ok ? row : 0)) * d.res_pitch + ch0 + c * 4;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(t + (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4))),
+                 "l"(src), "r"(ok ? 16u : 0u)
+                 : "memory");
+  }
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(ptx::smem_u32(bar)) : "memory");
+}
+
 // contiguous share of the tile list for CTA `cta` of `ncta`
 __device__ __forceinline__ void fv_tile_range(int total, int cta, int ncta, int& start, int& count) {
   const int base = total / ncta, rem = total - base * ncta;
@@ -293,7 +314,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       ptx::mbar_init(&tmem_full[i], 1);
       ptx::mbar_init(&tmem_empty[i], FV_EPI_WARPS);
     }
-    for (int i = 0; i < FV_EPI_WARPS * 2; ++i) ptx::mbar_init(&res_full[i], 1);
+    for (int i = 0; i < FV_EPI_WARPS * 2; ++i) ptx::mbar_init(&res_full[i], 32);   // one deferred arrive per lane
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -521,14 +542,13 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const int ch0 = lg * 32, chan = ch0 + lane;
     const float bias_c = d.bias ? __ldg(d.bias + chan) : 0.f;
     const int n_items = t_count * NRC;
-    auto issue_res = [&](int n) {   // lane 0: TMA the residual tile of item n into staging buffer n & 1
+    auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
       if (n >= n_items) return;
       const int tile = t_start + n / NRC, rc = n % NRC;
       const int b = tile / m_tiles, row0 = (tile - b * m_tiles) * 256 + half * 128 + rc * 32;
-      ptx::mbar_expect_tx(&rbar[n & 1], 4096);
-      ptx::tma_load_3d(stg0 + (n & 1) * Cfg::STG_HALF, &tmRes, &rbar[n & 1], ch0, row0, b);
+      fv_issue_res(d, b, row0, ch0, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
     };
-    if (has_res && lane == 0) { issue_res(0); issue_res(1); }
+    if (has_res) { issue_res(0); issue_res(1); }
     double acc_s = 0.0, acc_q = 0.0;   // fp64 running instance-norm sums of this thread's channel
     int stat_b = -1;
     FV_DBG_DECL(w_tfull); FV_DBG_DECL(w_res);
@@ -615,11 +635,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           else store_bf16(ap, d.act_pitch, v, nvalid);
         }
         if (has_res) {
-          __syncwarp();                                  // everyone is done reading this staging tile
-          if (lane == 0) {
-            if (via_smem) ptx::bulk_wait_read<0>();      // ... and so is the TMA engine
-            issue_res(n + 2);
-          }
+          if (via_smem && lane == 0) ptx::bulk_wait_read<0>();   // the TMA engine is done reading this staging tile
+          __syncwarp();                                          // ... and so is every lane
+          issue_res(n + 2);
         }
       }
     }
@@ -640,14 +658,13 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const bool out_aligned_act = d.out_act != nullptr;
     const int n_items = t_count * NCH;
 
-    auto issue_res = [&](int n) {   // lane 0: TMA the residual tile of item n into staging buffer n & 1
+    auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
       if (n >= n_items) return;
       const int tile = t_start + n / NCH, c = n % NCH;
       const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128 + lg * 32;
-      ptx::mbar_expect_tx(&rbar[n & 1], 4096);
-      ptx::tma_load_3d(stg0 + (n & 1) * Cfg::STG_HALF, &tmRes, &rbar[n & 1], (chunk0 + c) * 32, m0, b);
+      fv_issue_res(d, b, m0, (chunk0 + c) * 32, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
     };
-    if (has_res && lane == 0) { issue_res(0); issue_res(1); }
+    if (has_res) { issue_res(0); issue_res(1); }
 
     double acc_s[NCH], acc_q[NCH];   // fp64 running instance-norm sums of column `lane` of each chunk
 #pragma unroll
@@ -769,10 +786,12 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           acc_s[c] += (double)(s0 + s1);
           acc_q[c] += (double)(q0 + q1);
         }
-        __syncwarp();                                    // everyone is done reading this staging tile
-        if (has_res && lane == 0) {
-          if (has_st) ptx::bulk_wait_read<0>();          // ... and so is the TMA store
+        if (has_res) {
+          if (has_st && lane == 0) ptx::bulk_wait_read<0>();   // the TMA store is done reading this staging tile
+          __syncwarp();                                        // ... and so is every lane
           issue_res(n + 2);
+        } else {
+          __syncwarp();
         }
       }
     }
