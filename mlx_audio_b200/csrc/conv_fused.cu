@@ -540,7 +540,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const bool do_stats = d.stats != nullptr;
     const bool via_smem = has_st;   // fp32 results leave by TMA (store and/or reduce-add) from the staging tile
     const int ch0 = lg * 32, chan = ch0 + lane;
-    const float bias_c = d.bias ? __ldg(d.bias + chan) : 0.f;
+    const float bias_s = (d.bias ? __ldg(d.bias + chan) : 0.f) * d.scale;   // (v + bias) * scale = fma(v, scale, bias * scale)
     const int n_items = t_count * NRC;
     auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
       if (n >= n_items) return;
@@ -609,14 +609,22 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           }
         }
         float s_ = 0.f, q_ = 0.f;
+        if (nvalid >= 32) {   // whole chunk inside the utterance (all but the last tile of an utterance): no masks
 #pragma unroll
-        for (int jj = 0; jj < 32; ++jj) {
-          v[jj] = jj < nvalid ? (v[jj] + bias_c) * d.scale : 0.f;
-          s_ += v[jj];
-          q_ = fmaf(v[jj], v[jj], q_);
+          for (int jj = 0; jj < 32; ++jj) v[jj] = fmaf(v[jj], d.scale, bias_s);
+        } else {
+#pragma unroll
+          for (int jj = 0; jj < 32; ++jj) v[jj] = jj < nvalid ? fmaf(v[jj], d.scale, bias_s) : 0.f;
         }
-        acc_s += (double)s_;
-        acc_q += (double)q_;
+        if (do_stats) {
+#pragma unroll
+          for (int jj = 0; jj < 32; ++jj) {
+            s_ += v[jj];
+            q_ = fmaf(v[jj], v[jj], q_);
+          }
+          acc_s += (double)s_;
+          acc_q += (double)q_;
+        }
         if (via_smem) {
 #pragma unroll
           for (int jj = 0; jj < 32; ++jj)
