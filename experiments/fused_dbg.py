@@ -22,6 +22,7 @@ def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
     w = (torch.randn(Cc, k * Cc, device=dev) / (Cc * k) ** 0.5).to(torch.bfloat16)
     bias = torch.zeros(Cc, device=dev)
     res = torch.randn(B, Lr, Cc, device=dev) if with_res else None
+    if with_res == "bf16": res = res.to(torch.bfloat16)
     out = torch.empty(B, Lr, Cc, device=dev) if with_out else None
     oact = None if with_out else torch.empty(B, Lr, Cc, device=dev, dtype=torch.bfloat16)
     ostats = torch.zeros(B, Cc, 2, dtype=torch.float64, device=dev)
@@ -34,6 +35,7 @@ def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
     d.M, d.N, d.C_out, d.up, d.up_off, d.L_true, d.left_pad, d.L_out = Lr, Cc, Cc, 1, 0, Lr, 0, Lr
     d.bias = bias.data_ptr()
     if with_res: d.res, d.res_pitch, d.res_shift, d.L_res = res.data_ptr(), Cc, 0, Lr
+    d.res_is_bf16 = int(with_res == "bf16")
     d.scale = 1.0
     if with_out: d.out, d.out_pitch = out.data_ptr(), Cc
     else: d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = oact.data_ptr(), Cc, 1, 1.0
@@ -49,6 +51,18 @@ def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
           + "  ".join(f"{n}={v[i] / tot * 100:.0f}%" for i, n in enumerate(NAMES) if n != "-" and i != 10))
 
 import os
+if os.environ.get("DBG_SET") == "s16":
+    for k in (3, 7, 11):
+        run(64, 38401, 128, k, 1, False, False, False)   # fp32 in -> bf16 out (fp32-stream conv1)
+        run(64, 38401, 128, k, 1, True, False, False)    # bf16 in -> bf16 out (bf16-stream conv1)
+        run(64, 38401, 128, k, 1, True, "bf16", False)   # bf16 in + bf16 residual -> bf16 out (bf16-stream conv2)
+        run(64, 38401, 128, k, 1, True, True, True)      # bf16 in + fp32 residual -> fp32 out (fp32-stream conv2)
+    for k in (3, 7):
+        run(64, 6400, 256, k, 1, False, False, False)
+        run(64, 6400, 256, k, 1, True, False, False)
+        run(64, 6400, 256, k, 1, True, "bf16", False)
+        run(64, 6400, 256, k, 1, True, True, True)
+    sys.exit(0)
 if os.environ.get("DBG_SET") == "c256":
     run(64, 6400, 256, 11, 1, False, False, False)   # fp32 in, bf16 out
     run(64, 6400, 256, 11, 1, True, False, False)    # bf16 in, bf16 out

@@ -97,6 +97,8 @@ typedef struct kk_conv_desc {
   void* out_act; int act_pitch, act_is_bf16; float act_slope;
   float* out_add; int add_pitch;   /* optional: out_add (B, L_out, add_pitch) += result (the MRF sum over resblocks,
                                       istftnet.py:795-800); kk_conv1d_adain_bf16_tc only (TMA reduce-add)          */
+  int res_is_bf16;                 /* `res` points at bf16 (B, L_res, res_pitch) data: the bf16 residual stream of
+                                      AdaINResBlock1 (x = x + xt, istftnet.py:394); kk_conv1d_adain_bf16_tc only   */
 } kk_conv_desc;
 
 /* fp32 CUDA-core kernel (strict-fp32 parity path; also the tiny / strided layers). x, w fp32. */

@@ -37,7 +37,7 @@ class ConvDesc(C.Structure):
         ("out", C.c_void_p), ("out_pitch", C.c_int),
         ("stats", C.c_void_p),
         ("out_act", C.c_void_p), ("act_pitch", C.c_int), ("act_is_bf16", C.c_int), ("act_slope", C.c_float),
-        ("out_add", C.c_void_p), ("add_pitch", C.c_int),
+        ("out_add", C.c_void_p), ("add_pitch", C.c_int), ("res_is_bf16", C.c_int),
     ]
 
 

@@ -125,6 +125,10 @@ extern "C" int kk_conv1d_f32(const float* x, const float* w, const kk_conv_desc*
   KK_CHECK_ARG(x && w, "kk_conv1d_f32: null tensor");
   int rc = kk::validate_conv_desc(d, "kk_conv1d_f32");
   if (rc) return rc;
+  if (d->res && d->res_is_bf16) {
+    kk::set_error("kk_conv1d_f32: a bf16 residual is implemented by kk_conv1d_adain_bf16_tc only");
+    return KK_ERR_UNSUPPORTED;
+  }
   if (d->out_add) {
     kk::set_error("kk_conv1d_f32: out_add is implemented by kk_conv1d_adain_bf16_tc only");
     return KK_ERR_UNSUPPORTED;

@@ -206,23 +206,39 @@ __device__ unsigned long long* g_fv_dbg = nullptr;
 #define FV_DBG_OUT(idx, v)
 #endif
 
-// Residual tile (32 rows x 32 fp32 channels at utterance b, row row0, channel ch0) -> staging tile in the 128B-swizzle
-// layout, by 16-byte cp.async from all 32 lanes (8 lanes = one 128-byte row segment); completion = one deferred
-// arrive per lane on `bar` (initialised with count 32).  Deliberately NOT a TMA load: residual boxes in the TMA queue
-// delayed the weight and input loads behind them (C=256 k=11: weight-ring stalls 18 % -> 47 % of the issuer's time).
+// Residual tile (32 rows x 32 channels at utterance b, row row0, channel ch0) -> staging tile, by 16-byte cp.async from
+// all 32 lanes; completion = one deferred arrive per lane on `bar` (initialised with count 32).  fp32: 128-byte rows in
+// the 128B-swizzle layout (chunk ^= row & 7); bf16 (res_is_bf16): 64-byte rows, chunk ^= (row >> 1) & 3.
+// Deliberately NOT a TMA load: residual boxes in the TMA queue delayed the weight and input loads behind them
+// (C=256 k=11: weight-ring stalls 18 % -> 47 % of the issuer's time).
 __device__ __forceinline__ void fv_issue_res(const kk_conv_desc& d, int b, int row0, int ch0, uint8_t* tile, uint64_t* bar,
                                              int lane) {
   const uint32_t t = ptx::smem_u32(tile);
-  const int c = lane & 7;
+  if (d.res_is_bf16) {
+    const int c = lane & 3;
+    const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(d.res);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r = i * 4 + (lane >> 3);
-    const int row = row0 + r;
-    const bool ok = row < d.L_res;
-    const float* src = d.res + ((size_t)b * d.L_res + (ok ? row : 0)) * d.res_pitch + ch0 + c * 4;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(t + (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4))),
-                 "l"(src), "r"(ok ? 16u : 0u)
-                 : "memory");
+    for (int i = 0; i < 4; ++i) {
+      const int r = i * 8 + (lane >> 2);
+      const int row = row0 + r;
+      const bool ok = row < d.L_res;
+      const __nv_bfloat16* src = base + ((size_t)b * d.L_res + (ok ? row : 0)) * d.res_pitch + ch0 + c * 8;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(t + (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4))),
+                   "l"(src), "r"(ok ? 16u : 0u)
+                   : "memory");
+    }
+  } else {
+    const int c = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = i * 4 + (lane >> 3);
+      const int row = row0 + r;
+      const bool ok = row < d.L_res;
+      const float* src = d.res + ((size_t)b * d.L_res + (ok ? row : 0)) * d.res_pitch + ch0 + c * 4;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(t + (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4))),
+                   "l"(src), "r"(ok ? 16u : 0u)
+                   : "memory");
+    }
   }
   asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(ptx::smem_u32(bar)) : "memory");
 }
@@ -268,6 +284,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const int R = 128 * MT + halo;                         // slot rows a tile needs
   const int nbox = (R + FV_BOX_ROWS - 1) / FV_BOX_ROWS;  // 32-row TMA boxes per block
   const bool has_res = d.res != nullptr;
+  const size_t res_esz = d.res_is_bf16 ? 2 : 4;
   const bool act_id = d.act_slope == 1.0f;   // out_act is a plain bf16 copy
   const bool has_st = d.out != nullptr || d.out_add != nullptr;   // the staging tile leaves by TMA (store and/or reduce-add)
   // fp32 input comes without a residual (host-checked): the raw ring lives in the second staging half
@@ -434,9 +451,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
                                   (uint32_t)((size_t)(l1 - l0) * a.x_pitch * xesz));
           int r1 = nm0 + 128 * MT;
           r1 = r1 > d.M ? d.M : r1;
-          if (has_res)
-            ptx::prefetch_l2_bulk(d.res + ((size_t)nb_ * d.L_res + nm0) * d.res_pitch,
-                                  (uint32_t)((size_t)(r1 - nm0) * d.res_pitch * 4));
+          if (has_res && !(flags & 4))
+            ptx::prefetch_l2_bulk(reinterpret_cast<const uint8_t*>(d.res) + ((size_t)nb_ * d.L_res + nm0) * d.res_pitch * res_esz,
+                                  (uint32_t)((size_t)(r1 - nm0) * d.res_pitch * res_esz));
         }
         for (int cb = 0; cb < CB; ++cb, ++ga) {
           const uint32_t slot = ga % Cfg::NSLOT, sph = (ga / Cfg::NSLOT) & 1;
@@ -539,6 +556,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
     const bool via_smem = has_st;   // fp32 results leave by TMA (store and/or reduce-add) from the staging tile
+    const bool res16 = d.res_is_bf16 != 0;
     const int ch0 = lg * 32, chan = ch0 + lane;
     const float bias_s = (d.bias ? __ldg(d.bias + chan) : 0.f) * d.scale;   // (v + bias) * scale = fma(v, scale, bias * scale)
     const int n_items = t_count * NRC;
@@ -600,7 +618,18 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         // lane = channel: element (row jj, channel) of the swizzled tile; conflict-free for every jj.
         const uint32_t sbase = ptx::smem_u32(st) + (uint32_t)(lane & 3) * 4u;
         const uint32_t lchunk = (uint32_t)(lane >> 2);
-        if (has_res) {
+        if (has_res && res16) {
+          // bf16 residual tile: 64-byte rows, lane = channel reads 2 bytes of row jj (one contiguous row per instruction)
+          const uint32_t hbase = ptx::smem_u32(st) + (uint32_t)(lane & 7) * 2u;
+          const uint32_t hchunk = (uint32_t)(lane >> 3);
+#pragma unroll
+          for (int jj = 0; jj < 32; ++jj) {
+            uint16_t r;
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(r) : "r"(hbase + (uint32_t)jj * 64u + ((hchunk ^ (uint32_t)((jj >> 1) & 3)) << 4)));
+            v[jj] += __uint_as_float((uint32_t)r << 16);
+          }
+          if (via_smem) __syncwarp();   // the fp32 result tile overlays the (smaller) bf16 residual tile
+        } else if (has_res) {
 #pragma unroll
           for (int jj = 0; jj < 32; ++jj) {
             float r;
@@ -664,6 +693,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
     const bool out_aligned_act = d.out_act != nullptr;
+    const bool res16 = d.res_is_bf16 != 0;
     const int n_items = t_count * NCH;
 
     auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
@@ -719,14 +749,26 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
           __syncwarp();
           if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
         }
-        const bool rd = has_res;
+        const bool rd = has_res && !res16;
+        uint4 rb[4];
+        if (has_res && res16) {   // bf16 residual: this lane's 64-byte row, read whole before the fp32 tile overlays it
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            rb[i] = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(st) + lane * 64 + ((i ^ ((lane >> 1) & 3)) << 4));
+          __syncwarp();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) rb[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
 #pragma unroll
         for (int h2 = 0; h2 < 2; ++h2) {   // loads batched ahead of the stores, four 16-byte chunks at a time
           float4 rr[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int c4 = h2 * 4 + i;
-            rr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const uint32_t lo = (c4 & 1) ? rb[c4 >> 1].z : rb[c4 >> 1].x, hi = (c4 & 1) ? rb[c4 >> 1].w : rb[c4 >> 1].y;
+            rr[i] = make_float4(__uint_as_float(lo << 16), __uint_as_float(lo & 0xffff0000u), __uint_as_float(hi << 16),
+                                __uint_as_float(hi & 0xffff0000u));
             if (rd) rr[i] = *reinterpret_cast<const float4*>(st + lane * 32 + ((c4 ^ (lane & 7)) << 2));
           }
 #pragma unroll
@@ -849,7 +891,7 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   }
   tmRes = tmB;
   tmOut = tmB;
-  if (d->res) {
+  if (d->res && !d->res_is_bf16) {
     cuuint64_t dims[3] = {(cuuint64_t)d->C_out, (cuuint64_t)d->L_res, (cuuint64_t)d->B};
     cuuint64_t strides[2] = {(cuuint64_t)d->res_pitch * 4, (cuuint64_t)d->L_res * d->res_pitch * 4};
     cuuint32_t box[3] = {32, 32, 1};
@@ -878,8 +920,8 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   int grid = (int)(total < num_sms() ? total : num_sms());
-  // experiment knobs: bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring
-  static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 1;
+  // experiment knobs: bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring, bit 2 = no residual prefetch
+  static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 5;
   if constexpr (CL > 1) {
     grid -= grid % CL;                        // whole clusters (callers fall back to CL = 1 for tiny problems)
     cudaLaunchConfig_t cfg = {};
@@ -932,9 +974,10 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
                "kk_conv1d_adain_bf16_tc: out must be 16-byte aligned with a pitch multiple of 4");
   KK_CHECK_ARG(!d->out_add || (((uintptr_t)d->out_add & 15) == 0 && d->add_pitch % 4 == 0),
                "kk_conv1d_adain_bf16_tc: out_add must be 16-byte aligned with a pitch multiple of 4");
-  KK_CHECK_ARG(!d->res || (((uintptr_t)d->res & 15) == 0 && d->res_pitch % 4 == 0 && d->res_shift == 0 &&
-                           d->L_res == d->L_out),
-               "kk_conv1d_adain_bf16_tc: residual must be 16-byte aligned, same length as the output, no shift");
+  KK_CHECK_ARG(!d->res || (((uintptr_t)d->res & 15) == 0 && d->res_pitch % (d->res_is_bf16 ? 8 : 4) == 0 &&
+                           d->res_shift == 0 && d->L_res == d->L_out),
+               "kk_conv1d_adain_bf16_tc: residual must be 16-byte aligned (pointer and row pitch), same length as the "
+               "output, no shift");
   if (d->res2) {
     kk::set_error("kk_conv1d_adain_bf16_tc: a second residual is not supported here; accumulate with out_add instead");
     return KK_ERR_UNSUPPORTED;

@@ -503,6 +503,10 @@ extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_des
     kk::set_error("kk_conv1d_bf16_tc: needs an sm_100 (Blackwell) device");
     return KK_ERR_UNSUPPORTED;
   }
+  if (d->res && d->res_is_bf16) {
+    kk::set_error("kk_conv1d_bf16_tc: a bf16 residual is implemented by kk_conv1d_adain_bf16_tc only");
+    return KK_ERR_UNSUPPORTED;
+  }
   if (d->out_add) {
     kk::set_error("kk_conv1d_bf16_tc: out_add is implemented by kk_conv1d_adain_bf16_tc only");
     return KK_ERR_UNSUPPORTED;

@@ -138,6 +138,8 @@ class DecoderEngine:
         self.tc = mode == "bf16"
         import os as _os
         self.fused = self.tc and _os.environ.get("KK_FUSED", "1") != "0"   # A/B knob: 0 = separate AdaIN kernels
+        # bf16 residual stream inside AdaINResBlock1: 0 = off, 1 = the 128-channel stage, 2 = both stages
+        self.res16 = int(_os.environ.get("KK_RES16", "1")) if self.fused else 0
         if self.tc and not self.lib.kk_device_is_sm100():
             raise L.KokoroB200Error("bf16 tensor-core mode needs an sm_100 (B200) device")
         self.dev = next(iter(weights.values())).device
@@ -331,7 +333,8 @@ class DecoderEngine:
         d.left_pad = 0
         d.bias = self._addr(pc.bias) if pc.bias is not None else None
         if res is not None:
-            d.res, d.res_pitch, d.res_shift, d.L_res = res
+            d.res, d.res_pitch, d.res_shift, d.L_res = res[:4]
+            d.res_is_bf16 = int(len(res) > 4 and res[4])
         if res2 is not None:
             d.res2, d.res2_pitch = res2
         d.scale = scale
@@ -362,7 +365,7 @@ class DecoderEngine:
     # ------------------------------------------------------------------ blocks
     def _adain_resblock1(self, plan: Plan, prefix: str, B: int, L_: int, C_: int, k: int, dils, h_all,
                          x_in: torch.Tensor, stats_in: int, work: torch.Tensor, act: torch.Tensor, y: torch.Tensor,
-                         final: dict):
+                         final: dict, x16_in: Optional[torch.Tensor] = None):
         """AdaINResBlock1 (istftnet.py:341-396).  x_in (B,L,C) fp32 with stats_in known; the running stream lives
         in ``work`` after the first iteration (work may be x_in itself: fully in place).  ``final`` gives the
         last conv2 epilogue: dict(out_addr, out_pitch, res2, scale, stats_addr, out_act).  Fused path only:
@@ -379,6 +382,16 @@ class DecoderEngine:
             ybf = plan.buffers.get(f"ybf.{B}.{L_}.{C_}")
             if ybf is None:
                 ybf = self._buf(plan, f"ybf.{B}.{L_}.{C_}", (B, L_, C_), torch.bfloat16)
+            # bf16 residual stream (KK_RES16, default on): the running x is written by conv2 as bf16 only (statistics
+            # still from the fp32 accumulators) and read back as bf16 by the next conv1 (input) and conv2 (residual);
+            # x16_in = bf16 copy of x_in from its producer.  The block's output and the MRF sum stay fp32.
+            s16 = x16_in is not None
+            w16 = None
+            if s16:
+                w16 = plan.buffers.get(f"w16.{B}.{L_}.{C_}")
+                if w16 is None:
+                    w16 = self._buf(plan, f"w16.{B}.{L_}.{C_}", (B, L_, C_), torch.bfloat16)
+                cur = x16_in
             for it in range(3):
                 d = dils[it]
                 c1 = self.convs[f"{prefix}.convs1.{it}"]
@@ -387,15 +400,16 @@ class DecoderEngine:
                 self._conv_fused(plan, c1, cur, C_, cur_stats, f"{prefix}.adain1.{it}", snake, 0.0,
                                  self.w[f"{prefix}.alpha1.{it}"], h_all, B, L_, dil=d, pad_left=(k * d - d) // 2,
                                  out_stats=st_y, out_act=(self._addr(ybf), C_, 1, 1.0))
-                res = (self._addr(cur), C_, 0, L_)
+                res = (self._addr(cur), C_, 0, L_, s16)
                 fold = final.get("fold_into")
                 if it < 2:
                     st_n = self._stats(plan, B, C_)
                     self._conv_fused(plan, c2, ybf, C_, st_y, f"{prefix}.adain2.{it}", snake, 0.0,
                                      self.w[f"{prefix}.alpha2.{it}"], h_all, B, L_, pad_left=(k - 1) // 2,
-                                     out_addr=self._addr(work), out_pitch=C_, res=res, out_stats=st_n,
+                                     out_addr=None if s16 else self._addr(work), out_pitch=C_, res=res, out_stats=st_n,
+                                     out_act=(self._addr(w16), C_, 1, 1.0) if s16 else None,
                                      out_add=fold if it == 1 else None)
-                    cur, cur_stats = work, st_n
+                    cur, cur_stats = (w16 if s16 else work), st_n
                 else:
                     if fold is not None:
                         res = (fold[0], fold[1], 0, L_)
@@ -485,24 +499,25 @@ class DecoderEngine:
                  B, self.ada_R, cfg["style_dim"])
         # ---- front: x = cat[asr, F0, N] (:951); xcat = cat[x(1024), asr_res(64), F0, N] (:957)
         c_cat0, c_cat = din + 2, 1024 + 64 + 2
+        p_cat = (c_cat + 3) // 4 * 4      # 16-byte row pitch: the conv epilogues then store xcat by TMA
         xcat0 = self._buf(plan, "xcat0", (B, T, c_cat0))
-        xcat = self._buf(plan, "xcat", (B, T, c_cat))
+        xcat = self._buf(plan, "xcat", (B, T, p_cat))
         plan.add(lib.kk_front_assemble, self._addr(asr), self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
                  self._addr(self.n_w3b), self._addr(xcat0), c_cat0, 0, din, din + 1, B, din, T, launches=2)
         plan.add(lib.kk_front_assemble, None, self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
-                 self._addr(self.n_w3b), self._addr(xcat), c_cat, 0, 1024 + 64, 1024 + 65, B, din, T)
+                 self._addr(self.n_w3b), self._addr(xcat), p_cat, 0, 1024 + 64, 1024 + 65, B, din, T)
         self._conv(plan, self.convs["asr_res.0"], self._addr(xcat0), B, T, c_cat0, T,
-                   out_addr=self._addr(xcat, 1024), out_pitch=c_cat, force_f32=True)  # :953
+                   out_addr=self._addr(xcat, 1024), out_pitch=p_cat, force_f32=True)  # :953
         self._adain_resblk1d(plan, "encode", B, T, c_cat0, 1024, h_all, self._addr(xcat0), c_cat0, self._addr(xcat),
-                             c_cat, name="encode")
+                             p_cat, name="encode")
         self._tap(plan, "encode", xcat, lambda t: t[:, :, :1024].transpose(1, 2))
         for i in range(3):
-            self._adain_resblk1d(plan, f"decode.{i}", B, T, c_cat, 1024, h_all, self._addr(xcat), c_cat,
-                                 self._addr(xcat), c_cat, name=f"decode{i}")
+            self._adain_resblk1d(plan, f"decode.{i}", B, T, c_cat, 1024, h_all, self._addr(xcat), p_cat,
+                                 self._addr(xcat), p_cat, name=f"decode{i}")
             self._tap(plan, f"decode{i}", xcat, lambda t: t[:, :, :1024].transpose(1, 2))
         x3 = self._buf(plan, "x3", (B, T2, C0))
         a_prev = self._buf(plan, "a0", (B, T2, self._act_pitch(C0)), adt, zero=True)
-        self._adain_resblk1d(plan, "decode.3", B, T, c_cat, C0, h_all, self._addr(xcat), c_cat, self._addr(x3), C0,
+        self._adain_resblk1d(plan, "decode.3", B, T, c_cat, C0, h_all, self._addr(xcat), p_cat, self._addr(x3), C0,
                              upsample=True, out_act=(self._addr(a_prev), self._act_pitch(C0), int(self.tc), 0.1),
                              name="decode3")
         self._tap(plan, "decode3", x3, lambda t: t.transpose(1, 2))
@@ -534,14 +549,20 @@ class DecoderEngine:
             nconv = self.convs[f"{g}.noise_convs.{i}"]
             xs = self._buf(plan, f"g{i}.xs", (B, Li, Ci))
             st_xs = self._stats(plan, B, Ci)
+            fused_i = self.fused and Ci in (128, 256)
+            s16 = fused_i and (self.res16 >= 2 or (self.res16 == 1 and Ci == 128))
+            xs16 = self._buf(plan, f"g{i}.xs16", (B, Li, Ci), torch.bfloat16) if s16 else None
+            x16 = self._buf(plan, f"g{i}.x16", (B, Li, Ci), torch.bfloat16) if s16 else None
+            xs_out = None if s16 else self._addr(xs)     # bf16 stream: the noise conv's result is only ever read as bf16
             if self.tc:
                 ntc = self.convs[f"{g}.noise_convs.{i}.tc"]
+                oa = (self._addr(xs16), Ci, 1, 1.0) if s16 else None
                 if i == 0:   # (B, L20+1 rows of r1 frames, r1*24 channels), 3 taps, left pad 1
                     self._conv(plan, ntc, self._addr(har16), B, L20 + 1, r1 * 24, Li, pad_left=1,
-                               out_addr=self._addr(xs), out_pitch=Ci, stats_addr=st_xs)
+                               out_addr=xs_out, out_pitch=Ci, stats_addr=st_xs, out_act=oa)
                 else:        # 1x1 over the frames; rows >= L3 of har16 are never read (M = L3)
-                    self._conv(plan, ntc, self._addr(har16), B, har_rows, 24, Li, out_addr=self._addr(xs),
-                               out_pitch=Ci, stats_addr=st_xs)
+                    self._conv(plan, ntc, self._addr(har16), B, har_rows, 24, Li, out_addr=xs_out,
+                               out_pitch=Ci, stats_addr=st_xs, out_act=oa)
             elif i == 0:
                 stride_f0 = r1
                 self._conv(plan, nconv, self._addr(har), B, L3, 24, Li, stride=stride_f0, pad_left=(stride_f0 + 1) // 2,
@@ -549,26 +570,26 @@ class DecoderEngine:
             else:
                 self._conv(plan, nconv, self._addr(har), B, L3, 24, Li, out_addr=self._addr(xs), out_pitch=Ci,
                            stats_addr=st_xs, force_f32=True)
-            self._tap(plan, f"noise_conv{i}", xs, lambda t: t.transpose(1, 2))
-            fused_i = self.fused and Ci in (128, 256)
+            self._tap(plan, f"noise_conv{i}", xs16 if s16 else xs, lambda t: t.transpose(1, 2))
             act = None if fused_i else self._buf(plan, f"g{i}.act", (B, Li, ap), adt, zero=True)
             y = None if fused_i else self._buf(plan, f"g{i}.y", (B, Li, Ci))
             self._adain_resblock1(plan, f"{g}.noise_res.{i}", B, Li, Ci, 7 if i == 0 else 11, (1, 3, 5), h_all, xs,
-                                  st_xs, xs, act, y, dict(out_addr=self._addr(xs), out_pitch=Ci))
+                                  st_xs, xs, act, y, dict(out_addr=self._addr(xs), out_pitch=Ci), x16_in=xs16)
             self._tap(plan, f"noise_res{i}", xs, lambda t: t.transpose(1, 2))
             # ups[i]: polyphase transposed conv, + x_source fused as residual (:783-788)
             u = cfg["upsample_rates"][i]
             kk_ = cfg["upsample_kernel_sizes"][i]
-            x = self._buf(plan, f"g{i}.x", (B, Li, Ci))
+            x = None if s16 else self._buf(plan, f"g{i}.x", (B, Li, Ci))
             st_x = self._stats(plan, B, Ci)
             last = i == 1
             self._conv(plan, self.convs[f"{g}.ups.{i}"], self._addr(a_prev), B, L_prev, self._act_pitch(C_prev),
                        L_prev + 1, pad_left=1, up_off=(kk_ - u) // 2, L_true=L_prev * u, L_out=Li,
-                       left_pad=1 if last else 0, out_addr=self._addr(x), out_pitch=Ci,
-                       res=(self._addr(xs), Ci, 0, Li), stats_addr=st_x)
-            self._tap(plan, f"x_stage{i}", x, lambda t: t.transpose(1, 2))
+                       left_pad=1 if last else 0, out_addr=None if s16 else self._addr(x),
+                       out_pitch=Ci, res=(self._addr(xs), Ci, 0, Li), stats_addr=st_x,
+                       out_act=(self._addr(x16), Ci, 1, 1.0) if s16 else None)
+            self._tap(plan, f"x_stage{i}", x16 if s16 else x, lambda t: t.transpose(1, 2))
             # MRF: mean of three AdaINResBlock1 on the same input (:790-796)
-            work = self._buf(plan, f"g{i}.work", (B, Li, Ci))
+            work = None if s16 else self._buf(plan, f"g{i}.work", (B, Li, Ci))
             acc = self._buf(plan, f"g{i}.mrf", (B, Li, Ci))
             a_next = self._buf(plan, f"a{i + 1}", (B, Li, ap), adt, zero=True)
             for j in range(n_k):
@@ -584,7 +605,8 @@ class DecoderEngine:
                     final["scale"] = 1.0 / n_k
                     final["out_act"] = (self._addr(a_next), ap, int(self.tc), 0.1 if i == 0 else 0.01)
                 self._adain_resblock1(plan, f"{g}.resblocks.{i * n_k + j}", B, Li, Ci, cfg["resblock_kernel_sizes"][j],
-                                      cfg["resblock_dilation_sizes"][j], h_all, x, st_x, work, act, y, final)
+                                      cfg["resblock_dilation_sizes"][j], h_all, x, st_x, work, act, y, final,
+                                      x16_in=x16)
             self._tap(plan, f"mrf{i}", acc, lambda t: t.transpose(1, 2))
             a_prev, L_prev, C_prev = a_next, Li, Ci
         # ---- conv_post + iSTFT head (:798-806)

@@ -344,12 +344,35 @@ def _fused_case(lib, B, Lin, Cch, k, dil, x_bf16=False, act="snake", with_res=Tr
     L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused/out_add only")
     torch.cuda.synchronize()
     np.testing.assert_array_equal(addd2.cpu().numpy(), addg)
+    if with_res:
+        # bf16 residual (res_is_bf16): (i) with the fp32 output - the result tile overlays the residual tile in
+        # shared memory; (ii) bf16 output only - the configuration of the running stream inside AdaINResBlock1
+        r16 = rd.to(bf).contiguous()
+        exp16 = got + (r16.float().cpu().numpy() - res) * scale
+        out2 = torch.full((B, Lin, Cch), float("nan"), device="cuda")
+        d.res, d.res_is_bf16 = L.ptr(r16), 1
+        d.out, d.out_add = L.ptr(out2), None
+        ostats.zero_()
+        L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused/res16")
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(out2.cpu().numpy(), exp16, rtol=0, atol=2e-6)
+        oact2 = torch.zeros(B, Lin, Cch, dtype=bf, device="cuda")
+        st2 = torch.zeros_like(ostats)
+        d.out, d.out_act, d.stats = None, L.ptr(oact2), L.ptr(st2)
+        L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), L.ptr(wp), C.byref(d), L.stream()), "fused/res16 bf16 out only")
+        torch.cuda.synchronize()
+        assert torch.equal(oact2, out2.to(bf))
+        np.testing.assert_allclose(st2.cpu().numpy(), ostats.cpu().numpy(), rtol=1e-12, atol=1e-9)
+        ostats.copy_(st2)
+        got_stats = out2.cpu().numpy()
+    else:
+        got_stats = got
     # tolerance: the kernel's fp32 affine / MUFU sine may round an operand to the neighbouring bf16 value
     err = np.abs(got - ref)
     assert np.isfinite(got).all()
     assert err.max() < 3e-2 and err.mean() < 2e-3, (err.max(), err.mean())
-    np.testing.assert_allclose(ostats[..., 0].cpu().numpy(), got.astype(np.float64).sum(1), rtol=1e-4, atol=1e-2)
-    np.testing.assert_allclose(ostats[..., 1].cpu().numpy(), (got.astype(np.float64) ** 2).sum(1), rtol=1e-4, atol=1e-2)
+    np.testing.assert_allclose(ostats[..., 0].cpu().numpy(), got_stats.astype(np.float64).sum(1), rtol=1e-4, atol=1e-2)
+    np.testing.assert_allclose(ostats[..., 1].cpu().numpy(), (got_stats.astype(np.float64) ** 2).sum(1), rtol=1e-4, atol=1e-2)
     np.testing.assert_allclose(oact.float().cpu().numpy(), got, rtol=1e-2, atol=1e-2)
 
 
