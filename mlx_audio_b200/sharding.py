@@ -49,7 +49,7 @@ def bucket_by_length(indices: Sequence[int], frames: Sequence[int], max_batch: i
 
 
 def gather_waveforms(local: Dict[int, torch.Tensor], frames: Sequence[int], assignment: List[List[int]],
-                     dst: int = 0, group=None) -> Optional[List[torch.Tensor]]:
+                     dst: int = 0, group=None, packed: Optional[torch.Tensor] = None) -> Optional[List[torch.Tensor]]:
     """gather(v) of ragged waveforms to ``dst``.  ``local``: {utterance index: (600*T,) float32 tensor} for the
     utterances this rank decoded.  Every rank packs its waveforms into ONE flat buffer (order = its assignment
     list) and rank ``dst`` receives each peer's buffer with a single point-to-point transfer (sizes are known
@@ -60,7 +60,11 @@ def gather_waveforms(local: Dict[int, torch.Tensor], frames: Sequence[int], assi
     mine = assignment[rank]
     dev = next(iter(local.values())).device if local else torch.device("cpu")
     sizes = [[int(frames[i]) * SAMPLES_PER_FRAME for i in assignment[r]] for r in range(world)]
-    flat = torch.cat([local[i].reshape(-1) for i in mine]) if mine else torch.empty(0, dtype=torch.float32, device=dev)
+    if packed is not None:      # the caller already holds its waveforms packed in assignment order
+        flat = packed
+        dev = packed.device
+    else:
+        flat = torch.cat([local[i].reshape(-1) for i in mine]) if mine else torch.empty(0, dtype=torch.float32, device=dev)
     if flat.numel() != sum(sizes[rank]):
         raise ValueError(f"rank {rank}: packed {flat.numel()} samples, expected {sum(sizes[rank])}")
     if rank != dst:
@@ -82,21 +86,84 @@ def gather_waveforms(local: Dict[int, torch.Tensor], frames: Sequence[int], assi
     return out  # type: ignore[return-value]
 
 
+def assign_buckets(frames: Sequence[int], world: int, max_batch: int) -> List[List[Tuple[int, List[int]]]]:
+    """Bucket first, then balance: utterances of equal length T are split into near-equal batches of at most
+    ``max_batch`` and the BATCHES (cost = size * T) are assigned longest-processing-time-first to ``world`` ranks,
+    so that a rank decodes few, large same-T batches instead of many small ones (a ragged corpus dealt utterance by
+    utterance leaves every rank with a handful of utterances per length).  Deterministic on every rank.  Returns
+    per rank [(T, [utterance indices])] ordered by decreasing T."""
+    if world < 1:
+        raise ValueError("world must be >= 1")
+    if max_batch < 1:
+        raise ValueError("max_batch must be >= 1")
+    by_t: Dict[int, List[int]] = {}
+    for i, t in enumerate(frames):
+        by_t.setdefault(int(t), []).append(i)
+    batches: List[Tuple[int, List[int]]] = []
+    for t, ids in by_t.items():
+        n_b = -(-len(ids) // max_batch)
+        base, rem = divmod(len(ids), n_b)
+        k = 0
+        for j in range(n_b):
+            n = base + (1 if j < rem else 0)
+            batches.append((t, ids[k:k + n]))
+            k += n
+    load = [0] * world
+    out: List[List[Tuple[int, List[int]]]] = [[] for _ in range(world)]
+    for t, ids in sorted(batches, key=lambda b: (-len(b[1]) * b[0], -b[0], b[1][0])):
+        r = min(range(world), key=lambda r: (load[r], r))
+        out[r].append((t, ids))
+        load[r] += len(ids) * t
+    # refinement: whole batches leave the ranks up to one batch apart; move the tail of one batch from the most to the
+    # least loaded rank (at most `world` moves), which brings the spread down to about one utterance
+    for _ in range(world):
+        hi = max(range(world), key=lambda r: (load[r], -r))
+        lo = min(range(world), key=lambda r: (load[r], r))
+        gap = load[hi] - load[lo]
+        cand = [(k, b) for k, b in enumerate(out[hi]) if len(b[1]) > 1 and b[0] <= gap // 2]
+        if not cand:
+            break
+        k, (t, ids) = max(cand, key=lambda kb: (len(kb[1][1]), kb[1][0]))
+        n = min(len(ids) - 1, gap // (2 * t))
+        out[hi][k] = (t, ids[:-n])
+        out[lo].append((t, ids[-n:]))
+        load[hi] -= n * t
+        load[lo] += n * t
+    return [sorted(a, key=lambda b: (-b[0], b[1][0])) for a in out]
+
+
 def decode_sharded(decode_batch: Callable[[int, List[int]], torch.Tensor], frames: Sequence[int], max_batch: int = 64,
                    dst: int = 0, group=None) -> Optional[List[torch.Tensor]]:
     """Decode ``len(frames)`` utterances over all ranks.  ``decode_batch(T, ids)`` must return the (len(ids), 1,
     600*T) waveforms of utterances ``ids`` (all of length T) - on the GPU path it is ``Decoder.__call__`` on
-    the rank's own inputs.  Returns the utterance-ordered waveform list on ``dst``."""
+    the rank's own inputs.  Batches are formed and balanced by ``assign_buckets``; each rank writes its waveforms
+    straight into ONE flat buffer (batch order), which is what the gather sends.  Returns the utterance-ordered
+    waveform list on ``dst`` (views of the received buffers), None elsewhere."""
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    assignment = lpt_assign(frames, world)
-    local: Dict[int, torch.Tensor] = {}
-    for t, ids in bucket_by_length(assignment[rank], frames, max_batch):
+    plan = assign_buckets(frames, world, max_batch)
+    assignment = [[i for _, ids in plan[r] for i in ids] for r in range(world)]
+    flat: Optional[torch.Tensor] = None
+    off = 0
+    total = sum(int(frames[i]) for i in assignment[rank]) * SAMPLES_PER_FRAME
+    for t, ids in plan[rank]:
         y = decode_batch(t, ids)
         if y.shape[0] != len(ids) or y.shape[-1] != t * SAMPLES_PER_FRAME:
             raise ValueError(f"decode_batch returned {tuple(y.shape)} for {len(ids)} utterances of T={t}")
-        for k, i in enumerate(ids):
-            local[i] = y[k].reshape(-1).clone()   # the decoder reuses its output buffer
+        if flat is None:
+            flat = torch.empty(total, dtype=torch.float32, device=y.device)
+        n = len(ids) * t * SAMPLES_PER_FRAME
+        flat[off:off + n].copy_(y.reshape(-1))        # the decoder reuses its output buffer
+        off += n
+    if flat is None:   # this rank owns no utterances (fewer batches than ranks)
+        on_gpu = dist.is_initialized() and dist.get_backend(group) == "nccl"
+        flat = torch.empty(0, dtype=torch.float32, device=torch.device("cuda", torch.cuda.current_device()) if on_gpu else "cpu")
+    local: Dict[int, torch.Tensor] = {}
+    off = 0
+    for i in assignment[rank]:
+        n = int(frames[i]) * SAMPLES_PER_FRAME
+        local[i] = flat[off:off + n]
+        off += n
     if world == 1:
         return [local[i] for i in range(len(frames))]
-    return gather_waveforms(local, frames, assignment, dst=dst, group=group)
+    return gather_waveforms(local, frames, assignment, dst=dst, group=group, packed=flat)

@@ -76,6 +76,7 @@ class Plan:
         self._arena_used = 0
         self.captured: Dict[str, torch.Tensor] = {}
         self.capture = False
+        self.zero_bufs: List[torch.Tensor] = []  # buffers whose pad rows / columns must read as zero
         self.conv_ops: Dict[int, ConvDesc] = {}  # op index -> descriptor (for FLOP accounting)
 
     def add(self, fn, *args, launches: int = 1):
@@ -145,7 +146,14 @@ class DecoderEngine:
         self.dev = next(iter(weights.values())).device
         self.w = weights
         self.convs: Dict[str, PreparedConv] = {}
-        self.plans: Dict[Tuple[int, int, bool], Plan] = {}
+        self.plans: Dict[Tuple[int, int], Plan] = {}
+        # Workspace shared by every plan (one forward runs at a time, on one stream): a named pool of byte buffers,
+        # each as large as the largest shape built so far.  Ragged workloads (one plan per (B, T) bucket) then cost
+        # the memory of the largest plan, not the sum (161 distinct lengths).
+        self.pool: Dict[str, torch.Tensor] = {}
+        self.arena_pool: List[torch.Tensor] = []
+        self.pool_grew = False
+        self.active_plan: Optional[Plan] = None
         self.up_scale = int(math.prod(cfg["upsample_rates"])) * cfg["gen_istft_hop_size"]
         assert cfg["gen_istft_n_fft"] == 20 and cfg["gen_istft_hop_size"] == 5, "iSTFT head is specialised for 20/5"
         self._prepare()
@@ -238,16 +246,41 @@ class DecoderEngine:
         return t.data_ptr() + off_elems * t.element_size()
 
     def _buf(self, plan: Plan, name: str, shape, dtype=torch.float32, zero: bool = False) -> torch.Tensor:
-        t = (torch.zeros if zero else torch.empty)(shape, dtype=dtype, device=self.dev)
-        plan.buffers[name] = t
-        return t
+        """A view of the pool entry ``name`` (grown when this shape needs more).  ``zero``: the plan relies on the
+        regions no kernel writes (channel / row padding) reading as zero - see ``activate``."""
+        assert name not in plan.buffers, name
+        nbytes = int(math.prod(shape)) * dtype.itemsize
+        t = self.pool.get(name)
+        if t is None or t.numel() < nbytes:
+            self.pool_grew = self.pool_grew or t is not None
+            t = torch.empty((nbytes + 255) // 256 * 256, dtype=torch.uint8, device=self.dev)
+            self.pool[name] = t
+        v = t[:nbytes].view(dtype).view(shape)
+        plan.buffers[name] = v
+        if zero:
+            plan.zero_bufs.append(v)
+        return v
+
+    def activate(self, plan: Plan):
+        """Make ``plan`` the owner of the shared workspace: another shape may have written where this plan expects
+        zero padding, so those buffers are cleared when the active plan changes (a few memsets, < 1 % of a forward)."""
+        if self.active_plan is not plan:
+            for t in plan.zero_bufs:
+                t.zero_()
+            self.active_plan = plan
 
     def _stats(self, plan: Plan, B: int, C: int) -> int:
         """Carve a zero-initialised (B, C, 2) double slot; returns its device address."""
         need = B * C * 2
         arenas = plan.arenas
         if not arenas or plan._arena_used + need > arenas[-1].numel():
-            arenas.append(torch.zeros(max(need, B * 2 * 8192), dtype=torch.float64, device=self.dev))
+            idx, size = len(arenas), max(need, B * 2 * 8192)
+            if idx == len(self.arena_pool):
+                self.arena_pool.append(torch.zeros(size, dtype=torch.float64, device=self.dev))
+            elif self.arena_pool[idx].numel() < size:
+                self.pool_grew = True
+                self.arena_pool[idx] = torch.zeros(size, dtype=torch.float64, device=self.dev)
+            arenas.append(self.arena_pool[idx][:size])
             plan._arena_used = 0
         a = arenas[-1]
         addr = a.data_ptr() + plan._arena_used * 8
@@ -379,18 +412,18 @@ class DecoderEngine:
         if self.fused and C_ in (128, 256):
             # tensor-core mode: AdaIN + Snake run inside the conv (A-operand transform); the conv1 output y is kept
             # in bf16 (it is only ever normalised, activated and rounded to bf16 again), the residual stream in fp32
-            ybf = plan.buffers.get(f"ybf.{B}.{L_}.{C_}")
+            ybf = plan.buffers.get(f"ybf.{C_}")
             if ybf is None:
-                ybf = self._buf(plan, f"ybf.{B}.{L_}.{C_}", (B, L_, C_), torch.bfloat16)
+                ybf = self._buf(plan, f"ybf.{C_}", (B, L_, C_), torch.bfloat16)
             # bf16 residual stream (KK_RES16, default on): the running x is written by conv2 as bf16 only (statistics
             # still from the fp32 accumulators) and read back as bf16 by the next conv1 (input) and conv2 (residual);
             # x16_in = bf16 copy of x_in from its producer.  The block's output and the MRF sum stay fp32.
             s16 = x16_in is not None
             w16 = None
             if s16:
-                w16 = plan.buffers.get(f"w16.{B}.{L_}.{C_}")
+                w16 = plan.buffers.get(f"w16.{C_}")
                 if w16 is None:
-                    w16 = self._buf(plan, f"w16.{B}.{L_}.{C_}", (B, L_, C_), torch.bfloat16)
+                    w16 = self._buf(plan, f"w16.{C_}", (B, L_, C_), torch.bfloat16)
                 cur = x16_in
             for it in range(3):
                 d = dils[it]

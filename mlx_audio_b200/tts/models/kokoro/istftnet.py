@@ -113,9 +113,21 @@ class Decoder:
     def _plan(self, B: int, T: int) -> Plan:
         eng = self.engine
         key = (B, T)
-        if key not in eng.plans:
-            eng.plans[key] = eng.build_plan(B, T)
-        return eng.plans[key]
+        plan = eng.plans.get(key)
+        if plan is None:
+            eng.pool_grew = False
+            plan = eng.build_plan(B, T)
+            if eng.pool_grew:
+                # a workspace buffer was re-allocated: plans (and graphs) built against the old one would keep it
+                # alive, so they are dropped and rebuilt on demand (call reserve(B_max, T_max) first to avoid this)
+                eng.plans.clear()
+                self._graphs.clear()
+            eng.plans[key] = plan
+        return plan
+
+    def reserve(self, B: int, T: int) -> None:
+        """Size the shared workspace for the largest (B, T) the caller will decode (ragged / bucketed workloads)."""
+        self._plan(B, T)
 
     def __call__(self, asr, F0_curve, N, s, *, noise=None, seed: Optional[int] = None, capture_taps: bool = False):
         L.require_cuda()
@@ -132,6 +144,7 @@ class Decoder:
         if tuple(s.shape) != (B, self.cfg["style_dim"]):
             raise ValueError(f"s must be (B, {self.cfg['style_dim']}), got {tuple(s.shape)}")
         plan = self._plan(B, T)
+        self.engine.activate(plan)
         bufs = plan.buffers
         bufs["in.asr"].copy_(asr, non_blocking=True)
         bufs["in.F0_curve"].copy_(F0_curve, non_blocking=True)

@@ -300,3 +300,26 @@ def test_decoder_default_noise_and_cuda_graph(dec_bf16):
         dec_bf16.use_cuda_graph = False
     torch.cuda.synchronize()
     assert torch.allclose(g1, a, atol=1e-5) and torch.allclose(g1, g2, atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_shared_workspace_across_shapes(dec_bf16):
+    """Plans of different (B, T) share one workspace (ragged corpora: one plan per length bucket).  Switching
+    shapes - including a larger one that re-allocates pool buffers - must not change any result: the zero padding
+    a plan relies on is restored when it becomes active again."""
+    shapes = [(2, 40), (3, 24), (1, 71), (4, 90), (2, 40), (1, 71)]
+    first = {}
+    for B, T in shapes:
+        inp = synth.synth_decoder_inputs(B, T, seed=B * 1000 + T)
+        y = _run(dec_bf16, inp)
+        assert y.shape == (B, 1, 600 * T) and np.isfinite(y).all()
+        if (B, T) in first:
+            np.testing.assert_array_equal(y, first[(B, T)])
+        else:
+            first[(B, T)] = y.copy()
+    eng = dec_bf16.engine
+    # one allocation per named buffer, however many shapes were decoded
+    assert all(t.dtype == torch.uint8 for t in eng.pool.values())
+    for plan in eng.plans.values():
+        for name, v in plan.buffers.items():
+            assert v.untyped_storage().data_ptr() == eng.pool[name].untyped_storage().data_ptr(), name

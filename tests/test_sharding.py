@@ -34,6 +34,30 @@ def test_bucket_by_length():
         sharding.bucket_by_length([0], frames, 0)
 
 
+def test_assign_buckets_partitions_batches_and_balances():
+    rng = np.random.default_rng(4001)
+    frames = rng.integers(240, 401, size=4096).tolist()
+    for world in (1, 2, 4, 8):
+        plan = sharding.assign_buckets(frames, world, 64)
+        assert plan == sharding.assign_buckets(frames, world, 64)
+        assert sorted(i for r in plan for _, ids in r for i in ids) == list(range(4096))
+        for r in plan:
+            assert all(1 <= len(ids) <= 64 and all(frames[i] == t for i in ids) for t, ids in r)
+            assert [t for t, _ in r] == sorted((t for t, _ in r), reverse=True)
+        loads = [sum(t * len(ids) for t, ids in r) for r in plan]
+        assert max(loads) <= 1.005 * (sum(frames) / world)        # within 0.5 % of perfect balance on this corpus
+        # batches stay large: a rank sees every length it owns in one (or, above max_batch, few) batches
+        assert sum(len(r) for r in plan) <= 161 + 4096 // 64 + world
+    # equal lengths: whole batches of 64
+    plan = sharding.assign_buckets([320] * 4096, 8, 64)
+    assert all(len(r) == 8 and all(len(ids) == 64 for _, ids in r) for r in plan)
+    assert sharding.assign_buckets([], 2, 4) == [[], []]
+    with pytest.raises(ValueError):
+        sharding.assign_buckets([1], 0, 4)
+    with pytest.raises(ValueError):
+        sharding.assign_buckets([1], 1, 0)
+
+
 def _fake_wave(i, t):
     """Deterministic stand-in for the decoder output of utterance i (T = t)."""
     n = t * sharding.SAMPLES_PER_FRAME
@@ -85,10 +109,9 @@ def test_decode_sharded_world2_gloo():
     gather = [m for m in msgs if m[0] == "gather"][0]
     assert gather[1] is True and gather[2] == len(frames)
     calls = {m[1]: m[2] for m in msgs if m[0] == "calls"}
-    assign = sharding.lpt_assign(frames, 2)
+    plan = sharding.assign_buckets(frames, 2, 2)
     for r in (0, 1):
-        seen = sorted(i for _, ids in calls[r] for i in ids)
-        assert seen == assign[r]                      # every rank decodes exactly its shard
+        assert calls[r] == [(t, list(ids)) for t, ids in plan[r]]   # every rank decodes exactly its batches, in order
         assert all(len(ids) <= 2 for _, ids in calls[r])
         assert all(frames[i] == t for t, ids in calls[r] for i in ids)
 
