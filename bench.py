@@ -139,7 +139,6 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     inp = synth.synth_decoder_inputs(B, T, seed=1000 + 17 * rank, with_noise=False)
     host = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
     devt = {k: v.to(dev) for k, v in host.items()}
-    out_host = torch.empty(B, 1, S, dtype=torch.float32).pin_memory()
     gather_list = [torch.empty(B, 1, S, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
 
     def step(src):
@@ -174,12 +173,26 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     ms_total = timed(lambda: step(devt), args.steps)
     clocks = sampler.stop() if rank == 0 else None
 
-    def e2e_step():
-        y = step(host)                       # H2D of this step's inputs from pinned memory inside dec()
-        out_host.copy_(y, non_blocking=True)  # D2H of the step's result
-    for _ in range(2):
-        e2e_step()
-    e2e_ms = timed(e2e_step, args.steps)
+    # end to end through the public streaming API: every step copies its inputs from pinned host memory and its
+    # waveforms back to pinned host memory; the copies of neighbouring steps overlap the forward (3 streams)
+    from mlx_audio_b200.streaming import StreamingDecoder
+    sd = StreamingDecoder(dec, depth=2, post=(lambda y: dist.gather(y, gather_list, dst=0)) if world > 1 else None)
+
+    def e2e_run(steps):
+        for wav in sd.run(host for _ in range(steps)):
+            out_host = wav                   # pinned host tensor holding this step's (B, 1, 600 T) result
+        return out_host
+    e2e_run(2)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out_host = e2e_run(args.steps)           # returns after the last device->host copy has completed
+    e1.record()
+    barrier()
+    e2e_t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_t.item())
     h2d = sum(v.numel() * v.element_size() for v in host.values())
     d2h = out_host.numel() * out_host.element_size()
 

@@ -323,3 +323,28 @@ def test_shared_workspace_across_shapes(dec_bf16):
     for plan in eng.plans.values():
         for name, v in plan.buffers.items():
             assert v.untyped_storage().data_ptr() == eng.pool[name].untyped_storage().data_ptr(), name
+
+
+@pytest.mark.gpu
+def test_streaming_decoder_matches_direct_calls(dec_bf16):
+    """StreamingDecoder (copies overlapped with the forward on side streams) returns exactly what one blocking
+    Decoder call per batch returns, in order, for batches of different shapes."""
+    from mlx_audio_b200.streaming import StreamingDecoder
+    shapes = [(2, 30), (2, 30), (1, 55), (3, 18), (2, 30)]
+    batches = []
+    for i, (B, T) in enumerate(shapes):
+        inp = synth.synth_decoder_inputs(B, T, seed=500 + i, with_noise=False)
+        batches.append({k: torch.from_numpy(inp[k]).pin_memory() for k in ("asr", "F0_curve", "N", "s")})
+    dec_bf16.seed = 1234
+    direct = []
+    for b in batches:
+        y = dec_bf16(b["asr"], b["F0_curve"], b["N"], b["s"])
+        torch.cuda.synchronize()
+        direct.append(y.cpu().numpy().copy())
+    dec_bf16.seed = 1234
+    got = [w.numpy().copy() for w in StreamingDecoder(dec_bf16, depth=2).run(iter(batches))]
+    assert len(got) == len(direct)
+    for a, b in zip(got, direct):
+        np.testing.assert_array_equal(a, b)
+    with pytest.raises(ValueError):
+        StreamingDecoder(dec_bf16, depth=1)
