@@ -153,11 +153,15 @@ template <int BN>
 struct TpCfg {
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
-  static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 4 : 6);
+  static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 4 : (BN >= 64 ? 5 : 6));
   static constexpr int NBUF = EPI_NBUF;                      // residual staging tiles per epilogue warp
   static constexpr int STAGING_BYTES = TP_EPI_WARPS * NBUF * EPI_TILE_BYTES;
   static constexpr int STATS_BYTES = 2 * 8 * BN * 4;  // double-buffered [4 lane groups][sum, sumsq][BN]
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES + 384 + 1024;
+  // one 32 x 32 bf16 tile per epilogue warp for the box store of the activation copy (no room next to BN = 256 stages)
+  static constexpr int ACT_BYTES = BN <= 128 ? TP_EPI_WARPS * 2048 : 0;
+  static constexpr int OFF_ACT = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES;
+  static constexpr int OFF_BAR = OFF_ACT + ACT_BYTES;
+  static constexpr int SMEM_BYTES = OFF_BAR + 384 + 1024;
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
   static constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
 };
@@ -166,15 +170,14 @@ template <int BN>
 __global__ void __launch_bounds__(TP_THREADS, 1)
 conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                               const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                              const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles,
+                              const __grid_constant__ CUtensorMap tmAct, const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles,
                               const int direct_epi) {
   using Cfg = TpCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* staging = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
   float* s_stats_all = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::STAGING_BYTES);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::STAGING_BYTES +
-                                                   Cfg::STATS_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::OFF_BAR);
   uint64_t* empty_bar = full_bar + Cfg::STAGES;
   uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
@@ -307,7 +310,8 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
         float cs = 0.f, cq = 0.f;
         if (direct_epi) {
           const uint32_t bufi = item % NBUF;
-          epilogue_chunk_direct(d, &tmOut, b, m0 + lg * 32, n0 + ch * 32, lane,
+          epilogue_chunk_direct(d, &tmOut, &tmAct, Cfg::ACT_BYTES ? smem + Cfg::OFF_ACT + ew * 2048 : nullptr, b,
+                                m0 + lg * 32, n0 + ch * 32, lane,
                                 tmem_base + acc * BN + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32),
                                 stg + bufi * EPI_TILE_BYTES, &rbar[bufi], (item / NBUF) & 1, do_stats, cs, cq);
           if (d.res) {
@@ -466,7 +470,7 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
                      (!d->out_act || (d->act_is_bf16 && al16(d->out_act, (long long)d->act_pitch * 2)));
   // rank-4 polyphase views (tc_epilogue.cuh) of the residual and output tensors; only coordinates whose rows lie
   // inside the utterance are ever issued, so the (possibly negative) row offset folded into the base is harmless
-  CUtensorMap tmRes = tmB, tmOut = tmB;
+  CUtensorMap tmRes = tmB, tmOut = tmB, tmAct = tmB;
   if (direct) {
     const long long off = (long long)d->left_pad - d->up_off;
     cuuint32_t box[4] = {32, 1, 32, 1};
@@ -487,7 +491,17 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
       if (rc) return rc;
     }
   }
-  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, tmRes, tmOut, *d, m_tiles, n_tiles,
+  if (direct && d->out_act && Cfg::ACT_BYTES) {
+    const long long off = (long long)d->left_pad - d->up_off;
+    cuuint32_t box[4] = {32, 1, 32, 1};
+    cuuint64_t dims[4] = {(cuuint64_t)d->C_out, (cuuint64_t)d->up, (cuuint64_t)d->M, (cuuint64_t)d->B};
+    cuuint64_t strides[3] = {(cuuint64_t)d->act_pitch * 2, (cuuint64_t)d->up * d->act_pitch * 2,
+                             (cuuint64_t)d->L_out * d->act_pitch * 2};
+    int rc = make_tmap(&tmAct, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (const __nv_bfloat16*)d->out_act + off * d->act_pitch, 4,
+                       dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
+    if (rc) return rc;
+  }
+  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, tmRes, tmOut, tmAct, *d, m_tiles, n_tiles,
                                                                                (int)total, direct);
   KK_LAUNCH_CHECK("conv1d_bf16_tc_persist_kernel");
   return KK_OK;
