@@ -114,6 +114,73 @@ def decoder_param_specs(cfg: dict = None) -> List[Tuple[str, Tuple[int, ...], st
     return specs
 
 
+def prosody_param_specs(style_dim: int = 128, d_hid: int = 512) -> List[Tuple[str, Tuple[int, ...], str]]:
+    """(name, shape, kind) of the parameters ``ProsodyPredictor.F0Ntrain`` touches (modules.py:295-340), reference key
+    naming, MLX layout: ``predictor.{F0,N}.{0,1,2}.*`` (AdainResBlk1d), ``predictor.{F0,N}_proj.{weight,bias}``
+    (nn.Conv1d(d_hid/2, 1, 1): weight (1, 1, d_hid/2)) and the ``predictor.shared`` bi-LSTM (modules.py:110-150)."""
+    specs: List[Tuple[str, Tuple[int, ...], str]] = []
+    h2 = d_hid // 2
+    for head in ("F0", "N"):
+        for i, (cin, cout, up) in enumerate([(d_hid, d_hid, False), (d_hid, h2, True), (h2, h2, False)]):
+            p = f"predictor.{head}.{i}"
+            for cname, ci, co, k in (("conv1", cin, cout, 3), ("conv2", cout, cout, 3)):
+                specs += [(f"{p}.{cname}.weight_g", (co, 1, 1), "g"), (f"{p}.{cname}.weight_v", (co, k, ci), "v"),
+                          (f"{p}.{cname}.bias", (co,), "bias")]
+            specs += [(f"{p}.norm1.fc.weight", (2 * cin, style_dim), "fc_w"), (f"{p}.norm1.fc.bias", (2 * cin,), "fc_b"),
+                      (f"{p}.norm2.fc.weight", (2 * cout, style_dim), "fc_w"), (f"{p}.norm2.fc.bias", (2 * cout,), "fc_b")]
+            if cin != cout:
+                specs += [(f"{p}.conv1x1.weight_g", (cout, 1, 1), "g"), (f"{p}.conv1x1.weight_v", (cout, 1, cin), "v")]
+            if up:
+                specs += [(f"{p}.pool.weight_g", (cin, 1, 1), "g"), (f"{p}.pool.weight_v", (cin, 3, 1), "v"),
+                          (f"{p}.pool.bias", (cin,), "bias")]
+        specs += [(f"predictor.{head}_proj.weight", (1, 1, h2), "proj_w"), (f"predictor.{head}_proj.bias", (1,), "bias")]
+    for d in ("forward", "backward"):
+        specs += [(f"predictor.shared.Wx_{d}", (2 * d_hid, d_hid + style_dim), "lstm"),
+                  (f"predictor.shared.Wh_{d}", (2 * d_hid, h2), "lstm"),
+                  (f"predictor.shared.bias_ih_{d}", (2 * d_hid,), "lstm"),
+                  (f"predictor.shared.bias_hh_{d}", (2 * d_hid,), "lstm")]
+    return specs
+
+
+def synth_prosody_weights(seed: int = 2100, style_dim: int = 128, d_hid: int = 512) -> Dict[str, np.ndarray]:
+    """Random-init ``predictor.*`` weights with the decoder recipe; projections ~ N(0, 1/C) scaled so that
+    F0 lands in a voiced range (x 60 + bias 150 Hz for F0_proj); LSTM ~ U[-1/sqrt(H), 1/sqrt(H)] (modules.py:108)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    out: Dict[str, np.ndarray] = {}
+    for name, shape, kind in prosody_param_specs(style_dim, d_hid):
+        if kind == "v":
+            a = rng.standard_normal(shape, dtype=np.float32)
+        elif kind == "g":
+            a = rng.uniform(0.7, 1.3, size=shape).astype(np.float32)
+        elif kind == "bias":
+            a = 0.02 * rng.standard_normal(shape, dtype=np.float32)
+        elif kind == "fc_w":
+            a = rng.standard_normal(shape, dtype=np.float32) * np.float32(0.1 / np.sqrt(shape[1]))
+        elif kind == "fc_b":
+            a = np.zeros(shape, np.float32)
+        elif kind == "proj_w":
+            a = rng.standard_normal(shape, dtype=np.float32) / np.float32(np.sqrt(shape[2]))
+            if "F0_proj" in name:
+                a = a * np.float32(60.0)
+        elif kind == "lstm":
+            sc = 1.0 / np.sqrt(d_hid // 2)
+            a = rng.uniform(-sc, sc, size=shape).astype(np.float32)
+        else:  # pragma: no cover
+            raise AssertionError(kind)
+        if name.endswith("F0_proj.bias"):
+            a = a + np.float32(150.0)
+        out[name] = np.ascontiguousarray(a, dtype=np.float32)
+    return out
+
+
+def synth_prosody_inputs(batch: int, frames: int, seed: int = 1100, style_dim: int = 128, d_hid: int = 512
+                         ) -> Dict[str, np.ndarray]:
+    """x ~ N(0,1) (B, d_hid + style, L) (``en``, kokoro.py:157), s ~ 0.5 N(0,1) (B, style)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    return dict(x=rng.standard_normal((batch, d_hid + style_dim, frames), dtype=np.float32),
+                s=(0.5 * rng.standard_normal((batch, style_dim), dtype=np.float32)).astype(np.float32))
+
+
 def synth_decoder_weights(seed: int = 2000, cfg: dict = None) -> Dict[str, np.ndarray]:
     """Random-init decoder weights (float32, MLX layout) following SURVEY.md 8(d):
     weight_v ~ N(0,1); weight_g ~ U[0.7,1.3]; conv bias ~ 0.02 N(0,1);

@@ -154,9 +154,14 @@ class DecoderEngine:
         self.arena_pool: List[torch.Tensor] = []
         self.pool_grew = False
         self.active_plan: Optional[Plan] = None
+        self.pools: Dict[str, Tuple[torch.Tensor, torch.Tensor]] = {}   # depthwise ConvTranspose "pool" per block
+        self._check_cfg()
+        self._prepare()
+
+    def _check_cfg(self):
+        cfg = self.cfg
         self.up_scale = int(math.prod(cfg["upsample_rates"])) * cfg["gen_istft_hop_size"]
         assert cfg["gen_istft_n_fft"] == 20 and cfg["gen_istft_hop_size"] == 5, "iSTFT head is specialised for 20/5"
-        self._prepare()
 
     # ------------------------------------------------------------------ weights
     def _fold(self, prefix: str) -> torch.Tensor:
@@ -173,9 +178,9 @@ class DecoderEngine:
         self.convs[prefix] = PreparedConv(prefix, self._fold(prefix), self.w.get(f"{prefix}.bias"), up,
                                           need_bf16=tc, need_f32=not tc)
 
-    def _prepare(self):
-        w, cfg = self.w, self.cfg
-        # AdaIN fc layers: one concatenated (R, style) matrix -> a single projection launch per forward
+    def _prepare_adain(self):
+        """AdaIN fc layers: one concatenated (R, style) matrix -> a single projection launch per forward."""
+        w = self.w
         self.ada_off: Dict[str, int] = {}
         ws, bs, off = [], [], 0
         for k in sorted(k for k in w if k.endswith(".fc.weight")):
@@ -187,14 +192,23 @@ class DecoderEngine:
         self.ada_W = torch.cat(ws, 0).contiguous()
         self.ada_b = torch.cat(bs, 0).contiguous()
         self.ada_R = off
+
+    def _prep_resblk1d(self, blk: str):
+        """Weights of one AdainResBlk1d (istftnet.py:853-861): conv1, conv2, [conv1x1], [pool]."""
+        w = self.w
+        self._prep_wn(f"{blk}.conv1")
+        self._prep_wn(f"{blk}.conv2")
+        if f"{blk}.conv1x1.weight_v" in w:
+            self._prep_wn(f"{blk}.conv1x1")
+        if f"{blk}.pool.weight_v" in w:
+            self.pools[blk] = (self._fold(f"{blk}.pool").reshape(-1, 3).contiguous(), w[f"{blk}.pool.bias"].contiguous())
+
+    def _prepare(self):
+        w, cfg = self.w, self.cfg
+        self._prepare_adain()
         # front
         for blk in ["encode", "decode.0", "decode.1", "decode.2", "decode.3"]:
-            self._prep_wn(f"{blk}.conv1")
-            self._prep_wn(f"{blk}.conv2")
-            if f"{blk}.conv1x1.weight_v" in w:
-                self._prep_wn(f"{blk}.conv1x1")
-        self.pool_w = self._fold("decode.3.pool").reshape(-1, 3).contiguous()
-        self.pool_b = w["decode.3.pool.bias"].contiguous()
+            self._prep_resblk1d(blk)
         self._prep_wn("asr_res.0", tc=False)
         self.f0_w3b = torch.cat([self._fold("F0_conv").reshape(-1), w["F0_conv.bias"].reshape(-1)]).contiguous()
         self.n_w3b = torch.cat([self._fold("N_conv").reshape(-1), w["N_conv.bias"].reshape(-1)]).contiguous()
@@ -384,12 +398,12 @@ class DecoderEngine:
 
     def _ada(self, plan: Plan, x_addr: int, x_pitch: int, stats_addr: Optional[int], ada_prefix: Optional[str],
              act: int, slope: float, alpha: Optional[torch.Tensor], out: torch.Tensor, out_pitch: int, B: int, L_: int,
-             C_: int, h_all: torch.Tensor, pool: bool = False):
+             C_: int, h_all: torch.Tensor, pool: Optional[str] = None):
         h_addr = self._addr(h_all, self.ada_off[ada_prefix]) if ada_prefix is not None else None
         plan.add(self.lib.kk_adain_act, x_addr, x_pitch, stats_addr, h_addr, self.ada_R,
                  self._addr(alpha), act, slope, self._addr(out), 1 if out.dtype == torch.bfloat16 else 0, out_pitch,
-                 B, L_, C_, 1 if pool else 0, self._addr(self.pool_w) if pool else None,
-                 self._addr(self.pool_b) if pool else None)
+                 B, L_, C_, 1 if pool else 0, self._addr(self.pools[pool][0]) if pool else None,
+                 self._addr(self.pools[pool][1]) if pool else None)
 
     def _tap(self, plan: Plan, name: str, t: torch.Tensor, view: Optional[Callable] = None):
         plan.taps[name] = (t, view)
@@ -487,14 +501,20 @@ class DecoderEngine:
         plan.add(self.lib.kk_instnorm_stats, x_in_addr, st_in, B, L_, C_in, x_pitch)
         act1 = self._buf(plan, f"{name}.act1", (B, Lo, api), adt, zero=True)
         self._ada(plan, x_in_addr, x_pitch, st_in, f"{prefix}.norm1", L.KK_ACT_LEAKY, 0.2, None, act1, api, B, L_, C_in,
-                  h_all, pool=upsample)
-        # shortcut: [nearest x2] -> 1x1 conv without bias; the 1x1 commutes with the repeat, so it runs at L
-        xin_act = self._buf(plan, f"{name}.xin_act", (B, L_, api), adt, zero=True)
-        plan.add(self.lib.kk_convert_act, x_in_addr, x_pitch, self._addr(xin_act), 1 if self.tc else 0, api,
-                 B * L_, C_in, 1.0)
-        sc = self._buf(plan, f"{name}.sc", (B, L_, C_out))
-        self._conv(plan, self.convs[f"{prefix}.conv1x1"], self._addr(xin_act), B, L_, api, L_, use_bias=False,
-                   out_addr=self._addr(sc), out_pitch=C_out)
+                  h_all, pool=prefix if upsample else None)
+        # shortcut: [nearest x2] -> 1x1 conv without bias; the 1x1 commutes with the repeat, so it runs at L.
+        # Without a learned shortcut (dim_in == dim_out, istftnet.py:840) the input itself is the residual.
+        if f"{prefix}.conv1x1" in self.convs:
+            xin_act = self._buf(plan, f"{name}.xin_act", (B, L_, api), adt, zero=True)
+            plan.add(self.lib.kk_convert_act, x_in_addr, x_pitch, self._addr(xin_act), 1 if self.tc else 0, api,
+                     B * L_, C_in, 1.0)
+            sc = self._buf(plan, f"{name}.sc", (B, L_, C_out))
+            self._conv(plan, self.convs[f"{prefix}.conv1x1"], self._addr(xin_act), B, L_, api, L_, use_bias=False,
+                       out_addr=self._addr(sc), out_pitch=C_out)
+            sc_res = (self._addr(sc), C_out, 1 if upsample else 0, L_)
+        else:
+            assert C_in == C_out, (prefix, C_in, C_out)
+            sc_res = (x_in_addr, x_pitch, 1 if upsample else 0, L_)
         y1 = self._buf(plan, f"{name}.y1", (B, Lo, C_out))
         st1 = self._stats(plan, B, C_out)
         self._conv(plan, self.convs[f"{prefix}.conv1"], self._addr(act1), B, Lo, api, Lo, pad_left=1,
@@ -503,8 +523,7 @@ class DecoderEngine:
         self._ada(plan, self._addr(y1), C_out, st1, f"{prefix}.norm2", L.KK_ACT_LEAKY, 0.2, None, act2, apo, B, Lo,
                   C_out, h_all)
         self._conv(plan, self.convs[f"{prefix}.conv2"], self._addr(act2), B, Lo, apo, Lo, pad_left=1,
-                   out_addr=out_addr, out_pitch=out_pitch, res=(self._addr(sc), C_out, 1 if upsample else 0, L_),
-                   scale=1.0 / math.sqrt(2.0), out_act=out_act)
+                   out_addr=out_addr, out_pitch=out_pitch, res=sc_res, scale=1.0 / math.sqrt(2.0), out_act=out_act)
 
     # ------------------------------------------------------------------ the whole decoder
     def build_plan(self, B: int, T: int) -> Plan:

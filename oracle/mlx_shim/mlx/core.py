@@ -167,6 +167,12 @@ abs = _unary(np.abs)  # noqa: A001
 round = _unary(np.round)  # noqa: A001
 
 
+def addmm(c, a, b, alpha=1.0, beta=1.0):
+    """mx.addmm: beta * c + alpha * (a @ b) (used by the reference LSTM, modules.py:156-158)."""
+    a, b, c = _f(a), _f(b), _f(c)
+    return _wrap((np.float32(beta) * c + np.float32(alpha) * np.matmul(a, b)).astype(np.float32))
+
+
 def sigmoid(x):
     x = _f(x)
     return _wrap(1.0 / (1.0 + np.exp(-x)))
@@ -383,6 +389,12 @@ class _Random:
             a = self.rng.standard_normal(shape, dtype=np.float32)
         self.log.append(shape)
         return _wrap(a * np.float32(scale) + np.float32(loc))
+
+    def uniform(self, low=0.0, high=1.0, shape=(), dtype=float32, key=None):
+        """Parameter initialisers of the reference modules (e.g. modules.py:111); values are always overwritten by
+        set_parameter before use."""
+        shape = tuple(int(s) for s in shape)
+        return _wrap(self.rng.uniform(low, high, size=shape).astype(np.float32))
 
     def seed(self, s):
         self.rng = np.random.Generator(np.random.PCG64(s))

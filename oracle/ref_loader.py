@@ -101,3 +101,26 @@ def run_reference_decoder(weights, cfg, asr, F0_curve, N, s, noise):
     out = dec(mx.array(asr), mx.array(F0_curve), mx.array(N), mx.array(s))
     assert not mx.random.queue, "reference drew fewer random tensors than expected"
     return np.asarray(out)
+
+
+def load_reference_modules():
+    """The reference's kokoro/modules.py (ProsodyPredictor, LSTM ...) on the same stubbed package chain."""
+    ns = load_reference()
+    if not hasattr(ns, "modules"):
+        ns.modules = _load("mlx_audio.tts.models.kokoro.modules",
+                           os.path.join(REFERENCE_ROOT, "mlx_audio", "tts", "models", "kokoro", "modules.py"))
+    return ns.modules
+
+
+def run_reference_f0ntrain(weights, x, s, style_dim=128, d_hid=512):
+    """Run the reference ``ProsodyPredictor.F0Ntrain(x, s)`` (modules.py:355-377) with ``weights`` (keys
+    ``predictor.*``: the F0 / N blocks, the projections and the shared LSTM).  Returns (F0, N) numpy arrays."""
+    import numpy as np
+    ns = load_reference()
+    mod = load_reference_modules()
+    pp = mod.ProsodyPredictor(style_dim, d_hid, 3, 50, 0.2)
+    for k, v in weights.items():
+        assert k.startswith("predictor."), k
+        pp.set_parameter(k[len("predictor."):], v)
+    F0, N = pp.F0Ntrain(ns.mx.array(x), ns.mx.array(s))
+    return np.asarray(F0), np.asarray(N)

@@ -114,6 +114,13 @@ def main():
         har_spec=np.asarray(spec).astype(np.float32),
         har_phase=np.asarray(phase).astype(np.float32),
     )
+    # ---- 4. ProsodyPredictor.F0Ntrain (modules.py:355-377): reference modules.py + istftnet.AdainResBlk1d, unmodified
+    Bp, Lp = 2, 12
+    wp = synth.synth_prosody_weights(seed=2100)
+    ip = synth.synth_prosody_inputs(Bp, Lp, seed=1100)
+    F0, N = ref_loader.run_reference_f0ntrain(wp, ip["x"], ip["s"])
+    np.savez_compressed(os.path.join(HERE, "prosody_b2_l12.npz"), backend=backend, weight_seed=2100, input_seed=1100,
+                        batch=Bp, frames=Lp, F0=F0.astype(np.float32), N=N.astype(np.float32))
     print("wrote", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
 
 

@@ -1,0 +1,95 @@
+"""GPU parity of ProsodyPredictor.F0Ntrain against the CPU oracle and the reference golden."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from mlx_audio_b200 import _lib as L
+from mlx_audio_b200 import synth
+from mlx_audio_b200.tts.models.kokoro.modules import build_prosody_predictor
+from oracle.prosody import F0NOracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def weights():
+    return synth.synth_prosody_weights(seed=2100)
+
+
+@pytest.fixture(scope="module")
+def oracle(weights):
+    return F0NOracle(weights)
+
+
+def _np(t):
+    torch.cuda.synchronize()
+    return t.cpu().numpy().copy()
+
+
+def test_f0ntrain_fp32_matches_reference_golden(golden_dir, weights):
+    g = np.load(os.path.join(golden_dir, "prosody_b2_l12.npz"))
+    inp = synth.synth_prosody_inputs(int(g["batch"]), int(g["frames"]), seed=int(g["input_seed"]))
+    pp = build_prosody_predictor(weights, dtype="fp32")
+    F0, N = pp.F0Ntrain(inp["x"], inp["s"])
+    F0, N = _np(F0), _np(N)
+    assert F0.shape == g["F0"].shape and N.shape == g["N"].shape
+    # F0 is in Hz (~100-300): 1e-3 relative to its scale; N is O(1): 1e-3 absolute (the decoder's fp32 gate)
+    assert np.abs(F0 - g["F0"]).max() <= 1e-3 * np.abs(g["F0"]).max(), np.abs(F0 - g["F0"]).max()
+    assert np.abs(N - g["N"]).max() <= 1e-3, np.abs(N - g["N"]).max()
+
+
+@pytest.mark.parametrize("B,Lq", [(1, 200), (3, 37)])
+def test_f0ntrain_fp32_vs_oracle(weights, oracle, B, Lq):
+    inp = synth.synth_prosody_inputs(B, Lq, seed=1200 + Lq)
+    hidden = oracle.hidden_of(inp["x"])
+    F0r, Nr = oracle(s=inp["s"], hidden=hidden)
+    pp = build_prosody_predictor(weights, dtype="fp32")
+    F0, N = pp.F0Ntrain(s=inp["s"], hidden=hidden)           # conv path alone
+    assert np.abs(_np(F0) - F0r).max() <= 1e-3 * np.abs(F0r).max()
+    assert np.abs(_np(N) - Nr).max() <= 1e-3
+    F0b, Nb = pp.F0Ntrain(inp["x"], inp["s"])                # with the cuDNN LSTM in front
+    assert np.abs(_np(F0b) - F0r).max() <= 1e-3 * np.abs(F0r).max()
+    assert np.abs(_np(Nb) - Nr).max() <= 1e-3
+
+
+def test_f0ntrain_bf16_vs_oracle(weights, oracle):
+    if not L.load().kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    inp = synth.synth_prosody_inputs(4, 160, seed=1300)
+    hidden = oracle.hidden_of(inp["x"])
+    F0r, Nr = oracle(s=inp["s"], hidden=hidden)
+    pp = build_prosody_predictor(weights, dtype="bf16")
+    F0, N = pp.F0Ntrain(s=inp["s"], hidden=hidden)
+    F0, N = _np(F0), _np(N)
+    # bf16 operands / fp32 accumulate: stated tolerance 3e-2 relative L2 (same as the decoder's bf16 gate)
+    rel_f0 = np.linalg.norm(F0 - F0r) / np.linalg.norm(F0r - F0r.mean())
+    rel_n = np.linalg.norm(N - Nr) / np.linalg.norm(Nr)
+    print("bf16 F0Ntrain rel-l2:", rel_f0, rel_n)
+    assert rel_f0 <= 3e-2 and rel_n <= 3e-2
+
+
+def test_f0ntrain_feeds_decoder(weights):
+    """F0Ntrain output has the decoder's F0_curve / N contract: (B, 2L) for asr (B, 512, L)."""
+    from mlx_audio_b200.tts.models.kokoro import build_decoder
+    B, Lq = 2, 16
+    inp = synth.synth_prosody_inputs(B, Lq, seed=1400)
+    pp = build_prosody_predictor(weights, dtype="fp32")
+    F0, N = pp.F0Ntrain(inp["x"], inp["s"])
+    assert tuple(F0.shape) == tuple(N.shape) == (B, 2 * Lq)
+    dec = build_decoder(synth.synth_decoder_weights(seed=2000), dtype="fp32")
+    di = synth.synth_decoder_inputs(B, Lq, seed=1000)
+    y = dec(di["asr"], F0.clone(), N.clone(), di["s"], noise=di["noise"])
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, 1, 600 * Lq) and bool(torch.isfinite(y).all())
+
+
+def test_f0ntrain_errors(weights):
+    pp = build_prosody_predictor(weights, dtype="fp32")
+    with pytest.raises(ValueError):
+        pp.F0Ntrain(np.zeros((1, 100, 8), np.float32), np.zeros((1, 128), np.float32))
+    with pytest.raises(ValueError):
+        pp.F0Ntrain(np.zeros((1, 640, 8), np.float32), np.zeros((2, 128), np.float32))
+    with pytest.raises(ValueError):
+        build_prosody_predictor({"predictor.bogus": np.zeros(1, np.float32)})

@@ -209,3 +209,52 @@ def test_param_specs_match_survey_counts(synth_weights):
     assert synth_weights["decoder.generator.ups.0.weight_v"].shape == (512, 20, 256)
     assert synth_weights["decoder.generator.ups.0.bias"].shape == (256,)
     assert synth_weights["decoder.decode.3.pool.weight_v"].shape == (1090, 3, 1)
+
+
+# ------------------------------------------------------------------ ProsodyPredictor.F0Ntrain
+def test_f0ntrain_golden(golden_dir):
+    from oracle.prosody import F0NOracle
+    g = _g(golden_dir, "prosody_b2_l12.npz")
+    w = synth.synth_prosody_weights(seed=int(g["weight_seed"]))
+    inp = synth.synth_prosody_inputs(int(g["batch"]), int(g["frames"]), seed=int(g["input_seed"]))
+    F0, N = F0NOracle(w)(inp["x"], inp["s"])
+    assert F0.shape == g["F0"].shape == (2, 24)
+    assert np.abs(F0 - g["F0"]).max() <= 1e-5 * np.abs(g["F0"]).max()
+    assert np.abs(N - g["N"]).max() <= 1e-5
+
+
+@pytest.mark.skipif(not ref_loader.reference_available(), reason="reference tree not present")
+def test_f0ntrain_oracle_matches_reference_source_live():
+    from oracle.prosody import F0NOracle
+    w = synth.synth_prosody_weights(seed=7)
+    inp = synth.synth_prosody_inputs(1, 9, seed=8)
+    F0r, Nr = ref_loader.run_reference_f0ntrain(w, inp["x"], inp["s"])
+    F0, N = F0NOracle(w)(inp["x"], inp["s"])
+    assert np.abs(F0 - F0r).max() <= 1e-5 * np.abs(F0r).max() and np.abs(N - Nr).max() <= 1e-5
+
+
+def test_f0ntrain_lstm_matches_cudnn_gate_order():
+    # the product runs the shared bi-LSTM through torch (cuDNN on the GPU); gate order i, f, g, o must agree
+    from oracle.prosody import F0NOracle
+    w = synth.synth_prosody_weights(seed=9)
+    inp = synth.synth_prosody_inputs(2, 7, seed=10)
+    o = F0NOracle(w)
+    lstm = torch.nn.LSTM(640, 256, batch_first=True, bidirectional=True)
+    with torch.no_grad():
+        for sfx, d in (("", "forward"), ("_reverse", "backward")):
+            getattr(lstm, f"weight_ih_l0{sfx}").copy_(o.w[f"shared.Wx_{d}"])
+            getattr(lstm, f"weight_hh_l0{sfx}").copy_(o.w[f"shared.Wh_{d}"])
+            getattr(lstm, f"bias_ih_l0{sfx}").copy_(o.w[f"shared.bias_ih_{d}"])
+            getattr(lstm, f"bias_hh_l0{sfx}").copy_(o.w[f"shared.bias_hh_{d}"])
+        got = lstm(torch.from_numpy(inp["x"]).transpose(1, 2))[0].numpy()
+    assert np.abs(got - o.hidden_of(inp["x"])).max() <= 2e-6
+
+
+def test_prosody_sanitize_mirrors_reference():
+    from mlx_audio_b200.tts.models.kokoro.modules import ProsodyPredictor
+    v = np.zeros((256, 512, 3), np.float32)                      # torch layout (O, I, K)
+    assert ProsodyPredictor.sanitize("predictor.F0.1.conv1.weight_v", v)["predictor.F0.1.conv1.weight_v"].shape == (256, 3, 512)
+    assert ProsodyPredictor.sanitize("predictor.F0_proj.weight", np.zeros((1, 256, 1), np.float32))[
+        "predictor.F0_proj.weight"].shape == (1, 1, 256)
+    out = ProsodyPredictor.sanitize("predictor.shared.weight_ih_l0_reverse", np.zeros((1024, 640), np.float32))
+    assert list(out) == ["predictor.shared.Wx_backward"]
