@@ -468,33 +468,43 @@ __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a
   }
 }
 
-// Inverse, streaming form (hop divides n_fft, R = n_fft / hop <= 4): a block walks its frames four at a time; every
-// group inverse-transforms one frame straight from the global half spectrum into its windowed time frame, the block
-// adds the four frames into a ring of running overlap-add sums (gather form: no atomics), emits the four hops that
-// are now complete (divided by the window sum, utils.py:138-150) and moves on.  A block first replays the R - 1
-// frames before its range (warm-up, nothing emitted), the last block drains the tail.
+// Inverse, streaming form (hop divides n_fft, R = n_fft / hop in {1, 2, 4}): a block walks its frames four at a time;
+// every group inverse-transforms one frame straight from the global half spectrum into its (scaled, not yet windowed)
+// time frame in shared memory.  Overlap-add is a gather with the running sums in REGISTERS: thread `tid` owns the
+// output offsets tid + 256 o (o < hop / 256) of every hop, keeps the synthesis-window taps that can touch them
+// (R x hop/256 = 4 values) and the R - 1 partial sums that later frames still add to; per iteration it reads the 16
+// samples of the four new frames that land on its offsets, adds them in increasing frame order (the reference's
+// scatter-add order, utils.py:138-147), emits the four hops that are now complete divided by the window sum
+// (utils.py:150, same order) and carries the rest.  No ring buffer, no atomics, no second pass over the output.
+// A block first replays the frames before its range (warm-up, nothing emitted); the last block drains the tail.
 struct IstftStreamArgs {
   const float* spec; const float* window; float* out;
   int frames, hop, trim, out_len, frames_per_block, R;
 };
 
-__global__ void __launch_bounds__(ff::THREADS) istft_stream_kernel(const IstftStreamArgs a) {
+template <int R>
+__global__ void __launch_bounds__(ff::THREADS, 4) istft_stream_kernel(const IstftStreamArgs a) {
   extern __shared__ __align__(16) unsigned char smem_[];
   constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1, G = ff::GROUPS;
+  constexpr int hop = n_fft / R, OFFS = hop / ff::THREADS;     // R * OFFS == 4
+  static_assert(R * OFFS == 4 && R - 1 <= G, "streaming iSTFT: hop must be 256, 512 or 1024");
   float2* tw = reinterpret_cast<float2*>(smem_);
   float2* tw2 = tw + ff::TW;
-  float* win = reinterpret_cast<float*>(tw2 + bins + 1);
-  float2* bufs = reinterpret_cast<float2*>(win + n_fft);
-  float* ring = reinterpret_cast<float*>(bufs + 2 * G * ff::BUF);   // (G + R) hops of running sums
+  float2* bufs = tw2 + bins + 1;
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
-  const int hop = a.hop, R = a.R;
-  const int ring_len = (G + R) * hop;
 
   ff::fill_tables(tw, tw2);
-  for (int i = threadIdx.x; i < n_fft; i += blockDim.x) win[i] = a.window[i];
-  for (int i = threadIdx.x; i < ring_len; i += blockDim.x) ring[i] = 0.f;
+  // synthesis-window taps of this thread's offsets, and the partial sums carried between iterations
+  float w[OFFS][R], carry[OFFS][R > 1 ? R - 1 : 1];
+#pragma unroll
+  for (int o = 0; o < OFFS; ++o) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) w[o][r] = a.window[r * hop + threadIdx.x + ff::THREADS * o];
+#pragma unroll
+    for (int c = 0; c < (R > 1 ? R - 1 : 1); ++c) carry[o][c] = 0.f;
+  }
   __syncthreads();
 
   const int b = blockIdx.y;
@@ -510,18 +520,29 @@ __global__ void __launch_bounds__(ff::THREADS) istft_stream_kernel(const IstftSt
     const int f = fi + g;
     const bool live = f < a.frames;
     {
+      // L2 prefetch of the next iteration's four spectrum rows (contiguous: 4 * 4104 bytes = 129 lines)
+      const long long nf = (long long)fi + G;
+      if (nf < a.frames) {
+        const char* nx = reinterpret_cast<const char*>(sb + (size_t)nf * bins);
+        const long long nbytes = (long long)min((long long)G, (long long)a.frames - nf) * bins * 8;
+        const long long o = (long long)threadIdx.x * 128;
+        if (o < nbytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(nx + o));
+      }
       // pack: Z[k] = E[k] + i O[k], E = (X[k]+conj(X[nc-k]))/2, O = (X[k]-conj(X[nc-k]))/2 * e^{+2 pi i k/n};
       // the inverse transform is conj(FFT(conj(Z)))/nc, so conj(Z) goes in.  irfft ignores Im X[0], Im X[nc].
       float2 v[8];
       const float2* X = sb + (size_t)(live ? f : 0) * bins;
+      float2 xk[8], xc[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) { xk[t] = __ldg(X + j + NT * t); xc[t] = __ldg(X + NC - (j + NT * t)); }
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         const int k = j + NT * t;
-        float2 xk = __ldg(X + k), xc = __ldg(X + NC - k);
-        if (k == 0) { xk.y = 0.f; xc.y = 0.f; }
-        xc.y = -xc.y;
-        const float2 e = make_float2(0.5f * (xk.x + xc.x), 0.5f * (xk.y + xc.y));
-        const float2 dd = make_float2(0.5f * (xk.x - xc.x), 0.5f * (xk.y - xc.y));
+        float2 a_ = xk[t], c_ = xc[t];
+        if (k == 0) { a_.y = 0.f; c_.y = 0.f; }
+        c_.y = -c_.y;
+        const float2 e = make_float2(0.5f * (a_.x + c_.x), 0.5f * (a_.y + c_.y));
+        const float2 dd = make_float2(0.5f * (a_.x - c_.x), 0.5f * (a_.y - c_.y));
         float2 w2 = tw2[k];
         w2.y = -w2.y;
         const float2 o = ff::cm(dd, w2);
@@ -535,47 +556,55 @@ __global__ void __launch_bounds__(ff::THREADS) istft_stream_kernel(const IstftSt
     {
       float2 v[8];
       ff::pass3(Bf, tw, j, v);
-      float2* tfg = A;   // the group's windowed time frame (n_fft floats), reusing its first exchange buffer
+      float2* tfg = A;   // the group's time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
-        const int i = j + NT * q;
         // conj and the 1/n normalisation of irfft (1/nc here, the factor 1/2 is already inside E and O)
-        tfg[i] = live ? make_float2((v[q].x * inv_nc) * win[2 * i], (-v[q].y * inv_nc) * win[2 * i + 1])
-                      : make_float2(0.f, 0.f);
+        tfg[j + NT * q] = live ? make_float2(v[q].x * inv_nc, -v[q].y * inv_nc) : make_float2(0.f, 0.f);
       }
     }
     __syncthreads();
-    // add the four frames into the ring; the first G hops of the span are complete afterwards.  Position = (hop
-    // hh of the span, offset off inside it): no divisions, frame / window indices follow from hh alone.
-    const int rb = (fi % (G + R)) * hop;                 // ring position of sample fi * hop
-    for (int hh = 0; hh < G - 1 + R; ++hh) {
-      const int hcur = fi + hh;                          // absolute hop index
-      const bool emit = hh < G && hcur >= H0 && hcur < H1;
-      for (int off = threadIdx.x; off < hop; off += blockDim.x) {
-        float sum = 0.f;
+#pragma unroll
+    for (int o = 0; o < OFFS; ++o) {
+      const int off = threadIdx.x + ff::THREADS * o;
+      // the 16 (frame, hop-of-frame) samples on this offset: frame gg's r-th hop lands on hop fi + gg + r
+      float tv[G][R];
+#pragma unroll
+      for (int gg = 0; gg < G; ++gg)
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          tv[gg][r] = __fmul_rn(reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[r * hop + off], w[o][r]);
+#pragma unroll
+      for (int hh = 0; hh < G; ++hh) {
+        float acc = (hh < R - 1) ? carry[o][hh < R - 1 ? hh : 0] : 0.f;
 #pragma unroll
         for (int gg = 0; gg < G; ++gg) {
-          const int r = hh - gg;                         // frame fi + gg covers this hop with its r-th hop
-          if (r >= 0 && r < R) sum += reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[r * hop + off];
+          const int r = hh - gg;
+          if (r >= 0 && r < R) acc = __fadd_rn(acc, tv[gg][r]);
         }
-        int ri = rb + hh * hop + off;
-        if (ri >= ring_len) ri -= ring_len;
-        const float acc = ring[ri] + sum;
-        if (hh < G) {
-          ring[ri] = 0.f;
-          const long long u = (long long)hcur * hop + off;
-          const long long oi = u - a.trim;
-          if (emit && u < total && oi >= 0 && oi < a.out_len) {
-            float ws = 0.f;
-            for (int r = R - 1; r >= 0; --r) {           // increasing frame order, like the reference's loop
-              const int fr = hcur - r;                   // frames covering this sample
-              if (fr >= 0 && fr < a.frames) ws += win[r * hop + off];
-            }
-            a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+        const int hcur = fi + hh;
+        const long long u = (long long)hcur * hop + off;
+        const long long oi = u - a.trim;
+        if (hcur >= H0 && hcur < H1 && u < total && oi >= 0 && oi < a.out_len) {
+          float ws = 0.f;
+#pragma unroll
+          for (int r = R - 1; r >= 0; --r) {             // increasing frame order, like the reference's loop
+            const int fr = hcur - r;                     // frames covering this sample
+            if (fr >= 0 && fr < a.frames) ws = __fadd_rn(ws, w[o][r]);
           }
-        } else {
-          ring[ri] = acc;
+          a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
         }
+      }
+      // partial sums of the next R - 1 hops (frames of this iteration that reach past it)
+#pragma unroll
+      for (int c = 0; c < R - 1; ++c) {
+        float acc = 0.f;
+#pragma unroll
+        for (int gg = 0; gg < G; ++gg) {
+          const int r = G + c - gg;
+          if (r >= 0 && r < R) acc = __fadd_rn(acc, tv[gg][r]);
+        }
+        carry[o][c] = acc;
       }
     }
     __syncthreads();
@@ -671,7 +700,7 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
   a.spec = spec; a.window = window; a.out = out; a.frames = frames; a.hop = hop; a.trim = trim; a.out_len = out_len;
   a.group = kk::stft_group(p.nc) > 4 ? 4 : kk::stft_group(p.nc);
   const int overlap = kk::cdiv(n_fft, hop);
-  if (n_fft == 2 * kk::ff::NC && n_fft % hop == 0 && n_fft / hop <= 4) {   // register-resident radix-8, streaming OLA
+  if (n_fft == 2 * kk::ff::NC && (hop == 256 || hop == 512 || hop == 1024)) {   // register-resident radix-8, streaming OLA
     kk::IstftStreamArgs sa = {};
     sa.spec = spec; sa.window = window; sa.out = out; sa.frames = frames; sa.hop = hop; sa.trim = trim;
     sa.out_len = out_len; sa.R = n_fft / hop;
@@ -680,11 +709,16 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
     int fpb = 32;   // multiple of GROUPS; the R - 1 warm-up frames cost (GROUPS / fpb) extra
     while (fpb < 256 && (long long)kk::cdiv(hops_total, fpb * 2) * B >= 148 * 16) fpb *= 2;
     sa.frames_per_block = fpb;
-    size_t smem = (size_t)kk::ff::TW * 8 + (size_t)(kk::ff::NC + 2) * 8 + (size_t)n_fft * 4 +
-                  (size_t)2 * kk::ff::GROUPS * kk::ff::BUF * 8 + (size_t)(kk::ff::GROUPS + sa.R) * hop * 4 + 16;
-    KK_CUDA(cudaFuncSetAttribute(kk::istft_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    size_t smem = (size_t)kk::ff::TW * 8 + (size_t)(kk::ff::NC + 2) * 8 + (size_t)2 * kk::ff::GROUPS * kk::ff::BUF * 8 + 16;
     dim3 grid(kk::cdiv(hops_total, fpb), B);
-    kk::istft_stream_kernel<<<grid, kk::ff::THREADS, smem, (cudaStream_t)stream>>>(sa);
+    auto launch = [&](auto kern) -> int {
+      KK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      kern<<<grid, kk::ff::THREADS, smem, (cudaStream_t)stream>>>(sa);
+      return KK_OK;
+    };
+    int lrc = sa.R == 4 ? launch(kk::istft_stream_kernel<4>) : sa.R == 2 ? launch(kk::istft_stream_kernel<2>)
+                                                                       : launch(kk::istft_stream_kernel<1>);
+    if (lrc) return lrc;
     KK_LAUNCH_CHECK("istft_stream_kernel");
     return KK_OK;
   }

@@ -191,6 +191,25 @@ def test_vocos_shape_pin_and_batched_roundtrip():
         np.testing.assert_allclose(yb[b].cpu().numpy(), ref, atol=1e-5)
 
 
+@pytest.mark.parametrize("hop", [256, 512, 1024])
+@pytest.mark.parametrize("n", [30000, 24577, 2500])
+def test_istft_streaming_overlap_add_all_hops(hop, n):
+    """The streaming (register-accumulator) iSTFT path: n_fft 1024 with R = n_fft / hop in {4, 2, 1}, ragged lengths
+    (several blocks, warm-up frames, tail drain), with and without ``length=`` - against the oracle restatement of
+    utils.istft (utils.py:104-158), which sums frames in the reference's order."""
+    x = synth.synth_audio(3, n, seed=100 + hop)
+    S = np.stack([dsp.stft(x[b], n_fft=1024, hop_length=hop) for b in range(3)])       # (3, frames, 513)
+    St = torch.from_numpy(S).cuda().transpose(1, 2)
+    y = utils.istft(St, hop_length=hop, win_length=1024)
+    y5 = utils.istft(St, hop_length=hop, win_length=1024, length=n - 777)
+    for b in range(3):
+        ref = dsp.istft(S[b].T, hop_length=hop, win_length=1024)
+        assert tuple(y[b].shape) == ref.shape
+        np.testing.assert_allclose(y[b].cpu().numpy(), ref, atol=1e-5)
+        ref5 = dsp.istft(S[b].T, hop_length=hop, win_length=1024, length=n - 777)
+        np.testing.assert_allclose(y5[b].cpu().numpy(), ref5, atol=1e-5)
+
+
 def test_log_mel_recipes():
     sig = synth.synth_audio(3, 24000, seed=12)
     got = utils.log_mel_spectrogram(torch.from_numpy(sig), n_fft=1024, hop_length=256, n_mels=80)
