@@ -300,7 +300,7 @@ constexpr int MEL_ITEMS = 384;   // <= 8-bin pieces of the filterbank's non-zero
 constexpr int MEL_MAX = 128;     // mel rows with a shared-memory accumulator
 
 template <int MODE>
-__global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a) {
+__global__ void __launch_bounds__(ff::THREADS, 4) stft_fast_kernel(const StftArgs a) {
   extern __shared__ __align__(16) unsigned char smem_[];
   constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1;
   float2* tw = reinterpret_cast<float2*>(smem_);
@@ -408,18 +408,15 @@ __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a
     gsync();
     ff::pass2(A, Bf, tw, j);
     gsync();
-    {
-      float2 v[8];
-      ff::pass3(Bf, tw, j, v);
+    float2 z[8];                                  // z[q] = Z[j + 64 q]: kept in registers for the unpack
+    ff::pass3(Bf, tw, j, z);
 #pragma unroll
-      for (int q = 0; q < 8; ++q) A[ff::pad(j + NT * q)] = v[q];
-    }
+    for (int q = 0; q < 8; ++q) A[ff::pad(j + NT * q)] = z[q];
     gsync();
-    // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i)
+    // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i); Z[k] is this thread's
+    // own z[k / 64], only the mirrored point comes from shared memory
     float* P = reinterpret_cast<float*>(Bf);   // MODE 1: |X|^p of this frame (513 floats <= BUF float2)
-    for (int k = j; k < bins; k += NT) {
-      const float2 zk = A[ff::pad(k & (NC - 1))];
-      float2 zc = A[ff::pad((NC - k) & (NC - 1))];
+    auto unpack_one = [&](int k, float2 zk, float2 zc) {
       zc.y = -zc.y;
       const float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
       const float2 d = ff::cs(zk, zc);
@@ -432,6 +429,14 @@ __global__ void __launch_bounds__(ff::THREADS) stft_fast_kernel(const StftArgs a
         const float m2 = X.x * X.x + X.y * X.y;
         P[k] = a.power == 2 ? m2 : sqrtf(m2);
       }
+    };
+    {
+      float2 zc[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) zc[q] = A[ff::pad((NC - (j + NT * q)) & (NC - 1))];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) unpack_one(j + NT * q, z[q], zc[q]);
+      if (j == 0) unpack_one(NC, z[0], z[0]);
     }
     gsync();
     if (MODE == 1) {

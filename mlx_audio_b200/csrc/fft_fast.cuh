@@ -1,8 +1,8 @@
 // Register-resident 512-point complex FFT (= 1024-point real transform, the n_fft of the reference's 24 kHz mel / Vocos
 // front ends: indextts/mel.py:20-37, codec/models/vocos/mel.py:22-33) for the general STFT / log-mel / iSTFT kernels.
 // One transform = 64 threads x 8 points: three radix-8 Stockham passes, butterflies in registers, two exchanges
-// through shared memory (padded by one element per eight: every exchange is bank-conflict free); a block runs four
-// transforms side by side.  The first pass reads global memory directly (windowed samples / packed half spectrum).
+// through shared memory (XOR-swizzled, see swz(): every exchange access pattern is bank-conflict free); a block runs
+// four transforms side by side.  The first pass reads global memory directly (windowed samples / packed half spectrum).
 #pragma once
 #include "common.cuh"
 
@@ -13,9 +13,17 @@ constexpr int NC = 512;            // complex points
 constexpr int NT = NC / 8;         // threads per transform
 constexpr int GROUPS = 4;          // transforms per block
 constexpr int THREADS = NT * GROUPS;
-constexpr int BUF = NC + NC / 8;   // padded exchange buffer (float2 elements)
+constexpr int BUF = NC;            // exchange buffer (float2 elements), swizzled, no padding
 
-__device__ __forceinline__ int pad(int i) { return i + (i >> 3); }
+// Exchange-buffer swizzle.  A 64-bit shared access is served per half-warp: 16 float2 = the 32 banks once.  Patterns:
+//   consecutive runs  i = j + 64 t          (pass-2 / pass-3 loads, pass-3 stores, unpack)  - any XOR of the low 4
+//                                             bits by a function of i >> 4 keeps an aligned run a permutation;
+//   stride 8          i = 8 j + q           (pass-1 stores): low4 = 8 (j & 1) + q, i >> 4 = j >> 1  -> XOR (i >> 4) & 7
+//                                             spreads the eight j >> 1 over the low three bits;
+//   two octets        i = 64 h + k + 8 q    (pass-2 stores, h = 0 / 1, k < 8): XOR bit 3 with bit 6 (= h) separates them.
+// (The former i + (i >> 3) padding left a 2-way conflict on every consecutive access: 16 elements span 17 slots - ncu
+// counted 3.0 wavefronts per 64-bit load request instead of 2.)
+__device__ __forceinline__ int pad(int i) { return i ^ (((i >> 4) & 7) | ((i >> 3) & 8)); }
 __device__ __forceinline__ float2 cm(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 __device__ __forceinline__ float2 ca(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 cs(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
