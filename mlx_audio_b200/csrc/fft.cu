@@ -299,8 +299,8 @@ __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const Fft
 constexpr int MEL_ITEMS = 384;   // <= 8-bin pieces of the filterbank's non-zero spans (80 htk mels at 1024: ~170)
 constexpr int MEL_MAX = 128;     // mel rows with a shared-memory accumulator
 
-template <int MODE>
-__global__ void __launch_bounds__(ff::THREADS, 4) stft_fast_kernel(const StftArgs a) {
+template <int MODE, bool RT>
+__global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(const StftArgs a) {
   extern __shared__ __align__(16) unsigned char smem_[];
   constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1;
   float2* tw = reinterpret_cast<float2*>(smem_);
@@ -320,8 +320,21 @@ __global__ void __launch_bounds__(ff::THREADS, 4) stft_fast_kernel(const StftArg
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
 
-  ff::fill_tables(tw, tw2);
-  for (int i = threadIdx.x; i < NC; i += blockDim.x) win[i] = make_float2(a.window[2 * i], a.window[2 * i + 1]);
+  // RT: window, twiddles and unpack factors of this thread live in registers (two blocks per SM instead of four)
+  float2 rw[8], rt2[8], rt3[8], ru[8];
+  if (RT) {
+    ff::fill_reg_twiddles(j, rt2, rt3);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      rw[t] = make_float2(a.window[2 * (j + NT * t)], a.window[2 * (j + NT * t) + 1]);
+      float sn, cs_;
+      sincospif(-(float)(j + NT * t) / (float)NC, &sn, &cs_);
+      ru[t] = make_float2(cs_, sn);
+    }
+  } else {
+    ff::fill_tables(tw, tw2);
+    for (int i = threadIdx.x; i < NC; i += blockDim.x) win[i] = make_float2(a.window[2 * i], a.window[2 * i + 1]);
+  }
   if (MODE == 1) {   // non-zero span of every mel filter: one warp per row
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int m = warp; m < a.n_mels; m += ff::THREADS / 32) {
@@ -401,27 +414,30 @@ __global__ void __launch_bounds__(ff::THREADS, 4) stft_fast_kernel(const StftArg
     {
       float2 v[8];
 #pragma unroll
-      for (int t = 0; t < 8; ++t) { const float2 w = win[j + NT * t]; v[t] = make_float2(nx[t].x * w.x, nx[t].y * w.y); }
+      for (int t = 0; t < 8; ++t) {
+        const float2 w = RT ? rw[t] : win[j + NT * t];
+        v[t] = make_float2(nx[t].x * w.x, nx[t].y * w.y);
+      }
       load_frame(f + ff::GROUPS, nx);
       ff::pass1_store(v, A, j);
     }
     gsync();
-    ff::pass2(A, Bf, tw, j);
+    if (RT) ff::pass2_r(A, Bf, rt2, j); else ff::pass2(A, Bf, tw, j);
     gsync();
     float2 z[8];                                  // z[q] = Z[j + 64 q]: kept in registers for the unpack
-    ff::pass3(Bf, tw, j, z);
+    if (RT) ff::pass3_r(Bf, rt3, j, z); else ff::pass3(Bf, tw, j, z);
 #pragma unroll
     for (int q = 0; q < 8; ++q) A[ff::pad(j + NT * q)] = z[q];
     gsync();
     // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i); Z[k] is this thread's
     // own z[k / 64], only the mirrored point comes from shared memory
     float* P = reinterpret_cast<float*>(Bf);   // MODE 1: |X|^p of this frame (513 floats <= BUF float2)
-    auto unpack_one = [&](int k, float2 zk, float2 zc) {
+    auto unpack_one = [&](int k, float2 zk, float2 zc, float2 u) {
       zc.y = -zc.y;
       const float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
       const float2 d = ff::cs(zk, zc);
       const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);  // d / (2i)
-      float2 X = ff::ca(e, ff::cm(tw2[k], o));
+      float2 X = ff::ca(e, ff::cm(u, o));
       if (k == 0 || k == NC) X.y = 0.f;
       if (MODE == 0) {
         if (live) reinterpret_cast<float2*>(a.out)[((size_t)b * a.frames + f) * bins + k] = X;
@@ -435,8 +451,8 @@ __global__ void __launch_bounds__(ff::THREADS, 4) stft_fast_kernel(const StftArg
 #pragma unroll
       for (int q = 0; q < 8; ++q) zc[q] = A[ff::pad((NC - (j + NT * q)) & (NC - 1))];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) unpack_one(j + NT * q, z[q], zc[q]);
-      if (j == 0) unpack_one(NC, z[0], z[0]);
+      for (int q = 0; q < 8; ++q) unpack_one(j + NT * q, z[q], zc[q], RT ? ru[q] : tw2[j + NT * q]);
+      if (j == 0) unpack_one(NC, z[0], z[0], make_float2(-1.f, -0.f));   // e^{-i pi} as sincospif(-1) returns it
     }
     gsync();
     if (MODE == 1) {
@@ -487,8 +503,8 @@ struct IstftStreamArgs {
   int frames, hop, trim, out_len, frames_per_block, R;
 };
 
-template <int R>
-__global__ void __launch_bounds__(ff::THREADS, 4) istft_stream_kernel(const IstftStreamArgs a) {
+template <int R, bool RT>
+__global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(const IstftStreamArgs a) {
   extern __shared__ __align__(16) unsigned char smem_[];
   constexpr int NC = ff::NC, NT = ff::NT, n_fft = 2 * NC, bins = NC + 1, G = ff::GROUPS;
   constexpr int hop = n_fft / R, OFFS = hop / ff::THREADS;     // R * OFFS == 4
@@ -500,7 +516,18 @@ __global__ void __launch_bounds__(ff::THREADS, 4) istft_stream_kernel(const Istf
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
 
-  ff::fill_tables(tw, tw2);
+  float2 rt2[8], rt3[8], ru[8];     // RT: twiddles and pack factors in registers (see stft_fast_kernel)
+  if (RT) {
+    ff::fill_reg_twiddles(j, rt2, rt3);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      float sn, cs_;
+      sincospif(-(float)(j + NT * t) / (float)NC, &sn, &cs_);
+      ru[t] = make_float2(cs_, sn);
+    }
+  } else {
+    ff::fill_tables(tw, tw2);
+  }
   // synthesis-window taps of this thread's offsets, and the partial sums carried between iterations
   float w[OFFS][R], carry[OFFS][R > 1 ? R - 1 : 1];
 #pragma unroll
@@ -548,7 +575,7 @@ __global__ void __launch_bounds__(ff::THREADS, 4) istft_stream_kernel(const Istf
         c_.y = -c_.y;
         const float2 e = make_float2(0.5f * (a_.x + c_.x), 0.5f * (a_.y + c_.y));
         const float2 dd = make_float2(0.5f * (a_.x - c_.x), 0.5f * (a_.y - c_.y));
-        float2 w2 = tw2[k];
+        float2 w2 = RT ? ru[t] : tw2[k];
         w2.y = -w2.y;
         const float2 o = ff::cm(dd, w2);
         v[t] = make_float2(e.x - o.y, -(e.y + o.x));   // conj(e + i*o)
@@ -556,11 +583,11 @@ __global__ void __launch_bounds__(ff::THREADS, 4) istft_stream_kernel(const Istf
       ff::pass1_store(v, A, j);
     }
     gsync();
-    ff::pass2(A, Bf, tw, j);
+    if (RT) ff::pass2_r(A, Bf, rt2, j); else ff::pass2(A, Bf, tw, j);
     gsync();
     {
       float2 v[8];
-      ff::pass3(Bf, tw, j, v);
+      if (RT) ff::pass3_r(Bf, rt3, j, v); else ff::pass3(Bf, tw, j, v);
       float2* tfg = A;   // the group's time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
@@ -632,9 +659,17 @@ static int launch_stft(const StftArgs& a0, const FftPlan& p, int B, cudaStream_t
     size_t smem = (size_t)ff::TW * 8 + (size_t)(ff::NC + 2) * 8 + (size_t)ff::NC * 8 +
                   (size_t)2 * ff::GROUPS * ff::BUF * 8 +
                   (MODE == 1 ? (size_t)2 * (a.n_mels + 4) * 4 + (size_t)MEL_ITEMS * (8 + 32) + (size_t)ff::GROUPS * MEL_MAX * 4 + 16 : 0) + 16;
-    KK_CUDA(cudaFuncSetAttribute(stft_fast_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     dim3 grid(cdiv(a.frames, fpb), B);
-    stft_fast_kernel<MODE><<<grid, ff::THREADS, smem, st>>>(a);
+    // register-table variant once a thread runs enough frames to amortise its 24 sincospif (A/B knob KK_FFT_RT=0/1)
+    static const int rt_env = [] { const char* e = getenv("KK_FFT_RT"); return e ? atoi(e) : -1; }();
+    const bool rt = MODE == 0 && (rt_env >= 0 ? rt_env != 0 : fpb >= 64);   // log-mel: measured slower (2.26 -> 2.66 ms)
+    if (rt) {
+      KK_CUDA(cudaFuncSetAttribute(stft_fast_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      stft_fast_kernel<MODE, true><<<grid, ff::THREADS, smem, st>>>(a);
+    } else {
+      KK_CUDA(cudaFuncSetAttribute(stft_fast_kernel<MODE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      stft_fast_kernel<MODE, false><<<grid, ff::THREADS, smem, st>>>(a);
+    }
     KK_LAUNCH_CHECK("stft_fast_kernel");
     return KK_OK;
   }
@@ -721,8 +756,12 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
       kern<<<grid, kk::ff::THREADS, smem, (cudaStream_t)stream>>>(sa);
       return KK_OK;
     };
-    int lrc = sa.R == 4 ? launch(kk::istft_stream_kernel<4>) : sa.R == 2 ? launch(kk::istft_stream_kernel<2>)
-                                                                       : launch(kk::istft_stream_kernel<1>);
+    // register-table variant: measured slower here (1.35 -> 1.50 ms: the inverse leans on occupancy to cover its
+    // spectrum loads); kept behind KK_IFFT_RT=1 for A/B
+    static const bool rt = [] { const char* e = getenv("KK_IFFT_RT"); return e && atoi(e) != 0; }();
+    int lrc = sa.R == 4 ? (rt ? launch(kk::istft_stream_kernel<4, true>) : launch(kk::istft_stream_kernel<4, false>))
+            : sa.R == 2 ? (rt ? launch(kk::istft_stream_kernel<2, true>) : launch(kk::istft_stream_kernel<2, false>))
+                        : (rt ? launch(kk::istft_stream_kernel<1, true>) : launch(kk::istft_stream_kernel<1, false>));
     if (lrc) return lrc;
     KK_LAUNCH_CHECK("istft_stream_kernel");
     return KK_OK;

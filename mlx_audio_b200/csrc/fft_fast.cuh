@@ -97,5 +97,42 @@ __device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, 
   fft8(v);
 }
 
+
+// Register-table variants: the twiddles a thread needs are the same for every frame (they depend on j only), so a
+// kernel that can afford ~60 more registers keeps them out of shared memory altogether (30 of the 78 64-bit shared
+// requests per thread and frame are table reads).  Same sincospif arguments as fill_tables: bit-identical values.
+__device__ __forceinline__ void fill_reg_twiddles(int j, float2 (&t2)[8], float2 (&t3)[8]) {
+  const int k = j & 7;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    float s, c;
+    sincospif(-2.0f * (float)(t * k) / 64.0f, &s, &c);
+    t2[t] = make_float2(c, s);
+    sincospif(-2.0f * (float)(t * j) / (float)NC, &s, &c);
+    t3[t] = make_float2(c, s);
+  }
+}
+__device__ __forceinline__ void pass2_r(const float2* A, float2* B, const float2 (&t2)[8], int j) {
+  float2 v[8];
+  const int k = j & 7;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    v[t] = A[pad(j + NT * t)];
+    if (t) v[t] = cm(v[t], t2[t]);
+  }
+  fft8(v);
+  const int o = (j >> 3) * 64 + k;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) B[pad(o + 8 * q)] = v[q];
+}
+__device__ __forceinline__ void pass3_r(const float2* B, const float2 (&t3)[8], int j, float2 (&v)[8]) {
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    v[t] = B[pad(j + NT * t)];
+    if (t) v[t] = cm(v[t], t3[t]);
+  }
+  fft8(v);
+}
+
 }  // namespace ff
 }  // namespace kk
