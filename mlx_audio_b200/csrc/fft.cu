@@ -319,6 +319,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
+  const ff::SwzIdx sz(j);
 
   // RT: window, twiddles and unpack factors of this thread live in registers (two blocks per SM instead of four)
   float2 rw[8], rt2[8], rt3[8], ru[8];
@@ -419,15 +420,15 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
         v[t] = make_float2(nx[t].x * w.x, nx[t].y * w.y);
       }
       load_frame(f + ff::GROUPS, nx);
-      ff::pass1_store(v, A, j);
+      ff::pass1_store(v, A, sz);
     }
     gsync();
-    if (RT) ff::pass2_r(A, Bf, rt2, j); else ff::pass2(A, Bf, tw, j);
+    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, tw, j, sz);
     gsync();
     float2 z[8];                                  // z[q] = Z[j + 64 q]: kept in registers for the unpack
-    if (RT) ff::pass3_r(Bf, rt3, j, z); else ff::pass3(Bf, tw, j, z);
+    if (RT) ff::pass3_r(Bf, rt3, sz, z); else ff::pass3(Bf, tw, j, sz, z);
 #pragma unroll
-    for (int q = 0; q < 8; ++q) A[ff::pad(j + NT * q)] = z[q];
+    for (int q = 0; q < 8; ++q) A[sz.cons(q)] = z[q];
     gsync();
     // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i); Z[k] is this thread's
     // own z[k / 64], only the mirrored point comes from shared memory
@@ -449,7 +450,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     {
       float2 zc[8];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) zc[q] = A[ff::pad((NC - (j + NT * q)) & (NC - 1))];
+      for (int q = 0; q < 8; ++q) zc[q] = A[sz.mirror(q)];
 #pragma unroll
       for (int q = 0; q < 8; ++q) unpack_one(j + NT * q, z[q], zc[q], RT ? ru[q] : tw2[j + NT * q]);
       if (j == 0) unpack_one(NC, z[0], z[0], make_float2(-1.f, -0.f));   // e^{-i pi} as sincospif(-1) returns it
@@ -515,6 +516,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
   float2* A = bufs + (2 * g) * ff::BUF;
   float2* Bf = A + ff::BUF;
+  const ff::SwzIdx sz(j);
 
   float2 rt2[8], rt3[8], ru[8];     // RT: twiddles and pack factors in registers (see stft_fast_kernel)
   if (RT) {
@@ -529,13 +531,16 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
     ff::fill_tables(tw, tw2);
   }
   // synthesis-window taps of this thread's offsets, and the partial sums carried between iterations
-  float w[OFFS][R], carry[OFFS][R > 1 ? R - 1 : 1];
+  float w[OFFS][R], carry[OFFS][R > 1 ? R - 1 : 1], ws_full[OFFS];
 #pragma unroll
   for (int o = 0; o < OFFS; ++o) {
 #pragma unroll
     for (int r = 0; r < R; ++r) w[o][r] = a.window[r * hop + threadIdx.x + ff::THREADS * o];
 #pragma unroll
     for (int c = 0; c < (R > 1 ? R - 1 : 1); ++c) carry[o][c] = 0.f;
+    ws_full[o] = 0.f;
+#pragma unroll
+    for (int r = R - 1; r >= 0; --r) ws_full[o] = __fadd_rn(ws_full[o], w[o][r]);   // all R frames present
   }
   __syncthreads();
 
@@ -580,14 +585,14 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
         const float2 o = ff::cm(dd, w2);
         v[t] = make_float2(e.x - o.y, -(e.y + o.x));   // conj(e + i*o)
       }
-      ff::pass1_store(v, A, j);
+      ff::pass1_store(v, A, sz);
     }
     gsync();
-    if (RT) ff::pass2_r(A, Bf, rt2, j); else ff::pass2(A, Bf, tw, j);
+    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, tw, j, sz);
     gsync();
     {
       float2 v[8];
-      if (RT) ff::pass3_r(Bf, rt3, j, v); else ff::pass3(Bf, tw, j, v);
+      if (RT) ff::pass3_r(Bf, rt3, sz, v); else ff::pass3(Bf, tw, j, sz, v);
       float2* tfg = A;   // the group's time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
@@ -606,6 +611,12 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
 #pragma unroll
         for (int r = 0; r < R; ++r)
           tv[gg][r] = __fmul_rn(reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[r * hop + off], w[o][r]);
+      // interior iterations (every hop inside this block's range, every covering frame present, every sample inside
+      // the trimmed output): precomputed window sum, 32-bit addressing
+      const bool interior = fi >= H0 && fi + G <= H1 && fi >= R - 1 && fi + G <= a.frames &&
+                            (long long)fi * hop >= a.trim && (long long)(fi + G) * hop <= total &&
+                            (long long)(fi + G) * hop - a.trim <= a.out_len;
+      float* orow = a.out + (size_t)b * a.out_len + ((long long)fi * hop - a.trim) + off;
 #pragma unroll
       for (int hh = 0; hh < G; ++hh) {
         float acc = (hh < R - 1) ? carry[o][hh < R - 1 ? hh : 0] : 0.f;
@@ -613,6 +624,10 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
         for (int gg = 0; gg < G; ++gg) {
           const int r = hh - gg;
           if (r >= 0 && r < R) acc = __fadd_rn(acc, tv[gg][r]);
+        }
+        if (interior) {
+          orow[hh * hop] = (ws_full[o] != 0.f) ? acc / ws_full[o] : acc;
+          continue;
         }
         const int hcur = fi + hh;
         const long long u = (long long)hcur * hop + off;

@@ -24,6 +24,29 @@ constexpr int BUF = NC;            // exchange buffer (float2 elements), swizzle
 // (The former i + (i >> 3) padding left a 2-way conflict on every consecutive access: 16 elements span 17 slots - ncu
 // counted 3.0 wavefronts per 64-bit load request instead of 2.)
 __device__ __forceinline__ int pad(int i) { return i ^ (((i >> 4) & 7) | ((i >> 3) & 8)); }
+
+// The swizzled addresses of one thread (j < 64) in closed form, so that an access costs an immediate offset or one
+// logic op instead of the five of pad() (address arithmetic was ~30 % of the issued instructions):
+//   cons(t)   = pad(j + 64 t)                        consecutive runs
+//   st1(q)    = pad(8 j + q)                          pass-1 stores
+//   st2(q)    = pad(64 (j >> 3) + (j & 7) + 8 q)      pass-2 stores
+//   mirror(q) = pad((512 - (j + 64 q)) & 511)         the conjugate-symmetric partner of point j + 64 q
+struct SwzIdx {
+  int c0, c1, p1, m7, e, o, kk, d0, d1, zoff;
+  __device__ __forceinline__ explicit SwzIdx(int j) {
+    c0 = j ^ (j >> 4); c1 = c0 ^ 12;
+    p1 = (8 * j) ^ (j & 8); m7 = (j >> 1) & 7;
+    const int h = j >> 3, hb = h & 1;
+    kk = (j & 7) ^ (4 * hb); e = 64 * h + 8 * hb; o = 64 * h + 8 - 8 * hb;
+    const int jm = (64 - j) & 63, m0 = jm ^ (jm >> 4), m1 = m0 ^ 12;
+    zoff = j == 0 ? 64 : 0;
+    d0 = j == 0 ? m1 : m0; d1 = j == 0 ? m0 : m1;
+  }
+  __device__ __forceinline__ int cons(int t) const { return 64 * t + ((t & 1) ? c1 : c0); }
+  __device__ __forceinline__ int st1(int q) const { return p1 + (q ^ m7); }
+  __device__ __forceinline__ int st2(int q) const { return ((q & 1) ? o : e) + 16 * (q >> 1) + (kk ^ (q >> 1)); }
+  __device__ __forceinline__ int mirror(int q) const { return ((64 * (7 - q) + zoff) & 511) + (((7 - q) & 1) ? d1 : d0); }
+};
 __device__ __forceinline__ float2 cm(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 __device__ __forceinline__ float2 ca(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 cs(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
@@ -68,30 +91,29 @@ __device__ __forceinline__ void fill_tables(float2* tw, float2* tw2) {
 }
 
 // pass 1 (ns = 1): v holds points j + 64 t; result to A
-__device__ __forceinline__ void pass1_store(float2 (&v)[8], float2* A, int j) {
+__device__ __forceinline__ void pass1_store(float2 (&v)[8], float2* A, const SwzIdx& z) {
   fft8(v);
 #pragma unroll
-  for (int q = 0; q < 8; ++q) A[pad(8 * j + q)] = v[q];
+  for (int q = 0; q < 8; ++q) A[z.st1(q)] = v[q];
 }
 // pass 2 (ns = 8): A -> B
-__device__ __forceinline__ void pass2(const float2* A, float2* B, const float2* tw, int j) {
+__device__ __forceinline__ void pass2(const float2* A, float2* B, const float2* tw, int j, const SwzIdx& z) {
   float2 v[8];
   const int k = j & 7;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    v[t] = A[pad(j + NT * t)];
+    v[t] = A[z.cons(t)];
     if (t) v[t] = cm(v[t], tw[t * 8 + k]);
   }
   fft8(v);
-  const int o = (j >> 3) * 64 + k;
 #pragma unroll
-  for (int q = 0; q < 8; ++q) B[pad(o + 8 * q)] = v[q];
+  for (int q = 0; q < 8; ++q) B[z.st2(q)] = v[q];
 }
 // pass 3 (ns = 64): B -> registers; v[q] = point j + 64 q of the transform
-__device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, float2 (&v)[8]) {
+__device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, const SwzIdx& z, float2 (&v)[8]) {
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    v[t] = B[pad(j + NT * t)];
+    v[t] = B[z.cons(t)];
     if (t) v[t] = cm(v[t], tw[64 + t * 64 + j]);
   }
   fft8(v);
@@ -112,23 +134,21 @@ __device__ __forceinline__ void fill_reg_twiddles(int j, float2 (&t2)[8], float2
     t3[t] = make_float2(c, s);
   }
 }
-__device__ __forceinline__ void pass2_r(const float2* A, float2* B, const float2 (&t2)[8], int j) {
+__device__ __forceinline__ void pass2_r(const float2* A, float2* B, const float2 (&t2)[8], const SwzIdx& z) {
   float2 v[8];
-  const int k = j & 7;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    v[t] = A[pad(j + NT * t)];
+    v[t] = A[z.cons(t)];
     if (t) v[t] = cm(v[t], t2[t]);
   }
   fft8(v);
-  const int o = (j >> 3) * 64 + k;
 #pragma unroll
-  for (int q = 0; q < 8; ++q) B[pad(o + 8 * q)] = v[q];
+  for (int q = 0; q < 8; ++q) B[z.st2(q)] = v[q];
 }
-__device__ __forceinline__ void pass3_r(const float2* B, const float2 (&t3)[8], int j, float2 (&v)[8]) {
+__device__ __forceinline__ void pass3_r(const float2* B, const float2 (&t3)[8], const SwzIdx& z, float2 (&v)[8]) {
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
-    v[t] = B[pad(j + NT * t)];
+    v[t] = B[z.cons(t)];
     if (t) v[t] = cm(v[t], t3[t]);
   }
   fft8(v);
