@@ -162,6 +162,13 @@ int kk_logmel_f32(const float* x, const float* window, const float* fb, float* o
  * out (B, out_len): out[i] = ola[i + trim] / wsum (where wsum != 0), ola length (frames-1)*hop + n_fft. */
 int kk_istft_f32(const float* spec, const float* window, float* out, int B, int frames, int n_fft, int hop,
                  int trim, int out_len, void* stream);
+/* Vocos ISTFTHead polar stage (mlx_audio/codec/models/vocos/vocos.py:126-133): x (rows, x_pitch) holding
+ * [log-magnitude (bins) | phase (bins)] per frame -> spec (rows, bins, 2) = min(exp(m), clip) * (cos p, sin p),
+ * frame-major like kk_stft_f32's output, ready for kk_istft_f32. */
+int kk_polar_to_spec(const float* x, int x_pitch, float* spec, long long rows, int bins, float clip, void* stream);
+/* Whisper log-mel dynamic-range step (mlx_audio/stt/models/whisper/audio.py:80-81), in place, per signal of n_per
+ * values: m = max(x); x = (max(x, m - range) + add) * scale   [reference: range 8, add 4, scale 1/4]. */
+int kk_clamp_below_max_affine(float* x, int B, long long n_per, float range, float add, float scale, void* stream);
 
 #ifdef __cplusplus
 }

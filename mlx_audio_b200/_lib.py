@@ -76,6 +76,8 @@ PROTOTYPES = {
     "kk_stft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "kk_logmel_f32": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "kk_istft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
+    "kk_polar_to_spec": [_P, _I, _P, _LL, _I, _F, _P],
+    "kk_clamp_below_max_affine": [_P, _I, _LL, _F, _F, _F, _P],
 }
 
 _lib: Optional[C.CDLL] = None

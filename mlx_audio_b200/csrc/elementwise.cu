@@ -344,6 +344,63 @@ extern "C" int kk_copy_channels(const float* src, int src_pitch, int src_off, fl
   return KK_OK;
 }
 
+namespace kk {
+// Vocos ISTFTHead (codec/models/vocos/vocos.py:126-133): rows of [log-magnitude (bins) | phase (bins)] ->
+// S = min(exp(m), clip) * (cos p + i sin p), written frame-major (rows, bins, 2) - the layout kk_istft_f32 reads.
+__global__ void __launch_bounds__(256) polar_to_spec_kernel(const float* __restrict__ x, int x_pitch,
+                                                            float2* __restrict__ spec, long long rows, int bins,
+                                                            float clip) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * bins) return;
+  const long long r = i / bins;
+  const int k = (int)(i - r * bins);
+  const float* xr = x + r * x_pitch;
+  const float mag = fminf(expf(xr[k]), clip);
+  float sn, cs;
+  sincosf(xr[bins + k], &sn, &cs);
+  spec[i] = make_float2(mag * cs, mag * sn);
+}
+}  // namespace kk
+
+extern "C" int kk_polar_to_spec(const float* x, int x_pitch, float* spec, long long rows, int bins, float clip,
+                                void* stream) {
+  KK_CHECK_ARG(x && spec && rows > 0 && bins > 0 && x_pitch >= 2 * bins, "kk_polar_to_spec: bad arguments");
+  const long long total = rows * bins;
+  KK_CHECK_ARG(kk::cdiv(total, 256) <= 0x7fffffffLL, "kk_polar_to_spec: too many elements");
+  kk::polar_to_spec_kernel<<<(unsigned)kk::cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      x, x_pitch, reinterpret_cast<float2*>(spec), rows, bins, clip);
+  KK_LAUNCH_CHECK("polar_to_spec_kernel");
+  return KK_OK;
+}
+
+namespace kk {
+// Whisper log-mel dynamic-range step (stt/models/whisper/audio.py:80-81): per signal m = max(x),
+// x <- (max(x, m - range) + add) * scale.  One block per signal (<= 3000 x 128 values): two passes over L2-resident data.
+__global__ void __launch_bounds__(1024) clamp_below_max_affine_kernel(float* __restrict__ x, long long n_per,
+                                                                      float range, float add, float scale) {
+  __shared__ float red[32];
+  float* xb = x + (size_t)blockIdx.x * n_per;
+  float m = -INFINITY;
+  for (long long i = threadIdx.x; i < n_per; i += blockDim.x) m = fmaxf(m, xb[i]);
+  for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  m = red[threadIdx.x & 31];
+  for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+  const float lo = __fadd_rn(m, -range);
+  for (long long i = threadIdx.x; i < n_per; i += blockDim.x)
+    xb[i] = __fmul_rn(__fadd_rn(fmaxf(xb[i], lo), add), scale);
+}
+}  // namespace kk
+
+extern "C" int kk_clamp_below_max_affine(float* x, int B, long long n_per, float range, float add, float scale,
+                                         void* stream) {
+  KK_CHECK_ARG(x && B > 0 && n_per > 0, "kk_clamp_below_max_affine: bad arguments");
+  kk::clamp_below_max_affine_kernel<<<B, 1024, 0, (cudaStream_t)stream>>>(x, n_per, range, add, scale);
+  KK_LAUNCH_CHECK("clamp_below_max_affine_kernel");
+  return KK_OK;
+}
+
 extern "C" int kk_convert_act(const float* x, int x_pitch, void* out, int out_is_bf16, int out_pitch, long long rows,
                               int C, float slope, void* stream) {
   KK_CHECK_ARG(x && out && rows > 0 && C > 0, "kk_convert_act: bad arguments");

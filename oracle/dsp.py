@@ -180,3 +180,17 @@ def log_mel_whisper(x, n_mels=80, n_fft=400, hop_length=160, sample_rate=16000, 
     log_spec = np.log10(np.maximum(mel, dt(1e-10))).astype(dtype)
     log_spec = np.maximum(log_spec, log_spec.max() - dt(8.0))
     return ((log_spec + dt(4.0)) / dt(4.0)).astype(dtype)
+
+
+def istft_head_vocos(x, weight, bias, n_fft: int, hop_length: int, dtype=np.float32) -> np.ndarray:
+    """codec/models/vocos/vocos.py:119-140 ``ISTFTHead``: x (1, L, dim); Linear(dim, n_fft + 2) -> [log-mag | phase]
+    -> min(exp(mag), 1e2) * (cos p + i sin p) -> istft with the SYMMETRIC hanning(n_fft) window (passed as an array, so
+    utils.istft does not make it periodic), hop_length, win_length = n_fft.  Returns the 1-D signal."""
+    x = np.asarray(x, dtype)
+    h = (x @ np.asarray(weight, dtype).T + np.asarray(bias, dtype)).astype(dtype)     # nn.Linear :124
+    h = np.swapaxes(h, 1, 2)                                                           # (1, n_fft + 2, L)
+    mag, p = np.split(h, 2, axis=1)
+    mag = np.minimum(np.exp(mag), dtype(1e2))                                          # :129-130
+    S = mag * (np.cos(p) + 1j * np.sin(p))
+    return istft(S[0].astype(np.complex64), window=hanning(n_fft, dtype), hop_length=hop_length, win_length=n_fft,
+                 dtype=dtype)

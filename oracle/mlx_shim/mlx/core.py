@@ -138,6 +138,9 @@ class array(np.ndarray):
     def flatten(self, *a, **k):
         return _wrap(np.ndarray.flatten(_raw(self)))
 
+    def split(self, n, axis=0):          # mx.array.split(indices_or_sections, axis)
+        return [_wrap(np.ascontiguousarray(p)) for p in np.split(_raw(self), n, axis=axis)]
+
     def astype(self, dtype, *a, **k):
         return _raw(self).astype(dtype).view(array)
 

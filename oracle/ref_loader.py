@@ -124,3 +124,32 @@ def run_reference_f0ntrain(weights, x, s, style_dim=128, d_hid=512):
         pp.set_parameter(k[len("predictor."):], v)
     F0, N = pp.F0Ntrain(ns.mx.array(x), ns.mx.array(s))
     return np.asarray(F0), np.asarray(N)
+
+
+def load_reference_frontends():
+    """The reference's log-mel front ends and the Vocos ``ISTFTHead``, loaded from their own source
+    files: codec/models/vocos/{mel,vocos}.py, tts/models/indextts/mel.py, stt/models/whisper/audio.py.  Unrelated
+    imports of those files (Encodec, load_audio) are stubbed; nothing of them is on the tested path."""
+    ns = load_reference()
+    if hasattr(ns, "vocos"):
+        return ns
+    root = os.path.join(REFERENCE_ROOT, "mlx_audio")
+    _pkg("mlx_audio.codec", os.path.join(root, "codec"))
+    _pkg("mlx_audio.codec.models", os.path.join(root, "codec", "models"))
+    _pkg("mlx_audio.codec.models.vocos", os.path.join(root, "codec", "models", "vocos"))
+    enc = _pkg("mlx_audio.codec.models.encodec", os.path.join(root, "codec", "models", "encodec"))
+    enc.Encodec = type("Encodec", (), {})
+    _pkg("mlx_audio.tts.models.indextts", os.path.join(root, "tts", "models", "indextts"))
+    stt = _pkg("mlx_audio.stt", os.path.join(root, "stt"))
+    stt_utils = types.ModuleType("mlx_audio.stt.utils")
+    stt_utils.load_audio = lambda *a, **k: (_ for _ in ()).throw(RuntimeError("load_audio is stubbed"))
+    sys.modules["mlx_audio.stt.utils"] = stt_utils
+    stt.utils = stt_utils
+    _pkg("mlx_audio.stt.models", os.path.join(root, "stt", "models"))
+    _pkg("mlx_audio.stt.models.whisper", os.path.join(root, "stt", "models", "whisper"))
+    ns.vocos_mel = _load("mlx_audio.codec.models.vocos.mel", os.path.join(root, "codec", "models", "vocos", "mel.py"))
+    ns.vocos = _load("mlx_audio.codec.models.vocos.vocos", os.path.join(root, "codec", "models", "vocos", "vocos.py"))
+    ns.indextts_mel = _load("mlx_audio.tts.models.indextts.mel", os.path.join(root, "tts", "models", "indextts", "mel.py"))
+    ns.whisper_audio = _load("mlx_audio.stt.models.whisper.audio",
+                             os.path.join(root, "stt", "models", "whisper", "audio.py"))
+    return ns

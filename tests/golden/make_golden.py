@@ -121,6 +121,28 @@ def main():
     F0, N = ref_loader.run_reference_f0ntrain(wp, ip["x"], ip["s"])
     np.savez_compressed(os.path.join(HERE, "prosody_b2_l12.npz"), backend=backend, weight_seed=2100, input_seed=1100,
                         batch=Bp, frames=Lp, F0=F0.astype(np.float32), N=N.astype(np.float32))
+    # ---- 5. consumers of the shared DSP: the reference's own front-end files
+    fe = ref_loader.load_reference_frontends()
+    sig24 = synth.synth_audio(1, 24000, seed=12)[0]
+    rngh = np.random.Generator(np.random.PCG64(31))
+    dim, Lh = 64, 20
+    hw = (rngh.standard_normal((1026, dim), dtype=np.float32) * np.float32(0.2)).astype(np.float32)
+    hb = (rngh.standard_normal((1026,), dtype=np.float32) * np.float32(0.1)).astype(np.float32)
+    hb[:513] -= np.float32(1.0)
+    hx = rngh.standard_normal((1, Lh, dim), dtype=np.float32)
+    head = fe.vocos.ISTFTHead(dim, 1024, 256)
+    head.set_parameter("out.weight", hw)
+    head.set_parameter("out.bias", hb)
+    np.savez_compressed(
+        os.path.join(HERE, "frontends.npz"), backend=backend, audio_seed=12, n=24000, head_seed=31, head_dim=dim,
+        head_frames=Lh,
+        vocos_mel=np.asarray(fe.vocos_mel.log_mel_spectrogram(mx.array(sig24))).astype(np.float32),
+        vocos_mel_pad=np.asarray(fe.vocos_mel.log_mel_spectrogram(mx.array(sig24), n_mels=80, padding=300)).astype(np.float32),
+        indextts_mel=np.asarray(fe.indextts_mel.log_mel_spectrogram(mx.array(sig24))).astype(np.float32),
+        whisper_mel=np.asarray(fe.whisper_audio.log_mel_spectrogram(sig24)).astype(np.float32),
+        whisper_mel_128=np.asarray(fe.whisper_audio.log_mel_spectrogram(sig24, n_mels=128, padding=480)).astype(np.float32),
+        istft_head=np.asarray(head(mx.array(hx))).astype(np.float32),
+    )
     print("wrote", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
 
 

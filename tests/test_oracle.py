@@ -258,3 +258,30 @@ def test_prosody_sanitize_mirrors_reference():
         "predictor.F0_proj.weight"].shape == (1, 1, 256)
     out = ProsodyPredictor.sanitize("predictor.shared.weight_ih_l0_reverse", np.zeros((1024, 640), np.float32))
     assert list(out) == ["predictor.shared.Wx_backward"]
+
+
+# ------------------------------------------------------------------ shared-DSP consumers
+def _head_inputs(g):
+    rng = np.random.Generator(np.random.PCG64(int(g["head_seed"])))
+    dim, Lh = int(g["head_dim"]), int(g["head_frames"])
+    hw = (rng.standard_normal((1026, dim), dtype=np.float32) * np.float32(0.2)).astype(np.float32)
+    hb = (rng.standard_normal((1026,), dtype=np.float32) * np.float32(0.1)).astype(np.float32)
+    hb[:513] -= np.float32(1.0)
+    hx = rng.standard_normal((1, Lh, dim), dtype=np.float32)
+    return hw, hb, hx
+
+
+def test_frontends_golden(golden_dir):
+    g = _g(golden_dir, "frontends.npz")
+    sig = synth.synth_audio(1, int(g["n"]), seed=int(g["audio_seed"]))[0]
+    v = dsp.log_mel_vocos(sig, n_mels=100, drop_last=True)
+    assert g["vocos_mel"].shape == (1,) + v.shape == (1, 93, 100)
+    assert np.abs(v - g["vocos_mel"][0]).max() < 2e-4
+    i = dsp.log_mel_vocos(sig, n_mels=100)
+    assert g["indextts_mel"].shape == (1, 94, 100) and np.abs(i - g["indextts_mel"][0]).max() < 2e-4
+    w = dsp.log_mel_whisper(sig)
+    assert g["whisper_mel"].shape == w.shape == (150, 80) and np.abs(w - g["whisper_mel"]).max() < 2e-4
+    hw, hb, hx = _head_inputs(g)
+    y = dsp.istft_head_vocos(hx, hw, hb, 1024, 256)
+    assert y.shape == g["istft_head"].shape == ((int(g["head_frames"]) - 1) * 256,)
+    assert np.abs(y - g["istft_head"]).max() < 1e-5 * max(1.0, float(np.abs(g["istft_head"]).max()))
