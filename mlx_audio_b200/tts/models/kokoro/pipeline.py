@@ -65,15 +65,26 @@ class KokoroPipeline:
             raise ValueError(f"voice pack must be (N, 1, 256), got {pack.shape}")
         self.voices[name] = pack
 
-    def load_voice(self, voice: str) -> np.ndarray:
+    def load_single_voice(self, voice: str) -> np.ndarray:
+        """pipeline.py:129-145 for local files: a registered name or a path to a .pt / .npy / .npz / .safetensors pack."""
         if voice in self.voices:
             return self.voices[voice]
-        if voice.endswith(".npy") or voice.endswith(".npz"):
-            arr = np.load(voice)
-            self.add_voice(voice, arr if isinstance(arr, np.ndarray) else arr[arr.files[0]])
+        if voice.endswith((".pt", ".pth", ".npy", ".npz", ".safetensors")):
+            from .voice import load_voice_tensor
+            self.add_voice(voice, load_voice_tensor(voice))
             return self.voices[voice]
-        raise ValueError(f"unknown voice {voice!r}: register it with add_voice(name, pack) or pass a .npy path "
-                         "(downloading voice packs from the hub is outside this path)")
+        raise ValueError(f"unknown voice {voice!r}: register it with add_voice(name, pack) or pass a path to a .pt "
+                         "pack (downloading voice packs from the hub is outside this path)")
+
+    def load_voice(self, voice: str, delimiter: str = ",") -> np.ndarray:
+        """pipeline.py:154-163: ``"a,b"`` averages the packs."""
+        if voice in self.voices:
+            return self.voices[voice]
+        packs = [self.load_single_voice(v) for v in voice.split(delimiter)]
+        if len(packs) == 1:
+            return packs[0]
+        self.voices[voice] = np.mean(np.stack(packs), axis=0).astype(np.float32)
+        return self.voices[voice]
 
     # ---- G2P (lazy; out of scope, pluggable)
     @property
