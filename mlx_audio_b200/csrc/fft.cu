@@ -297,7 +297,7 @@ __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const Fft
 // global memory (float2, coalesced; reflect / zero padding only on the edge frames), the half spectrum is unpacked
 // from the last exchange buffer.  MODE 1 (log-mel) keeps |X|^p in shared memory and projects it there.
 constexpr int MEL_ITEMS = 384;   // <= 8-bin pieces of the filterbank's non-zero spans (80 htk mels at 1024: ~170)
-constexpr int MEL_MAX = 128;     // mel rows with a shared-memory accumulator
+constexpr int MEL_MAX = 128;     // sizes the flag array: GROUPS * MEL_MAX >= MEL_ITEMS words
 
 template <int MODE, bool RT>
 __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(const StftArgs a) {
@@ -314,7 +314,8 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
   int* it_m = mel_hi + (MODE == 1 ? nm2 : 0);               // [MEL_ITEMS] mel row of the item
   int* it_k = it_m + (MODE == 1 ? MEL_ITEMS : 0);           // [MEL_ITEMS] first bin
   float* fbc = reinterpret_cast<float*>(it_k + (MODE == 1 ? MEL_ITEMS : 0));   // [MEL_ITEMS][8] weights, zero padded
-  float* melacc = fbc + (MODE == 1 ? MEL_ITEMS * 8 : 0);    // [GROUPS][MEL_MAX]
+  int* it_f = reinterpret_cast<int*>(fbc + (MODE == 1 ? MEL_ITEMS * 8 : 0));   // [MEL_ITEMS] reduction flags (<= GROUPS * MEL_MAX words)
+  float* melacc = reinterpret_cast<float*>(it_f);
   int* n_items_s = reinterpret_cast<int*>(melacc + (MODE == 1 ? ff::GROUPS * MEL_MAX : 0));
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
   float2* A = bufs + (2 * g) * ff::BUF;
@@ -351,21 +352,32 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     }
     __syncthreads();
     if (threadIdx.x == 0) {   // item list (serial over the rows: a few hundred cheap steps, once per block)
+      // A row's items are consecutive and never straddle a group of 32 (dummy items pad the group), so that a warp
+      // reduces them with shuffles and the row's first item owns the result: no atomics, no accumulator array.
+      // it_f: bit d (d < 4) = item + 2^d belongs to the same row; bit 4 = first item of its row.
       int n = 0;
-      for (int m = 0; m < a.n_mels && n >= 0; ++m)
-        for (int k0 = mel_lo[m]; k0 < mel_hi[m]; k0 += 8) {
-          if (n >= MEL_ITEMS) { n = -1; break; }   // too dense for the table: row-loop fallback
-          it_m[n] = m; it_k[n] = k0; ++n;
+      auto dummy = [&]() { it_m[n] = -1; it_k[n] = 0; it_f[n] = 0; ++n; };
+      for (int m = 0; m < a.n_mels && n >= 0; ++m) {
+        const int lo = mel_lo[m], hi = mel_hi[m];
+        const int cnt = lo < hi ? (hi - lo + 7) / 8 : 1;     // an all-zero row still reports log(floor)
+        if (cnt > 16) { n = -1; break; }                     // four shuffle steps cover 16 items
+        if ((n & 31) + cnt > 32) while ((n & 31) && n < MEL_ITEMS) dummy();
+        if (n + cnt > MEL_ITEMS) { n = -1; break; }          // too dense for the table: row-loop fallback
+        for (int c = 0; c < cnt; ++c) {
+          int fl = c == 0 ? 16 : 0;
+          for (int d = 0; d < 4; ++d) if (c + (1 << d) < cnt) fl |= 1 << d;
+          it_m[n] = m; it_k[n] = lo < hi ? lo + 8 * c : 0; it_f[n] = fl; ++n;
         }
-      if (a.n_mels > MEL_MAX) n = -1;
+      }
+      if (n > 0) while ((n & 31) && n < MEL_ITEMS) dummy();
+      if (n > 0 && (n & 31)) n = -1;
       *n_items_s = n;
     }
     __syncthreads();
     for (int i = threadIdx.x; i < max(*n_items_s, 0) * 8; i += blockDim.x) {
-      const int it = i >> 3, k = it_k[it] + (i & 7);
-      fbc[i] = k < mel_hi[it_m[it]] ? a.fb[(size_t)it_m[it] * bins + k] : 0.f;
+      const int it = i >> 3, k = it_k[it] + (i & 7), m = it_m[it];
+      fbc[i] = (m >= 0 && k >= mel_lo[m] && k < mel_hi[m]) ? a.fb[(size_t)m * bins + k] : 0.f;
     }
-    for (int i = threadIdx.x; i < ff::GROUPS * MEL_MAX; i += blockDim.x) melacc[i] = 0.f;
   }
   __syncthreads();
   const int n_items = MODE == 1 ? *n_items_s : 0;
@@ -457,33 +469,36 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     }
     gsync();
     if (MODE == 1) {
-      float* macc = melacc + g * MEL_MAX;
-      if (n_items >= 0) {
-        for (int it = j; it < n_items; it += NT) {
-          const float* pk = P + it_k[it];                 // (bins past 512 read exchange-buffer leftovers x 0)
-          const float4 w0 = *reinterpret_cast<const float4*>(fbc + it * 8);
-          const float4 w1 = *reinterpret_cast<const float4*>(fbc + it * 8 + 4);
-          float acc = pk[0] * w0.x;
-          acc = fmaf(pk[1], w0.y, acc); acc = fmaf(pk[2], w0.z, acc); acc = fmaf(pk[3], w0.w, acc);
-          acc = fmaf(pk[4], w1.x, acc); acc = fmaf(pk[5], w1.y, acc); acc = fmaf(pk[6], w1.z, acc);
-          acc = fmaf(pk[7], w1.w, acc);
-          atomicAdd(macc + it_m[it], acc);
-        }
-        gsync();
-      }
-      for (int m = j; m < a.n_mels; m += NT) {
-        float acc;
-        if (n_items >= 0) {
-          acc = macc[m];
-          macc[m] = 0.f;
-        } else {
-          const float* row = a.fb + (size_t)m * bins;
-          acc = 0.f;
-          for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[k], __ldg(row + k), acc);
-        }
+      auto finish = [&](float acc, int m) {
         if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
         else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
         if (live) a.out[((size_t)b * a.frames + f) * a.n_mels + m] = acc;
+      };
+      if (n_items >= 0) {
+        // 32 items per warp step; lane l reads element (i + (l >> 2)) & 7 of its 8-bin piece at step i: consecutive
+        // items of a row sit 8 floats apart, the skew spreads the 32 lanes over all banks (P and weights alike)
+        const int lane = j & 31, skew = lane >> 2;
+        for (int it = (j & 32) + lane; it < n_items; it += NT) {
+          const float* pk = P + it_k[it];                 // (bins past 512 read exchange-buffer leftovers x 0)
+          const float* wk = fbc + it * 8;
+          const int fl = it_f[it];
+          float acc = 0.f;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { const int e = (i + skew) & 7; acc = fmaf(pk[e], wk[e], acc); }
+#pragma unroll
+          for (int d = 0; d < 4; ++d) {
+            const float o = __shfl_down_sync(0xffffffffu, acc, 1 << d);
+            if (fl & (1 << d)) acc += o;
+          }
+          if (fl & 16) finish(acc, it_m[it]);
+        }
+      } else {
+        for (int m = j; m < a.n_mels; m += NT) {
+          const float* row = a.fb + (size_t)m * bins;
+          float acc = 0.f;
+          for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[k], __ldg(row + k), acc);
+          finish(acc, m);
+        }
       }
       gsync();
     }
