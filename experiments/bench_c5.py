@@ -92,8 +92,8 @@ def main():
             "frames_per_chunk": T, "batch": B, "batches_per_rank": len(sizes), "dtype": args.dtype,
             "seconds": float(tt.item()), "audio_seconds_per_second": audio_s / float(tt.item()),
             "rtf": float(tt.item()) / audio_s,
-            "h2d_bytes": int(sum(n for n in sizes) * (512 * T + 4 * T + 128) * 4),
-            "d2h_bytes": int(sum(n for n in sizes) * 600 * T * 4),
+            "h2d_bytes_rank0": int(sum(n for n in sizes) * (512 * T + 4 * T + 128) * 4),
+            "d2h_bytes_rank0": int(sum(n for n in sizes) * 600 * T * 4),
             "timing": "host wall clock around the whole stream (copies included), max over ranks",
             "data": f"synthetic, {args.distinct} distinct pinned host batches per rank cycled", "finite": peak == peak}))
     if world > 1:
