@@ -153,7 +153,7 @@ int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, v
  * spec out: (B, frames, n_fft/2+1, 2) float (re, im).  n_fft must factor into {2,3,5} and be <= 4096. */
 int kk_stft_f32(const float* x, const float* window, float* spec, int B, int n, int n_fft, int hop,
                 int pad_mode, int frames, void* stream);
-/* power: 1 -> |X|, 2 -> |X|^2.  mel: fb (n_mels, n_fft/2+1).  log_mode: 0 none, 1 ln(max(.,floor)),
+/* power: 1 -> |X|, 2 -> |X|^2.  mel: fb (n_mels, n_fft/2+1).  log_mode: 0 none, 3 ln(. + floor) [parakeet], 1 ln(max(.,floor)),
  * 2 log10(max(.,floor)).  out (B, frames, n_mels).  Spectrogram is never materialised. */
 int kk_logmel_f32(const float* x, const float* window, const float* fb, float* out, int B, int n, int n_fft,
                   int hop, int pad_mode, int frames, int n_mels, int power, int log_mode, float floor_,
@@ -169,6 +169,10 @@ int kk_polar_to_spec(const float* x, int x_pitch, float* spec, long long rows, i
 /* Whisper log-mel dynamic-range step (mlx_audio/stt/models/whisper/audio.py:80-81), in place, per signal of n_per
  * values: m = max(x); x = (max(x, m - range) + add) * scale   [reference: range 8, add 4, scale 1/4]. */
 int kk_clamp_below_max_affine(float* x, int B, long long n_per, float range, float add, float scale, void* stream);
+/* Parakeet feature normalisation (mlx_audio/stt/models/parakeet/audio.py:56-63), in place on x (B, frames, n_feat):
+ * per_feature = 1: (x - mean_f) / (std_f + eps) with mean / population std over the frames of each feature;
+ * per_feature = 0: one mean / std per signal. */
+int kk_normalize_features(float* x, int B, int frames, int n_feat, int per_feature, float eps, void* stream);
 
 #ifdef __cplusplus
 }

@@ -401,6 +401,65 @@ extern "C" int kk_clamp_below_max_affine(float* x, int B, long long n_per, float
   return KK_OK;
 }
 
+namespace kk {
+// Parakeet normalisation: one block per signal, thread (ty, f) walks frames ty, ty + 8, ... of feature f (coalesced
+// across features), fp64 partial sums combined through shared memory; then the same walk applies the normalisation.
+__global__ void __launch_bounds__(1024) normalize_features_kernel(float* __restrict__ x, int frames, int n_feat,
+                                                                  int per_feature, float eps) {
+  extern __shared__ double sm[];           // [2][rows][n_feat]
+  const int rows = blockDim.y, ty = threadIdx.y;
+  float* xb = x + (size_t)blockIdx.x * frames * n_feat;
+  double* ssum = sm;
+  double* ssq = sm + (size_t)rows * n_feat + 2;
+  const int gslot = rows * n_feat;          // per-signal totals (per_feature == 0)
+  for (int f = threadIdx.x; f < n_feat; f += blockDim.x) {
+    double s = 0.0, q = 0.0;
+    for (int t = ty; t < frames; t += rows) { const double v = xb[(size_t)t * n_feat + f]; s += v; q += v * v; }
+    ssum[ty * n_feat + f] = s; ssq[ty * n_feat + f] = q;
+  }
+  __syncthreads();
+  if (ty == 0) {
+    for (int f = threadIdx.x; f < n_feat; f += blockDim.x) {
+      double s = 0.0, q = 0.0;
+      for (int r = 0; r < rows; ++r) { s += ssum[r * n_feat + f]; q += ssq[r * n_feat + f]; }
+      ssum[f] = s; ssq[f] = q;
+    }
+  }
+  __syncthreads();
+  if (!per_feature) {
+    if (ty == 0 && threadIdx.x == 0) {
+      double s = 0.0, q = 0.0;
+      for (int f = 0; f < n_feat; ++f) { s += ssum[f]; q += ssq[f]; }
+      ssum[gslot] = s; ssq[gslot] = q;
+    }
+    __syncthreads();
+  }
+  const double cnt = per_feature ? (double)frames : (double)frames * n_feat;
+  for (int f = threadIdx.x; f < n_feat; f += blockDim.x) {
+    const double s = per_feature ? ssum[f] : ssum[gslot], q = per_feature ? ssq[f] : ssq[gslot];
+    const double mean = s / cnt;
+    const double var = fmax(q / cnt - mean * mean, 0.0);
+    const float m = (float)mean, inv = 1.0f / ((float)sqrt(var) + eps);
+    for (int t = ty; t < frames; t += rows) {
+      const size_t i = (size_t)t * n_feat + f;
+      xb[i] = (xb[i] - m) * inv;
+    }
+  }
+}
+}  // namespace kk
+
+extern "C" int kk_normalize_features(float* x, int B, int frames, int n_feat, int per_feature, float eps, void* stream) {
+  KK_CHECK_ARG(x && B > 0 && frames > 0 && n_feat > 0 && n_feat <= 1024, "kk_normalize_features: bad arguments");
+  int tx = n_feat >= 128 ? 128 : (n_feat >= 64 ? 64 : 32);
+  int rows = 1024 / tx;
+  while (rows > 1 && (size_t)2 * (rows * n_feat + 2) * 8 > 96 * 1024) rows >>= 1;
+  const size_t smem = (size_t)2 * ((size_t)rows * n_feat + 2) * 8;
+  KK_CUDA(cudaFuncSetAttribute(kk::normalize_features_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  kk::normalize_features_kernel<<<B, dim3(tx, rows), smem, (cudaStream_t)stream>>>(x, frames, n_feat, per_feature, eps);
+  KK_LAUNCH_CHECK("normalize_features_kernel");
+  return KK_OK;
+}
+
 extern "C" int kk_convert_act(const float* x, int x_pitch, void* out, int out_is_bf16, int out_pitch, long long rows,
                               int C, float slope, void* stream) {
   KK_CHECK_ARG(x && out && rows > 0 && C > 0, "kk_convert_act: bad arguments");

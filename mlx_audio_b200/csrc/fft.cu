@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPl
         for (int k = mel_lo[m]; k < mel_hi[m]; ++k) acc = fmaf(P[g * bins + k], __ldg(row + k), acc);
         if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
         else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
+        else if (a.log_mode == 3) acc = logf(acc + a.floor_);
         a.out[((size_t)b * a.frames + f0 + g) * a.n_mels + m] = acc;
       }
       __syncthreads();
@@ -472,6 +473,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
       auto finish = [&](float acc, int m) {
         if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
         else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
+        else if (a.log_mode == 3) acc = logf(acc + a.floor_);
         if (live) a.out[((size_t)b * a.frames + f) * a.n_mels + m] = acc;
       };
       if (n_items >= 0) {
@@ -749,7 +751,7 @@ extern "C" int kk_logmel_f32(const float* x, const float* window, const float* f
   kk::FftPlan p;
   int rc = check_stft_args("kk_logmel_f32", x, window, out, B, n, n_fft, hop, pad_mode, frames, &p);
   if (rc) return rc;
-  KK_CHECK_ARG(fb && n_mels > 0 && n_mels <= 1024 && (power == 1 || power == 2) && log_mode >= 0 && log_mode <= 2,
+  KK_CHECK_ARG(fb && n_mels > 0 && n_mels <= 1024 && (power == 1 || power == 2) && log_mode >= 0 && log_mode <= 3,
                "kk_logmel_f32: bad mel arguments");
   kk::StftArgs a = {};
   a.x = x; a.window = window; a.out = out; a.n = n; a.hop = hop; a.pad_mode = pad_mode; a.frames = frames;

@@ -219,7 +219,7 @@ def log_mel_spectrogram(x, sample_rate=24000, n_fft=1024, hop_length=256, n_mels
     fb = mel_filters(sample_rate, n_fft, n_mels, 0, None, norm, mel_scale).contiguous()
     B, n = x.shape
     out = torch.empty(B, frames, n_mels, dtype=torch.float32, device=x.device)
-    log_mode = {None: 0, "none": 0, "ln": 1, "log": 1, "log10": 2}[log]
+    log_mode = {None: 0, "none": 0, "ln": 1, "log": 1, "log10": 2, "ln_add": 3}[log]   # ln_add: log(x + floor)
     L.check(L.load().kk_logmel_f32(L.ptr(x), L.ptr(w), L.ptr(fb), L.ptr(out), B, n, n_fft, hop, mode, frames, n_mels,
                                    int(power), log_mode, float(floor), L.stream()), "kk_logmel_f32")
     return out[0] if squeeze else out

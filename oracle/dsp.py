@@ -194,3 +194,20 @@ def istft_head_vocos(x, weight, bias, n_fft: int, hop_length: int, dtype=np.floa
     S = mag * (np.cos(p) + 1j * np.sin(p))
     return istft(S[0].astype(np.complex64), window=hanning(n_fft, dtype), hop_length=hop_length, win_length=n_fft,
                  dtype=dtype)
+
+
+def log_mel_parakeet(x, sample_rate=16000, n_fft=512, win_length=400, hop_length=160, features=80, window="hann",
+                     normalize="per_feature", dtype=np.float32) -> np.ndarray:
+    """stt/models/parakeet/audio.py:38-70: power spectrum, mel_filters(norm=normalize, mel_scale=None), log(x + 1e-5),
+    (x - mean) / (std + 1e-5) per feature over time (or over everything) -> (1, frames, features)."""
+    fn = STR_TO_WINDOW_FN.get(window)
+    w = fn(win_length, dtype) if fn else hanning(win_length, dtype)
+    S = stft(x, n_fft, hop_length, win_length, w, dtype=dtype)
+    p = (np.abs(S).astype(dtype)) ** 2
+    fb = mel_filters(sample_rate, n_fft, features, norm=normalize, mel_scale=None, dtype=dtype)
+    m = np.log((fb @ p.T).astype(dtype) + dtype(1e-5))                      # (features, frames)
+    if normalize == "per_feature":
+        mean, std = m.mean(axis=1, keepdims=True), m.std(axis=1, keepdims=True)
+    else:
+        mean, std = m.mean(), m.std()
+    return ((m - mean) / (std + dtype(1e-5))).T[None].astype(dtype)

@@ -170,6 +170,11 @@ abs = _unary(np.abs)  # noqa: A001
 round = _unary(np.round)  # noqa: A001
 
 
+def square(x):
+    x = _f(x)
+    return _wrap(x * x)
+
+
 def addmm(c, a, b, alpha=1.0, beta=1.0):
     """mx.addmm: beta * c + alpha * (a @ b) (used by the reference LSTM, modules.py:156-158)."""
     a, b, c = _f(a), _f(b), _f(c)
@@ -208,6 +213,10 @@ def mean(x, axis=None, keepdims=False):
 
 def var(x, axis=None, keepdims=False, ddof=0):
     return _wrap(np.var(_raw(x), axis=_ax(axis), keepdims=keepdims, ddof=ddof, dtype=_raw(x).dtype))
+
+
+def std(x, axis=None, keepdims=False, ddof=0):
+    return _wrap(np.std(_raw(x), axis=_ax(axis), keepdims=keepdims, ddof=ddof).astype(np.float32))
 
 
 def prod(x, axis=None, keepdims=False):

@@ -152,4 +152,7 @@ def load_reference_frontends():
     ns.indextts_mel = _load("mlx_audio.tts.models.indextts.mel", os.path.join(root, "tts", "models", "indextts", "mel.py"))
     ns.whisper_audio = _load("mlx_audio.stt.models.whisper.audio",
                              os.path.join(root, "stt", "models", "whisper", "audio.py"))
+    _pkg("mlx_audio.stt.models.parakeet", os.path.join(root, "stt", "models", "parakeet"))
+    ns.parakeet_audio = _load("mlx_audio.stt.models.parakeet.audio",
+                              os.path.join(root, "stt", "models", "parakeet", "audio.py"))
     return ns

@@ -142,6 +142,10 @@ def main():
         whisper_mel=np.asarray(fe.whisper_audio.log_mel_spectrogram(sig24)).astype(np.float32),
         whisper_mel_128=np.asarray(fe.whisper_audio.log_mel_spectrogram(sig24, n_mels=128, padding=480)).astype(np.float32),
         istft_head=np.asarray(head(mx.array(hx))).astype(np.float32),
+        parakeet_mel=np.asarray(fe.parakeet_audio.log_mel_spectrogram(mx.array(sig24), fe.parakeet_audio.PreprocessArgs(
+            16000, "per_feature", 0.025, 0.01, "hann", 80, 512, 0.0))).astype(np.float32),
+        parakeet_mel_global=np.asarray(fe.parakeet_audio.log_mel_spectrogram(mx.array(sig24), fe.parakeet_audio.PreprocessArgs(
+            16000, "all", 0.025, 0.01, "hamming", 128, 512, 0.0, pad_to=30000))).astype(np.float32),
     )
     print("wrote", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
 

@@ -54,6 +54,17 @@ def test_whisper_log_mel(g, sig):
         whisper.log_mel_spectrogram("file.wav")
 
 
+def test_parakeet_log_mel(g, sig):
+    from mlx_audio_b200.stt.models.parakeet.audio import PreprocessArgs, log_mel_spectrogram
+    a = PreprocessArgs(16000, "per_feature", 0.025, 0.01, "hann", 80, 512, 0.0)
+    _cmp(log_mel_spectrogram(sig, a), g["parakeet_mel"], mean_tol=2e-4, max_tol=5e-3)
+    a2 = PreprocessArgs(16000, "all", 0.025, 0.01, "hamming", 128, 512, 0.0, pad_to=30000)
+    _cmp(log_mel_spectrogram(sig, a2), g["parakeet_mel_global"], mean_tol=2e-4, max_tol=5e-3)
+    b = log_mel_spectrogram(torch.from_numpy(np.stack([sig, 0.5 * sig])), a)
+    assert tuple(b.shape) == (2, 151, 80)
+    _cmp(b[0:1], g["parakeet_mel"], mean_tol=2e-4, max_tol=5e-3)
+
+
 def test_vocos_istft_head(g):
     rng = np.random.Generator(np.random.PCG64(int(g["head_seed"])))
     dim, Lh = int(g["head_dim"]), int(g["head_frames"])

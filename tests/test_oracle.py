@@ -285,3 +285,14 @@ def test_frontends_golden(golden_dir):
     y = dsp.istft_head_vocos(hx, hw, hb, 1024, 256)
     assert y.shape == g["istft_head"].shape == ((int(g["head_frames"]) - 1) * 256,)
     assert np.abs(y - g["istft_head"]).max() < 1e-5 * max(1.0, float(np.abs(g["istft_head"]).max()))
+
+
+def test_parakeet_frontend_golden(golden_dir):
+    g = _g(golden_dir, "frontends.npz")
+    sig = synth.synth_audio(1, int(g["n"]), seed=int(g["audio_seed"]))[0]
+    m = dsp.log_mel_parakeet(sig)
+    assert m.shape == g["parakeet_mel"].shape == (1, 151, 80)
+    assert np.abs(m - g["parakeet_mel"]).max() < 1e-3          # normalised log values, O(1)
+    sp = np.concatenate([sig, np.zeros(6000, np.float32)])
+    m2 = dsp.log_mel_parakeet(sp, features=128, window="hamming", normalize="all")
+    assert m2.shape == g["parakeet_mel_global"].shape and np.abs(m2 - g["parakeet_mel_global"]).max() < 1e-3
