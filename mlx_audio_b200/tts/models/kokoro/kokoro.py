@@ -17,6 +17,7 @@ import numpy as np
 
 from ....synth import KOKORO_DECODER, synth_f0
 from .istftnet import Decoder
+from .modules import ProsodyPredictor
 
 
 @dataclass
@@ -86,6 +87,10 @@ class Model:
         self.frontend = frontend
         self.decoder = Decoder(dim_in=config.hidden_dim, style_dim=config.style_dim, dim_out=config.n_mels,
                                **config.istftnet, dtype=dtype, device=device)    # kokoro.py:107-112
+        # F0 / energy heads (kokoro.py:160, modules.py:355-377): used when the front end hands over ``en`` instead of
+        # finished F0 / N curves and the ``predictor.*`` weights were loaded
+        self.predictor = ProsodyPredictor(style_dim=config.style_dim, d_hid=config.hidden_dim, nlayers=config.n_layer,
+                                          max_dur=config.max_dur, dropout=config.dropout, dtype=dtype, device=device)
         self.sample_rate = config.sample_rate
 
     # ---- weights
@@ -93,14 +98,22 @@ class Model:
         """kokoro.py:172-252 restricted to the decoder: ``decoder.*`` keys go through Decoder.sanitize
         (istftnet.py:965-979), every other sub-module's weights belong to the out-of-scope front end."""
         out = {}
+        wanted = set("predictor." + n for n in self.predictor.parameter_shapes())
         for k, v in weights.items():
             if k.startswith("decoder."):
                 out[k] = self.decoder.sanitize(k, np.asarray(v))
+            elif k.startswith("predictor."):                 # kokoro.py:213-247 (F0 / N heads, projections, shared LSTM)
+                for nk, nv in self.predictor.sanitize(k, np.asarray(v)).items():
+                    if nk in wanted:
+                        out[nk] = nv
         return out
 
     def load_weights(self, weights, strict: bool = True):
         items = list(weights.items() if isinstance(weights, dict) else weights)
         self.decoder.load_weights([(k, v) for k, v in items if k.startswith("decoder.")], strict=strict)
+        pred = [(k, v) for k, v in items if k.startswith("predictor.")]
+        if pred:
+            self.predictor.load_weights(pred, strict=strict)
         return self
 
     # ---- forward
@@ -113,7 +126,18 @@ class Model:
                 "reference's text front end (ALBERT / TextEncoder / ProsodyPredictor, kokoro.py:142-162) is outside "
                 "the rebuilt hot path; pass your own or mlx_audio_b200...kokoro.SyntheticFrontend for testing")
         ref_s = np.asarray(ref_s, dtype=np.float32) if not hasattr(ref_s, "shape") else ref_s
-        asr, F0_pred, N_pred, pred_dur = self.frontend(phonemes, ref_s, speed)
+        feats = self.frontend(phonemes, ref_s, speed)
+        if isinstance(feats, dict):
+            # front end stops at kokoro.py:157-159: {"asr", "en" (1, d_hid + style, T), "pred_dur"}; the F0 / N heads
+            # run here with the prosody half of the style vector, s = ref_s[:, 128:] (kokoro.py:143, 160)
+            asr, pred_dur = feats["asr"], feats.get("pred_dur")
+            if "en" in feats:
+                F0_pred, N_pred = self.predictor.F0Ntrain(feats["en"], ref_s[:, 128:])
+                F0_pred, N_pred = F0_pred.clone(), N_pred.clone()
+            else:
+                F0_pred, N_pred = feats["F0_pred"], feats["N_pred"]
+        else:
+            asr, F0_pred, N_pred, pred_dur = feats
         dec = decoder if decoder is not None else self.decoder
         audio = dec(asr, F0_pred, N_pred, ref_s[:, :128])[0]                            # kokoro.py:165
         if hasattr(audio, "clone"):

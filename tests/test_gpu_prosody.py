@@ -93,3 +93,29 @@ def test_f0ntrain_errors(weights):
         pp.F0Ntrain(np.zeros((1, 640, 8), np.float32), np.zeros((2, 128), np.float32))
     with pytest.raises(ValueError):
         build_prosody_predictor({"predictor.bogus": np.zeros(1, np.float32)})
+
+
+def test_model_runs_f0ntrain_when_frontend_returns_en(weights):
+    """Model.__call__ (kokoro.py:157-165): a front end that stops at ``en`` -> F0Ntrain(en, ref_s[:, 128:]) -> decoder."""
+    from mlx_audio_b200.tts.models.kokoro import Model, ModelConfig, build_decoder
+    T = 10
+    pin = synth.synth_prosody_inputs(1, T, seed=1500)
+    din = synth.synth_decoder_inputs(1, T, seed=1501)
+    dw = synth.synth_decoder_weights(seed=2000)
+
+    def frontend(phonemes, ref_s, speed):
+        return {"asr": din["asr"], "en": pin["x"], "pred_dur": np.ones(len(phonemes) + 2, np.int32)}
+
+    m = Model(ModelConfig(), frontend=frontend, dtype="fp32")
+    ck = dict(dw)
+    ck.update(weights)
+    ck["bert.encoder.dummy"] = np.zeros(2, np.float32)
+    m.load_weights(ck)          # MLX-layout weights: no sanitize; keys outside decoder.* / predictor.* are ignored
+    ref_s = np.concatenate([din["s"], pin["s"]], axis=1)                    # [decoder style | prosody style]
+    m.decoder.seed = 3
+    out = m("abcdefgh", ref_s, return_output=True)
+    torch.cuda.synchronize()
+    F0, N = build_prosody_predictor(weights, dtype="fp32").F0Ntrain(pin["x"], pin["s"])
+    y = build_decoder(dw, dtype="fp32")(din["asr"], F0.clone(), N.clone(), din["s"], seed=3)
+    torch.testing.assert_close(out.audio, y[0], rtol=0, atol=1e-6)
+    assert out.pred_dur.shape == (10,)
