@@ -56,16 +56,18 @@ __global__ void instnorm_stats_kernel(const float* __restrict__ x, double* __res
   int c = blockIdx.x * 32 + threadIdx.x;
   int l0 = blockIdx.y * rows_per_block;
   int l1 = min(L, l0 + rows_per_block);
-  float s = 0.f, ss = 0.f;
+  // fp64 partial sums: the row split (rows_per_block) depends on the batch size, and fp32 partials would make an
+  // utterance's statistics - hence, after bf16 rounding downstream, its audio - depend on what it is batched with
+  double s = 0.0, ss = 0.0;
   if (c < C) {
     const float* xb = x + (size_t)b * L * pitch + c;
     for (int l = l0 + threadIdx.y; l < l1; l += 8) {
-      float v = xb[(size_t)l * pitch];
+      const double v = xb[(size_t)l * pitch];
       s += v;
-      ss = fmaf(v, v, ss);
+      ss = fma(v, v, ss);
     }
   }
-  __shared__ float sh[2][8][33];
+  __shared__ double sh[2][8][33];
   sh[0][threadIdx.y][threadIdx.x] = s;
   sh[1][threadIdx.y][threadIdx.x] = ss;
   __syncthreads();

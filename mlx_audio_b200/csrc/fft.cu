@@ -430,7 +430,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         const float2 w = RT ? rw[t] : win[j + NT * t];
-        v[t] = make_float2(nx[t].x * w.x, nx[t].y * w.y);
+        v[t] = make_float2(__fmul_rn(nx[t].x, w.x), __fmul_rn(nx[t].y, w.y));   // no contraction into the first butterfly
       }
       load_frame(f + ff::GROUPS, nx);
       ff::pass1_store(v, A, sz);

@@ -47,7 +47,11 @@ struct SwzIdx {
   __device__ __forceinline__ int st2(int q) const { return ((q & 1) ? o : e) + 16 * (q >> 1) + (kk ^ (q >> 1)); }
   __device__ __forceinline__ int mirror(int q) const { return ((64 * (7 - q) + zoff) & 511) + (((7 - q) & 1) ? d1 : d0); }
 };
-__device__ __forceinline__ float2 cm(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+// complex product with the contraction spelled out, so that every kernel variant (shared-memory or register tables,
+// any batch size) produces the same bits for the same frame
+__device__ __forceinline__ float2 cm(float2 a, float2 b) {
+  return make_float2(fmaf(a.x, b.x, -__fmul_rn(a.y, b.y)), fmaf(a.x, b.y, __fmul_rn(a.y, b.x)));
+}
 __device__ __forceinline__ float2 ca(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 cs(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
 __device__ __forceinline__ float2 mi(float2 a) { return make_float2(a.y, -a.x); }   // -i * a
@@ -62,12 +66,15 @@ __device__ __forceinline__ void fft8(float2 (&v)[8]) {
   const float2 b0 = ca(a0, a2), b2 = cs(a0, a2), b4 = ca(a4, a6), b6 = cs(a4, a6);
   const float2 b1 = ca(a1, a3), b3 = mi(cs(a1, a3));
   const float2 s5 = ca(a5, a7), d7 = cs(a5, a7);
-  const float2 b5 = make_float2(h * (s5.x + s5.y), h * (s5.y - s5.x));     // * (1 - i)/sqrt 2
-  const float2 b7 = make_float2(h * (d7.y - d7.x), -h * (d7.x + d7.y));    // * (-1 - i)/sqrt 2
+  // b5 = s5 (1 - i)/sqrt 2, b7 = d7 (-1 - i)/sqrt 2 folded into the last butterflies as explicit FMAs: left to the
+  // compiler, the contraction of h * (..) +- b differs between kernel variants and with it the low bits of the result
+  const float p5 = s5.x + s5.y, q5 = s5.y - s5.x, r7 = d7.y - d7.x, u7 = d7.x + d7.y;
   v[0] = ca(b0, b1); v[4] = cs(b0, b1);
   v[2] = ca(b2, b3); v[6] = cs(b2, b3);
-  v[1] = ca(b4, b5); v[5] = cs(b4, b5);
-  v[3] = ca(b6, b7); v[7] = cs(b6, b7);
+  v[1] = make_float2(fmaf(h, p5, b4.x), fmaf(h, q5, b4.y));
+  v[5] = make_float2(fmaf(-h, p5, b4.x), fmaf(-h, q5, b4.y));
+  v[3] = make_float2(fmaf(h, r7, b6.x), fmaf(-h, u7, b6.y));
+  v[7] = make_float2(fmaf(-h, r7, b6.x), fmaf(h, u7, b6.y));
 }
 
 // Twiddle tables laid out per pass so that a warp reads consecutive addresses (a single exp(-2 pi i j/512) table
