@@ -552,15 +552,16 @@ class DecoderEngine:
         # ---- front: x = cat[asr, F0, N] (:951); xcat = cat[x(1024), asr_res(64), F0, N] (:957)
         c_cat0, c_cat = din + 2, 1024 + 64 + 2
         p_cat = (c_cat + 3) // 4 * 4      # 16-byte row pitch: the conv epilogues then store xcat by TMA
-        xcat0 = self._buf(plan, "xcat0", (B, T, c_cat0))
+        p_cat0 = (c_cat0 + 3) // 4 * 4    # same for the first concatenation (vectorised elementwise kernels)
+        xcat0 = self._buf(plan, "xcat0", (B, T, p_cat0), zero=True)
         xcat = self._buf(plan, "xcat", (B, T, p_cat))
         plan.add(lib.kk_front_assemble, self._addr(asr), self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
-                 self._addr(self.n_w3b), self._addr(xcat0), c_cat0, 0, din, din + 1, B, din, T, launches=2)
+                 self._addr(self.n_w3b), self._addr(xcat0), p_cat0, 0, din, din + 1, B, din, T, launches=2)
         plan.add(lib.kk_front_assemble, None, self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
                  self._addr(self.n_w3b), self._addr(xcat), p_cat, 0, 1024 + 64, 1024 + 65, B, din, T)
-        self._conv(plan, self.convs["asr_res.0"], self._addr(xcat0), B, T, c_cat0, T,
+        self._conv(plan, self.convs["asr_res.0"], self._addr(xcat0), B, T, p_cat0, T,
                    out_addr=self._addr(xcat, 1024), out_pitch=p_cat, force_f32=True)  # :953
-        self._adain_resblk1d(plan, "encode", B, T, c_cat0, 1024, h_all, self._addr(xcat0), c_cat0, self._addr(xcat),
+        self._adain_resblk1d(plan, "encode", B, T, c_cat0, 1024, h_all, self._addr(xcat0), p_cat0, self._addr(xcat),
                              p_cat, name="encode")
         self._tap(plan, "encode", xcat, lambda t: t[:, :, :1024].transpose(1, 2))
         for i in range(3):
@@ -584,6 +585,10 @@ class DecoderEngine:
         har_rows = r1 * (L20 + 1)       # rows of the bf16 copy: whole 6-frame rows for the stride-6 noise conv
         if self.tc:
             har16 = self._buf(plan, "har16", (B, har_rows, 24), torch.bfloat16, zero=True)
+            # the convolutions read the bf16 rows only; the fp32 copy (row-strided scalar stores, 236 MB at B=64 x
+            # T=320) is written when a caller asks for the intermediate taps (Decoder.__call__ patches argument 1)
+            plan.stft_op_index = len(plan.ops)
+            plan.har_addr = self._addr(har)
             plan.add(lib.kk_stft_n20_bf16, self._addr(har_source), self._addr(har), 24, self._addr(har16), 24, har_rows,
                      B, S)
         else:

@@ -158,6 +158,10 @@ class Decoder:
                 raise ValueError(f"noise must be (B, {S}, 9), got {tuple(noise_t.shape)}")
         self._set_source(plan, noise_t, self.seed if seed is None else seed)
         plan.capture = capture_taps
+        i = getattr(plan, "stft_op_index", None)
+        if i is not None:               # fp32 copy of the harmonic-source STFT: only for the taps (see engine.build_plan)
+            fn, args = plan.ops[i]
+            plan.ops[i] = (fn, (args[0], plan.har_addr if capture_taps else None) + tuple(args[2:]))
         use_graph = self.use_cuda_graph and noise_t is None and not capture_taps
         if use_graph:
             self._run_graph(plan, (B, T))
