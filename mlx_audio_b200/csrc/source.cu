@@ -124,10 +124,14 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
   const float* pb = phase + (size_t)b * NH * T2;
 #pragma unroll
   for (int k = 0; k < NH; ++k) {
-    const float* p = pb + (size_t)k * T2;
-    float ph = __fadd_rn(__fmul_rn(p[lo], one_m), __fmul_rn(p[hi], fr));  // interpolate.py:106
-    float sine = __fmul_rn(sin_large(ph), 0.1f);                           // :579, :613
-    float hk = voiced ? __fadd_rn(sine, __fmul_rn(amp, nz[k])) : __fmul_rn(amp, nz[k]);  // :622
+    float hk = __fmul_rn(amp, nz[k]);
+    if (voiced) {   // sine * uv: unvoiced samples never see the sine (uv = 0, :622) - and f0 is constant over 300
+                    // consecutive samples, so the branch is warp-uniform but for the segment edges
+      const float* p = pb + (size_t)k * T2;
+      float ph = __fadd_rn(__fmul_rn(p[lo], one_m), __fmul_rn(p[hi], fr));  // interpolate.py:106
+      float sine = __fmul_rn(sin_large(ph), 0.1f);                           // :579, :613
+      hk = __fadd_rn(sine, hk);
+    }
     acc = fmaf(hk, lin_w[k], acc);
   }
   out[idx] = tanhf(acc + lin_b[0]);  // l_linear + tanh (:666, :677)
