@@ -324,15 +324,17 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
   const ff::SwzIdx sz(j);
 
   // RT: window, twiddles and unpack factors of this thread live in registers (two blocks per SM instead of four)
-  float2 rw[8], rt2[8], rt3[8], ru[8];
+  float2 rw[8], rt2[8], rt3[8], ru[4];
   if (RT) {
     ff::fill_reg_twiddles(j, rt2, rt3);
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
       rw[t] = make_float2(a.window[2 * (j + NT * t)], a.window[2 * (j + NT * t) + 1]);
-      float sn, cs_;
-      sincospif(-(float)(j + NT * t) / (float)NC, &sn, &cs_);
-      ru[t] = make_float2(cs_, sn);
+      if (t < 4) {
+        float sn, cs_;
+        sincospif(-(float)(j + NT * t) / (float)NC, &sn, &cs_);
+        ru[t] = make_float2(cs_, sn);
+      }
     }
   } else {
     ff::fill_tables(tw, tw2);
@@ -440,19 +442,15 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     gsync();
     float2 z[8];                                  // z[q] = Z[j + 64 q]: kept in registers for the unpack
     if (RT) ff::pass3_r(Bf, rt3, sz, z); else ff::pass3(Bf, tw, j, sz, z);
+    // ---- unpack in conjugate pairs: with E = (Z[k] + conj Z[nc-k]) / 2, O = (Z[k] - conj Z[nc-k]) / (2i),
+    // u = e^{-2 pi i k / n}:   X[k] = E + u O   and   X[nc-k] = conj(E - u O).
+    // Thread j owns the pairs of its lower four points k = j + 64 q (q < 4); their partners are the upper four points
+    // of thread 64 - j, the only values that cross shared memory (thread 0 pairs with itself, and owns k = nc / 2).
 #pragma unroll
-    for (int q = 0; q < 8; ++q) A[sz.cons(q)] = z[q];
+    for (int q = 4; q < 8; ++q) A[sz.cons(q)] = z[q];
     gsync();
-    // ---- unpack: X[k] = (Z[k]+conj(Z[nc-k]))/2 + e^{-2 pi i k/n} (Z[k]-conj(Z[nc-k]))/(2i); Z[k] is this thread's
-    // own z[k / 64], only the mirrored point comes from shared memory
     float* P = reinterpret_cast<float*>(Bf);   // MODE 1: |X|^p of this frame (513 floats <= BUF float2)
-    auto unpack_one = [&](int k, float2 zk, float2 zc, float2 u) {
-      zc.y = -zc.y;
-      const float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
-      const float2 d = ff::cs(zk, zc);
-      const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);  // d / (2i)
-      float2 X = ff::ca(e, ff::cm(u, o));
-      if (k == 0 || k == NC) X.y = 0.f;
+    auto emit = [&](int k, float2 X) {
       if (MODE == 0) {
         if (live) reinterpret_cast<float2*>(a.out)[((size_t)b * a.frames + f) * bins + k] = X;
       } else {
@@ -460,13 +458,26 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
         P[k] = a.power == 2 ? m2 : sqrtf(m2);
       }
     };
+    auto unpack_pair = [&](int k, float2 zk, float2 zc, float2 u, bool self) {
+      zc.y = -zc.y;
+      const float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
+      const float2 d = ff::cs(zk, zc);
+      const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);  // d / (2i)
+      const float2 t = ff::cm(u, o);
+      float2 X1 = ff::ca(e, t);
+      float2 X2 = make_float2(e.x - t.x, t.y - e.y);           // conj(e - t)
+      if (k == 0) { X1.y = 0.f; X2.y = 0.f; }                  // rfft: DC and Nyquist are real
+      emit(k, X1);
+      if (!self) emit(NC - k, X2);
+    };
     {
-      float2 zc[8];
+      float2 zc[4];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) zc[q] = A[sz.mirror(q)];
+      for (int q = 0; q < 4; ++q) zc[q] = A[sz.mirror(q)];
+      if (j == 0) zc[0] = z[0];                                // k = 0 pairs with nc = 0 (mod nc): its own point
 #pragma unroll
-      for (int q = 0; q < 8; ++q) unpack_one(j + NT * q, z[q], zc[q], RT ? ru[q] : tw2[j + NT * q]);
-      if (j == 0) unpack_one(NC, z[0], z[0], make_float2(-1.f, -0.f));   // e^{-i pi} as sincospif(-1) returns it
+      for (int q = 0; q < 4; ++q) unpack_pair(j + NT * q, z[q], zc[q], RT ? ru[q] : tw2[j + NT * q], false);
+      if (j == 0) unpack_pair(NC / 2, z[4], z[4], make_float2(0.f, -1.f), true);   // e^{-i pi / 2}
     }
     gsync();
     if (MODE == 1) {
