@@ -92,6 +92,8 @@ class Model:
         self.predictor = ProsodyPredictor(style_dim=config.style_dim, d_hid=config.hidden_dim, nlayers=config.n_layer,
                                           max_dur=config.max_dur, dropout=config.dropout, dtype=dtype, device=device)
         self.sample_rate = config.sample_rate
+        self._pipelines: Dict[str, Any] = {}
+        self._g2p: Optional[Callable[[str], Any]] = None     # pluggable G2P handed to the pipelines (see pipeline.py)
 
     # ---- weights
     def sanitize(self, weights: Dict[str, Any]) -> Dict[str, Any]:
@@ -143,3 +145,49 @@ class Model:
         if hasattr(audio, "clone"):
             audio = audio.clone()       # the Decoder returns a view of its persistent output buffer
         return self.Output(audio=audio, pred_dur=pred_dur) if return_output else audio
+
+    # ---- text -> audio segments (the route the reference's CLI and server take: kokoro.py:258-346)
+    def _get_pipeline(self, lang_code: str):
+        """kokoro.py:258-267: one cached KokoroPipeline per language code."""
+        from .pipeline import KokoroPipeline
+        if lang_code not in self._pipelines:
+            self._pipelines[lang_code] = KokoroPipeline(lang_code=lang_code, model=self, repo_id=self.repo_id,
+                                                        g2p=self._g2p)
+        return self._pipelines[lang_code]
+
+    def generate(self, text: str, voice: Optional[str] = None, speed: float = 1.0, lang_code: str = "a",
+                 split_pattern: str = r"\n+", **kwargs):
+        """kokoro.py:269-346: yields one ``GenerationResult`` per segment with duration / real-time-factor statistics.
+        Differences, all forced by the scope: voices must be registered (``pipeline.add_voice`` or a pack path - the hub
+        download of :280-283 is outside the path, so the voice cache is not reset); ``samples`` is the true sample count
+        (the reference reports ``audio.shape[0]``, which is 1 for its (1, S) audio, :297); peak memory is CUDA's."""
+        import time
+
+        import torch
+
+        from ..base import GenerationResult
+        pipeline = self._get_pipeline(lang_code)
+        if voice is None:
+            voice = "af_heart"
+        start = time.time()
+        for segment_idx, (graphemes, phonemes, audio) in enumerate(
+                pipeline(text, voice=voice, speed=speed, split_pattern=split_pattern)):
+            if hasattr(audio, "is_cuda") and audio.is_cuda:
+                torch.cuda.current_stream(audio.device).synchronize()     # mx.eval(audio) of kokoro.py:168
+            now = time.time()
+            segment_time, start = now - start, now
+            samples = int(audio.shape[-1]) if audio is not None else 0
+            assert samples > 0, "No audio generated"
+            token_count = len(phonemes) if phonemes is not None else 0
+            dur = samples / self.sample_rate
+            duration_str = f"{int(dur // 3600):02d}:{int(dur // 60):02d}:{int(dur % 60):02d}.{int((dur % 1) * 1000):03d}"
+            yield GenerationResult(
+                audio=audio[0], samples=samples, sample_rate=self.sample_rate, segment_idx=segment_idx,
+                token_count=token_count, audio_duration=duration_str,
+                real_time_factor=round(segment_time / dur, 2) if dur > 0 else 0,
+                prompt={"tokens": token_count,
+                        "tokens-per-sec": round(token_count / segment_time, 2) if segment_time > 0 else 0},
+                audio_samples={"samples": samples,
+                               "samples-per-sec": round(samples / segment_time, 2) if segment_time > 0 else 0},
+                processing_time_seconds=segment_time,
+                peak_memory_usage=(torch.cuda.max_memory_allocated() / 1e9) if torch.cuda.is_available() else 0.0)

@@ -124,3 +124,31 @@ def test_load_model_roundtrip_and_pipeline_on_gpu(tmp_path):
     torch.testing.assert_close(r2.audio, y[0], rtol=0, atol=1e-6)
     outs = p.batch_tokens(["abc", "xyz", "hello"], voice="v")
     assert [tuple(o.shape) for o in outs] == [(600 * 10,), (600 * 10,), (600 * 14,)]
+
+
+def test_model_generate_and_generate_audio_write_wavs(tmp_path):
+    """Model.generate (kokoro.py:269-346) and generate_audio (tts/generate.py:203-360) on the host logic."""
+    import wave
+
+    from mlx_audio_b200.tts.generate import generate_audio
+    m = _model()
+    m._g2p = lambda text: (text.replace(" ", ""), None)             # stand-in G2P: letters as phonemes
+    pipe = m._get_pipeline("a")
+    assert m._get_pipeline("a") is pipe                              # cached per language (kokoro.py:258-267)
+    pipe.add_voice("af_heart", np.zeros((510, 1, 256), np.float32))
+    res = list(m.generate("hello world\nsecond line"))               # default voice af_heart, split on newlines
+    assert [r.segment_idx for r in res] == [0, 1]
+    T0 = 2 * (10 + 2)
+    assert res[0].samples == 600 * T0 and res[0].sample_rate == 24000 and res[0].token_count == 10
+    assert res[0].audio.shape == (600 * T0,) and res[0].audio_duration == "00:00:00.600"
+    assert res[0].audio_samples["samples"] == 600 * T0 and res[0].processing_time_seconds >= 0
+    files = generate_audio("hello world\nsecond line", m, file_prefix=str(tmp_path / "out"), verbose=False)
+    assert [os.path.basename(f) for f in files] == ["out_000.wav", "out_001.wav"]
+    with wave.open(files[0], "rb") as f:
+        assert f.getframerate() == 24000 and f.getnframes() == 600 * T0 and f.getsampwidth() == 2
+    joined = generate_audio("hello world\nsecond line", m, file_prefix=str(tmp_path / "all"), join_audio=True,
+                            verbose=False)
+    with wave.open(joined[0], "rb") as f:
+        assert f.getnframes() == 600 * (T0 + 2 * (10 + 2))
+    with pytest.raises(ValueError):
+        generate_audio("x", m, audio_format="flac")
