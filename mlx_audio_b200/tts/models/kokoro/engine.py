@@ -345,13 +345,19 @@ class DecoderEngine:
         return d
 
     def _auto_block_n(self, pc: PreparedConv) -> int:
-        """N tile of the tensor-core kernel (0 = library default: 128 for N > 64).  Experiment knobs:
-        KK_TC_BN=<n> forces the tile, KK_TC_LEGACY=1 selects the one-tile-per-CTA kernel."""
+        """N tile of the tensor-core kernel (0 = library default: 128 for N > 64).  Measured per layer at B=64 x T=320
+        (experiments/ab_bn_ops.sh): a 256-wide tile is 20-25 % faster on the front convolutions (N = 1024: 210 -> 162 us),
+        on decode.3's 1090 -> 512 convolutions and on noise_convs[0] (N = 256), slower on the 512 -> 512 conv2 of
+        decode.3 (fewer, heavier epilogue tiles: 4.3 waves of 148 CTAs) and on the polyphase ups.1 (N = 768).
+        Experiment knobs: KK_TC_BN=<n> forces the tile, KK_TC_LEGACY=1 selects the one-tile-per-CTA kernel."""
         import os
         bn = 0
         env = os.environ.get("KK_TC_BN")
-        if env and pc.N >= int(env):
-            bn = int(env)
+        if env:
+            if pc.N >= int(env):
+                bn = int(env)
+        elif pc.N % 256 == 0 and (pc.N >= 1024 or pc.N == 256 or (pc.N == 512 and pc.C_in > 512)):
+            bn = 256
         if os.environ.get("KK_TC_LEGACY") == "1":
             bn |= 0x1000
         return bn
