@@ -212,11 +212,12 @@ def mel_filters(sample_rate: int, n_fft: int, n_mels: int, f_min: float = 0, f_m
 
 
 def log_mel_spectrogram(x, sample_rate=24000, n_fft=1024, hop_length=256, n_mels=80, window="hann", power=1,
-                        log="ln", floor=1e-5, norm=None, mel_scale="htk", center=True, pad_mode="reflect"):
+                        log="ln", floor=1e-5, norm=None, mel_scale="htk", center=True, pad_mode="reflect",
+                        f_min=0, f_max=None):
     """Fused STFT -> |X|^power -> mel -> log.  Defaults = indextts/mel.py:20-37 (``log(max(|X| @ fb.T, 1e-5))``).
     Returns (frames, n_mels) [batched: (B, frames, n_mels)]; the spectrogram is never written to HBM."""
     x, w, hop, mode, frames, squeeze = _prep_stft(x, n_fft, hop_length, n_fft, window, center, pad_mode)
-    fb = mel_filters(sample_rate, n_fft, n_mels, 0, None, norm, mel_scale).contiguous()
+    fb = mel_filters(sample_rate, n_fft, n_mels, f_min, f_max, norm, mel_scale).contiguous()
     B, n = x.shape
     out = torch.empty(B, frames, n_mels, dtype=torch.float32, device=x.device)
     log_mode = {None: 0, "none": 0, "ln": 1, "log": 1, "log10": 2, "ln_add": 3}[log]   # ln_add: log(x + floor)

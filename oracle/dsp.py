@@ -211,3 +211,26 @@ def log_mel_parakeet(x, sample_rate=16000, n_fft=512, win_length=400, hop_length
     else:
         mean, std = m.mean(), m.std()
     return ((m - mean) / (std + dtype(1e-5))).T[None].astype(dtype)
+
+
+def log_mel_s3(x, sample_rate=16000, n_mels=128, n_fft=400, hop_length=160, dtype=np.float32) -> np.ndarray:
+    """codec/models/s3/utils.py:8-42: periodic Hann, power spectrum (all frames), slaney mel, log10(max(., 1e-10)),
+    clamp to max - 8, (x + 4) / 4 -> (n_mels, frames)."""
+    dt = np.dtype(dtype).type
+    w = hanning(n_fft + 1, dtype)[:-1]
+    S = stft(x, n_fft=n_fft, hop_length=hop_length, win_length=n_fft, window=w, dtype=dtype).T
+    mag = (np.abs(S).astype(dtype)) ** 2
+    fb = mel_filters(sample_rate, n_fft, n_mels, norm="slaney", mel_scale="slaney", dtype=dtype)
+    ls = np.log10(np.maximum((fb @ mag).astype(dtype), dt(1e-10))).astype(dtype)
+    ls = np.maximum(ls, ls.max() - dt(8.0))
+    return ((ls + dt(4.0)) / dt(4.0)).astype(dtype)
+
+
+def mel_spark(x, sample_rate=16000, n_mels=128, n_fft=1024, f_min=10, f_max=None, hop_length=320, win_length=640,
+              dtype=np.float32) -> np.ndarray:
+    """tts/models/spark/bicodec.py:22-52: periodic Hann(win_length) zero-extended to n_fft, |X| @ slaney mel (f_min 10)
+    -> (1, frames, n_mels); no logarithm."""
+    w = hanning(win_length + 1, dtype)[:-1]
+    S = stft(x, n_fft=n_fft, hop_length=hop_length, win_length=win_length, window=w, dtype=dtype)
+    fb = mel_filters(sample_rate, n_fft, n_mels, f_min=f_min, f_max=f_max, norm="slaney", mel_scale="slaney", dtype=dtype)
+    return (np.abs(S).astype(dtype) @ fb.T).astype(dtype)[None]

@@ -10,6 +10,8 @@ import types
 
 import numpy as np
 
+Dtype = np.dtype
+bfloat16 = np.float32  # (names referenced by reference signatures / annotations only)
 float32 = np.dtype("float32")
 int32 = np.dtype("int32")
 int64 = np.dtype("int64")

@@ -126,6 +126,20 @@ def run_reference_f0ntrain(weights, x, s, style_dim=128, d_hid=512):
     return np.asarray(F0), np.asarray(N)
 
 
+def _function_from_source(path, name, namespace):
+    """Compile ONE top-level function of a reference file (unmodified source text, parsed with ``ast``) in a namespace
+    that supplies its free names - for files whose module-level imports (omegaconf, safetensors.torch, whole model
+    trees) cannot be satisfied here.  The function body that runs is the reference's own."""
+    import ast
+    import typing
+    tree = ast.parse(open(path, encoding="utf-8").read(), filename=path)
+    fn = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == name)
+    mod = ast.Module(body=[fn], type_ignores=[])
+    env = dict(namespace, Optional=typing.Optional, Any=typing.Any, Dict=typing.Dict)
+    exec(compile(mod, path, "exec"), env)
+    return env[name]
+
+
 def load_reference_frontends():
     """The reference's log-mel front ends and the Vocos ``ISTFTHead``, loaded from their own source
     files: codec/models/vocos/{mel,vocos}.py, tts/models/indextts/mel.py, stt/models/whisper/audio.py.  Unrelated
@@ -155,4 +169,9 @@ def load_reference_frontends():
     _pkg("mlx_audio.stt.models.parakeet", os.path.join(root, "stt", "models", "parakeet"))
     ns.parakeet_audio = _load("mlx_audio.stt.models.parakeet.audio",
                               os.path.join(root, "stt", "models", "parakeet", "audio.py"))
+    _pkg("mlx_audio.codec.models.s3", os.path.join(root, "codec", "models", "s3"))
+    ns.s3_utils = _load("mlx_audio.codec.models.s3.utils", os.path.join(root, "codec", "models", "s3", "utils.py"))
+    ns.spark_mel_spectrogram = _function_from_source(
+        os.path.join(root, "tts", "models", "spark", "bicodec.py"), "mel_spectrogram",
+        dict(mx=ns.mx, hanning=ns.utils.hanning, mel_filters=ns.utils.mel_filters, stft=ns.utils.stft))
     return ns

@@ -144,6 +144,8 @@ def main():
         istft_head=np.asarray(head(mx.array(hx))).astype(np.float32),
         parakeet_mel=np.asarray(fe.parakeet_audio.log_mel_spectrogram(mx.array(sig24), fe.parakeet_audio.PreprocessArgs(
             16000, "per_feature", 0.025, 0.01, "hann", 80, 512, 0.0))).astype(np.float32),
+        s3_mel=np.asarray(fe.s3_utils.log_mel_spectrogram(mx.array(sig24))).astype(np.float32),
+        spark_mel=np.asarray(fe.spark_mel_spectrogram(mx.array(sig24))).astype(np.float32),
         parakeet_mel_global=np.asarray(fe.parakeet_audio.log_mel_spectrogram(mx.array(sig24), fe.parakeet_audio.PreprocessArgs(
             16000, "all", 0.025, 0.01, "hamming", 128, 512, 0.0, pad_to=30000))).astype(np.float32),
     )

@@ -65,6 +65,19 @@ def test_parakeet_log_mel(g, sig):
     _cmp(b[0:1], g["parakeet_mel"], mean_tol=2e-4, max_tol=5e-3)
 
 
+def test_s3_and_spark_mel(g, sig):
+    from mlx_audio_b200.codec.models.s3.utils import log_mel_spectrogram as s3_mel
+    from mlx_audio_b200.tts.models.spark.bicodec import mel_spectrogram as spark_mel
+    _cmp(s3_mel(sig), g["s3_mel"])
+    b = s3_mel(torch.from_numpy(np.stack([sig, 0.3 * sig])))
+    assert tuple(b.shape) == (2, 128, 151)
+    _cmp(b[0], g["s3_mel"])
+    got = spark_mel(sig).cpu().numpy()
+    ref = g["spark_mel"]
+    assert got.shape == ref.shape
+    assert np.abs(got - ref).max() <= 1e-4 * max(1.0, float(np.abs(ref).max()))
+
+
 def test_vocos_istft_head(g):
     rng = np.random.Generator(np.random.PCG64(int(g["head_seed"])))
     dim, Lh = int(g["head_dim"]), int(g["head_frames"])

@@ -296,3 +296,13 @@ def test_parakeet_frontend_golden(golden_dir):
     sp = np.concatenate([sig, np.zeros(6000, np.float32)])
     m2 = dsp.log_mel_parakeet(sp, features=128, window="hamming", normalize="all")
     assert m2.shape == g["parakeet_mel_global"].shape and np.abs(m2 - g["parakeet_mel_global"]).max() < 1e-3
+
+
+def test_s3_and_spark_frontends_golden(golden_dir):
+    g = _g(golden_dir, "frontends.npz")
+    sig = synth.synth_audio(1, int(g["n"]), seed=int(g["audio_seed"]))[0]
+    m = dsp.log_mel_s3(sig)
+    assert m.shape == g["s3_mel"].shape == (128, 151) and np.abs(m - g["s3_mel"]).max() < 2e-4
+    sp = dsp.mel_spark(sig)
+    assert sp.shape == g["spark_mel"].shape == (1, 76, 128)
+    assert np.abs(sp - g["spark_mel"]).max() < 1e-4 * max(1.0, float(np.abs(g["spark_mel"]).max()))
