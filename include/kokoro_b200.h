@@ -173,6 +173,12 @@ int kk_clamp_below_max_affine(float* x, int B, long long n_per, float range, flo
  * per_feature = 1: (x - mean_f) / (std_f + eps) with mean / population std over the frames of each feature;
  * per_feature = 0: one mean / std per signal. */
 int kk_normalize_features(float* x, int B, int frames, int n_feat, int per_feature, float eps, void* stream);
+/* Snake activations of the codec generators (mlx_audio/codec/models/bigvgan/activation.py:5-51 Snake / SnakeBeta,
+ * codec/models/descript/nn/layers.py:116-129 snake / Snake1d): y = x + 1/(b_c + eps) * sin(a_c x)^2 over an
+ * (outer, C, inner) tensor (inner = 1: channels-last); beta may be NULL (b = a); logscale: a, b = exp(parameter).
+ * out may alias x. */
+int kk_snake_f32(const float* x, float* out, const float* alpha, const float* beta, long long outer, int C,
+                 long long inner, int logscale, float eps, void* stream);
 
 #ifdef __cplusplus
 }

@@ -490,6 +490,36 @@ extern "C" int kk_normalize_features(float* x, int B, int frames, int n_feat, in
   return KK_OK;
 }
 
+namespace kk {
+// Snake activations of the codec generators (BigVGAN Snake / SnakeBeta, codec/models/bigvgan/activation.py:5-51; DAC
+// Snake1d, codec/models/descript/nn/layers.py:116-129):  y = x + 1 / (b_c + eps) * sin(a_c x)^2,  b = a unless a
+// separate beta is given, a / b = exp(.) of the parameters in log-scale mode.  Element (o, c, i) of an (outer, C, inner)
+// tensor: inner = 1 is channels-last, inner = L channels-first.  Reference op order, no contraction.
+__global__ void __launch_bounds__(256) snake_kernel(const float* __restrict__ x, float* __restrict__ out,
+                                                    const float* __restrict__ alpha, const float* __restrict__ beta,
+                                                    long long total, int C, long long inner, int logscale, float eps) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c = (int)((i / inner) % C);
+  float a = alpha[c], b = beta ? beta[c] : a;
+  if (logscale) { a = expf(a); b = beta ? expf(b) : a; }
+  const float v = x[i];
+  const float s = sinf(__fmul_rn(v, a));
+  out[i] = __fadd_rn(v, __fmul_rn(__fdiv_rn(1.0f, __fadd_rn(b, eps)), __fmul_rn(s, s)));
+}
+}  // namespace kk
+
+extern "C" int kk_snake_f32(const float* x, float* out, const float* alpha, const float* beta, long long outer, int C,
+                            long long inner, int logscale, float eps, void* stream) {
+  KK_CHECK_ARG(x && out && alpha && outer > 0 && C > 0 && inner > 0, "kk_snake_f32: bad arguments");
+  const long long total = outer * C * inner;
+  KK_CHECK_ARG((total + 255) / 256 <= 0x7fffffffLL, "kk_snake_f32: too many elements");
+  kk::snake_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, out, alpha, beta, total, C, inner,
+                                                                                     logscale, eps);
+  KK_LAUNCH_CHECK("snake_kernel");
+  return KK_OK;
+}
+
 extern "C" int kk_convert_act(const float* x, int x_pitch, void* out, int out_is_bf16, int out_pitch, long long rows,
                               int C, float slope, void* stream) {
   KK_CHECK_ARG(x && out && rows > 0 && C > 0, "kk_convert_act: bad arguments");

@@ -234,3 +234,15 @@ def mel_spark(x, sample_rate=16000, n_mels=128, n_fft=1024, f_min=10, f_max=None
     S = stft(x, n_fft=n_fft, hop_length=hop_length, win_length=win_length, window=w, dtype=dtype)
     fb = mel_filters(sample_rate, n_fft, n_mels, f_min=f_min, f_max=f_max, norm="slaney", mel_scale="slaney", dtype=dtype)
     return (np.abs(S).astype(dtype) @ fb.T).astype(dtype)[None]
+
+
+def snake(x, alpha, beta=None, logscale=False, channels_first=False, eps=1e-9, dtype=np.float32) -> np.ndarray:
+    """codec/models/bigvgan/activation.py:16-24 (Snake: channels-first), :41-51 (SnakeBeta: channels-last, beta),
+    codec/models/descript/nn/layers.py:116-119: x + 1 / (b + eps) * sin(a x)^2, a / b = exp(.) in log-scale mode."""
+    x = np.asarray(x, dtype)
+    shp = (1, -1, 1) if channels_first else (1, 1, -1)
+    a = np.asarray(alpha, dtype).reshape(shp)
+    b = a if beta is None else np.asarray(beta, dtype).reshape(shp)
+    if logscale:
+        a, b = np.exp(a), np.exp(b)
+    return (x + (dtype(1.0) / (b + dtype(eps))) * np.power(np.sin(x * a), 2)).astype(dtype)

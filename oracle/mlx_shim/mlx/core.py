@@ -177,6 +177,14 @@ def square(x):
     return _wrap(x * x)
 
 
+def power(x, p):
+    return _wrap(np.power(_f(x), _f(p)).astype(np.float32))
+
+
+def reciprocal(x):
+    return _wrap((np.float32(1.0) / _f(x)).astype(np.float32))
+
+
 def addmm(c, a, b, alpha=1.0, beta=1.0):
     """mx.addmm: beta * c + alpha * (a @ b) (used by the reference LSTM, modules.py:156-158)."""
     a, b, c = _f(a), _f(b), _f(c)

@@ -171,6 +171,13 @@ def load_reference_frontends():
                               os.path.join(root, "stt", "models", "parakeet", "audio.py"))
     _pkg("mlx_audio.codec.models.s3", os.path.join(root, "codec", "models", "s3"))
     ns.s3_utils = _load("mlx_audio.codec.models.s3.utils", os.path.join(root, "codec", "models", "s3", "utils.py"))
+    _pkg("mlx_audio.codec.models.bigvgan", os.path.join(root, "codec", "models", "bigvgan"))
+    ns.bigvgan_activation = _load("mlx_audio.codec.models.bigvgan.activation",
+                                  os.path.join(root, "codec", "models", "bigvgan", "activation.py"))
+    _pkg("mlx_audio.codec.models.descript", os.path.join(root, "codec", "models", "descript"))
+    _pkg("mlx_audio.codec.models.descript.nn", os.path.join(root, "codec", "models", "descript", "nn"))
+    ns.dac_layers = _load("mlx_audio.codec.models.descript.nn.layers",
+                          os.path.join(root, "codec", "models", "descript", "nn", "layers.py"))
     ns.spark_mel_spectrogram = _function_from_source(
         os.path.join(root, "tts", "models", "spark", "bicodec.py"), "mel_spectrogram",
         dict(mx=ns.mx, hanning=ns.utils.hanning, mel_filters=ns.utils.mel_filters, stft=ns.utils.stft))

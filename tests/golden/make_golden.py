@@ -149,6 +149,21 @@ def main():
         parakeet_mel_global=np.asarray(fe.parakeet_audio.log_mel_spectrogram(mx.array(sig24), fe.parakeet_audio.PreprocessArgs(
             16000, "all", 0.025, 0.01, "hamming", 128, 512, 0.0, pad_to=30000))).astype(np.float32),
     )
+    # ---- 6. Snake activations of the codec generators
+    rs = np.random.Generator(np.random.PCG64(41))
+    xs = (2.0 * rs.standard_normal((2, 12, 50), dtype=np.float32)).astype(np.float32)
+    al = rs.uniform(0.3, 2.0, 12).astype(np.float32)
+    be = rs.uniform(0.3, 2.0, 50).astype(np.float32)
+    al50 = rs.uniform(-1.0, 1.0, 50).astype(np.float32)
+    sn = fe.bigvgan_activation.Snake(12); sn.alpha = mx.array(al)
+    snl = fe.bigvgan_activation.Snake(12, alpha_logscale=True); snl.alpha = mx.array(al - 1.0)
+    sb = fe.bigvgan_activation.SnakeBeta(50, alpha_logscale=True); sb.alpha = mx.array(al50); sb.beta = mx.array(be - 1.0)
+    np.savez_compressed(
+        os.path.join(HERE, "snake.npz"), backend=backend, seed=41,
+        snake=np.asarray(sn(mx.array(xs.copy()))).astype(np.float32),
+        snake_log=np.asarray(snl(mx.array(xs.copy()))).astype(np.float32),
+        snakebeta_log=np.asarray(sb(mx.array(xs.copy()))).astype(np.float32),
+        dac_snake=np.asarray(fe.dac_layers.snake(mx.array(xs.copy()), mx.array(be.reshape(1, 1, 50)))).astype(np.float32))
     print("wrote", sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
 
 

@@ -106,3 +106,25 @@ def test_vocos_istft_head(g):
         head(np.zeros((1, 4, dim + 1), np.float32))
     with pytest.raises(ValueError):
         ISTFTHead(dim, 1024, 256).load_weights({"out.weight": np.zeros((3, 3), np.float32)})
+
+
+def test_snake_activations(golden_dir):
+    from mlx_audio_b200.codec.models.bigvgan.activation import Snake, SnakeBeta
+    from mlx_audio_b200.codec.models.descript.nn.layers import Snake1d, snake
+    gs = np.load(os.path.join(golden_dir, "snake.npz"))
+    rs = np.random.Generator(np.random.PCG64(41))
+    xs = (2.0 * rs.standard_normal((2, 12, 50), dtype=np.float32)).astype(np.float32)
+    al = rs.uniform(0.3, 2.0, 12).astype(np.float32)
+    be = rs.uniform(0.3, 2.0, 50).astype(np.float32)
+    al50 = rs.uniform(-1.0, 1.0, 50).astype(np.float32)
+    sn = Snake(12); sn.alpha = torch.from_numpy(al)
+    assert np.abs(sn(xs).cpu().numpy() - gs["snake"]).max() < 5e-6
+    snl = Snake(12, alpha_logscale=True); snl.alpha = torch.from_numpy(al - 1.0)
+    assert np.abs(snl(xs).cpu().numpy() - gs["snake_log"]).max() < 5e-6
+    sb = SnakeBeta(50, alpha_logscale=True); sb.alpha = torch.from_numpy(al50); sb.beta = torch.from_numpy(be - 1.0)
+    assert np.abs(sb(xs).cpu().numpy() - gs["snakebeta_log"]).max() < 5e-6
+    assert np.abs(snake(xs, be.reshape(1, 1, 50)).cpu().numpy() - gs["dac_snake"]).max() < 5e-6
+    s1 = Snake1d(50)                                        # alpha = 1: x + sin(x)^2 / (1 + 1e-9)
+    assert np.abs(s1(xs).cpu().numpy() - dsp.snake(xs, np.ones(50, np.float32))).max() < 5e-6
+    with pytest.raises(ValueError):
+        sn(np.zeros((2, 13, 5), np.float32))

@@ -306,3 +306,21 @@ def test_s3_and_spark_frontends_golden(golden_dir):
     sp = dsp.mel_spark(sig)
     assert sp.shape == g["spark_mel"].shape == (1, 76, 128)
     assert np.abs(sp - g["spark_mel"]).max() < 1e-4 * max(1.0, float(np.abs(g["spark_mel"]).max()))
+
+
+def _snake_inputs():
+    rs = np.random.Generator(np.random.PCG64(41))
+    xs = (2.0 * rs.standard_normal((2, 12, 50), dtype=np.float32)).astype(np.float32)
+    al = rs.uniform(0.3, 2.0, 12).astype(np.float32)
+    be = rs.uniform(0.3, 2.0, 50).astype(np.float32)
+    al50 = rs.uniform(-1.0, 1.0, 50).astype(np.float32)
+    return xs, al, be, al50
+
+
+def test_snake_activations_golden(golden_dir):
+    g = _g(golden_dir, "snake.npz")
+    xs, al, be, al50 = _snake_inputs()
+    assert np.abs(dsp.snake(xs, al, channels_first=True) - g["snake"]).max() < 2e-6
+    assert np.abs(dsp.snake(xs, al - 1.0, logscale=True, channels_first=True) - g["snake_log"]).max() < 2e-6
+    assert np.abs(dsp.snake(xs, al50, be - 1.0, logscale=True) - g["snakebeta_log"]).max() < 2e-6
+    assert np.abs(dsp.snake(xs, be) - g["dac_snake"]).max() < 2e-6
