@@ -179,6 +179,10 @@ int kk_normalize_features(float* x, int B, int frames, int n_feat, int per_featu
  * out may alias x. */
 int kk_snake_f32(const float* x, float* out, const float* alpha, const float* beta, long long outer, int C,
                  long long inner, int logscale, float eps, void* stream);
+/* Weight-norm fold with the epsilon and operation order as parameters: g_first = 1, eps = 0 is the DAC form
+ * w = (g * v) / ||v|| of mlx_audio/codec/models/descript/nn/layers.py:7-12,57 (norm over (K, I) per output channel). */
+int kk_fold_weight_norm_ex(const float* v, const float* g, float* w, int O, int KI, float eps, int g_first,
+                           void* stream);
 
 #ifdef __cplusplus
 }

@@ -80,6 +80,7 @@ PROTOTYPES = {
     "kk_clamp_below_max_affine": [_P, _I, _LL, _F, _F, _F, _P],
     "kk_normalize_features": [_P, _I, _I, _I, _I, _F, _P],
     "kk_snake_f32": [_P, _P, _P, _P, _LL, _I, _LL, _I, _F, _P],
+    "kk_fold_weight_norm_ex": [_P, _P, _P, _I, _I, _F, _I, _P],
 }
 
 _lib: Optional[C.CDLL] = None

@@ -6,7 +6,7 @@ namespace kk {
 // One block per output channel: n = sqrt(sum v^2) (double accumulation), w = v / (n + 1e-7) * g.
 // Reference: weight_norm istftnet.py:87-93 with dim=0 (:130).
 __global__ void fold_weight_norm_kernel(const float* __restrict__ v, const float* __restrict__ g,
-                                        float* __restrict__ w, int KI) {
+                                        float* __restrict__ w, int KI, float eps, int g_first) {
   int o = blockIdx.x;
   const float* vo = v + (size_t)o * KI;
   double acc = 0.0;
@@ -25,9 +25,11 @@ __global__ void fold_weight_norm_kernel(const float* __restrict__ v, const float
   }
   __syncthreads();
   float n = sqrtf((float)sh[0]);
-  float denom = n + 1e-7f;
+  float denom = n + eps;
   float go = g[o];
-  for (int i = threadIdx.x; i < KI; i += blockDim.x) w[(size_t)o * KI + i] = (vo[i] / denom) * go;
+  // g_first: (g * v) / n, the order of the DAC layers (descript/nn/layers.py:57); else (v / (n + eps)) * g (istftnet.py:92-93)
+  if (g_first) for (int i = threadIdx.x; i < KI; i += blockDim.x) w[(size_t)o * KI + i] = __fdiv_rn(__fmul_rn(go, vo[i]), denom);
+  else for (int i = threadIdx.x; i < KI; i += blockDim.x) w[(size_t)o * KI + i] = (vo[i] / denom) * go;
 }
 
 template <typename OutT>
@@ -65,7 +67,15 @@ __global__ void pack_conv_weight_kernel(const float* __restrict__ w, OutT* __res
 
 extern "C" int kk_fold_weight_norm(const float* v, const float* g, float* w, int O, int KI, void* stream) {
   KK_CHECK_ARG(v && g && w && O > 0 && KI > 0, "kk_fold_weight_norm: bad arguments O=%d KI=%d", O, KI);
-  kk::fold_weight_norm_kernel<<<O, 256, 0, (cudaStream_t)stream>>>(v, g, w, KI);
+  kk::fold_weight_norm_kernel<<<O, 256, 0, (cudaStream_t)stream>>>(v, g, w, KI, 1e-7f, 0);
+  KK_LAUNCH_CHECK("fold_weight_norm_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_fold_weight_norm_ex(const float* v, const float* g, float* w, int O, int KI, float eps, int g_first,
+                                      void* stream) {
+  KK_CHECK_ARG(v && g && w && O > 0 && KI > 0 && eps >= 0.f, "kk_fold_weight_norm_ex: bad arguments O=%d KI=%d", O, KI);
+  kk::fold_weight_norm_kernel<<<O, 256, 0, (cudaStream_t)stream>>>(v, g, w, KI, eps, g_first);
   KK_LAUNCH_CHECK("fold_weight_norm_kernel");
   return KK_OK;
 }

@@ -20,6 +20,9 @@ class Module:
     def eval(self):
         return self
 
+    def __contains__(self, key):      # mlx.nn.Module is a dict of its members ("bias" in self, descript/nn/layers.py:59)
+        return vars(self).get(key) is not None
+
     # -- flat parameter access by the dotted names MLX would produce
     def named_parameters(self, prefix=""):
         out = {}

@@ -158,8 +158,15 @@ def main():
     sn = fe.bigvgan_activation.Snake(12); sn.alpha = mx.array(al)
     snl = fe.bigvgan_activation.Snake(12, alpha_logscale=True); snl.alpha = mx.array(al - 1.0)
     sb = fe.bigvgan_activation.SnakeBeta(50, alpha_logscale=True); sb.alpha = mx.array(al50); sb.beta = mx.array(be - 1.0)
+    wn = fe.dac_layers.WNConv1d(6, 10, 5, stride=2, padding=3, dilation=2)
+    wv = rs.standard_normal((10, 5, 6), dtype=np.float32)
+    wg = rs.uniform(0.5, 1.5, (10, 1, 1)).astype(np.float32)
+    wb = (0.1 * rs.standard_normal((10,), dtype=np.float32)).astype(np.float32)
+    xw = rs.standard_normal((2, 37, 6), dtype=np.float32)
+    wn.weight_v, wn.weight_g, wn.bias = mx.array(wv), mx.array(wg), mx.array(wb)
     np.savez_compressed(
         os.path.join(HERE, "snake.npz"), backend=backend, seed=41,
+        wnconv=np.asarray(wn(mx.array(xw))).astype(np.float32),
         snake=np.asarray(sn(mx.array(xs.copy()))).astype(np.float32),
         snake_log=np.asarray(snl(mx.array(xs.copy()))).astype(np.float32),
         snakebeta_log=np.asarray(sb(mx.array(xs.copy()))).astype(np.float32),

@@ -128,3 +128,26 @@ def test_snake_activations(golden_dir):
     assert np.abs(s1(xs).cpu().numpy() - dsp.snake(xs, np.ones(50, np.float32))).max() < 5e-6
     with pytest.raises(ValueError):
         sn(np.zeros((2, 13, 5), np.float32))
+
+
+def test_dac_wnconv1d(golden_dir):
+    from mlx_audio_b200.codec.models.descript.nn.layers import WNConv1d
+    gs = np.load(os.path.join(golden_dir, "snake.npz"))
+    rs = np.random.Generator(np.random.PCG64(41))
+    rs.standard_normal((2, 12, 50), dtype=np.float32); rs.uniform(0.3, 2.0, 12); rs.uniform(0.3, 2.0, 50)
+    rs.uniform(-1.0, 1.0, 50)                                    # the draws of the Snake cases come first
+    wv = rs.standard_normal((10, 5, 6), dtype=np.float32)
+    wg = rs.uniform(0.5, 1.5, (10, 1, 1)).astype(np.float32)
+    wb = (0.1 * rs.standard_normal((10,), dtype=np.float32)).astype(np.float32)
+    xw = rs.standard_normal((2, 37, 6), dtype=np.float32)
+    conv = WNConv1d(6, 10, 5, stride=2, padding=3, dilation=2)
+    conv.weight_v, conv.weight_g, conv.bias = torch.from_numpy(wv), torch.from_numpy(wg), torch.from_numpy(wb)
+    y = conv(xw)
+    torch.cuda.synchronize()
+    ref = gs["wnconv"]
+    assert tuple(y.shape) == ref.shape == (2, 18, 10)
+    assert np.abs(y.cpu().numpy() - ref).max() < 1e-5
+    with pytest.raises(NotImplementedError):
+        WNConv1d(6, 12, 3, groups=2)
+    with pytest.raises(ValueError):
+        conv(np.zeros((1, 4, 7), np.float32))

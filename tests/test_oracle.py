@@ -324,3 +324,19 @@ def test_snake_activations_golden(golden_dir):
     assert np.abs(dsp.snake(xs, al - 1.0, logscale=True, channels_first=True) - g["snake_log"]).max() < 2e-6
     assert np.abs(dsp.snake(xs, al50, be - 1.0, logscale=True) - g["snakebeta_log"]).max() < 2e-6
     assert np.abs(dsp.snake(xs, be) - g["dac_snake"]).max() < 2e-6
+
+
+def test_dac_wnconv1d_golden(golden_dir):
+    """WNConv1d (codec/models/descript/nn/layers.py:15-59) restated with the oracle's conv: w = g v / ||v|| (no eps)."""
+    from oracle.istftnet import conv1d_mlx
+    g = _g(golden_dir, "snake.npz")
+    rs = np.random.Generator(np.random.PCG64(41))
+    rs.standard_normal((2, 12, 50), dtype=np.float32); rs.uniform(0.3, 2.0, 12); rs.uniform(0.3, 2.0, 50)
+    rs.uniform(-1.0, 1.0, 50)
+    wv = torch.from_numpy(rs.standard_normal((10, 5, 6), dtype=np.float32))
+    wg = torch.from_numpy(rs.uniform(0.5, 1.5, (10, 1, 1)).astype(np.float32))
+    wb = torch.from_numpy((0.1 * rs.standard_normal((10,), dtype=np.float32)).astype(np.float32))
+    xw = torch.from_numpy(rs.standard_normal((2, 37, 6), dtype=np.float32))
+    w = wg * wv / torch.sqrt((wv ** 2).sum(dim=(1, 2), keepdim=True))
+    y = conv1d_mlx(xw, w, stride=2, padding=3, dilation=2) + wb
+    assert tuple(y.shape) == g["wnconv"].shape and np.abs(y.numpy() - g["wnconv"]).max() < 1e-5
