@@ -455,7 +455,9 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
         if (live) reinterpret_cast<float2*>(a.out)[((size_t)b * a.frames + f) * bins + k] = X;
       } else {
         const float m2 = X.x * X.x + X.y * X.y;
-        P[k] = a.power == 2 ? m2 : sqrtf(m2);
+        float mg = m2;
+        if (a.power != 2) asm("sqrt.approx.f32 %0, %1;" : "=f"(mg) : "f"(m2));   // 1 ulp, no slow-path branch
+        P[k] = mg;
       }
     };
     auto unpack_pair = [&](int k, float2 zk, float2 zc, float2 u, bool self) {
