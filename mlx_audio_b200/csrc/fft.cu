@@ -626,8 +626,9 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
       float2* tfg = A;   // the group's time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
-        // conj and the 1/n normalisation of irfft (1/nc here, the factor 1/2 is already inside E and O)
-        tfg[j + NT * q] = live ? make_float2(v[q].x * inv_nc, -v[q].y * inv_nc) : make_float2(0.f, 0.f);
+        // conj only (the factor 1/2 of 1/n is already inside E and O): the 1/nc of irfft is a power of two, so it commutes exactly with the window products and the
+        // overlap-add sums and is applied once per output sample below instead of twice per transform point
+        tfg[j + NT * q] = live ? make_float2(v[q].x, -v[q].y) : make_float2(0.f, 0.f);
       }
     }
     __syncthreads();
@@ -656,6 +657,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
           if (r >= 0 && r < R) acc = __fadd_rn(acc, tv[gg][r]);
         }
         if (interior) {
+          acc = __fmul_rn(acc, inv_nc);
           orow[hh * hop] = (ws_full[o] != 0.f) ? acc / ws_full[o] : acc;
           continue;
         }
@@ -669,6 +671,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
             const int fr = hcur - r;                     // frames covering this sample
             if (fr >= 0 && fr < a.frames) ws = __fadd_rn(ws, w[o][r]);
           }
+          acc = __fmul_rn(acc, inv_nc);
           a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
         }
       }
