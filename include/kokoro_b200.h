@@ -131,11 +131,13 @@ int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, const kk_conv_d
 /* ---- harmonic source (SineGen / SourceModuleHnNSF istftnet.py:531-680, interpolate.py:82-106,
  * nn.Upsample :718-720) fused with MLXSTFT.transform (:463-495, utils.stft n_fft=20 hop=5):
  * f0 (B, 2T) -> har_source (B, 600T) -> har (B, 120T+1, har_pitch) = [|X| (11) , angle(X) (11)].
- * noise (B, 600T, 9) N(0,1) or NULL (then a Philox counter RNG seeded with `seed` is used).
+ * noise (B, 600T, 9) N(0,1) or NULL (then a Philox counter RNG is used, seeded with *seed_dev when seed_dev is a
+ * device pointer - so that a captured CUDA graph draws fresh noise on every replay, as mx.random.normal does on
+ * every call (istftnet.py:620) - else with `seed`).
  * phase_ws: scratch (B, 9, 2T) floats.  lin_w (9), lin_b (1): m_source.l_linear. */
-int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const float* lin_w,
-                   const float* lin_b, float* phase_ws, float* har_source, int B, int T2, int upsample,
-                   void* stream);
+int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const unsigned long long* seed_dev,
+                   const float* lin_w, const float* lin_b, float* phase_ws, float* har_source, int B, int T2,
+                   int upsample, void* stream);
 int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream);
 /* Same transform, additionally (or only, har == NULL) written as bf16 into (B, bf_rows, bf_pitch) with
  * bf_rows >= 120T+1: the tensor-core noise_convs (istftnet.py:778) read it as (B, bf_rows/6, 6*bf_pitch) rows

@@ -87,6 +87,7 @@ __device__ __forceinline__ float sin_large(float ph) {
 // negative-index wrap (interpolate.py:88-106), sin, uv gate, noise, 9->1 linear, tanh.
 __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __restrict__ phase,
                                    const float* __restrict__ noise, unsigned long long seed,
+                                   const unsigned long long* __restrict__ seed_dev,
                                    const float* __restrict__ lin_w, const float* __restrict__ lin_b,
                                    float* __restrict__ out, int B, int T2, int upsample, float inv_up, float half_inv_up) {
   const long long S = (long long)T2 * upsample;
@@ -112,6 +113,7 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
 #pragma unroll
     for (int k = 0; k < NH; ++k) nz[k] = np_[k];
   } else {
+    if (seed_dev) seed = __ldg(seed_dev);   // device-resident seed: a captured CUDA graph draws fresh noise per replay
     uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
 #pragma unroll
     for (int g = 0; g < 3; ++g) {
@@ -201,9 +203,9 @@ stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_
 
 }  // namespace kk
 
-extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const float* lin_w,
-                              const float* lin_b, float* phase_ws, float* har_source, int B, int T2, int upsample,
-                              void* stream) {
+extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed,
+                              const unsigned long long* seed_dev, const float* lin_w, const float* lin_b,
+                              float* phase_ws, float* har_source, int B, int T2, int upsample, void* stream) {
   KK_CHECK_ARG(f0 && lin_w && lin_b && phase_ws && har_source, "kk_hnsf_source: null pointer");
   KK_CHECK_ARG(B > 0 && T2 > 1 && upsample > 1, "kk_hnsf_source: bad shape B=%d T2=%d up=%d", B, T2, upsample);
   KK_CHECK_ARG((long long)T2 * upsample < (1LL << 24), "kk_hnsf_source: utterance too long for float32 sample index");
@@ -214,7 +216,7 @@ extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long
   float inv_up = (float)(1.0 / (double)upsample);
   float half_inv_up = (float)(0.5 * (1.0 / (double)upsample));
   long long total = (long long)B * T2 * upsample;
-  kk::hnsf_sample_kernel<<<kk::cdiv(total, 256), 256, 0, st>>>(f0, phase_ws, noise, seed, lin_w, lin_b, har_source, B,
+  kk::hnsf_sample_kernel<<<kk::cdiv(total, 256), 256, 0, st>>>(f0, phase_ws, noise, seed, seed_dev, lin_w, lin_b, har_source, B,
                                                               T2, upsample, inv_up, half_inv_up);
   KK_LAUNCH_CHECK("hnsf_sample_kernel");
   return KK_OK;

@@ -52,7 +52,7 @@ class StreamingDecoder:
                 sl["in_ready"] = self.h2d.record_event()
             compute.wait_event(sl["in_ready"])
             x = sl["in"]
-            y = self.dec(x["asr"], x["F0_curve"], x["N"], x["s"])
+            y = self.dec(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)   # copied out below
             if self.post is not None:
                 self.post(y)
             if "out_done" in sl:

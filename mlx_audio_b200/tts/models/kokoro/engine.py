@@ -585,7 +585,10 @@ class DecoderEngine:
         har_source = self._buf(plan, "har_source", (B, S))
         har = self._buf(plan, "har", (B, L3, 24))
         plan.source_op_index = len(plan.ops)
-        plan.add(lib.kk_hnsf_source, self._addr(f0c), None, 0, self._addr(self.lin_w), self._addr(self.lin_b),
+        # the Philox seed lives in device memory (written before every run / graph replay): a captured graph then
+        # draws fresh noise per call like the reference's mx.random.normal (istftnet.py:620)
+        seed_buf = self._buf(plan, "seed", (1,), torch.int64)
+        plan.add(lib.kk_hnsf_source, self._addr(f0c), None, 0, self._addr(seed_buf), self._addr(self.lin_w), self._addr(self.lin_b),
                  self._addr(phase_ws), self._addr(har_source), B, T2, up, launches=2)
         har16 = None
         har_rows = r1 * (L20 + 1)       # rows of the bf16 copy: whole 6-frame rows for the stride-6 noise conv

@@ -12,7 +12,8 @@ plan).  There is no CPU path: without a CUDA device or the built shared library 
 Extensions over the reference signature (keyword-only, defaults keep reference behaviour):
   * ``noise``: (B, 600T, 9) standard-normal tensor replacing the reference's ``mx.random.normal`` draw in
     SineGen (istftnet.py:620) so results are reproducible / comparable with the oracle; default: on-device
-    Philox RNG seeded by ``seed``.
+    Philox RNG seeded by ``seed`` (a fresh seed per call, also under CUDA graphs: the seed is read from device memory).
+  * ``borrow``: return the persistent output buffer instead of a copy (see ``__call__``).
 """
 from __future__ import annotations
 
@@ -129,7 +130,11 @@ class Decoder:
         """Size the shared workspace for the largest (B, T) the caller will decode (ragged / bucketed workloads)."""
         self._plan(B, T)
 
-    def __call__(self, asr, F0_curve, N, s, *, noise=None, seed: Optional[int] = None, capture_taps: bool = False):
+    def __call__(self, asr, F0_curve, N, s, *, noise=None, seed: Optional[int] = None, capture_taps: bool = False,
+                 borrow: bool = False):
+        """Returns a fresh (B, 1, 600 T) tensor like the reference (istftnet.py:963).  ``borrow=True`` hands out the
+        decoder's persistent output buffer instead (zero copy): it is overwritten by the next call of ANY shape, so only
+        callers that consume it before calling again (StreamingDecoder, decode_sharded, bench.py) should ask for it."""
         L.require_cuda()
         dev = self.device
         asr = _to_cuda_f32(asr, dev)
@@ -169,15 +174,15 @@ class Decoder:
             plan.run(L.stream())
         if seed is None:
             self.seed += 1
-        return bufs["audio"]
+        return bufs["audio"] if borrow else bufs["audio"].clone()
 
     def _set_source(self, plan: Plan, noise_t: Optional[torch.Tensor], seed: int):
         i = plan.source_op_index
         fn, args = plan.ops[i]
         args = list(args)
         args[1] = noise_t.data_ptr() if noise_t is not None else None
-        args[2] = int(seed) & 0xFFFFFFFFFFFFFFFF
         plan.ops[i] = (fn, tuple(args))
+        plan.buffers["seed"].fill_(int(seed) & 0x7FFFFFFFFFFFFFFF)   # outside any captured graph
         plan.keep_noise = noise_t
 
     def _run_graph(self, plan: Plan, key):

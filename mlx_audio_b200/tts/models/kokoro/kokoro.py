@@ -135,15 +135,12 @@ class Model:
             asr, pred_dur = feats["asr"], feats.get("pred_dur")
             if "en" in feats:
                 F0_pred, N_pred = self.predictor.F0Ntrain(feats["en"], ref_s[:, 128:])
-                F0_pred, N_pred = F0_pred.clone(), N_pred.clone()
             else:
                 F0_pred, N_pred = feats["F0_pred"], feats["N_pred"]
         else:
             asr, F0_pred, N_pred, pred_dur = feats
         dec = decoder if decoder is not None else self.decoder
         audio = dec(asr, F0_pred, N_pred, ref_s[:, :128])[0]                            # kokoro.py:165
-        if hasattr(audio, "clone"):
-            audio = audio.clone()       # the Decoder returns a view of its persistent output buffer
         return self.Output(audio=audio, pred_dur=pred_dur) if return_output else audio
 
     # ---- text -> audio segments (the route the reference's CLI and server take: kokoro.py:258-346)

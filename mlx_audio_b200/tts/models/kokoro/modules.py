@@ -173,9 +173,12 @@ class ProsodyPredictor:
             return self._lstm(x_blc)[0]
 
     # ------------------------------------------------------------------ forward
-    def F0Ntrain(self, x=None, s=None, *, hidden=None, capture_taps: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+    def F0Ntrain(self, x=None, s=None, *, hidden=None, capture_taps: bool = False,
+                 borrow: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
         """modules.py:355-377.  ``x``: (B, d_hid + style_dim, L) (``en`` of kokoro.py:157-159); ``s``: (B, style_dim).
-        Extension: ``hidden`` = (B, L, d_hid) output of the shared LSTM, skipping it.  Returns (F0, N), each (B, 2L)."""
+        Extension: ``hidden`` = (B, L, d_hid) output of the shared LSTM, skipping it.  Returns (F0, N), each (B, 2L):
+        fresh tensors like the reference; ``borrow=True`` returns the persistent workspace views (overwritten by the
+        next call)."""
         L.require_cuda()
         dev = self.device
         s = _to_cuda_f32(s, dev)
@@ -203,7 +206,8 @@ class ProsodyPredictor:
         plan.buffers["pp.in.s"].copy_(s, non_blocking=True)
         plan.capture = capture_taps
         plan.run(L.stream())
-        return plan.buffers["pp.out.F0"], plan.buffers["pp.out.N"]
+        f0, n = plan.buffers["pp.out.F0"], plan.buffers["pp.out.N"]
+        return (f0, n) if borrow else (f0.clone(), n.clone())
 
     def launches_per_forward(self, B: int, L_: int) -> int:
         return self.engine.plans[(B, L_)].n_launches

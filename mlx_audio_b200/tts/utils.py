@@ -9,8 +9,6 @@ import os
 from pathlib import Path
 from typing import Union
 
-import numpy as np
-
 MODEL_REMAPPING = {"kokoro": "kokoro"}
 
 
@@ -21,6 +19,21 @@ def load_config(model_path: Union[str, Path]) -> dict:
         raise FileNotFoundError(f"Config not found at {model_path}")
     with open(cfg, encoding="utf-8") as f:
         return json.load(f)
+
+
+def read_checkpoint(files, prefixes=("decoder.", "predictor.")) -> dict:
+    """Read the tensors of the rebuilt sub-modules from safetensors files as float32 NumPy arrays.  Goes through the
+    "pt" framework: safetensors' NumPy loader has no bfloat16, and the reference's default checkpoint
+    (mlx-community/Kokoro-82M-bf16, tts/generate.py:366) is bf16.  Keys outside ``prefixes`` (the out-of-scope text
+    front end: bert.*, bert_encoder.*, text_encoder.*) are never decoded."""
+    from safetensors import safe_open
+    weights = {}
+    for wf in files:
+        with safe_open(str(wf), framework="pt", device="cpu") as f:
+            for k in f.keys():
+                if k.startswith(tuple(prefixes)):
+                    weights[k] = f.get_tensor(k).float().numpy()
+    return weights
 
 
 def load_model(model_path: Union[str, Path], lazy: bool = False, strict: bool = True, **kwargs):
@@ -40,12 +53,9 @@ def load_model(model_path: Union[str, Path], lazy: bool = False, strict: bool = 
     files = sorted(glob.glob(str(model_path / "*.safetensors")))
     if not files:
         raise FileNotFoundError(f"No safetensors found in {model_path}")
-    from safetensors.numpy import load_file
-    weights = {}
-    for wf in files:
-        weights.update(load_file(wf))
+    weights = read_checkpoint(files)
     model = Model(ModelConfig.from_dict(config), repo_id=str(model_path), frontend=kwargs.get("frontend"),
                   dtype=kwargs.get("dtype", "bf16"), device=kwargs.get("device"))
-    weights = model.sanitize({k: np.asarray(v, dtype=np.float32) if v.dtype != np.float32 else v for k, v in weights.items()})
+    weights = model.sanitize(weights)
     model.load_weights(weights, strict=strict)
     return model

@@ -98,3 +98,22 @@ def test_decoder_sanitize_follows_reference_heuristic():
     np.testing.assert_array_equal(dec.sanitize(nk, nw), w[nk])
     b = w["decoder.generator.conv_post.bias"]
     assert dec.sanitize("decoder.generator.conv_post.bias", b) is b
+
+
+def test_read_checkpoint_decodes_bf16_and_skips_front_end(tmp_path):
+    """The reference's default checkpoint is bf16 (tts/generate.py:366): the loader must decode bfloat16 tensors (the
+    NumPy safetensors loader cannot) and must not touch the out-of-scope front-end keys."""
+    from safetensors.torch import save_file
+    from mlx_audio_b200.tts.utils import read_checkpoint
+    g = torch.Generator().manual_seed(3)
+    w = torch.randn(8, 3, 4, generator=g)
+    ck = {"decoder.generator.conv_post.weight_v": w.to(torch.bfloat16),
+          "decoder.generator.conv_post.bias": torch.randn(8, generator=g),
+          "predictor.F0_proj.bias": torch.ones(1, dtype=torch.float16),
+          "bert.embeddings.word_embeddings.weight": torch.zeros(4, 4, dtype=torch.bfloat16)}
+    save_file(ck, str(tmp_path / "m.safetensors"))
+    got = read_checkpoint([tmp_path / "m.safetensors"])
+    assert sorted(got) == ["decoder.generator.conv_post.bias", "decoder.generator.conv_post.weight_v",
+                           "predictor.F0_proj.bias"]
+    assert all(v.dtype == np.float32 for v in got.values())
+    np.testing.assert_array_equal(got["decoder.generator.conv_post.weight_v"], w.to(torch.bfloat16).float().numpy())

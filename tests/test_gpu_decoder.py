@@ -64,7 +64,7 @@ def test_hnsf_source_and_stft_n20(lib, oracle, synth_weights):
     lb = dev(synth_weights["decoder.generator.m_source.l_linear.bias"].reshape(-1))
     ws = torch.empty(B, 9, 2 * T, device="cuda")
     src = torch.empty(B, 600 * T, device="cuda")
-    L.check(lib.kk_hnsf_source(L.ptr(dev(inp["F0_curve"])), L.ptr(dev(inp["noise"])), 0, L.ptr(lw), L.ptr(lb), L.ptr(ws),
+    L.check(lib.kk_hnsf_source(L.ptr(dev(inp["F0_curve"])), L.ptr(dev(inp["noise"])), 0, None, L.ptr(lw), L.ptr(lb), L.ptr(ws),
                                L.ptr(src), B, 2 * T, 300, L.stream()))
     got = src.cpu().numpy()
     # the phase chain is bit-faithful; sin / tanh / the 9-term dot product differ by a few ulp
@@ -86,7 +86,7 @@ def test_hnsf_source_philox_noise_statistics(lib, synth_weights):
     lw = synth_weights["decoder.generator.m_source.l_linear.weight"].reshape(-1)
     ws = torch.empty(B, 9, 2 * T, device="cuda")
     src = torch.empty(B, 600 * T, device="cuda")
-    L.check(lib.kk_hnsf_source(L.ptr(dev(f0)), None, 1234, L.ptr(dev(lw)), L.ptr(dev(np.zeros(1, np.float32))), L.ptr(ws),
+    L.check(lib.kk_hnsf_source(L.ptr(dev(f0)), None, 1234, None, L.ptr(dev(lw)), L.ptr(dev(np.zeros(1, np.float32))), L.ptr(ws),
                                L.ptr(src), B, 2 * T, 300, L.stream()))
     x = np.arctanh(src.cpu().numpy().astype(np.float64))
     sigma = (0.1 / 3) * np.sqrt((lw.astype(np.float64) ** 2).sum())
@@ -94,7 +94,7 @@ def test_hnsf_source_philox_noise_statistics(lib, synth_weights):
     assert abs(x.std() / sigma - 1) < 0.02
     assert abs(np.corrcoef(x[0, :-1], x[0, 1:])[0, 1]) < 0.02
     src2 = torch.empty_like(src)
-    L.check(lib.kk_hnsf_source(L.ptr(dev(f0)), None, 1235, L.ptr(dev(lw)), L.ptr(dev(np.zeros(1, np.float32))), L.ptr(ws),
+    L.check(lib.kk_hnsf_source(L.ptr(dev(f0)), None, 1235, None, L.ptr(dev(lw)), L.ptr(dev(np.zeros(1, np.float32))), L.ptr(ws),
                                L.ptr(src2), B, 2 * T, 300, L.stream()))
     assert not torch.equal(src, src2)
 
@@ -349,10 +349,23 @@ def test_decoder_default_noise_and_cuda_graph(dec_bf16):
     try:
         g1 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7).clone()
         g2 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7).clone()
+        # the seed is read from device memory: a replay with another seed draws other noise (the reference draws fresh
+        # mx.random.normal per call, istftnet.py:620) and matches the un-captured run with that seed
+        g3 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=8).clone()
+        dec_bf16.seed = 100
+        d1 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"])       # default: a fresh seed per call
+        d2 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"])
     finally:
         dec_bf16.use_cuda_graph = False
     torch.cuda.synchronize()
     assert torch.allclose(g1, a, atol=1e-5) and torch.allclose(g1, g2, atol=1e-5)
+    assert torch.allclose(g3, c, atol=1e-5) and not torch.allclose(g3, g1, atol=1e-3)
+    assert not torch.allclose(d1, d2, atol=1e-3)
+    # results are fresh tensors (the reference returns a new array per call); borrow=True is the zero-copy opt-in
+    assert d1.data_ptr() != d2.data_ptr()
+    b1 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=7, borrow=True)
+    b2 = dec_bf16(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=8, borrow=True)
+    assert b1.data_ptr() == b2.data_ptr()
 
 
 @pytest.mark.gpu
