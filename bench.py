@@ -8,7 +8,17 @@ wall-second at 24 kHz, decoder + iSTFT).
 A step = one pass of ``Decoder.__call__`` over one synthetic batch (config "Kokoro-82M full decoder + iSTFT
 bf16, batch 64 synthetic sentences (~8 s each), 1 B200": B=64, T=320 frames = 8 s each, random-init weights).
 With N>1 ranks (torchrun) every rank decodes its own batch (utterance sharding, weak scaling) and the
-waveforms are gathered to rank 0 with NCCL inside the timed region.  Prints ONE JSON line on rank 0.
+waveforms are gathered to rank 0 with NCCL inside the timed region (on a side stream, overlapping the next
+forward).  Prints ONE JSON line on rank 0.
+
+Besides the headline (BASELINE config 3) the line carries one sub-object per remaining BASELINE config
+(SURVEY 8(d) "Configs -> concrete shapes"), each measured in this same run:
+  ``dsp``      config 2: utils STFT / iSTFT / 80-bin log-mel on 256 x 30 s, ms + fraction of the measured HBM peak
+  ``c4``       config 4: 4096 ragged utterances (T ~ U[240,400]) strong-scaled over the N ranks, gather inside
+  ``c5``       config 5: 10 h of audio streamed from pinned host memory through the decoder
+  ``latency``  config 1's shape on the GPU: B=1 x T=200 forward, bf16 and fp32, with and without CUDA graph
+  ``fp32``     config 3 in the strict fp32 mode
+(``--skip`` drops any of them; a failing sub-benchmark is reported as {"error": ...} and never costs the headline).
 """
 from __future__ import annotations
 
@@ -29,7 +39,7 @@ from mlx_audio_b200 import synth  # noqa: E402
 
 METRIC = "audio_seconds_generated_per_second_24khz_kokoro_decoder"
 UNIT = "audio-s/s"
-TC_NAMES = ("kk_conv1d_bf16_tc", "kk_conv1d_adain_bf16_tc")   # the tcgen05 implicit-GEMM convolutions
+TC_NAMES = ("kk_conv1d_bf16_tc", "kk_conv1d_adain_bf16_tc", "kk_conv1d_tf32_tc")   # the tcgen05 implicit-GEMM convolutions
 
 
 def load_peaks():
@@ -119,10 +129,269 @@ def run_reference(args, rank: int):
     }))
 
 
+# ---------------------------------------------------------------------------------------------- sub-benchmarks
+def _median(xs):
+    return float(np.median(np.asarray(xs, dtype=np.float64)))
+
+
+def bench_dsp(dev, peaks):
+    """BASELINE config 2 / SURVEY 8(d): utils.stft / istft / fused log-mel on 256 signals x 720 000 samples (30 s at
+    24 kHz), n_fft 1024, hop 256, Hann - CUDA events through the C ABI, buffers resident (3.7 GB working set >> L2),
+    against the HBM floor of the algorithmic bytes."""
+    import torch
+    from mlx_audio_b200 import _lib as L
+    from mlx_audio_b200 import utils as U
+    lib = L.load()
+    B, n, n_fft, hop = 256, 720000, 1024, 256
+    frames, bins = 1 + n // hop, n_fft // 2 + 1
+    g = torch.Generator(device=dev).manual_seed(3001)
+    x = 0.1 * torch.randn(B, n, device=dev, generator=g)
+    w = U.hanning(n_fft).contiguous()
+    wp = U._resolve_window("hann", n_fft, periodic=True).contiguous()
+    spec = torch.empty(B, frames, bins, 2, device=dev)
+    sig = torch.empty(B, (frames - 1) * hop, device=dev)
+    fb = U.mel_filters(24000, n_fft, 80).contiguous()
+    mel = torch.empty(B, frames, 80, device=dev)
+    st = L.stream()
+    calls = {
+        "stft": ("kk_stft_f32", lambda: lib.kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(spec), B, n, n_fft, hop, 1, frames, st),
+                 x.numel() * 4 + spec.numel() * 4),
+        "istft": ("kk_istft_f32", lambda: lib.kk_istft_f32(L.ptr(spec), L.ptr(wp), L.ptr(sig), B, frames, n_fft, hop,
+                                                           n_fft // 2, sig.shape[1], st),
+                  spec.numel() * 4 + sig.numel() * 4),
+        "logmel": ("kk_logmel_f32", lambda: lib.kk_logmel_f32(L.ptr(x), L.ptr(w), L.ptr(fb), L.ptr(mel), B, n, n_fft, hop,
+                                                              1, frames, 80, 1, 1, 1e-5, st),
+                   x.numel() * 4 + mel.numel() * 4),
+    }
+    out = {"workload": f"{B} signals x {n} samples (30 s, 24 kHz), n_fft {n_fft}, hop {hop}, Hann; inputs resident; "
+                       "median of 20 launches, CUDA events", "peak_gbs": peaks["hbm"], "peak_source": peaks["source"]}
+    for key, (name, fn, nbytes) in calls.items():
+        for _ in range(3):
+            L.check(fn(), name)
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(20):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            L.check(fn(), name)
+            e1.record()
+            e1.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ms = _median(ts)
+        gbs = nbytes / ms / 1e6
+        out[key] = {"kernel": name, "ms": ms, "algorithmic_gb": nbytes / 1e9, "achieved_gbs": gbs,
+                    "frac": gbs / peaks["hbm"], "audio_seconds_per_second": B * n / 24000 / (ms / 1e3)}
+    # round trip: the reference normalises by sum(w), not sum(w^2) (utils.py:142-150) -> 0.75 x for Hann at hop n/4
+    out["roundtrip_max_abs_err"] = float((sig[:, 2048:-2048] - 0.75 * x[:, 2048:sig.shape[1] - 2048]).abs().max())
+    del x, spec, sig, mel
+    torch.cuda.empty_cache()
+    return out
+
+
+def bench_latency(dev, weights, decs):
+    """Config 1's shape on the GPU (the production caller decodes one chunk per call at batch 1, kokoro.py:135-168):
+    B=1 x T=200 (5 s of audio), per-call latency = CUDA events around one Decoder.__call__ (inputs resident), median
+    of 30, with and without CUDA-graph replay."""
+    import torch
+    B, T = 1, 200
+    inp = synth.synth_decoder_inputs(B, T, seed=1000, with_noise=False)
+    x = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
+    out = {"workload": f"B={B} x T={T} ({T / 40:.1f} s of audio), inputs resident, median of 30 calls"}
+    for mode, dec in decs.items():
+        for graph in (0, 1):
+            dec.use_cuda_graph = bool(graph)
+            for _ in range(4):
+                dec(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)
+            torch.cuda.synchronize()
+            ts, wall = [], []
+            for _ in range(30):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0 = time.perf_counter()
+                e0.record()
+                dec(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)
+                e1.record()
+                e1.synchronize()
+                wall.append((time.perf_counter() - t0) * 1e3)
+                ts.append(e0.elapsed_time(e1))
+            ms = _median(ts)
+            out[f"{mode}_graph{graph}"] = {"ms": ms, "wall_ms": _median(wall), "rtf": ms / 1e3 / (T / 40.0),
+                                           "launches": dec.launches_per_forward(B, T)}
+    return out
+
+
+def bench_fp32(dev, dec32, B, T, world):
+    """Config 3 in the strict fp32 mode (the <= 1e-3 parity mode): device-resident inputs, CUDA events, 3 steps."""
+    import torch
+    inp = synth.synth_decoder_inputs(B, T, seed=1000, with_noise=False)
+    x = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
+    dec32.use_cuda_graph = False
+    for _ in range(2):
+        dec32(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)
+    torch.cuda.synchronize()
+    steps = 3
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        dec32(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)
+    e1.record()
+    e1.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    plan = dec32._plan(B, T)
+    kinds = {}
+    for fn, _ in plan.ops:
+        if fn is not None:
+            kinds[fn.__name__] = kinds.get(fn.__name__, 0) + 1
+    audio_s = B * T * synth.SAMPLES_PER_FRAME / synth.SAMPLE_RATE
+    flops = audio_s * synth.FLOP_PER_AUDIO_SECOND
+    return {"workload": f"batch {B} x T={T}, strict fp32 mode, per GPU", "ms_per_step": ms,
+            "value": audio_s / (ms / 1e3), "unit": UNIT + " per GPU", "tflops": flops / (ms / 1e3) / 1e12,
+            "conv_kernels": {k: v for k, v in kinds.items() if "conv" in k}, "steps": steps}
+
+
+def bench_c4(dev, dec, rank, world, max_batch=64, reps=5, utterances=4096):
+    """BASELINE config 4 / SURVEY 8(d) C4: a ragged corpus of 4096 utterances, T ~ U[240, 400] frames (seed 4001),
+    decoded in batches of <= 64, strong-scaled over the ranks of one box (sharding.assign_*), waveforms gathered on
+    rank 0 over NCCL inside the timed region.  Whole-job audio-s/s from the median of `reps` passes (CUDA events, max
+    over ranks), after one untimed pass that builds the launch plans (its wall time is reported)."""
+    import torch
+    import torch.distributed as dist
+    from mlx_audio_b200 import sharding
+    frames = np.random.default_rng(4001).integers(240, 401, size=utterances).tolist()
+    ragged = hasattr(sharding, "assign_ragged")
+    if ragged:
+        plan = sharding.assign_ragged(frames, world, max_batch)
+    else:
+        plan = sharding.assign_buckets(frames, world, max_batch)
+    mine = plan[rank]
+    inputs = {}
+    for t, ids in mine:
+        g = torch.Generator(device=dev).manual_seed(1000 + ids[0])
+        n = len(ids)
+        inputs[ids[0]] = dict(
+            asr=torch.randn(n, 512, t, device=dev, generator=g),
+            F0_curve=torch.from_numpy(synth.synth_f0(n, 2 * t, seed=1004 + ids[0])).to(dev),
+            N=torch.randn(n, 2 * t, device=dev, generator=g),
+            s=0.5 * torch.randn(n, 128, device=dev, generator=g))
+        if ragged:
+            inputs[ids[0]]["lengths"] = torch.tensor([frames[i] for i in ids], dtype=torch.int32, device=dev)
+    dec.use_cuda_graph = False     # every (B, T) shape is seen once per pass
+    if mine:
+        dec.reserve(max(len(ids) for _, ids in mine), max(t for t, _ in mine))
+
+    def decode_batch(t, ids):
+        x = inputs[ids[0]]
+        if ragged:
+            return dec(x["asr"], x["F0_curve"], x["N"], x["s"], lengths=x["lengths"], borrow=True)
+        return dec(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)
+
+    def run():
+        if ragged:
+            return sharding.decode_sharded(decode_batch, frames, max_batch=max_batch, ragged=True)
+        return sharding.decode_sharded(decode_batch, frames, max_batch=max_batch)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    barrier()
+    t0 = time.perf_counter()
+    out = run()
+    barrier()
+    first = time.perf_counter() - t0
+    if rank == 0:
+        assert len(out) == utterances and all(o.numel() == 600 * f for o, f in zip(out, frames))
+        assert all(bool(torch.isfinite(o).all()) for o in out[:: max(1, utterances // 64)])
+    del out
+    times = []
+    for _ in range(reps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = run()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        times.append(float(ms.item()))
+        del out
+    audio_s = sum(frames) * synth.SAMPLES_PER_FRAME / synth.SAMPLE_RATE
+    med = _median(times)
+    padded = sum(t * len(ids) for r in plan for t, ids in r)
+    res = {"workload": f"{utterances} utterances, T ~ U[240,400] (seed 4001), "
+                       + ("mixed-length batches (per-utterance lengths inside one launch)" if ragged else "same-length batches")
+                       + f" <= {max_batch}, sharded over {world} GPU(s), NCCL gather to rank 0 inside the timed region",
+           "scaling": "strong", "value": audio_s / (med / 1e3), "unit": UNIT, "ms_total_median": med, "ms_all_reps": times,
+           "reps": reps, "audio_seconds": audio_s, "batches_per_rank": [len(r) for r in plan],
+           "mean_batch": utterances / max(1, sum(len(r) for r in plan)), "plans_rank0": len(dec.engine.plans),
+           "padding_overhead": padded / float(sum(frames)) - 1.0, "first_pass_s": first}
+    inputs.clear()
+    torch.cuda.empty_cache()
+    return res
+
+
+def bench_c5(dev, dec, rank, world, hours=10.0, T=320, B=64, distinct=4, reps=3):
+    """BASELINE config 5 / SURVEY 8(d) C5: 10 h of audio = 4 500 chunks of T=320 streamed from pinned HOST buffers
+    through StreamingDecoder (H2D of batch i+1 / D2H of batch i-1 under the forward of batch i), chunks dealt to the
+    ranks in contiguous runs, no collective on the data path.  Wall clock around the whole stream (copies included),
+    max over ranks, median of `reps`."""
+    import torch
+    import torch.distributed as dist
+    from mlx_audio_b200.streaming import StreamingDecoder, split_batches
+    chunk_s = 600 * T / 24000.0
+    chunks = int(round(hours * 3600 / chunk_s))
+    lo, hi = rank * chunks // world, (rank + 1) * chunks // world
+    sizes = split_batches(hi - lo, B)
+    dec.use_cuda_graph = True
+    host = []
+    for d in range(distinct):
+        inp = synth.synth_decoder_inputs(B, T, seed=5000 + 17 * rank + d, with_noise=False)
+        host.append({k: torch.from_numpy(inp[k]).pin_memory() for k in ("asr", "F0_curve", "N", "s")})
+
+    def batches():
+        for i, n in enumerate(sizes):
+            h = host[i % len(host)]
+            yield h if n == B else {k: v[:n] for k, v in h.items()}
+
+    sd = StreamingDecoder(dec, depth=2)
+    for _ in sd.run(({k: v[:n] for k, v in host[0].items()} for n in sorted(set(sizes)) * 2)):   # plans, graphs, slots
+        pass
+    torch.cuda.synchronize()
+    secs, samples = [], 0
+    for _ in range(reps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        samples, peak = 0, 0.0
+        for wav in sd.run(batches()):
+            samples += wav.shape[0] * wav.shape[2]
+            peak = max(peak, float(wav[0, 0, :1024].abs().max()))     # touch the host result
+        torch.cuda.synchronize()
+        tt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        secs.append(float(tt.item()))
+    ss = torch.tensor([samples], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ss, op=dist.ReduceOp.SUM)
+    audio_s = float(ss.item()) / 24000.0
+    med = _median(secs)
+    dec.use_cuda_graph = False
+    return {"workload": f"{audio_s / 3600:.2f} h of audio = {chunks} chunks of T={T}, batches of <= {B} streamed from pinned "
+                        f"host memory (head / tail batches split to shorten pipeline fill and drain), {world} GPU(s)",
+            "value": audio_s / med, "unit": UNIT, "hours_per_second": audio_s / 3600.0 / med, "seconds_median": med,
+            "seconds_all_reps": secs, "batches_per_rank": len(sizes), "batch_sizes_rank0": sizes[:4] + ["..."] + sizes[-4:],
+            "h2d_bytes_rank0": int(sum(sizes) * (512 * T + 4 * T + 128) * 4), "d2h_bytes_rank0": int(sum(sizes) * 600 * T * 4),
+            "timing": "host wall clock around the whole stream, max over ranks", "finite": peak == peak}
+
+
+# ---------------------------------------------------------------------------------------------- this repo's arm
 def run_ours(args, rank: int, world: int, local_rank: int):
     import torch
     import torch.distributed as dist
-    from mlx_audio_b200 import _lib
+    from mlx_audio_b200 import _lib, sharding
     from mlx_audio_b200.tts.models.kokoro import build_decoder
 
     _lib.require_cuda()
@@ -139,12 +408,14 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     inp = synth.synth_decoder_inputs(B, T, seed=1000 + 17 * rank, with_noise=False)
     host = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
     devt = {k: v.to(dev) for k, v in host.items()}
-    gather_list = [torch.empty(B, 1, S, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+    # the path's only exchange: waveform gather to rank 0, issued per step on a side stream so that it
+    # overlaps the next forward (double-buffered staging copy of the decoder's output buffer)
+    gather = sharding.OverlappedGather((B, 1, S), dev) if world > 1 else None
 
     def step(src):
-        y = dec(src["asr"], src["F0_curve"], src["N"], src["s"])
-        if world > 1:  # the path's only exchange: waveform gather to rank 0
-            dist.gather(y, gather_list, dst=0)
+        y = dec(src["asr"], src["F0_curve"], src["N"], src["s"], borrow=True)
+        if gather is not None:
+            gather(y)
         return y
 
     def barrier():
@@ -158,6 +429,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         e0.record()
         for _ in range(steps):
             fn()
+        if gather is not None:
+            gather.wait()                    # the last gather is inside the timed region
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -172,11 +445,17 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         sampler.start()
     ms_total = timed(lambda: step(devt), args.steps)
     clocks = sampler.stop() if rank == 0 else None
+    # A/B of the CUDA-graph replay on the same shape (the other arm of --graph), 5 steps
+    dec.use_cuda_graph = not bool(args.graph)
+    for _ in range(3):
+        step(devt)
+    ms_other = timed(lambda: step(devt), 5) / 5
+    dec.use_cuda_graph = bool(args.graph)
 
     # end to end through the public streaming API: every step copies its inputs from pinned host memory and its
     # waveforms back to pinned host memory; the copies of neighbouring steps overlap the forward (3 streams)
     from mlx_audio_b200.streaming import StreamingDecoder
-    sd = StreamingDecoder(dec, depth=2, post=(lambda y: dist.gather(y, gather_list, dst=0)) if world > 1 else None)
+    sd = StreamingDecoder(dec, depth=2, post=gather)
 
     def e2e_run(steps):
         for wav in sd.run(host for _ in range(steps)):
@@ -187,6 +466,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     out_host = e2e_run(args.steps)           # returns after the last device->host copy has completed
+    if gather is not None:
+        gather.wait()
     e1.record()
     barrier()
     e2e_t = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -198,8 +479,10 @@ def run_ours(args, rank: int, world: int, local_rank: int):
 
     # per-kernel accounting on rank 0: CUDA events around every launch of one forward
     result = None
+    peaks = load_peaks()
     if rank == 0:
         plan = dec._plan(B, T)
+        dec.engine.activate(plan)
         recs = plan.run_timed(_lib.stream())
         recs = plan.run_timed(_lib.stream())
         by = {}
@@ -218,25 +501,27 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                     d = plan.conv_ops[idx]
                     fl = plan.conv_flops(idx)
                     rec.update(C_in=d.C_in, N=d.N, taps=d.taps, dil=d.dil, M=d.M, B=d.B, gflop=fl / 1e9,
-                               tflops=fl / (ms / 1e3) / 1e12)
+                               tflops=fl / (ms / 1e3) / 1e12, res=bool(d.res), out=bool(d.out), out_add=bool(d.out_add))
                 ops.append(rec)
             json.dump(ops, open(args.ops_json, "w"), indent=0)
-        peaks = load_peaks()
         ms_step = ms_total / args.steps
         value = world * audio_s_per_step / (ms_step / 1e3)
         e2e_val = world * audio_s_per_step / (e2e_ms / args.steps / 1e3)
         dom = "kk_conv1d_adain_bf16_tc" if (args.dtype == "bf16" and "kk_conv1d_adain_bf16_tc" in by) else (
-            "kk_conv1d_bf16_tc" if args.dtype == "bf16" else "kk_conv1d_f32")
+            "kk_conv1d_bf16_tc" if args.dtype == "bf16" else max(by, key=lambda k: by[k][1]))
         peak = peaks["bf16_sustained"]
         # dominant kernel: algorithmic FLOPs of its launches / their CUDA-event durations (same stream, per launch)
-        d_fl = sum(plan.conv_flops(i) for n, i, _ in recs if n == dom)
+        d_fl = sum(plan.conv_flops(i) for n, i, _ in recs if n == dom and i in plan.conv_ops)
         d_ms, d_n = by[dom][1], by[dom][0]
         ach = d_fl / (d_ms / 1e3) / 1e12
         traffic, traffic_src = None, None
-        tp = os.path.join(ROOT, "profiles", "r01_fused_traffic.json")
-        if dom == "kk_conv1d_adain_bf16_tc" and os.path.exists(tp):
-            tj = json.load(open(tp))
-            traffic, traffic_src = tj["traffic_bytes_per_launch"], "profiles/r01_fused_traffic.json (ncu dram__bytes_read+write, mean per launch)"
+        for tp in ("r02_fused_traffic.json", "r01_fused_traffic.json"):
+            tp = os.path.join(ROOT, "profiles", tp)
+            if dom == "kk_conv1d_adain_bf16_tc" and os.path.exists(tp):
+                tj = json.load(open(tp))
+                traffic = tj["traffic_bytes_per_launch"]
+                traffic_src = f"profiles/{os.path.basename(tp)} (ncu dram__bytes_read+write, mean per launch)"
+                break
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 "traffic": traffic, "traffic_source": traffic_src,
                 "kernel": {"kk_conv1d_adain_bf16_tc": "conv1d_adain_tc_kernel (fused AdaIN+Snake+conv, tcgen05)",
@@ -250,7 +535,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                                            "launches": sum(by[n][0] for n in TC_NAMES if n in by),
                                            "kernel_ms_per_step": tc_ms, "share_of_step": tc_ms / tot}
         else:
-            roof["note"] = "fp32 CUDA-core mode; fraction still quoted against the bf16 tensor peak"
+            roof["note"] = "fp32 mode; fraction still quoted against the bf16 tensor peak"
         end_to_end_tflops = value * synth.FLOP_PER_AUDIO_SECOND / 1e12 / world
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -258,7 +543,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": f"Kokoro-82M ISTFTNet decoder + iSTFT, random-init weights, batch {B} x T={T} frames "
                                    f"({T / 40:.1f} s each) per GPU, {args.dtype}; utterance-sharded over {world} GPU(s)"
-                                   + (", NCCL waveform gather to rank 0" if world > 1 else ""),
+                                   + (", NCCL waveform gather to rank 0 (side stream, overlapping the next forward)"
+                                      if world > 1 else ""),
                        "batch_per_gpu": B, "frames": T, "audio_seconds_per_step": world * audio_s_per_step,
                        "l2": "per-step activations (~10 GB) far exceed the 126 MB L2; no explicit flush needed",
                        "cuda_graph": bool(args.graph)},
@@ -271,11 +557,45 @@ def run_ours(args, rank: int, world: int, local_rank: int):
             "decoder_tflops_per_gpu": end_to_end_tflops,
             "decoder_frac_of_bf16_peak": end_to_end_tflops / peaks["bf16_sustained"],
             "kernel_ms": {k: {"launches": v[0], "ms": round(v[1], 3)} for k, v in sorted(by.items(), key=lambda kv: -kv[1][1])},
+            "cuda_graph_ab": {"graph" if args.graph else "no_graph": ms_step, "no_graph" if args.graph else "graph": ms_other,
+                              "unit": "ms per step", "note": "same run, the other arm timed over 5 steps"},
             "clocks": clocks,
-            "peak_memory_gb": torch.cuda.max_memory_allocated() / 1e9,
         }
     if world > 1:
         dist.barrier()
+
+    # ---- the other BASELINE configs (every rank takes part; rank 0 reports)
+    skip = set(x for x in args.skip.split(",") if x)
+    subs = {}
+
+    def sub(name, fn):
+        if name in skip:
+            return
+        t0 = time.perf_counter()
+        try:
+            r = fn()
+            r["bench_seconds"] = time.perf_counter() - t0
+        except Exception as e:   # a sub-benchmark never costs the headline
+            import traceback
+            r = {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc()[-800:]}
+            if world > 1:        # ranks may now be out of step: stop issuing collectives
+                skip.update({"c4", "c5", "dsp", "latency", "fp32"})
+        subs[name] = r
+        torch.cuda.synchronize()
+
+    if args.dtype == "bf16":
+        sub("c4", lambda: bench_c4(dev, dec, rank, world))
+        sub("c5", lambda: bench_c5(dev, dec, rank, world))
+        if rank == 0:
+            sub("dsp", lambda: bench_dsp(dev, peaks))
+            if not ({"latency", "fp32"} <= skip):
+                dec32 = build_decoder(weights, dtype="fp32", device=str(dev))
+                sub("latency", lambda: bench_latency(dev, weights, {"bf16": dec, "fp32": dec32}))
+                sub("fp32", lambda: bench_fp32(dev, dec32, B, T, world))
+                del dec32
+    if world > 1:
+        dist.barrier()
+
     # CPU baseline: rank 0, N=1 only, bounded sample of the same workload
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         import torch as _t
@@ -294,6 +614,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
                                   "sample": f"{n_rep} decodes of B=1 x T={Tc} ({Tc / 40:.1f} s audio), float32 oracle "
                                             f"(torch-CPU/NumPy restatement; MLX not installable), {cores} threads"}
     if rank == 0:
+        result.update(subs)
+        result["peak_memory_gb"] = torch.cuda.max_memory_allocated() / 1e9
         print(json.dumps(result))
     if world > 1:
         dist.destroy_process_group()
@@ -308,7 +630,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--frames", type=int, default=320)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
-    ap.add_argument("--graph", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=1, help="replay the forward as a CUDA graph (default on)")
+    ap.add_argument("--skip", default="", help="comma-separated sub-benchmarks to skip: dsp,c4,c5,latency,fp32")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ops-json", default="", help="dump the per-launch event timings of one forward")
     args = ap.parse_args()

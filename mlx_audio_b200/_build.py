@@ -33,16 +33,20 @@ def _stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every CUDA source for sm_100a and link the shared library.  Returns its path."""
-    if not force and not _stale():
+    """Compile every CUDA source for sm_100a and link the shared library.  Returns its path.
+    KK_TUNE=1 / KK_FUSED_DBG=1 in the environment add -DKK_TUNE (experiment knobs read from the environment) /
+    -DKK_FUSED_DBG (per-barrier wait counters in the fused kernel) - lab builds, never the default."""
+    extra = [f"-D{k}" for k in ("KK_TUNE", "KK_FUSED_DBG") if os.environ.get(k) == "1"]
+    if not force and not extra and not _stale():
         return LIB_PATH
     nvcc = _nvcc()
-    objdir = os.path.join(PKG_DIR, "build")
+    lib_path = LIB_PATH if not extra else os.path.join(PKG_DIR, "libkokoro_b200_lab.so")   # lab builds never shadow the product
+    objdir = os.path.join(PKG_DIR, "build" if not extra else "build_lab")
     os.makedirs(objdir, exist_ok=True)
     procs = []
     for src in SOURCES:
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             print(" ".join(cmd), file=sys.stderr)
         procs.append((src, obj, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -54,14 +58,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
         if verbose and out.strip():
             print(out, file=sys.stderr)
         objs.append(obj)
-    tmp = LIB_PATH + ".tmp"
+    tmp = lib_path + ".tmp"
     cmd = [nvcc, "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-lcudart_static",
            "-Xcompiler", "-fPIC"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}")
-    os.replace(tmp, LIB_PATH)
-    return LIB_PATH
+    os.replace(tmp, lib_path)
+    return lib_path
 
 
 if __name__ == "__main__":

@@ -11,7 +11,8 @@ from typing import Optional
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libkokoro_b200.so")
+# KK_LIB selects another build of the same ABI (experiments: the -DKK_TUNE / -DKK_FUSED_DBG "lab" library)
+LIB_PATH = os.environ.get("KK_LIB") or os.path.join(_PKG, "libkokoro_b200.so")
 
 KK_ACT_NONE, KK_ACT_LEAKY, KK_ACT_SNAKE, KK_ACT_SNAKE_FAST = 0, 1, 2, 3
 KK_ERR_INVALID_ARG, KK_ERR_UNSUPPORTED, KK_ERR_CUDA = -1, -2, -3

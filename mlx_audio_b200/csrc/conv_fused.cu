@@ -868,6 +868,18 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, const void* base, int rank
               const cuuint64_t* strides, const cuuint32_t* box, CUtensorMapSwizzle swz);   // conv_tc.cu
 int num_sms();                                                                             // conv_tc.cu
 
+// Experiment knob: the environment variable `name` in -DKK_TUNE builds (KK_TUNE=1 python -m mlx_audio_b200._build), the
+// default otherwise - the product library reads no environment.
+static inline int fv_tune_int(const char* name, int dflt) {
+#ifdef KK_TUNE
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+#else
+  (void)name;
+  return dflt;
+#endif
+}
+
 template <int MT, int BN, int CB, bool SWAP, int CL = 1>
 static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc* d, cudaStream_t st) {
   using Cfg = FvCfg<MT, BN, CB>;
@@ -920,8 +932,9 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
   int grid = (int)(total < num_sms() ? total : num_sms());
-  // experiment knobs: bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring, bit 2 = no residual prefetch
-  static const int flags = getenv("KK_L2PF") ? atoi(getenv("KK_L2PF")) : 5;
+  // bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring, bit 2 = no residual prefetch (on).  The
+  // environment is read in -DKK_TUNE builds only (experiments); the product build has no knobs.
+  static const int flags = fv_tune_int("KK_L2PF", 5);
   if constexpr (CL > 1) {
     grid -= grid % CL;                        // whole clusters (callers fall back to CL = 1 for tiny problems)
     cudaLaunchConfig_t cfg = {};
@@ -995,11 +1008,11 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
     return KK_ERR_UNSUPPORTED;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  static const bool swap128 = !(getenv("KK_FUSED_SWAP") && atoi(getenv("KK_FUSED_SWAP")) == 0);   // A/B knob
+  static const bool swap128 = kk::fv_tune_int("KK_FUSED_SWAP", 1) != 0;
   // cluster pairs (shared weight stream): KK_FUSED_CL bit 0 = 256-channel configuration, bit 1 = 128.  Default
   // off: measured neutral to slightly negative (C=256 k=7: 5.05 -> 5.20 ms per 12 launches), i.e. the weight stalls
   // are a latency / ring-depth effect, not L2 bandwidth.  Kept as an A/B knob.
-  static const int cl_mask = getenv("KK_FUSED_CL") ? atoi(getenv("KK_FUSED_CL")) : 0;
+  static const int cl_mask = kk::fv_tune_int("KK_FUSED_CL", 0);
   const long long tiles128 = (long long)kk::cdiv(d->M, 256) * d->B, tiles256 = (long long)kk::cdiv(d->M, 128) * d->B;
   if (d->C_in == 128 && d->N == 128) {
     if (!swap128) return kk::launch_fused<2, 128, 2, false>(a, w, d, st);

@@ -2,11 +2,11 @@
 //   TMA (cp.async.bulk.tensor, 128B swizzle) -> shared-memory ring -> tcgen05.mma (bf16 x bf16 -> fp32 in
 //   tensor memory) -> tcgen05.ld epilogue (bias, residuals, scale, instance-norm partial sums, optional
 //   activated bf16 copy).
-// One CTA computes a 128 (positions) x BN (output channels) tile of one utterance.  The K loop walks
-// (tap, 64-channel block): the A tile of a tap is the SAME activation tensor shifted by tap*dil - pad rows;
-// TMA's out-of-bounds zero fill provides the per-utterance conv zero padding for free (tensor map dims are
-// (C, L, B), so a box never bleeds into the neighbouring utterance).
-// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-5 = epilogue
+// A tile = 128 (positions) x BN (output channels) of one utterance.  The K loop walks (tap, 64-channel block): the A
+// tile of a tap is the SAME activation tensor shifted by tap*dil - pad rows; TMA's out-of-bounds zero fill provides
+// the per-utterance conv zero padding for free (tensor map dims are (C, L, B), so a box never bleeds into the
+// neighbouring utterance).
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-9 = epilogue
 // (warp w owns TMEM lanes 32*(w%4)..+31); warp 2 also allocates / frees tensor memory.
 #include "tc_epilogue.cuh"
 #include <stdlib.h>
@@ -15,136 +15,11 @@ namespace kk {
 
 constexpr int TC_BM = 128;       // UMMA M
 constexpr int TC_BK = 64;        // bf16 elements per K block = one 128-byte swizzle row
-constexpr int TC_THREADS = 192;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;  // 16 KB
 
-template <int BN>
-struct TcCfg {
-  static constexpr int B_BYTES = BN * TC_BK * 2;
-  static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
-  static constexpr int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 3 : 4);
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 8 * BN * 4 /*stats: 4 warps x (sum, sumsq) x BN*/;
-};
-
-
-template <int BN>
-__global__ void __launch_bounds__(TC_THREADS)
-conv1d_bf16_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      const kk_conv_desc d) {
-  using Cfg = TcCfg<BN>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* tail = smem + Cfg::STAGES * Cfg::STAGE_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
-  uint64_t* empty_bar = full_bar + Cfg::STAGES;
-  uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-  float* s_stats = reinterpret_cast<float*>(tail + 256);  // [4 warps][2][BN], no atomics: deterministic
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * TC_BM;
-  const int n0 = blockIdx.y * BN;
-  const int b = blockIdx.z;
-  const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
-  const int num_kb = d.taps * cblocks;
-
-  if (warp == 0 && lane == 0) {
-    ptx::prefetch_tmap(&tmA);
-    ptx::prefetch_tmap(&tmB);
-    for (int s = 0; s < Cfg::STAGES; ++s) {
-      ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
-    }
-    ptx::mbar_init(tmem_full_bar, 1);
-    ptx::fence_barrier_init();
-  }
-  if (warp == 2) ptx::tmem_alloc<BN>(tmem_slot);
-  ptx::tc_fence_before();
-  __syncthreads();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::STAGES;
-        const uint32_t ph = (kb / Cfg::STAGES) & 1;
-        ptx::mbar_wait(&empty_bar[s], ph ^ 1);
-        const int t = kb / cblocks, cb = kb - t * cblocks;
-        uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
-        uint8_t* sb = sa + TC_A_BYTES;
-        ptx::mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
-        ptx::tma_load_3d(sa, &tmA, &full_bar[s], cb * TC_BK, m0 + t * d.dil - d.pad_left, b);
-        ptx::tma_load_2d(sb, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, BN);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % Cfg::STAGES;
-        const uint32_t ph = (kb / Cfg::STAGES) & 1;
-        ptx::mbar_wait(&full_bar[s], ph);
-        ptx::tc_fence_after();
-        const uint32_t sa = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES);
-        const uint32_t sb = sa + TC_A_BYTES;
-#pragma unroll
-        for (int k = 0; k < TC_BK / 16; ++k) {
-          // K-major, 128B swizzle: rows are 128 B apart, 8-row atoms 1024 B apart; +32 B per 16-element K step
-          const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-          const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-          ptx::umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
-        }
-        ptx::umma_commit(&empty_bar[s]);  // frees the smem slot when these MMAs have read it
-      }
-      ptx::umma_commit(tmem_full_bar);    // accumulator complete
-    }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int lg = warp & 3;                 // TMEM lane group this warp may access
-    const bool do_stats = d.stats != nullptr;
-    // every MMA has completed (tmem_full), so the operand ring is idle: reuse it as epilogue staging
-    float* stage_w = reinterpret_cast<float*>(smem) + lg * 1024;
-    float4 tres[8];
-    epi_prefetch_chunk(d, b, m0, n0, 0, lg, lane, tres);   // residual loads fly while the accumulator completes
-    ptx::mbar_wait(tmem_full_bar, 0);
-    ptx::tc_fence_after();
-#pragma unroll 1
-    for (int ch = 0; ch < BN / 32; ++ch) {
-      float cs = 0.f, cq = 0.f;
-      epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base, stage_w, do_stats, cs, cq, tres, ch + 1 < BN / 32, b, m0,
-                         n0, ch + 1);
-      if (do_stats) { s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = cs; s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = cq; }
-    }
-    if (do_stats) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps
-      for (int i = threadIdx.x - 64; i < BN; i += 128) {
-        int n = n0 + i;
-        if (n < d.N) {
-          int c = d.up > 1 ? n % d.C_out : n;
-          // fixed-order combine of the four warps, then one double atomic per (tile, column)
-          float ts = (s_stats[0 * BN + i] + s_stats[2 * BN + i]) + (s_stats[4 * BN + i] + s_stats[6 * BN + i]);
-          float tq = (s_stats[1 * BN + i] + s_stats[3 * BN + i]) + (s_stats[5 * BN + i] + s_stats[7 * BN + i]);
-          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2, (double)ts);
-          atomicAdd(d.stats + ((size_t)b * d.C_out + c) * 2 + 1, (double)tq);
-        }
-      }
-    }
-  }
-  ptx::tc_fence_before();
-  __syncthreads();
-  if (warp == 2) ptx::tmem_dealloc<BN>(tmem_base);
-}
-
-}  // namespace kk
-
-// ---------------------------------------------------------------------------------------------------------
-// Persistent variant: one CTA per SM loops over output tiles.  Tensor memory holds TWO accumulators so the
+// Persistent kernel: one CTA per SM loops over output tiles.  Tensor memory holds TWO accumulators so the
 // epilogue of tile i (8 warps) overlaps the TMA/MMA main loop of tile i+1; barrier set-up, TMEM allocation and
 // tensor-map prefetch are paid once per SM instead of once per tile.
-namespace kk {
 
 constexpr int TP_EPI_WARPS = 8;
 constexpr int TP_THREADS = 64 + TP_EPI_WARPS * 32;  // 320
@@ -394,35 +269,6 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const cuuint64_t*
   return make_tmap(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, base, rank, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
-template <int BN>
-static int launch_tc(const void* x, const void* w, const kk_conv_desc* d, cudaStream_t st) {
-  using Cfg = TcCfg<BN>;
-  CUtensorMap tmA, tmB;
-  {
-    cuuint64_t dims[3] = {(cuuint64_t)d->C_in, (cuuint64_t)d->L_in, (cuuint64_t)d->B};
-    cuuint64_t strides[2] = {(cuuint64_t)d->x_pitch * 2, (cuuint64_t)d->L_in * d->x_pitch * 2};
-    cuuint32_t box[3] = {TC_BK, TC_BM, 1};
-    int rc = make_tmap_bf16(&tmA, x, 3, dims, strides, box);
-    if (rc) return rc;
-  }
-  {
-    cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
-    cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * 2};
-    cuuint32_t box[2] = {TC_BK, BN};
-    int rc = make_tmap_bf16(&tmB, w, 2, dims, strides, box);
-    if (rc) return rc;
-  }
-  static bool attr_set = false;
-  if (!attr_set) {
-    KK_CUDA(cudaFuncSetAttribute(conv1d_bf16_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
-  }
-  dim3 grid(cdiv(d->M, TC_BM), cdiv(d->N, BN), d->B);
-  conv1d_bf16_tc_kernel<BN><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, *d);
-  KK_LAUNCH_CHECK("conv1d_bf16_tc_kernel");
-  return KK_OK;
-}
-
 int num_sms() {
   static int n = 0;
   if (!n) {
@@ -463,8 +309,7 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
   const int grid = (int)(total < num_sms() ? total : num_sms());
   // direct epilogue (tc_epilogue.cuh): every 32-column chunk full, 16-byte aligned rows, one residual at most
   auto al16 = [](const void* p, long long pitch_bytes) { return (((uintptr_t)p | (uintptr_t)pitch_bytes) & 15) == 0; };
-  static const bool allow_direct = !(getenv("KK_TC_DIRECT") && atoi(getenv("KK_TC_DIRECT")) == 0);   // A/B knob
-  const int direct = allow_direct && d->N % 32 == 0 && (d->up == 1 || d->C_out % 32 == 0) && !d->res2 &&
+  const int direct = d->N % 32 == 0 && (d->up == 1 || d->C_out % 32 == 0) && !d->res2 &&
                      (!d->out || al16(d->out, (long long)d->out_pitch * 4)) &&
                      (!d->res || al16(d->res, (long long)d->res_pitch * 4)) && (!d->bias || al16(d->bias, 0)) &&
                      (!d->out_act || (d->act_is_bf16 && al16(d->out_act, (long long)d->act_pitch * 2)));
@@ -531,25 +376,13 @@ extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_des
   KK_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kk_conv1d_bf16_tc: operands must be 16-byte aligned");
   KK_CHECK_ARG(d->up == 1 || d->C_out % 32 == 0, "kk_conv1d_bf16_tc: polyphase needs C_out %% 32 == 0");
   KK_CHECK_ARG(d->B <= 65535, "kk_conv1d_bf16_tc: batch too large");
-  // bit 12 of block_n selects the one-tile-per-CTA kernel (kept for A/B comparison); default is persistent
-  const bool legacy = (block_n & 0x1000) != 0;
-  block_n &= 0xfff;
   if (block_n == 0) block_n = d->N > 64 ? 128 : (d->N > 32 ? 64 : 32);
   cudaStream_t st = (cudaStream_t)stream;
-  if (!legacy) {
-    switch (block_n) {
-      case 32: return kk::launch_tc_persist<32>(x, w, d, st);
-      case 64: return kk::launch_tc_persist<64>(x, w, d, st);
-      case 128: return kk::launch_tc_persist<128>(x, w, d, st);
-      case 256: return kk::launch_tc_persist<256>(x, w, d, st);
-      default: kk::set_error("kk_conv1d_bf16_tc: block_n %d not in {32,64,128,256}", block_n); return KK_ERR_INVALID_ARG;
-    }
-  }
   switch (block_n) {
-    case 32: return kk::launch_tc<32>(x, w, d, st);
-    case 64: return kk::launch_tc<64>(x, w, d, st);
-    case 128: return kk::launch_tc<128>(x, w, d, st);
-    case 256: return kk::launch_tc<256>(x, w, d, st);
+    case 32: return kk::launch_tc_persist<32>(x, w, d, st);
+    case 64: return kk::launch_tc_persist<64>(x, w, d, st);
+    case 128: return kk::launch_tc_persist<128>(x, w, d, st);
+    case 256: return kk::launch_tc_persist<256>(x, w, d, st);
     default: kk::set_error("kk_conv1d_bf16_tc: block_n %d not in {32,64,128,256}", block_n); return KK_ERR_INVALID_ARG;
   }
 }

@@ -7,11 +7,22 @@ Host logic only: every byte of audio is computed by ``Decoder.__call__``.
 """
 from __future__ import annotations
 
+import math
 from typing import Callable, Dict, Iterable, Iterator, List, Optional
 
 import torch
 
 _KEYS = ("asr", "F0_curve", "N", "s")
+
+
+def split_batches(n: int, max_batch: int) -> List[int]:
+    """Batch sizes for ``n`` equal-length chunks: full batches of ``max_batch`` with the remainder FIRST, so that the
+    pipeline's un-overlapped head (the first host->device copy + the first forward's ramp) is the short batch and every
+    later copy hides under a full forward."""
+    if n <= 0:
+        return []
+    full, rem = divmod(n, max_batch)
+    return ([rem] if rem else []) + [max_batch] * full
 
 
 class StreamingDecoder:
@@ -29,12 +40,22 @@ class StreamingDecoder:
         self.slots: List[Dict[str, object]] = [dict(shape=None) for _ in range(depth)]
 
     def _slot(self, k: int, shapes) -> Dict[str, object]:
+        """Staging buffers of slot ``k`` viewed at ``shapes``.  The backing stores only ever grow (pinned-host and device
+        allocations cost milliseconds: a stream whose batch shapes vary must not re-allocate per batch)."""
         sl = self.slots[k]
         if sl["shape"] != shapes:
             B, T = shapes[0][0], shapes[0][2]
-            sl["in"] = {n: torch.empty(sh, dtype=torch.float32, device=self.dev) for n, sh in zip(_KEYS, shapes)}
-            sl["out_dev"] = torch.empty(B, 1, 600 * T, dtype=torch.float32, device=self.dev)
-            sl["out_host"] = torch.empty(B, 1, 600 * T, dtype=torch.float32).pin_memory()
+            need = {n: math.prod(sh) for n, sh in zip(_KEYS, shapes)}
+            need["out"] = B * 600 * T
+            store = sl.setdefault("store", {})
+            for n, cnt in need.items():
+                if n not in store or store[n].numel() < cnt:
+                    store[n] = torch.empty(cnt, dtype=torch.float32, device=self.dev)
+                    if n == "out":
+                        store["out_host"] = torch.empty(cnt, dtype=torch.float32).pin_memory()
+            sl["in"] = {n: store[n][:need[n]].view(sh) for n, sh in zip(_KEYS, shapes)}
+            sl["out_dev"] = store["out"][:need["out"]].view(B, 1, 600 * T)
+            sl["out_host"] = store["out_host"][:need["out"]].view(B, 1, 600 * T)
             sl["shape"] = shapes
         return sl
 

@@ -15,12 +15,16 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
 
 from .... import _lib as L
 from ...._lib import AdainIn, ConvDesc
+
+
+_NVTX = os.environ.get("KK_NVTX", "0") == "1"   # NVTX range per decoder stage (profiling aid, off by default)
 
 
 def _ceil(a: int, m: int) -> int:
@@ -83,11 +87,25 @@ class Plan:
         self.ops.append((fn, args))
         self.n_launches += launches
 
+    def stage(self, name: str):
+        """Stage boundary (front / source / stage0 / stage1 / post): an NVTX range when KK_NVTX=1 - the counterpart of the
+        BenchmarkTimer spans of the reference's Swift port (Swift-TTS/Kokoro/Decoder.swift:74-105)."""
+        self.ops.append((None, ("@stage", name)))
+
     def run(self, stream: int):
+        nvtx = torch.cuda.nvtx if _NVTX else None
+        open_range = False
         for a in self.arenas:
             a.zero_()
         for fn, args in self.ops:
-            if fn is None:  # debug tap
+            if fn is None:  # stage marker / debug tap
+                if args[0] == "@stage":
+                    if nvtx is not None:
+                        if open_range:
+                            nvtx.range_pop()
+                        nvtx.range_push("kokoro." + args[1])
+                        open_range = True
+                    continue
                 if self.capture:
                     t, view = self.taps[args[0]]
                     self.captured[args[0]] = (view(t) if view else t).detach().float().clone()
@@ -95,6 +113,8 @@ class Plan:
             rc = fn(*args, stream)
             if rc != 0:
                 L.check(rc, getattr(fn, "__name__", "kernel"))
+        if open_range:
+            nvtx.range_pop()
 
     def run_timed(self, stream: int):
         """One forward with a CUDA-event pair around every C-ABI call (on the launching stream).
@@ -129,18 +149,23 @@ class DecoderEngine:
     "fp32" (CUDA-core float32 convolutions, the strict parity mode).
     """
 
-    def __init__(self, weights: Dict[str, torch.Tensor], cfg: dict, mode: str = "bf16"):
+    def __init__(self, weights: Dict[str, torch.Tensor], cfg: dict, mode: str = "bf16", fused: bool = True,
+                 res16: int = 1):
+        """``fused`` / ``res16`` select engine arms of the bf16 mode (defaults = the measured-fastest; every arm has a
+        parity test, tests/test_gpu_decoder.py::test_decoder_bf16_engine_arms): fused = AdaIN + Snake inside the
+        convolution's operand path (False: separate elementwise kernels, the layout the fp32 mode uses); res16 = bf16
+        residual stream inside AdaINResBlock1 (0 off, 1 the 128-channel stage, 2 both stages)."""
         if mode not in ("bf16", "fp32"):
             raise ValueError(f"mode must be 'bf16' or 'fp32', got {mode!r}")
+        if res16 not in (0, 1, 2):
+            raise ValueError(f"res16 must be 0, 1 or 2, got {res16!r}")
         L.require_cuda()
         self.lib = L.load()
         self.cfg = cfg
         self.mode = mode
         self.tc = mode == "bf16"
-        import os as _os
-        self.fused = self.tc and _os.environ.get("KK_FUSED", "1") != "0"   # A/B knob: 0 = separate AdaIN kernels
-        # bf16 residual stream inside AdaINResBlock1: 0 = off, 1 = the 128-channel stage, 2 = both stages
-        self.res16 = int(_os.environ.get("KK_RES16", "1")) if self.fused else 0
+        self.fused = self.tc and bool(fused)
+        self.res16 = int(res16) if self.fused else 0
         if self.tc and not self.lib.kk_device_is_sm100():
             raise L.KokoroB200Error("bf16 tensor-core mode needs an sm_100 (B200) device")
         self.dev = next(iter(weights.values())).device
@@ -348,19 +373,10 @@ class DecoderEngine:
         """N tile of the tensor-core kernel (0 = library default: 128 for N > 64).  Measured per layer at B=64 x T=320
         (experiments/ab_bn_ops.sh): a 256-wide tile is 20-25 % faster on the front convolutions (N = 1024: 210 -> 162 us),
         on decode.3's 1090 -> 512 convolutions and on noise_convs[0] (N = 256), slower on the 512 -> 512 conv2 of
-        decode.3 (fewer, heavier epilogue tiles: 4.3 waves of 148 CTAs) and on the polyphase ups.1 (N = 768).
-        Experiment knobs: KK_TC_BN=<n> forces the tile, KK_TC_LEGACY=1 selects the one-tile-per-CTA kernel."""
-        import os
-        bn = 0
-        env = os.environ.get("KK_TC_BN")
-        if env:
-            if pc.N >= int(env):
-                bn = int(env)
-        elif pc.N % 256 == 0 and (pc.N >= 1024 or pc.N == 256 or (pc.N == 512 and pc.C_in > 512)):
-            bn = 256
-        if os.environ.get("KK_TC_LEGACY") == "1":
-            bn |= 0x1000
-        return bn
+        decode.3 (fewer, heavier epilogue tiles: 4.3 waves of 148 CTAs) and on the polyphase ups.1 (N = 768)."""
+        if pc.N % 256 == 0 and (pc.N >= 1024 or pc.N == 256 or (pc.N == 512 and pc.C_in > 512)):
+            return 256
+        return 0
 
     def _conv_fused(self, plan: Plan, pc: PreparedConv, x: torch.Tensor, x_pitch: int, stats_addr: Optional[int],
                     ada_prefix: Optional[str], act: int, slope: float, alpha: Optional[torch.Tensor], h_all, B: int,
@@ -435,7 +451,7 @@ class DecoderEngine:
             ybf = plan.buffers.get(f"ybf.{C_}")
             if ybf is None:
                 ybf = self._buf(plan, f"ybf.{C_}", (B, L_, C_), torch.bfloat16)
-            # bf16 residual stream (KK_RES16, default on): the running x is written by conv2 as bf16 only (statistics
+            # bf16 residual stream (res16, default: the 128-channel stage): the running x is written by conv2 as bf16 only (statistics
             # still from the fp32 accumulators) and read back as bf16 by the next conv1 (input) and conv2 (residual);
             # x16_in = bf16 copy of x_in from its producer.  The block's output and the MRF sum stay fp32.
             s16 = x16_in is not None
@@ -553,6 +569,7 @@ class DecoderEngine:
         noise = self._buf(plan, "in.noise", (B, S, 9)) if False else None
         plan.noise_buf = noise
         h_all = self._buf(plan, "h_all", (B, self.ada_R))
+        plan.stage("front")
         plan.add(lib.kk_style_affine, self._addr(s), self._addr(self.ada_W), self._addr(self.ada_b), self._addr(h_all),
                  B, self.ada_R, cfg["style_dim"])
         # ---- front: x = cat[asr, F0, N] (:951); xcat = cat[x(1024), asr_res(64), F0, N] (:957)
@@ -581,6 +598,7 @@ class DecoderEngine:
                              name="decode3")
         self._tap(plan, "decode3", x3, lambda t: t.transpose(1, 2))
         # ---- harmonic source + STFT(20,5) (:770-775)
+        plan.stage("source")
         phase_ws = self._buf(plan, "phase_ws", (B, 9, T2))
         har_source = self._buf(plan, "har_source", (B, S))
         har = self._buf(plan, "har", (B, L3, 24))
@@ -611,6 +629,7 @@ class DecoderEngine:
         L_prev, C_prev = T2, C0
         for i in range(2):
             Li, Ci = Ls[i], Cs[i]
+            plan.stage(f"stage{i}")
             ap = self._act_pitch(Ci)
             nconv = self.convs[f"{g}.noise_convs.{i}"]
             xs = self._buf(plan, f"g{i}.xs", (B, Li, Ci))
@@ -676,6 +695,7 @@ class DecoderEngine:
             self._tap(plan, f"mrf{i}", acc, lambda t: t.transpose(1, 2))
             a_prev, L_prev, C_prev = a_next, Li, Ci
         # ---- conv_post + iSTFT head (:798-806)
+        plan.stage("post")
         ypost = self._buf(plan, "ypost", (B, L3, 24))
         pc_post = self.convs[f"{g}.conv_post"]
         if self.fused and Cs[1] == 128 and pc_post.N <= 32 and self._act_pitch(Cs[1]) == 128:

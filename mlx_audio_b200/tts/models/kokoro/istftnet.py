@@ -44,7 +44,7 @@ class Decoder:
 
     def __init__(self, dim_in, style_dim, dim_out, resblock_kernel_sizes, upsample_rates, upsample_initial_channel,
                  resblock_dilation_sizes, upsample_kernel_sizes, gen_istft_n_fft, gen_istft_hop_size,
-                 dtype: str = "bf16", device: Optional[str] = None):
+                 dtype: str = "bf16", device: Optional[str] = None, engine_options: Optional[dict] = None):
         self.cfg = dict(dim_in=dim_in, style_dim=style_dim, dim_out=dim_out,
                         resblock_kernel_sizes=list(resblock_kernel_sizes), upsample_rates=list(upsample_rates),
                         upsample_initial_channel=upsample_initial_channel,
@@ -61,6 +61,7 @@ class Decoder:
         self._weights: Dict[str, torch.Tensor] = {}
         self._engine: Optional[DecoderEngine] = None
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
+        self._engine_options = dict(engine_options or {})   # DecoderEngine arms: fused=, res16= (see engine.py)
         self.use_cuda_graph = False
         self.seed = 0
 
@@ -107,7 +108,7 @@ class Decoder:
         if self._engine is None:
             if len(self._weights) != len(self._specs):
                 raise L.KokoroB200Error("Decoder weights are not loaded (call load_weights first)")
-            self._engine = DecoderEngine(self._weights, self.cfg, self.mode)
+            self._engine = DecoderEngine(self._weights, self.cfg, self.mode, **self._engine_options)
         return self._engine
 
     # ------------------------------------------------------------------ forward
@@ -203,9 +204,10 @@ class Decoder:
         return self._plan(B, T).n_launches
 
 
-def build_decoder(weights=None, cfg: Optional[dict] = None, dtype: str = "bf16", device: Optional[str] = None) -> Decoder:
+def build_decoder(weights=None, cfg: Optional[dict] = None, dtype: str = "bf16", device: Optional[str] = None,
+                  engine_options: Optional[dict] = None) -> Decoder:
     """Convenience constructor: Decoder(**cfg) + load_weights."""
-    dec = Decoder(**(cfg or KOKORO_DECODER), dtype=dtype, device=device)
+    dec = Decoder(**(cfg or KOKORO_DECODER), dtype=dtype, device=device, engine_options=engine_options)
     if weights is not None:
         dec.load_weights(weights)
     return dec
