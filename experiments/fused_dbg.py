@@ -1,11 +1,12 @@
-"""Debug driver: where does conv1d_adain_tc_kernel wait?  Runs single fused convs at bench size on a
--DKK_FUSED_DBG build (experiments/build_dbg.sh) and prints per-role barrier wait time as a share of kernel time."""
+"""Debug driver: where does conv1d_adain_tc_kernel wait?  Runs single fused convs at bench size on the lab build
+(`KK_TUNE=1 KK_FUSED_DBG=1 python -m mlx_audio_b200._build` -> mlx_audio_b200/libkokoro_b200_lab.so) and prints per-role
+barrier wait time as a share of kernel time."""
 import ctypes as C, os, sys
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from mlx_audio_b200 import _lib as L
-L.LIB_PATH = os.path.join(ROOT, "experiments", "libkokoro_b200_dbg.so")
+L.LIB_PATH = os.path.join(ROOT, "mlx_audio_b200", "libkokoro_b200_lab.so")
 from mlx_audio_b200._lib import AdainIn, ConvDesc
 lib = L.load()
 lib.kk_debug_fused_buffer.argtypes = [C.c_void_p]; lib.kk_debug_fused_buffer.restype = C.c_int

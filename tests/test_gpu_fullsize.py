@@ -7,6 +7,9 @@ import torch
 from mlx_audio_b200 import _lib as L
 from mlx_audio_b200 import synth, utils
 from mlx_audio_b200.tts.models.kokoro import build_decoder
+from oracle import dsp
+from oracle.istftnet import DecoderOracle
+from parity_gates import BF16_MAX_ABS, BF16_MEL_L1, BF16_REL_L2, record
 
 pytestmark = pytest.mark.gpu
 
@@ -80,3 +83,55 @@ def test_config3_decoder_batch_independence_determinism_and_range():
     # measured 0.0 (bit-identical) since the statistics kernels keep fp64 partial sums; the bound leaves room for one
     # fp64-atomic reordering flipping a bf16 rounding somewhere in the 50 layers
     assert rel < 1e-3, rel
+
+
+def test_config2_two_signals_vs_oracle(signals):
+    """Two of the 256 config-2 signals through the CPU oracle (oracle.dsp restates utils.py:52-158): pins the long-run
+    variants of the kernels (the register-table STFT only switches on for blocks of >= 64 frames, i.e. at this size)."""
+    x = signals
+    S = utils.stft(x, n_fft=1024, hop_length=256)                        # (256, 2813, 513)
+    y = utils.istft(S.transpose(1, 2), hop_length=256, win_length=1024)
+    mel = utils.log_mel_spectrogram(x, n_fft=1024, hop_length=256, n_mels=80)
+    for b in (3, 200):
+        xb = x[b].cpu().numpy()
+        ref = dsp.stft(xb, n_fft=1024, hop_length=256)                   # (frames, bins) complex64
+        got = S[b].cpu().numpy()
+        scale = np.abs(ref).max()
+        e_stft = np.abs(got - ref).max() / scale
+        yref = dsp.istft(ref.T, hop_length=256, win_length=1024)
+        e_istft = np.abs(y[b].cpu().numpy() - yref).max()
+        fb = utils.mel_filters(24000, 1024, 80).cpu().numpy()
+        mref = np.log(np.maximum(np.abs(ref) @ fb.T, 1e-5))
+        dm = np.abs(mel[b].cpu().numpy() - mref)
+        record(f"config2 signal {b}", stft_rel=e_stft, istft_abs=e_istft, logmel_mean=dm.mean(), logmel_max=dm.max())
+        assert e_stft < 1e-4 and e_istft < 1e-4, (e_stft, e_istft)
+        assert dm.mean() < 1e-4 and dm.max() < 2e-3, (dm.mean(), dm.max())
+    del S, y, mel
+
+
+def test_config3_batch_vs_oracle():
+    """The real bench batch (B=64 x T=320, bf16, explicit noise) against the CPU oracle on utterances 0, 17 and 63
+    (~0.5 s of CPU each): closes the gap between the small-shape oracle tests and the full-size self-consistency test."""
+    if not L.load().kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    B, T = 64, 320
+    w = synth.synth_decoder_weights(seed=2000)
+    dec = build_decoder(w, dtype="bf16")
+    inp = synth.synth_decoder_inputs(B, T, seed=1000, with_noise=False)
+    g = torch.Generator(device="cuda").manual_seed(77)
+    noise = torch.randn(B, 600 * T, 9, device="cuda", generator=g)
+    y = dec(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], noise=noise)
+    torch.cuda.synchronize()
+    orc = DecoderOracle(w)
+    for b in (0, 17, 63):
+        ref = orc(inp["asr"][b:b + 1], inp["F0_curve"][b:b + 1], inp["N"][b:b + 1], inp["s"][b:b + 1],
+                  noise[b:b + 1].cpu().numpy(), keep_taps=True)
+        ph = orc.taps["har"][:, 11:]
+        if (np.abs(np.abs(ph) - np.pi) < 1e-5)[:, 1:10].any():      # atan2 branch cut (DESIGN.md section 2): not comparable
+            continue
+        got = y[b:b + 1].cpu().numpy()
+        rel = np.linalg.norm(got - ref) / np.linalg.norm(ref)
+        mel = np.abs(dsp.log_mel_vocos(ref[0, 0]) - dsp.log_mel_vocos(got[0, 0])).mean()
+        record(f"bf16 C3 B=64 T=320 utterance {b}", max_abs=np.abs(got - ref).max(), rel_l2=rel, mel_l1=mel,
+               peak=np.abs(ref).max())
+        assert np.abs(got - ref).max() <= BF16_MAX_ABS and rel <= BF16_REL_L2 and mel <= BF16_MEL_L1
