@@ -25,6 +25,15 @@ extern "C" {
 #define KK_ACT_SNAKE 2 /* x + (1/alpha) sin(alpha x)^2          istftnet.py:382, :389     */
 #define KK_ACT_SNAKE_FAST 3 /* Snake with the hardware (MUFU) sine; for bf16-output pipelines */
 
+/* ---- ragged batches (per-utterance lengths inside ONE launch) -------------------------------------------------
+ * The reference decodes one utterance per call (kokoro.py:135-165), so every utterance has its own length; a batch here
+ * is a PADDED tensor (B, L, pitch) plus `lens`, a device array of B ints giving each utterance's length in asr FRAMES
+ * (T_b <= T).  A kernel working at a level with `mul*T + add` rows per utterance receives (lens, len_mul, len_add) and
+ * treats rows >= len_mul*lens[b] + len_add as padding: they are excluded from instance-norm statistics (and from their
+ * divisor), read as the convolution's zero padding, and activation tensors that a later convolution reads through TMA
+ * are written as ZERO there.  lens == NULL: every utterance has the full length (the arguments are ignored).
+ * Results of utterance b are then identical to decoding it alone (no op mixes utterances, istftnet.py:221-230). */
+
 int kk_version(void);
 const char* kk_last_error(void);
 /* 1 when the current device is compute capability 10.x (tcgen05/TMEM/TMA paths usable). */
@@ -48,7 +57,8 @@ int kk_style_affine(const float* s, const float* W, const float* bias, float* h,
 
 /* ---- instance-norm statistics (InstanceNorm1d, istftnet.py:229-230): accumulates per (b,c) sum and
  * sum of squares over time into stats (B, C, 2) doubles (caller zeroes them). */
-int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pitch, void* stream);
+int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pitch, const int* lens, int len_mul,
+                      int len_add, void* stream);
 
 /* ---- AdaIN apply + activation (istftnet.py:337 then :382/:389 Snake or :876/:889 LeakyReLU):
  * y = act((1+gamma)*(x-mean)/sqrt(var+1e-5)+beta); gamma = h[b][c], beta = h[b][C+c] (h row stride h_stride).
@@ -57,14 +67,16 @@ int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pi
  * left zero pad (istftnet.py:880-881): output has 2L rows; pool_w is the folded (C,3) weight. */
 int kk_adain_act(const float* x, int x_pitch, const double* stats, const float* h, int h_stride,
                  const float* alpha, int act, float slope, void* out, int out_is_bf16, int out_pitch,
-                 int B, int L, int C, int pool, const float* pool_w, const float* pool_b, void* stream);
+                 int B, int L, int C, int pool, const float* pool_w, const float* pool_b, const int* lens, int len_mul,
+                 int len_add, void* stream);
 
 /* ---- Decoder front glue (istftnet.py:949-953,:957): F0_conv / N_conv (k3 s2 p1 on one channel) and the
  * channels-first -> channels-last transpose of asr, written into out (B, T, out_pitch) at channel offsets
- * asr_off (512 channels; skipped when asr == NULL), f0_off, n_off.  w3b = {w0,w1,w2,bias} folded. */
+ * asr_off (512 channels; skipped when asr == NULL), f0_off, n_off.  w3b = {w0,w1,w2,bias} folded.
+ * lens (frames per utterance, or NULL): curve samples at or beyond 2*lens[b] read as the conv's zero padding. */
 int kk_front_assemble(const float* asr, const float* F0_curve, const float* N, const float* f0_w3b,
                       const float* n_w3b, float* out, int out_pitch, int asr_off, int f0_off, int n_off,
-                      int B, int C_asr, int T, void* stream);
+                      int B, int C_asr, int T, const int* lens, void* stream);
 /* Strided channel-block copy between channels-last tensors (the concatenations of :957). */
 int kk_copy_channels(const float* src, int src_pitch, int src_off, float* dst, int dst_pitch, int dst_off,
                      int rows, int C, void* stream);
@@ -99,6 +111,11 @@ typedef struct kk_conv_desc {
                                       istftnet.py:795-800); kk_conv1d_adain_bf16_tc only (TMA reduce-add)          */
   int res_is_bf16;                 /* `res` points at bf16 (B, L_res, res_pitch) data: the bf16 residual stream of
                                       AdaINResBlock1 (x = x + xt, istftnet.py:394); kk_conv1d_adain_bf16_tc only   */
+  const int* lens; int len_mul, len_add; /* ragged batch (see top): utterance b has L_true_b = min(L_true, len_mul *
+                                      lens[b] + len_add) true output rows (and L_out_b = L_true_b + L_out - L_true
+                                      output rows); rows beyond are excluded from `stats`, written as zero to
+                                      `out_act`, and - kk_conv1d_adain_bf16_tc, where L_in = M = L_true - masked on the
+                                      input side too (zero AFTER the activation, statistics divisor L_true_b)      */
 } kk_conv_desc;
 
 /* fp32 CUDA-core kernel (strict-fp32 parity path; also the tiny / strided layers). x, w fp32. */
@@ -134,21 +151,29 @@ int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, const kk_conv_d
  * noise (B, 600T, 9) N(0,1) or NULL (then a Philox counter RNG is used, seeded with *seed_dev when seed_dev is a
  * device pointer - so that a captured CUDA graph draws fresh noise on every replay, as mx.random.normal does on
  * every call (istftnet.py:620) - else with `seed`).
- * phase_ws: scratch (B, 9, 2T) floats.  lin_w (9), lin_b (1): m_source.l_linear. */
+ * phase_ws: scratch (B, 9, 2T) floats.  lin_w (9), lin_b (1): m_source.l_linear.
+ * lens (frames per utterance, or NULL): utterance b has T2_b = 2*lens[b] f0 samples (the interpolation's edge clamp and
+ * index wrap follow T2_b); har_source samples at or beyond T2_b*upsample are written as zero. */
 int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const unsigned long long* seed_dev,
                    const float* lin_w, const float* lin_b, float* phase_ws, float* har_source, int B, int T2,
-                   int upsample, void* stream);
-int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream);
+                   int upsample, const int* lens, void* stream);
+/* lens (frames, or NULL): utterance b has S_b = len_mul*lens[b] samples (the reflect pad mirrors at S_b) and S_b/5 + 1
+ * frames; frames beyond are written as zero. */
+int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, const int* lens, int len_mul,
+                void* stream);
 /* Same transform, additionally (or only, har == NULL) written as bf16 into (B, bf_rows, bf_pitch) with
  * bf_rows >= 120T+1: the tensor-core noise_convs (istftnet.py:778) read it as (B, bf_rows/6, 6*bf_pitch) rows
  * of six frames (stride-6 conv) or as is (1x1 conv).  Rows >= 120T+1 are not touched (caller keeps them zero). */
 int kk_stft_n20_bf16(const float* har_source, float* har, int har_pitch, void* har_bf16, int bf_pitch, int bf_rows,
-                     int B, int S, void* stream);
+                     int B, int S, const int* lens, int len_mul, void* stream);
 
 /* ---- iSTFT head (Generator tail istftnet.py:804-806, MLXSTFT.inverse :497-523, utils.istft :104-158):
  * y (B, F, y_pitch) conv_post output -> spec=exp(y[:11]), phase=sin(y[11:]) -> irfft(20) * periodic hann,
- * overlap-add hop 5, divide by window sum, trim 10 -> audio (B, 5*(F-1)). */
-int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, void* stream);
+ * overlap-add hop 5, divide by window sum, trim 10 -> audio (B, 5*(F-1)).
+ * lens (frames, or NULL): utterance b has F_b = len_mul*lens[b] + len_add spectrogram frames; samples beyond 5*(F_b-1)
+ * are written as zero. */
+int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, const int* lens, int len_mul, int len_add,
+                      void* stream);
 
 /* ---- general STFT / iSTFT / log-mel (mlx_audio/utils.py:52-158,164-237), batched over signals.
  * window: n_fft floats (already zero-extended).  pad_mode: 0 none(center=False) 1 reflect 2 constant.

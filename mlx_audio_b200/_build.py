@@ -37,11 +37,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     KK_TUNE=1 / KK_FUSED_DBG=1 in the environment add -DKK_TUNE (experiment knobs read from the environment) /
     -DKK_FUSED_DBG (per-barrier wait counters in the fused kernel) - lab builds, never the default."""
     extra = [f"-D{k}" for k in ("KK_TUNE", "KK_FUSED_DBG") if os.environ.get(k) == "1"]
+    extra += os.environ.get("KK_DEFS", "").split()          # further -D flags of a lab build (A/B experiments)
     if not force and not extra and not _stale():
         return LIB_PATH
     nvcc = _nvcc()
-    lib_path = LIB_PATH if not extra else os.path.join(PKG_DIR, "libkokoro_b200_lab.so")   # lab builds never shadow the product
-    objdir = os.path.join(PKG_DIR, "build" if not extra else "build_lab")
+    lib_path = LIB_PATH if not extra else os.path.join(PKG_DIR, f"libkokoro_b200_{os.environ.get('KK_LAB_NAME', 'lab')}.so")   # lab builds never shadow the product
+    objdir = os.path.join(PKG_DIR, "build" if not extra else f"build_{os.environ.get('KK_LAB_NAME', 'lab')}")
     os.makedirs(objdir, exist_ok=True)
     procs = []
     for src in SOURCES:

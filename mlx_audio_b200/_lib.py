@@ -39,6 +39,7 @@ class ConvDesc(C.Structure):
         ("stats", C.c_void_p),
         ("out_act", C.c_void_p), ("act_pitch", C.c_int), ("act_is_bf16", C.c_int), ("act_slope", C.c_float),
         ("out_add", C.c_void_p), ("add_pitch", C.c_int), ("res_is_bf16", C.c_int),
+        ("lens", C.c_void_p), ("len_mul", C.c_int), ("len_add", C.c_int),
     ]
 
 
@@ -62,18 +63,18 @@ PROTOTYPES = {
     "kk_fold_weight_norm": [_P, _P, _P, _I, _I, _P],
     "kk_pack_conv_weight": [_P, _P, _I, _I, _I, _I, _I, _I, _I, _P],
     "kk_style_affine": [_P, _P, _P, _P, _I, _I, _I, _P],
-    "kk_instnorm_stats": [_P, _P, _I, _I, _I, _I, _P],
-    "kk_adain_act": [_P, _I, _P, _P, _I, _P, _I, _F, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P],
-    "kk_front_assemble": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P],
+    "kk_instnorm_stats": [_P, _P, _I, _I, _I, _I, _P, _I, _I, _P],
+    "kk_adain_act": [_P, _I, _P, _P, _I, _P, _I, _F, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _I, _I, _P],
+    "kk_front_assemble": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P, _P],
     "kk_copy_channels": [_P, _I, _I, _P, _I, _I, _I, _I, _P],
     "kk_convert_act": [_P, _I, _P, _I, _I, _LL, _I, _F, _P],
     "kk_conv1d_f32": [_P, _P, C.POINTER(ConvDesc), _P],
     "kk_conv1d_bf16_tc": [_P, _P, C.POINTER(ConvDesc), _I, _P],
     "kk_conv1d_adain_bf16_tc": [C.POINTER(AdainIn), _P, C.POINTER(ConvDesc), _P],
-    "kk_hnsf_source": [_P, _P, _ULL, _P, _P, _P, _P, _P, _I, _I, _I, _P],
-    "kk_stft_n20": [_P, _P, _I, _I, _I, _P],
-    "kk_stft_n20_bf16": [_P, _P, _I, _P, _I, _I, _I, _I, _P],
-    "kk_istft_head_n20": [_P, _I, _P, _I, _I, _P],
+    "kk_hnsf_source": [_P, _P, _ULL, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P],
+    "kk_stft_n20": [_P, _P, _I, _I, _I, _P, _I, _P],
+    "kk_stft_n20_bf16": [_P, _P, _I, _P, _I, _I, _I, _I, _P, _I, _P],
+    "kk_istft_head_n20": [_P, _I, _P, _I, _I, _P, _I, _I, _P],
     "kk_stft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "kk_logmel_f32": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
     "kk_istft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],

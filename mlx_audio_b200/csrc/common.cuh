@@ -38,4 +38,15 @@ static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b)
 
 __device__ __forceinline__ float leaky(float v, float slope) { return v > 0.f ? v : v * slope; }
 
+// Ragged batches (kokoro_b200.h): rows of utterance b at a level with mul*T + add rows per utterance, capped by the
+// padded length L.  lens == NULL: L.
+__device__ __forceinline__ int ragged_len(const int* __restrict__ lens, int mul, int add, int b, int L) {
+#ifdef KK_NO_RAGGED   // lab builds: compile the ragged paths out (A/B of their cost)
+  return L;
+#endif
+  if (!lens) return L;
+  const int v = __ldg(lens + b) * mul + add;
+  return v < L ? (v < 0 ? 0 : v) : L;
+}
+
 }  // namespace kk

@@ -67,6 +67,7 @@ conv1d_f32_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
 
   // ---- epilogue
   const bool do_stats = d.stats != nullptr;
+  const EpiLim lim = epi_lim(d, b);
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     int n = n0 + tx * 4 + j;
@@ -76,9 +77,9 @@ conv1d_f32_kernel(const float* __restrict__ x, const float* __restrict__ w, cons
       for (int i = 0; i < 8; ++i) {
         int m = m0 + ty * 8 + i;
         if (m >= d.M) continue;
-        EpiCoord e = epi_coord(d, m, n);
+        EpiCoord e = epi_coord(d, lim, m, n);
         if (e.out_row < 0) continue;
-        float v = epi_value(d, b, e, acc[i][j]);
+        float v = epi_value(d, b, e, acc[i][j]);   // 0 on the padding rows of a ragged batch (stored, not counted)
         epi_store(d, b, e, v);
         cs += v;
         cq = fmaf(v, v, cq);

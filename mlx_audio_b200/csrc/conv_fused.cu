@@ -25,6 +25,7 @@
 // as the first statement of every role branch (ptxas then allocates each branch against its own budget).  Persistent: CTA i walks a contiguous range of the (utterance, row-tile) list.
 #include "conv_epilogue.cuh"
 #include "ptx_sm100.cuh"
+#include "ragged_tiles.cuh"
 #include <stdlib.h>
 
 namespace kk {
@@ -62,7 +63,8 @@ struct FvCfg {
   static constexpr int OFF_RAW = OFF_STG + STG_HALF;             // aliases staging half 1
   static constexpr int OFF_COEF = OFF_STG + 2 * STG_HALF;
   static constexpr int OFF_BAR = OFF_COEF + COEF_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + 640 + 1024;
+  static constexpr int OFF_RG = OFF_BAR + 640;                   // ragged tile table (RG_MAX_B + 1 ints)
+  static constexpr int SMEM_BYTES = OFF_RG + (RG_MAX_B + 1) * 4 + 12 + 1024;
   static constexpr uint32_t TMEM_COLS = 512;
   static_assert(SLOT_ROWS >= 128 * MT + FV_HALO_MAX && SLOT_ROWS % 32 == 0, "slot too small");
   static_assert(2 * MT * BN <= 512, "accumulators exceed tensor memory");
@@ -260,7 +262,7 @@ template <int MT, int BN, int CB, bool SWAP, int CL>
 __global__ void __launch_bounds__(FV_THREADS, 1)
 conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                       const __grid_constant__ CUtensorMap tmAdd, const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles,
+                       const __grid_constant__ CUtensorMap tmAdd, const kk_conv_desc d, const kk_adain_in a, const int m_tiles, const int total_tiles_uniform,
                        const int flags) {
   using Cfg = FvCfg<MT, BN, CB>;
   extern __shared__ uint8_t smem_raw[];
@@ -278,6 +280,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   uint64_t* tmem_empty = tmem_full + 2;                                  // [2]
   uint64_t* res_full = tmem_empty + 2;                                   // [FV_EPI_WARPS * 2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + FV_EPI_WARPS * 2);
+  int* rg_ts = reinterpret_cast<int*>(smem + Cfg::OFF_RG);              // ragged batches: first tile of each utterance
+  const int* ts = d.lens ? rg_ts : nullptr;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int halo = (d.taps - 1) * d.dil;
@@ -296,17 +300,6 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   const uint32_t nraw = deep_raw ? 2 * Cfg::NRAW : Cfg::NRAW;
   uint8_t* sRaw = smem + (deep_raw ? Cfg::OFF_STG : Cfg::OFF_RAW);
   const uint32_t nst = (half0_free && !deep_raw) ? Cfg::STAGES + Cfg::STG_HALF / Cfg::B_BYTES : Cfg::STAGES;
-  int t_start, t_count;
-  fv_tile_range(total_tiles, blockIdx.x, gridDim.x, t_start, t_count);
-  // the weight pipeline of a pair runs for the longer of the two tile lists (the other CTA passes phantom slabs)
-  int t_pair = t_count;
-  uint32_t crank = 0;
-  if constexpr (CL > 1) {
-    int s2, c2;
-    fv_tile_range(total_tiles, blockIdx.x ^ 1, gridDim.x, s2, c2);
-    t_pair = c2 > t_count ? c2 : t_count;
-    crank = ptx::cluster_ctarank();
-  }
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmB);
@@ -335,11 +328,24 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  if (warp == 3 && d.lens) rg_build(rg_ts, d, 128 * MT, lane);   // ragged batch: the tile list follows the lengths
   ptx::tc_fence_before();
   if constexpr (CL > 1) ptx::cluster_sync();   // the peer's barriers exist before anything is multicast at them
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const int total_tiles = ts ? ts[d.B] : total_tiles_uniform;
+  int t_start, t_count;
+  fv_tile_range(total_tiles, blockIdx.x, gridDim.x, t_start, t_count);
+  // the weight pipeline of a pair runs for the longer of the two tile lists (the other CTA passes phantom slabs)
+  int t_pair = t_count;
+  uint32_t crank = 0;
+  if constexpr (CL > 1) {
+    int s2, c2;
+    fv_tile_range(total_tiles, blockIdx.x ^ 1, gridDim.x, s2, c2);
+    t_pair = c2 > t_count ? c2 : t_count;
+    crank = ptx::cluster_ctarank();
+  }
 
   if (warp == 0) {
     // ===================== TMA producer: weight slabs, order (tile, channel block, tap) =====================
@@ -435,13 +441,18 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     if (lane == 0) {
       uint32_t ga = 0, gr = 0;
       FV_DBG_DECL(w_xprod);
+      RgMap map(ts, m_tiles), map_next(ts, m_tiles);
       for (int j = 0; j < t_count; ++j) {
         const int tile = t_start + j;
-        const int b = tile / m_tiles, l_base = (tile - b * m_tiles) * (128 * MT) - d.pad_left;
+        int b, mtile;
+        map.locate(tile, b, mtile);
+        const int l_base = mtile * (128 * MT) - d.pad_left;
         if ((flags & 1) && j + 1 < t_count) {
           // pull the NEXT tile's rows (input and residual) into L2 now: the TMA loads one tile later then see
           // L2-hit latency instead of HBM latency
-          const int nt = tile + 1, nb_ = nt / m_tiles, nm0 = (nt - nb_ * m_tiles) * (128 * MT);
+          int nb_, nmt;
+          map_next.locate(tile + 1, nb_, nmt);
+          const int nm0 = nmt * (128 * MT);
           const size_t xesz = a.x_is_bf16 ? 2 : 4;
           int l0 = nm0 - d.pad_left + (nb_ == b ? R - halo : 0), l1 = nm0 - d.pad_left + R;   // rows not already fetched
           l0 = l0 < 0 ? 0 : l0;
@@ -484,17 +495,22 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     int cur_b = -1;
     uint32_t ga = 0, gr = 0;
     FV_DBG_DECL(w_xdata); FV_DBG_DECL(w_xslot);
+    RgMap map(ts, m_tiles);
     for (int j = 0; j < t_count; ++j) {
       const int tile = t_start + j;
-      const int b = tile / m_tiles, l_base = (tile - b * m_tiles) * (128 * MT) - d.pad_left;
+      int b, mtile;
+      map.locate(tile, b, mtile);
+      const int l_base = mtile * (128 * MT) - d.pad_left;
+      // ragged batch: rows of this utterance (rows beyond are padding: zero after the activation, not in the divisor)
+      const int Lb = ragged_len(d.lens, d.len_mul, d.len_add, b, d.L_in);
       if (b != cur_b) {
         asm volatile("bar.sync 2, %0;" ::"n"(FV_XF_THREADS) : "memory");   // everyone is done with the old table
         for (int c = xt; c < CB * 64; c += FV_XF_THREADS) {
           float4 k = make_float4(1.f, 0.f, 1.f, 1.f);
           if (a.stats) {
             const double s = a.stats[((size_t)b * d.C_in + c) * 2], ss = a.stats[((size_t)b * d.C_in + c) * 2 + 1];
-            const double mean = s / d.L_in;
-            double var = ss / d.L_in - mean * mean;
+            const double mean = s / Lb;
+            double var = ss / Lb - mean * mean;
             if (var < 0.0) var = 0.0;
             const float rstd = 1.0f / sqrtf((float)var + 1e-5f);
             const float g1 = 1.0f + a.h[(size_t)b * a.h_stride + c];
@@ -512,9 +528,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const uint32_t sp = ptx::smem_u32(smem + slot * Cfg::SLOT_BYTES);
         if (a.x_is_bf16) {
           FV_WAIT(&x_full[slot], sph, w_xdata);
-          if (snake) fv_xf_inplace<KK_ACT_SNAKE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
-          else if (a.act == KK_ACT_LEAKY) fv_xf_inplace<KK_ACT_LEAKY>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
-          else if (a.stats) fv_xf_inplace<KK_ACT_NONE>(sp, coef, a.slope, cb, R, l_base, d.L_in, xw, lane);
+          if (snake) fv_xf_inplace<KK_ACT_SNAKE>(sp, coef, a.slope, cb, R, l_base, Lb, xw, lane);
+          else if (a.act == KK_ACT_LEAKY) fv_xf_inplace<KK_ACT_LEAKY>(sp, coef, a.slope, cb, R, l_base, Lb, xw, lane);
+          else if (a.stats) fv_xf_inplace<KK_ACT_NONE>(sp, coef, a.slope, cb, R, l_base, Lb, xw, lane);
           // else: no normalisation and no activation - the operand is exactly what TMA wrote (rows outside the
           // utterance were zero-filled by the tensor map), so the slot is handed to the MMA as is
         } else {
@@ -527,9 +543,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             const uint32_t s = gr % nraw, ph = (gr / nraw) & 1;
             FV_WAIT(&raw_full[s], ph, w_xdata);
             const uint32_t rp = ptx::smem_u32(sRaw + s * FV_RAW_BYTES);
-            if (snake) fv_xf_raw<KK_ACT_SNAKE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw & 1, lane);
-            else if (a.act == KK_ACT_LEAKY) fv_xf_raw<KK_ACT_LEAKY>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw & 1, lane);
-            else fv_xf_raw<KK_ACT_NONE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, d.L_in, xw & 1, lane);
+            if (snake) fv_xf_raw<KK_ACT_SNAKE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, Lb, xw & 1, lane);
+            else if (a.act == KK_ACT_LEAKY) fv_xf_raw<KK_ACT_LEAKY>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, Lb, xw & 1, lane);
+            else fv_xf_raw<KK_ACT_NONE>(rp, sp, k, a.slope, i * FV_BOX_ROWS, R, l_base, Lb, xw & 1, lane);
             __syncwarp();                              // the warp's reads of the stage are complete
             if (lane == 0) ptx::mbar_arrive(&raw_empty[s]);
           }
@@ -560,10 +576,13 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const int ch0 = lg * 32, chan = ch0 + lane;
     const float bias_s = (d.bias ? __ldg(d.bias + chan) : 0.f) * d.scale;   // (v + bias) * scale = fma(v, scale, bias * scale)
     const int n_items = t_count * NRC;
+    RgMap map(ts, m_tiles), map_res(ts, m_tiles);
     auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
       if (n >= n_items) return;
       const int tile = t_start + n / NRC, rc = n % NRC;
-      const int b = tile / m_tiles, row0 = (tile - b * m_tiles) * 256 + half * 128 + rc * 32;
+      int b, mtile;
+      map_res.locate(tile, b, mtile);
+      const int row0 = mtile * 256 + half * 128 + rc * 32;
       fv_issue_res(d, b, row0, ch0, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
     };
     if (has_res) { issue_res(0); issue_res(1); }
@@ -589,7 +608,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     };
     for (int j = 0; j < t_count; ++j) {
       const int tile = t_start + j;
-      const int b = tile / m_tiles, tm0 = (tile - b * m_tiles) * 256 + half * 128;
+      int b, mtile;
+      map.locate(tile, b, mtile);
+      const int tm0 = mtile * 256 + half * 128;
+      const int Mb = ragged_len(d.lens, d.len_mul, d.len_add, b, d.M);   // rows of this utterance (ragged batches)
       if (do_stats && b != stat_b) { flush_stats(stat_b); stat_b = b; }
       const uint32_t buf = j & 1, aph = (j >> 1) & 1;
       FV_WAIT(&tmem_full[buf], aph, w_tfull);
@@ -601,7 +623,8 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const int p = has_res ? (n & 1) : 0;
         float* st = reinterpret_cast<float*>(stg0 + p * Cfg::STG_HALF);
         const int row0 = tm0 + rc * 32;
-        const int nvalid = d.M - row0;           // rows of this chunk inside the utterance (may be <= 0 or >= 32)
+        const int nvalid = Mb - row0;            // rows of this chunk inside the utterance (may be <= 0 or >= 32)
+        const int nstore = d.M - row0;           // rows of this chunk inside the tensors: padding rows are stored as 0
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
         if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
@@ -666,10 +689,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             ptx::bulk_commit();
           }
         }
-        if (d.out_act && nvalid > 0) {
+        if (d.out_act && nstore > 0) {
           __nv_bfloat16* ap = (__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0) * d.act_pitch + chan;
-          if (d.act_pitch == 128) store_bf16(ap, 128, v, nvalid);
-          else store_bf16(ap, d.act_pitch, v, nvalid);
+          if (d.act_pitch == 128) store_bf16(ap, 128, v, nstore);
+          else store_bf16(ap, d.act_pitch, v, nstore);
         }
         if (has_res) {
           if (via_smem && lane == 0) ptx::bulk_wait_read<0>();   // the TMA engine is done reading this staging tile
@@ -695,11 +718,14 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const bool out_aligned_act = d.out_act != nullptr;
     const bool res16 = d.res_is_bf16 != 0;
     const int n_items = t_count * NCH;
+    RgMap map(ts, m_tiles), map_res(ts, m_tiles);
 
     auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
       if (n >= n_items) return;
       const int tile = t_start + n / NCH, c = n % NCH;
-      const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128 + lg * 32;
+      int b, mtile;
+      map_res.locate(tile, b, mtile);
+      const int m0 = mtile * (128 * MT) + mt * 128 + lg * 32;
       fv_issue_res(d, b, m0, (chunk0 + c) * 32, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
     };
     if (has_res) { issue_res(0); issue_res(1); }
@@ -722,14 +748,17 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
 
     for (int j = 0; j < t_count; ++j) {
       const int tile = t_start + j;
-      const int b = tile / m_tiles, m0 = (tile - b * m_tiles) * (128 * MT) + mt * 128 + lg * 32;   // first row of the warp
+      int b, mtile;
+      map.locate(tile, b, mtile);
+      const int m0 = mtile * (128 * MT) + mt * 128 + lg * 32;   // first row of the warp
+      const int Mb = ragged_len(d.lens, d.len_mul, d.len_add, b, d.M);   // rows of this utterance (ragged batches)
       if (do_stats && b != stat_b) { flush_stats(stat_b); stat_b = b; }
       const uint32_t buf = j & 1, aph = (j >> 1) & 1;
       FV_WAIT(&tmem_full[buf], aph, w_tfull);
       ptx::tc_fence_after();
       const uint32_t tacc = tmem_base + buf * (MT * BN) + mt * BN + ((uint32_t)(lg * 32) << 16);
       const int m = m0 + lane;
-      const bool row_ok = m < d.M;
+      const bool row_ok = m < Mb;              // rows beyond the utterance are stored as zeros
 #pragma unroll
       for (int c = 0; c < NCH; ++c) {
         const int n = j * NCH + c;
@@ -931,6 +960,7 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   const int m_tiles = cdiv(d->M, 128 * MT);
   const long long total = (long long)m_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_adain_bf16_tc: too many tiles");
+  KK_CHECK_ARG(!d->lens || d->B <= RG_MAX_B, "kk_conv1d_adain_bf16_tc: a ragged batch holds at most %d utterances", RG_MAX_B);
   int grid = (int)(total < num_sms() ? total : num_sms());
   // bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring, bit 2 = no residual prefetch (on).  The
   // environment is read in -DKK_TUNE builds only (experiments); the product build has no knobs.

@@ -9,6 +9,7 @@
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-9 = epilogue
 // (warp w owns TMEM lanes 32*(w%4)..+31); warp 2 also allocates / frees tensor memory.
 #include "tc_epilogue.cuh"
+#include "ragged_tiles.cuh"
 #include <stdlib.h>
 
 namespace kk {
@@ -36,7 +37,8 @@ struct TpCfg {
   static constexpr int ACT_BYTES = BN <= 128 ? TP_EPI_WARPS * 2048 : 0;
   static constexpr int OFF_ACT = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES;
   static constexpr int OFF_BAR = OFF_ACT + ACT_BYTES;
-  static constexpr int SMEM_BYTES = OFF_BAR + 384 + 1024;
+  static constexpr int OFF_RG = OFF_BAR + 384;               // ragged tile table (RG_MAX_B + 1 ints)
+  static constexpr int SMEM_BYTES = OFF_RG + (RG_MAX_B + 1) * 4 + 12 + 1024;
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
   static constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
 };
@@ -45,7 +47,7 @@ template <int BN>
 __global__ void __launch_bounds__(TP_THREADS, 1)
 conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                               const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                              const __grid_constant__ CUtensorMap tmAct, const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles,
+                              const __grid_constant__ CUtensorMap tmAct, const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles_uniform,
                               const int direct_epi) {
   using Cfg = TpCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
@@ -58,6 +60,8 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
   uint64_t* res_bar = tmem_empty_bar + 2;              // [TP_EPI_WARPS * NBUF]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + TP_EPI_WARPS * Cfg::NBUF);
+  int* rg_ts = reinterpret_cast<int*>(smem + Cfg::OFF_RG);   // ragged batches: first row tile of each utterance
+  const int* ts = d.lens ? rg_ts : nullptr;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cblocks = (d.C_in + TC_BK - 1) / TC_BK;
@@ -78,19 +82,24 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  if (warp == 3 && d.lens) rg_build(rg_ts, d, TC_BM, lane);   // ragged batch: the tile list follows the lengths
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // tile = (utterance x row tile) * n_tiles + column tile
+  const int total_tiles = ts ? ts[d.B] * n_tiles : total_tiles_uniform;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t kbg = 0;
+      RgMap map(ts, m_tiles);
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int nt = tile % n_tiles;
         const int rest = tile / n_tiles;
-        const int mt = rest % m_tiles, b = rest / m_tiles;
+        int mt, b;
+        map.locate(rest, b, mt);
         const int m0 = mt * TC_BM, n0 = nt * BN;
         for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
           const int s = kbg % Cfg::STAGES;
@@ -150,11 +159,13 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
     uint8_t* stg = reinterpret_cast<uint8_t*>(staging) + ew * (NBUF * EPI_TILE_BYTES);
     uint64_t* rbar = res_bar + ew * NBUF;
     uint32_t item = 0;
+    RgMap map(ts, m_tiles), map_res(ts, m_tiles), map_next(ts, m_tiles);
     auto issue_res = [&](uint32_t n) {
       const int tl = blockIdx.x + (int)(n / (uint32_t)n_mine) * gridDim.x;
       if (tl >= total_tiles) return;
-      const int rest = tl / n_tiles;
-      epi_issue_res(d, &tmRes, rest / m_tiles, (rest % m_tiles) * TC_BM + lg * 32,
+      int rb, rmt;
+      map_res.locate(tl / n_tiles, rb, rmt);
+      epi_issue_res(d, &tmRes, rb, rmt * TC_BM + lg * 32,
                     (tl % n_tiles) * BN + (ch_first + (int)(n % (uint32_t)n_mine)) * 32, lane,
                     stg + (n % NBUF) * EPI_TILE_BYTES, &rbar[n % NBUF]);
     };
@@ -162,18 +173,21 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
       if (d.res && n_mine > 0)
         for (int i = 0; i < NBUF; ++i) issue_res(i);
     } else if (n_mine > 0 && (int)blockIdx.x < total_tiles) {
-      const int rest = blockIdx.x / n_tiles;
-      epi_prefetch_chunk(d, rest / m_tiles, (rest % m_tiles) * TC_BM, (blockIdx.x % n_tiles) * BN, ch_first, lg, lane, tres);
+      int fb, fmt;
+      map_next.locate(blockIdx.x / n_tiles, fb, fmt);
+      epi_prefetch_chunk(d, fb, fmt * TC_BM, (blockIdx.x % n_tiles) * BN, ch_first, lg, lane, tres);
     }
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
       const int nt = tile % n_tiles;
       const int rest = tile / n_tiles;
-      const int mt = rest % m_tiles, b = rest / m_tiles;
+      int mt, b;
+      map.locate(rest, b, mt);
       const int m0 = mt * TC_BM, n0 = nt * BN;
       const int ntile = tile + gridDim.x;
       const bool more = ntile < total_tiles;
-      const int nrest = ntile / n_tiles;
-      const int nx_b = nrest / m_tiles, nx_m0 = (nrest % m_tiles) * TC_BM, nx_n0 = (ntile % n_tiles) * BN;
+      int nx_b = 0, nx_mt = 0;
+      if (more) map_next.locate(ntile / n_tiles, nx_b, nx_mt);
+      const int nx_m0 = nx_mt * TC_BM, nx_n0 = (ntile % n_tiles) * BN;
       const uint32_t acc = it & 1, aph = (it >> 1) & 1;
       float* s_stats = s_stats_all + acc * (8 * BN);
       ptx::mbar_wait(&tmem_full_bar[acc], aph);
@@ -197,7 +211,7 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
           }
           ++item;
         } else {
-          epilogue_chunk<BN>(d, b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, do_stats, cs, cq, tres,
+          epilogue_chunk<BN>(d, epi_lim(d, b), b, m0, n0, ch, lg, lane, tmem_base + acc * BN, stage_w, do_stats, cs, cq, tres,
                              last ? more : true, last ? nx_b : b, last ? nx_m0 : m0, last ? nx_n0 : n0,
                              last ? ch_first : ch + 1);
         }
@@ -306,6 +320,7 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
   const int m_tiles = cdiv(d->M, TC_BM), n_tiles = cdiv(d->N, BN);
   const long long total = (long long)m_tiles * n_tiles * d->B;
   KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_bf16_tc: too many tiles");
+  KK_CHECK_ARG(!d->lens || d->B <= RG_MAX_B, "kk_conv1d_bf16_tc: a ragged batch holds at most %d utterances", RG_MAX_B);
   const int grid = (int)(total < num_sms() ? total : num_sms());
   // direct epilogue (tc_epilogue.cuh): every 32-column chunk full, 16-byte aligned rows, one residual at most
   auto al16 = [](const void* p, long long pitch_bytes) { return (((uintptr_t)p | (uintptr_t)pitch_bytes) & 15) == 0; };

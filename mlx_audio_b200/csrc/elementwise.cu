@@ -51,11 +51,12 @@ style_affine_kernel(const float* __restrict__ s, const float* __restrict__ W, co
 // ---------------------------------------------------------------- instance-norm statistics
 // block (32 channels, 8 row lanes); rows [l0, l0+rows_per_block).  fp32 partials -> double atomics.
 __global__ void instnorm_stats_kernel(const float* __restrict__ x, double* __restrict__ stats, int L, int C,
-                                      int pitch, int rows_per_block) {
+                                      int pitch, int rows_per_block, const int* __restrict__ lens, int len_mul,
+                                      int len_add) {
   int b = blockIdx.z;
   int c = blockIdx.x * 32 + threadIdx.x;
   int l0 = blockIdx.y * rows_per_block;
-  int l1 = min(L, l0 + rows_per_block);
+  int l1 = min(ragged_len(lens, len_mul, len_add, b, L), l0 + rows_per_block);   // padding rows are not statistics
   // fp64 partial sums: the row split (rows_per_block) depends on the batch size, and fp32 partials would make an
   // utterance's statistics - hence, after bf16 rounding downstream, its audio - depend on what it is batched with
   double s = 0.0, ss = 0.0;
@@ -109,16 +110,17 @@ __global__ void adain_act_kernel(const float* __restrict__ x, int x_pitch, const
                                  const float* __restrict__ h, int h_stride, const float* __restrict__ alpha, int act,
                                  float slope, OutT* __restrict__ out, int out_pitch, int L, int C,
                                  const float* __restrict__ pool_w, const float* __restrict__ pool_b,
-                                 int rows_per_block) {
+                                 int rows_per_block, const int* __restrict__ lens, int len_mul, int len_add) {
   int b = blockIdx.z;
   int c = blockIdx.x * 32 + threadIdx.x;
   if (c >= C) return;
+  const int Lb = ragged_len(lens, len_mul, len_add, b, L);   // rows of this utterance; [Lb, L) is padding -> zeros
   AdaCoef k = {0.f, 1.f, 1.f, 0.f, 1.f, 1.f};
   bool norm = stats != nullptr;
   if (norm) {
     double s = stats[((size_t)b * C + c) * 2], ss = stats[((size_t)b * C + c) * 2 + 1];
-    double mean = s / L;
-    double var = ss / L - mean * mean;
+    double mean = s / Lb;
+    double var = ss / Lb - mean * mean;
     if (var < 0.0) var = 0.0;
     k.mean = (float)mean;
     k.rstd = 1.0f / sqrtf((float)var + 1e-5f);
@@ -132,19 +134,26 @@ __global__ void adain_act_kernel(const float* __restrict__ x, int x_pitch, const
   if (!POOL) {
     OutT* ob = out + (size_t)b * L * out_pitch + c;
     for (int l = l0 + threadIdx.y; l < l1; l += 8)
-      store_out<OutT>(ob + (size_t)l * out_pitch, ada_act(xb[(size_t)l * x_pitch], k, norm, act, slope));
+      store_out<OutT>(ob + (size_t)l * out_pitch, l < Lb ? ada_act(xb[(size_t)l * x_pitch], k, norm, act, slope) : 0.f);
   } else {
     // depthwise ConvTranspose1d k3 s2 p1 + bias, then left zero pad (istftnet.py:880-881):
     // P[0]=0, P[2i+1] = a[i] w1 + b, P[2i+2] = a[i] w2 + a[i+1] w0 + b   (i+1 < L)
     float w0 = pool_w[c * 3 + 0], w1 = pool_w[c * 3 + 1], w2 = pool_w[c * 3 + 2], pb = pool_b[c];
     OutT* ob = out + (size_t)b * (2 * L) * out_pitch + c;
     for (int l = l0 + threadIdx.y; l < l1; l += 8) {
-      float a0 = ada_act(xb[(size_t)l * x_pitch], k, norm, act, slope);
       if (l == 0) store_out<OutT>(ob, 0.f);
+      if (l >= Lb) {   // padding rows of a ragged batch: the convolution that reads this tensor expects zeros
+        store_out<OutT>(ob + (size_t)(2 * l + 1) * out_pitch, 0.f);
+        if (l + 1 < L) store_out<OutT>(ob + (size_t)(2 * l + 2) * out_pitch, 0.f);
+        continue;
+      }
+      float a0 = ada_act(xb[(size_t)l * x_pitch], k, norm, act, slope);
       store_out<OutT>(ob + (size_t)(2 * l + 1) * out_pitch, a0 * w1 + pb);
-      if (l + 1 < L) {
+      if (l + 1 < Lb) {
         float a1 = ada_act(xb[(size_t)(l + 1) * x_pitch], k, norm, act, slope);
         store_out<OutT>(ob + (size_t)(2 * l + 2) * out_pitch, a0 * w2 + a1 * w0 + pb);
+      } else if (l + 1 < L) {
+        store_out<OutT>(ob + (size_t)(2 * l + 2) * out_pitch, 0.f);   // row 2 Lb: first padding row
       }
     }
   }
@@ -157,10 +166,12 @@ template <typename OutT>
 __global__ void __launch_bounds__(256)
 adain_act_vec4_kernel(const float* __restrict__ x, int x_pitch, const double* __restrict__ stats,
                       const float* __restrict__ h, int h_stride, const float* __restrict__ alpha, int act, float slope,
-                      OutT* __restrict__ out, int out_pitch, int L, int C, int rows_per_block) {
+                      OutT* __restrict__ out, int out_pitch, int L, int C, int rows_per_block,
+                      const int* __restrict__ lens, int len_mul, int len_add) {
   const int b = blockIdx.z;
   const int c = (blockIdx.x * 32 + threadIdx.x) * 4;
   if (c >= C) return;
+  const int Lb = ragged_len(lens, len_mul, len_add, b, L);
   AdaCoef k[4];
   const bool norm = stats != nullptr;
 #pragma unroll
@@ -168,8 +179,8 @@ adain_act_vec4_kernel(const float* __restrict__ x, int x_pitch, const double* __
     k[i] = AdaCoef{0.f, 1.f, 1.f, 0.f, 1.f, 1.f};
     if (norm) {
       double s = stats[((size_t)b * C + c + i) * 2], ss = stats[((size_t)b * C + c + i) * 2 + 1];
-      double mean = s / L;
-      double var = ss / L - mean * mean;
+      double mean = s / Lb;
+      double var = ss / Lb - mean * mean;
       if (var < 0.0) var = 0.0;
       k[i].mean = (float)mean;
       k[i].rstd = 1.0f / sqrtf((float)var + 1e-5f);
@@ -187,6 +198,7 @@ adain_act_vec4_kernel(const float* __restrict__ x, int x_pitch, const double* __
     float4 v = __ldg(reinterpret_cast<const float4*>(xb + (size_t)l * x_pitch));
     float y0 = ada_act(v.x, k[0], norm, act, slope), y1 = ada_act(v.y, k[1], norm, act, slope);
     float y2 = ada_act(v.z, k[2], norm, act, slope), y3 = ada_act(v.w, k[3], norm, act, slope);
+    if (l >= Lb) y0 = y1 = y2 = y3 = 0.f;   // padding rows of a ragged batch read as the next conv's zero padding
     if (sizeof(OutT) == 4) {
       *reinterpret_cast<float4*>(ob + (size_t)l * out_pitch) = make_float4(y0, y1, y2, y3);
     } else {
@@ -220,15 +232,16 @@ __global__ void transpose_cf_to_cl_kernel(const float* __restrict__ src, float* 
 // F0_conv / N_conv: ConvWeighted(1,1,k3,stride 2,padding 1) on a (B, 2T) curve (istftnet.py:933-934, :949-950)
 __global__ void f0n_conv_kernel(const float* __restrict__ f0, const float* __restrict__ nn,
                                 const float* __restrict__ wf, const float* __restrict__ wn, float* __restrict__ out,
-                                int out_pitch, int f0_off, int n_off, int B, int T) {
+                                int out_pitch, int f0_off, int n_off, int B, int T, const int* __restrict__ lens) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= B * T) return;
   int b = idx / T, t = idx - b * T;
   const float* f = f0 + (size_t)b * 2 * T;
   const float* g = nn + (size_t)b * 2 * T;
-  float fm = t > 0 ? f[2 * t - 1] : 0.f, gm = t > 0 ? g[2 * t - 1] : 0.f;
-  float vf = fm * wf[0] + f[2 * t] * wf[1] + f[2 * t + 1] * wf[2] + wf[3];
-  float vn = gm * wn[0] + g[2 * t] * wn[1] + g[2 * t + 1] * wn[2] + wn[3];
+  const int n2 = 2 * ragged_len(lens, 1, 0, b, T);          // curve samples of this utterance; beyond: zero padding
+  auto at = [&](const float* p, int j) { return (j >= 0 && j < n2) ? p[j] : 0.f; };
+  float vf = at(f, 2 * t - 1) * wf[0] + at(f, 2 * t) * wf[1] + at(f, 2 * t + 1) * wf[2] + wf[3];
+  float vn = at(g, 2 * t - 1) * wn[0] + at(g, 2 * t) * wn[1] + at(g, 2 * t + 1) * wn[2] + wn[3];
   out[(size_t)idx * out_pitch + f0_off] = vf;
   out[(size_t)idx * out_pitch + n_off] = vn;
 }
@@ -302,19 +315,21 @@ static int rows_per_block_for(int L, int B, int cblocks) {
   return rpb;
 }
 
-extern "C" int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pitch, void* stream) {
+extern "C" int kk_instnorm_stats(const float* x, double* stats, int B, int L, int C, int pitch, const int* lens,
+                                 int len_mul, int len_add, void* stream) {
   KK_CHECK_ARG(x && stats && B > 0 && L > 0 && C > 0 && pitch >= C, "kk_instnorm_stats: bad arguments");
   int cb = kk::cdiv(C, 32);
   int rpb = rows_per_block_for(L, B, cb);
   dim3 grid(cb, kk::cdiv(L, rpb), B), block(32, 8);
-  kk::instnorm_stats_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(x, stats, L, C, pitch, rpb);
+  kk::instnorm_stats_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(x, stats, L, C, pitch, rpb, lens, len_mul, len_add);
   KK_LAUNCH_CHECK("instnorm_stats_kernel");
   return KK_OK;
 }
 
 extern "C" int kk_adain_act(const float* x, int x_pitch, const double* stats, const float* h, int h_stride,
                             const float* alpha, int act, float slope, void* out, int out_is_bf16, int out_pitch,
-                            int B, int L, int C, int pool, const float* pool_w, const float* pool_b, void* stream) {
+                            int B, int L, int C, int pool, const float* pool_w, const float* pool_b, const int* lens,
+                            int len_mul, int len_add, void* stream) {
   KK_CHECK_ARG(x && out && B > 0 && L > 0 && C > 0 && x_pitch >= C && out_pitch >= C, "kk_adain_act: bad shape");
   KK_CHECK_ARG(act >= KK_ACT_NONE && act <= KK_ACT_SNAKE_FAST, "kk_adain_act: act=%d", act);
   KK_CHECK_ARG((act != KK_ACT_SNAKE && act != KK_ACT_SNAKE_FAST) || alpha, "kk_adain_act: snake needs alpha");
@@ -332,15 +347,16 @@ extern "C" int kk_adain_act(const float* x, int x_pitch, const double* stats, co
     dim3 grid4(cb4, kk::cdiv(L, rpb4), B);
     if (out_is_bf16)
       kk::adain_act_vec4_kernel<__nv_bfloat16><<<grid4, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, slope,
-                                                                        (__nv_bfloat16*)out, out_pitch, L, C, rpb4);
+                                                                        (__nv_bfloat16*)out, out_pitch, L, C, rpb4, lens,
+                                                                        len_mul, len_add);
     else
       kk::adain_act_vec4_kernel<float><<<grid4, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, slope,
-                                                                (float*)out, out_pitch, L, C, rpb4);
+                                                                (float*)out, out_pitch, L, C, rpb4, lens, len_mul, len_add);
     KK_LAUNCH_CHECK("adain_act_vec4_kernel");
     return KK_OK;
   }
 #define KK_ADA(T, P) kk::adain_act_kernel<T, P><<<grid, block, 0, st>>>(x, x_pitch, stats, h, h_stride, alpha, act, \
-    slope, (T*)out, out_pitch, L, C, pool_w, pool_b, rpb)
+    slope, (T*)out, out_pitch, L, C, pool_w, pool_b, rpb, lens, len_mul, len_add)
   if (out_is_bf16) { if (pool) KK_ADA(__nv_bfloat16, true); else KK_ADA(__nv_bfloat16, false); }
   else { if (pool) KK_ADA(float, true); else KK_ADA(float, false); }
 #undef KK_ADA
@@ -350,7 +366,7 @@ extern "C" int kk_adain_act(const float* x, int x_pitch, const double* stats, co
 
 extern "C" int kk_front_assemble(const float* asr, const float* F0_curve, const float* N, const float* f0_w3b,
                                  const float* n_w3b, float* out, int out_pitch, int asr_off, int f0_off, int n_off,
-                                 int B, int C_asr, int T, void* stream) {
+                                 int B, int C_asr, int T, const int* lens, void* stream) {
   KK_CHECK_ARG(F0_curve && N && f0_w3b && n_w3b && out && B > 0 && T > 0, "kk_front_assemble: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   if (asr) {
@@ -359,7 +375,7 @@ extern "C" int kk_front_assemble(const float* asr, const float* F0_curve, const 
     KK_LAUNCH_CHECK("transpose_cf_to_cl_kernel");
   }
   kk::f0n_conv_kernel<<<kk::cdiv((long long)B * T, 256), 256, 0, st>>>(F0_curve, N, f0_w3b, n_w3b, out, out_pitch,
-                                                                      f0_off, n_off, B, T);
+                                                                      f0_off, n_off, B, T, lens);
   KK_LAUNCH_CHECK("f0n_conv_kernel");
   return KK_OK;
 }

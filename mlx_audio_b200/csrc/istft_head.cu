@@ -19,9 +19,13 @@ __device__ constexpr float IH_WIN[20] = {0.000000000e+00f, 2.447174185e-02f, 9.5
 // inverse DFT with compile-time twiddles, cos even / sin odd symmetry) -> shared memory; then a gather-form
 // overlap-add of the 4 frames covering every output sample.
 __global__ void __launch_bounds__(IH_THREADS)
-istft_head_n20_kernel(const float* __restrict__ y, int y_pitch, float* __restrict__ audio, int F, int S) {
+istft_head_n20_kernel(const float* __restrict__ y, int y_pitch, float* __restrict__ audio, const int F_pad,
+                      const int S_pad, const int* __restrict__ lens, const int len_mul, const int len_add) {
   __shared__ float s_fr[IH_THREADS][21];
   const int b = blockIdx.y;
+  // ragged batch: this utterance has F spectrogram frames / S samples inside buffers pitched for F_pad / S_pad
+  const int F = ragged_len(lens, len_mul, len_add, b, F_pad);
+  const int S = 5 * (F - 1);
   const int g0 = blockIdx.x * IH_FT;       // first output frame; first output sample = 5*g0 (trimmed index)
   const int fbase = g0 - 1;                // u0 = 5*g0 + 10 -> u0/5 - 3
   const int f = fbase + (int)threadIdx.x;
@@ -29,7 +33,7 @@ istft_head_n20_kernel(const float* __restrict__ y, int y_pitch, float* __restric
 #pragma unroll
   for (int n = 0; n < 20; ++n) fr[n] = 0.f;
   if (f >= 0 && f < F) {
-    const float* yr = y + ((size_t)b * F + f) * y_pitch;
+    const float* yr = y + ((size_t)b * F_pad + f) * y_pitch;
     float v[22];
     if ((y_pitch & 3) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
 #pragma unroll
@@ -73,7 +77,8 @@ istft_head_n20_kernel(const float* __restrict__ y, int y_pitch, float* __restric
   // gather overlap-add: untrimmed position u = i + 10 receives frames f with 5f <= u < 5f + 20
   for (int it = threadIdx.x; it < IH_FT * 5; it += IH_THREADS) {
     const int i = 5 * g0 + it;
-    if (i >= S) break;
+    if (i >= S_pad) break;
+    if (i >= S) { audio[(size_t)b * S_pad + i] = 0.f; continue; }   // padding of a ragged batch
     const int u = i + 10;
     const int fhi = u / 5;
     float acc = 0.f, ws = 0.f;
@@ -85,18 +90,19 @@ istft_head_n20_kernel(const float* __restrict__ y, int y_pitch, float* __restric
       acc += s_fr[ff - fbase][n];
       ws += IH_WIN[n];
     }
-    audio[(size_t)b * S + i] = (ws != 0.f) ? acc / ws : acc;   // utils.py:150
+    audio[(size_t)b * S_pad + i] = (ws != 0.f) ? acc / ws : acc;   // utils.py:150
   }
 }
 
 }  // namespace kk
 
-extern "C" int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, void* stream) {
+extern "C" int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, const int* lens, int len_mul,
+                                 int len_add, void* stream) {
   KK_CHECK_ARG(y && audio && B > 0 && F > 1 && y_pitch >= 22, "kk_istft_head_n20: bad arguments");
   int S = 5 * (F - 1);
   dim3 grid(kk::cdiv(F - 1, kk::IH_FT), B);
   KK_CHECK_ARG(grid.y <= 65535, "kk_istft_head_n20: batch too large");
-  kk::istft_head_n20_kernel<<<grid, kk::IH_THREADS, 0, (cudaStream_t)stream>>>(y, y_pitch, audio, F, S);
+  kk::istft_head_n20_kernel<<<grid, kk::IH_THREADS, 0, (cudaStream_t)stream>>>(y, y_pitch, audio, F, S, lens, len_mul, len_add);
   KK_LAUNCH_CHECK("istft_head_n20_kernel");
   return KK_OK;
 }

@@ -89,12 +89,17 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
                                    const float* __restrict__ noise, unsigned long long seed,
                                    const unsigned long long* __restrict__ seed_dev,
                                    const float* __restrict__ lin_w, const float* __restrict__ lin_b,
-                                   float* __restrict__ out, int B, int T2, int upsample, float inv_up, float half_inv_up) {
-  const long long S = (long long)T2 * upsample;
+                                   float* __restrict__ out, int B, int T2_pad, int upsample, float inv_up, float half_inv_up,
+                                   const int* __restrict__ lens) {
+  const long long S = (long long)T2_pad * upsample;
   long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long long)B * S) return;
   int b = (int)(idx / S);
   int i = (int)(idx - (long long)b * S);
+  // ragged batch: this utterance has T2 f0 samples (the interpolation clamps / wraps at ITS last frame); the rest of the
+  // padded row is silence
+  const int T2 = ragged_len(lens, 2, 0, b, T2_pad);
+  if (i >= T2 * upsample) { out[idx] = 0.f; return; }
   // x = ((float(i) * fl32(1/300)) + fl32(1/600)) - 0.5
   float x = __fsub_rn(__fadd_rn(__fmul_rn((float)i, inv_up), half_inv_up), 0.5f);
   float lo_f = floorf(x);
@@ -103,7 +108,7 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
   int hi = min(lo + 1, T2 - 1);
   if (lo < 0) lo += T2;  // MLX gather wraps index -1 to the last frame
   float one_m = __fsub_rn(1.0f, fr);
-  float f0v = f0[(size_t)b * T2 + i / upsample];
+  float f0v = f0[(size_t)b * T2_pad + i / upsample];
   bool voiced = f0v > 10.0f;                          // voiced_threshold 10 (:716, :553)
   float amp = voiced ? 0.003f : __fdiv_rn(0.1f, 3.0f);  // uv*noise_std + (1-uv)*sine_amp/3 (:619)
 
@@ -123,13 +128,13 @@ __global__ void hnsf_sample_kernel(const float* __restrict__ f0, const float* __
     }
   }
   float acc = 0.f;
-  const float* pb = phase + (size_t)b * NH * T2;
+  const float* pb = phase + (size_t)b * NH * T2_pad;
 #pragma unroll
   for (int k = 0; k < NH; ++k) {
     float hk = __fmul_rn(amp, nz[k]);
     if (voiced) {   // sine * uv: unvoiced samples never see the sine (uv = 0, :622) - and f0 is constant over 300
                     // consecutive samples, so the branch is warp-uniform but for the segment edges
-      const float* p = pb + (size_t)k * T2;
+      const float* p = pb + (size_t)k * T2_pad;
       float ph = __fadd_rn(__fmul_rn(p[lo], one_m), __fmul_rn(p[hi], fr));  // interpolate.py:106
       float sine = __fmul_rn(sin_large(ph), 0.1f);                           // :579, :613
       hk = __fadd_rn(sine, hk);
@@ -146,17 +151,21 @@ constexpr int ST_FR = 128;   // frames per block (= threads)
 
 __global__ void __launch_bounds__(ST_FR)
 stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_pitch,
-                __nv_bfloat16* __restrict__ har16, int pitch16, int rows16, int B, int S, int F,
-                const Dft20Tables tb) {
+                __nv_bfloat16* __restrict__ har16, int pitch16, int rows16, int B, const int S_pad, const int F_pad,
+                const Dft20Tables tb, const int* __restrict__ lens, const int len_mul) {
   // block = 128 consecutive frames of one utterance: the 655 samples they cover are staged in shared memory
   // (coalesced reads) and, when the bf16 rows are 24 wide, so is the output (128 x 48 B = 6 KB contiguous)
   __shared__ float s_in[ST_FR * 5 + 16];
   __shared__ __align__(16) __nv_bfloat16 s_out[ST_FR * 24];
-  const int blocks_per_b = (F + ST_FR - 1) / ST_FR;
+  const int blocks_per_b = (F_pad + ST_FR - 1) / ST_FR;
   const int b = blockIdx.x / blocks_per_b;
   const int f0 = (blockIdx.x - b * blocks_per_b) * ST_FR;
   const int f = f0 + threadIdx.x;
-  const float* x = sig + (size_t)b * S;
+  // ragged batch: S samples / F frames of this utterance inside rows pitched for S_pad / F_pad; the reflect pad mirrors
+  // at S, frames in [F, F_pad) are written as zeros (the convolutions that read them expect zero padding)
+  const int S = ragged_len(lens, len_mul, 0, b, S_pad);   // len_mul = samples per frame
+  const int F = S / 5 + 1;
+  const float* x = sig + (size_t)b * S_pad;
   for (int i = threadIdx.x; i < ST_FR * 5 + 15; i += ST_FR) {
     int p = 5 * f0 + i - 10;
     if (p < 0) p = -p;                       // reflect without edge repeat (utils.py:81-84)
@@ -164,12 +173,13 @@ stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_
     s_in[i] = (p >= 0 && p < S) ? x[p] : 0.f;   // (frames past F are not stored)
   }
   __syncthreads();
-  const bool live = f < F;
+  const bool live = f < F_pad;          // row exists in the output tensors
+  const bool real = f < F;              // ... and is a frame of this utterance
   float v[20];
 #pragma unroll
-  for (int n = 0; n < 20; ++n) v[n] = s_in[5 * threadIdx.x + n] * tb.win[n];
+  for (int n = 0; n < 20; ++n) v[n] = real ? s_in[5 * threadIdx.x + n] * tb.win[n] : 0.f;
   const bool staged = har16 && pitch16 == 24;
-  float* o = (har && live) ? har + ((size_t)b * F + f) * har_pitch : nullptr;
+  float* o = (har && live) ? har + ((size_t)b * F_pad + f) * har_pitch : nullptr;
   __nv_bfloat16* o16 = (har16 && live && !staged) ? har16 + ((size_t)b * rows16 + f) * pitch16 : nullptr;
   __nv_bfloat16* os = s_out + threadIdx.x * 24;
 #pragma unroll
@@ -193,7 +203,7 @@ stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_
   if (staged) {
     os[22] = os[23] = __float2bfloat16(0.f);
     __syncthreads();
-    const int nf = min(ST_FR, F - f0);               // live frames of this block
+    const int nf = min(ST_FR, F_pad - f0);           // live frames of this block
     const int n16 = nf * 3;                          // 16-byte chunks (48 B per frame)
     uint4* dst = reinterpret_cast<uint4*>(har16 + ((size_t)b * rows16 + f0) * 24);   // 16-byte aligned: f0 % 128 == 0
     const uint4* src = reinterpret_cast<const uint4*>(s_out);
@@ -205,7 +215,8 @@ stft_n20_kernel(const float* __restrict__ sig, float* __restrict__ har, int har_
 
 extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed,
                               const unsigned long long* seed_dev, const float* lin_w, const float* lin_b,
-                              float* phase_ws, float* har_source, int B, int T2, int upsample, void* stream) {
+                              float* phase_ws, float* har_source, int B, int T2, int upsample, const int* lens,
+                              void* stream) {
   KK_CHECK_ARG(f0 && lin_w && lin_b && phase_ws && har_source, "kk_hnsf_source: null pointer");
   KK_CHECK_ARG(B > 0 && T2 > 1 && upsample > 1, "kk_hnsf_source: bad shape B=%d T2=%d up=%d", B, T2, upsample);
   KK_CHECK_ARG((long long)T2 * upsample < (1LL << 24), "kk_hnsf_source: utterance too long for float32 sample index");
@@ -217,13 +228,13 @@ extern "C" int kk_hnsf_source(const float* f0, const float* noise, unsigned long
   float half_inv_up = (float)(0.5 * (1.0 / (double)upsample));
   long long total = (long long)B * T2 * upsample;
   kk::hnsf_sample_kernel<<<kk::cdiv(total, 256), 256, 0, st>>>(f0, phase_ws, noise, seed, seed_dev, lin_w, lin_b, har_source, B,
-                                                              T2, upsample, inv_up, half_inv_up);
+                                                              T2, upsample, inv_up, half_inv_up, lens);
   KK_LAUNCH_CHECK("hnsf_sample_kernel");
   return KK_OK;
 }
 
 static int stft_n20_launch(const float* har_source, float* har, int har_pitch, void* har16, int pitch16, int rows16,
-                           int B, int S, void* stream) {
+                           int B, int S, const int* lens, int len_mul, void* stream) {
   kk::Dft20Tables tb;
   for (int n = 0; n < 20; ++n) {
     tb.win[n] = (float)(0.5 * (1.0 - cos(2.0 * M_PI * n / 19.0)));  // symmetric hanning(20) utils.py:11-14
@@ -235,21 +246,22 @@ static int stft_n20_launch(const float* har_source, float* har, int har_pitch, v
   (void)total;
   const int blocks = B * ((F + kk::ST_FR - 1) / kk::ST_FR);
   kk::stft_n20_kernel<<<blocks, kk::ST_FR, 0, (cudaStream_t)stream>>>(
-      har_source, har, har_pitch, (__nv_bfloat16*)har16, pitch16, rows16, B, S, F, tb);
+      har_source, har, har_pitch, (__nv_bfloat16*)har16, pitch16, rows16, B, S, F, tb, lens, len_mul);
   KK_LAUNCH_CHECK("stft_n20_kernel");
   return KK_OK;
 }
 
-extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, void* stream) {
+extern "C" int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, const int* lens, int len_mul,
+                           void* stream) {
   KK_CHECK_ARG(har_source && har && B > 0 && S > 10 && har_pitch >= 22 && S % 5 == 0, "kk_stft_n20: bad arguments");
-  return stft_n20_launch(har_source, har, har_pitch, nullptr, 0, 0, B, S, stream);
+  return stft_n20_launch(har_source, har, har_pitch, nullptr, 0, 0, B, S, lens, len_mul, stream);
 }
 
 extern "C" int kk_stft_n20_bf16(const float* har_source, float* har, int har_pitch, void* har_bf16, int bf_pitch,
-                                int bf_rows, int B, int S, void* stream) {
+                                int bf_rows, int B, int S, const int* lens, int len_mul, void* stream) {
   KK_CHECK_ARG(har_source && har_bf16 && B > 0 && S > 10 && S % 5 == 0, "kk_stft_n20_bf16: bad arguments");
   KK_CHECK_ARG(bf_pitch != 24 || ((uintptr_t)har_bf16 & 15) == 0, "kk_stft_n20_bf16: har_bf16 must be 16-byte aligned");
   KK_CHECK_ARG((!har || har_pitch >= 22) && bf_pitch >= 22 && bf_rows >= S / 5 + 1,
                "kk_stft_n20_bf16: pitch / rows too small (bf_rows %d < frames %d)", bf_rows, S / 5 + 1);
-  return stft_n20_launch(har_source, har, har_pitch, har_bf16, bf_pitch, bf_rows, B, S, stream);
+  return stft_n20_launch(har_source, har, har_pitch, har_bf16, bf_pitch, bf_rows, B, S, lens, len_mul, stream);
 }

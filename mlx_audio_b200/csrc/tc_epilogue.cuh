@@ -65,7 +65,7 @@ __device__ __forceinline__ void epi_prefetch_chunk(const kk_conv_desc& d, const 
 // the prefetch of the NEXT chunk (has_next: tile origin (nx_m0, nx_n0) of utterance nx_b, chunk nx_ch) is issued so
 // that its latency hides behind this chunk's TMEM read, arithmetic and stores.
 template <int BN>
-__device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int b, const int m0, const int n0,
+__device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const EpiLim lim, const int b, const int m0, const int n0,
                                                const int ch, const int lg, const int lane, const uint32_t tmem_base,
                                                float* stage_w, const bool do_stats, float& col_sum, float& col_sq,
                                                float4 (&t)[8], const bool has_next, const int nx_b, const int nx_m0,
@@ -89,9 +89,10 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
       ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32), v);
       ptx::tmem_ld_wait();
       const int j = m * d.up + ph - d.up_off;
-      const bool acc_valid = (j >= 0) && (j < d.L_true);
+      const bool acc_valid = (j >= 0) && (j < lim.lt);
       const int out_row = j + d.left_pad;
-      const bool row_ok = (m < d.M) && (out_row >= 0) && (out_row < d.L_out);
+      const bool row_ok = (m < d.M) && (out_row >= 0) && (out_row < d.L_out);   // row exists in the tensors
+      const bool row_live = row_ok && out_row < lim.lo;                         // ... and belongs to the utterance
       const size_t orow = (size_t)b * d.L_out + (row_ok ? out_row : 0);
       const float* resp = d.res ? d.res + ((size_t)b * d.L_res + ((row_ok ? out_row : 0) >> d.res_shift)) * d.res_pitch + cbase : nullptr;
       const float* res2p = d.res2 ? d.res2 + orow * d.res2_pitch + cbase : nullptr;
@@ -111,10 +112,10 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
             float x1 = acc_valid ? v[c4 * 4 + 1] + bs.y : 0.f;
             float x2 = acc_valid ? v[c4 * 4 + 2] + bs.z : 0.f;
             float x3 = acc_valid ? v[c4 * 4 + 3] + bs.w : 0.f;
-            x0 = row_ok ? (x0 + rr.x) * d.scale : 0.f;
-            x1 = row_ok ? (x1 + rr.y) * d.scale : 0.f;
-            x2 = row_ok ? (x2 + rr.z) * d.scale : 0.f;
-            x3 = row_ok ? (x3 + rr.w) * d.scale : 0.f;
+            x0 = row_live ? (x0 + rr.x) * d.scale : 0.f;
+            x1 = row_live ? (x1 + rr.y) * d.scale : 0.f;
+            x2 = row_live ? (x2 + rr.z) * d.scale : 0.f;
+            x3 = row_live ? (x3 + rr.w) * d.scale : 0.f;
             v[c4 * 4 + 0] = x0; v[c4 * 4 + 1] = x1; v[c4 * 4 + 2] = x2; v[c4 * 4 + 3] = x3;
           }
         }
@@ -159,7 +160,7 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
       for (int i = 0; i < 32; ++i) {
         const bool col_ok = (nb + i) < d.N;
         float x = 0.f;
-        if (row_ok && col_ok) {
+        if (row_live && col_ok) {
           if (acc_valid) x = v[i] + (d.bias ? __ldg(d.bias + cbase + i) : 0.f);
           if (resp) x += __ldg(resp + i);
           if (res2p) x += __ldg(res2p + i);
@@ -248,32 +249,36 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const int 
 constexpr int EPI_TILE_BYTES = 4096;
 constexpr int EPI_NBUF = 2;        // staging tiles per epilogue warp = residual prefetch distance
 
-struct EpiRow { int ph, cbase, out_row; bool acc_valid, row_ok; };
+struct EpiRow { int ph, cbase, out_row; bool acc_valid, row_ok, live; };
 
-__device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const int m, const int nb) {
+// row_ok: the row exists in the tensors; live: ... and belongs to the utterance (ragged batches: rows in
+// [lim.lo, L_out) are padding - stored as zero, never counted)
+__device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const EpiLim& lim, const int m, const int nb) {
   EpiRow e;
   e.ph = 0; e.cbase = nb;
   if (d.up > 1) { e.ph = nb / d.C_out; e.cbase = nb - e.ph * d.C_out; }
   const int j = m * d.up + e.ph - d.up_off;
-  e.acc_valid = (j >= 0) && (j < d.L_true);
+  e.acc_valid = (j >= 0) && (j < lim.lt);
   e.out_row = j + d.left_pad;
   e.row_ok = (m < d.M) && (e.out_row >= 0) && (e.out_row < d.L_out);
+  e.live = e.row_ok && e.out_row < lim.lo;
   return e;
 }
 
 // warp-uniform: do rows m0w .. m0w+31 of the chunk starting at column nb all land inside the utterance (and inside
 // the true convolution output, so that no element needs masking)?
-__device__ __forceinline__ bool epi_interior(const kk_conv_desc& d, const int m0w, const int nb) {
+__device__ __forceinline__ bool epi_interior(const kk_conv_desc& d, const EpiLim& lim, const int m0w, const int nb) {
   const int ph = d.up > 1 ? nb / d.C_out : 0;
   const int j0 = m0w * d.up + ph - d.up_off, r0 = j0 + d.left_pad;
-  return m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < d.L_out && j0 >= 0 && j0 + 31 * d.up < d.L_true;
+  return m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < lim.lo && j0 >= 0 && j0 + 31 * d.up < lim.lt;
 }
 
 // all lanes: start the residual transfer of the chunk whose first column is nb, rows m0w..m0w+31 (lane = row)
 __device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const CUtensorMap* tmRes, const int b, const int m0w,
                                               const int nb, const int lane, uint8_t* st, uint64_t* bar) {
-  const EpiRow e = epi_row(d, m0w + lane, nb);
-  if (d.res_shift == 0 && epi_interior(d, m0w, nb)) {
+  const EpiLim lim = epi_lim(d, b);
+  const EpiRow e = epi_row(d, lim, m0w + lane, nb);
+  if (d.res_shift == 0 && epi_interior(d, lim, m0w, nb)) {
     if (lane == 0) {
       ptx::mbar_expect_tx(bar, EPI_TILE_BYTES);
       ptx::tma_load_4d(st, tmRes, bar, e.cbase, e.ph, m0w, b);
@@ -290,13 +295,13 @@ __device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const CUten
 
 // INTERIOR: no masking anywhere, swizzled tile, box transfers.  Otherwise: per-element masks, plain tile, row copies.
 template <bool INTERIOR>
-__device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, const CUtensorMap* tmOut,
+__device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, const EpiLim lim, const CUtensorMap* tmOut,
                                                         const CUtensorMap* tmAct, uint8_t* act_tile, const int b,
                                                         const int m0w, const int nb, const int lane,
                                                         const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
                                                         const uint32_t rparity, const bool do_stats, float& col_sum,
                                                         float& col_sq) {
-  const EpiRow e = epi_row(d, m0w + lane, nb);
+  const EpiRow e = epi_row(d, lim, m0w + lane, nb);
   constexpr int WSW = INTERIOR ? 7 : 0;                                  // swizzle mask of the result tile
   const int rsw = (INTERIOR && d.res_shift == 0) ? 7 : 0;               // ... and of the tile as the residual arrived
   const bool acc_valid = INTERIOR || e.acc_valid, row_ok = INTERIOR || e.row_ok;
@@ -331,7 +336,7 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
         if (d.res && row_ok) rr = rrow[c4];
         v[c4 * 4 + 0] = rr.x; v[c4 * 4 + 1] = rr.y; v[c4 * 4 + 2] = rr.z; v[c4 * 4 + 3] = rr.w;
       }
-      if (!row_ok) v[c4 * 4 + 0] = v[c4 * 4 + 1] = v[c4 * 4 + 2] = v[c4 * 4 + 3] = 0.f;
+      if (!e.live) v[c4 * 4 + 0] = v[c4 * 4 + 1] = v[c4 * 4 + 2] = v[c4 * 4 + 3] = 0.f;
     }
   }
   if (d.scale != 1.0f) {
@@ -412,10 +417,11 @@ __device__ __forceinline__ void epilogue_chunk_direct(const kk_conv_desc& d, con
                                                       const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
                                                       const uint32_t rparity, const bool do_stats, float& col_sum,
                                                       float& col_sq) {
-  if (epi_interior(d, m0w, nb))
-    epilogue_chunk_direct_t<true>(d, tmOut, tmAct, act_tile, b, m0w, nb, lane, tmem_addr, st, rbar, rparity, do_stats, col_sum, col_sq);
+  const EpiLim lim = epi_lim(d, b);
+  if (epi_interior(d, lim, m0w, nb))
+    epilogue_chunk_direct_t<true>(d, lim, tmOut, tmAct, act_tile, b, m0w, nb, lane, tmem_addr, st, rbar, rparity, do_stats, col_sum, col_sq);
   else
-    epilogue_chunk_direct_t<false>(d, tmOut, tmAct, act_tile, b, m0w, nb, lane, tmem_addr, st, rbar, rparity, do_stats, col_sum, col_sq);
+    epilogue_chunk_direct_t<false>(d, lim, tmOut, tmAct, act_tile, b, m0w, nb, lane, tmem_addr, st, rbar, rparity, do_stats, col_sum, col_sq);
 }
 
 }  // namespace kk

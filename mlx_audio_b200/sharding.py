@@ -132,20 +132,50 @@ def assign_buckets(frames: Sequence[int], world: int, max_batch: int) -> List[Li
     return [sorted(a, key=lambda b: (-b[0], b[1][0])) for a in out]
 
 
+def assign_ragged(frames: Sequence[int], world: int, max_batch: int, bucket: int = 32) -> List[List[Tuple[int, List[int]]]]:
+    """Mixed-length batches for ``Decoder.__call__(..., lengths=)``: the utterances, sorted by length, are dealt to the
+    ranks in snake order (every rank sees the same length distribution: near-equal load without moving single
+    utterances afterwards), and each rank cuts its sorted share into batches of ``max_batch`` (the short remainder
+    last).  A batch is padded to its longest utterance rounded up to a multiple of ``bucket`` frames, so that a corpus
+    needs a handful of launch plans (one per (batch size, padded length)) instead of one per distinct length; the
+    padding costs no convolution work (the kernels build their tile lists from the lengths).  Deterministic on every
+    rank.  Returns per rank [(T_padded, [utterance indices])], longest first."""
+    if world < 1 or max_batch < 1 or bucket < 1:
+        raise ValueError("world, max_batch and bucket must be >= 1")
+    order = sorted(range(len(frames)), key=lambda i: (-int(frames[i]), i))
+    share: List[List[int]] = [[] for _ in range(world)]
+    for k, i in enumerate(order):
+        rnd, pos = divmod(k, world)
+        share[pos if rnd % 2 == 0 else world - 1 - pos].append(i)
+    out: List[List[Tuple[int, List[int]]]] = []
+    for ids in share:
+        batches = []
+        for k in range(0, len(ids), max_batch):
+            sel = ids[k:k + max_batch]
+            t = max(int(frames[i]) for i in sel)
+            batches.append((-(-t // bucket) * bucket, sel))
+        out.append(batches)
+    return out
+
+
 def decode_sharded(decode_batch: Callable[[int, List[int]], torch.Tensor], frames: Sequence[int], max_batch: int = 64,
-                   dst: int = 0, group=None) -> Optional[List[torch.Tensor]]:
+                   dst: int = 0, group=None, ragged: bool = False, bucket: int = 32) -> Optional[List[torch.Tensor]]:
     """Decode ``len(frames)`` utterances over all ranks.  ``decode_batch(T, ids)`` must return the (len(ids), 1,
-    600*T) waveforms of utterances ``ids`` (all of length T) - on the GPU path it is ``Decoder.__call__`` on
-    the rank's own inputs.  Batches are formed and balanced by ``assign_buckets``; each rank writes its waveforms
-    straight into ONE flat buffer (batch order), which is what the gather sends.  Returns the utterance-ordered
-    waveform list on ``dst`` (views of the received buffers), None elsewhere."""
+    600*T) waveforms of utterances ``ids`` - on the GPU path it is ``Decoder.__call__`` on the rank's own inputs.
+    ``ragged=False``: batches hold utterances of ONE length T (``assign_buckets``); ``ragged=True``: mixed lengths padded
+    to T (``assign_ragged``; ``decode_batch`` passes ``lengths=`` and the waveform of utterance i is the first
+    600*frames[i] samples of its row).  Each rank writes its batches straight into ONE flat buffer, which is what the
+    gather sends (ragged: the padded rows travel, <= bucket/2 frames of padding per utterance on average).  Returns the
+    utterance-ordered waveform list on ``dst`` (views of the received buffers), None elsewhere."""
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    plan = assign_buckets(frames, world, max_batch)
+    plan = assign_ragged(frames, world, max_batch, bucket) if ragged else assign_buckets(frames, world, max_batch)
     assignment = [[i for _, ids in plan[r] for i in ids] for r in range(world)]
+    # samples each utterance occupies in its rank's flat buffer (its row's padded length), and the samples that count
+    pitch = [[t * SAMPLES_PER_FRAME for t, ids in plan[r] for _ in ids] for r in range(world)]
     flat: Optional[torch.Tensor] = None
     off = 0
-    total = sum(int(frames[i]) for i in assignment[rank]) * SAMPLES_PER_FRAME
+    total = sum(pitch[rank])
     for t, ids in plan[rank]:
         y = decode_batch(t, ids)
         if y.shape[0] != len(ids) or y.shape[-1] != t * SAMPLES_PER_FRAME:
@@ -158,15 +188,32 @@ def decode_sharded(decode_batch: Callable[[int, List[int]], torch.Tensor], frame
     if flat is None:   # this rank owns no utterances (fewer batches than ranks)
         on_gpu = dist.is_initialized() and dist.get_backend(group) == "nccl"
         flat = torch.empty(0, dtype=torch.float32, device=torch.device("cuda", torch.cuda.current_device()) if on_gpu else "cpu")
-    local: Dict[int, torch.Tensor] = {}
-    off = 0
-    for i in assignment[rank]:
-        n = int(frames[i]) * SAMPLES_PER_FRAME
-        local[i] = flat[off:off + n]
-        off += n
+
+    def views(buf: torch.Tensor, r: int) -> Dict[int, torch.Tensor]:
+        o, res = 0, {}
+        for i, p in zip(assignment[r], pitch[r]):
+            res[i] = buf[o:o + int(frames[i]) * SAMPLES_PER_FRAME]
+            o += p
+        return res
+
     if world == 1:
+        local = views(flat, 0)
         return [local[i] for i in range(len(frames))]
-    return gather_waveforms(local, frames, assignment, dst=dst, group=group, packed=flat)
+    if rank != dst:
+        if flat.numel():
+            dist.send(flat, dst=dst, group=group)
+        return None
+    out: List[Optional[torch.Tensor]] = [None] * len(frames)
+    for r in range(world):
+        if r == dst:
+            buf = flat
+        else:
+            buf = torch.empty(sum(pitch[r]), dtype=torch.float32, device=flat.device)
+            if buf.numel():
+                dist.recv(buf, src=r, group=group)
+        for i, v in views(buf, r).items():
+            out[i] = v
+    return out  # type: ignore[return-value]
 
 
 class OverlappedGather:

@@ -82,10 +82,21 @@ class Plan:
         self.capture = False
         self.zero_bufs: List[torch.Tensor] = []  # buffers whose pad rows / columns must read as zero
         self.conv_ops: Dict[int, ConvDesc] = {}  # op index -> descriptor (for FLOP accounting)
+        # ragged batch (per-utterance frame counts in one launch, kokoro_b200.h): device address of the (B,) int32
+        # lengths, and the row count of every level as (mul, add): rows = mul * frames + add
+        self.lens_addr: Optional[int] = None
+        self.levels: Dict[int, Tuple[int, int]] = {}
 
     def add(self, fn, *args, launches: int = 1):
         self.ops.append((fn, args))
         self.n_launches += launches
+
+    def lens(self, rows: int) -> Tuple[Optional[int], int, int]:
+        """(lens, len_mul, len_add) arguments of a kernel working on `rows` rows per (padded) utterance."""
+        if self.lens_addr is None:
+            return None, 0, 0
+        mul, add = self.levels[rows]
+        return self.lens_addr, mul, add
 
     def stage(self, name: str):
         """Stage boundary (front / source / stage0 / stage1 / post): an NVTX range when KK_NVTX=1 - the counterpart of the
@@ -358,6 +369,7 @@ class DecoderEngine:
         d.stats = stats_addr
         if out_act is not None:
             d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
+        d.lens, d.len_mul, d.len_add = plan.lens(d.L_true)
         plan.keep.append(d)
         plan.conv_ops[len(plan.ops)] = d
         if use_tc:
@@ -413,6 +425,7 @@ class DecoderEngine:
             d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
         if out_add is not None:
             d.out_add, d.add_pitch = out_add
+        d.lens, d.len_mul, d.len_add = plan.lens(L_)
         plan.keep.extend([a, d])
         plan.conv_ops[len(plan.ops)] = d
         plan.add(self.lib.kk_conv1d_adain_bf16_tc, C.byref(a), self._addr(pc.w16), C.byref(d))
@@ -425,7 +438,7 @@ class DecoderEngine:
         plan.add(self.lib.kk_adain_act, x_addr, x_pitch, stats_addr, h_addr, self.ada_R,
                  self._addr(alpha), act, slope, self._addr(out), 1 if out.dtype == torch.bfloat16 else 0, out_pitch,
                  B, L_, C_, 1 if pool else 0, self._addr(self.pools[pool][0]) if pool else None,
-                 self._addr(self.pools[pool][1]) if pool else None)
+                 self._addr(self.pools[pool][1]) if pool else None, *plan.lens(L_))
 
     def _tap(self, plan: Plan, name: str, t: torch.Tensor, view: Optional[Callable] = None):
         plan.taps[name] = (t, view)
@@ -520,7 +533,7 @@ class DecoderEngine:
         adt = self._act_dtype()
         api, apo = self._act_pitch(C_in), self._act_pitch(C_out)
         st_in = self._stats(plan, B, C_in)
-        plan.add(self.lib.kk_instnorm_stats, x_in_addr, st_in, B, L_, C_in, x_pitch)
+        plan.add(self.lib.kk_instnorm_stats, x_in_addr, st_in, B, L_, C_in, x_pitch, *plan.lens(L_))
         act1 = self._buf(plan, f"{name}.act1", (B, Lo, api), adt, zero=True)
         self._ada(plan, x_in_addr, x_pitch, st_in, f"{prefix}.norm1", L.KK_ACT_LEAKY, 0.2, None, act1, api, B, L_, C_in,
                   h_all, pool=prefix if upsample else None)
@@ -548,8 +561,9 @@ class DecoderEngine:
                    out_addr=out_addr, out_pitch=out_pitch, res=sc_res, scale=1.0 / math.sqrt(2.0), out_act=out_act)
 
     # ------------------------------------------------------------------ the whole decoder
-    def build_plan(self, B: int, T: int) -> Plan:
-        """Decoder.__call__ (istftnet.py:947-963) + Generator.__call__ (:769-807) for a fixed (B, T)."""
+    def build_plan(self, B: int, T: int, ragged: bool = False) -> Plan:
+        """Decoder.__call__ (istftnet.py:947-963) + Generator.__call__ (:769-807) for a fixed (B, T).  ``ragged``: the
+        batch is padded to T frames and every kernel takes the per-utterance frame counts (buffer ``in.lens``)."""
         cfg, lib = self.cfg, self.lib
         plan = Plan()
         T2, up = 2 * T, self.up_scale
@@ -566,8 +580,11 @@ class DecoderEngine:
         f0c = self._buf(plan, "in.F0_curve", (B, T2))
         nc = self._buf(plan, "in.N", (B, T2))
         s = self._buf(plan, "in.s", (B, cfg["style_dim"]))
-        noise = self._buf(plan, "in.noise", (B, S, 9)) if False else None
-        plan.noise_buf = noise
+        if ragged:
+            plan.lens_addr = self._addr(self._buf(plan, "in.lens", (B,), torch.int32))
+            plan.levels = {T: (1, 0), T2: (2, 0), L20: (r0 * 2, 0), L3 - 1: (r0 * r1 * 2, 0), L3: (r0 * r1 * 2, 1)}
+            assert len(plan.levels) == 5, "level row counts must be distinct"
+        lens_addr = plan.lens_addr
         h_all = self._buf(plan, "h_all", (B, self.ada_R))
         plan.stage("front")
         plan.add(lib.kk_style_affine, self._addr(s), self._addr(self.ada_W), self._addr(self.ada_b), self._addr(h_all),
@@ -579,9 +596,9 @@ class DecoderEngine:
         xcat0 = self._buf(plan, "xcat0", (B, T, p_cat0), zero=True)
         xcat = self._buf(plan, "xcat", (B, T, p_cat))
         plan.add(lib.kk_front_assemble, self._addr(asr), self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
-                 self._addr(self.n_w3b), self._addr(xcat0), p_cat0, 0, din, din + 1, B, din, T, launches=2)
+                 self._addr(self.n_w3b), self._addr(xcat0), p_cat0, 0, din, din + 1, B, din, T, lens_addr, launches=2)
         plan.add(lib.kk_front_assemble, None, self._addr(f0c), self._addr(nc), self._addr(self.f0_w3b),
-                 self._addr(self.n_w3b), self._addr(xcat), p_cat, 0, 1024 + 64, 1024 + 65, B, din, T)
+                 self._addr(self.n_w3b), self._addr(xcat), p_cat, 0, 1024 + 64, 1024 + 65, B, din, T, lens_addr)
         self._conv(plan, self.convs["asr_res.0"], self._addr(xcat0), B, T, p_cat0, T,
                    out_addr=self._addr(xcat, 1024), out_pitch=p_cat, force_f32=True)  # :953
         self._adain_resblk1d(plan, "encode", B, T, c_cat0, 1024, h_all, self._addr(xcat0), p_cat0, self._addr(xcat),
@@ -607,7 +624,7 @@ class DecoderEngine:
         # draws fresh noise per call like the reference's mx.random.normal (istftnet.py:620)
         seed_buf = self._buf(plan, "seed", (1,), torch.int64)
         plan.add(lib.kk_hnsf_source, self._addr(f0c), None, 0, self._addr(seed_buf), self._addr(self.lin_w), self._addr(self.lin_b),
-                 self._addr(phase_ws), self._addr(har_source), B, T2, up, launches=2)
+                 self._addr(phase_ws), self._addr(har_source), B, T2, up, lens_addr, launches=2)
         har16 = None
         har_rows = r1 * (L20 + 1)       # rows of the bf16 copy: whole 6-frame rows for the stride-6 noise conv
         if self.tc:
@@ -617,9 +634,9 @@ class DecoderEngine:
             plan.stft_op_index = len(plan.ops)
             plan.har_addr = self._addr(har)
             plan.add(lib.kk_stft_n20_bf16, self._addr(har_source), self._addr(har), 24, self._addr(har16), 24, har_rows,
-                     B, S)
+                     B, S, lens_addr, S // T)
         else:
-            plan.add(lib.kk_stft_n20, self._addr(har_source), self._addr(har), 24, B, S)
+            plan.add(lib.kk_stft_n20, self._addr(har_source), self._addr(har), 24, B, S, lens_addr, S // T)
         self._tap(plan, "har_source", har_source)
         self._tap(plan, "har", har, lambda t: t[:, :, :22].transpose(1, 2))
         # ---- generator stages (:776-796)
@@ -707,6 +724,6 @@ class DecoderEngine:
                        out_addr=self._addr(ypost), out_pitch=24)
         self._tap(plan, "conv_post", ypost, lambda t: t[:, :, :22].transpose(1, 2))
         audio = self._buf(plan, "audio", (B, 1, S))
-        plan.add(lib.kk_istft_head_n20, self._addr(ypost), 24, self._addr(audio), B, L3)
+        plan.add(lib.kk_istft_head_n20, self._addr(ypost), 24, self._addr(audio), B, L3, *plan.lens(L3))
         plan.shape = (B, T)
         return plan

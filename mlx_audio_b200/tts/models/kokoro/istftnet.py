@@ -112,13 +112,13 @@ class Decoder:
         return self._engine
 
     # ------------------------------------------------------------------ forward
-    def _plan(self, B: int, T: int) -> Plan:
+    def _plan(self, B: int, T: int, ragged: bool = False) -> Plan:
         eng = self.engine
-        key = (B, T)
+        key = (B, T, ragged)
         plan = eng.plans.get(key)
         if plan is None:
             eng.pool_grew = False
-            plan = eng.build_plan(B, T)
+            plan = eng.build_plan(B, T, ragged)
             if eng.pool_grew:
                 # a workspace buffer was re-allocated: plans (and graphs) built against the old one would keep it
                 # alive, so they are dropped and rebuilt on demand (call reserve(B_max, T_max) first to avoid this)
@@ -127,15 +127,21 @@ class Decoder:
             eng.plans[key] = plan
         return plan
 
-    def reserve(self, B: int, T: int) -> None:
+    def reserve(self, B: int, T: int, ragged: bool = False) -> None:
         """Size the shared workspace for the largest (B, T) the caller will decode (ragged / bucketed workloads)."""
-        self._plan(B, T)
+        self._plan(B, T, ragged)
 
     def __call__(self, asr, F0_curve, N, s, *, noise=None, seed: Optional[int] = None, capture_taps: bool = False,
-                 borrow: bool = False):
+                 borrow: bool = False, lengths=None):
         """Returns a fresh (B, 1, 600 T) tensor like the reference (istftnet.py:963).  ``borrow=True`` hands out the
         decoder's persistent output buffer instead (zero copy): it is overwritten by the next call of ANY shape, so only
-        callers that consume it before calling again (StreamingDecoder, decode_sharded, bench.py) should ask for it."""
+        callers that consume it before calling again (StreamingDecoder, decode_sharded, bench.py) should ask for it.
+
+        ``lengths`` (B,) ints: a RAGGED batch - utterance b has ``lengths[b] <= T`` asr frames, the inputs are padded to
+        T (the padding's content is irrelevant).  Every kernel of the one launch plan masks per utterance (padding rows
+        are the convolutions' zero padding and stay out of the instance-norm statistics), so ``out[b, 0, :600 *
+        lengths[b]]`` equals decoding utterance b alone - the reference decodes one utterance per call
+        (kokoro.py:135-165) - and ``out[b, 0, 600 * lengths[b]:]`` is zero."""
         L.require_cuda()
         dev = self.device
         asr = _to_cuda_f32(asr, dev)
@@ -149,9 +155,19 @@ class Decoder:
             raise ValueError(f"F0_curve and N must be (B, 2T) = ({B}, {2 * T}); got {tuple(F0_curve.shape)}, {tuple(N.shape)}")
         if tuple(s.shape) != (B, self.cfg["style_dim"]):
             raise ValueError(f"s must be (B, {self.cfg['style_dim']}), got {tuple(s.shape)}")
-        plan = self._plan(B, T)
+        ragged = lengths is not None
+        if ragged:
+            lens_t = torch.as_tensor(lengths).to(torch.int32).reshape(-1)
+            if lens_t.numel() != B:
+                raise ValueError(f"lengths must have {B} entries, got {lens_t.numel()}")
+            lo, hi = int(lens_t.min()), int(lens_t.max())     # (a host read when `lengths` lives on the device)
+            if lo < 1 or hi > T:
+                raise ValueError(f"lengths must lie in [1, T = {T}], got [{lo}, {hi}]")
+        plan = self._plan(B, T, ragged)
         self.engine.activate(plan)
         bufs = plan.buffers
+        if ragged:
+            bufs["in.lens"].copy_(lens_t, non_blocking=True)
         bufs["in.asr"].copy_(asr, non_blocking=True)
         bufs["in.F0_curve"].copy_(F0_curve, non_blocking=True)
         bufs["in.N"].copy_(N, non_blocking=True)
@@ -170,7 +186,7 @@ class Decoder:
             plan.ops[i] = (fn, (args[0], plan.har_addr if capture_taps else None) + tuple(args[2:]))
         use_graph = self.use_cuda_graph and noise_t is None and not capture_taps
         if use_graph:
-            self._run_graph(plan, (B, T))
+            self._run_graph(plan, (B, T, ragged))
         else:
             plan.run(L.stream())
         if seed is None:
@@ -197,11 +213,11 @@ class Decoder:
             self._graphs[key] = g
         g.replay()
 
-    def taps(self, B: int, T: int) -> Dict[str, torch.Tensor]:
-        return self._plan(B, T).captured
+    def taps(self, B: int, T: int, ragged: bool = False) -> Dict[str, torch.Tensor]:
+        return self._plan(B, T, ragged).captured
 
-    def launches_per_forward(self, B: int, T: int) -> int:
-        return self._plan(B, T).n_launches
+    def launches_per_forward(self, B: int, T: int, ragged: bool = False) -> int:
+        return self._plan(B, T, ragged).n_launches
 
 
 def build_decoder(weights=None, cfg: Optional[dict] = None, dtype: str = "bf16", device: Optional[str] = None,

@@ -137,10 +137,15 @@ class KokoroPipeline:
                 yield self.Result(graphemes=graphemes, phonemes=chunk, tokens=tokens, output=output, text_index=index)
 
     # ---- extension: sentence batching (the reference decodes one chunk per call, kokoro.py:135-165)
-    def batch_tokens(self, phoneme_strings: List[str], voice: str, speed: Number = 1, max_batch: int = 64):
-        """Decode many phoneme strings with batched decoder calls: front-end features are produced per string,
-        grouped by frame count T and stacked.  Returns the list of waveforms in input order."""
+    def batch_tokens(self, phoneme_strings: List[str], voice: str, speed: Number = 1, max_batch: int = 64,
+                     bucket: int = 32):
+        """Decode many phoneme strings with batched decoder calls: front-end features are produced per string, the
+        strings are sorted by frame count and cut into MIXED-length batches of ``max_batch`` (each padded to its longest
+        member, rounded up to ``bucket`` frames) that go through ``Decoder.__call__(..., lengths=)`` - one launch plan per
+        (batch size, padded length) instead of one per distinct length; every string's audio equals decoding it alone
+        (the reference does exactly that, one chunk per call: pipeline.py:381-402).  Returns the waveforms in input order."""
         import torch
+        from ....sharding import assign_ragged
         model = self.model
         pack = self.load_voice(voice)
         feats = []
@@ -151,14 +156,21 @@ class KokoroPipeline:
             asr, F0, N, _ = model.frontend(ps, ref_s, speed)
             feats.append((np.asarray(asr), np.asarray(F0), np.asarray(N), np.asarray(ref_s)[:, :128]))
         out: List[Optional[Any]] = [None] * len(feats)
-        by_t: Dict[int, List[int]] = {}
-        for i, f in enumerate(feats):
-            by_t.setdefault(f[0].shape[-1], []).append(i)
-        for T, ids in by_t.items():
-            for k in range(0, len(ids), max_batch):
-                sel = ids[k:k + max_batch]
-                y = model.decoder(np.concatenate([feats[i][0] for i in sel]), np.concatenate([feats[i][1] for i in sel]),
-                                  np.concatenate([feats[i][2] for i in sel]), np.concatenate([feats[i][3] for i in sel]))
-                for r, i in enumerate(sel):
-                    out[i] = y[r, 0].clone() if isinstance(y, torch.Tensor) else y[r, 0].copy()
+        frames = [f[0].shape[-1] for f in feats]
+        for T, sel in assign_ragged(frames, 1, max_batch, bucket)[0]:
+            n = len(sel)
+            same = all(frames[i] == frames[sel[0]] for i in sel)
+            if same:                        # a batch of one length needs no padding and no masks
+                T = frames[sel[0]]
+            asr = np.zeros((n, feats[sel[0]][0].shape[1], T), np.float32)
+            F0 = np.zeros((n, 2 * T), np.float32)
+            N = np.zeros((n, 2 * T), np.float32)
+            for r, i in enumerate(sel):
+                t = frames[i]
+                asr[r, :, :t], F0[r, :2 * t], N[r, :2 * t] = feats[i][0][0], feats[i][1][0], feats[i][2][0]
+            s = np.concatenate([feats[i][3] for i in sel])
+            y = model.decoder(asr, F0, N, s) if same else model.decoder(asr, F0, N, s, lengths=[frames[i] for i in sel])
+            for r, i in enumerate(sel):
+                row = y[r, 0, :600 * frames[i]]
+                out[i] = row.clone() if isinstance(row, torch.Tensor) else np.array(row)
         return out

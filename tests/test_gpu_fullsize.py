@@ -9,7 +9,7 @@ from mlx_audio_b200 import synth, utils
 from mlx_audio_b200.tts.models.kokoro import build_decoder
 from oracle import dsp
 from oracle.istftnet import DecoderOracle
-from parity_gates import BF16_MAX_ABS, BF16_MEL_L1, BF16_REL_L2, record
+from parity_gates import BF16_MEL_L1, bf16_ok, record
 
 pytestmark = pytest.mark.gpu
 
@@ -111,7 +111,10 @@ def test_config2_two_signals_vs_oracle(signals):
 
 def test_config3_batch_vs_oracle():
     """The real bench batch (B=64 x T=320, bf16, explicit noise) against the CPU oracle on utterances 0, 17 and 63
-    (~0.5 s of CPU each): closes the gap between the small-shape oracle tests and the full-size self-consistency test."""
+    (~2.5 s of CPU each): closes the gap between the small-shape oracle tests and the full-size self-consistency test.
+    Frames whose harmonic-source phase sits on atan2's branch cut (0-1 of an utterance's 38 401
+    frames) make +pi / -pi a coin toss for ANY implementation; the samples inside the generator's receptive field
+    around such a frame (+-4000 samples) are left out of the comparison, everything else is compared."""
     if not L.load().kk_device_is_sm100():
         pytest.skip("needs sm_100")
     B, T = 64, 320
@@ -120,18 +123,26 @@ def test_config3_batch_vs_oracle():
     inp = synth.synth_decoder_inputs(B, T, seed=1000, with_noise=False)
     g = torch.Generator(device="cuda").manual_seed(77)
     noise = torch.randn(B, 600 * T, 9, device="cuda", generator=g)
+    picks = (0, 17, 63)
+    host_noise = {b: np.random.Generator(np.random.PCG64(7700 + b)).standard_normal((1, 600 * T, 9), dtype=np.float32)
+                  for b in picks}
+    for b in picks:
+        noise[b] = torch.from_numpy(host_noise[b][0]).cuda()
     y = dec(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], noise=noise)
     torch.cuda.synchronize()
     orc = DecoderOracle(w)
-    for b in (0, 17, 63):
-        ref = orc(inp["asr"][b:b + 1], inp["F0_curve"][b:b + 1], inp["N"][b:b + 1], inp["s"][b:b + 1],
-                  noise[b:b + 1].cpu().numpy(), keep_taps=True)
+    for b in picks:
+        ref = orc(inp["asr"][b:b + 1], inp["F0_curve"][b:b + 1], inp["N"][b:b + 1], inp["s"][b:b + 1], host_noise[b],
+                  keep_taps=True)
         ph = orc.taps["har"][:, 11:]
-        if (np.abs(np.abs(ph) - np.pi) < 1e-5)[:, 1:10].any():      # atan2 branch cut: not comparable
-            continue
-        got = y[b:b + 1].cpu().numpy()
-        rel = np.linalg.norm(got - ref) / np.linalg.norm(ref)
-        mel = np.abs(dsp.log_mel_vocos(ref[0, 0]) - dsp.log_mel_vocos(got[0, 0])).mean()
-        record(f"bf16 C3 B=64 T=320 utterance {b}", max_abs=np.abs(got - ref).max(), rel_l2=rel, mel_l1=mel,
-               peak=np.abs(ref).max())
-        assert np.abs(got - ref).max() <= BF16_MAX_ABS and rel <= BF16_REL_L2 and mel <= BF16_MEL_L1
+        cut = np.nonzero((np.abs(np.abs(ph) - np.pi) < 1e-5)[:, 1:10].any(axis=1)[0])[0]
+        keep = np.ones(600 * T, bool)
+        for f in cut:
+            keep[max(0, 5 * f - 4000): 5 * f + 4000] = False
+        assert keep.mean() > 0.8, f"utterance {b}: {len(cut)} branch-cut frames - pick another seed"
+        got, r = y[b, 0].cpu().numpy()[keep], ref[0, 0][keep]
+        rel = np.linalg.norm(got - r) / np.linalg.norm(r)
+        mel = np.abs(dsp.log_mel_vocos(ref[0, 0]) - dsp.log_mel_vocos(y[b, 0].cpu().numpy()))[5:-5].mean()
+        record(f"bf16 C3 B=64 T=320 utterance {b}", max_abs=np.abs(got - r).max(), rel_l2=rel, mel_l1=mel,
+               peak=np.abs(r).max(), branch_cut_frames=len(cut))
+        assert bf16_ok(got, r) and mel <= BF16_MEL_L1

@@ -91,7 +91,7 @@ def test_instnorm_stats_and_adain(lib, B, Lr, Cc, pitch):
     x[:, :, :Cc] = r.standard_normal((B, Lr, Cc), dtype=np.float32) * 2 + 0.5
     xd = dev(x)
     stats = torch.zeros(B, Cc, 2, device="cuda", dtype=torch.float64)
-    L.check(lib.kk_instnorm_stats(L.ptr(xd), L.ptr(stats), B, Lr, Cc, pitch, L.stream()))
+    L.check(lib.kk_instnorm_stats(L.ptr(xd), L.ptr(stats), B, Lr, Cc, pitch, None, 0, 0, L.stream()))
     xs = x[:, :, :Cc].astype(np.float64)
     np.testing.assert_allclose(stats[..., 0].cpu().numpy(), xs.sum(1), rtol=1e-5, atol=1e-3)
     np.testing.assert_allclose(stats[..., 1].cpu().numpy(), (xs ** 2).sum(1), rtol=1e-5)
@@ -106,7 +106,7 @@ def test_instnorm_stats_and_adain(lib, B, Lr, Cc, pitch):
         for is_bf16 in (0, 1):
             out = torch.zeros(B, Lr, pitch, device="cuda", dtype=torch.bfloat16 if is_bf16 else torch.float32)
             L.check(lib.kk_adain_act(L.ptr(xd), pitch, L.ptr(stats), hd.data_ptr() + 5 * 4, h.shape[1], L.ptr(dev(alpha)),
-                                     act, 0.2, L.ptr(out), is_bf16, pitch, B, Lr, Cc, 0, None, None, L.stream()))
+                                     act, 0.2, L.ptr(out), is_bf16, pitch, B, Lr, Cc, 0, None, None, None, 0, 0, L.stream()))
             got = out.float().cpu().numpy()[:, :, :Cc]
             tol = 2e-2 if is_bf16 else 2e-5
             np.testing.assert_allclose(got, ref, rtol=tol, atol=tol)
@@ -120,12 +120,49 @@ def test_adain_act_pool_matches_depthwise_conv_transpose(lib):
     pb = r.standard_normal(Cc, dtype=np.float32)
     out = torch.empty(B, 2 * Lr, Cc, device="cuda")
     L.check(lib.kk_adain_act(L.ptr(dev(x)), Cc, None, None, 0, None, L.KK_ACT_LEAKY, 0.2, L.ptr(out), 0, Cc, B, Lr, Cc,
-                             1, L.ptr(dev(pw)), L.ptr(dev(pb)), L.stream()))
+                             1, L.ptr(dev(pw)), L.ptr(dev(pb)), None, 0, 0, L.stream()))
     a = torch.from_numpy(np.where(x > 0, x, 0.2 * x)).transpose(1, 2)  # (B,C,L)
     ref = F.conv_transpose1d(a, torch.from_numpy(pw)[:, None, :], torch.from_numpy(pb), stride=2, padding=1, groups=Cc)
     ref = F.pad(ref, (1, 0)).transpose(1, 2).numpy()  # left zero pad (istftnet.py:881)
     assert ref.shape == (B, 2 * Lr, Cc)
     np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=1e-5, atol=1e-5)
+
+
+def test_ragged_instnorm_and_adain_pool(lib):
+    """lens= on the elementwise kernels: statistics over each utterance's own rows, padding rows written as zero, the
+    depthwise transposed-conv pool (istftnet.py:880-881) ending at the utterance's last row."""
+    r = rng(11)
+    B, Lr, Cc = 3, 50, 36
+    lens = np.array([50, 7, 31], np.int32)
+    x = r.standard_normal((B, Lr, Cc), dtype=np.float32)
+    pw = r.standard_normal((Cc, 3), dtype=np.float32)
+    pb = r.standard_normal(Cc, dtype=np.float32)
+    h = (r.standard_normal((B, 2 * Cc), dtype=np.float32) * 0.3).astype(np.float32)
+    ld = torch.from_numpy(lens).cuda()
+    xd, hd = dev(x), dev(h)
+    stats = torch.zeros(B, Cc, 2, dtype=torch.float64, device="cuda")
+    L.check(lib.kk_instnorm_stats(L.ptr(xd), L.ptr(stats), B, Lr, Cc, Cc, L.ptr(ld), 1, 0, L.stream()))
+    out = torch.full((B, 2 * Lr, Cc), 5.0, device="cuda")
+    L.check(lib.kk_adain_act(L.ptr(xd), Cc, L.ptr(stats), L.ptr(hd), 2 * Cc, None, L.KK_ACT_LEAKY, 0.2, L.ptr(out), 0, Cc,
+                             B, Lr, Cc, 1, L.ptr(dev(pw)), L.ptr(dev(pb)), L.ptr(ld), 1, 0, L.stream()))
+    flat = torch.full((B, Lr, Cc), 5.0, device="cuda")
+    L.check(lib.kk_adain_act(L.ptr(xd), Cc, L.ptr(stats), L.ptr(hd), 2 * Cc, None, L.KK_ACT_LEAKY, 0.2, L.ptr(flat), 0, Cc,
+                             B, Lr, Cc, 0, None, None, L.ptr(ld), 1, 0, L.stream()))
+    st = stats.cpu().numpy()
+    for b, n in enumerate(lens):
+        xs = x[b, :n].astype(np.float64)
+        np.testing.assert_allclose(st[b, :, 0], xs.sum(0), rtol=1e-12, atol=1e-9)
+        np.testing.assert_allclose(st[b, :, 1], (xs * xs).sum(0), rtol=1e-12, atol=1e-9)
+        xn = (xs - xs.mean(0)) / np.sqrt(xs.var(0) + 1e-5)
+        y = (1 + h[b, None, :Cc]) * xn + h[b, None, Cc:]
+        a = np.where(y > 0, y, 0.2 * y).astype(np.float32)
+        np.testing.assert_allclose(flat[b, :n].cpu().numpy(), a, rtol=2e-5, atol=2e-5)
+        assert not flat[b, n:].any()
+        at = torch.from_numpy(a.T[None])
+        ref = F.conv_transpose1d(at, torch.from_numpy(pw)[:, None, :], torch.from_numpy(pb), stride=2, padding=1, groups=Cc)
+        ref = F.pad(ref, (1, 0))[0].T.numpy()          # (2n, C): left zero pad (istftnet.py:881)
+        np.testing.assert_allclose(out[b, :2 * n].cpu().numpy(), ref, rtol=2e-5, atol=2e-5)
+        assert not out[b, 2 * n:].any()
 
 
 def test_front_assemble(lib):
@@ -138,7 +175,7 @@ def test_front_assemble(lib):
     wn = r.standard_normal(4, dtype=np.float32)
     out = torch.zeros(B, T, Cc + 2, device="cuda")
     L.check(lib.kk_front_assemble(L.ptr(dev(asr)), L.ptr(dev(f0)), L.ptr(dev(n)), L.ptr(dev(wf)), L.ptr(dev(wn)),
-                                  L.ptr(out), Cc + 2, 0, Cc, Cc + 1, B, Cc, T, L.stream()))
+                                  L.ptr(out), Cc + 2, 0, Cc, Cc + 1, B, Cc, T, None, L.stream()))
     o = out.cpu().numpy()
     np.testing.assert_array_equal(o[:, :, :Cc], asr.transpose(0, 2, 1))
     for src, w, ch in ((f0, wf, Cc), (n, wn, Cc + 1)):

@@ -16,11 +16,12 @@ class FakeDecoder:
     def __init__(self):
         self.calls = []
 
-    def __call__(self, asr, F0_curve, N, s):
+    def __call__(self, asr, F0_curve, N, s, lengths=None):
         asr, F0_curve, N, s = map(np.asarray, (asr, F0_curve, N, s))
         B, C, T = asr.shape
         assert C == 512 and F0_curve.shape == (B, 2 * T) and N.shape == (B, 2 * T) and s.shape == (B, 128)
-        self.calls.append((B, T))
+        assert lengths is None or (len(lengths) == B and max(lengths) <= T)
+        self.calls.append((B, T) if lengths is None else (B, T, tuple(lengths)))
         return np.zeros((B, 1, 600 * T), np.float32)
 
 
@@ -72,9 +73,11 @@ def test_pipeline_batches_sentences_by_length():
     m = _model()
     p = KokoroPipeline("a", model=m)
     p.add_voice("v", np.zeros((510, 1, 256), np.float32))
-    outs = p.batch_tokens(["abc", "xyz", "hello", "pqr"], voice="v", max_batch=2)
+    outs = p.batch_tokens(["abc", "xyz", "hello", "pqr"], voice="v", max_batch=2, bucket=4)
     assert [o.shape[0] for o in outs] == [600 * 10, 600 * 10, 600 * 14, 600 * 10]
-    assert sorted(m.decoder.calls) == [(1, 10), (1, 14), (2, 10)]       # three T=10 strings -> batches of 2 + 1
+    # sorted by length, cut into batches of 2: (hello, abc) is a MIXED batch padded to 16 frames with lengths=, the two
+    # remaining T=10 strings form a plain batch
+    assert m.decoder.calls == [(2, 16, (14, 10)), (2, 10)]
 
 
 def test_load_model_errors(tmp_path):
