@@ -125,6 +125,16 @@ int kk_conv1d_f32(const float* x, const float* w, const kk_conv_desc* d, void* s
  * Returns KK_ERR_UNSUPPORTED on a non-sm_100 device. */
 int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_desc* d, int block_n, void* stream);
 
+/* Same GEMM with fp32 operands on the tensor cores (kind::tf32): the strict-fp32 mode.  terms = 3: error-compensated
+ * 3xTF32 - every operand is split into hi (its 19 leading bits) + lo (x - hi) and lo*hi + hi*lo + hi*hi accumulate in
+ * fp32, which restores fp32-level accuracy (the reference arithmetic is fp32, istftnet.py:128-166); terms = 1: plain
+ * TF32 (hi*hi only; 10-bit mantissa operands).  x: fp32 (B, L_in, x_pitch), x_pitch multiple of 4.  w_hi / w_lo:
+ * kk_pack_conv_weight(out_is_bf16=0, Cp multiple of 32) split by kk_split_tf32.  The activation tile is split on the
+ * fly in shared memory.  Epilogue identical to kk_conv1d_bf16_tc. */
+int kk_split_tf32(const float* x, float* hi, float* lo, long long n, void* stream);
+int kk_conv1d_tf32_tc(const float* x, const float* w_hi, const float* w_lo, const kk_conv_desc* d, int terms,
+                      void* stream);
+
 /* ---- fused AdaIN + activation + convolution (AdaINResBlock1's `conv(snake(adain(x, s)))` pairs,
  * istftnet.py:377-396, and AdainResBlk1d's `conv(leaky(norm(x, s)))`, :874-894) on the tensor cores.
  * The raw (pre-normalisation) tensor x is read ONCE per output tile (tile + dilation halo); the instance-norm

@@ -22,34 +22,50 @@ constexpr int TC_A_BYTES = TC_BM * TC_BK * 2;  // 16 KB
 // epilogue of tile i (8 warps) overlaps the TMA/MMA main loop of tile i+1; barrier set-up, TMEM allocation and
 // tensor-map prefetch are paid once per SM instead of once per tile.
 
+// fp32 -> nearest value with 10 explicit mantissa bits (exactly representable in TF32): round half away from zero
+__device__ __forceinline__ float tf32_rn(float v) { return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u); }
+
 constexpr int TP_EPI_WARPS = 8;
 constexpr int TP_THREADS = 64 + TP_EPI_WARPS * 32;  // 320
+constexpr int TP_SPLIT_WARPS = 4;                   // TF32x3 only: hi / lo operand split of the A tile
+constexpr int TP_THREADS_TF32 = TP_THREADS + TP_SPLIT_WARPS * 32;
 
-template <int BN>
+// TF32 = false: bf16 operands (K block = 64 channels).  TF32 = true: fp32 operands on the kind::tf32 path with the
+// error-compensated 3xTF32 split (the strict-fp32 mode of the reference arithmetic, istftnet.py:128-166): the K block
+// is 32 channels (the same 128-byte swizzle rows), every operand exists as hi = x with the 13 low mantissa bits
+// rounded away (exactly representable in TF32, so the tensor core's own conversion cannot change it) and lo = x - hi
+// (exact in fp32, then rounded to TF32 as well); three MMAs per K step accumulate lo*hi + hi*lo + hi*hi into the same fp32 accumulator.  The
+// weights are split at pack time (kk_split_tf32), the activation tile in shared memory by four extra warps, so the
+// fp32 activation tensor crosses HBM once.
+template <int BN, bool TF32 = false>
 struct TpCfg {
-  static constexpr int B_BYTES = BN * TC_BK * 2;
-  static constexpr int STAGE_BYTES = TC_A_BYTES + B_BYTES;
-  static constexpr int STAGES = BN >= 256 ? 3 : (BN >= 128 ? 4 : (BN >= 64 ? 5 : 6));
+  static constexpr int BK = TF32 ? 32 : 64;                  // channels per K block (128 bytes per row)
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int STAGE_BYTES = TF32 ? 2 * TC_A_BYTES + 2 * B_BYTES : TC_A_BYTES + B_BYTES;   // [A | A_lo | B | B_lo]
+  static constexpr int TX_BYTES = TF32 ? TC_A_BYTES + 2 * B_BYTES : STAGE_BYTES;                  // bytes TMA delivers
+  static constexpr int STAGES = TF32 ? 2 : (BN >= 256 ? 3 : (BN >= 128 ? 4 : (BN >= 64 ? 5 : 6)));
   static constexpr int NBUF = EPI_NBUF;                      // residual staging tiles per epilogue warp
   static constexpr int STAGING_BYTES = TP_EPI_WARPS * NBUF * EPI_TILE_BYTES;
   static constexpr int STATS_BYTES = 2 * 8 * BN * 4;  // double-buffered [4 lane groups][sum, sumsq][BN]
   // one 32 x 32 bf16 tile per epilogue warp for the box store of the activation copy (no room next to BN = 256 stages)
-  static constexpr int ACT_BYTES = BN <= 128 ? TP_EPI_WARPS * 2048 : 0;
+  static constexpr int ACT_BYTES = (BN <= 128 && !TF32) ? TP_EPI_WARPS * 2048 : 0;
   static constexpr int OFF_ACT = STAGES * STAGE_BYTES + STAGING_BYTES + STATS_BYTES;
   static constexpr int OFF_BAR = OFF_ACT + ACT_BYTES;
-  static constexpr int OFF_RG = OFF_BAR + 384;               // ragged tile table (RG_MAX_B + 1 ints)
+  static constexpr int OFF_RG = OFF_BAR + 448;               // ragged tile table (RG_MAX_B + 1 ints)
   static constexpr int SMEM_BYTES = OFF_RG + (RG_MAX_B + 1) * 4 + 12 + 1024;
   static_assert(SMEM_BYTES <= 232448, "shared memory budget");
   static constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(TP_THREADS, 1)
-conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                              const __grid_constant__ CUtensorMap tmRes, const __grid_constant__ CUtensorMap tmOut,
-                              const __grid_constant__ CUtensorMap tmAct, const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles_uniform,
-                              const int direct_epi) {
-  using Cfg = TpCfg<BN>;
+template <int BN, bool TF32>
+__global__ void __launch_bounds__(TF32 ? TP_THREADS_TF32 : TP_THREADS, 1)
+conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ CUtensorMap tmRes,
+                         const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmAct,
+                         const kk_conv_desc d, const int m_tiles, const int n_tiles, const int total_tiles_uniform,
+                         const int direct_epi, const int terms) {
+  using Cfg = TpCfg<BN, TF32>;
+  constexpr int TC_BK = Cfg::BK;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* staging = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
@@ -59,7 +75,8 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
   uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;        // [2]
   uint64_t* res_bar = tmem_empty_bar + 2;              // [TP_EPI_WARPS * NBUF]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_bar + TP_EPI_WARPS * Cfg::NBUF);
+  uint64_t* split_bar = res_bar + TP_EPI_WARPS * Cfg::NBUF;   // [STAGES] TF32x3: the stage's A tile has been split
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(split_bar + 6);
   int* rg_ts = reinterpret_cast<int*>(smem + Cfg::OFF_RG);   // ragged batches: first row tile of each utterance
   const int* ts = d.lens ? rg_ts : nullptr;
 
@@ -79,6 +96,7 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
       ptx::mbar_init(&tmem_empty_bar[a], TP_EPI_WARPS * 32);
     }
     for (int i = 0; i < TP_EPI_WARPS * Cfg::NBUF; ++i) ptx::mbar_init(&res_bar[i], 1);
+    for (int s = 0; s < Cfg::STAGES; ++s) ptx::mbar_init(&split_bar[s], TP_SPLIT_WARPS);
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -107,16 +125,21 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
           ptx::mbar_wait(&empty_bar[s], ph ^ 1);
           const int t = kb / cblocks, cb = kb - t * cblocks;
           uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
-          ptx::mbar_expect_tx(&full_bar[s], Cfg::STAGE_BYTES);
+          ptx::mbar_expect_tx(&full_bar[s], Cfg::TX_BYTES);
           ptx::tma_load_3d(sa, &tmA, &full_bar[s], cb * TC_BK, m0 + t * d.dil - d.pad_left, b);
-          ptx::tma_load_2d(sa + TC_A_BYTES, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+          if constexpr (TF32) {
+            ptx::tma_load_2d(sa + 2 * TC_A_BYTES, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+            ptx::tma_load_2d(sa + 2 * TC_A_BYTES + Cfg::B_BYTES, &tmB2, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+          } else {
+            ptx::tma_load_2d(sa + TC_A_BYTES, &tmB, &full_bar[s], t * d.Cw + cb * TC_BK, n0);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(TC_BM, BN);
+      constexpr uint32_t idesc = TF32 ? ptx::umma_idesc_tf32(TC_BM, BN) : ptx::umma_idesc_bf16(TC_BM, BN);
       uint32_t kbg = 0, it = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
         const uint32_t acc = it & 1, aph = (it >> 1) & 1;
@@ -126,19 +149,71 @@ conv1d_bf16_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __g
         for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
           const int s = kbg % Cfg::STAGES;
           const uint32_t ph = (kbg / Cfg::STAGES) & 1;
-          ptx::mbar_wait(&full_bar[s], ph);
-          ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(smem + s * Cfg::STAGE_BYTES);
-          const uint32_t sb = sa + TC_A_BYTES;
+          if constexpr (TF32) {
+            ptx::mbar_wait(&split_bar[s], ph);           // TMA landed AND the A tile is split into hi / lo
+            ptx::tc_fence_after();
+            const uint32_t sal = sa + TC_A_BYTES, sb = sa + 2 * TC_A_BYTES, sbl = sb + Cfg::B_BYTES;
 #pragma unroll
-          for (int k = 0; k < TC_BK / 16; ++k) {
-            const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-            const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-            ptx::umma_bf16(tacc, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < 4; ++k) {                // K = 8 fp32 = 32 bytes per MMA
+              const uint64_t ah = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t al = ptx::umma_desc(sal + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t bh = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t bl = ptx::umma_desc(sbl + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              if (terms == 3) {                          // small terms first, the dominant product last
+                ptx::umma_tf32(tacc, al, bh, idesc, (kb | k) != 0 ? 1u : 0u);
+                ptx::umma_tf32(tacc, ah, bl, idesc, 1u);
+                ptx::umma_tf32(tacc, ah, bh, idesc, 1u);
+              } else {
+                ptx::umma_tf32(tacc, ah, bh, idesc, (kb | k) != 0 ? 1u : 0u);
+              }
+            }
+          } else {
+            ptx::mbar_wait(&full_bar[s], ph);
+            ptx::tc_fence_after();
+            const uint32_t sb = sa + TC_A_BYTES;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {                // K = 16 bf16 = 32 bytes per MMA
+              const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              ptx::umma_bf16(tacc, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
           }
           ptx::umma_commit(&empty_bar[s]);
         }
         ptx::umma_commit(&tmem_full_bar[acc]);
+      }
+    }
+  } else if (TF32 && warp >= 2 + TP_EPI_WARPS) {
+    // ===================== TF32x3: split the landed A tile into hi / lo (warps 10..13) =====================
+    // Elementwise and position-preserving, so the 128B swizzle TMA applied is irrelevant: A[i] -> (hi, lo) at the same
+    // byte offset of the hi and the lo tile.  hi = x rounded to TF32, lo = x - hi rounded to TF32.
+    const int st = threadIdx.x - (2 + TP_EPI_WARPS) * 32;          // 0..127
+    uint32_t kbg = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
+        const int s = kbg % Cfg::STAGES;
+        const uint32_t ph = (kbg / Cfg::STAGES) & 1;
+        ptx::mbar_wait(&full_bar[s], ph);
+        float4* hi = reinterpret_cast<float4*>(smem + s * Cfg::STAGE_BYTES);
+        float4* lo = reinterpret_cast<float4*>(smem + s * Cfg::STAGE_BYTES + TC_A_BYTES);
+        if (terms == 3) {
+#pragma unroll
+          for (int i = 0; i < TC_A_BYTES / 16 / (TP_SPLIT_WARPS * 32); ++i) {
+            const int j = i * (TP_SPLIT_WARPS * 32) + st;
+            const float4 v = hi[j];
+            float4 h, l;
+            h.x = tf32_rn(v.x); l.x = tf32_rn(v.x - h.x);      // hi + lo = x to 2^-24 |x|; both exact TF32 values
+            h.y = tf32_rn(v.y); l.y = tf32_rn(v.y - h.y);
+            h.z = tf32_rn(v.z); l.z = tf32_rn(v.z - h.z);
+            h.w = tf32_rn(v.w); l.w = tf32_rn(v.w - h.w);
+            hi[j] = h;
+            lo[j] = l;
+          }
+          ptx::fence_proxy_async();                      // generic-proxy stores -> visible to the tensor core
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&split_bar[s]);
       }
     }
   } else {
@@ -293,34 +368,40 @@ int num_sms() {
   return n;
 }
 
-template <int BN>
-static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d, cudaStream_t st) {
-  using Cfg = TpCfg<BN>;
-  CUtensorMap tmA, tmB;
+template <int BN, bool TF32>
+static int launch_tc_persist(const void* x, const void* w, const void* w_lo, const kk_conv_desc* d, int terms,
+                             cudaStream_t st) {
+  using Cfg = TpCfg<BN, TF32>;
+  constexpr int ESZ = TF32 ? 4 : 2;
+  const CUtensorMapDataType dt = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const char* who = TF32 ? "kk_conv1d_tf32_tc" : "kk_conv1d_bf16_tc";
+  CUtensorMap tmA, tmB, tmB2;
   {
     cuuint64_t dims[3] = {(cuuint64_t)d->C_in, (cuuint64_t)d->L_in, (cuuint64_t)d->B};
-    cuuint64_t strides[2] = {(cuuint64_t)d->x_pitch * 2, (cuuint64_t)d->L_in * d->x_pitch * 2};
-    cuuint32_t box[3] = {TC_BK, TC_BM, 1};
-    int rc = make_tmap_bf16(&tmA, x, 3, dims, strides, box);
+    cuuint64_t strides[2] = {(cuuint64_t)d->x_pitch * ESZ, (cuuint64_t)d->L_in * d->x_pitch * ESZ};
+    cuuint32_t box[3] = {Cfg::BK, TC_BM, 1};
+    int rc = make_tmap(&tmA, dt, x, 3, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)d->taps * d->Cw, (cuuint64_t)d->N};
-    cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * 2};
-    cuuint32_t box[2] = {TC_BK, BN};
-    int rc = make_tmap_bf16(&tmB, w, 2, dims, strides, box);
+    cuuint64_t strides[1] = {(cuuint64_t)d->taps * d->Cw * ESZ};
+    cuuint32_t box[2] = {Cfg::BK, BN};
+    int rc = make_tmap(&tmB, dt, w, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
+    tmB2 = tmB;
+    if (TF32 && (rc = make_tmap(&tmB2, dt, w_lo, 2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B))) return rc;
   }
   static bool attr_set = false;
   if (!attr_set) {
-    KK_CUDA(cudaFuncSetAttribute(conv1d_bf16_tc_persist_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    KK_CUDA(cudaFuncSetAttribute(conv1d_tc_persist_kernel<BN, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  Cfg::SMEM_BYTES));
     attr_set = true;
   }
   const int m_tiles = cdiv(d->M, TC_BM), n_tiles = cdiv(d->N, BN);
   const long long total = (long long)m_tiles * n_tiles * d->B;
-  KK_CHECK_ARG(total < (1LL << 31), "kk_conv1d_bf16_tc: too many tiles");
-  KK_CHECK_ARG(!d->lens || d->B <= RG_MAX_B, "kk_conv1d_bf16_tc: a ragged batch holds at most %d utterances", RG_MAX_B);
+  KK_CHECK_ARG(total < (1LL << 31), "%s: too many tiles", who);
+  KK_CHECK_ARG(!d->lens || d->B <= RG_MAX_B, "%s: a ragged batch holds at most %d utterances", who, RG_MAX_B);
   const int grid = (int)(total < num_sms() ? total : num_sms());
   // direct epilogue (tc_epilogue.cuh): every 32-column chunk full, 16-byte aligned rows, one residual at most
   auto al16 = [](const void* p, long long pitch_bytes) { return (((uintptr_t)p | (uintptr_t)pitch_bytes) & 15) == 0; };
@@ -361,10 +442,21 @@ static int launch_tc_persist(const void* x, const void* w, const kk_conv_desc* d
                        dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
   }
-  conv1d_bf16_tc_persist_kernel<BN><<<grid, TP_THREADS, Cfg::SMEM_BYTES, st>>>(tmA, tmB, tmRes, tmOut, tmAct, *d, m_tiles, n_tiles,
-                                                                               (int)total, direct);
-  KK_LAUNCH_CHECK("conv1d_bf16_tc_persist_kernel");
+  conv1d_tc_persist_kernel<BN, TF32><<<grid, TF32 ? TP_THREADS_TF32 : TP_THREADS, Cfg::SMEM_BYTES, st>>>(
+      tmA, tmB, tmB2, tmRes, tmOut, tmAct, *d, m_tiles, n_tiles, (int)total, direct, terms);
+  KK_LAUNCH_CHECK(TF32 ? "conv1d_tc_persist_kernel<tf32>" : "conv1d_tc_persist_kernel<bf16>");
   return KK_OK;
+}
+
+// fp32 -> (hi, lo) with hi = x rounded to TF32's 10 mantissa bits, lo = x - hi (exact) rounded the same way, so that
+// the tensor core's own conversion cannot change either operand
+__global__ void split_tf32_kernel(const float* __restrict__ x, float* __restrict__ hi, float* __restrict__ lo, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float v = x[i];
+  const float h = tf32_rn(v);
+  hi[i] = h;
+  lo[i] = tf32_rn(v - h);
 }
 
 }  // namespace kk
@@ -394,10 +486,43 @@ extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_des
   if (block_n == 0) block_n = d->N > 64 ? 128 : (d->N > 32 ? 64 : 32);
   cudaStream_t st = (cudaStream_t)stream;
   switch (block_n) {
-    case 32: return kk::launch_tc_persist<32>(x, w, d, st);
-    case 64: return kk::launch_tc_persist<64>(x, w, d, st);
-    case 128: return kk::launch_tc_persist<128>(x, w, d, st);
-    case 256: return kk::launch_tc_persist<256>(x, w, d, st);
+    case 32: return kk::launch_tc_persist<32, false>(x, w, nullptr, d, 1, st);
+    case 64: return kk::launch_tc_persist<64, false>(x, w, nullptr, d, 1, st);
+    case 128: return kk::launch_tc_persist<128, false>(x, w, nullptr, d, 1, st);
+    case 256: return kk::launch_tc_persist<256, false>(x, w, nullptr, d, 1, st);
     default: kk::set_error("kk_conv1d_bf16_tc: block_n %d not in {32,64,128,256}", block_n); return KK_ERR_INVALID_ARG;
   }
+}
+
+extern "C" int kk_split_tf32(const float* x, float* hi, float* lo, long long n, void* stream) {
+  KK_CHECK_ARG(x && hi && lo && n > 0, "kk_split_tf32: bad arguments");
+  kk::split_tf32_kernel<<<kk::cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(x, hi, lo, n);
+  KK_LAUNCH_CHECK("split_tf32_kernel");
+  return KK_OK;
+}
+
+extern "C" int kk_conv1d_tf32_tc(const float* x, const float* w_hi, const float* w_lo, const kk_conv_desc* d, int terms,
+                                 void* stream) {
+  KK_CHECK_ARG(x && w_hi && w_lo, "kk_conv1d_tf32_tc: null tensor");
+  int rc = kk::validate_conv_desc(d, "kk_conv1d_tf32_tc");
+  if (rc) return rc;
+  if (!kk_device_is_sm100()) {
+    kk::set_error("kk_conv1d_tf32_tc: needs an sm_100 (Blackwell) device");
+    return KK_ERR_UNSUPPORTED;
+  }
+  if ((d->res && d->res_is_bf16) || d->out_add) {
+    kk::set_error("kk_conv1d_tf32_tc: bf16 residuals / out_add are implemented by kk_conv1d_adain_bf16_tc only");
+    return KK_ERR_UNSUPPORTED;
+  }
+  KK_CHECK_ARG(terms == 1 || terms == 3, "kk_conv1d_tf32_tc: terms must be 1 (plain TF32) or 3 (3xTF32), got %d", terms);
+  KK_CHECK_ARG(d->stride == 1, "kk_conv1d_tf32_tc: stride must be 1 (got %d)", d->stride);
+  KK_CHECK_ARG(d->Cw % 32 == 0, "kk_conv1d_tf32_tc: Cw (%d) must be a multiple of 32", d->Cw);
+  KK_CHECK_ARG(d->x_pitch % 4 == 0, "kk_conv1d_tf32_tc: x_pitch (%d) must be a multiple of 4", d->x_pitch);
+  KK_CHECK_ARG((((uintptr_t)x | (uintptr_t)w_hi | (uintptr_t)w_lo) & 15) == 0, "kk_conv1d_tf32_tc: operands must be 16-byte aligned");
+  KK_CHECK_ARG(d->up == 1 || d->C_out % 32 == 0, "kk_conv1d_tf32_tc: polyphase needs C_out %% 32 == 0");
+  KK_CHECK_ARG(d->B <= 65535, "kk_conv1d_tf32_tc: batch too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->N > 64) return kk::launch_tc_persist<128, true>(x, w_hi, w_lo, d, terms, st);
+  if (d->N > 32) return kk::launch_tc_persist<64, true>(x, w_hi, w_lo, d, terms, st);
+  return kk::launch_tc_persist<32, true>(x, w_hi, w_lo, d, terms, st);
 }

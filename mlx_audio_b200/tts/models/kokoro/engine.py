@@ -35,7 +35,7 @@ class PreparedConv:
     """A conv layer folded (weight norm) and packed for both convolution kernels."""
 
     def __init__(self, name: str, w_folded: torch.Tensor, bias: Optional[torch.Tensor], transposed_up: int = 0,
-                 need_bf16: bool = True, need_f32: bool = True):
+                 need_bf16: bool = True, need_f32: bool = True, need_tf32: bool = False):
         lib = L.load()
         st = L.stream()
         self.name = name
@@ -61,6 +61,15 @@ class PreparedConv:
                 self.w32 = torch.empty(self.N, self.taps * self.Cw32, dtype=torch.float32, device=dev)
                 L.check(lib.kk_pack_conv_weight(L.ptr(w_folded), L.ptr(self.w32), 0, mode, O, K, I, self.up, self.Cw32,
                                                 st), "kk_pack_conv_weight")
+        self.w32hi = self.w32lo = None
+        self.CwT = _ceil(self.C_in, 32)
+        if need_tf32:
+            # fp32 operands of the kind::tf32 kernel: K-major pack with 32-channel blocks, split into hi + lo (3xTF32)
+            wt = torch.empty(self.N, self.taps * self.CwT, dtype=torch.float32, device=dev)
+            L.check(lib.kk_pack_conv_weight(L.ptr(w_folded), L.ptr(wt), 0, mode, O, K, I, self.up, self.CwT, st),
+                    "kk_pack_conv_weight")
+            self.w32hi, self.w32lo = torch.empty_like(wt), torch.empty_like(wt)
+            L.check(lib.kk_split_tf32(L.ptr(wt), L.ptr(self.w32hi), L.ptr(self.w32lo), wt.numel(), st), "kk_split_tf32")
         if need_bf16:
             self.w16 = torch.empty(self.N, self.taps * self.Cw16, dtype=torch.bfloat16, device=dev)
             L.check(lib.kk_pack_conv_weight(L.ptr(w_folded), L.ptr(self.w16), 1, mode, O, K, I, self.up, self.Cw16, st),
@@ -161,7 +170,7 @@ class DecoderEngine:
     """
 
     def __init__(self, weights: Dict[str, torch.Tensor], cfg: dict, mode: str = "bf16", fused: bool = True,
-                 res16: int = 1):
+                 res16: int = 1, fp32_conv: str = "tf32x3"):
         """``fused`` / ``res16`` select engine arms of the bf16 mode (defaults = the measured-fastest; every arm has a
         parity test, tests/test_gpu_decoder.py::test_decoder_bf16_engine_arms): fused = AdaIN + Snake inside the
         convolution's operand path (False: separate elementwise kernels, the layout the fp32 mode uses); res16 = bf16
@@ -170,11 +179,16 @@ class DecoderEngine:
             raise ValueError(f"mode must be 'bf16' or 'fp32', got {mode!r}")
         if res16 not in (0, 1, 2):
             raise ValueError(f"res16 must be 0, 1 or 2, got {res16!r}")
+        if fp32_conv not in ("tf32x3", "tf32", "ffma"):
+            raise ValueError(f"fp32_conv must be 'tf32x3', 'tf32' or 'ffma', got {fp32_conv!r}")
         L.require_cuda()
         self.lib = L.load()
         self.cfg = cfg
         self.mode = mode
         self.tc = mode == "bf16"
+        # fp32 mode: where the stride-1 convolutions run - "tf32x3" = tcgen05 kind::tf32 with the error-compensated
+        # hi/lo split (fp32-grade, the default), "tf32" = plain TF32 (reported, misses the 1e-3 gate), "ffma" = CUDA cores
+        self.fp32_conv = fp32_conv if (mode == "fp32" and self.lib.kk_device_is_sm100()) else "ffma"
         self.fused = self.tc and bool(fused)
         self.res16 = int(res16) if self.fused else 0
         if self.tc and not self.lib.kk_device_is_sm100():
@@ -212,7 +226,8 @@ class DecoderEngine:
     def _prep_wn(self, prefix: str, up: int = 0, tc: Optional[bool] = None):
         tc = self.tc if tc is None else tc
         self.convs[prefix] = PreparedConv(prefix, self._fold(prefix), self.w.get(f"{prefix}.bias"), up,
-                                          need_bf16=tc, need_f32=not tc)
+                                          need_bf16=tc, need_f32=not tc,
+                                          need_tf32=(not tc) and self.fp32_conv != "ffma")
 
     def _prepare_adain(self):
         """AdaIN fc layers: one concatenated (R, style) matrix -> a single projection launch per forward."""
@@ -341,7 +356,9 @@ class DecoderEngine:
         return torch.bfloat16 if self.tc else torch.float32
 
     def _act_pitch(self, C: int) -> int:
-        return _ceil(C, 64) if self.tc else C
+        if self.tc:
+            return _ceil(C, 64)
+        return _ceil(C, 4) if self.fp32_conv != "ffma" else C    # TMA needs 16-byte row pitches
 
     def _conv(self, plan: Plan, pc: PreparedConv, x_addr: int, B: int, L_in: int, x_pitch: int, M: int, *,
               dil: int = 1, pad_left: int = 0, stride: int = 1, L_true: Optional[int] = None,
@@ -370,9 +387,16 @@ class DecoderEngine:
         if out_act is not None:
             d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = out_act
         d.lens, d.len_mul, d.len_add = plan.lens(d.L_true)
+        use_tf32 = (not self.tc) and self.fp32_conv != "ffma" and not force_f32 and stride == 1 and \
+            pc.w32hi is not None and x_pitch % 4 == 0 and x_addr % 16 == 0
+        if use_tf32:
+            d.Cw = pc.CwT
         plan.keep.append(d)
         plan.conv_ops[len(plan.ops)] = d
-        if use_tc:
+        if use_tf32:
+            plan.add(self.lib.kk_conv1d_tf32_tc, x_addr, self._addr(pc.w32hi), self._addr(pc.w32lo), C.byref(d),
+                     3 if self.fp32_conv == "tf32x3" else 1)
+        elif use_tc:
             if block_n == 0:
                 block_n = self._auto_block_n(pc)
             plan.add(self.lib.kk_conv1d_bf16_tc, x_addr, self._addr(pc.w16), C.byref(d), block_n)

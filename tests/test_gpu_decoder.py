@@ -263,6 +263,36 @@ def test_decoder_fp32_config1_vs_oracle_waveform_and_mel(dec_fp32, oracle):
     assert np.abs(mel_ref - mel_got).mean() <= 1e-3
 
 
+@pytest.mark.parametrize("arm", ["ffma", "tf32"])
+def test_decoder_fp32_engine_arms(arm, synth_weights, oracle, lib):
+    """fp32 mode, non-default convolution arms (engine.DecoderEngine fp32_conv=): "ffma" (CUDA cores, the round-1 path)
+    meets the same 1e-3 gate as the default 3xTF32 tensor-core path; plain "tf32" (10-bit operands) is measured and
+    reported - SURVEY 7.2 expects it to miss 1e-3 - and only gated loosely."""
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    dec = build_decoder(synth_weights, dtype="fp32", engine_options=dict(fp32_conv=arm))
+    inp = synth.synth_decoder_inputs(2, 64, seed=2024)
+    ref = oracle(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], inp["noise"])
+    y = _run(dec, inp)
+    err = np.abs(y - ref).max()
+    record(f"fp32 arm {arm} B=2 T=64", max_abs=err, rel_l2=np.linalg.norm(y - ref) / np.linalg.norm(ref),
+           peak=np.abs(ref).max())
+    if arm == "ffma":
+        assert err <= 1e-3, err
+    else:
+        assert np.isfinite(y).all() and err <= 5e-2 * np.abs(ref).max(), err
+
+
+def test_decoder_fp32_runs_on_tensor_cores(dec_fp32, lib):
+    """The default fp32 mode issues its stride-1 convolutions through kk_conv1d_tf32_tc (tcgen05 kind::tf32, 3xTF32)."""
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    plan = dec_fp32._plan(1, 8)
+    names = [fn.__name__ for fn, _ in plan.ops if fn is not None]
+    assert names.count("kk_conv1d_tf32_tc") >= 60 and names.count("kk_conv1d_f32") <= 8, \
+        (names.count("kk_conv1d_tf32_tc"), names.count("kk_conv1d_f32"))
+
+
 def test_decoder_bf16_vs_oracle(dec_bf16, oracle):
     # bf16 operands / fp32 accumulate.  Stated tolerance: tests/parity_gates.py (about 3x the measured errors).
     inp = synth.synth_decoder_inputs(2, 64, seed=2024)
