@@ -167,6 +167,16 @@ int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, const kk_conv_d
 int kk_hnsf_source(const float* f0, const float* noise, unsigned long long seed, const unsigned long long* seed_dev,
                    const float* lin_w, const float* lin_b, float* phase_ws, float* har_source, int B, int T2,
                    int upsample, const int* lens, void* stream);
+/* kk_hnsf_source without caller-provided scratch.  NO counterpart in the reference: added
+ * for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The phase scratch is a static device array of KK_HNSF_NOALLOC_MAX_FLOATS floats (4 MiB, held by every
+ * GPU that loads the library until exit); B*9*T2 beyond that is rejected with KK_ERR_INVALID_ARG.  The call allocates
+ * nothing.  Every call shares the array (it keeps the last call's contents; nothing in it needs clearing): calls that
+ * overlap on the GPU race - serialise them on one stream.  Otherwise identical to kk_hnsf_source. */
+#define KK_HNSF_NOALLOC_MAX_FLOATS (1 << 20)
+int kk_hnsf_source_noalloc(const float* f0, const float* noise, unsigned long long seed,
+                           const unsigned long long* seed_dev, const float* lin_w, const float* lin_b,
+                           float* har_source, int B, int T2, int upsample, const int* lens, void* stream);
 /* lens (frames, or NULL): utterance b has S_b = len_mul*lens[b] samples (the reflect pad mirrors at S_b) and S_b/5 + 1
  * frames; frames beyond are written as zero. */
 int kk_stft_n20(const float* har_source, float* har, int har_pitch, int B, int S, const int* lens, int len_mul,

@@ -74,6 +74,7 @@ PROTOTYPES = {
     "kk_split_tf32": [_P, _P, _P, _LL, _P],
     "kk_conv1d_tf32_tc": [_P, _P, _P, C.POINTER(ConvDesc), _I, _P],
     "kk_hnsf_source": [_P, _P, _ULL, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P],
+    "kk_hnsf_source_noalloc": [_P, _P, _ULL, _P, _P, _P, _P, _I, _I, _I, _P, _P],
     "kk_stft_n20": [_P, _P, _I, _I, _I, _P, _I, _P],
     "kk_stft_n20_bf16": [_P, _P, _I, _P, _I, _I, _I, _I, _P, _I, _P],
     "kk_istft_head_n20": [_P, _I, _P, _I, _I, _P, _I, _I, _P],

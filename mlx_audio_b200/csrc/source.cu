@@ -265,3 +265,37 @@ extern "C" int kk_stft_n20_bf16(const float* har_source, float* har, int har_pit
                "kk_stft_n20_bf16: pitch / rows too small (bf_rows %d < frames %d)", bf_rows, S / 5 + 1);
   return stft_n20_launch(har_source, har, har_pitch, har_bf16, bf_pitch, bf_rows, B, S, lens, len_mul, stream);
 }
+
+// ---- kk_hnsf_source_noalloc: the same harmonic source with its phase scratch in a file-scope device array, for callers
+// that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No
+// counterpart in the reference.  Every GPU that loads the library holds the
+// array (4 MiB) until exit.  All calls share it and it keeps the last call's contents; nothing in it has to start at
+// zero (hnsf_phase_kernel writes every element hnsf_sample_kernel reads), but calls that overlap on the GPU (different
+// streams, or graphs replayed concurrently) race on it.
+namespace kk {
+static __device__ __align__(256) float g_hnsf_phase_scratch[KK_HNSF_NOALLOC_MAX_FLOATS];
+}
+
+extern "C" int kk_hnsf_source_noalloc(const float* f0, const float* noise, unsigned long long seed,
+                                      const unsigned long long* seed_dev, const float* lin_w, const float* lin_b,
+                                      float* har_source, int B, int T2, int upsample, const int* lens, void* stream) {
+  KK_CHECK_ARG(B > 0 && T2 > 1, "kk_hnsf_source_noalloc: bad shape B=%d T2=%d", B, T2);
+  const long long need = (long long)B * kk::NH * T2;
+  KK_CHECK_ARG(need <= (long long)KK_HNSF_NOALLOC_MAX_FLOATS,
+               "kk_hnsf_source_noalloc: B*9*T2 = %lld floats of phase scratch exceed the static maximum of %lld "
+               "(KK_HNSF_NOALLOC_MAX_FLOATS); use kk_hnsf_source with caller-provided scratch",
+               need, (long long)KK_HNSF_NOALLOC_MAX_FLOATS);
+  // In host code the array's name is a host-side stand-in, not a device address: resolve it once per device, with that
+  // device current (cudaGetSymbolAddress allocates nothing).
+  constexpr int MAX_DEV = 64;
+  static float* scratch_of[MAX_DEV] = {nullptr};
+  int dev = 0;
+  KK_CUDA(cudaGetDevice(&dev));
+  KK_CHECK_ARG(dev >= 0 && dev < MAX_DEV, "kk_hnsf_source_noalloc: device ordinal %d out of range", dev);
+  float* ws = scratch_of[dev];
+  if (!ws) {
+    KK_CUDA(cudaGetSymbolAddress((void**)&ws, kk::g_hnsf_phase_scratch));
+    scratch_of[dev] = ws;   // (two threads racing here store the same value)
+  }
+  return kk_hnsf_source(f0, noise, seed, seed_dev, lin_w, lin_b, ws, har_source, B, T2, upsample, lens, stream);
+}
