@@ -274,7 +274,7 @@ def bench_c4(dev, dec, rank, world, max_batch=64, reps=5, utterances=4096):
             s=0.5 * torch.randn(n, 128, device=dev, generator=g))
         if ragged:
             inputs[ids[0]]["lengths"] = torch.tensor([frames[i] for i in ids], dtype=torch.int32, device=dev)
-    dec.use_cuda_graph = False     # every (B, T) shape is seen once per pass
+    dec.use_cuda_graph = ragged    # ragged: a handful of (B, T_padded) shapes, replayed; else every shape is seen once per pass
     if mine:
         dec.reserve(max(len(ids) for _, ids in mine), max(t for t, _ in mine))
 
