@@ -226,6 +226,16 @@ int kk_normalize_features(float* x, int B, int frames, int n_feat, int per_featu
  * out may alias x. */
 int kk_snake_f32(const float* x, float* out, const float* alpha, const float* beta, long long outer, int C,
                  long long inner, int logscale, float eps, void* stream);
+/* ---- SNAC generator pieces (mlx_audio/codec/models/snac/layers.py), channels-last fp32:
+ * depthwise WNConv1d, groups = C, 'same' padding ((K-1)*dil = 2*pad) (:18-61, ResidualUnit :205-214): w (C, K),
+ * out = bias + sum_t w[c][t] x[l + t*dil - pad][c] (+ res);  NoiseBlock (:217-228): out = x + noise * h with noise
+ * (B, C) - constant over time, the reference draws (B, 1, T) on a channels-last tensor, i.e. one value per channel;
+ * Tanh head (:199). */
+int kk_dwconv1d_f32(const float* x, const float* w, const float* bias, const float* res, float* out, int B, int L, int C,
+                    int K, int dil, int pad, void* stream);
+int kk_noise_mix_f32(const float* x, const float* h, const float* noise, float* out, int B, long long L, int C,
+                     void* stream);
+int kk_tanh_f32(const float* x, float* out, long long n, void* stream);
 /* Weight-norm fold with the epsilon and operation order as parameters: g_first = 1, eps = 0 is the DAC form
  * w = (g * v) / ||v|| of mlx_audio/codec/models/descript/nn/layers.py:7-12,57 (norm over (K, I) per output channel). */
 int kk_fold_weight_norm_ex(const float* v, const float* g, float* w, int O, int KI, float eps, int g_first,

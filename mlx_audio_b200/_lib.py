@@ -85,6 +85,9 @@ PROTOTYPES = {
     "kk_clamp_below_max_affine": [_P, _I, _LL, _F, _F, _F, _P],
     "kk_normalize_features": [_P, _I, _I, _I, _I, _F, _P],
     "kk_snake_f32": [_P, _P, _P, _P, _LL, _I, _LL, _I, _F, _P],
+    "kk_dwconv1d_f32": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
+    "kk_noise_mix_f32": [_P, _P, _P, _P, _I, _LL, _I, _P],
+    "kk_tanh_f32": [_P, _P, _LL, _P],
     "kk_fold_weight_norm_ex": [_P, _P, _P, _I, _I, _F, _I, _P],
 }
 

@@ -364,8 +364,13 @@ def conv1d(x, w, stride=1, padding=0, dilation=1, groups=1):
     return _wrap(y.transpose(1, 2).contiguous().numpy())
 
 
-def conv_transpose1d(x, w, stride=1, padding=0, dilation=1, groups=1):
-    """x (N,L,C_in), w (C_out,K,C_in/groups) -> (N,(L-1)s-2p+d(K-1)+1,C_out)."""
+def conv_transpose1d(x, w, stride=1, padding=0, dilation=1, output_padding=0, groups=1):
+    """x (N,L,C_in), w (C_out,K,C_in/groups) -> (N,(L-1)s-2p+d(K-1)+1+output_padding,C_out).
+    Signature of the MLX the reference pins (requirements.txt:7 mlx>=0.25.2): ``output_padding`` is the SIXTH positional
+    argument, before ``groups`` - codec/models/bigvgan/conv.py:108-110 passes its output_padding there, and the
+    reference's own SNAC shape test (codec/tests/test_snac.py:36: 120 907 = 512 * 236 + 75 samples) only holds with it:
+    snac/layers.py:111-118 and descript/nn/layers.py:108-110 pass ``self.groups`` (= 1) in that position, i.e. every
+    transposed convolution of those codecs runs with output_padding = 1.  Kokoro passes keywords (istftnet.py:150-157)."""
     torch, F = _torch()
     xt = torch.from_numpy(np.ascontiguousarray(_raw(x))).transpose(1, 2)
     wn = torch.from_numpy(np.ascontiguousarray(_raw(w)))
@@ -377,7 +382,7 @@ def conv_transpose1d(x, w, stride=1, padding=0, dilation=1, groups=1):
         # torch: (C_in, C_out/groups, K); group g owns C_in/groups inputs and C_out/groups outputs
         cog = cout // groups
         wt = wn.reshape(groups, cog, k, cin_g).permute(0, 3, 1, 2).reshape(groups * cin_g, cog, k)
-    y = F.conv_transpose1d(xt, wt, None, int(stride), int(padding), 0, groups, int(dilation))
+    y = F.conv_transpose1d(xt, wt, None, int(stride), int(padding), int(output_padding), groups, int(dilation))
     return _wrap(y.transpose(1, 2).contiguous().numpy())
 
 

@@ -116,3 +116,20 @@ class Dropout(Module):
 class Identity(Module):
     def __call__(self, x, *a, **k):
         return x
+
+
+class Sequential(Module):
+    """mlx.nn.Sequential: members live in ``.layers`` (parameter names ``layers.<i>....``)."""
+
+    def __init__(self, *modules):
+        self.layers = list(modules)
+
+    def __call__(self, x):
+        for m in self.layers:
+            x = m(x)
+        return x
+
+
+class Tanh(Module):
+    def __call__(self, x):
+        return mx.array(np.tanh(np.asarray(x)))

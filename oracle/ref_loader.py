@@ -182,3 +182,20 @@ def load_reference_frontends():
         os.path.join(root, "tts", "models", "spark", "bicodec.py"), "mel_spectrogram",
         dict(mx=ns.mx, hanning=ns.utils.hanning, mel_filters=ns.utils.mel_filters, stft=ns.utils.stft))
     return ns
+
+
+def load_reference_snac():
+    """The reference's SNAC layers (codec/models/snac/{attention,layers}.py: WNConv1d, WNConvTranspose1d, Snake1d,
+    ResidualUnit, NoiseBlock, DecoderBlock, Decoder), unmodified, on the shim - SURVEY 8(f) row 4."""
+    ns = load_reference()
+    if hasattr(ns, "snac_layers"):
+        return ns
+    root = os.path.join(REFERENCE_ROOT, "mlx_audio")
+    for name, sub in (("mlx_audio.codec", ("codec",)), ("mlx_audio.codec.models", ("codec", "models")),
+                      ("mlx_audio.codec.models.snac", ("codec", "models", "snac"))):
+        if name not in sys.modules:
+            _pkg(name, os.path.join(root, *sub))
+    ns.snac_attention = _load("mlx_audio.codec.models.snac.attention",
+                              os.path.join(root, "codec", "models", "snac", "attention.py"))
+    ns.snac_layers = _load("mlx_audio.codec.models.snac.layers", os.path.join(root, "codec", "models", "snac", "layers.py"))
+    return ns

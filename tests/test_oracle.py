@@ -340,3 +340,17 @@ def test_dac_wnconv1d_golden(golden_dir):
     w = wg * wv / torch.sqrt((wv ** 2).sum(dim=(1, 2), keepdim=True))
     y = conv1d_mlx(xw, w, stride=2, padding=3, dilation=2) + wb
     assert tuple(y.shape) == g["wnconv"].shape and np.abs(y.numpy() - g["wnconv"]).max() < 1e-5
+
+
+def test_reference_snac_shape_pin_on_the_shim():
+    """codec/tests/test_snac.py:25-36 on oracle/mlx_shim: the reference's own SNAC decoder must produce 120 907 samples
+    from 236 latent frames - this pins the shim's reading of mx.conv_transpose1d (output_padding is the sixth positional
+    argument in the MLX the reference requires, so snac/layers.py:111-118 runs with output_padding = groups = 1)."""
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("reference tree not present")
+    ns = ref_loader.load_reference_snac()
+    dec = ns.snac_layers.Decoder(24, 64, [8, 8, 4, 2], True, depthwise=True, attn_window_size=None)
+    y = np.asarray(dec(ns.mx.array(np.zeros((1, 236, 24), np.float32))))
+    assert y.shape == (1, 120907, 1)
+    assert [tuple(s) for s in ns.mx.random.log[-4:]] == [(1, 1, 32), (1, 1, 16), (1, 1, 8), (1, 1, 4)]   # noise is (B, 1, C)
