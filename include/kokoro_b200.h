@@ -110,7 +110,9 @@ typedef struct kk_conv_desc {
   float* out_add; int add_pitch;   /* optional: out_add (B, L_out, add_pitch) += result (the MRF sum over resblocks,
                                       istftnet.py:795-800); kk_conv1d_adain_bf16_tc only (TMA reduce-add)          */
   int res_is_bf16;                 /* `res` points at bf16 (B, L_res, res_pitch) data: the bf16 residual stream of
-                                      AdaINResBlock1 (x = x + xt, istftnet.py:394); kk_conv1d_adain_bf16_tc only   */
+                                      AdaINResBlock1 (x = x + xt, istftnet.py:394) and of the generator's noise branch
+                                      (x = x + x_source, :788); kk_conv1d_adain_bf16_tc, and the tcgen05 kernels when
+                                      their TMA epilogue applies (N % 32 == 0, aligned rows, no res2, res_shift 0) */
   const int* lens; int len_mul, len_add; /* ragged batch (see top): utterance b has L_true_b = min(L_true, len_mul *
                                       lens[b] + len_add) true output rows (and L_out_b = L_true_b + L_out - L_true
                                       output rows); rows beyond are excluded from `stats`, written as zero to

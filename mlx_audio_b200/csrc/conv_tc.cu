@@ -407,7 +407,7 @@ static int launch_tc_persist(const void* x, const void* w, const void* w_lo, con
   auto al16 = [](const void* p, long long pitch_bytes) { return (((uintptr_t)p | (uintptr_t)pitch_bytes) & 15) == 0; };
   const int direct = d->N % 32 == 0 && (d->up == 1 || d->C_out % 32 == 0) && !d->res2 &&
                      (!d->out || al16(d->out, (long long)d->out_pitch * 4)) &&
-                     (!d->res || al16(d->res, (long long)d->res_pitch * 4)) && (!d->bias || al16(d->bias, 0)) &&
+                     (!d->res || al16(d->res, (long long)d->res_pitch * (d->res_is_bf16 ? 2 : 4))) && (!d->bias || al16(d->bias, 0)) &&
                      (!d->out_act || (d->act_is_bf16 && al16(d->out_act, (long long)d->act_pitch * 2)));
   // rank-4 polyphase views (tc_epilogue.cuh) of the residual and output tensors; only coordinates whose rows lie
   // inside the utterance are ever issued, so the (possibly negative) row offset folded into the base is harmless
@@ -416,11 +416,13 @@ static int launch_tc_persist(const void* x, const void* w, const void* w_lo, con
     const long long off = (long long)d->left_pad - d->up_off;
     cuuint32_t box[4] = {32, 1, 32, 1};
     if (d->res && d->res_shift == 0) {
+      const cuuint64_t rsz = d->res_is_bf16 ? 2 : 4;     // bf16 residual: 32 x 32 box of 64-byte rows, 64-byte swizzle
       cuuint64_t dims[4] = {(cuuint64_t)d->C_out, (cuuint64_t)d->up, (cuuint64_t)d->M, (cuuint64_t)d->B};
-      cuuint64_t strides[3] = {(cuuint64_t)d->res_pitch * 4, (cuuint64_t)d->up * d->res_pitch * 4,
-                               (cuuint64_t)d->L_res * d->res_pitch * 4};
-      int rc = make_tmap(&tmRes, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, d->res + off * d->res_pitch, 4, dims, strides, box,
-                         CU_TENSOR_MAP_SWIZZLE_128B);
+      cuuint64_t strides[3] = {(cuuint64_t)d->res_pitch * rsz, (cuuint64_t)d->up * d->res_pitch * rsz,
+                               (cuuint64_t)d->L_res * d->res_pitch * rsz};
+      const char* base = reinterpret_cast<const char*>(d->res) + off * d->res_pitch * (long long)rsz;
+      int rc = make_tmap(&tmRes, d->res_is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, 4,
+                         dims, strides, box, d->res_is_bf16 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B);
       if (rc) return rc;
     }
     if (d->out) {
@@ -441,6 +443,11 @@ static int launch_tc_persist(const void* x, const void* w, const void* w_lo, con
     int rc = make_tmap(&tmAct, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (const __nv_bfloat16*)d->out_act + off * d->act_pitch, 4,
                        dims, strides, box, CU_TENSOR_MAP_SWIZZLE_64B);
     if (rc) return rc;
+  }
+  if (d->res && d->res_is_bf16 && !(direct && d->res_shift == 0)) {
+    set_error("%s: a bf16 residual needs the TMA epilogue (N %% 32 == 0, 16-byte aligned rows, no second residual, "
+              "res_shift 0)", who);
+    return KK_ERR_UNSUPPORTED;
   }
   conv1d_tc_persist_kernel<BN, TF32><<<grid, TF32 ? TP_THREADS_TF32 : TP_THREADS, Cfg::SMEM_BYTES, st>>>(
       tmA, tmB, tmB2, tmRes, tmOut, tmAct, *d, m_tiles, n_tiles, (int)total, direct, terms);
@@ -467,10 +474,6 @@ extern "C" int kk_conv1d_bf16_tc(const void* x, const void* w, const kk_conv_des
   if (rc) return rc;
   if (!kk_device_is_sm100()) {
     kk::set_error("kk_conv1d_bf16_tc: needs an sm_100 (Blackwell) device");
-    return KK_ERR_UNSUPPORTED;
-  }
-  if (d->res && d->res_is_bf16) {
-    kk::set_error("kk_conv1d_bf16_tc: a bf16 residual is implemented by kk_conv1d_adain_bf16_tc only");
     return KK_ERR_UNSUPPORTED;
   }
   if (d->out_add) {
@@ -510,8 +513,8 @@ extern "C" int kk_conv1d_tf32_tc(const float* x, const float* w_hi, const float*
     kk::set_error("kk_conv1d_tf32_tc: needs an sm_100 (Blackwell) device");
     return KK_ERR_UNSUPPORTED;
   }
-  if ((d->res && d->res_is_bf16) || d->out_add) {
-    kk::set_error("kk_conv1d_tf32_tc: bf16 residuals / out_add are implemented by kk_conv1d_adain_bf16_tc only");
+  if (d->out_add) {
+    kk::set_error("kk_conv1d_tf32_tc: out_add is implemented by kk_conv1d_adain_bf16_tc only");
     return KK_ERR_UNSUPPORTED;
   }
   KK_CHECK_ARG(terms == 1 || terms == 3, "kk_conv1d_tf32_tc: terms must be 1 (plain TF32) or 3 (3xTF32), got %d", terms);

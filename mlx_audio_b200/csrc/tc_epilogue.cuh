@@ -278,19 +278,23 @@ __device__ __forceinline__ void epi_issue_res(const kk_conv_desc& d, const CUten
                                               const int nb, const int lane, uint8_t* st, uint64_t* bar) {
   const EpiLim lim = epi_lim(d, b);
   const EpiRow e = epi_row(d, lim, m0w + lane, nb);
+  // bf16 residual (res_is_bf16): 64-byte rows - a 2 KB box with the 64-byte swizzle, or 64-byte row copies
+  const uint32_t rowb = d.res_is_bf16 ? 64u : 128u;
   if (d.res_shift == 0 && epi_interior(d, lim, m0w, nb)) {
     if (lane == 0) {
-      ptx::mbar_expect_tx(bar, EPI_TILE_BYTES);
+      ptx::mbar_expect_tx(bar, 32u * rowb);
       ptx::tma_load_4d(st, tmRes, bar, e.cbase, e.ph, m0w, b);
     }
     return;
   }
   const unsigned mask = __ballot_sync(0xffffffffu, e.row_ok);
-  if (lane == 0) ptx::mbar_expect_tx(bar, (uint32_t)__popc(mask) * 128u);
+  if (lane == 0) ptx::mbar_expect_tx(bar, (uint32_t)__popc(mask) * rowb);
   __syncwarp();
-  if (e.row_ok)
-    ptx::bulk_load_g2s(st + lane * 128, d.res + ((size_t)b * d.L_res + (e.out_row >> d.res_shift)) * d.res_pitch + e.cbase,
-                       128u, bar);
+  if (e.row_ok) {
+    const size_t off = ((size_t)b * d.L_res + (e.out_row >> d.res_shift)) * d.res_pitch + e.cbase;
+    const void* src = d.res_is_bf16 ? (const void*)(reinterpret_cast<const __nv_bfloat16*>(d.res) + off) : (const void*)(d.res + off);
+    ptx::bulk_load_g2s(st + lane * rowb, src, rowb, bar);
+  }
 }
 
 // INTERIOR: no masking anywhere, swizzled tile, box transfers.  Otherwise: per-element masks, plain tile, row copies.
@@ -310,13 +314,32 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
   if (d.res) ptx::mbar_wait(rbar, rparity);
   ptx::tmem_ld_wait();
   float* row = reinterpret_cast<float*>(st) + lane * 32;
-  if (d.res) {
+  float rres[32];                                     // this lane's residual row (kept: the non-interior masks re-use it)
 #pragma unroll
-    for (int c4 = 0; c4 < 8; ++c4) {
-      float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (row_ok) rr = *reinterpret_cast<const float4*>(row + ((c4 ^ (lane & rsw)) << 2));
-      v[c4 * 4 + 0] += rr.x; v[c4 * 4 + 1] += rr.y; v[c4 * 4 + 2] += rr.z; v[c4 * 4 + 3] += rr.w;
+  for (int i = 0; i < 32; ++i) rres[i] = 0.f;
+  if (d.res && row_ok) {
+    if (d.res_is_bf16) {                              // 64-byte rows, 16-byte chunk ^= (row >> 1) & 3 when it came as a box
+      const uint8_t* r16 = st + lane * 64;
+      const int sw = rsw ? ((lane >> 1) & 3) : 0;
+#pragma unroll
+      for (int c8 = 0; c8 < 4; ++c8) {
+        const uint4 q = *reinterpret_cast<const uint4*>(r16 + ((c8 ^ sw) << 4));
+        const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          rres[c8 * 8 + 2 * i] = __uint_as_float(w4[i] << 16);
+          rres[c8 * 8 + 2 * i + 1] = __uint_as_float(w4[i] & 0xffff0000u);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int c4 = 0; c4 < 8; ++c4) {
+        const float4 rr = *reinterpret_cast<const float4*>(row + ((c4 ^ (lane & rsw)) << 2));
+        rres[c4 * 4 + 0] = rr.x; rres[c4 * 4 + 1] = rr.y; rres[c4 * 4 + 2] = rr.z; rres[c4 * 4 + 3] = rr.w;
+      }
     }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] += rres[i];
   }
   if (d.bias) {
 #pragma unroll
@@ -328,13 +351,11 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
   if (!INTERIOR) {
     // accumulator rows outside the true output contribute nothing (the residual still does); rows outside the
     // utterance are zero
-    const float4* rrow = reinterpret_cast<const float4*>(row);
 #pragma unroll
     for (int c4 = 0; c4 < 8; ++c4) {
       if (!acc_valid) {
-        float4 rr = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (d.res && row_ok) rr = rrow[c4];
-        v[c4 * 4 + 0] = rr.x; v[c4 * 4 + 1] = rr.y; v[c4 * 4 + 2] = rr.z; v[c4 * 4 + 3] = rr.w;
+        v[c4 * 4 + 0] = rres[c4 * 4 + 0]; v[c4 * 4 + 1] = rres[c4 * 4 + 1];
+        v[c4 * 4 + 2] = rres[c4 * 4 + 2]; v[c4 * 4 + 3] = rres[c4 * 4 + 3];
       }
       if (!e.live) v[c4 * 4 + 0] = v[c4 * 4 + 1] = v[c4 * 4 + 2] = v[c4 * 4 + 3] = 0.f;
     }

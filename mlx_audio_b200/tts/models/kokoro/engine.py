@@ -378,7 +378,8 @@ class DecoderEngine:
         d.left_pad = left_pad
         d.bias = self._addr(pc.bias) if (use_bias and pc.bias is not None) else None
         if res is not None:
-            d.res, d.res_pitch, d.res_shift, d.L_res = res
+            d.res, d.res_pitch, d.res_shift, d.L_res = res[:4]
+            d.res_is_bf16 = int(len(res) > 4 and res[4])
         if res2 is not None:
             d.res2, d.res2_pitch = res2
         d.scale = scale
@@ -673,10 +674,13 @@ class DecoderEngine:
             plan.stage(f"stage{i}")
             ap = self._act_pitch(Ci)
             nconv = self.convs[f"{g}.noise_convs.{i}"]
-            xs = self._buf(plan, f"g{i}.xs", (B, Li, Ci))
             st_xs = self._stats(plan, B, Ci)
             fused_i = self.fused and Ci in (128, 256)
             s16 = fused_i and (self.res16 >= 2 or (self.res16 == 1 and Ci == 128))
+            # bf16 stream: the noise branch x_source exists only as bf16 - written by noise_convs, rewritten by the last
+            # conv of noise_res (its input copy is free by then) and read back as the bf16 residual of ups (x + x_source,
+            # istftnet.py:788): 0.63 GB instead of 1.26 GB written and read at B=64 x T=320
+            xs = None if s16 else self._buf(plan, f"g{i}.xs", (B, Li, Ci))
             xs16 = self._buf(plan, f"g{i}.xs16", (B, Li, Ci), torch.bfloat16) if s16 else None
             x16 = self._buf(plan, f"g{i}.x16", (B, Li, Ci), torch.bfloat16) if s16 else None
             xs_out = None if s16 else self._addr(xs)     # bf16 stream: the noise conv's result is only ever read as bf16
@@ -700,8 +704,10 @@ class DecoderEngine:
             act = None if fused_i else self._buf(plan, f"g{i}.act", (B, Li, ap), adt, zero=True)
             y = None if fused_i else self._buf(plan, f"g{i}.y", (B, Li, Ci))
             self._adain_resblock1(plan, f"{g}.noise_res.{i}", B, Li, Ci, 7 if i == 0 else 11, (1, 3, 5), h_all, xs,
-                                  st_xs, xs, act, y, dict(out_addr=self._addr(xs), out_pitch=Ci), x16_in=xs16)
-            self._tap(plan, f"noise_res{i}", xs, lambda t: t.transpose(1, 2))
+                                  st_xs, xs, act, y,
+                                  dict(out_act=(self._addr(xs16), Ci, 1, 1.0)) if s16 else dict(out_addr=self._addr(xs), out_pitch=Ci),
+                                  x16_in=xs16)
+            self._tap(plan, f"noise_res{i}", xs16 if s16 else xs, lambda t: t.transpose(1, 2))
             # ups[i]: polyphase transposed conv, + x_source fused as residual (:783-788)
             u = cfg["upsample_rates"][i]
             kk_ = cfg["upsample_kernel_sizes"][i]
@@ -711,7 +717,8 @@ class DecoderEngine:
             self._conv(plan, self.convs[f"{g}.ups.{i}"], self._addr(a_prev), B, L_prev, self._act_pitch(C_prev),
                        L_prev + 1, pad_left=1, up_off=(kk_ - u) // 2, L_true=L_prev * u, L_out=Li,
                        left_pad=1 if last else 0, out_addr=None if s16 else self._addr(x),
-                       out_pitch=Ci, res=(self._addr(xs), Ci, 0, Li), stats_addr=st_x,
+                       out_pitch=Ci, res=(self._addr(xs16), Ci, 0, Li, True) if s16 else (self._addr(xs), Ci, 0, Li),
+                       stats_addr=st_x,
                        out_act=(self._addr(x16), Ci, 1, 1.0) if s16 else None)
             self._tap(plan, f"x_stage{i}", x16 if s16 else x, lambda t: t.transpose(1, 2))
             # MRF: mean of three AdaINResBlock1 on the same input (:790-796)

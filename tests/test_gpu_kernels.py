@@ -186,7 +186,7 @@ def test_front_assemble(lib):
 
 # ------------------------------------------------------------------ convolutions
 def _conv_case(lib, tc, B, Lin, Cin, Cout, k, dil, stride=1, transposed_up=0, with_res=True, left_pad=0, seed=0,
-               block_n=0, tf32_terms=0):
+               block_n=0, tf32_terms=0, bf16_res=False):
     """tc: bf16 tensor-core kernel; tf32_terms = 3 / 1: fp32 operands through kk_conv1d_tf32_tc (3xTF32 / plain TF32)."""
     tf32 = tf32_terms > 0
     assert not (tc and tf32)
@@ -221,6 +221,9 @@ def _conv_case(lib, tc, B, Lin, Cin, Cout, k, dil, stride=1, transposed_up=0, wi
     assert y.shape == (B, Lout, Cout), (y.shape, (B, Lout, Cout))
     res = r.standard_normal((B, Lout, Cout), dtype=np.float32) if with_res else None
     res2 = r.standard_normal((B, Lout, Cout), dtype=np.float32) if with_res else None
+    if bf16_res:      # bf16 residual stream (res_is_bf16): one residual, rounded to bf16, through the TMA epilogue
+        res = torch.from_numpy(res).to(bf).float().numpy()
+        res2 = np.zeros_like(res)
     scale = 0.7
     ref = y.numpy()
     if with_res:
@@ -245,7 +248,11 @@ def _conv_case(lib, tc, B, Lin, Cin, Cout, k, dil, stride=1, transposed_up=0, wi
     d.L_true, d.left_pad, d.L_out = Ltrue, left_pad, Lout
     bd, rd, r2d = dev(bias), (dev(res) if with_res else None), (dev(res2) if with_res else None)
     d.bias = L.ptr(bd)
-    if with_res:
+    if with_res and bf16_res:
+        rd = rd.to(bf).contiguous()
+        _KEEP.append(rd)
+        d.res, d.res_pitch, d.res_shift, d.L_res, d.res_is_bf16 = L.ptr(rd), Cout, 0, Lout, 1
+    elif with_res:
         d.res, d.res_pitch, d.res_shift, d.L_res = L.ptr(rd), Cout, 0, Lout
         d.res2, d.res2_pitch = L.ptr(r2d), Cout
     d.scale = scale
@@ -309,6 +316,9 @@ TC_CASES = [
     dict(B=2, Lin=40, Cin=512, Cout=256, k=0, dil=1, transposed_up=10),  # ups.0 geometry
     dict(B=1, Lin=150, Cin=256, Cout=128, k=0, dil=1, transposed_up=6, left_pad=1),  # ups.1 geometry
     dict(B=3, Lin=64, Cin=64, Cout=64, k=3, dil=1, block_n=64),
+    # bf16 residual through the TMA epilogue: plain conv (edge chunks: Lin not a multiple of 32) and the ups.1 geometry
+    dict(B=2, Lin=300, Cin=128, Cout=128, k=3, dil=1, bf16_res=True),
+    dict(B=2, Lin=150, Cin=256, Cout=128, k=0, dil=1, transposed_up=6, left_pad=1, bf16_res=True),
 ]
 
 
