@@ -252,8 +252,11 @@ __device__ __forceinline__ void fv_tile_range(int total, int cta, int ncta, int&
   start = cta * base + (cta < rem ? cta : rem);
 }
 
-// SWAP (MT == 2, BN == 128 only): the MMA runs "transposed" - weights as the M = 128 operand, the 256 tile rows
-// as N = 256 - so one 128x256x16 MMA replaces two 128x128x16 ones (12 KB instead of 16 KB of shared-memory
+// SWAP: the MMA runs "transposed" - weights as the M = 128 operand, the tile rows as N.  <MT = 2, BN = 128>: the 256
+// tile rows are N = 256; <MT = 1, BN = 256> (round 2): 128-row tiles, two 128-channel M blocks per K step (same 256
+// accumulator columns).  The accumulator is [channel lanes][row columns], so the epilogue is lane = channel:
+// per-thread statistics, no staging round trip for the bf16 copy.  At 128 channels
+// one 128x256x16 MMA replaces two 128x128x16 ones (12 KB instead of 16 KB of shared-memory
 // operand reads per 128 tensor cycles).  The accumulator is then [channel lanes][row columns].
 // CL = 2: CTAs run as cluster pairs that share the weight stream - each loads half of every weight slab and
 // TMA-multicasts it into both shared memories (the slab sequence is the same for every tile), halving the L2 -> SM
@@ -373,8 +376,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     // ===================== MMA issuer =====================
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FV_REGS_CTRL));
     if (lane == 0) {
-      constexpr uint32_t idesc = SWAP ? ptx::umma_idesc_bf16(128, 256) : ptx::umma_idesc_bf16(128, BN);
-      static_assert(!SWAP || (MT == 2 && BN == 128), "SWAP is the 256-row x 128-channel configuration");
+      // SWAP: M = 128 output channels (BN / 128 such blocks), N = the tile's 128 * MT rows
+      constexpr uint32_t idesc = SWAP ? ptx::umma_idesc_bf16(128, 128 * MT) : ptx::umma_idesc_bf16(128, BN);
+      static_assert(!SWAP || (MT == 2 && BN == 128) || (MT == 1 && BN == 256),
+                    "SWAP: 256 rows x 128 channels, or 128 rows x 2 blocks of 128 channels (256 TMEM columns per tile)");
       uint32_t gb = 0, ga = 0;
       FV_DBG_DECL(w_tempty); FV_DBG_DECL(w_afull); FV_DBG_DECL(w_bfull);
 #ifdef KK_FUSED_DBG
@@ -404,12 +409,15 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             ptx::tc_fence_after();
             const uint32_t sb = ptx::smem_u32(sB + s * Cfg::B_BYTES);
             if (SWAP) {
-              const uint32_t sx = sa0 + (uint32_t)(t * d.dil) * 128u;                // rows t*dil .. +255 of the slot
+              const uint32_t sx = sa0 + (uint32_t)(t * d.dil) * 128u;                // rows t*dil .. of the slot
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const uint64_t wd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
                 const uint64_t xd = ptx::umma_desc(sx + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-                ptx::umma_bf16(tacc, wd, xd, idesc, (cb | t | k) != 0 ? 1u : 0u);
+#pragma unroll
+                for (int mb = 0; mb < BN / 128; ++mb) {   // 128-channel blocks of the slab: accumulator columns mb * rows
+                  const uint64_t wd = ptx::umma_desc(sb + mb * 16384 + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+                  ptx::umma_bf16(tacc + mb * (128 * MT), wd, xd, idesc, (cb | t | k) != 0 ? 1u : 0u);
+                }
               }
             } else {
 #pragma unroll
@@ -564,16 +572,21 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     // rc) of this warp: channels 32*lg..+31 (lane = channel) x rows half*128 + rc*32..+31.  fp32 results are
     // written into the staging tile (in place over the residual) and leave by TMA (store / reduce-add; register
     // stores measured slower); the bf16 copy goes straight from registers, one 64-byte row segment per store.
+    // Two shapes share this code: 256 rows x 128 channels (`half` = which 128 rows) and 128 rows x 256 channels (`half`
+    // = which 128-channel block); either way the warp's accumulator columns are half * 128 + rc * 32.
     const int ew = warp - FV_EPI_WARP0;
     const int lg = warp & 3;
     const int half = ew >> 2;
     constexpr int NRC = 4;
+    constexpr int TR = 128 * MT;                       // rows per tile
+    constexpr bool CHB = BN == 256;                    // `half` selects a channel block (else a row half)
+    const int row_half = CHB ? 0 : half * 128;
     uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // [32 rows][32 channels] fp32, 16-byte chunk ^= row & 7
     uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
     const bool via_smem = has_st;   // fp32 results leave by TMA (store and/or reduce-add) from the staging tile
     const bool res16 = d.res_is_bf16 != 0;
-    const int ch0 = lg * 32, chan = ch0 + lane;
+    const int ch0 = lg * 32 + (CHB ? half * 128 : 0), chan = ch0 + lane;
     const float bias_s = (d.bias ? __ldg(d.bias + chan) : 0.f) * d.scale;   // (v + bias) * scale = fma(v, scale, bias * scale)
     const int n_items = t_count * NRC;
     RgMap map(ts, m_tiles), map_res(ts, m_tiles);
@@ -582,7 +595,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       const int tile = t_start + n / NRC, rc = n % NRC;
       int b, mtile;
       map_res.locate(tile, b, mtile);
-      const int row0 = mtile * 256 + half * 128 + rc * 32;
+      const int row0 = mtile * TR + row_half + rc * 32;
       fv_issue_res(d, b, row0, ch0, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
     };
     if (has_res) { issue_res(0); issue_res(1); }
@@ -610,7 +623,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       const int tile = t_start + j;
       int b, mtile;
       map.locate(tile, b, mtile);
-      const int tm0 = mtile * 256 + half * 128;
+      const int tm0 = mtile * TR + row_half;
       const int Mb = ragged_len(d.lens, d.len_mul, d.len_add, b, d.M);   // rows of this utterance (ragged batches)
       if (do_stats && b != stat_b) { flush_stats(stat_b); stat_b = b; }
       const uint32_t buf = j & 1, aph = (j >> 1) & 1;
@@ -692,6 +705,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         if (d.out_act && nstore > 0) {
           __nv_bfloat16* ap = (__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0) * d.act_pitch + chan;
           if (d.act_pitch == 128) store_bf16(ap, 128, v, nstore);
+          else if (d.act_pitch == 256) store_bf16(ap, 256, v, nstore);
           else store_bf16(ap, d.act_pitch, v, nstore);
         }
         if (has_res) {
@@ -1049,9 +1063,18 @@ extern "C" int kk_conv1d_adain_bf16_tc(const kk_adain_in* a, const void* w, cons
     return ((cl_mask & 2) && tiles128 >= 4) ? kk::launch_fused<2, 128, 2, true, 2>(a, w, d, st)
                                             : kk::launch_fused<2, 128, 2, true>(a, w, d, st);
   }
-  if (d->C_in == 256 && d->N == 256)
+  if (d->C_in == 256 && d->N == 256) {
+    // Transposed form (128-row tiles, two 128-channel M blocks, lane = channel epilogue) vs the row-major one, chosen per
+    // launch from what was measured at B=64 x T=320 (profiles/r02_fused_experiments.txt, item 4): the transposed
+    // epilogue is ~1.4x cheaper, its MMAs read 128 instead of 96 B/clk of operands - it wins where the CUDA-core roles
+    // bound the launch (k = 3: 0.67-0.80x; k = 7 with a residual: 0.87x) and loses where the MMA does (k = 7 conv1
+    // 1.08x, k = 11 1.03-1.27x).  Mask bits: 1 taps <= 3, 2 taps <= 7 with residual, 4 taps <= 7 without, 8 longer.
+    static const int swap256 = kk::fv_tune_int("KK_FUSED_SWAP256", 3);
+    const int bit = d->taps <= 3 ? 1 : (d->taps <= 7 ? (d->res ? 2 : 4) : 8);
+    if (swap256 & bit) return kk::launch_fused<1, 256, 4, true>(a, w, d, st);
     return ((cl_mask & 1) && tiles256 >= 4) ? kk::launch_fused<1, 256, 4, false, 2>(a, w, d, st)
                                             : kk::launch_fused<1, 256, 4, false>(a, w, d, st);
+  }
   if (d->C_in == 128 && d->N <= 32) {   // narrow head (conv_post, istftnet.py:798-803): no stats / bf16 copy / residual
     KK_CHECK_ARG(!d->stats && !d->out_act && !d->res && !d->out_add && d->out,
                  "kk_conv1d_adain_bf16_tc: the N <= 32 configuration writes `out` only");
