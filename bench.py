@@ -403,7 +403,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     S = T * synth.SAMPLES_PER_FRAME
     audio_s_per_step = B * S / synth.SAMPLE_RATE
     weights = synth.synth_decoder_weights(seed=2000)
-    dec = build_decoder(weights, dtype=args.dtype, device=str(dev))
+    eng_opts = {"res16": args.res16} if args.res16 >= 0 else None
+    dec = build_decoder(weights, dtype=args.dtype, device=str(dev), engine_options=eng_opts)
     dec.use_cuda_graph = bool(args.graph)
     inp = synth.synth_decoder_inputs(B, T, seed=1000 + 17 * rank, with_noise=False)
     host = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
@@ -632,6 +633,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=1, help="replay the forward as a CUDA graph (default on)")
     ap.add_argument("--skip", default="", help="comma-separated sub-benchmarks to skip: dsp,c4,c5,latency,fp32")
+    ap.add_argument("--res16", type=int, default=-1, help="lab: engine arm res16 (0/1/2); default: the engine's own")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ops-json", default="", help="dump the per-launch event timings of one forward")
     args = ap.parse_args()
