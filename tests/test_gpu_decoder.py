@@ -545,3 +545,36 @@ def test_streaming_decoder_matches_direct_calls(dec_bf16):
         np.testing.assert_array_equal(a, b)
     with pytest.raises(ValueError):
         StreamingDecoder(dec_bf16, depth=1)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_decoder_workspace_poisoning(mode, dec_fp32, dec_bf16):
+    """Stand-in for compute-sanitizer's initcheck (the tool is closed on this pool, profiles/r02_sanitizer.txt): every
+    workspace buffer of the engine - activations, staging copies, padding - is filled with 0xFF bytes (NaN in fp32 and
+    bf16) before a forward; the plan's declared zero-padding buffers are then re-cleared the way a plan switch does.
+    Any kernel that reads a row, a pad column or a halo it did not write this forward, or that relies on stale data from
+    an earlier forward, turns the NaN into the waveform.  Uniform and ragged batches; the result must equal the clean
+    run bit for bit (same launches, same inputs)."""
+    dec = dec_fp32 if mode == "fp32" else dec_bf16
+    eng = dec.engine
+
+    def poison():
+        torch.cuda.synchronize()
+        for name, t in eng.pool.items():
+            if not name.startswith("in."):
+                t.fill_(0xFF)
+        eng.active_plan = None                    # activate() re-clears the buffers a plan declares as zero padding
+
+    inp = synth.synth_decoder_inputs(3, 21, seed=808)
+    clean = _run(dec, inp)
+    poison()
+    again = _run(dec, inp)
+    assert np.isfinite(again).all()
+    np.testing.assert_array_equal(again, clean)
+    lens = [21, 5, 14]
+    rin, lens, _ = _ragged_inputs(3, 21, lens, seed=809)
+    y0 = dec(rin["asr"], rin["F0_curve"], rin["N"], rin["s"], noise=rin["noise"], lengths=lens).cpu().numpy()
+    poison()
+    y1 = dec(rin["asr"], rin["F0_curve"], rin["N"], rin["s"], noise=rin["noise"], lengths=lens).cpu().numpy()
+    assert np.isfinite(y1).all()
+    np.testing.assert_array_equal(y1, y0)
