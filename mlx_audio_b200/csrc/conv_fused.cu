@@ -577,10 +577,11 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const int ew = warp - FV_EPI_WARP0;
     const int lg = warp & 3;
     const int half = ew >> 2;
-    constexpr int NRC = 4;
     constexpr int TR = 128 * MT;                       // rows per tile
     constexpr bool CHB = BN == 256;                    // `half` selects a channel block (else a row half)
-    const int row_half = CHB ? 0 : half * 128;
+    constexpr int HR = CHB ? TR : TR / 2;              // rows a warp covers per tile, in NRC chunks of 32
+    constexpr int NRC = HR / 32;
+    const int row_half = CHB ? 0 : half * HR;
     uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // [32 rows][32 channels] fp32, 16-byte chunk ^= row & 7
     uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
@@ -629,7 +630,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       const uint32_t buf = j & 1, aph = (j >> 1) & 1;
       FV_WAIT(&tmem_full[buf], aph, w_tfull);
       ptx::tc_fence_after();
-      const uint32_t tacc = tmem_base + buf * 256 + (uint32_t)(half * 128) + ((uint32_t)(lg * 32) << 16);
+      const uint32_t tacc = tmem_base + buf * (MT * BN) + (uint32_t)(half * HR) + ((uint32_t)(lg * 32) << 16);
 #pragma unroll 1
       for (int rc = 0; rc < NRC; ++rc) {
         const int n = j * NRC + rc;
