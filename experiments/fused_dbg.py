@@ -51,7 +51,34 @@ def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
     print(f"C={Cc} k={k} d={dil} x_bf16={x_bf16} res={with_res} out={'f32' if with_out else 'bf16'}: {e0.elapsed_time(e1):.3f} ms; "
           + "  ".join(f"{n}={v[i] / tot * 100:.0f}%" for i, n in enumerate(NAMES) if n != "-" and i != 10))
 
+def run_post(B, Lr):
+    """conv_post shape: C=128 -> 22, k=7, bf16 input that is already activated (no normalisation, no activation)."""
+    dev = "cuda"
+    x = torch.randn(B, Lr, 128, device=dev).to(torch.bfloat16).contiguous()
+    w = (torch.randn(22, 7 * 128, device=dev) / 30).to(torch.bfloat16)
+    bias = torch.zeros(24, device=dev)
+    out = torch.empty(B, Lr, 24, device=dev)
+    dbg = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
+    L.check(lib.kk_debug_fused_buffer(dbg.data_ptr()))
+    a = AdainIn(); a.x, a.x_is_bf16, a.x_pitch, a.act = x.data_ptr(), 1, 128, 0
+    d = ConvDesc(); d.B, d.L_in, d.C_in, d.x_pitch = B, Lr, 128, 128
+    d.taps, d.dil, d.pad_left, d.stride, d.Cw = 7, 1, 3, 1, 128
+    d.M, d.N, d.C_out, d.up, d.up_off, d.L_true, d.left_pad, d.L_out = Lr, 22, 22, 1, 0, Lr, 0, Lr
+    d.bias, d.scale, d.out, d.out_pitch = bias.data_ptr(), 1.0, out.data_ptr(), 24
+    for _ in range(2):
+        L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), w.data_ptr(), C.byref(d), L.stream()))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), w.data_ptr(), C.byref(d), L.stream())); e1.record()
+    torch.cuda.synchronize()
+    v = dbg.view(148, 16).double().mean(0).cpu().numpy()
+    print(f"conv_post 128->22 k=7: {e0.elapsed_time(e1):.3f} ms; total {v[10]:.0f} clk; "
+          + "  ".join(f"{n}={v[i] / v[10] * 100:.0f}%" for i, n in enumerate(NAMES) if n != "-" and i != 10))
+
+
 import os
+if os.environ.get("DBG_SET") == "post":
+    run_post(64, 38401)
+    sys.exit(0)
 if os.environ.get("DBG_SET") == "s16":
     for k in (3, 7, 11):
         run(64, 38401, 128, k, 1, False, False, False)   # fp32 in -> bf16 out (fp32-stream conv1)

@@ -410,25 +410,26 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             const uint32_t sb = ptx::smem_u32(sB + s * Cfg::B_BYTES);
             if (SWAP) {
               const uint32_t sx = sa0 + (uint32_t)(t * d.dil) * 128u;                // rows t*dil .. of the slot
+              // descriptors once per slab; a K step of 16 elements = 32 bytes = +2 in the (address >> 4) field (one
+              // integer add instead of rebuilding the descriptor; measured neutral - profiles/r02_fused_experiments.txt)
+              const uint64_t xd0 = ptx::umma_desc(sx, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t wd0 = ptx::umma_desc(sb, 16, 1024, ptx::UMMA_LAYOUT_SW128);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const uint64_t xd = ptx::umma_desc(sx + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
 #pragma unroll
-                for (int mb = 0; mb < BN / 128; ++mb) {   // 128-channel blocks of the slab: accumulator columns mb * rows
-                  const uint64_t wd = ptx::umma_desc(sb + mb * 16384 + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-                  ptx::umma_bf16(tacc + mb * (128 * MT), wd, xd, idesc, (cb | t | k) != 0 ? 1u : 0u);
-                }
+                for (int mb = 0; mb < BN / 128; ++mb)     // 128-channel blocks of the slab: accumulator columns mb * rows
+                  ptx::umma_bf16(tacc + mb * (128 * MT), wd0 + (uint64_t)(mb * 1024 + k * 2), xd0 + (uint64_t)(k * 2), idesc,
+                                 (cb | t | k) != 0 ? 1u : 0u);
               }
             } else {
+              const uint64_t bd0 = ptx::umma_desc(sb, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t ad0 = ptx::umma_desc(sa0 + (uint32_t)(t * d.dil) * 128u, 16, 1024, ptx::UMMA_LAYOUT_SW128);
 #pragma unroll
-              for (int mt = 0; mt < MT; ++mt) {
-                const uint32_t sa = sa0 + (uint32_t)(mt * 128 + t * d.dil) * 128u;   // row-shifted view of the slot
+              for (int mt = 0; mt < MT; ++mt) {           // row-shifted views of the slot: +128 rows = +1024 in the field
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-                  const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-                  ptx::umma_bf16(tacc + mt * BN, ad, bd, idesc, (cb | t | k) != 0 ? 1u : 0u);
-                }
+                for (int k = 0; k < 4; ++k)
+                  ptx::umma_bf16(tacc + mt * BN, ad0 + (uint64_t)(mt * 1024 + k * 2), bd0 + (uint64_t)(k * 2), idesc,
+                                 (cb | t | k) != 0 ? 1u : 0u);
               }
             }
             if constexpr (CL > 1) ptx::umma_commit_mc(&b_empty[s], (uint16_t)((1u << CL) - 1));

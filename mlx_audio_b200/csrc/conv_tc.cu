@@ -154,12 +154,12 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             ptx::mbar_wait(&split_bar[s], ph);           // TMA landed AND the A tile is split into hi / lo
             ptx::tc_fence_after();
             const uint32_t sal = sa + TC_A_BYTES, sb = sa + 2 * TC_A_BYTES, sbl = sb + Cfg::B_BYTES;
+            // descriptors once per stage; +32 bytes per K step = +2 in the (address >> 4) field
+            const uint64_t ah0 = ptx::umma_desc(sa, 16, 1024, ptx::UMMA_LAYOUT_SW128), al0 = ptx::umma_desc(sal, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+            const uint64_t bh0 = ptx::umma_desc(sb, 16, 1024, ptx::UMMA_LAYOUT_SW128), bl0 = ptx::umma_desc(sbl, 16, 1024, ptx::UMMA_LAYOUT_SW128);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {                // K = 8 fp32 = 32 bytes per MMA
-              const uint64_t ah = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-              const uint64_t al = ptx::umma_desc(sal + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-              const uint64_t bh = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-              const uint64_t bl = ptx::umma_desc(sbl + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
+              const uint64_t ah = ah0 + 2 * k, al = al0 + 2 * k, bh = bh0 + 2 * k, bl = bl0 + 2 * k;
               if (terms == 3) {                          // small terms first, the dominant product last
                 ptx::umma_tf32(tacc, al, bh, idesc, (kb | k) != 0 ? 1u : 0u);
                 ptx::umma_tf32(tacc, ah, bl, idesc, 1u);
@@ -172,12 +172,10 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             ptx::mbar_wait(&full_bar[s], ph);
             ptx::tc_fence_after();
             const uint32_t sb = sa + TC_A_BYTES;
+            const uint64_t ad0 = ptx::umma_desc(sa, 16, 1024, ptx::UMMA_LAYOUT_SW128), bd0 = ptx::umma_desc(sb, 16, 1024, ptx::UMMA_LAYOUT_SW128);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {                // K = 16 bf16 = 32 bytes per MMA
-              const uint64_t ad = ptx::umma_desc(sa + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-              const uint64_t bd = ptx::umma_desc(sb + k * 32, 16, 1024, ptx::UMMA_LAYOUT_SW128);
-              ptx::umma_bf16(tacc, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
+            for (int k = 0; k < 4; ++k)                  // K = 16 bf16 = 32 bytes per MMA: +2 in the (address >> 4) field
+              ptx::umma_bf16(tacc, ad0 + 2 * k, bd0 + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           }
           ptx::umma_commit(&empty_bar[s]);
         }
