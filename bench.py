@@ -526,7 +526,7 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 "traffic": traffic, "traffic_source": traffic_src,
                 "kernel": {"kk_conv1d_adain_bf16_tc": "conv1d_adain_tc_kernel (fused AdaIN+Snake+conv, tcgen05)",
-                           "kk_conv1d_bf16_tc": "conv1d_bf16_tc_persist_kernel (tcgen05)"}.get(dom, dom),
+                           "kk_conv1d_bf16_tc": "conv1d_tc_persist_kernel<BN, bf16> (tcgen05)"}.get(dom, dom),
                 "launches": d_n, "flop_per_launch": d_fl / d_n, "ms_per_launch": d_ms / d_n,
                 "kernel_ms_per_step": d_ms, "share_of_step": d_ms / tot,
                 "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}

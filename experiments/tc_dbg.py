@@ -1,4 +1,4 @@
-"""Where does conv1d_bf16_tc_persist_kernel spend its time on the memory-bound generator layers?  Runs the noise_convs[1]
+"""Where does conv1d_tc_persist_kernel spend its time on the memory-bound generator layers?  Runs the noise_convs[1]
 (1x1, 24->128 at 120T+1) and ups[1] (polyphase 256->128 x6) shapes with the epilogue outputs switched on and off."""
 import ctypes as C, os, sys
 import torch
