@@ -199,3 +199,28 @@ def load_reference_snac():
                               os.path.join(root, "codec", "models", "snac", "attention.py"))
     ns.snac_layers = _load("mlx_audio.codec.models.snac.layers", os.path.join(root, "codec", "models", "snac", "layers.py"))
     return ns
+
+
+def load_reference_dac():
+    """The reference's DAC generator (codec/models/descript/dac.py: ResidualUnit, DecoderBlock, Decoder, unmodified, over
+    its own nn/layers.py) on the shim.  ``base.CodecMixin`` (soundfile I/O) and ``nn.quantize`` are stubbed: neither is on
+    the decoder's path."""
+    ns = load_reference_frontends()
+    if hasattr(ns, "dac"):
+        return ns
+    root = os.path.join(REFERENCE_ROOT, "mlx_audio")
+    base = types.ModuleType("mlx_audio.codec.models.descript.base")
+    base.CodecMixin = type("CodecMixin", (), {})
+    sys.modules[base.__name__] = base
+    quant = types.ModuleType("mlx_audio.codec.models.descript.nn.quantize")
+    quant.ResidualVectorQuantize = type("ResidualVectorQuantize", (), {})
+    sys.modules[quant.__name__] = quant
+    if "huggingface_hub" not in sys.modules:
+        try:
+            import huggingface_hub  # noqa: F401
+        except Exception:
+            hub = types.ModuleType("huggingface_hub")
+            hub.snapshot_download = lambda *a, **k: (_ for _ in ()).throw(RuntimeError("no network"))
+            sys.modules["huggingface_hub"] = hub
+    ns.dac = _load("mlx_audio.codec.models.descript.dac", os.path.join(root, "codec", "models", "descript", "dac.py"))
+    return ns

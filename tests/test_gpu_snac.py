@@ -89,3 +89,30 @@ def test_depthwise_wnconv1d(C, K, dil):
     lib = L.load()
     xd = torch.zeros(1, 8, 4, device="cuda")
     assert lib.kk_dwconv1d_f32(L.ptr(xd), L.ptr(xd), None, None, L.ptr(xd), 1, 8, 4, 7, 1, 2, L.stream()) == L.KK_ERR_INVALID_ARG
+
+
+DAC_CASES = {"wide": (32, 256, [4, 3, 2]), "small": (16, 64, [2, 5])}
+
+
+@pytest.mark.parametrize("name", sorted(DAC_CASES))
+def test_dac_decoder_matches_reference_golden(golden_dir, name):
+    """DAC's generator (codec/models/descript/dac.py:83-131): same layer types as SNAC's dense one, transposed-conv weights
+    in MLX's (out, K, in) layout normalised per input channel; golden from tests/golden/make_golden_dac.py."""
+    from mlx_audio_b200.codec.models.descript import dac as D
+    g = np.load(os.path.join(golden_dir, "dac_decoder.npz"))
+    cin, ch, rates = DAC_CASES[name]
+    dec = D.Decoder(cin, ch, rates)
+    shapes = {k: tuple(v.shape) for k, v in dec.named_parameters().items()}
+    assert sorted(shapes) == [str(s) for s in g[f"{name}.param_names"]]
+    dec.load_weights(synth.synth_named_weights(shapes, seed=int(g[f"{name}.seed"])))
+    y = dec(g[f"{name}.z"])
+    h = torch.as_tensor(g[f"{name}.z"]).cuda()
+    for layer in dec.model.layers[:-1]:
+        h = layer(h)
+    torch.cuda.synchronize()
+    ref, pre = g[f"{name}.y"], g[f"{name}.pre_tanh"]
+    assert tuple(y.shape) == ref.shape
+    e_pre = np.abs(h.cpu().numpy() - pre).max() / np.abs(pre).max()
+    e_y = np.abs(y.cpu().numpy() - ref).max()
+    record(f"dac decoder {name}", pre_tanh_rel=e_pre, y_abs=e_y, peak=np.abs(ref).max())
+    assert e_pre < 1e-4 and e_y < 1e-5, (e_pre, e_y)
