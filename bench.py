@@ -198,8 +198,9 @@ def bench_latency(dev, weights, decs):
     x = {k: torch.from_numpy(v).to(dev) for k, v in inp.items()}
     out = {"workload": f"B={B} x T={T} ({T / 40:.1f} s of audio), inputs resident, median of 30 calls"}
     for mode, dec in decs.items():
-        for graph in (0, 1):
+        for graph, par in ((0, True), (1, True), (1, False)):   # True (the default): noise branch on a side stream
             dec.use_cuda_graph = bool(graph)
+            dec.parallel_branches = par
             for _ in range(4):
                 dec(x["asr"], x["F0_curve"], x["N"], x["s"], borrow=True)
             torch.cuda.synchronize()
@@ -214,8 +215,10 @@ def bench_latency(dev, weights, decs):
                 wall.append((time.perf_counter() - t0) * 1e3)
                 ts.append(e0.elapsed_time(e1))
             ms = _median(ts)
-            out[f"{mode}_graph{graph}"] = {"ms": ms, "wall_ms": _median(wall), "rtf": ms / 1e3 / (T / 40.0),
+            out[f"{mode}_graph{graph}" + ("" if par else "_serial")] = {"ms": ms, "wall_ms": _median(wall), "rtf": ms / 1e3 / (T / 40.0),
                                            "launches": dec.launches_per_forward(B, T)}
+        dec.parallel_branches = True
+    out["note"] = "graph0 / graph1: default schedule (noise branch of the generator parallel to the front); graph1_serial: one stream"
     return out
 
 
@@ -406,6 +409,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     eng_opts = {"res16": args.res16} if args.res16 >= 0 else None
     dec = build_decoder(weights, dtype=args.dtype, device=str(dev), engine_options=eng_opts)
     dec.use_cuda_graph = bool(args.graph)
+    if args.parallel >= 0:
+        dec.parallel_branches = bool(args.parallel)
     inp = synth.synth_decoder_inputs(B, T, seed=1000 + 17 * rank, with_noise=False)
     host = {k: torch.from_numpy(v).pin_memory() for k, v in inp.items()}
     devt = {k: v.to(dev) for k, v in host.items()}
@@ -633,6 +638,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=1, help="replay the forward as a CUDA graph (default on)")
     ap.add_argument("--skip", default="", help="comma-separated sub-benchmarks to skip: dsp,c4,c5,latency,fp32")
+    ap.add_argument("--parallel", type=int, default=-1, help="lab: force Decoder.parallel_branches off / on (0 / 1)")
     ap.add_argument("--res16", type=int, default=-1, help="lab: engine arm res16 (0/1/2); default: the engine's own")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ops-json", default="", help="dump the per-launch event timings of one forward")

@@ -63,6 +63,11 @@ class Decoder:
         self._graphs: Dict[tuple, torch.cuda.CUDAGraph] = {}
         self._engine_options = dict(engine_options or {})   # DecoderEngine arms: fused=, res16= (see engine.py)
         self.use_cuda_graph = False
+        # run the generator's noise branch on a side stream (a parallel branch inside a CUDA graph).  Measured on B200
+        # (bf16, graph replay): B=1 x T=200 2.10 -> 1.72 ms, B=8 3.85 -> 3.50, B=16 x T=320 9.58 -> 9.32, B=64 36.4 -> 36.3:
+        # on by default; "auto" = only while B * T <= 2048 frames; False = one stream
+        self.parallel_branches = True
+        self._side: Optional[torch.cuda.Stream] = None
         self.seed = 0
 
     # ------------------------------------------------------------------ weights
@@ -187,11 +192,14 @@ class Decoder:
         if i is not None:               # fp32 copy of the harmonic-source STFT: only for the taps (see engine.build_plan)
             fn, args = plan.ops[i]
             plan.ops[i] = (fn, (args[0], plan.har_addr if capture_taps else None) + tuple(args[2:]))
+        par = self.parallel_branches
+        par = (B * T <= 2048) if par == "auto" else bool(par)
+        par = par and not capture_taps and plan.fork_index is not None
         use_graph = self.use_cuda_graph and noise_t is None and not capture_taps
         if use_graph:
-            self._run_graph(plan, (B, T, ragged))
+            self._run_graph(plan, (B, T, ragged, par), par)
         else:
-            plan.run(L.stream())
+            self._run_plan(plan, par)
         if seed is None:
             self.seed += 1
         return bufs["audio"] if borrow else bufs["audio"].clone()
@@ -205,14 +213,22 @@ class Decoder:
         plan.buffers["seed"].fill_(int(seed) & 0x7FFFFFFFFFFFFFFF)   # outside any captured graph
         plan.keep_noise = noise_t
 
-    def _run_graph(self, plan: Plan, key):
+    def _run_plan(self, plan: Plan, par: bool):
+        if par:
+            if self._side is None:
+                self._side = torch.cuda.Stream(self.device)
+            plan.run_parallel(self._side)
+        else:
+            plan.run(L.stream())
+
+    def _run_graph(self, plan: Plan, key, par: bool = False):
         g = self._graphs.get(key)
         if g is None:
             plan.run(L.stream())  # warm-up: sets kernel attributes outside capture
             torch.cuda.current_stream().synchronize()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                plan.run(L.stream())
+                self._run_plan(plan, par)
             self._graphs[key] = g
         g.replay()
 

@@ -578,3 +578,30 @@ def test_decoder_workspace_poisoning(mode, dec_fp32, dec_bf16):
     y1 = dec(rin["asr"], rin["F0_curve"], rin["N"], rin["s"], noise=rin["noise"], lengths=lens).cpu().numpy()
     assert np.isfinite(y1).all()
     np.testing.assert_array_equal(y1, y0)
+
+
+@pytest.mark.parametrize("mode", ["fp32", "bf16"])
+def test_decoder_parallel_noise_branch(mode, dec_fp32, dec_bf16):
+    """Decoder.parallel_branches: the generator's noise branch on a side stream (eager) / as a parallel graph branch
+    must give the bits of the serial schedule - same launches, same buffers, only the order between independent
+    kernels changes.  Repeated, so that a missing join would show as run-to-run differences."""
+    dec = dec_fp32 if mode == "fp32" else dec_bf16
+    inp = synth.synth_decoder_inputs(2, 30, seed=515)
+    rin, lens, _ = _ragged_inputs(3, 24, [24, 9, 17], seed=516)
+    old = dec.parallel_branches
+    try:
+        dec.parallel_branches = False
+        ref = _run(dec, inp)
+        ref_r = dec(rin["asr"], rin["F0_curve"], rin["N"], rin["s"], noise=rin["noise"], lengths=lens).cpu().numpy()
+        refg = dec(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=3).cpu().numpy()
+        dec.parallel_branches = True
+        for _ in range(5):
+            np.testing.assert_array_equal(_run(dec, inp), ref)
+            y = dec(rin["asr"], rin["F0_curve"], rin["N"], rin["s"], noise=rin["noise"], lengths=lens).cpu().numpy()
+            np.testing.assert_array_equal(y, ref_r)
+        dec.use_cuda_graph = True
+        for _ in range(3):
+            np.testing.assert_array_equal(dec(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], seed=3).cpu().numpy(), refg)
+    finally:
+        dec.use_cuda_graph = False
+        dec.parallel_branches = old
