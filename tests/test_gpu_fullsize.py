@@ -146,3 +146,42 @@ def test_config3_batch_vs_oracle():
         record(f"bf16 C3 B=64 T=320 utterance {b}", max_abs=np.abs(got - r).max(), rel_l2=rel, mel_l1=mel,
                peak=np.abs(r).max(), branch_cut_frames=len(cut))
         assert bf16_ok(got, r) and mel <= BF16_MEL_L1
+
+
+def test_config4_ragged_batch_at_full_size():
+    """BASELINE config 4's shape: one MIXED-length batch of 64 utterances, T ~ U[240, 400] padded to 416 frames (the C4
+    bucket), decoded with lengths= in one launch plan.  Utterances 0 / 31 / 63 must equal decoding them alone (same
+    kernels, per-utterance masks: <= 2e-5, fp64-atomic ordering), the padding must be silent, and the shortest one is
+    also compared with the CPU oracle at the bf16 gates."""
+    if not L.load().kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    B, T = 64, 416
+    w = synth.synth_decoder_weights(seed=2000)
+    dec = build_decoder(w, dtype="bf16")
+    lens = np.sort(np.random.default_rng(4001).integers(240, 401, size=B))[::-1].copy()
+    inp = synth.synth_decoder_inputs(B, T, seed=1234, with_noise=False)
+    g = torch.Generator(device="cuda").manual_seed(78)
+    noise = torch.randn(B, 600 * T, 9, device="cuda", generator=g)
+    y = dec(inp["asr"], inp["F0_curve"], inp["N"], inp["s"], noise=noise, lengths=lens)
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, 1, 600 * T) and bool(torch.isfinite(y).all())
+    for b in (0, 31, 63):
+        t = int(lens[b])
+        one = dec(inp["asr"][b:b + 1, :, :t], inp["F0_curve"][b:b + 1, :2 * t], inp["N"][b:b + 1, :2 * t], inp["s"][b:b + 1],
+                  noise=noise[b:b + 1, :600 * t])
+        d = float((y[b, 0, :600 * t] - one[0, 0]).abs().max())
+        assert d <= 2e-5, (b, t, d)
+        assert not bool(y[b, 0, 600 * t:].any())
+    b, t = 63, int(lens[63])
+    orc = DecoderOracle(w)
+    ref = orc(inp["asr"][b:b + 1, :, :t], inp["F0_curve"][b:b + 1, :2 * t], inp["N"][b:b + 1, :2 * t], inp["s"][b:b + 1],
+              noise[b:b + 1, :600 * t].cpu().numpy(), keep_taps=True)
+    ph = orc.taps["har"][:, 11:]
+    cut = np.nonzero((np.abs(np.abs(ph) - np.pi) < 1e-5)[:, 1:10].any(axis=1)[0])[0]
+    keep = np.ones(600 * t, bool)
+    for f in cut:                                   # atan2 branch-cut frames (DESIGN.md section 2)
+        keep[max(0, 5 * f - 4000): 5 * f + 4000] = False
+    got = y[b, 0, :600 * t].cpu().numpy()
+    record(f"bf16 C4 ragged B=64 T<=416 utterance {b} (T={t})", max_abs=np.abs(got - ref[0, 0])[keep].max(),
+           rel_l2=np.linalg.norm((got - ref[0, 0])[keep]) / np.linalg.norm(ref[0, 0][keep]), peak=np.abs(ref).max())
+    assert bf16_ok(got[keep], ref[0, 0][keep])
