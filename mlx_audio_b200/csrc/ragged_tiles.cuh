@@ -8,13 +8,17 @@ namespace kk {
 
 constexpr int RG_MAX_B = 256;   // utterances per ragged launch (table size in shared memory)
 // Rows past an utterance's end that are still processed - and therefore WRITTEN AS ZERO in the activation outputs: the
-// next convolution reads up to (taps - 1) * dil / 2 <= 28 rows beyond the end as its zero padding (through TMA, unmasked).
+// next convolution reads them through TMA, unmasked, as its zero padding.  Generator levels (20 T, 120 T rows): up to
+// (taps - 1) * dil / 2 <= 28 rows (k = 11, dilation 5) -> 64.  Front levels (T and 2 T rows, len_mul <= 2): the
+// consumers are k = 3 convolutions, the depthwise pool and the first polyphase upsampler (one or two rows) -> 8; with
+// 128-row tiles over a few hundred rows the larger margin often costs a whole tile.
 constexpr int RG_ZPAD = 64;
+constexpr int RG_ZPAD_FRONT = 8;
 
-// GEMM rows of utterance b that need processing (rows with an output row inside the utterance, plus RG_ZPAD)
+// GEMM rows of utterance b that need processing (rows with an output row inside the utterance, plus the margin)
 __device__ __forceinline__ int rg_rows(const kk_conv_desc& d, int b) {
   const int lt = ragged_len(d.lens, d.len_mul, d.len_add, b, d.L_true);
-  const int m = (lt + d.up_off + d.up - 1) / d.up + RG_ZPAD;
+  const int m = (lt + d.up_off + d.up - 1) / d.up + (d.len_mul <= 2 ? RG_ZPAD_FRONT : RG_ZPAD);
   return m < d.M ? m : d.M;
 }
 
