@@ -7,6 +7,9 @@
 // spectrogram never touch HBM.
 #include "common.cuh"
 #include "fft_fast.cuh"
+#ifdef KK_FFT_R32   // lab build: the single-exchange forward kernel (measured slower, profiles/r02_fft_experiments.txt)
+#include "fft_r32.cuh"
+#endif
 #include <math.h>
 
 namespace kk {
@@ -319,21 +322,23 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
   float* melacc = reinterpret_cast<float*>(it_f);
   int* n_items_s = reinterpret_cast<int*>(melacc + (MODE == 1 ? ff::GROUPS * MEL_MAX : 0));
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
-  float2* A = bufs + (2 * g) * ff::BUF;
-  float2* Bf = A + ff::BUF;
+  using ff::c2; using ff::pk; using ff::up;
+  c2* A = reinterpret_cast<c2*>(bufs + (2 * g) * ff::BUF);
+  c2* Bf = A + ff::BUF;
+  const c2* twc = reinterpret_cast<const c2*>(tw);
   const ff::SwzIdx sz(j);
 
   // RT: window, twiddles and unpack factors of this thread live in registers (two blocks per SM instead of four)
-  float2 rw[8], rt2[8], rt3[8], ru[4];
+  c2 rw[8], rt2[8], rt3[8], ru[4];
   if (RT) {
     ff::fill_reg_twiddles(j, rt2, rt3);
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
-      rw[t] = make_float2(a.window[2 * (j + NT * t)], a.window[2 * (j + NT * t) + 1]);
+      rw[t] = pk(a.window[2 * (j + NT * t)], a.window[2 * (j + NT * t) + 1]);
       if (t < 4) {
         float sn, cs_;
         sincospif(-(float)(j + NT * t) / (float)NC, &sn, &cs_);
-        ru[t] = make_float2(cs_, sn);
+        ru[t] = pk(cs_, sn);
       }
     }
   } else {
@@ -428,20 +433,17 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     const bool live = f < f_end;
     // ---- pass 1: windowed samples packed as complex points; the next frame's samples are requested first
     {
-      float2 v[8];
+      c2 v[8];
 #pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        const float2 w = RT ? rw[t] : win[j + NT * t];
-        v[t] = make_float2(__fmul_rn(nx[t].x, w.x), __fmul_rn(nx[t].y, w.y));   // no contraction into the first butterfly
-      }
+      for (int t = 0; t < 8; ++t) v[t] = ff::mul2(pk(nx[t]), RT ? rw[t] : pk(win[j + NT * t]));   // rounded products: no contraction into the first butterfly
       load_frame(f + ff::GROUPS, nx);
       ff::pass1_store(v, A, sz);
     }
     gsync();
-    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, tw, j, sz);
+    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, twc, j, sz);
     gsync();
-    float2 z[8];                                  // z[q] = Z[j + 64 q]: kept in registers for the unpack
-    if (RT) ff::pass3_r(Bf, rt3, sz, z); else ff::pass3(Bf, tw, j, sz, z);
+    c2 z[8];                                      // z[q] = Z[j + 64 q]: kept in registers for the unpack
+    if (RT) ff::pass3_r(Bf, rt3, sz, z); else ff::pass3(Bf, twc, j, sz, z);
     // ---- unpack in conjugate pairs: with E = (Z[k] + conj Z[nc-k]) / 2, O = (Z[k] - conj Z[nc-k]) / (2i),
     // u = e^{-2 pi i k / n}:   X[k] = E + u O   and   X[nc-k] = conj(E - u O).
     // Thread j owns the pairs of its lower four points k = j + 64 q (q < 4); their partners are the upper four points
@@ -450,36 +452,38 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     for (int q = 4; q < 8; ++q) A[sz.cons(q)] = z[q];
     gsync();
     float* P = reinterpret_cast<float*>(Bf);   // MODE 1: |X|^p of this frame (513 floats <= BUF float2)
-    auto emit = [&](int k, float2 X) {
+    auto emit = [&](int k, c2 Xp) {
       if (MODE == 0) {
-        if (live) reinterpret_cast<float2*>(a.out)[((size_t)b * a.frames + f) * bins + k] = X;
+        if (live) reinterpret_cast<c2*>(a.out)[((size_t)b * a.frames + f) * bins + k] = Xp;
       } else {
+        const float2 X = up(Xp);
         const float m2 = X.x * X.x + X.y * X.y;
         float mg = m2;
         if (a.power != 2) asm("sqrt.approx.f32 %0, %1;" : "=f"(mg) : "f"(m2));   // 1 ulp, no slow-path branch
         P[k] = mg;
       }
     };
-    auto unpack_pair = [&](int k, float2 zk, float2 zc, float2 u, bool self) {
-      zc.y = -zc.y;
-      const float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
-      const float2 d = ff::cs(zk, zc);
-      const float2 o = make_float2(0.5f * d.y, -0.5f * d.x);  // d / (2i)
-      const float2 t = ff::cm(u, o);
-      float2 X1 = ff::ca(e, t);
-      float2 X2 = make_float2(e.x - t.x, t.y - e.y);           // conj(e - t)
-      if (k == 0) { X1.y = 0.f; X2.y = 0.f; }                  // rfft: DC and Nyquist are real
+    auto unpack_pair = [&](int k, c2 zk, c2 zc, c2 u, bool self) {
+      // with zc' = conj(zc):  e = (zk + zc') / 2,  o = (zk - zc') / (2i),  t = u o
+      const c2 s = ff::fma2(zc, pk(1.f, -1.f), zk);
+      const c2 d = ff::fma2(zc, pk(-1.f, 1.f), zk);
+      const c2 e = ff::mul2(s, pk(0.5f, 0.5f)), ec = ff::mul2(s, pk(0.5f, -0.5f));
+      const c2 o = ff::mul2(ff::sw(d), pk(0.5f, -0.5f));
+      const c2 t = ff::cm(u, o);
+      c2 X1 = ff::add2(e, t);
+      c2 X2 = ff::fma2(t, pk(-1.f, 1.f), ec);                  // conj(e - t) = (e.x - t.x, t.y - e.y)
+      if (k == 0) { X1 = pk(up(X1).x, 0.f); X2 = pk(up(X2).x, 0.f); }   // rfft: DC and Nyquist are real
       emit(k, X1);
       if (!self) emit(NC - k, X2);
     };
     {
-      float2 zc[4];
+      c2 zc[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) zc[q] = A[sz.mirror(q)];
       if (j == 0) zc[0] = z[0];                                // k = 0 pairs with nc = 0 (mod nc): its own point
 #pragma unroll
-      for (int q = 0; q < 4; ++q) unpack_pair(j + NT * q, z[q], zc[q], RT ? ru[q] : tw2[j + NT * q], false);
-      if (j == 0) unpack_pair(NC / 2, z[4], z[4], make_float2(0.f, -1.f), true);   // e^{-i pi / 2}
+      for (int q = 0; q < 4; ++q) unpack_pair(j + NT * q, z[q], zc[q], RT ? ru[q] : pk(tw2[j + NT * q]), false);
+      if (j == 0) unpack_pair(NC / 2, z[4], z[4], pk(0.f, -1.f), true);   // e^{-i pi / 2}
     }
     gsync();
     if (MODE == 1) {
@@ -520,6 +524,157 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
   }
 }
 
+#ifdef KK_FFT_R32
+// ---------------------------------------------------------------- single-exchange forward kernel (fft_r32.cuh)
+// 16 threads per frame, two frames per warp, 16 per block iteration; no block-level synchronisation after the tables.
+// Pass 1 reads the samples straight from global memory (thread m: the float2 at 2 (m + 16 t), 128 contiguous bytes per
+// frame and request; reflect / zero padding only on the edge frames) and multiplies by the window (shared table, the
+// two frames of a warp read the same words: one wavefront).  The half spectrum leaves from the registers of pass 2.
+#ifndef R32_BLOCKS
+#define R32_BLOCKS 1
+#endif
+template <int MODE>
+__global__ void __launch_bounds__(fr::THREADS, R32_BLOCKS) stft_r32_kernel(const StftArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_[];
+  using fr::c2; using fr::pk; using fr::up;
+  constexpr int NC = fr::NC, n_fft = 2 * NC, bins = NC + 1;
+  c2* win = reinterpret_cast<c2*>(smem_);           // (w[2 i], w[2 i + 1]) at i
+  c2* tg = win + NC;
+  c2* xbuf = tg + fr::TG;
+  const int lane = threadIdx.x & 31, m = lane & 15, slot = threadIdx.x >> 4;
+  c2* X = xbuf + slot * fr::XBUF;
+  const fr::Twid tw(tg, m);
+  fr::fill_tables(tg);
+  // real-transform factor of the pair this lane unpacks for lane 0 (rows 16 and 0, see below): k = 16 + 32 q or 32 q
+  c2 u_coop;
+  {
+    float sn, cs_;
+    sincospif(-(float)(m < 8 ? 16 + 32 * m : 32 * (m - 8)) / (float)NC, &sn, &cs_);
+    u_coop = pk(cs_, sn);
+  }
+  for (int i = threadIdx.x; i < NC; i += blockDim.x) win[i] = pk(a.window[2 * i], a.window[2 * i + 1]);
+  __syncthreads();
+
+  const int b = blockIdx.y;
+  const float* xb = a.x + (size_t)b * a.n;
+  const int pad = a.pad_mode == 0 ? 0 : NC;
+  const bool vec_ok = ((a.hop | pad) & 1) == 0 && ((reinterpret_cast<uintptr_t>(xb) & 7) == 0);
+  const int f_begin = blockIdx.x * a.frames_per_block;
+  const int f_end = min(a.frames, f_begin + a.frames_per_block);
+  // Software pipeline: there is no register room for a second frame, and at 16 warps per SM the wait for a frame's 32
+  // loads was 36 % of a warp's time (ncu stall_long_sb).  The loads of the NEXT frame are issued inside the unpack
+  // loop of this one, two per pair, into the registers the consumed spectrum points free.
+  struct Src { const float2* vec; int base; bool live, fast; };
+  auto source = [&](int f) {
+    Src s;
+    s.base = f * a.hop - pad;
+    s.live = f < f_end;
+    s.fast = s.live && vec_ok && s.base >= 0 && s.base + n_fft <= a.n;
+    s.vec = reinterpret_cast<const float2*>(xb + s.base) + m;                  // dereferenced only if fast
+    return s;
+  };
+  // an ordered (not .nc) load behind a __syncwarp: stays behind the pairs whose registers it reuses (left to the
+  // compiler, all 32 loads are hoisted above the unpack and 64 registers spill)
+  auto ldg_ordered = [](const float2* p) -> c2 {
+    c2 r;
+    asm volatile("ld.global.b64 %0, [%1];" : "=l"(r) : "l"(p) : "memory");
+    return r;
+  };
+  auto load_point = [&](const Src& s, int t) -> c2 {   // edge frames: padding resolved per sample
+    float sv[2] = {0.f, 0.f};
+    if (s.live) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        int q = s.base + 2 * (m + 16 * t) + e;
+        if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
+          if (q < 0) q = -q;
+          if (q >= a.n) q = 2 * (a.n - 1) - q;
+          sv[e] = xb[q];
+        } else if (q >= 0 && q < a.n) {
+          sv[e] = xb[q];
+        }
+      }
+    }
+    return pk(sv[0], sv[1]);
+  };
+  // the loop bound is warp uniform (a warp's second frame may be past the end: it computes on zeros, stores nothing)
+  c2 v[32];
+  bool have = false;             // v already holds this iteration's samples (warp uniform)
+  for (int f0 = f_begin + (slot & ~1); f0 < f_end; f0 += fr::SLOTS) {
+    const int f = f0 + (slot & 1);
+    const bool live = f < f_end;
+    if (!have) {                 // first iteration, and frames that need padding: loaded here, not pipelined
+      const Src cur = source(f);
+      if (__all_sync(0xffffffffu, cur.fast || !cur.live)) {
+        if (cur.fast) {
+#pragma unroll
+          for (int t = 0; t < 32; ++t) v[t] = pk(__ldg(cur.vec + 16 * t));
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < 32; ++t) v[t] = load_point(cur, t);
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 32; ++t) v[t] = ff::mul2(v[t], win[m + 16 * t]);
+    c2 A[16], B[16];
+    fr::forward512(v, X, tw, m, A, B);
+    // ---- unpack: with E = (Z[k] + conj Z[nc-k]) / 2, O = (Z[k] - conj Z[nc-k]) / (2i), u = e^{-2 pi i k / n}:
+    //      X[k] = E + u O   and   X[nc-k] = conj(E - u O)
+    c2* orow = reinterpret_cast<c2*>(a.out) + ((size_t)b * a.frames + (live ? f : 0)) * bins;
+    const Src nxt = source(f + fr::SLOTS);
+    // warp-uniform: the next frames of both halves load unpadded (a frame past the end loads nothing, computes on
+    // whatever its registers hold and stores nothing)
+    const bool nfast = __all_sync(0xffffffffu, nxt.fast || !nxt.live);
+    // uh = u / 2
+    auto unpack_pair = [&](c2 zk, c2 zc, c2 uh, c2& X1, c2& X2) {
+      const c2 s = ff::fma2(zc, pk(1.f, -1.f), zk);            // zk + conj(zc) = 2 E
+      const float2 d = up(ff::fma2(zc, pk(-1.f, 1.f), zk));    // zk - conj(zc) = 2i O
+      const float2 t = up(ff::cm(uh, pk(d.y, -d.x)));          // u O
+      X1 = ff::fma2(s, pk(0.5f, 0.5f), pk(t));
+      X2 = ff::fma2(s, pk(0.5f, -0.5f), pk(-t.x, t.y));
+    };
+    if (MODE == 0) {
+      if (nfast && nxt.fast) {
+#pragma unroll
+        for (int t = 0; t < 32; ++t) v[t] = pk(__ldg(nxt.vec + 16 * t));
+      }
+      // lane 0 holds rows 0 and 16, which pair up inside themselves: handed to the 16 lanes through a scratch
+      __syncwarp();
+      if (m == 0) {
+#pragma unroll
+        for (int k2 = 0; k2 < 16; ++k2) {   // volatile: merged into 128-bit stores, the rows get permuted through local memory
+          *reinterpret_cast<volatile c2*>(X + k2) = A[fr::o16(k2)];
+          *reinterpret_cast<volatile c2*>(X + 16 + k2) = B[fr::o16(k2)];
+        }
+        if (live) orow[NC / 2] = fr::conj2(A[fr::o16(8)]);     // k = 256 pairs with itself: X = conj(Z)
+      }
+      // rows m and 32 - m of lanes 1..15: point k = m + 32 k2 pairs with 512 - k = (32 - m) + 32 (15 - k2)
+#pragma unroll
+      for (int k2 = 0; k2 < 16; ++k2) {
+        c2 X1, X2;
+        unpack_pair(A[fr::o16(k2)], B[fr::o16(15 - k2)], tw.u(k2, 0.5f), X1, X2);
+        if (live && m) { orow[m + 32 * k2] = X1; orow[NC - m - 32 * k2] = X2; }
+      }
+      __syncwarp();
+      {
+        // lanes 0..7: row 16, Z[16 + 32 q] with Z[16 + 32 (15 - q)]; lanes 8..15: row 0, Z[32 q] with Z[32 (16 - q)]
+        // (q = 0: DC and Nyquist, both from Z[0])
+        const int q = m & 7, rowb = m < 8;
+        const c2 zk = X[rowb ? 16 + q : q], zc = X[rowb ? 31 - q : ((16 - q) & 15)];
+        const int k = rowb ? 16 + 32 * q : 32 * q;
+        c2 X1, X2;
+        unpack_pair(zk, zc, ff::mul2(u_coop, pk(0.5f, 0.5f)), X1, X2);
+        if (k == 0) { X1 = pk(up(X1).x, 0.f); X2 = pk(up(X2).x, 0.f); }   // rfft: DC and Nyquist are real
+        if (live) { orow[k] = X1; orow[NC - k] = X2; }
+      }
+      __syncwarp();
+    }
+    have = nfast;
+  }
+}
+#endif  // KK_FFT_R32
+
 // Inverse, streaming form (hop divides n_fft, R = n_fft / hop in {1, 2, 4}): a block walks its frames four at a time;
 // every group inverse-transforms one frame straight from the global half spectrum into its (scaled, not yet windowed)
 // time frame in shared memory.  Overlap-add is a gather with the running sums in REGISTERS: thread `tid` owns the
@@ -544,18 +699,20 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
   float2* tw2 = tw + ff::TW;
   float2* bufs = tw2 + bins + 1;
   const int g = threadIdx.x / NT, j = threadIdx.x % NT;
-  float2* A = bufs + (2 * g) * ff::BUF;
-  float2* Bf = A + ff::BUF;
+  using ff::c2; using ff::pk; using ff::up;
+  c2* A = reinterpret_cast<c2*>(bufs + (2 * g) * ff::BUF);
+  c2* Bf = A + ff::BUF;
+  const c2* twc = reinterpret_cast<const c2*>(tw);
   const ff::SwzIdx sz(j);
 
-  float2 rt2[8], rt3[8], ru[8];     // RT: twiddles and pack factors in registers (see stft_fast_kernel)
+  c2 rt2[8], rt3[8], ru[8];         // RT: twiddles and pack factors in registers (see stft_fast_kernel)
   if (RT) {
     ff::fill_reg_twiddles(j, rt2, rt3);
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
       float sn, cs_;
       sincospif(-(float)(j + NT * t) / (float)NC, &sn, &cs_);
-      ru[t] = make_float2(cs_, sn);
+      ru[t] = pk(cs_, sn);
     }
   } else {
     ff::fill_tables(tw, tw2);
@@ -597,7 +754,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
       }
       // pack: Z[k] = E[k] + i O[k], E = (X[k]+conj(X[nc-k]))/2, O = (X[k]-conj(X[nc-k]))/2 * e^{+2 pi i k/n};
       // the inverse transform is conj(FFT(conj(Z)))/nc, so conj(Z) goes in.  irfft ignores Im X[0], Im X[nc].
-      float2 v[8];
+      c2 v[8];
       const float2* X = sb + (size_t)(live ? f : 0) * bins;
       float2 xk[8], xc[8];
 #pragma unroll
@@ -607,28 +764,29 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
         const int k = j + NT * t;
         float2 a_ = xk[t], c_ = xc[t];
         if (k == 0) { a_.y = 0.f; c_.y = 0.f; }
-        c_.y = -c_.y;
-        const float2 e = make_float2(0.5f * (a_.x + c_.x), 0.5f * (a_.y + c_.y));
-        const float2 dd = make_float2(0.5f * (a_.x - c_.x), 0.5f * (a_.y - c_.y));
-        float2 w2 = RT ? ru[t] : tw2[k];
-        w2.y = -w2.y;
-        const float2 o = ff::cm(dd, w2);
-        v[t] = make_float2(e.x - o.y, -(e.y + o.x));   // conj(e + i*o)
+        // with c' = conj(c):  e = (a + c') / 2,  dd = (a - c') / 2
+        const c2 e = ff::mul2(ff::fma2(pk(c_), pk(1.f, -1.f), pk(a_)), pk(0.5f, 0.5f));
+        const c2 dd = ff::mul2(ff::fma2(pk(c_), pk(-1.f, 1.f), pk(a_)), pk(0.5f, 0.5f));
+        const float2 w2 = up(RT ? ru[t] : pk(tw2[k]));
+        const c2 o = ff::cm(dd, pk(w2.x, -w2.y));
+        const float2 z = up(ff::fma2(ff::sw(o), pk(-1.f, 1.f), e));   // e + i*o = (e.x - o.y, e.y + o.x)
+        v[t] = pk(z.x, -z.y);                                         // conj
       }
       ff::pass1_store(v, A, sz);
     }
     gsync();
-    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, tw, j, sz);
+    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, twc, j, sz);
     gsync();
     {
-      float2 v[8];
-      if (RT) ff::pass3_r(Bf, rt3, sz, v); else ff::pass3(Bf, tw, j, sz, v);
-      float2* tfg = A;   // the group's time frame (n_fft floats), reusing its first exchange buffer
+      c2 v[8];
+      if (RT) ff::pass3_r(Bf, rt3, sz, v); else ff::pass3(Bf, twc, j, sz, v);
+      c2* tfg = A;       // the group's time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         // conj only (the factor 1/2 of 1/n is already inside E and O): the 1/nc of irfft is a power of two, so it commutes exactly with the window products and the
         // overlap-add sums and is applied once per output sample below instead of twice per transform point
-        tfg[j + NT * q] = live ? make_float2(v[q].x, -v[q].y) : make_float2(0.f, 0.f);
+        const float2 vq = up(v[q]);
+        tfg[j + NT * q] = live ? pk(vq.x, -vq.y) : pk(0.f, 0.f);
       }
     }
     __syncthreads();
@@ -700,6 +858,18 @@ static int stft_group(int nc) { int g = 2048 / nc; return g < 1 ? 1 : (g > 8 ? 8
 template <int MODE>
 static int launch_stft(const StftArgs& a0, const FftPlan& p, int B, cudaStream_t st) {
   StftArgs a = a0;
+#ifdef KK_FFT_R32
+  if (p.n_fft == 2 * fr::NC && MODE == 0) {   // single-exchange radix-32 x 16 path
+    int fpb = 32;
+    while (fpb < 256 && (long long)cdiv(a.frames, fpb * 2) * B >= 148 * 16) fpb *= 2;
+    a.frames_per_block = fpb;
+    const size_t smem = (size_t)(fr::NC + fr::TG + fr::SLOTS * fr::XBUF) * 8;
+    KK_CUDA(cudaFuncSetAttribute(stft_r32_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    stft_r32_kernel<MODE><<<dim3(cdiv(a.frames, fpb), B), fr::THREADS, smem, st>>>(a);
+    KK_LAUNCH_CHECK("stft_r32_kernel");
+    return KK_OK;
+  }
+#endif
   if (p.n_fft == 2 * ff::NC) {   // register-resident radix-8 path
     int fpb = 32;
     while (fpb < 256 && (long long)cdiv(a.frames, fpb * 2) * B >= 148 * 16) fpb *= 2;

@@ -47,34 +47,54 @@ struct SwzIdx {
   __device__ __forceinline__ int st2(int q) const { return ((q & 1) ? o : e) + 16 * (q >> 1) + (kk ^ (q >> 1)); }
   __device__ __forceinline__ int mirror(int q) const { return ((64 * (7 - q) + zoff) & 511) + (((7 - q) & 1) ? d1 : d0); }
 };
+// Packed arithmetic: a complex value is one 64-bit register pair and every complex add / subtract / scale is ONE
+// FADD2 / FFMA2 (sm_100 f32x2: both lanes IEEE round-to-nearest, so the bits equal the scalar forms').  ptxas folds
+// the lane swap, a per-lane negation and a scalar broadcast into operand modifiers (R.F32x2.LO_HI, .NP, R.F32), so a
+// multiply by -i costs nothing and a complex product is FMUL2 + FFMA2.  These kernels are issue bound (ncu: 70 % of
+// the issue slots, 25 % occupancy): the scalar forms spent 2-4 slots where these spend 1-2.
+typedef unsigned long long c2;
+__device__ __forceinline__ c2 pk(float lo, float hi) { c2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ c2 pk(float2 v) { return pk(v.x, v.y); }
+__device__ __forceinline__ float2 up(c2 v) { float2 r; asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v)); return r; }
+__device__ __forceinline__ c2 sw(c2 v) { const float2 t = up(v); return pk(t.y, t.x); }
+__device__ __forceinline__ c2 add2(c2 a, c2 b) { c2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ c2 sub2(c2 a, c2 b) { c2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ c2 mul2(c2 a, c2 b) { c2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ c2 fma2(c2 a, c2 b, c2 c) { c2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+// a + (-i) d  and  a - (-i) d  (d's lanes swapped, signs from the constant: the products by +-1 are exact)
+__device__ __forceinline__ c2 add_mi(c2 a, c2 d) { return fma2(sw(d), pk(1.f, -1.f), a); }
+__device__ __forceinline__ c2 sub_mi(c2 a, c2 d) { return fma2(sw(d), pk(-1.f, 1.f), a); }
 // complex product with the contraction spelled out, so that every kernel variant (shared-memory or register tables,
-// any batch size) produces the same bits for the same frame
-__device__ __forceinline__ float2 cm(float2 a, float2 b) {
-  return make_float2(fmaf(a.x, b.x, -__fmul_rn(a.y, b.y)), fmaf(a.x, b.y, __fmul_rn(a.y, b.x)));
+// any batch size) produces the same bits for the same frame:
+//   (fma(a.x, b.x, -(a.y * b.y)), fma(a.x, b.y, a.y * b.x))
+__device__ __forceinline__ c2 cm(c2 a, c2 b) {
+  const float2 af = up(a);
+  float2 t = up(mul2(pk(af.y, af.y), sw(b)));
+  t.x = -t.x;
+  return fma2(pk(af.x, af.x), b, pk(t));
 }
-__device__ __forceinline__ float2 ca(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 cs(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
-__device__ __forceinline__ float2 mi(float2 a) { return make_float2(a.y, -a.x); }   // -i * a
+__device__ __forceinline__ float2 cm(float2 a, float2 b) { return up(cm(pk(a), pk(b))); }
+__device__ __forceinline__ float2 ca(float2 a, float2 b) { return up(add2(pk(a), pk(b))); }
+__device__ __forceinline__ float2 cs(float2 a, float2 b) { return up(sub2(pk(a), pk(b))); }
 
-// forward 8-point DFT (e^{-2 pi i t q / 8}), natural order in and out
-__device__ __forceinline__ void fft8(float2 (&v)[8]) {
+// forward 8-point DFT (e^{-2 pi i t q / 8}), natural order in and out: 26 packed instructions
+__device__ __forceinline__ void fft8(c2 (&v)[8]) {
   const float h = 0.70710678118654752440f;
-  const float2 a0 = ca(v[0], v[4]), a4 = cs(v[0], v[4]);
-  const float2 a2 = ca(v[2], v[6]), a6 = mi(cs(v[2], v[6]));
-  const float2 a1 = ca(v[1], v[5]), a5 = cs(v[1], v[5]);
-  const float2 a3 = ca(v[3], v[7]), a7 = mi(cs(v[3], v[7]));
-  const float2 b0 = ca(a0, a2), b2 = cs(a0, a2), b4 = ca(a4, a6), b6 = cs(a4, a6);
-  const float2 b1 = ca(a1, a3), b3 = mi(cs(a1, a3));
-  const float2 s5 = ca(a5, a7), d7 = cs(a5, a7);
-  // b5 = s5 (1 - i)/sqrt 2, b7 = d7 (-1 - i)/sqrt 2 folded into the last butterflies as explicit FMAs: left to the
-  // compiler, the contraction of h * (..) +- b differs between kernel variants and with it the low bits of the result
-  const float p5 = s5.x + s5.y, q5 = s5.y - s5.x, r7 = d7.y - d7.x, u7 = d7.x + d7.y;
-  v[0] = ca(b0, b1); v[4] = cs(b0, b1);
-  v[2] = ca(b2, b3); v[6] = cs(b2, b3);
-  v[1] = make_float2(fmaf(h, p5, b4.x), fmaf(h, q5, b4.y));
-  v[5] = make_float2(fmaf(-h, p5, b4.x), fmaf(-h, q5, b4.y));
-  v[3] = make_float2(fmaf(h, r7, b6.x), fmaf(-h, u7, b6.y));
-  v[7] = make_float2(fmaf(-h, r7, b6.x), fmaf(h, u7, b6.y));
+  const c2 a0 = add2(v[0], v[4]), a4 = sub2(v[0], v[4]);
+  const c2 a2 = add2(v[2], v[6]), d26 = sub2(v[2], v[6]);
+  const c2 a1 = add2(v[1], v[5]), a5 = sub2(v[1], v[5]);
+  const c2 a3 = add2(v[3], v[7]), d37 = sub2(v[3], v[7]);
+  const c2 b0 = add2(a0, a2), b2 = sub2(a0, a2), b4 = add_mi(a4, d26), b6 = sub_mi(a4, d26);
+  const c2 b1 = add2(a1, a3), d13 = sub2(a1, a3);
+  const c2 s5 = add_mi(a5, d37), d7 = sub_mi(a5, d37);
+  // b5 = s5 (1 - i)/sqrt 2 and b7 = d7 (-1 - i)/sqrt 2 folded into the last butterflies as explicit FMAs:
+  // pq = (s5.x + s5.y, s5.y - s5.x), ru = (d7.y - d7.x, d7.x + d7.y)
+  const c2 pq = fma2(sw(s5), pk(1.f, -1.f), s5);
+  const c2 ru = fma2(d7, pk(-1.f, 1.f), sw(d7));
+  v[0] = add2(b0, b1); v[4] = sub2(b0, b1);
+  v[2] = add_mi(b2, d13); v[6] = sub_mi(b2, d13);
+  v[1] = fma2(pk(h, h), pq, b4); v[5] = fma2(pk(-h, -h), pq, b4);
+  v[3] = fma2(pk(h, -h), ru, b6); v[7] = fma2(pk(-h, h), ru, b6);
 }
 
 // Twiddle tables laid out per pass so that a warp reads consecutive addresses (a single exp(-2 pi i j/512) table
@@ -98,14 +118,14 @@ __device__ __forceinline__ void fill_tables(float2* tw, float2* tw2) {
 }
 
 // pass 1 (ns = 1): v holds points j + 64 t; result to A
-__device__ __forceinline__ void pass1_store(float2 (&v)[8], float2* A, const SwzIdx& z) {
+__device__ __forceinline__ void pass1_store(c2 (&v)[8], c2* A, const SwzIdx& z) {
   fft8(v);
 #pragma unroll
   for (int q = 0; q < 8; ++q) A[z.st1(q)] = v[q];
 }
 // pass 2 (ns = 8): A -> B
-__device__ __forceinline__ void pass2(const float2* A, float2* B, const float2* tw, int j, const SwzIdx& z) {
-  float2 v[8];
+__device__ __forceinline__ void pass2(const c2* A, c2* B, const c2* tw, int j, const SwzIdx& z) {
+  c2 v[8];
   const int k = j & 7;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
@@ -117,7 +137,7 @@ __device__ __forceinline__ void pass2(const float2* A, float2* B, const float2* 
   for (int q = 0; q < 8; ++q) B[z.st2(q)] = v[q];
 }
 // pass 3 (ns = 64): B -> registers; v[q] = point j + 64 q of the transform
-__device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, const SwzIdx& z, float2 (&v)[8]) {
+__device__ __forceinline__ void pass3(const c2* B, const c2* tw, int j, const SwzIdx& z, c2 (&v)[8]) {
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = B[z.cons(t)];
@@ -130,19 +150,19 @@ __device__ __forceinline__ void pass3(const float2* B, const float2* tw, int j, 
 // Register-table variants: the twiddles a thread needs are the same for every frame (they depend on j only), so a
 // kernel that can afford ~60 more registers keeps them out of shared memory altogether (30 of the 78 64-bit shared
 // requests per thread and frame are table reads).  Same sincospif arguments as fill_tables: bit-identical values.
-__device__ __forceinline__ void fill_reg_twiddles(int j, float2 (&t2)[8], float2 (&t3)[8]) {
+__device__ __forceinline__ void fill_reg_twiddles(int j, c2 (&t2)[8], c2 (&t3)[8]) {
   const int k = j & 7;
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     float s, c;
     sincospif(-2.0f * (float)(t * k) / 64.0f, &s, &c);
-    t2[t] = make_float2(c, s);
+    t2[t] = pk(c, s);
     sincospif(-2.0f * (float)(t * j) / (float)NC, &s, &c);
-    t3[t] = make_float2(c, s);
+    t3[t] = pk(c, s);
   }
 }
-__device__ __forceinline__ void pass2_r(const float2* A, float2* B, const float2 (&t2)[8], const SwzIdx& z) {
-  float2 v[8];
+__device__ __forceinline__ void pass2_r(const c2* A, c2* B, const c2 (&t2)[8], const SwzIdx& z) {
+  c2 v[8];
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = A[z.cons(t)];
@@ -152,7 +172,7 @@ __device__ __forceinline__ void pass2_r(const float2* A, float2* B, const float2
 #pragma unroll
   for (int q = 0; q < 8; ++q) B[z.st2(q)] = v[q];
 }
-__device__ __forceinline__ void pass3_r(const float2* B, const float2 (&t3)[8], const SwzIdx& z, float2 (&v)[8]) {
+__device__ __forceinline__ void pass3_r(const c2* B, const c2 (&t3)[8], const SwzIdx& z, c2 (&v)[8]) {
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = B[z.cons(t)];
