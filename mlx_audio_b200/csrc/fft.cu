@@ -345,6 +345,14 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
     ff::fill_tables(tw, tw2);
     for (int i = threadIdx.x; i < NC; i += blockDim.x) win[i] = make_float2(a.window[2 * i], a.window[2 * i + 1]);
   }
+  // log-mel: the unpack factor of point j + 64 q as u0 * W16^q (u0 = exp(-i pi j / 512) in two registers, second factor
+  // a compile-time constant) instead of a table read
+  c2 u0 = 0;
+  if (MODE == 1) {
+    float sn, cs_;
+    sincospif(-(float)j / (float)NC, &sn, &cs_);
+    u0 = pk(cs_, sn);
+  }
   if (MODE == 1) {   // non-zero span of every mel filter: one warp per row
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int m = warp; m < a.n_mels; m += ff::THREADS / 32) {
@@ -440,10 +448,11 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
       ff::pass1_store(v, A, sz);
     }
     gsync();
-    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, twc, j, sz);
+    constexpr bool POW = MODE == 1;   // log-mel: no bit-for-bit twin, twiddles as products (see ff::tw_powers)
+    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2<POW>(A, Bf, twc, j, sz);
     gsync();
     c2 z[8];                                      // z[q] = Z[j + 64 q]: kept in registers for the unpack
-    if (RT) ff::pass3_r(Bf, rt3, sz, z); else ff::pass3(Bf, twc, j, sz, z);
+    if (RT) ff::pass3_r(Bf, rt3, sz, z); else ff::pass3<POW>(Bf, twc, j, sz, z);
     // ---- unpack in conjugate pairs: with E = (Z[k] + conj Z[nc-k]) / 2, O = (Z[k] - conj Z[nc-k]) / (2i),
     // u = e^{-2 pi i k / n}:   X[k] = E + u O   and   X[nc-k] = conj(E - u O).
     // Thread j owns the pairs of its lower four points k = j + 64 q (q < 4); their partners are the upper four points
@@ -482,7 +491,9 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
       for (int q = 0; q < 4; ++q) zc[q] = A[sz.mirror(q)];
       if (j == 0) zc[0] = z[0];                                // k = 0 pairs with nc = 0 (mod nc): its own point
 #pragma unroll
-      for (int q = 0; q < 4; ++q) unpack_pair(j + NT * q, z[q], zc[q], RT ? ru[q] : pk(tw2[j + NT * q]), false);
+      for (int q = 0; q < 4; ++q)
+        unpack_pair(j + NT * q, z[q], zc[q],
+                    RT ? ru[q] : MODE == 1 ? (q ? ff::cmc(u0, ff::w32c(2 * q), -ff::w32s(2 * q)) : u0) : pk(tw2[j + NT * q]), false);
       if (j == 0) unpack_pair(NC / 2, z[4], z[4], pk(0.f, -1.f), true);   // e^{-i pi / 2}
     }
     gsync();
@@ -717,6 +728,15 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
   } else {
     ff::fill_tables(tw, tw2);
   }
+  // table variant: the pack factor of point j + 64 t is u0 * W16^t, u0 = exp(-i pi j / 512) in two registers and the
+  // second factor a compile-time constant (8 fewer 64-bit shared loads per thread and frame: the L1 / shared data pipe
+  // is what bounds this kernel)
+  c2 u0;
+  {
+    float sn, cs_;
+    sincospif(-(float)j / (float)NC, &sn, &cs_);
+    u0 = pk(cs_, sn);
+  }
   // synthesis-window taps of this thread's offsets, and the partial sums carried between iterations
   float w[OFFS][R], carry[OFFS][R > 1 ? R - 1 : 1], ws_full[OFFS];
 #pragma unroll
@@ -767,7 +787,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
         // with c' = conj(c):  e = (a + c') / 2,  dd = (a - c') / 2
         const c2 e = ff::mul2(ff::fma2(pk(c_), pk(1.f, -1.f), pk(a_)), pk(0.5f, 0.5f));
         const c2 dd = ff::mul2(ff::fma2(pk(c_), pk(-1.f, 1.f), pk(a_)), pk(0.5f, 0.5f));
-        const float2 w2 = up(RT ? ru[t] : pk(tw2[k]));
+        const float2 w2 = up(RT ? ru[t] : (t ? ff::cmc(u0, ff::w32c(2 * t), -ff::w32s(2 * t)) : u0));
         const c2 o = ff::cm(dd, pk(w2.x, -w2.y));
         const float2 z = up(ff::fma2(ff::sw(o), pk(-1.f, 1.f), e));   // e + i*o = (e.x - o.y, e.y + o.x)
         v[t] = pk(z.x, -z.y);                                         // conj
@@ -775,11 +795,11 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
       ff::pass1_store(v, A, sz);
     }
     gsync();
-    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2(A, Bf, twc, j, sz);
+    if (RT) ff::pass2_r(A, Bf, rt2, sz); else ff::pass2<true>(A, Bf, twc, j, sz);
     gsync();
     {
       c2 v[8];
-      if (RT) ff::pass3_r(Bf, rt3, sz, v); else ff::pass3(Bf, twc, j, sz, v);
+      if (RT) ff::pass3_r(Bf, rt3, sz, v); else ff::pass3<true>(Bf, twc, j, sz, v);
       c2* tfg = A;       // the group's time frame (n_fft floats), reusing its first exchange buffer
 #pragma unroll
       for (int q = 0; q < 8; ++q) {

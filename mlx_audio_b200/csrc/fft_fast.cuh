@@ -77,6 +77,86 @@ __device__ __forceinline__ float2 cm(float2 a, float2 b) { return up(cm(pk(a), p
 __device__ __forceinline__ float2 ca(float2 a, float2 b) { return up(add2(pk(a), pk(b))); }
 __device__ __forceinline__ float2 cs(float2 a, float2 b) { return up(sub2(pk(a), pk(b))); }
 
+__host__ __device__ constexpr float w32c(int e) {   // cos(2 pi e / 32), correctly rounded
+  switch (e & 31) {
+    case 0: return 0x1.0000000000000p+0f;   // 1
+    case 1: return 0x1.f6297c0000000p-1f;   // 0.980785251
+    case 2: return 0x1.d906bc0000000p-1f;   // 0.923879504
+    case 3: return 0x1.a9b6620000000p-1f;   // 0.831469595
+    case 4: return 0x1.6a09e60000000p-1f;   // 0.707106769
+    case 5: return 0x1.1c73b40000000p-1f;   // 0.555570245
+    case 6: return 0x1.87de2a0000000p-2f;   // 0.382683426
+    case 7: return 0x1.8f8b840000000p-3f;   // 0.195090324
+    case 8: return 0x0.0p+0f;   // 0
+    case 9: return -0x1.8f8b840000000p-3f;   // -0.195090324
+    case 10: return -0x1.87de2a0000000p-2f;   // -0.382683426
+    case 11: return -0x1.1c73b40000000p-1f;   // -0.555570245
+    case 12: return -0x1.6a09e60000000p-1f;   // -0.707106769
+    case 13: return -0x1.a9b6620000000p-1f;   // -0.831469595
+    case 14: return -0x1.d906bc0000000p-1f;   // -0.923879504
+    case 15: return -0x1.f6297c0000000p-1f;   // -0.980785251
+    case 16: return -0x1.0000000000000p+0f;   // -1
+    case 17: return -0x1.f6297c0000000p-1f;   // -0.980785251
+    case 18: return -0x1.d906bc0000000p-1f;   // -0.923879504
+    case 19: return -0x1.a9b6620000000p-1f;   // -0.831469595
+    case 20: return -0x1.6a09e60000000p-1f;   // -0.707106769
+    case 21: return -0x1.1c73b40000000p-1f;   // -0.555570245
+    case 22: return -0x1.87de2a0000000p-2f;   // -0.382683426
+    case 23: return -0x1.8f8b840000000p-3f;   // -0.195090324
+    case 24: return 0x0.0p+0f;   // 0
+    case 25: return 0x1.8f8b840000000p-3f;   // 0.195090324
+    case 26: return 0x1.87de2a0000000p-2f;   // 0.382683426
+    case 27: return 0x1.1c73b40000000p-1f;   // 0.555570245
+    case 28: return 0x1.6a09e60000000p-1f;   // 0.707106769
+    case 29: return 0x1.a9b6620000000p-1f;   // 0.831469595
+    case 30: return 0x1.d906bc0000000p-1f;   // 0.923879504
+    case 31: return 0x1.f6297c0000000p-1f;   // 0.980785251
+  }
+  return 0.f;
+}
+__host__ __device__ constexpr float w32s(int e) {   // sin(2 pi e / 32), correctly rounded
+  switch (e & 31) {
+    case 0: return 0x0.0p+0f;   // 0
+    case 1: return 0x1.8f8b840000000p-3f;   // 0.195090324
+    case 2: return 0x1.87de2a0000000p-2f;   // 0.382683426
+    case 3: return 0x1.1c73b40000000p-1f;   // 0.555570245
+    case 4: return 0x1.6a09e60000000p-1f;   // 0.707106769
+    case 5: return 0x1.a9b6620000000p-1f;   // 0.831469595
+    case 6: return 0x1.d906bc0000000p-1f;   // 0.923879504
+    case 7: return 0x1.f6297c0000000p-1f;   // 0.980785251
+    case 8: return 0x1.0000000000000p+0f;   // 1
+    case 9: return 0x1.f6297c0000000p-1f;   // 0.980785251
+    case 10: return 0x1.d906bc0000000p-1f;   // 0.923879504
+    case 11: return 0x1.a9b6620000000p-1f;   // 0.831469595
+    case 12: return 0x1.6a09e60000000p-1f;   // 0.707106769
+    case 13: return 0x1.1c73b40000000p-1f;   // 0.555570245
+    case 14: return 0x1.87de2a0000000p-2f;   // 0.382683426
+    case 15: return 0x1.8f8b840000000p-3f;   // 0.195090324
+    case 16: return 0x0.0p+0f;   // 0
+    case 17: return -0x1.8f8b840000000p-3f;   // -0.195090324
+    case 18: return -0x1.87de2a0000000p-2f;   // -0.382683426
+    case 19: return -0x1.1c73b40000000p-1f;   // -0.555570245
+    case 20: return -0x1.6a09e60000000p-1f;   // -0.707106769
+    case 21: return -0x1.a9b6620000000p-1f;   // -0.831469595
+    case 22: return -0x1.d906bc0000000p-1f;   // -0.923879504
+    case 23: return -0x1.f6297c0000000p-1f;   // -0.980785251
+    case 24: return -0x1.0000000000000p+0f;   // -1
+    case 25: return -0x1.f6297c0000000p-1f;   // -0.980785251
+    case 26: return -0x1.d906bc0000000p-1f;   // -0.923879504
+    case 27: return -0x1.a9b6620000000p-1f;   // -0.831469595
+    case 28: return -0x1.6a09e60000000p-1f;   // -0.707106769
+    case 29: return -0x1.1c73b40000000p-1f;   // -0.555570245
+    case 30: return -0x1.87de2a0000000p-2f;   // -0.382683426
+    case 31: return -0x1.8f8b840000000p-3f;   // -0.195090324
+  }
+  return 0.f;
+}
+
+// a * (c + i s), contraction as ff::cm
+__device__ __forceinline__ c2 cmc(c2 a, float c, float s) {
+  const float2 af = up(a);
+  return fma2(pk(af.x, af.x), pk(c, s), mul2(pk(af.y, af.y), pk(-s, c)));
+}
 // forward 8-point DFT (e^{-2 pi i t q / 8}), natural order in and out: 26 packed instructions
 __device__ __forceinline__ void fft8(c2 (&v)[8]) {
   const float h = 0.70710678118654752440f;
@@ -117,6 +197,14 @@ __device__ __forceinline__ void fill_tables(float2* tw, float2* tw2) {
   }
 }
 
+// The seven twiddles w^t (t = 1..7) of a radix-8 pass from the three table values w, w^2, w^4: four complex products
+// instead of four more 64-bit shared loads per pass (the L1 / shared data pipe bounds these kernels).  Used (POW) by the
+// kernels whose output is not compared bit for bit with a register-table variant: the inverse and the log-mel.
+__device__ __forceinline__ void tw_powers(c2 w1, c2 w2, c2 w4, c2 (&w)[8]) {
+  w[1] = w1; w[2] = w2; w[4] = w4;
+  w[3] = cm(w1, w2); w[5] = cm(w1, w4); w[6] = cm(w2, w4); w[7] = cm(w[3], w4);
+}
+
 // pass 1 (ns = 1): v holds points j + 64 t; result to A
 __device__ __forceinline__ void pass1_store(c2 (&v)[8], c2* A, const SwzIdx& z) {
   fft8(v);
@@ -124,24 +212,29 @@ __device__ __forceinline__ void pass1_store(c2 (&v)[8], c2* A, const SwzIdx& z) 
   for (int q = 0; q < 8; ++q) A[z.st1(q)] = v[q];
 }
 // pass 2 (ns = 8): A -> B
+template <bool POW = false>
 __device__ __forceinline__ void pass2(const c2* A, c2* B, const c2* tw, int j, const SwzIdx& z) {
-  c2 v[8];
+  c2 v[8], w[8];
   const int k = j & 7;
+  if (POW) tw_powers(tw[8 + k], tw[16 + k], tw[32 + k], w);
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = A[z.cons(t)];
-    if (t) v[t] = cm(v[t], tw[t * 8 + k]);
+    if (t) v[t] = cm(v[t], POW ? w[t] : tw[t * 8 + k]);
   }
   fft8(v);
 #pragma unroll
   for (int q = 0; q < 8; ++q) B[z.st2(q)] = v[q];
 }
 // pass 3 (ns = 64): B -> registers; v[q] = point j + 64 q of the transform
+template <bool POW = false>
 __device__ __forceinline__ void pass3(const c2* B, const c2* tw, int j, const SwzIdx& z, c2 (&v)[8]) {
+  c2 w[8];
+  if (POW) tw_powers(tw[64 + 64 + j], tw[64 + 128 + j], tw[64 + 256 + j], w);
 #pragma unroll
   for (int t = 0; t < 8; ++t) {
     v[t] = B[z.cons(t)];
-    if (t) v[t] = cm(v[t], tw[64 + t * 64 + j]);
+    if (t) v[t] = cm(v[t], POW ? w[t] : tw[64 + t * 64 + j]);
   }
   fft8(v);
 }

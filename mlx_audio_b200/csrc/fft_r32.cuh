@@ -17,7 +17,7 @@
 namespace kk {
 namespace fr {
 using ff::c2; using ff::pk; using ff::up; using ff::sw; using ff::add2; using ff::sub2; using ff::mul2; using ff::fma2;
-using ff::add_mi; using ff::sub_mi; using ff::cm; using ff::fft8;
+using ff::add_mi; using ff::sub_mi; using ff::cm; using ff::fft8; using ff::w32c; using ff::w32s; using ff::cmc;
 
 constexpr int NC = 512;             // complex points
 constexpr int LANES = 16;           // threads per transform
@@ -29,86 +29,6 @@ constexpr int XBUF = 32 * PITCH;    // exchange buffer of one transform (c2 elem
 constexpr int THREADS = R32_THREADS;   // 8 warps = 16 transforms per block iteration
 constexpr int SLOTS = THREADS / LANES;
 
-__host__ __device__ constexpr float w32c(int e) {   // cos(2 pi e / 32), correctly rounded
-  switch (e & 31) {
-    case 0: return 0x1.0000000000000p+0f;   // 1
-    case 1: return 0x1.f6297c0000000p-1f;   // 0.980785251
-    case 2: return 0x1.d906bc0000000p-1f;   // 0.923879504
-    case 3: return 0x1.a9b6620000000p-1f;   // 0.831469595
-    case 4: return 0x1.6a09e60000000p-1f;   // 0.707106769
-    case 5: return 0x1.1c73b40000000p-1f;   // 0.555570245
-    case 6: return 0x1.87de2a0000000p-2f;   // 0.382683426
-    case 7: return 0x1.8f8b840000000p-3f;   // 0.195090324
-    case 8: return 0x0.0p+0f;   // 0
-    case 9: return -0x1.8f8b840000000p-3f;   // -0.195090324
-    case 10: return -0x1.87de2a0000000p-2f;   // -0.382683426
-    case 11: return -0x1.1c73b40000000p-1f;   // -0.555570245
-    case 12: return -0x1.6a09e60000000p-1f;   // -0.707106769
-    case 13: return -0x1.a9b6620000000p-1f;   // -0.831469595
-    case 14: return -0x1.d906bc0000000p-1f;   // -0.923879504
-    case 15: return -0x1.f6297c0000000p-1f;   // -0.980785251
-    case 16: return -0x1.0000000000000p+0f;   // -1
-    case 17: return -0x1.f6297c0000000p-1f;   // -0.980785251
-    case 18: return -0x1.d906bc0000000p-1f;   // -0.923879504
-    case 19: return -0x1.a9b6620000000p-1f;   // -0.831469595
-    case 20: return -0x1.6a09e60000000p-1f;   // -0.707106769
-    case 21: return -0x1.1c73b40000000p-1f;   // -0.555570245
-    case 22: return -0x1.87de2a0000000p-2f;   // -0.382683426
-    case 23: return -0x1.8f8b840000000p-3f;   // -0.195090324
-    case 24: return 0x0.0p+0f;   // 0
-    case 25: return 0x1.8f8b840000000p-3f;   // 0.195090324
-    case 26: return 0x1.87de2a0000000p-2f;   // 0.382683426
-    case 27: return 0x1.1c73b40000000p-1f;   // 0.555570245
-    case 28: return 0x1.6a09e60000000p-1f;   // 0.707106769
-    case 29: return 0x1.a9b6620000000p-1f;   // 0.831469595
-    case 30: return 0x1.d906bc0000000p-1f;   // 0.923879504
-    case 31: return 0x1.f6297c0000000p-1f;   // 0.980785251
-  }
-  return 0.f;
-}
-__host__ __device__ constexpr float w32s(int e) {   // sin(2 pi e / 32), correctly rounded
-  switch (e & 31) {
-    case 0: return 0x0.0p+0f;   // 0
-    case 1: return 0x1.8f8b840000000p-3f;   // 0.195090324
-    case 2: return 0x1.87de2a0000000p-2f;   // 0.382683426
-    case 3: return 0x1.1c73b40000000p-1f;   // 0.555570245
-    case 4: return 0x1.6a09e60000000p-1f;   // 0.707106769
-    case 5: return 0x1.a9b6620000000p-1f;   // 0.831469595
-    case 6: return 0x1.d906bc0000000p-1f;   // 0.923879504
-    case 7: return 0x1.f6297c0000000p-1f;   // 0.980785251
-    case 8: return 0x1.0000000000000p+0f;   // 1
-    case 9: return 0x1.f6297c0000000p-1f;   // 0.980785251
-    case 10: return 0x1.d906bc0000000p-1f;   // 0.923879504
-    case 11: return 0x1.a9b6620000000p-1f;   // 0.831469595
-    case 12: return 0x1.6a09e60000000p-1f;   // 0.707106769
-    case 13: return 0x1.1c73b40000000p-1f;   // 0.555570245
-    case 14: return 0x1.87de2a0000000p-2f;   // 0.382683426
-    case 15: return 0x1.8f8b840000000p-3f;   // 0.195090324
-    case 16: return 0x0.0p+0f;   // 0
-    case 17: return -0x1.8f8b840000000p-3f;   // -0.195090324
-    case 18: return -0x1.87de2a0000000p-2f;   // -0.382683426
-    case 19: return -0x1.1c73b40000000p-1f;   // -0.555570245
-    case 20: return -0x1.6a09e60000000p-1f;   // -0.707106769
-    case 21: return -0x1.a9b6620000000p-1f;   // -0.831469595
-    case 22: return -0x1.d906bc0000000p-1f;   // -0.923879504
-    case 23: return -0x1.f6297c0000000p-1f;   // -0.980785251
-    case 24: return -0x1.0000000000000p+0f;   // -1
-    case 25: return -0x1.f6297c0000000p-1f;   // -0.980785251
-    case 26: return -0x1.d906bc0000000p-1f;   // -0.923879504
-    case 27: return -0x1.a9b6620000000p-1f;   // -0.831469595
-    case 28: return -0x1.6a09e60000000p-1f;   // -0.707106769
-    case 29: return -0x1.1c73b40000000p-1f;   // -0.555570245
-    case 30: return -0x1.87de2a0000000p-2f;   // -0.382683426
-    case 31: return -0x1.8f8b840000000p-3f;   // -0.195090324
-  }
-  return 0.f;
-}
-
-// a * (c + i s), contraction as ff::cm
-__device__ __forceinline__ c2 cmc(c2 a, float c, float s) {
-  const float2 af = up(a);
-  return fma2(pk(af.x, af.x), pk(c, s), mul2(pk(af.y, af.y), pk(-s, c)));
-}
 __device__ __forceinline__ c2 mul_mi(c2 a) { const float2 t = up(a); return pk(t.y, -t.x); }   // -i * a
 __device__ __forceinline__ c2 conj2(c2 a) { const float2 t = up(a); return pk(t.x, -t.y); }
 
