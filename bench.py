@@ -154,13 +154,13 @@ def bench_dsp(dev, peaks):
     mel = torch.empty(B, frames, 80, device=dev)
     st = L.stream()
     calls = {
-        "stft": ("kk_stft_f32", lambda: lib.kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(spec), B, n, n_fft, hop, 1, frames, st),
+        "stft": ("kk_stft_f32", lambda: lib.kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(spec), B, n, n_fft, hop, 1, frames, None, st),
                  x.numel() * 4 + spec.numel() * 4),
         "istft": ("kk_istft_f32", lambda: lib.kk_istft_f32(L.ptr(spec), L.ptr(wp), L.ptr(sig), B, frames, n_fft, hop,
-                                                           n_fft // 2, sig.shape[1], st),
+                                                           n_fft // 2, sig.shape[1], None, 0, st),
                   spec.numel() * 4 + sig.numel() * 4),
         "logmel": ("kk_logmel_f32", lambda: lib.kk_logmel_f32(L.ptr(x), L.ptr(w), L.ptr(fb), L.ptr(mel), B, n, n_fft, hop,
-                                                              1, frames, 80, 1, 1, 1e-5, st),
+                                                              1, frames, 80, 1, 1, 1e-5, None, st),
                    x.numel() * 4 + mel.numel() * 4),
     }
     out = {"workload": f"{B} signals x {n} samples (30 s, 24 kHz), n_fft {n_fft}, hop {hop}, Hann; inputs resident; "

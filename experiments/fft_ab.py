@@ -25,9 +25,9 @@ def run(lib, B, n, n_fft=1024, hop=256, time_it=False):
     mel = torch.empty(B, frames, 80, device=dev)
     st = L.stream()
     calls = {
-        "stft": lambda: lib.kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(spec), B, n, n_fft, hop, 1, frames, st),
-        "istft": lambda: lib.kk_istft_f32(L.ptr(spec), L.ptr(wp), L.ptr(sig), B, frames, n_fft, hop, n_fft // 2, sig.shape[1], st),
-        "logmel": lambda: lib.kk_logmel_f32(L.ptr(x), L.ptr(w), L.ptr(fb), L.ptr(mel), B, n, n_fft, hop, 1, frames, 80, 1, 1, 1e-5, st),
+        "stft": lambda: lib.kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(spec), B, n, n_fft, hop, 1, frames, None, st),
+        "istft": lambda: lib.kk_istft_f32(L.ptr(spec), L.ptr(wp), L.ptr(sig), B, frames, n_fft, hop, n_fft // 2, sig.shape[1], None, 0, st),
+        "logmel": lambda: lib.kk_logmel_f32(L.ptr(x), L.ptr(w), L.ptr(fb), L.ptr(mel), B, n, n_fft, hop, 1, frames, 80, 1, 1, 1e-5, None, st),
     }
     res = {}
     for key, fn in calls.items():

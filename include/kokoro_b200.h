@@ -199,18 +199,24 @@ int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, c
 
 /* ---- general STFT / iSTFT / log-mel (mlx_audio/utils.py:52-158,164-237), batched over signals.
  * window: n_fft floats (already zero-extended).  pad_mode: 0 none(center=False) 1 reflect 2 constant.
- * spec out: (B, frames, n_fft/2+1, 2) float (re, im).  n_fft must factor into {2,3,5} and be <= 4096. */
+ * spec out: (B, frames, n_fft/2+1, 2) float (re, im).  n_fft must factor into {2,3,5} and be <= 4096.
+ * Ragged batches: lens (device, B ints; NULL = every signal has n samples) = valid samples per signal.  Signal b is
+ * transformed exactly as if it were given alone with lens[b] samples (its own reflect padding and last frame); its
+ * frames past 1 + (lens[b] + pad - n_fft) / hop are written as zeros (all of them if it is too short to transform). */
 int kk_stft_f32(const float* x, const float* window, float* spec, int B, int n, int n_fft, int hop,
-                int pad_mode, int frames, void* stream);
+                int pad_mode, int frames, const int* lens, void* stream);
 /* power: 1 -> |X|, 2 -> |X|^2.  mel: fb (n_mels, n_fft/2+1).  log_mode: 0 none, 3 ln(. + floor) [parakeet], 1 ln(max(.,floor)),
  * 2 log10(max(.,floor)).  out (B, frames, n_mels).  Spectrogram is never materialised. */
 int kk_logmel_f32(const float* x, const float* window, const float* fb, float* out, int B, int n, int n_fft,
                   int hop, int pad_mode, int frames, int n_mels, int power, int log_mode, float floor_,
-                  void* stream);
+                  const int* lens, void* stream);
 /* spec (B, frames, n_fft/2+1, 2) [frames-major, i.e. the layout kk_stft_f32 writes] -> signal.
- * out (B, out_len): out[i] = ola[i + trim] / wsum (where wsum != 0), ola length (frames-1)*hop + n_fft. */
+ * out (B, out_len): out[i] = ola[i + trim] / wsum (where wsum != 0), ola length (frames-1)*hop + n_fft.
+ * Ragged batches: lens (device, B ints; NULL = all frames) = valid frames per signal; signal b is synthesised from its
+ * first lens[b] frames only and ends at (lens[b]-1)*hop + n_fft - trim - tail samples (tail = what the caller cuts
+ * from the end of a full-length signal: n_fft/2 with centre trimming, 0 with an explicit length); the rest is zeros. */
 int kk_istft_f32(const float* spec, const float* window, float* out, int B, int frames, int n_fft, int hop,
-                 int trim, int out_len, void* stream);
+                 int trim, int out_len, const int* lens, int tail, void* stream);
 /* Vocos ISTFTHead polar stage (mlx_audio/codec/models/vocos/vocos.py:126-133): x (rows, x_pitch) holding
  * [log-magnitude (bins) | phase (bins)] per frame -> spec (rows, bins, 2) = min(exp(m), clip) * (cos p, sin p),
  * frame-major like kk_stft_f32's output, ready for kk_istft_f32. */

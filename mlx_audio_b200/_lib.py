@@ -78,9 +78,9 @@ PROTOTYPES = {
     "kk_stft_n20": [_P, _P, _I, _I, _I, _P, _I, _P],
     "kk_stft_n20_bf16": [_P, _P, _I, _P, _I, _I, _I, _I, _P, _I, _P],
     "kk_istft_head_n20": [_P, _I, _P, _I, _I, _P, _I, _I, _P],
-    "kk_stft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
-    "kk_logmel_f32": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P],
-    "kk_istft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
+    "kk_stft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P],
+    "kk_logmel_f32": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P, _P],
+    "kk_istft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _I, _P],
     "kk_polar_to_spec": [_P, _I, _P, _LL, _I, _F, _P],
     "kk_clamp_below_max_affine": [_P, _I, _LL, _F, _F, _F, _P],
     "kk_normalize_features": [_P, _I, _I, _I, _I, _F, _P],

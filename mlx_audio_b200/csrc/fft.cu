@@ -113,12 +113,24 @@ __device__ __forceinline__ void fill_tables(float2* tw, float2* tw2, int nc, int
 }
 
 // ---------------------------------------------------------------- forward: STFT (MODE 0) / log-mel (MODE 1)
+// Ragged batches: `lens` (device, B ints or null) holds the valid samples of every signal (forward) / the valid frames
+// (inverse).  A signal is transformed as if it ended there (its own reflect padding, its own last frame); frames /
+// samples past its end are written as zeros.  ragged_samples / ragged_frames clamp to the padded extent.
 struct StftArgs {
-  const float* x; const float* window; float* out;
+  const float* x; const float* window; float* out; const int* lens;
   int n, hop, pad_mode, frames, frames_per_block, group;
   // log-mel only
   const float* fb; int n_mels, power, log_mode; float floor_;
 };
+
+// valid samples of signal b and the number of frames they give (0 if the signal is too short for a frame or, with
+// reflect padding, for the reflection)
+__device__ __forceinline__ int ragged_samples(const StftArgs& a, int b) { return a.lens ? min(max(a.lens[b], 0), a.n) : a.n; }
+__device__ __forceinline__ int ragged_frames(const StftArgs& a, int n_b, int n_fft) {
+  const int pad = a.pad_mode == 0 ? 0 : n_fft / 2;
+  if (n_b <= 0 || n_b + 2 * pad < n_fft || (a.pad_mode == 1 && n_b <= pad)) return 0;
+  return min(a.frames, 1 + (n_b + 2 * pad - n_fft) / a.hop);
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPlan p) {
@@ -148,6 +160,7 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPl
   const int b = blockIdx.y;
   const float* xb = a.x + (size_t)b * a.n;
   const int pad = a.pad_mode == 0 ? 0 : n_fft / 2;
+  const int n_b = ragged_samples(a, b), frames_b = ragged_frames(a, n_b, n_fft);
   const int f_begin = blockIdx.x * a.frames_per_block;
   const int f_end = min(a.frames, f_begin + a.frames_per_block);
   for (int f0 = f_begin; f0 < f_end; f0 += a.group) {
@@ -161,11 +174,12 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPl
       for (int e = 0; e < 2; ++e) {
         int q = base + 2 * i + e;
         float s = 0.f;
-        if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
+        if (f0 + g >= frames_b) {        // past the signal's last frame: zeros
+        } else if (a.pad_mode == 1) {    // reflect without edge repeat (utils.py:81-84)
           if (q < 0) q = -q;
-          if (q >= a.n) q = 2 * (a.n - 1) - q;
+          if (q >= n_b) q = 2 * (n_b - 1) - q;
           s = xb[q];
-        } else if (q >= 0 && q < a.n) {
+        } else if (q >= 0 && q < n_b) {
           s = xb[q];
         }
         v[e] = s * win[2 * i + e];
@@ -212,7 +226,7 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPl
         if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
         else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
         else if (a.log_mode == 3) acc = logf(acc + a.floor_);
-        a.out[((size_t)b * a.frames + f0 + g) * a.n_mels + m] = acc;
+        a.out[((size_t)b * a.frames + f0 + g) * a.n_mels + m] = f0 + g < frames_b ? acc : 0.f;
       }
       __syncthreads();
     }
@@ -221,10 +235,19 @@ __global__ void __launch_bounds__(256) stft_kernel(const StftArgs a, const FftPl
 
 
 // ---------------------------------------------------------------- inverse: iSTFT with gather overlap-add
+// lens: valid frames per signal (or null); `tail` = samples the caller cuts from the end of the full overlap-add
+// (n_fft/2 with centre trimming, 0 with an explicit length), so that a shorter signal ends where it would alone.
 struct IstftArgs {
-  const float* spec; const float* window; float* out;
-  int frames, hop, trim, out_len, hops_per_block, group, max_frames;
+  const float* spec; const float* window; float* out; const int* lens;
+  int frames, hop, trim, tail, out_len, hops_per_block, group, max_frames;
 };
+template <class Args>
+__device__ __forceinline__ void ragged_istft(const Args& a, int b, int n_fft, int hop, int& frames_b, long long& total_b,
+                                             long long& out_len_b) {
+  frames_b = a.lens ? min(max(a.lens[b], 0), a.frames) : a.frames;
+  total_b = frames_b > 0 ? (long long)(frames_b - 1) * hop + n_fft : 0;
+  out_len_b = a.lens ? min((long long)a.out_len, max(0LL, total_b - a.trim - a.tail)) : a.out_len;
+}
 
 __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const FftPlan p) {
   extern __shared__ __align__(16) unsigned char smem_[];
@@ -242,12 +265,14 @@ __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const Fft
 
   const int b = blockIdx.y;
   const long long total = (long long)(a.frames - 1) * a.hop + n_fft;   // untrimmed length (utils.py:126)
+  int frames_b; long long total_b, out_len_b;
+  ragged_istft(a, b, n_fft, a.hop, frames_b, total_b, out_len_b);
   const long long u0 = (long long)blockIdx.x * a.hops_per_block * a.hop;
   const long long u1 = min(total, u0 + (long long)a.hops_per_block * a.hop);
   if (u0 >= total) return;
   const int f_lo = u0 >= n_fft ? (int)((u0 - n_fft) / a.hop) + 1 : 0;
-  const int f_hi = min(a.frames - 1, (int)((u1 - 1) / a.hop));
-  const int nf = f_hi - f_lo + 1;
+  const int f_hi = min(frames_b - 1, (int)((u1 - 1) / a.hop));
+  const int nf = max(f_hi - f_lo + 1, 0);
   const float2* sb = reinterpret_cast<const float2*>(a.spec) + (size_t)b * a.frames * bins;
   const float inv_nc = 1.0f / (float)nc;
 
@@ -284,14 +309,14 @@ __global__ void __launch_bounds__(256) istft_kernel(const IstftArgs a, const Fft
     const long long oi = u - a.trim;
     if (oi < 0 || oi >= a.out_len) continue;
     int fa = u >= n_fft ? (int)((u - n_fft) / a.hop) + 1 : 0;
-    int fb_ = min(a.frames - 1, (int)(u / a.hop));
+    int fb_ = min(frames_b - 1, (int)(u / a.hop));
     float acc = 0.f, ws = 0.f;
     for (int f = fa; f <= fb_; ++f) {
       const int n = (int)(u - (long long)f * a.hop);
       acc += tf[(size_t)(f - f_lo) * n_fft + n];
       ws += win[n];
     }
-    a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+    a.out[(size_t)b * a.out_len + oi] = oi >= out_len_b ? 0.f : (ws != 0.f) ? acc / ws : acc;
   }
 }
 
@@ -402,12 +427,14 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
   const float* xb = a.x + (size_t)b * a.n;
   const int pad = a.pad_mode == 0 ? 0 : NC;
   const bool vec_ok = ((a.hop | pad) & 1) == 0 && ((reinterpret_cast<uintptr_t>(xb) & 7) == 0);
+  const int n_b = ragged_samples(a, b), frames_b = ragged_frames(a, n_b, n_fft);
   const int f_begin = blockIdx.x * a.frames_per_block;
   const int f_end = min(a.frames, f_begin + a.frames_per_block);
-  // samples 2(j + 64 t), +1 of frame f (zero for a frame past the block's range)
+  const int f_live = min(f_end, frames_b);       // frames past the signal's last one transform zeros
+  // samples 2(j + 64 t), +1 of frame f (zero for a frame past the block's range or the signal's end)
   auto load_frame = [&](int f, float2 (&v)[8]) {
     const int base = f * a.hop - pad;
-    if (f < f_end && vec_ok && base >= 0 && base + n_fft <= a.n) {
+    if (f < f_live && vec_ok && base >= 0 && base + n_fft <= n_b) {
       const float2* src = reinterpret_cast<const float2*>(xb + base);
 #pragma unroll
       for (int t = 0; t < 8; ++t) v[t] = __ldg(src + j + NT * t);
@@ -415,15 +442,15 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
         float sv[2] = {0.f, 0.f};
-        if (f < f_end) {
+        if (f < f_live) {
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             int q = base + 2 * (j + NT * t) + e;
             if (a.pad_mode == 1) {           // reflect without edge repeat (utils.py:81-84)
               if (q < 0) q = -q;
-              if (q >= a.n) q = 2 * (a.n - 1) - q;
+              if (q >= n_b) q = 2 * (n_b - 1) - q;
               sv[e] = xb[q];
-            } else if (q >= 0 && q < a.n) {
+            } else if (q >= 0 && q < n_b) {
               sv[e] = xb[q];
             }
           }
@@ -502,7 +529,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) stft_fast_kernel(cons
         if (a.log_mode == 1) acc = logf(fmaxf(acc, a.floor_));
         else if (a.log_mode == 2) acc = log10f(fmaxf(acc, a.floor_));
         else if (a.log_mode == 3) acc = logf(acc + a.floor_);
-        if (live) a.out[((size_t)b * a.frames + f) * a.n_mels + m] = acc;
+        if (live) a.out[((size_t)b * a.frames + f) * a.n_mels + m] = f < frames_b ? acc : 0.f;
       };
       if (n_items >= 0) {
         // 32 items per warp step; lane l reads element (i + (l >> 2)) & 7 of its 8-bin piece at step i: consecutive
@@ -696,8 +723,8 @@ __global__ void __launch_bounds__(fr::THREADS, R32_BLOCKS) stft_r32_kernel(const
 // (utils.py:150, same order) and carries the rest.  No ring buffer, no atomics, no second pass over the output.
 // A block first replays the frames before its range (warm-up, nothing emitted); the last block drains the tail.
 struct IstftStreamArgs {
-  const float* spec; const float* window; float* out;
-  int frames, hop, trim, out_len, frames_per_block, R;
+  const float* spec; const float* window; float* out; const int* lens;
+  int frames, hop, trim, tail, out_len, frames_per_block, R;
 };
 
 template <int R, bool RT>
@@ -753,6 +780,8 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
 
   const int b = blockIdx.y;
   const long long total = (long long)(a.frames - 1) * hop + n_fft;   // untrimmed length (utils.py:126)
+  int frames_b; long long total_b, out_len_b;                        // this signal's own extent (ragged batches)
+  ragged_istft(a, b, n_fft, hop, frames_b, total_b, out_len_b);
   const int hops_total = (int)((total + hop - 1) / hop);
   const int H0 = blockIdx.x * a.frames_per_block;
   const int H1 = (blockIdx.x == gridDim.x - 1) ? hops_total : min(hops_total, H0 + a.frames_per_block);
@@ -762,7 +791,7 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
 
   for (int fi = H0 >= G ? H0 - G : 0; fi < H1; fi += G) {
     const int f = fi + g;
-    const bool live = f < a.frames;
+    const bool live = f < frames_b;
     {
       // L2 prefetch of the next iteration's four spectrum rows (contiguous: 4 * 4104 bytes = 129 lines)
       const long long nf = (long long)fi + G;
@@ -822,9 +851,9 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
           tv[gg][r] = __fmul_rn(reinterpret_cast<const float*>(bufs + (2 * gg) * ff::BUF)[r * hop + off], w[o][r]);
       // interior iterations (every hop inside this block's range, every covering frame present, every sample inside
       // the trimmed output): precomputed window sum, 32-bit addressing
-      const bool interior = fi >= H0 && fi + G <= H1 && fi >= R - 1 && fi + G <= a.frames &&
-                            (long long)fi * hop >= a.trim && (long long)(fi + G) * hop <= total &&
-                            (long long)(fi + G) * hop - a.trim <= a.out_len;
+      const bool interior = fi >= H0 && fi + G <= H1 && fi >= R - 1 && fi + G <= frames_b &&
+                            (long long)fi * hop >= a.trim && (long long)(fi + G) * hop <= total_b &&
+                            (long long)(fi + G) * hop - a.trim <= out_len_b;
       float* orow = a.out + (size_t)b * a.out_len + ((long long)fi * hop - a.trim) + off;
 #pragma unroll
       for (int hh = 0; hh < G; ++hh) {
@@ -847,10 +876,10 @@ __global__ void __launch_bounds__(ff::THREADS, RT ? 2 : 4) istft_stream_kernel(c
 #pragma unroll
           for (int r = R - 1; r >= 0; --r) {             // increasing frame order, like the reference's loop
             const int fr = hcur - r;                     // frames covering this sample
-            if (fr >= 0 && fr < a.frames) ws = __fadd_rn(ws, w[o][r]);
+            if (fr >= 0 && fr < frames_b) ws = __fadd_rn(ws, w[o][r]);
           }
           acc = __fmul_rn(acc, inv_nc);
-          a.out[(size_t)b * a.out_len + oi] = (ws != 0.f) ? acc / ws : acc;
+          a.out[(size_t)b * a.out_len + oi] = oi >= out_len_b ? 0.f : (ws != 0.f) ? acc / ws : acc;   // past the signal's own end: zeros
         }
       }
       // partial sums of the next R - 1 hops (frames of this iteration that reach past it)
@@ -942,18 +971,19 @@ static int check_stft_args(const char* who, const float* x, const float* window,
 }
 
 extern "C" int kk_stft_f32(const float* x, const float* window, float* spec, int B, int n, int n_fft, int hop,
-                           int pad_mode, int frames, void* stream) {
+                           int pad_mode, int frames, const int* lens, void* stream) {
   kk::FftPlan p;
   int rc = check_stft_args("kk_stft_f32", x, window, spec, B, n, n_fft, hop, pad_mode, frames, &p);
   if (rc) return rc;
   kk::StftArgs a = {};
   a.x = x; a.window = window; a.out = spec; a.n = n; a.hop = hop; a.pad_mode = pad_mode; a.frames = frames;
+  a.lens = lens;
   return kk::launch_stft<0>(a, p, B, (cudaStream_t)stream);
 }
 
 extern "C" int kk_logmel_f32(const float* x, const float* window, const float* fb, float* out, int B, int n,
                              int n_fft, int hop, int pad_mode, int frames, int n_mels, int power, int log_mode,
-                             float floor_, void* stream) {
+                             float floor_, const int* lens, void* stream) {
   kk::FftPlan p;
   int rc = check_stft_args("kk_logmel_f32", x, window, out, B, n, n_fft, hop, pad_mode, frames, &p);
   if (rc) return rc;
@@ -961,13 +991,13 @@ extern "C" int kk_logmel_f32(const float* x, const float* window, const float* f
                "kk_logmel_f32: bad mel arguments");
   kk::StftArgs a = {};
   a.x = x; a.window = window; a.out = out; a.n = n; a.hop = hop; a.pad_mode = pad_mode; a.frames = frames;
-  a.fb = fb; a.n_mels = n_mels; a.power = power; a.log_mode = log_mode; a.floor_ = floor_;
+  a.fb = fb; a.n_mels = n_mels; a.power = power; a.log_mode = log_mode; a.floor_ = floor_; a.lens = lens;
   return kk::launch_stft<1>(a, p, B, (cudaStream_t)stream);
 }
 
 extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, int B, int frames, int n_fft, int hop,
-                            int trim, int out_len, void* stream) {
-  KK_CHECK_ARG(spec && window && out && B > 0 && B <= 65535 && frames > 0 && hop > 0 && trim >= 0 && out_len > 0,
+                            int trim, int out_len, const int* lens, int tail, void* stream) {
+  KK_CHECK_ARG(spec && window && out && B > 0 && B <= 65535 && frames > 0 && hop > 0 && trim >= 0 && out_len > 0 && tail >= 0,
                "kk_istft_f32: bad arguments");
   kk::FftPlan p;
   if (kk::make_fft_plan(n_fft, &p) != 0) {
@@ -976,11 +1006,13 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
   }
   kk::IstftArgs a = {};
   a.spec = spec; a.window = window; a.out = out; a.frames = frames; a.hop = hop; a.trim = trim; a.out_len = out_len;
+  a.lens = lens; a.tail = tail;
   a.group = kk::stft_group(p.nc) > 4 ? 4 : kk::stft_group(p.nc);
   const int overlap = kk::cdiv(n_fft, hop);
   if (n_fft == 2 * kk::ff::NC && (hop == 256 || hop == 512 || hop == 1024)) {   // register-resident radix-8, streaming OLA
     kk::IstftStreamArgs sa = {};
     sa.spec = spec; sa.window = window; sa.out = out; sa.frames = frames; sa.hop = hop; sa.trim = trim;
+    sa.lens = lens; sa.tail = tail;
     sa.out_len = out_len; sa.R = n_fft / hop;
     long long total = (long long)(frames - 1) * hop + n_fft;
     const int hops_total = (int)((total + hop - 1) / hop);

@@ -106,21 +106,44 @@ def _prep_stft(x, n_fft, hop_length, win_length, window, center, pad_mode):
     return x, w.contiguous(), hop_length, mode, num_frames, squeeze
 
 
+def _ragged_lengths(lengths, B: int, limit: int, what: str) -> Optional[torch.Tensor]:
+    """``lengths=`` of the batched transforms -> (B,) int32 on the device (None stays None).  Host-resident lengths are
+    validated; device-resident ones are trusted (the kernels clamp them to [0, limit])."""
+    if lengths is None:
+        return None
+    if isinstance(lengths, torch.Tensor) and lengths.is_cuda:
+        if lengths.numel() != B:
+            raise ValueError(f"lengths: expected {B} entries, got {lengths.numel()}")
+        return lengths.to(torch.int32).contiguous()
+    host = np.asarray(lengths.cpu() if isinstance(lengths, torch.Tensor) else lengths).astype(np.int64).reshape(-1)
+    if host.size != B:
+        raise ValueError(f"lengths: expected {B} entries, got {host.size}")
+    if host.size and (host.min() < 0 or host.max() > limit):
+        raise ValueError(f"lengths must lie in [0, {limit}] ({what}), got [{host.min()}, {host.max()}]")
+    return torch.from_numpy(host.astype(np.int32)).to(_dev())
+
+
 def stft(x, n_fft=800, hop_length=None, win_length=None, window: Union[torch.Tensor, str] = "hann", center=True,
-         pad_mode="reflect"):
-    """utils.py:52-101.  (N,) -> (num_frames, n_fft//2+1) complex64 [batched: (B, N) -> (B, frames, bins)]."""
+         pad_mode="reflect", lengths=None):
+    """utils.py:52-101.  (N,) -> (num_frames, n_fft//2+1) complex64 [batched: (B, N) -> (B, frames, bins)].
+    ``lengths`` (batched calls; not in the reference, which transforms one signal per call): valid samples per signal
+    of a zero-padded ragged batch.  Row b equals ``stft(x[b, :lengths[b]])`` - its own reflect padding and last frame -
+    followed by zero frames (all zeros when the signal is too short to transform)."""
     x, w, hop, mode, frames, squeeze = _prep_stft(x, n_fft, hop_length, win_length, window, center, pad_mode)
     B, n = x.shape
+    lens = _ragged_lengths(lengths, B, n, "samples")
     out = torch.empty(B, frames, n_fft // 2 + 1, 2, dtype=torch.float32, device=x.device)
-    L.check(L.load().kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(out), B, n, n_fft, hop, mode, frames, L.stream()),
-            "kk_stft_f32")
+    L.check(L.load().kk_stft_f32(L.ptr(x), L.ptr(w), L.ptr(out), B, n, n_fft, hop, mode, frames,
+                                 None if lens is None else L.ptr(lens), L.stream()), "kk_stft_f32")
     spec = torch.view_as_complex(out)
     return spec[0] if squeeze else spec
 
 
-def istft(x, hop_length=None, win_length=None, window="hann", center=True, length=None):
+def istft(x, hop_length=None, win_length=None, window="hann", center=True, length=None, lengths=None):
     """utils.py:104-158.  x (bins, frames) complex -> 1-D signal [batched: (B, bins, frames) -> (B, len)].
-    Normalised by the window sum (not its square), exactly like the reference."""
+    Normalised by the window sum (not its square), exactly like the reference.
+    ``lengths`` (batched calls; not in the reference): valid frames per signal of a ragged batch.  Row b equals
+    ``istft(x[b, :, :lengths[b]], win_length=..., ...)`` followed by zeros."""
     if not isinstance(x, torch.Tensor):
         x = torch.as_tensor(np.asarray(x))
     x = x.to(device=_dev())
@@ -156,10 +179,12 @@ def istft(x, hop_length=None, win_length=None, window="hann", center=True, lengt
         out_len = min(length, total)
     if out_len <= 0:
         raise ValueError("istft: empty output")
+    lens = _ragged_lengths(lengths, B, frames, "frames")
+    tail = -(-win_length // 2) if (center and length is None) else 0      # range(total)[w//2 : -w//2]
     out = torch.empty(B, out_len, dtype=torch.float32, device=x.device)
     spec = torch.view_as_real(xt)
     L.check(L.load().kk_istft_f32(L.ptr(spec), L.ptr(w.contiguous()), L.ptr(out), B, frames, n_fft, hop_length, trim,
-                                  out_len, L.stream()), "kk_istft_f32")
+                                  out_len, None if lens is None else L.ptr(lens), tail, L.stream()), "kk_istft_f32")
     return out[0] if squeeze else out
 
 
@@ -213,14 +238,17 @@ def mel_filters(sample_rate: int, n_fft: int, n_mels: int, f_min: float = 0, f_m
 
 def log_mel_spectrogram(x, sample_rate=24000, n_fft=1024, hop_length=256, n_mels=80, window="hann", power=1,
                         log="ln", floor=1e-5, norm=None, mel_scale="htk", center=True, pad_mode="reflect",
-                        f_min=0, f_max=None):
+                        f_min=0, f_max=None, lengths=None):
     """Fused STFT -> |X|^power -> mel -> log.  Defaults = indextts/mel.py:20-37 (``log(max(|X| @ fb.T, 1e-5))``).
-    Returns (frames, n_mels) [batched: (B, frames, n_mels)]; the spectrogram is never written to HBM."""
+    Returns (frames, n_mels) [batched: (B, frames, n_mels)]; the spectrogram is never written to HBM.
+    ``lengths``: valid samples per signal of a ragged batch (see ``stft``); frames past a signal's end are zeros."""
     x, w, hop, mode, frames, squeeze = _prep_stft(x, n_fft, hop_length, n_fft, window, center, pad_mode)
     fb = mel_filters(sample_rate, n_fft, n_mels, f_min, f_max, norm, mel_scale).contiguous()
     B, n = x.shape
+    lens = _ragged_lengths(lengths, B, n, "samples")
     out = torch.empty(B, frames, n_mels, dtype=torch.float32, device=x.device)
     log_mode = {None: 0, "none": 0, "ln": 1, "log": 1, "log10": 2, "ln_add": 3}[log]   # ln_add: log(x + floor)
     L.check(L.load().kk_logmel_f32(L.ptr(x), L.ptr(w), L.ptr(fb), L.ptr(out), B, n, n_fft, hop, mode, frames, n_mels,
-                                   int(power), log_mode, float(floor), L.stream()), "kk_logmel_f32")
+                                   int(power), log_mode, float(floor), None if lens is None else L.ptr(lens),
+                                   L.stream()), "kk_logmel_f32")
     return out[0] if squeeze else out

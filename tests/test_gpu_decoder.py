@@ -154,6 +154,59 @@ def test_istft_matches_reference_golden(golden_dir, tag, kw):
         np.testing.assert_allclose(y3.cpu().numpy(), g["istft_1024_256_symwin"], atol=1e-5)
 
 
+RAGGED_DSP = [dict(n_fft=1024, hop_length=256), dict(n_fft=400, hop_length=160),
+              dict(n_fft=256, hop_length=64, pad_mode="constant"), dict(n_fft=256, hop_length=64, center=False)]
+
+
+@pytest.mark.parametrize("kw", RAGGED_DSP, ids=lambda k: "_".join(str(v) for v in k.values()))
+def test_stft_logmel_istft_ragged_lengths_match_solo_calls(kw):
+    """``lengths=``: every row of a zero-padded ragged batch equals the transform of that signal
+    alone - its own reflect padding, last frame and overlap-add tail - bit for bit, followed by zeros; the padding
+    holds garbage.  One signal is too short to transform at all (all zeros), one ends on a frame boundary."""
+    from oracle import dsp
+    n_fft, hop = kw["n_fft"], kw["hop_length"]
+    n = 9000
+    lens = [n, 5000, n_fft + 3 * hop, n_fft // 2 + 5, n_fft // 4, 0, 7777]
+    x = torch.from_numpy(synth.synth_audio(len(lens), n, seed=91)).cuda()
+    for b, l in enumerate(lens):
+        x[b, l:] = 1e6                                               # garbage past the end must not leak in
+    for dev_lens in (False, True):
+        lengths = torch.tensor(lens, dtype=torch.int32, device="cuda") if dev_lens else lens
+        S = utils.stft(x, lengths=lengths, **kw)
+        M = utils.log_mel_spectrogram(x, sample_rate=24000, n_mels=40, lengths=lengths, **kw) if n_fft >= 256 else None
+        fr = []
+        for b, l in enumerate(lens):
+            try:
+                solo = utils.stft(x[b, :l], **kw) if l else None
+            except ValueError:
+                solo = None                                          # too short: the batched call writes zeros
+            f = 0 if solo is None else solo.shape[0]
+            fr.append(f)
+            if f:
+                assert torch.equal(S[b, :f], solo), (b, l)
+                assert torch.equal(M[b, :f], utils.log_mel_spectrogram(x[b, :l], sample_rate=24000, n_mels=40, **kw))
+            assert not S[b, f:].abs().any() and not M[b, f:].abs().any()
+        ref = dsp.stft(x[1, :lens[1]].cpu().numpy(), **kw)
+        assert np.abs(S[1, :fr[1]].cpu().numpy() - ref).max() < 1e-4 * max(1.0, float(np.abs(ref).max()))
+        # inverse: frames per signal -> each row is the solo synthesis, zeros after its own end
+        for b, f in enumerate(fr):
+            S[b, f:] = 1e6
+        fl = torch.tensor(fr, dtype=torch.int32, device="cuda") if dev_lens else fr
+        for ikw in (dict(), dict(length=4321)) if kw.get("center", True) else (dict(center=False),):
+            y = utils.istft(S.transpose(1, 2), hop_length=hop, win_length=n_fft, lengths=fl, **ikw)
+            for b, f in enumerate(fr):
+                m = 0
+                if f and ((f - 1) * hop > 0 or ikw):
+                    solo = utils.istft(S[b, :f].T, hop_length=hop, win_length=n_fft, **ikw)
+                    m = solo.shape[0]
+                    assert torch.equal(y[b, :m], solo), (b, f, ikw)
+                assert not y[b, m:].abs().any(), (b, f, ikw)
+    with pytest.raises(ValueError):
+        utils.stft(x, lengths=[n + 1] * len(lens), **kw)
+    with pytest.raises(ValueError):
+        utils.stft(x, lengths=[1, 2], **kw)
+
+
 def test_mel_filters_and_windows_golden(golden_dir):
     g = np.load(os.path.join(golden_dir, "dsp.npz"))
     np.testing.assert_allclose(utils.mel_filters(24000, 1024, 80).cpu().numpy(), g["mel_24000_1024_80_htk"], atol=1e-7)
