@@ -590,10 +590,11 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         torch.cuda.synchronize()
 
     if args.dtype == "bf16":
+        if rank == 0:   # single launches timed alone: before the long sub-benchmarks pull the clocks down to the power cap
+            sub("dsp", lambda: bench_dsp(dev, peaks))
         sub("c4", lambda: bench_c4(dev, dec, rank, world))
         sub("c5", lambda: bench_c5(dev, dec, rank, world))
         if rank == 0:
-            sub("dsp", lambda: bench_dsp(dev, peaks))
             if not ({"latency", "fp32"} <= skip):
                 dec32 = build_decoder(weights, dtype="fp32", device=str(dev))
                 sub("latency", lambda: bench_latency(dev, weights, {"bf16": dec, "fp32": dec32}))
