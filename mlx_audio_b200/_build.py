@@ -11,7 +11,7 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_NAME = "libkokoro_b200.so"
 LIB_PATH = os.path.join(PKG_DIR, LIB_NAME)
 SOURCES = ["common.cu", "weights.cu", "elementwise.cu", "conv_f32.cu", "conv_tc.cu", "conv_fused.cu", "source.cu", "istft_head.cu",
-           "fft.cu", "codec.cu"]
+           "fft.cu", "codec.cu", "lstm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
 

@@ -7,9 +7,10 @@
 
 The six AdainResBlk1d (istftnet.py:825-899, built at modules.py:299-337 - blocks 0 and 2 have no learned shortcut) and
 the two 1x1 projections run on the same hand-written kernels as the decoder front (launch plan: ``ProsodyEngine``,
-reusing ``DecoderEngine._adain_resblk1d``).  The recurrent ``shared`` LSTM (modules.py:93-286, gate order i, f, g, o -
-the same as cuDNN's) is sequential, not data parallel; it stays a torch (cuDNN) module, as SURVEY 8(f) states, and may
-be skipped by passing its output as ``hidden=``.  The rest of ``ProsodyPredictor`` (DurationEncoder, duration_proj)
+reusing ``DecoderEngine._adain_resblk1d``).  The recurrent ``shared`` LSTM (modules.py:93-286, gate order i, f, g, o)
+is native as well (round 2; it was a cuDNN module): one tensor-core GEMM for the input projections of all steps, then
+``kk_lstm_bidir_f32`` (``csrc/lstm.cu``) - clusters of 8 CTAs that keep the recurrent weights in shared memory and
+exchange h once per step.  It may still be skipped by passing its output as ``hidden=``.  The rest of ``ProsodyPredictor`` (DurationEncoder, duration_proj)
 is outside the rebuilt path.  Parameter names are the reference's (``F0.0.conv1.weight_v``, ``N_proj.weight`` ...),
 with or without the ``predictor.`` prefix.  No CPU path.
 """
@@ -92,7 +93,7 @@ class ProsodyPredictor:
         self._specs = {n[len("predictor."):]: shp for n, shp, _ in prosody_param_specs(style_dim, d_hid)}
         self._weights: Dict[str, torch.Tensor] = {}
         self._engine: Optional[ProsodyEngine] = None
-        self._lstm: Optional[torch.nn.LSTM] = None
+        self._lstm = None      # (input-projection GEMM, transposed recurrent weights) once the weights are loaded
 
     # ------------------------------------------------------------------ weights
     def parameter_shapes(self) -> Dict[str, tuple]:
@@ -152,25 +153,55 @@ class ProsodyPredictor:
             self._engine = ProsodyEngine(conv_w, self.cfg, self.mode)
         return self._engine
 
-    def shared(self, x_blc: torch.Tensor) -> torch.Tensor:
-        """``self.shared`` bi-LSTM (modules.py:93-286) through cuDNN: (B, L, d_hid + style) -> (B, L, d_hid)."""
+    def shared(self, x_blc: torch.Tensor, lengths=None) -> torch.Tensor:
+        """``self.shared`` bi-LSTM (modules.py:93-286, gate order i, f, g, o): (B, L, d_hid + style) -> (B, L, d_hid).
+        Input projection of every step and both directions = one 3xTF32 tensor-core GEMM (``kk_conv1d_tf32_tc`` as a
+        1x1 convolution, bias = b_ih + b_hh); the recurrence = ``kk_lstm_bidir_f32`` (thread-block clusters holding the
+        recurrent weights in shared memory).  fp32 in both modes - it is ~1 ms beside a 35 ms decode.
+        ``lengths`` (extension): valid steps per sequence of a zero-padded batch; the backward direction starts at each
+        sequence's own end, rows past it are zeros."""
+        from ...._lib import ConvDesc
+        import ctypes as C
+        lib = L.load()
+        w = self._weights
         if self._lstm is None:
-            w = self._weights
             if "shared.Wx_forward" not in w:
                 raise L.KokoroB200Error("the `shared` LSTM weights are not loaded: pass hidden= (its output) instead")
-            H = self.cfg["d_hid"] // 2
-            lstm = torch.nn.LSTM(self.cfg["d_hid"] + self.cfg["style_dim"], H, batch_first=True, bidirectional=True)
-            lstm = lstm.to(self.device)
-            with torch.no_grad():
-                for sfx, d in (("", "forward"), ("_reverse", "backward")):
-                    getattr(lstm, f"weight_ih_l0{sfx}").copy_(w[f"shared.Wx_{d}"])
-                    getattr(lstm, f"weight_hh_l0{sfx}").copy_(w[f"shared.Wh_{d}"])
-                    getattr(lstm, f"bias_ih_l0{sfx}").copy_(w[f"shared.bias_ih_{d}"])
-                    getattr(lstm, f"bias_hh_l0{sfx}").copy_(w[f"shared.bias_hh_{d}"])
-            self._lstm = lstm.eval()
-        # strict-fp32 mode: keep cuDNN's recurrent GEMMs out of TF32 (the parity gate is 1e-3 on the heads' outputs)
-        with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=self.mode != "fp32"):
-            return self._lstm(x_blc)[0]
+            dev = self.device
+            f32 = lambda t: t.to(device=dev, dtype=torch.float32)
+            wx = torch.cat([f32(w["shared.Wx_forward"]), f32(w["shared.Wx_backward"])], 0)          # (2 * 4H, D)
+            bias = torch.cat([f32(w["shared.bias_ih_forward"]) + f32(w["shared.bias_hh_forward"]),
+                              f32(w["shared.bias_ih_backward"]) + f32(w["shared.bias_hh_backward"])]).contiguous()
+            pc = PreparedConv("shared.Wx", wx[:, None, :].contiguous(), bias, need_bf16=False, need_f32=False,
+                              need_tf32=True)
+            whT = torch.stack([f32(w["shared.Wh_forward"]).t(), f32(w["shared.Wh_backward"]).t()]).contiguous()
+            self._lstm = (pc, whT)
+        pc, whT = self._lstm
+        x = x_blc.to(device=self.device, dtype=torch.float32).contiguous()
+        B, L_, D = x.shape
+        H = self.cfg["d_hid"] // 2
+        if D != pc.C_in or D % 4:
+            raise ValueError(f"shared LSTM input must be (B, L, {pc.C_in}), got {tuple(x.shape)}")
+        lens = None
+        if lengths is not None:
+            lens = torch.as_tensor(lengths).to(device=self.device, dtype=torch.int32).contiguous()
+            if lens.numel() != B:
+                raise ValueError(f"lengths: expected {B} entries, got {lens.numel()}")
+        xw = torch.empty(B, L_, 8 * H, device=self.device)
+        d = ConvDesc()
+        d.B, d.L_in, d.C_in, d.x_pitch = B, L_, D, D
+        d.taps, d.dil, d.pad_left, d.stride, d.Cw = 1, 1, 0, 1, pc.CwT
+        d.M, d.N, d.C_out, d.up, d.up_off = L_, pc.N, pc.C_out, 1, 0
+        d.L_true = d.L_out = L_
+        d.bias, d.scale = L.ptr(pc.bias), 1.0
+        d.out, d.out_pitch = L.ptr(xw), 8 * H
+        st = L.stream()
+        L.check(lib.kk_conv1d_tf32_tc(L.ptr(x), L.ptr(pc.w32hi), L.ptr(pc.w32lo), C.byref(d), 3, st), "kk_conv1d_tf32_tc")
+        h_ws = torch.empty(2, 2, B, H, device=self.device)
+        out = torch.empty(B, L_, 2 * H, device=self.device)
+        L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, L_, H,
+                                      None if lens is None else L.ptr(lens), st), "kk_lstm_bidir_f32")
+        return out
 
     # ------------------------------------------------------------------ forward
     def F0Ntrain(self, x=None, s=None, *, hidden=None, capture_taps: bool = False,

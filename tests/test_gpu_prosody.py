@@ -49,9 +49,66 @@ def test_f0ntrain_fp32_vs_oracle(weights, oracle, B, Lq):
     F0, N = pp.F0Ntrain(s=inp["s"], hidden=hidden)           # conv path alone
     assert np.abs(_np(F0) - F0r).max() <= 1e-3 * np.abs(F0r).max()
     assert np.abs(_np(N) - Nr).max() <= 1e-3
-    F0b, Nb = pp.F0Ntrain(inp["x"], inp["s"])                # with the cuDNN LSTM in front
+    F0b, Nb = pp.F0Ntrain(inp["x"], inp["s"])                # with the native LSTM in front
     assert np.abs(_np(F0b) - F0r).max() <= 1e-3 * np.abs(F0r).max()
     assert np.abs(_np(Nb) - Nr).max() <= 1e-3
+
+
+def _torch_lstm(weights, device="cuda"):
+    """The same layer as a torch module (cuDNN), TF32 off: the independent check of the recurrent kernel."""
+    w = {k[len("predictor."):] if k.startswith("predictor.") else k: torch.as_tensor(np.asarray(v)) for k, v in weights.items()}
+    H = w["shared.Wh_forward"].shape[1]
+    m = torch.nn.LSTM(w["shared.Wx_forward"].shape[1], H, batch_first=True, bidirectional=True).to(device)
+    with torch.no_grad():
+        for sfx, d in (("", "forward"), ("_reverse", "backward")):
+            getattr(m, f"weight_ih_l0{sfx}").copy_(w[f"shared.Wx_{d}"])
+            getattr(m, f"weight_hh_l0{sfx}").copy_(w[f"shared.Wh_{d}"])
+            getattr(m, f"bias_ih_l0{sfx}").copy_(w[f"shared.bias_ih_{d}"])
+            getattr(m, f"bias_hh_l0{sfx}").copy_(w[f"shared.bias_hh_{d}"])
+    return m.eval()
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("B,Lq", [(1, 1), (3, 37), (9, 200), (64, 320)])
+def test_shared_lstm_native_vs_oracle_and_cudnn(weights, oracle, B, Lq):
+    """``kk_lstm_bidir_f32`` + the 3xTF32 input GEMM against the numpy restatement of modules.py:93-286 and against
+    cuDNN (TF32 off).  h is in (-1, 1): 2e-5 absolute."""
+    inp = synth.synth_prosody_inputs(B, Lq, seed=1500 + Lq)
+    pp = build_prosody_predictor(weights, dtype="fp32")
+    x = torch.as_tensor(inp["x"]).cuda().transpose(1, 2).contiguous()
+    got = _np(pp.shared(x))
+    assert got.shape == (B, Lq, 512)
+    if B * Lq <= 2000:
+        assert np.abs(got - oracle.hidden_of(inp["x"])).max() <= 2e-5
+    with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        ref = _np(_torch_lstm(weights)(x)[0])
+    assert np.abs(got - ref).max() <= 2e-5, np.abs(got - ref).max()
+    if B == 64:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            pp.shared(x)
+        e1.record()
+        e1.synchronize()
+        print(f"native bi-LSTM B={B} L={Lq}: {e0.elapsed_time(e1) / 5:.3f} ms per call")
+
+
+@pytest.mark.timeout(120)
+def test_shared_lstm_ragged_lengths_match_solo(weights):
+    """lengths=: every sequence of a padded batch equals running it alone (the backward direction starts at its own last
+    step), zeros after its end; the padding holds garbage."""
+    B, Lq = 11, 50
+    lens = [50, 1, 17, 50, 33, 8, 49, 2, 25, 40, 5]
+    inp = synth.synth_prosody_inputs(B, Lq, seed=1600)
+    pp = build_prosody_predictor(weights, dtype="fp32")
+    x = torch.as_tensor(inp["x"]).cuda().transpose(1, 2).contiguous()
+    for b, l in enumerate(lens):
+        x[b, l:] = 1e4
+    got = pp.shared(x, lengths=lens)
+    for b, l in enumerate(lens):
+        solo = pp.shared(x[b:b + 1, :l].contiguous())
+        assert torch.equal(got[b, :l], solo[0]), b
+        assert not got[b, l:].abs().any(), b
 
 
 def test_f0ntrain_bf16_vs_oracle(weights, oracle):
