@@ -45,9 +45,14 @@ class ProsodyEngine(DecoderEngine):
                                                       w[f"{head}_proj.bias"], need_bf16=False, need_f32=True)
         torch.cuda.current_stream().synchronize()
 
-    def build_plan(self, B: int, L_: int) -> Plan:
+    def build_plan(self, B: int, L_: int, ragged: bool = False) -> Plan:
+        """``ragged``: the batch is padded to L_ frames and every kernel takes the per-sequence frame counts (buffer
+        ``pp.in.lens``), like the decoder's plans (engine.build_plan)."""
         plan = Plan()
         d, h2 = self.d_hid, self.d_hid // 2
+        if ragged:
+            plan.lens_addr = self._addr(self._buf(plan, "pp.in.lens", (B,), torch.int32))
+            plan.levels = {L_: (1, 0), 2 * L_: (2, 0)}
         x = self._buf(plan, "pp.in.x", (B, L_, d))            # shared-LSTM output, channels-last (modules.py:358)
         s = self._buf(plan, "pp.in.s", (B, self.cfg["style_dim"]))
         h_all = self._buf(plan, "pp.h_all", (B, self.ada_R))
@@ -205,34 +210,50 @@ class ProsodyPredictor:
 
     # ------------------------------------------------------------------ forward
     def F0Ntrain(self, x=None, s=None, *, hidden=None, capture_taps: bool = False,
-                 borrow: bool = False) -> Tuple[torch.Tensor, torch.Tensor]:
+                 borrow: bool = False, lengths=None) -> Tuple[torch.Tensor, torch.Tensor]:
         """modules.py:355-377.  ``x``: (B, d_hid + style_dim, L) (``en`` of kokoro.py:157-159); ``s``: (B, style_dim).
         Extension: ``hidden`` = (B, L, d_hid) output of the shared LSTM, skipping it.  Returns (F0, N), each (B, 2L):
         fresh tensors like the reference; ``borrow=True`` returns the persistent workspace views (overwritten by the
-        next call)."""
+        next call).  ``lengths`` (extension): frames per sequence of a zero-padded RAGGED batch - every sequence comes
+        out as if it were run alone (LSTM directions, instance-norm statistics, conv padding), zeros after 2 * length."""
         L.require_cuda()
         dev = self.device
         s = _to_cuda_f32(s, dev)
+        lens = None
+        if lengths is not None:
+            if isinstance(lengths, torch.Tensor) and lengths.is_cuda:
+                lens = lengths.to(torch.int32).contiguous()
+            else:
+                host = np.asarray(lengths.cpu() if isinstance(lengths, torch.Tensor) else lengths).astype(np.int64).reshape(-1)
+                Lmax = (x if hidden is None else hidden).shape[2 if hidden is None else 1]
+                if host.size and (host.min() < 1 or host.max() > Lmax):
+                    raise ValueError(f"lengths must lie in [1, {Lmax}], got [{host.min()}, {host.max()}]")
+                lens = torch.from_numpy(host.astype(np.int32)).to(dev)
         if hidden is None:
             x = _to_cuda_f32(x, dev)
             if x.dim() != 3 or x.shape[1] != self.cfg["d_hid"] + self.cfg["style_dim"]:
                 raise ValueError(f"x must be (B, {self.cfg['d_hid'] + self.cfg['style_dim']}, L), got {tuple(x.shape)}")
-            hidden = self.shared(x.transpose(1, 2).contiguous())
+            hidden = self.shared(x.transpose(1, 2).contiguous(), lengths=lens)
         hidden = _to_cuda_f32(hidden, dev)
         if hidden.dim() != 3 or hidden.shape[2] != self.cfg["d_hid"]:
             raise ValueError(f"hidden must be (B, L, {self.cfg['d_hid']}), got {tuple(hidden.shape)}")
         B, L_, _ = hidden.shape
         if tuple(s.shape) != (B, self.cfg["style_dim"]):
             raise ValueError(f"s must be (B, {self.cfg['style_dim']}), got {tuple(s.shape)}")
+        if lens is not None and lens.numel() != B:
+            raise ValueError(f"lengths: expected {B} entries, got {lens.numel()}")
         eng = self.engine
-        plan = eng.plans.get((B, L_))
+        key = (B, L_) if lens is None else (B, L_, True)
+        plan = eng.plans.get(key)
         if plan is None:
             eng.pool_grew = False
-            plan = eng.build_plan(B, L_)
+            plan = eng.build_plan(B, L_, ragged=lens is not None)
             if eng.pool_grew:
                 eng.plans.clear()
-            eng.plans[(B, L_)] = plan
+            eng.plans[key] = plan
         eng.activate(plan)
+        if lens is not None:
+            plan.buffers["pp.in.lens"].copy_(lens, non_blocking=True)
         plan.buffers["pp.in.x"].copy_(hidden, non_blocking=True)
         plan.buffers["pp.in.s"].copy_(s, non_blocking=True)
         plan.capture = capture_taps

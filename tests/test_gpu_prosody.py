@@ -111,6 +111,30 @@ def test_shared_lstm_ragged_lengths_match_solo(weights):
         assert not got[b, l:].abs().any(), b
 
 
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+def test_f0ntrain_ragged_lengths_match_solo(weights, dtype):
+    """F0Ntrain(lengths=): sequences of a padded batch come out as when run alone, zeros after 2 * length."""
+    if dtype == "bf16" and not L.load().kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    B, Lq = 7, 48
+    lens = [48, 5, 31, 48, 16, 40, 1]
+    inp = synth.synth_prosody_inputs(B, Lq, seed=1700)
+    x = torch.as_tensor(inp["x"]).cuda()
+    for b, l in enumerate(lens):
+        x[b, :, l:] = 100.0
+    pp = build_prosody_predictor(weights, dtype=dtype)
+    F0, N = pp.F0Ntrain(x, inp["s"], lengths=lens)
+    for b, l in enumerate(lens):
+        f0s, ns = pp.F0Ntrain(x[b:b + 1, :, :l].contiguous(), inp["s"][b:b + 1])
+        for got, solo in ((F0, f0s), (N, ns)):
+            scale = max(1.0, float(solo.abs().max()))
+            assert float((got[b, :2 * l] - solo[0]).abs().max()) <= 2e-5 * scale, (b, l)
+            assert not got[b, 2 * l:].abs().any(), (b, l)
+    with pytest.raises(ValueError):
+        pp.F0Ntrain(x, inp["s"], lengths=[49] * B)
+
+
 def test_f0ntrain_bf16_vs_oracle(weights, oracle):
     if not L.load().kk_device_is_sm100():
         pytest.skip("needs sm_100")
