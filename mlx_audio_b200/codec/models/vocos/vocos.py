@@ -1,5 +1,6 @@
 """Drop-in for the ``ISTFTHead`` of mlx_audio/codec/models/vocos/vocos.py:119-140: the same iSTFT
-kernels as ``utils.istft`` behind a Linear projection.  The projection is a plain library GEMM (torch / cuBLAS); the
+kernels as ``utils.istft`` behind a Linear projection.  The projection runs on the tensor cores in fp32 accuracy
+(``_gemm.LinearTF32x3``: ``kk_conv1d_tf32_tc`` as a 1x1 convolution; it was a cuBLAS call in round 1); the
 polar stage (exp, clip, cos, sin) is ``kk_polar_to_spec`` writing the frame-major spectrum ``kk_istft_f32`` reads, so
 no transposed copy is made.  No CPU path."""
 from __future__ import annotations
@@ -17,6 +18,7 @@ class ISTFTHead:
         self.device = torch.device(device or "cuda")
         self.weight = None        # out.weight (n_fft + 2, dim)
         self.bias = None          # out.bias   (n_fft + 2,)
+        self._lin = None
 
     def load_weights(self, weights, strict: bool = True):
         """``out.weight`` / ``out.bias`` (with or without a ``head.`` prefix)."""
@@ -29,10 +31,12 @@ class ISTFTHead:
                 if tuple(t.shape) != (self.n_fft + 2, self.dim):
                     raise ValueError(f"out.weight must be {(self.n_fft + 2, self.dim)}, got {tuple(t.shape)}")
                 self.weight = t.to(self.device).contiguous()
+                self._lin = None
             elif k == "out.bias":
                 if tuple(t.shape) != (self.n_fft + 2,):
                     raise ValueError(f"out.bias must be {(self.n_fft + 2,)}, got {tuple(t.shape)}")
                 self.bias = t.to(self.device).contiguous()
+                self._lin = None
             elif strict:
                 raise ValueError(f"Unexpected ISTFTHead parameter {k!r}")
         return self
@@ -47,9 +51,13 @@ class ISTFTHead:
             raise ValueError(f"x must be (B, L, {self.dim}), got {tuple(x.shape)}")
         B, frames, _ = x.shape
         bins = self.n_fft // 2 + 1
-        h = torch.addmm(self.bias, x.reshape(B * frames, self.dim), self.weight.t())       # nn.Linear :124 (cuBLAS)
+        if self._lin is None:
+            from ...._gemm import LinearTF32x3
+            self._lin = LinearTF32x3(self.weight, self.bias)
+        pitch = -(-(self.n_fft + 2) // 4) * 4
+        h = self._lin(x.contiguous(), pitch)                                                # nn.Linear :124
         spec = torch.empty(B, frames, bins, 2, dtype=torch.float32, device=x.device)
-        L.check(L.load().kk_polar_to_spec(L.ptr(h), self.n_fft + 2, L.ptr(spec), B * frames, bins, 1e2, L.stream()),
+        L.check(L.load().kk_polar_to_spec(L.ptr(h), pitch, L.ptr(spec), B * frames, bins, 1e2, L.stream()),
                 "kk_polar_to_spec")                                                        # :126-133
         # istft(S, window=hanning(n_fft) [symmetric, explicit array], hop_length, win_length=n_fft) :134-139
         y = U.istft(torch.view_as_complex(spec).transpose(1, 2), hop_length=self.hop_length, win_length=self.n_fft,

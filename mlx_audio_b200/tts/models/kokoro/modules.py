@@ -165,8 +165,7 @@ class ProsodyPredictor:
         recurrent weights in shared memory).  fp32 in both modes - it is ~1 ms beside a 35 ms decode.
         ``lengths`` (extension): valid steps per sequence of a zero-padded batch; the backward direction starts at each
         sequence's own end, rows past it are zeros."""
-        from ...._lib import ConvDesc
-        import ctypes as C
+        from ...._gemm import LinearTF32x3
         lib = L.load()
         w = self._weights
         if self._lstm is None:
@@ -177,31 +176,22 @@ class ProsodyPredictor:
             wx = torch.cat([f32(w["shared.Wx_forward"]), f32(w["shared.Wx_backward"])], 0)          # (2 * 4H, D)
             bias = torch.cat([f32(w["shared.bias_ih_forward"]) + f32(w["shared.bias_hh_forward"]),
                               f32(w["shared.bias_ih_backward"]) + f32(w["shared.bias_hh_backward"])]).contiguous()
-            pc = PreparedConv("shared.Wx", wx[:, None, :].contiguous(), bias, need_bf16=False, need_f32=False,
-                              need_tf32=True)
+            pc = LinearTF32x3(wx.contiguous(), bias)
             whT = torch.stack([f32(w["shared.Wh_forward"]).t(), f32(w["shared.Wh_backward"]).t()]).contiguous()
             self._lstm = (pc, whT)
         pc, whT = self._lstm
         x = x_blc.to(device=self.device, dtype=torch.float32).contiguous()
         B, L_, D = x.shape
         H = self.cfg["d_hid"] // 2
-        if D != pc.C_in or D % 4:
-            raise ValueError(f"shared LSTM input must be (B, L, {pc.C_in}), got {tuple(x.shape)}")
+        if D != pc.n_in:
+            raise ValueError(f"shared LSTM input must be (B, L, {pc.n_in}), got {tuple(x.shape)}")
         lens = None
         if lengths is not None:
             lens = torch.as_tensor(lengths).to(device=self.device, dtype=torch.int32).contiguous()
             if lens.numel() != B:
                 raise ValueError(f"lengths: expected {B} entries, got {lens.numel()}")
-        xw = torch.empty(B, L_, 8 * H, device=self.device)
-        d = ConvDesc()
-        d.B, d.L_in, d.C_in, d.x_pitch = B, L_, D, D
-        d.taps, d.dil, d.pad_left, d.stride, d.Cw = 1, 1, 0, 1, pc.CwT
-        d.M, d.N, d.C_out, d.up, d.up_off = L_, pc.N, pc.C_out, 1, 0
-        d.L_true = d.L_out = L_
-        d.bias, d.scale = L.ptr(pc.bias), 1.0
-        d.out, d.out_pitch = L.ptr(xw), 8 * H
+        xw = pc(x)                                              # (B, L, 2 * 4H)
         st = L.stream()
-        L.check(lib.kk_conv1d_tf32_tc(L.ptr(x), L.ptr(pc.w32hi), L.ptr(pc.w32lo), C.byref(d), 3, st), "kk_conv1d_tf32_tc")
         h_ws = torch.empty(2, 2, B, H, device=self.device)
         out = torch.empty(B, L_, 2 * H, device=self.device)
         L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, L_, H,
