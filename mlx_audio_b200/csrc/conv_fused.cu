@@ -33,7 +33,6 @@ namespace kk {
 constexpr int FV_XF_WARPS = 8;
 constexpr int FV_EPI_WARPS = 8;
 constexpr int FV_XF_THREADS = FV_XF_WARPS * 32;
-constexpr int FV_EPI_THREADS = FV_EPI_WARPS * 32;
 constexpr int FV_XF_WARP0 = 4;
 constexpr int FV_EPI_WARP0 = 12;
 constexpr int FV_THREADS = (FV_EPI_WARP0 + FV_EPI_WARPS) * 32;  // 640 = 5 warpgroups, launched with 96 registers

@@ -242,8 +242,6 @@ static int stft_n20_launch(const float* har_source, float* har, int har_pitch, v
     tb.sn[n] = (float)sin(2.0 * M_PI * n / 20.0);
   }
   int F = S / 5 + 1;
-  long long total = (long long)B * F;
-  (void)total;
   const int blocks = B * ((F + kk::ST_FR - 1) / kk::ST_FR);
   kk::stft_n20_kernel<<<blocks, kk::ST_FR, 0, (cudaStream_t)stream>>>(
       har_source, har, har_pitch, (__nv_bfloat16*)har16, pitch16, rows16, B, S, F, tb, lens, len_mul);
