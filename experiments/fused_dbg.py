@@ -13,7 +13,7 @@ lib.kk_debug_fused_buffer.argtypes = [C.c_void_p]; lib.kk_debug_fused_buffer.res
 NAMES = ["Bprod:b_empty", "MMA:tmem_empty", "MMA:a_full", "MMA:b_full", "Xprod:empty", "XF:data", "XF:slot_empty",
          "EPI:tmem_full", "EPI:res_full", "-", "MMA:total"]
 
-def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
+def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out, with_stats=True):
     dev = "cuda"
     x = torch.randn(B, Lr, Cc, device=dev)
     xd = x.to(torch.bfloat16).contiguous() if x_bf16 else x
@@ -40,7 +40,7 @@ def run(B, Lr, Cc, k, dil, x_bf16, with_res, with_out):
     d.scale = 1.0
     if with_out: d.out, d.out_pitch = out.data_ptr(), Cc
     else: d.out_act, d.act_pitch, d.act_is_bf16, d.act_slope = oact.data_ptr(), Cc, 1, 1.0
-    d.stats = ostats.data_ptr()
+    if with_stats: d.stats = ostats.data_ptr()
     for _ in range(2):
         L.check(lib.kk_conv1d_adain_bf16_tc(C.byref(a), w.data_ptr(), C.byref(d), L.stream()))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -78,6 +78,16 @@ def run_post(B, Lr):
 import os
 if os.environ.get("DBG_SET") == "post":
     run_post(64, 38401)
+    sys.exit(0)
+if os.environ.get("DBG_SET") == "res":   # KK_L2PF=5 / 21 / 37: residual path whole / fetched not added / added not fetched
+    for k in (3, 7):
+        run(64, 38401, 128, k, 1, True, False, False)
+        run(64, 38401, 128, k, 1, True, "bf16", False)
+    sys.exit(0)
+if os.environ.get("DBG_SET") == "nostats":   # how much of an epilogue-bound launch is the statistics arithmetic?
+    for k in (3, 7):
+        run(64, 38401, 128, k, 1, True, "bf16", False)
+        run(64, 38401, 128, k, 1, True, "bf16", False, with_stats=False)
     sys.exit(0)
 if os.environ.get("DBG_SET") == "s16":
     for k in (3, 7, 11):

@@ -208,12 +208,12 @@ __device__ unsigned long long* g_fv_dbg = nullptr;
 #endif
 
 // Residual tile (32 rows x 32 channels at utterance b, row row0, channel ch0) -> staging tile, by 16-byte cp.async from
-// all 32 lanes; completion = one deferred arrive per lane on `bar` (initialised with count 32).  fp32: 128-byte rows in
+// all 32 lanes; completion = the caller's cp.async group (commit after this call, wait_group + __syncwarp before the
+// tile is read; round 1's per-lane deferred mbarrier arrives cost 10 % of an epilogue-bound launch).  fp32: 128-byte rows in
 // the 128B-swizzle layout (chunk ^= row & 7); bf16 (res_is_bf16): 64-byte rows, chunk ^= (row >> 1) & 3.
 // Deliberately NOT a TMA load: residual boxes in the TMA queue delayed the weight and input loads behind them
 // (C=256 k=11: weight-ring stalls 18 % -> 47 % of the issuer's time).
-__device__ __forceinline__ void fv_issue_res(const kk_conv_desc& d, int b, int row0, int ch0, uint8_t* tile, uint64_t* bar,
-                                             int lane) {
+__device__ __forceinline__ void fv_issue_res(const kk_conv_desc& d, int b, int row0, int ch0, uint8_t* tile, int lane) {
   const uint32_t t = ptx::smem_u32(tile);
   if (d.res_is_bf16) {
     const int c = lane & 3;
@@ -241,7 +241,6 @@ __device__ __forceinline__ void fv_issue_res(const kk_conv_desc& d, int b, int r
                    : "memory");
     }
   }
-  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(ptx::smem_u32(bar)) : "memory");
 }
 
 // contiguous share of the tile list for CTA `cta` of `ncta`
@@ -280,7 +279,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
   uint64_t* b_empty = b_full + 8;                                        // [8]
   uint64_t* tmem_full = b_empty + 8;                                     // [2]
   uint64_t* tmem_empty = tmem_full + 2;                                  // [2]
-  uint64_t* res_full = tmem_empty + 2;                                   // [FV_EPI_WARPS * 2]
+  uint64_t* res_full = tmem_empty + 2;                                   // [FV_EPI_WARPS * 2] (unused since the residual copies complete by cp.async groups; kept for the layout)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_full + FV_EPI_WARPS * 2);
   int* rg_ts = reinterpret_cast<int*>(smem + Cfg::OFF_RG);              // ragged batches: first tile of each utterance
   const int* ts = d.lens ? rg_ts : nullptr;
@@ -326,7 +325,6 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       ptx::mbar_init(&tmem_full[i], 1);
       ptx::mbar_init(&tmem_empty[i], FV_EPI_WARPS);
     }
-    for (int i = 0; i < FV_EPI_WARPS * 2; ++i) ptx::mbar_init(&res_full[i], 32);   // one deferred arrive per lane
     ptx::fence_barrier_init();
   }
   if (warp == 2) ptx::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
@@ -583,26 +581,70 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     constexpr int NRC = HR / 32;
     const int row_half = CHB ? 0 : half * HR;
     uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // [32 rows][32 channels] fp32, 16-byte chunk ^= row & 7
-    uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
     const bool via_smem = has_st;   // fp32 results leave by TMA (store and/or reduce-add) from the staging tile
     const bool res16 = d.res_is_bf16 != 0;
     const int ch0 = lg * 32 + (CHB ? half * 128 : 0), chan = ch0 + lane;
     const float bias_s = (d.bias ? __ldg(d.bias + chan) : 0.f) * d.scale;   // (v + bias) * scale = fma(v, scale, bias * scale)
     const int n_items = t_count * NRC;
+#ifdef KK_TUNE   // lab knobs (KK_L2PF bits 4 / 5): residual fetched but not added / added (from stale staging) but not fetched
+    const bool dbg_noadd = (flags & 16) != 0, dbg_nofetch = (flags & 32) != 0;
+#else
+    constexpr bool dbg_noadd = false, dbg_nofetch = false;
+#endif
     RgMap map(ts, m_tiles), map_res(ts, m_tiles);
+    // bf16 residual: a running per-lane cursor.  The NRC chunks of a tile are consecutive rows, and a lane's four
+    // 16-byte pieces of a chunk are 8 rows apart, so within a tile the source pointer just advances by 8 rows per
+    // copy; the tile lookup and the 64-bit address arithmetic happen once per tile.  (Measured: with the address of
+    // every copy rebuilt from (b, row, pitch) the fetch cost an epilogue-bound launch 0.15 of 0.72 ms - instructions
+    // on the critical warps, not bytes: prefetching the rows into L2 changed nothing.)
+    const uint8_t* rcur = nullptr;
+    int rleft = 0;
+    const size_t rstep8 = (size_t)8 * d.res_pitch * 2;
+    const uint32_t rdst = (uint32_t)((lane >> 2) * 64 + (((lane & 3) ^ ((lane >> 3) & 3)) << 4));   // + i * 512: (r >> 1) & 3 = (lane >> 3) & 3 for r = 8 i + (lane >> 2)
+    // Completion by cp.async groups (one per item, committed even when there is nothing left to fetch, so that
+    // "all but the newest group" always means "item n has landed"): the mbarrier form - 32 per-lane arrives and a
+    // try_wait per chunk on the warps the launch waits for - cost 0.07 of 0.71 ms on the k = 3 conv2 of the 128-channel
+    // stage with the copies themselves switched off.
     auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
-      if (n >= n_items) return;
+      if (dbg_nofetch) return;
+      if (n >= n_items) { asm volatile("cp.async.commit_group;" ::: "memory"); return; }
+      if (res16) {
+        if (n % NRC == 0) {
+          int b, mtile;
+          map_res.locate(t_start + n / NRC, b, mtile);
+          const int row = mtile * TR + row_half + (lane >> 2);
+          rcur = reinterpret_cast<const uint8_t*>(d.res) + (((size_t)b * d.L_res + row) * d.res_pitch + ch0 + (lane & 3) * 8) * 2;
+          rleft = d.L_res - row;
+        }
+        const uint32_t t = ptx::smem_u32(stg0 + (n & 1) * Cfg::STG_HALF) + rdst;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const bool ok = rleft > 8 * i;
+#ifdef KK_TUNE
+          if ((flags & 64) && i) continue;          // lab: one copy of four
+          if ((flags & 128)) continue;              // lab: no copies, barrier protocol only
+#endif
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(t + (uint32_t)(i * 512)),
+                       "l"(ok ? rcur + i * rstep8 : reinterpret_cast<const uint8_t*>(d.res)), "r"(ok ? 16u : 0u)
+                       : "memory");
+        }
+        rcur += 4 * rstep8;
+        rleft -= 32;
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        return;
+      }
       const int tile = t_start + n / NRC, rc = n % NRC;
       int b, mtile;
       map_res.locate(tile, b, mtile);
       const int row0 = mtile * TR + row_half + rc * 32;
-      fv_issue_res(d, b, row0, ch0, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
+      fv_issue_res(d, b, row0, ch0, stg0 + (n & 1) * Cfg::STG_HALF, lane);
+      asm volatile("cp.async.commit_group;" ::: "memory");
     };
     if (has_res) { issue_res(0); issue_res(1); }
     double acc_s = 0.0, acc_q = 0.0;   // fp64 running instance-norm sums of this thread's channel
     int stat_b = -1;
-    FV_DBG_DECL(w_tfull); FV_DBG_DECL(w_res);
+    FV_DBG_DECL(w_tfull);
     auto flush_stats = [&](int b) {
       if (b < 0) return;
       atomicAdd(d.stats + ((size_t)b * d.C_out + chan) * 2, acc_s);
@@ -641,8 +683,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const int nstore = d.M - row0;           // rows of this chunk inside the tensors: padding rows are stored as 0
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
-        if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
-        else if (via_smem) {
+        if (has_res && !dbg_nofetch) {
+          asm volatile("cp.async.wait_group 1;" ::: "memory");   // this lane's copies of item n (item n + 1 may be in flight)
+          __syncwarp();                                           // ... and every other lane's
+        } else if (via_smem) {
           if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA operation has finished reading this tile
           __syncwarp();
         }
@@ -655,7 +699,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         // lane = channel: element (row jj, channel) of the swizzled tile; conflict-free for every jj.
         const uint32_t sbase = ptx::smem_u32(st) + (uint32_t)(lane & 3) * 4u;
         const uint32_t lchunk = (uint32_t)(lane >> 2);
-        if (has_res && res16) {
+        if (has_res && res16 && !dbg_noadd) {
           // bf16 residual tile: 64-byte rows, lane = channel reads 2 bytes of row jj (one contiguous row per instruction)
           const uint32_t hbase = ptx::smem_u32(st) + (uint32_t)(lane & 7) * 2u;
           const uint32_t hchunk = (uint32_t)(lane >> 3);
@@ -717,7 +761,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       }
     }
     if (do_stats) flush_stats(stat_b);
-    if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
+    if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, 0); }
     if (via_smem && lane == 0) ptx::bulk_wait<0>();      // all TMA stores have completed before the CTA retires
     } else {
     // Work item n = (tile j, chunk c) of this warp: 32 rows (TMEM lane group lg of sub-tile mt) x 32 columns.
@@ -728,7 +772,6 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     constexpr int NCH = MT == 2 ? BN / 32 : BN / 64;   // chunks per warp and tile
     const int chunk0 = MT == 2 ? 0 : half * NCH;
     uint8_t* stg0 = smem + Cfg::OFF_STG + ew * 4096;   // staging tile p at stg0 + p * STG_HALF (1024-aligned)
-    uint64_t* rbar = res_full + ew * 2;
     const bool do_stats = d.stats != nullptr;
     const bool out_aligned_act = d.out_act != nullptr;
     const bool res16 = d.res_is_bf16 != 0;
@@ -736,12 +779,14 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     RgMap map(ts, m_tiles), map_res(ts, m_tiles);
 
     auto issue_res = [&](int n) {   // all lanes: fetch the residual tile of item n into staging buffer n & 1
-      if (n >= n_items) return;
-      const int tile = t_start + n / NCH, c = n % NCH;
-      int b, mtile;
-      map_res.locate(tile, b, mtile);
-      const int m0 = mtile * (128 * MT) + mt * 128 + lg * 32;
-      fv_issue_res(d, b, m0, (chunk0 + c) * 32, stg0 + (n & 1) * Cfg::STG_HALF, &rbar[n & 1], lane);
+      if (n < n_items) {            // completion by cp.async groups, one per item (see the transposed epilogue above)
+        const int tile = t_start + n / NCH, c = n % NCH;
+        int b, mtile;
+        map_res.locate(tile, b, mtile);
+        const int m0 = mtile * (128 * MT) + mt * 128 + lg * 32;
+        fv_issue_res(d, b, m0, (chunk0 + c) * 32, stg0 + (n & 1) * Cfg::STG_HALF, lane);
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
     };
     if (has_res) { issue_res(0); issue_res(1); }
 
@@ -749,7 +794,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
 #pragma unroll
     for (int c = 0; c < NCH; ++c) acc_s[c] = acc_q[c] = 0.0;
     int stat_b = -1;
-    FV_DBG_DECL(w_tfull); FV_DBG_DECL(w_res);
+    FV_DBG_DECL(w_tfull);
     auto flush_stats = [&](int b) {
       if (b < 0) return;
 #pragma unroll
@@ -782,8 +827,10 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const int cbase = (chunk0 + c) * 32;
         float v[32];
         ptx::tmem_ld_32x32(tacc + (uint32_t)cbase, v);
-        if (has_res) FV_WAIT(&rbar[p], (uint32_t)(n >> 1) & 1, w_res);
-        else if (has_st) {
+        if (has_res) {
+          asm volatile("cp.async.wait_group 1;" ::: "memory");   // this lane's copies of item n (item n + 1 may be in flight)
+          __syncwarp();                                           // ... and every other lane's
+        } else if (has_st) {
           if (lane == 0) ptx::bulk_wait_read<0>();       // the previous TMA store has finished reading this tile
           __syncwarp();
         }
@@ -890,7 +937,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
       }
     }
     if (do_stats) flush_stats(stat_b);
-    if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, w_res); }
+    if (ew == 0 && lane == 0) { FV_DBG_OUT(7, w_tfull); FV_DBG_OUT(8, 0); }
     if (has_st && lane == 0) ptx::bulk_wait<0>();        // all TMA stores have completed before the CTA retires
     }  // !SWAP
   } else {
