@@ -589,8 +589,9 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
     const int n_items = t_count * NRC;
 #ifdef KK_TUNE   // lab knobs (KK_L2PF bits 4 / 5): residual fetched but not added / added (from stale staging) but not fetched
     const bool dbg_noadd = (flags & 16) != 0, dbg_nofetch = (flags & 32) != 0;
+    const bool dbg_notmem = (flags & 256) != 0, dbg_nostore = (flags & 512) != 0, dbg_nostats = (flags & 1024) != 0;   // knock-outs
 #else
-    constexpr bool dbg_noadd = false, dbg_nofetch = false;
+    constexpr bool dbg_noadd = false, dbg_nofetch = false, dbg_notmem = false, dbg_nostore = false, dbg_nostats = false;
 #endif
     RgMap map(ts, m_tiles), map_res(ts, m_tiles);
     // bf16 residual: a running per-lane cursor.  The NRC chunks of a tile are consecutive rows, and a lane's four
@@ -682,7 +683,11 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
         const int nvalid = Mb - row0;            // rows of this chunk inside the utterance (may be <= 0 or >= 32)
         const int nstore = d.M - row0;           // rows of this chunk inside the tensors: padding rows are stored as 0
         float v[32];
-        ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
+        if (!dbg_notmem) ptx::tmem_ld_32x32(tacc + (uint32_t)(rc * 32), v);
+        else {
+#pragma unroll
+          for (int jj = 0; jj < 32; ++jj) v[jj] = 0.f;
+        }
         if (has_res && !dbg_nofetch) {
           asm volatile("cp.async.wait_group 1;" ::: "memory");   // this lane's copies of item n (item n + 1 may be in flight)
           __syncwarp();                                           // ... and every other lane's
@@ -726,7 +731,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
 #pragma unroll
           for (int jj = 0; jj < 32; ++jj) v[jj] = jj < nvalid ? fmaf(v[jj], d.scale, bias_s) : 0.f;
         }
-        if (do_stats) {
+        if (do_stats && !dbg_nostats) {
 #pragma unroll
           for (int jj = 0; jj < 32; ++jj) {
             s_ += v[jj];
@@ -747,7 +752,7 @@ conv1d_adain_tc_kernel(const __grid_constant__ CUtensorMap tmB, const __grid_con
             ptx::bulk_commit();
           }
         }
-        if (d.out_act && nstore > 0) {
+        if (d.out_act && nstore > 0 && !dbg_nostore) {
           __nv_bfloat16* ap = (__nv_bfloat16*)d.out_act + ((size_t)b * d.L_out + row0) * d.act_pitch + chan;
           if (d.act_pitch == 128) store_bf16(ap, 128, v, nstore);
           else if (d.act_pitch == 256) store_bf16(ap, 256, v, nstore);
