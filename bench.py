@@ -405,6 +405,17 @@ def run_ours(args, rank: int, world: int, local_rank: int):
     B, T = args.batch, args.frames
     S = T * synth.SAMPLES_PER_FRAME
     audio_s_per_step = B * S / synth.SAMPLE_RATE
+    # config 2 first: its kernels are single launches timed ALONE (the roofline's burst peak is the denominator), so they
+    # are measured before the decoder loop pulls the clocks down to the box's power cap
+    early = {}
+    if rank == 0 and args.dtype == "bf16" and "dsp" not in args.skip.split(","):
+        t0 = time.perf_counter()
+        try:
+            early["dsp"] = bench_dsp(dev, load_peaks())
+            early["dsp"]["bench_seconds"] = time.perf_counter() - t0
+        except Exception as e:   # a sub-benchmark never costs the headline
+            early["dsp"] = {"error": f"{type(e).__name__}: {e}"}
+        torch.cuda.synchronize()
     weights = synth.synth_decoder_weights(seed=2000)
     eng_opts = {"res16": args.res16} if args.res16 >= 0 else None
     dec = build_decoder(weights, dtype=args.dtype, device=str(dev), engine_options=eng_opts)
@@ -589,9 +600,8 @@ def run_ours(args, rank: int, world: int, local_rank: int):
         subs[name] = r
         torch.cuda.synchronize()
 
+    subs.update(early)
     if args.dtype == "bf16":
-        if rank == 0:   # single launches timed alone: before the long sub-benchmarks pull the clocks down to the power cap
-            sub("dsp", lambda: bench_dsp(dev, peaks))
         sub("c4", lambda: bench_c4(dev, dec, rank, world))
         sub("c5", lambda: bench_c5(dev, dec, rank, world))
         if rank == 0:
