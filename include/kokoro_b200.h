@@ -256,6 +256,17 @@ int kk_dwconv1d_f32(const float* x, const float* w, const float* bias, const flo
 int kk_noise_mix_f32(const float* x, const float* h, const float* noise, float* out, int B, long long L, int C,
                      void* stream);
 int kk_tanh_f32(const float* x, float* out, long long n, void* stream);
+/* ---- BigVGAN anti-aliased activation (mlx_audio/codec/models/bigvgan/resample.py:152-177 `Activation1d` with its
+ * default ratios 2 / 2 and 12-tap kaiser-sinc filters; activation.py:5-51), fused, channels-last fp32 (B, L, C):
+ * edge-pad + depthwise transposed conv x2 (UpSample1d :104-134) -> v = u + sin^2(alpha u) / (beta + eps) (beta = NULL:
+ * Snake, beta := alpha; logscale: exp() of both) -> edge-pad + depthwise stride-2 low-pass (DownSample1d :137-149).
+ * up_filter / down_filter: HOST pointers to the 12 taps (`upsample.filter`, `downsample.lowpass.filter`). */
+/* out = min(max(x, lo), hi): BigVGAN's head when use_tanh_at_final is off (bigvgan.py:125-126) */
+int kk_clip_f32(const float* x, float* out, float lo, float hi, long long n, void* stream);
+/* out = a x + b y (y may be NULL): the sum over a stage's resblocks and its division by their number (bigvgan.py:113-117) */
+int kk_axpby_f32(const float* x, const float* y, float* out, float a, float b, long long n, void* stream);
+int kk_aa_act_f32(const float* x, float* out, const float* alpha, const float* beta, const float* up_filter,
+                  const float* down_filter, int B, int L, int C, int logscale, float eps, void* stream);
 /* Weight-norm fold with the epsilon and operation order as parameters: g_first = 1, eps = 0 is the DAC form
  * w = (g * v) / ||v|| of mlx_audio/codec/models/descript/nn/layers.py:7-12,57 (norm over (K, I) per output channel). */
 int kk_fold_weight_norm_ex(const float* v, const float* g, float* w, int O, int KI, float eps, int g_first,

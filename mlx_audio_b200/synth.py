@@ -282,7 +282,7 @@ FLOP_PER_AUDIO_SECOND = 2.0 * MAC_PER_FRAME * (SAMPLE_RATE / SAMPLES_PER_FRAME)
 
 def synth_named_weights(shapes: Dict[str, Tuple[int, ...]], seed: int = 0) -> Dict[str, np.ndarray]:
     """Seeded weights for a module tree given as {dotted parameter name: shape} (the codec generators, whose parameter
-    names end in weight_v / weight_g / bias / alpha).  Each tensor has its own generator keyed on (seed, name), so the
+    names end in weight_v / weight_g / bias / alpha / beta).  Each tensor has its own generator keyed on (seed, name), so the
     values do not depend on the order or on which other parameters exist."""
     import zlib
     out = {}
@@ -294,7 +294,7 @@ def synth_named_weights(shapes: Dict[str, Tuple[int, ...]], seed: int = 0) -> Di
             a = r.standard_normal(shape, dtype=np.float32) / np.float32(np.sqrt(fan))
         elif name.endswith("weight_g"):
             a = r.uniform(0.25, 0.5, shape).astype(np.float32)     # small gains: the tanh head must not saturate
-        elif name.endswith("alpha"):
+        elif name.endswith("alpha") or name.endswith("beta"):
             a = r.uniform(0.5, 2.0, shape).astype(np.float32)
         else:  # bias
             a = (0.1 * r.standard_normal(shape, dtype=np.float32)).astype(np.float32)

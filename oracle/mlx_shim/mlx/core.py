@@ -333,12 +333,17 @@ def transpose(x, axes=None):
     return _wrap(np.transpose(_raw(x), axes))
 
 
-def pad(x, pad_width, constant_values=0):
+def pad(x, pad_width, mode="constant", constant_values=0):
+    """mx.pad: mode "constant" or "edge" (codec/models/bigvgan/resample.py:84, 125 replicate the end samples)."""
     x = _raw(x)
     if isinstance(pad_width, numbers.Integral):
         pad_width = [(pad_width, pad_width)] * x.ndim
     elif isinstance(pad_width, tuple) and len(pad_width) == 2 and all(isinstance(p, numbers.Integral) for p in pad_width):
         pad_width = [tuple(pad_width)] * x.ndim
+    if mode == "edge":
+        return _wrap(np.pad(x, pad_width, mode="edge"))
+    if mode != "constant":
+        raise ValueError(f"mx.pad: unsupported mode {mode!r}")
     return _wrap(np.pad(x, pad_width, constant_values=constant_values))
 
 

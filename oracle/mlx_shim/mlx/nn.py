@@ -133,3 +133,7 @@ class Sequential(Module):
 class Tanh(Module):
     def __call__(self, x):
         return mx.array(np.tanh(np.asarray(x)))
+
+
+class ConvTranspose1d(Module):
+    """Named (never instantiated) by codec/models/bigvgan/conv.py:111, a bare expression statement."""

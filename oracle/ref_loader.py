@@ -224,3 +224,22 @@ def load_reference_dac():
             sys.modules["huggingface_hub"] = hub
     ns.dac = _load("mlx_audio.codec.models.descript.dac", os.path.join(root, "codec", "models", "descript", "dac.py"))
     return ns
+
+
+def load_reference_bigvgan():
+    """The reference's BigVGAN generator (codec/models/bigvgan/{activation,conv,resample,amp,bigvgan}.py: Snake /
+    SnakeBeta, the weight-normed convolutions, the kaiser-sinc anti-aliased ``Activation1d``, ``AMPBlock1/2``,
+    ``BigVGAN``), unmodified, on the shim - SURVEY 8(f) row 4."""
+    ns = load_reference()
+    if hasattr(ns, "bigvgan"):
+        return ns
+    root = os.path.join(REFERENCE_ROOT, "mlx_audio")
+    for name, sub in (("mlx_audio.codec", ("codec",)), ("mlx_audio.codec.models", ("codec", "models")),
+                      ("mlx_audio.codec.models.bigvgan", ("codec", "models", "bigvgan"))):
+        if name not in sys.modules:
+            _pkg(name, os.path.join(root, *sub))
+    d = os.path.join(root, "codec", "models", "bigvgan")
+    for mod in ("activation", "conv", "resample", "amp"):
+        setattr(ns, f"bigvgan_{mod}", _load(f"mlx_audio.codec.models.bigvgan.{mod}", os.path.join(d, f"{mod}.py")))
+    ns.bigvgan = _load("mlx_audio.codec.models.bigvgan.bigvgan", os.path.join(d, "bigvgan.py"))
+    return ns
