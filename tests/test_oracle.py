@@ -354,3 +354,38 @@ def test_reference_snac_shape_pin_on_the_shim():
     y = np.asarray(dec(ns.mx.array(np.zeros((1, 236, 24), np.float32))))
     assert y.shape == (1, 120907, 1)
     assert [tuple(s) for s in ns.mx.random.log[-4:]] == [(1, 1, 32), (1, 1, 16), (1, 1, 8), (1, 1, 4)]   # noise is (B, 1, C)
+
+
+def test_bigvgan_activation_closed_form_vs_reference_golden(golden_dir):
+    """oracle.codec.aa_activation (the clamped-index closed form the CUDA kernel evaluates) against the output of the
+    reference's own UpSample1d / SnakeBeta / DownSample1d (tests/golden/make_golden_bigvgan.py), incl. sequences
+    shorter than the filters."""
+    from oracle import codec
+    from mlx_audio_b200.codec.models.bigvgan.resample import kaiser_sinc_filter1d
+    g = np.load(os.path.join(golden_dir, "bigvgan.npz"))
+    f = kaiser_sinc_filter1d(0.25, 0.3, 12).numpy().reshape(-1)
+    for T in (1, 2, 3, 7, 8, 9, 40):
+        y = codec.aa_activation(g[f"act.T{T}.x"], g[f"act.T{T}.alpha"], g[f"act.T{T}.beta"], f, f, True)
+        ref = g[f"act.T{T}.y"]
+        assert y.shape == ref.shape and np.abs(y - ref).max() < 2e-6 * max(1.0, float(np.abs(ref).max())), T
+
+
+def test_reference_bigvgan_runs_on_the_shim_and_matches_its_golden(golden_dir):
+    """Live re-check: the reference's own BigVGAN on oracle/mlx_shim reproduces the committed golden (and yields
+    T * prod(upsample_rates) samples)."""
+    from oracle import ref_loader
+    if not ref_loader.reference_available():
+        pytest.skip("reference tree not present")
+    from mlx_audio_b200 import synth
+    g = np.load(os.path.join(golden_dir, "bigvgan.npz"))
+    ns = ref_loader.load_reference_bigvgan()
+    cfg = dict(num_mels=16, upsample_rates=[4, 2], upsample_kernel_sizes=[8, 4], upsample_initial_channel=64, resblock="1",
+               resblock_kernel_sizes=[3, 7], resblock_dilation_sizes=[[1, 3, 5], [1, 3, 5]], activation="snakebeta",
+               snake_logscale=True)
+    model = ns.bigvgan.BigVGAN(ns.bigvgan.BigVGANConfig(**cfg))
+    shapes = {k: tuple(v.shape) for k, v in model.named_parameters().items()}
+    for k, v in synth.synth_named_weights({k: s for k, s in shapes.items() if not k.endswith("filter")},
+                                          seed=int(g["amp1.seed"])).items():
+        model.set_parameter(k, v)
+    y = np.asarray(model(ns.mx.array(g["amp1.x"])))
+    assert y.shape == (2, 1, 20 * 8) and np.abs(y - g["amp1.y"]).max() < 1e-6
