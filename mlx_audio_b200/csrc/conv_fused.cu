@@ -104,9 +104,16 @@ __device__ __forceinline__ float4 fv_lds128(uint32_t addr) {
 // NB steps (4 rows each, FV_XF_WARPS steps apart) of the in-place transform: all loads, then all arithmetic, then all
 // stores (the shared-memory accesses are volatile asm, which the compiler will not reorder - the batching is what
 // exposes the instruction-level parallelism).
+#ifdef KK_TUNE
+__device__ int g_fv_xf_knock = 0;   // lab: 1 = no activation arithmetic (affine only), 2 = no arithmetic at all (load + store), 3 = nothing
+#define FV_XF_KNOCK g_fv_xf_knock
+#else
+#define FV_XF_KNOCK 0
+#endif
 template <int ACT, int NB>
 __device__ __forceinline__ void fv_xf_steps(uint32_t slot, const float4 (&k)[8], float slope, int s0, int nrows,
                                             int l_base, int L_in, int q, int sub) {
+  if (FV_XF_KNOCK == 3) return;
   uint4 t[NB];
   uint32_t p[NB];
   bool ok[NB];
@@ -121,6 +128,15 @@ __device__ __forceinline__ void fv_xf_steps(uint32_t slot, const float4 (&k)[8],
   }
 #pragma unroll
   for (int u = 0; u < NB; ++u) {   // branch-free so that the NB cosine chains interleave
+    if (FV_XF_KNOCK == 2) continue;
+    if (FV_XF_KNOCK == 1) {
+      const uint4 v = t[u];
+      t[u].x = fv_pack(fv_apply<KK_ACT_NONE>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<KK_ACT_NONE>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
+      t[u].y = fv_pack(fv_apply<KK_ACT_NONE>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<KK_ACT_NONE>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
+      t[u].z = fv_pack(fv_apply<KK_ACT_NONE>(__uint_as_float(v.z << 16), k[4], slope), fv_apply<KK_ACT_NONE>(__uint_as_float(v.z & 0xffff0000u), k[5], slope));
+      t[u].w = fv_pack(fv_apply<KK_ACT_NONE>(__uint_as_float(v.w << 16), k[6], slope), fv_apply<KK_ACT_NONE>(__uint_as_float(v.w & 0xffff0000u), k[7], slope));
+      continue;
+    }
     const uint4 v = t[u];
     const uint32_t x0 = fv_pack(fv_apply<ACT>(__uint_as_float(v.x << 16), k[0], slope), fv_apply<ACT>(__uint_as_float(v.x & 0xffff0000u), k[1], slope));
     const uint32_t x1 = fv_pack(fv_apply<ACT>(__uint_as_float(v.y << 16), k[2], slope), fv_apply<ACT>(__uint_as_float(v.y & 0xffff0000u), k[3], slope));
@@ -1032,6 +1048,13 @@ static int launch_fused(const kk_adain_in* a, const void* w, const kk_conv_desc*
   // bit 0 = next-tile L2 prefetch (on), bit 1 = disable the deep raw ring, bit 2 = no residual prefetch (on).  The
   // environment is read in -DKK_TUNE builds only (experiments); the product build has no knobs.
   static const int flags = fv_tune_int("KK_L2PF", 5);
+#ifdef KK_TUNE
+  {
+    static const int knock = fv_tune_int("KK_XF_KNOCK", 0);
+    static bool set = false;
+    if (!set) { cudaMemcpyToSymbol(g_fv_xf_knock, &knock, sizeof(int)); set = true; }
+  }
+#endif
   if constexpr (CL > 1) {
     grid -= grid % CL;                        // whole clusters (callers fall back to CL = 1 for tiny problems)
     cudaLaunchConfig_t cfg = {};
