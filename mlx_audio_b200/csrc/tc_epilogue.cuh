@@ -260,7 +260,10 @@ __device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const EpiLim& l
   const int j = m * d.up + e.ph - d.up_off;
   e.acc_valid = (j >= 0) && (j < lim.lt);
   e.out_row = j + d.left_pad;
-  e.row_ok = (m < d.M) && (e.out_row >= 0) && (e.out_row < d.L_out);
+  // nb >= N: a chunk of the last column tile past the GEMM's N (N a multiple of 32 but not of the tile width).  Its
+  // "phase" / channel offset lie outside the tensors: the box path is clipped by the tensor map, the per-row path must
+  // not store at all (phase = up lands on the NEXT row block's phase 0: it raced with the owner of those rows)
+  e.row_ok = (nb < d.N) && (m < d.M) && (e.out_row >= 0) && (e.out_row < d.L_out);
   e.live = e.row_ok && e.out_row < lim.lo;
   return e;
 }
@@ -270,7 +273,7 @@ __device__ __forceinline__ EpiRow epi_row(const kk_conv_desc& d, const EpiLim& l
 __device__ __forceinline__ bool epi_interior(const kk_conv_desc& d, const EpiLim& lim, const int m0w, const int nb) {
   const int ph = d.up > 1 ? nb / d.C_out : 0;
   const int j0 = m0w * d.up + ph - d.up_off, r0 = j0 + d.left_pad;
-  return m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < lim.lo && j0 >= 0 && j0 + 31 * d.up < lim.lt;
+  return nb < d.N && m0w + 31 < d.M && r0 >= 0 && r0 + 31 * d.up < lim.lo && j0 >= 0 && j0 + 31 * d.up < lim.lt;
 }
 
 // all lanes: start the residual transfer of the chunk whose first column is nb, rows m0w..m0w+31 (lane = row)
@@ -341,7 +344,7 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] += rres[i];
   }
-  if (d.bias) {
+  if (d.bias && nb < d.N) {
 #pragma unroll
     for (int c4 = 0; c4 < 8; ++c4) {
       const float4 bs = __ldg(reinterpret_cast<const float4*>(d.bias + e.cbase + c4 * 4));

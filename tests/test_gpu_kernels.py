@@ -342,6 +342,29 @@ TF32_CASES = [
 ]
 
 
+# N a multiple of 32 but not of the 128-column tile, rows not a multiple of 32: the last column tile has chunks past N,
+# and the edge row blocks take the per-row store path.  Round 2 found those chunks stored anyway there - a polyphase
+# chunk with "phase = up" landed on phase 0 of the next row block (bias only) and raced with its owner (SNAC's stride-7
+# upsampler failed once in ~10 full-suite runs); with up = 1 it wrote past the row.
+PAST_N_CASES = [
+    dict(B=2, Lin=37, Cin=96, Cout=32, k=0, dil=1, transposed_up=6, with_res=False),     # N = 192: chunks 6, 7 of tile 1 are past N
+    dict(B=2, Lin=45, Cin=64, Cout=96, k=3, dil=1, with_res=False),                       # N = 96 in a 128-wide tile
+    dict(B=2, Lin=45, Cin=64, Cout=96, k=3, dil=1),                                       # ... with residuals
+]
+
+
+@pytest.mark.parametrize("kind", ["bf16", "tf32x3"])
+@pytest.mark.parametrize("case", PAST_N_CASES)
+def test_conv_tc_chunks_past_n_are_not_stored(lib, case, kind):
+    if not lib.kk_device_is_sm100():
+        pytest.skip("needs sm_100")
+    for rep in range(12):            # a race: repeat with fresh buffers
+        if kind == "bf16":
+            _conv_case(lib, True, **case)
+        else:
+            _conv_case(lib, False, tf32_terms=3, **case)
+
+
 @pytest.mark.parametrize("terms", [3, 1])
 @pytest.mark.parametrize("case", TF32_CASES)
 def test_conv1d_tf32_tc(lib, case, terms):
