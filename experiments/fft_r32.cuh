@@ -1,3 +1,5 @@
+// LAB CODE (not part of the product build; csrc/fft.cu includes it only under -DKK_FFT_R32): measured slower than the
+// radix-8 kernels, kept for the record (profiles/r02_fft_experiments.txt 2).
 // Single-exchange 512-point complex FFT (= the 1024-point real transform of the general STFT / iSTFT / log-mel kernels,
 // mlx_audio/utils.py:52-158): one transform = 16 threads x 32 points, 512 = 32 x 16.
 //   forward:  pass 1  thread j holds x[j + 16 t] (t < 32): radix-32 in registers, twiddle W512^(j k1), ONE exchange
@@ -12,7 +14,7 @@
 // Exchange layout: row k1 at pitch 17 (Y[k1][j] at k1 * 17 + j): stores (fixed k1, lanes j) are consecutive, loads
 // (fixed j, lane m at row m or 32 - m) hit bank (j +- m) mod 16: both conflict free, every address is base + immediate.
 #pragma once
-#include "fft_fast.cuh"
+#include "../mlx_audio_b200/csrc/fft_fast.cuh"
 
 namespace kk {
 namespace fr {

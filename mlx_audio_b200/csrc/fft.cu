@@ -8,7 +8,7 @@
 #include "common.cuh"
 #include "fft_fast.cuh"
 #ifdef KK_FFT_R32   // lab build: the single-exchange forward kernel (measured slower, profiles/r02_fft_experiments.txt)
-#include "fft_r32.cuh"
+#include "../../experiments/fft_r32.cuh"
 #endif
 #include <math.h>
 
