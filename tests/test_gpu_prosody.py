@@ -94,6 +94,29 @@ def test_shared_lstm_native_vs_oracle_and_cudnn(weights, oracle, B, Lq):
 
 
 @pytest.mark.timeout(120)
+@pytest.mark.parametrize("H,D,B,Lq", [(64, 24, 3, 19), (128, 100, 9, 33), (192, 64, 1, 7), (256, 640, 5, 12)])
+def test_lstm_kernel_other_sizes_vs_cudnn(H, D, B, Lq):
+    """kk_lstm_bidir_f32 through the C ABI at every hidden size it accepts (clusters of 8 CTAs, H / 8 units each), with the
+    input projection done in fp64 on the host side of the test; H = 96 must be rejected."""
+    lib = L.load()
+    g = torch.Generator().manual_seed(H + Lq)
+    m = torch.nn.LSTM(D, H, batch_first=True, bidirectional=True).cuda().eval()
+    x = torch.randn(B, Lq, D, generator=g).cuda()
+    with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        ref = m(x)[0]
+    xw = torch.cat([(x.double() @ getattr(m, f"weight_ih_l0{s}").double().t()
+                     + getattr(m, f"bias_ih_l0{s}").double() + getattr(m, f"bias_hh_l0{s}").double()) for s in ("", "_reverse")],
+                   dim=2).float().contiguous()                                     # (B, L, 2 * 4H)
+    whT = torch.stack([m.weight_hh_l0.detach().t(), m.weight_hh_l0_reverse.detach().t()]).contiguous()
+    h_ws = torch.empty(2, 2, B, H, device="cuda")
+    out = torch.empty(B, Lq, 2 * H, device="cuda")
+    L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, Lq, H, None, L.stream()))
+    torch.cuda.synchronize()
+    assert float((out - ref).abs().max()) <= 2e-5
+    assert lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, Lq, 96, None, L.stream()) == L.KK_ERR_UNSUPPORTED
+
+
+@pytest.mark.timeout(120)
 def test_shared_lstm_ragged_lengths_match_solo(weights):
     """lengths=: every sequence of a padded batch equals running it alone (the backward direction starts at its own last
     step), zeros after its end; the padding holds garbage."""
