@@ -202,12 +202,12 @@ int kk_istft_head_n20(const float* y, int y_pitch, float* audio, int B, int F, c
  * xw  (B, L, 2, 4H): x Wx^T + b_ih + b_hh of every step, forward direction first (one GEMM, e.g. kk_conv1d_tf32_tc as
  *                    a 1x1 convolution with the two directions' weights stacked);
  * whT (2, H, 4H):    recurrent weights, transposed (whT[d][k][c] = Wh_d[c][k]);
- * h_ws (2, 2, B, H): scratch for the per-step exchange of h between the CTAs of a cluster;
  * out (B, L, 2H):    h of the forward direction in [0, H), of the backward direction in [H, 2H).
  * lens (B ints, device, or NULL): valid steps per sequence - the backward direction starts at each sequence's own last
- * step, rows past a sequence's end are zeros.  H in {64, 128, 192, 256}.  Thread-block clusters of 8 CTAs. */
-int kk_lstm_bidir_f32(const float* xw, const float* whT, float* h_ws, float* out, int B, int L, int H,
-                      const int* lens, void* stream);
+ * step, rows past a sequence's end are zeros.  H in {64, 128, 192, 256}.  Thread-block clusters of 8 CTAs; h of a step
+ * travels between them through distributed shared memory (no scratch). */
+int kk_lstm_bidir_f32(const float* xw, const float* whT, float* out, int B, int L, int H, const int* lens,
+                      void* stream);
 
 /* ---- general STFT / iSTFT / log-mel (mlx_audio/utils.py:52-158,164-237), batched over signals.
  * window: n_fft floats (already zero-extended).  pad_mode: 0 none(center=False) 1 reflect 2 constant.

@@ -81,7 +81,7 @@ PROTOTYPES = {
     "kk_clip_f32": [_P, _P, _F, _F, _LL, _P],
     "kk_axpby_f32": [_P, _P, _P, _F, _F, _LL, _P],
     "kk_aa_act_f32": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _P],
-    "kk_lstm_bidir_f32": [_P, _P, _P, _P, _I, _I, _I, _P, _P],
+    "kk_lstm_bidir_f32": [_P, _P, _P, _I, _I, _I, _P, _P],
     "kk_stft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P],
     "kk_logmel_f32": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P, _P],
     "kk_istft_f32": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _I, _P],

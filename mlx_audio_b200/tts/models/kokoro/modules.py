@@ -192,9 +192,8 @@ class ProsodyPredictor:
                 raise ValueError(f"lengths: expected {B} entries, got {lens.numel()}")
         xw = pc(x)                                              # (B, L, 2 * 4H)
         st = L.stream()
-        h_ws = torch.empty(2, 2, B, H, device=self.device)
         out = torch.empty(B, L_, 2 * H, device=self.device)
-        L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, L_, H,
+        L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(out), B, L_, H,
                                       None if lens is None else L.ptr(lens), st), "kk_lstm_bidir_f32")
         return out
 

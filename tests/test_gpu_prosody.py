@@ -108,12 +108,11 @@ def test_lstm_kernel_other_sizes_vs_cudnn(H, D, B, Lq):
                      + getattr(m, f"bias_ih_l0{s}").double() + getattr(m, f"bias_hh_l0{s}").double()) for s in ("", "_reverse")],
                    dim=2).float().contiguous()                                     # (B, L, 2 * 4H)
     whT = torch.stack([m.weight_hh_l0.detach().t(), m.weight_hh_l0_reverse.detach().t()]).contiguous()
-    h_ws = torch.empty(2, 2, B, H, device="cuda")
     out = torch.empty(B, Lq, 2 * H, device="cuda")
-    L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, Lq, H, None, L.stream()))
+    L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(out), B, Lq, H, None, L.stream()))
     torch.cuda.synchronize()
     assert float((out - ref).abs().max()) <= 2e-5
-    assert lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(h_ws), L.ptr(out), B, Lq, 96, None, L.stream()) == L.KK_ERR_UNSUPPORTED
+    assert lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(out), B, Lq, 96, None, L.stream()) == L.KK_ERR_UNSUPPORTED
 
 
 @pytest.mark.timeout(120)
