@@ -17,7 +17,7 @@ for i in range(n):
     a = min(x[i]["ms"] for x in A); b = min(x[i]["ms"] for x in B)
     tot[0] += a; tot[1] += b
     o = A[0][i]
-    if o["op"] == "kk_conv1d_adain_bf16_tc" and abs(a - b) > 0.01:
-        print(i, f"C={o.get('C_in')} taps={o.get('taps')} res={o.get('res')} out={o.get('out')} add={o.get('out_add')}  A {a:.3f}  B {b:.3f}  {b / a:.2f}x")
+    if abs(a - b) > 0.01:
+        print(i, o["op"], f"C={o.get('C_in')} taps={o.get('taps')} res={o.get('res')} out={o.get('out')} add={o.get('out_add')}  A {a:.3f}  B {b:.3f}  {b / a:.2f}x")
 print("total A %.2f  B %.2f" % tuple(tot))
 PY

@@ -66,6 +66,9 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                          const int direct_epi, const int terms) {
   using Cfg = TpCfg<BN, TF32>;
   constexpr int TC_BK = Cfg::BK;
+#ifdef KK_TP_DBG
+  const long long t_start_ = clock64();
+#endif
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   float* staging = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
@@ -122,7 +125,7 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
           const int s = kbg % Cfg::STAGES;
           const uint32_t ph = (kbg / Cfg::STAGES) & 1;
-          ptx::mbar_wait(&empty_bar[s], ph ^ 1);
+          { TP_T0; ptx::mbar_wait(&empty_bar[s], ph ^ 1); TP_ACC(0, 0); }
           const int t = kb / cblocks, cb = kb - t * cblocks;
           uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
           ptx::mbar_expect_tx(&full_bar[s], Cfg::TX_BYTES);
@@ -143,7 +146,7 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       uint32_t kbg = 0, it = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
         const uint32_t acc = it & 1, aph = (it >> 1) & 1;
-        ptx::mbar_wait(&tmem_empty_bar[acc], aph ^ 1);  // epilogue has drained this accumulator
+        { TP_T0; ptx::mbar_wait(&tmem_empty_bar[acc], aph ^ 1); TP_ACC(1, 32); }  // epilogue has drained this accumulator
         ptx::tc_fence_after();
         const uint32_t tacc = tmem_base + acc * BN;
         for (int kb = 0; kb < num_kb; ++kb, ++kbg) {
@@ -169,7 +172,7 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               }
             }
           } else {
-            ptx::mbar_wait(&full_bar[s], ph);
+            { TP_T0; ptx::mbar_wait(&full_bar[s], ph); TP_ACC(2, 32); }
             ptx::tc_fence_after();
             const uint32_t sb = sa + TC_A_BYTES;
             const uint64_t ad0 = ptx::umma_desc(sa, 16, 1024, ptx::UMMA_LAYOUT_SW128), bd0 = ptx::umma_desc(sb, 16, 1024, ptx::UMMA_LAYOUT_SW128);
@@ -263,10 +266,11 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int nx_m0 = nx_mt * TC_BM, nx_n0 = (ntile % n_tiles) * BN;
       const uint32_t acc = it & 1, aph = (it >> 1) & 1;
       float* s_stats = s_stats_all + acc * (8 * BN);
-      ptx::mbar_wait(&tmem_full_bar[acc], aph);
+      { TP_T0; ptx::mbar_wait(&tmem_full_bar[acc], aph); TP_ACC(3, 64); }
       ptx::tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < n_mine; ++c) {
+        TP_T0;
         const int ch = ch_first + c;
         const bool last = c + 1 == n_mine;
         float cs = 0.f, cq = 0.f;
@@ -277,7 +281,7 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                                 tmem_base + acc * BN + ((uint32_t)(lg * 32) << 16) + (uint32_t)(ch * 32),
                                 stg + bufi * EPI_TILE_BYTES, &rbar[bufi], (item / NBUF) & 1, do_stats, cs, cq);
           if (d.res) {
-            if (d.out) ptx::bulk_wait_read<0>();      // the lane's row store has read the tile
+            { TP_T0; if (d.out) ptx::bulk_wait_read<0>(); TP_ACC(6, 64); }      // the lane's row store has read the tile
             ptx::fence_proxy_async();                 // generic accesses to the tile precede the next TMA write
             __syncwarp();
             issue_res(item + NBUF);
@@ -289,6 +293,7 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                              last ? ch_first : ch + 1);
         }
         if (do_stats) { s_stats[(lg * 2 + 0) * BN + ch * 32 + lane] = cs; s_stats[(lg * 2 + 1) * BN + ch * 32 + lane] = cq; }
+        TP_ACC(8, 64);
       }
       // all tcgen05.ld of this thread have completed (wait::ld inside the chunk): hand the accumulator back
       ptx::tc_fence_before();
@@ -312,6 +317,9 @@ conv1d_tc_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 2) ptx::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+#ifdef KK_TP_DBG
+  if (blockIdx.x == 0 && threadIdx.x == 0) { g_tp_clk[7] += (unsigned long long)(clock64() - t_start_); g_tp_clk[9] += 1; }
+#endif
 }
 
 }  // namespace kk
@@ -452,6 +460,16 @@ static int launch_tc_persist(const void* x, const void* w, const void* w_lo, con
   KK_LAUNCH_CHECK(TF32 ? "conv1d_tc_persist_kernel<tf32>" : "conv1d_tc_persist_kernel<bf16>");
   return KK_OK;
 }
+
+#ifdef KK_TP_DBG
+}  // namespace kk
+extern "C" int kk_tp_dbg_read(unsigned long long* host16, int reset) {
+  cudaMemcpyFromSymbol(host16, kk::g_tp_clk, sizeof(unsigned long long) * 16);
+  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(kk::g_tp_clk, z, sizeof(z)); }
+  return 0;
+}
+namespace kk {
+#endif
 
 // fp32 -> (hi, lo) with hi = x rounded to TF32's 10 mantissa bits, lo = x - hi (exact) rounded the same way, so that
 // the tensor core's own conversion cannot change either operand

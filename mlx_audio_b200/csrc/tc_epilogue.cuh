@@ -246,6 +246,19 @@ __device__ __forceinline__ void epilogue_chunk(const kk_conv_desc& d, const EpiL
 //     valid row, unswizzled (rare, so the bank conflicts do not matter).  A 128-byte request costs the TMA unit
 //     about as much as a 4 KB one (~20 clk), which is why this is the fallback and not the rule.
 // The bf16 activation copy (64-byte row segments) goes straight from registers.
+#ifdef KK_TP_DBG
+// lab build: clocks one thread per role of CTA 0 spends waiting (persistent conv; read by kk_tp_dbg_read)
+static __device__ unsigned long long g_tp_clk[16];
+#define TP_T0 const long long t0_ = clock64()
+#define TP_ACC(i, who) do { if (blockIdx.x == 0 && threadIdx.x == (who)) g_tp_clk[i] += (unsigned long long)(clock64() - t0_); } while (0)
+#define TP_MARK0 long long tm_ = clock64()
+#define TP_MARK(i) do { const long long c_ = clock64(); if (blockIdx.x == 0 && threadIdx.x == 64) g_tp_clk[i] += (unsigned long long)(c_ - tm_); tm_ = c_; } while (0)
+#else
+#define TP_MARK0 do {} while (0)
+#define TP_MARK(i) do {} while (0)
+#define TP_T0 do {} while (0)
+#define TP_ACC(i, who) do {} while (0)
+#endif
 constexpr int EPI_TILE_BYTES = 4096;
 constexpr int EPI_NBUF = 2;        // staging tiles per epilogue warp = residual prefetch distance
 
@@ -308,14 +321,16 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
                                                         const uint32_t tmem_addr, uint8_t* st, uint64_t* rbar,
                                                         const uint32_t rparity, const bool do_stats, float& col_sum,
                                                         float& col_sq) {
+  TP_MARK0;
   const EpiRow e = epi_row(d, lim, m0w + lane, nb);
   constexpr int WSW = INTERIOR ? 7 : 0;                                  // swizzle mask of the result tile
   const int rsw = (INTERIOR && d.res_shift == 0) ? 7 : 0;               // ... and of the tile as the residual arrived
   const bool acc_valid = INTERIOR || e.acc_valid, row_ok = INTERIOR || e.row_ok;
   float v[32];
   ptx::tmem_ld_32x32(tmem_addr, v);
-  if (d.res) ptx::mbar_wait(rbar, rparity);
+  { TP_T0; if (d.res) ptx::mbar_wait(rbar, rparity); TP_ACC(4, 64); }
   ptx::tmem_ld_wait();
+  TP_MARK(10);
   float* row = reinterpret_cast<float*>(st) + lane * 32;
   float rres[32];                                     // this lane's residual row (kept: the non-interior masks re-use it)
 #pragma unroll
@@ -367,6 +382,7 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] *= d.scale;
   }
+  TP_MARK(11);
   const size_t orow = (size_t)b * d.L_out + (row_ok ? e.out_row : 0);
   // bf16 activation copy.  Interior chunks with a staging tile: 32 rows x 64 bytes written with the 64-byte swizzle
   // (16-byte chunk ^= (row >> 1) & 3: conflict-free for lane = row) and stored as ONE tensor-map box together with the
@@ -384,7 +400,9 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
       q[c8].z = *reinterpret_cast<uint32_t*>(&p2); q[c8].w = *reinterpret_cast<uint32_t*>(&p3);
     }
     if (act_box) {
+      TP_T0;
       ptx::bulk_wait_read<0>();                        // the previous box store has read the (single) bf16 tile
+      TP_ACC(5, 64);
       __syncwarp();
 #pragma unroll
       for (int c8 = 0; c8 < 4; ++c8)
@@ -395,6 +413,7 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
       for (int c8 = 0; c8 < 4; ++c8) ap[c8] = q[c8];
     }
   }
+  TP_MARK(12);
   if (d.out || do_stats) {
     if (!d.res) ptx::bulk_wait_read<EPI_NBUF - 1>();   // the store that left this tile EPI_NBUF items ago has read it
     __syncwarp();                                      // ... for every lane; and every lane holds its residual row
@@ -412,12 +431,14 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
       if (!act_box) ptx::bulk_commit();
     }
   }
+  TP_MARK(13);
   if (act_box) {                                       // one bulk group per chunk: fp32 box (if any) + bf16 box
     ptx::fence_proxy_async();
     __syncwarp();
     if (lane == 0) ptx::tma_store_4d(tmAct, act_tile, e.cbase, e.ph, m0w, b);
     ptx::bulk_commit();
   }
+  TP_MARK(14);
   if (do_stats) {
     __syncwarp();
     float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;   // lane = column: sums over the warp's 32 rows
@@ -432,6 +453,7 @@ __device__ __forceinline__ void epilogue_chunk_direct_t(const kk_conv_desc& d, c
     col_sum = s0 + s1;
     col_sq = q0 + q1;
   }
+  TP_MARK(15);
   __syncwarp();                                    // the tile may be overwritten by the next residual copy
 }
 
