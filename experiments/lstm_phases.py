@@ -18,7 +18,8 @@ def run():
     L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(out), B, Lq, H, None, L.stream()), "lstm")
 
 
-for _ in range(3):
+import os
+for _ in range(int(os.environ.get("WARM", "3"))):      # WARM=300: ~0.6 s of back-to-back launches, clocks fully ramped
     run()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

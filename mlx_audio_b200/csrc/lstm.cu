@@ -19,7 +19,6 @@ namespace kk {
 using namespace ptx;
 
 constexpr int LSTM_CS = 8;     // CTAs per cluster = slices of the hidden units
-constexpr int LSTM_R = 8;      // sequences per cluster
 
 __device__ __forceinline__ void cluster_sync_acqrel() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -41,16 +40,19 @@ __device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { f2 r; asm("fma.rn.f32x2 %
 #endif
 constexpr int LSTM_KQ = LSTM_KQ_;   // the k range of the recurrent product is split over this many threads per column pair
 
-// grid (LSTM_CS, ceil(B / LSTM_R), 2), cluster (LSTM_CS, 1, 1), block 2 UC LSTM_KQ threads (UC = H / LSTM_CS), the first LSTM_R UC of them own a cell.
-__global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const float* __restrict__ whT,
+// grid (LSTM_CS, ceil(B / R), 2), cluster (LSTM_CS, 1, 1), block 2 UC LSTM_KQ threads (UC = H / LSTM_CS), the first R UC of
+// them own a cell.  R = sequences per cluster: the result of a sequence does not depend on it (its sums run over k in the
+// same order whoever its neighbours are); the host picks it so that all clusters are co-resident.
+template <int R>
+__global__ void __launch_bounds__(LSTM_KQ * 64, 1) lstm_bidir_cluster_kernel(const float* __restrict__ xw, const float* __restrict__ whT,
                                           float* __restrict__ out, int B, int L, int H, const int* __restrict__ lens) {
   extern __shared__ __align__(16) unsigned char smem_[];
   const int UC = H / LSTM_CS, NCOL = 4 * UC;
   float* ws = reinterpret_cast<float*>(smem_);          // [H][NCOL]            recurrent weights of this CTA's units
-  float* hs = ws + (size_t)H * NCOL;                    // [2][LSTM_R][H]       h(t-1) / h(t) of the cluster's sequences
-  float* pre = hs + (size_t)2 * LSTM_R * H;             // [LSTM_KQ][LSTM_R][NCOL] partial h Wh^T of this step
+  float* hs = ws + (size_t)H * NCOL;                    // [2][R][H]       h(t-1) / h(t) of the cluster's sequences
+  float* pre = hs + (size_t)2 * R * H;             // [LSTM_KQ][R][NCOL] partial h Wh^T of this step
   const int j = (int)cluster_ctarank();                 // hidden-unit slice
-  const int dir = blockIdx.z, b0 = blockIdx.y * LSTM_R;
+  const int dir = blockIdx.z, b0 = blockIdx.y * R;
   const int tid = threadIdx.x, nthr = blockDim.x;
 
   // resident weights: column (g, uu) of this CTA = row g H + j UC + uu of Wh = column of whT[dir]
@@ -58,7 +60,7 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
     const int k = i / NCOL, c = i - k * NCOL, g = c / UC, uu = c - g * UC;
     ws[i] = whT[((size_t)dir * H + k) * (4 * H) + g * H + j * UC + uu];
   }
-  for (int i = tid; i < 2 * LSTM_R * H; i += nthr) hs[i] = 0.f;
+  for (int i = tid; i < 2 * R * H; i += nthr) hs[i] = 0.f;
   __shared__ __align__(8) uint64_t hbar[2];             // "h buffer [i] is complete" (same offset in every CTA of the cluster)
   if (tid == 0) {
     mbar_init(&hbar[0], 1);
@@ -69,13 +71,13 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
   // gate phase: thread -> (sequence r, unit uu); matvec phase: thread -> (column pair, quarter of the k range), all
   // eight sequences: per four k one 128-bit broadcast load of h per sequence and four 64-bit loads of two weights, 32
   // FFMA2 (the two columns of a pair in one instruction, h as the scalar operand).
-  const bool cell = tid < LSTM_R * UC;                  // (half of the block at LSTM_KQ = 8)
+  const bool cell = tid < R * UC;                  // (half of the block at LSTM_KQ = 8)
   const int r = cell ? tid / UC : 0, uu = cell ? tid - r * UC : 0;
   const int b = b0 + r;
   const bool row_ok = cell && b < B;
   const int len = row_ok ? (lens ? min(max(lens[b], 0), L) : L) : 0;
   int lmax = 0;
-  for (int i = 0; i < LSTM_R; ++i) {
+  for (int i = 0; i < R; ++i) {
     const int bi = b0 + i;
     if (bi < B) lmax = max(lmax, lens ? min(max(lens[bi], 0), L) : L);
   }
@@ -100,7 +102,7 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
     const int t = dir == 0 ? s : len - 1 - s;
     const int cur = s & 1;
     const bool last = s == lmax - 1;                    // (lmax is the same in every CTA of the cluster)
-    if (tid == 0 && !last) mbar_expect_tx(&hbar[cur ^ 1], (uint32_t)(LSTM_R * H * sizeof(float)));   // h(t) of this step
+    if (tid == 0 && !last) mbar_expect_tx(&hbar[cur ^ 1], (uint32_t)(R * H * sizeof(float)));   // h(t) of this step
     // this step's input projections (four gates of this thread's cell): in flight during the matvec
     float zi = 0.f, zf = 0.f, zg = 0.f, zo = 0.f;
     if (active) {
@@ -111,20 +113,20 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
     if (s > 0) mbar_wait(&hbar[cur], (uint32_t)(((s - 1) >> 1) & 1));   // all of h(t-1) is here
     LSTM_MARK(4);
     // h(t-1) Wh^T for this CTA's columns: partial sums over this thread's quarter of k
-    f2 acc[LSTM_R];
+    f2 acc[R];
 #pragma unroll
-    for (int q = 0; q < LSTM_R; ++q) acc[q] = 0ull;
+    for (int q = 0; q < R; ++q) acc[q] = 0ull;
     const f2* wp = reinterpret_cast<const f2*>(ws + (size_t)kq * kper * NCOL) + cp;
-    const float* hp = hs + (size_t)cur * LSTM_R * H + kq * kper;
+    const float* hp = hs + (size_t)cur * R * H + kq * kper;
 #pragma unroll 2
     for (int k = 0; k < kper; k += 4) {
-      float4 hv[LSTM_R];
+      float4 hv[R];
 #pragma unroll
-      for (int q = 0; q < LSTM_R; ++q) hv[q] = *reinterpret_cast<const float4*>(hp + (size_t)q * H + k);
+      for (int q = 0; q < R; ++q) hv[q] = *reinterpret_cast<const float4*>(hp + (size_t)q * H + k);
       const f2 w0 = wp[(size_t)(k + 0) * (NCOL / 2)], w1 = wp[(size_t)(k + 1) * (NCOL / 2)];
       const f2 w2 = wp[(size_t)(k + 2) * (NCOL / 2)], w3 = wp[(size_t)(k + 3) * (NCOL / 2)];
 #pragma unroll
-      for (int q = 0; q < LSTM_R; ++q) {
+      for (int q = 0; q < R; ++q) {
         acc[q] = fma2(pack2(hv[q].x, hv[q].x), w0, acc[q]);
         acc[q] = fma2(pack2(hv[q].y, hv[q].y), w1, acc[q]);
         acc[q] = fma2(pack2(hv[q].z, hv[q].z), w2, acc[q]);
@@ -132,9 +134,9 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
       }
     }
     {
-      f2* pp = reinterpret_cast<f2*>(pre + (size_t)kq * LSTM_R * NCOL) + cp;   // (row, column pair)
+      f2* pp = reinterpret_cast<f2*>(pre + (size_t)kq * R * NCOL) + cp;   // (row, column pair)
 #pragma unroll
-      for (int q = 0; q < LSTM_R; ++q) pp[(size_t)q * (NCOL / 2)] = acc[q];
+      for (int q = 0; q < R; ++q) pp[(size_t)q * (NCOL / 2)] = acc[q];
     }
     LSTM_MARK(1);
     __syncthreads();
@@ -147,7 +149,7 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
       for (int g = 0; g < 4; ++g) {
         float hw_ = pr[g * UC];
 #pragma unroll
-        for (int q = 1; q < LSTM_KQ; ++q) hw_ += pr[(size_t)q * LSTM_R * NCOL + g * UC];   // fixed order
+        for (int q = 1; q < LSTM_KQ; ++q) hw_ += pr[(size_t)q * R * NCOL + g * UC];   // fixed order
         z[g] += hw_;
       }
       const float ig = sigmoidf_(z[0]), fg = sigmoidf_(z[1]);
@@ -160,7 +162,7 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
     // the last step, whose h nobody reads.  WAR on the buffers: a peer can only send h(t+1) into the buffer this CTA
     // reads now after it has received this CTA's h(t), which is sent below - after the matvec of this step.
     if (cell && !last) {
-      const uint32_t off = (uint32_t)((cur ^ 1) * LSTM_R * H) * 4u, boff = bar_rel + 8u * (cur ^ 1);
+      const uint32_t off = (uint32_t)((cur ^ 1) * R * H) * 4u, boff = bar_rel + 8u * (cur ^ 1);
 #pragma unroll
       for (int c = 0; c < LSTM_CS; ++c)
         asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(peer[c] + off),
@@ -174,6 +176,45 @@ __global__ void lstm_bidir_cluster_kernel(const float* __restrict__ xw, const fl
   // sequences shorter than L inside a cluster whose longest is shorter than L too: zero the remaining rows
   if (row_ok)
     for (int s = max(lmax, len); s < L; ++s) out[((size_t)b * L + s) * (2 * H) + dir * H + j * UC + uu] = 0.f;
+}
+
+// Launch with R sequences per cluster; with `fit` != nullptr only report how many such clusters are co-resident.
+template <int R>
+static int lstm_launch(const float* xw, const float* whT, float* out, int B, int L, int H, const int* lens, cudaStream_t stream,
+                       int* fit) {
+  const int UC = H / LSTM_CS, NCOL = 4 * UC;
+  const size_t smem = ((size_t)H * NCOL + (size_t)2 * H * R + (size_t)LSTM_KQ * R * NCOL) * sizeof(float);
+  KK_CUDA(cudaFuncSetAttribute(lstm_bidir_cluster_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(LSTM_CS, (unsigned)cdiv(B, R), 2);
+  cfg.blockDim = dim3(2 * UC * LSTM_KQ);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = LSTM_CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (fit) {
+    KK_CUDA(cudaOccupancyMaxActiveClusters(fit, lstm_bidir_cluster_kernel<R>, &cfg));
+    return KK_OK;
+  }
+  KK_CUDA(cudaLaunchKernelEx(&cfg, lstm_bidir_cluster_kernel<R>, xw, whT, out, B, L, H, lens));
+  return KK_OK;
+}
+
+// co-resident clusters for (R, H) on the current device, cached (a property of the device and the kernel image)
+static int lstm_max_clusters(int R, int H) {
+  static int cache[3][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}};
+  const int ri = R == 8 ? 0 : R == 10 ? 1 : 2, hi = H / 64 - 1;
+  if (cache[ri][hi] == 0) {
+    int fit = 0, rc;
+    if (R == 8) rc = lstm_launch<8>(nullptr, nullptr, nullptr, 8, 1, H, nullptr, nullptr, &fit);
+    else if (R == 10) rc = lstm_launch<10>(nullptr, nullptr, nullptr, 8, 1, H, nullptr, nullptr, &fit);
+    else rc = lstm_launch<12>(nullptr, nullptr, nullptr, 8, 1, H, nullptr, nullptr, &fit);
+    if (rc != KK_OK) return -1;
+    cache[ri][hi] = fit > 0 ? fit : -2;     // -2: "none fit" is cached too
+  }
+  return cache[ri][hi] > 0 ? cache[ri][hi] : 0;
 }
 
 }  // namespace kk
@@ -193,19 +234,23 @@ extern "C" int kk_lstm_bidir_f32(const float* xw, const float* whT, float* out, 
     kk::set_error("kk_lstm_bidir_f32: hidden size %d (supported: 64, 128, 192, 256)", H);
     return KK_ERR_UNSUPPORTED;
   }
-  const int UC = H / kk::LSTM_CS, NCOL = 4 * UC;
-  const size_t smem = ((size_t)H * NCOL + (size_t)2 * H * kk::LSTM_R + (size_t)kk::LSTM_KQ * kk::LSTM_R * NCOL) * sizeof(float);
-  KK_CUDA(cudaFuncSetAttribute(kk::lstm_bidir_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(kk::LSTM_CS, (unsigned)kk::cdiv(B, kk::LSTM_R), 2);
-  cfg.blockDim = dim3(2 * UC * kk::LSTM_KQ);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = (cudaStream_t)stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kk::LSTM_CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
-  KK_CUDA(cudaLaunchKernelEx(&cfg, kk::lstm_bidir_cluster_kernel, xw, whT, out, B, L, H, lens));
+  // Sequences per cluster.  A cluster needs 8 SMs of one GPC (one CTA per SM: the weights fill shared memory), and a B200
+  // holds 15 such clusters, not 148 / 8 = 18: with 8 sequences per cluster B = 64 is 16 clusters = TWO waves (1.88 ms at
+  // L = 320); with 10 it is 14 clusters, one wave.  Smallest R whose grid is co-resident, else the largest.
+  int rc = KK_ERR_UNSUPPORTED;
+  const int cand[3] = {8, 10, 12};
+  int pick = 2;
+  for (int i = 0; i < 3; ++i) {
+    const int fit = kk::lstm_max_clusters(cand[i], H);
+    if (fit < 0) return KK_ERR_CUDA;
+    if (2 * kk::cdiv(B, cand[i]) <= fit) { pick = i; break; }
+  }
+  switch (cand[pick]) {
+    case 8: rc = kk::lstm_launch<8>(xw, whT, out, B, L, H, lens, (cudaStream_t)stream, nullptr); break;
+    case 10: rc = kk::lstm_launch<10>(xw, whT, out, B, L, H, lens, (cudaStream_t)stream, nullptr); break;
+    default: rc = kk::lstm_launch<12>(xw, whT, out, B, L, H, lens, (cudaStream_t)stream, nullptr); break;
+  }
+  if (rc != KK_OK) return rc;
   KK_LAUNCH_CHECK("lstm_bidir_cluster_kernel");
   return KK_OK;
 }

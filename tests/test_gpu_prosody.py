@@ -116,6 +116,30 @@ def test_lstm_kernel_other_sizes_vs_cudnn(H, D, B, Lq):
 
 
 @pytest.mark.timeout(120)
+@pytest.mark.parametrize("B", [64, 100, 150])
+def test_lstm_result_does_not_depend_on_the_batch_partition(B):
+    """The kernel picks the number of sequences per cluster from B (8, 10 or 12: all clusters co-resident when they can
+    be - 8 per cluster would make B = 64 two waves) and runs more than one wave beyond that.  A sequence's result must not
+    depend on it: the big batch equals its slices of 8 bit for bit (ragged lengths included)."""
+    H, Lq = 256, 24
+    lib = L.load()
+    g = torch.Generator(device="cuda").manual_seed(B)
+    xw = torch.randn(B, Lq, 2 * 4 * H, device="cuda", generator=g) * 0.7
+    whT = torch.randn(2, H, 4 * H, device="cuda", generator=g) / 16
+    lens = torch.randint(1, Lq + 1, (B,), device="cuda", generator=g, dtype=torch.int32)
+    lens[0] = Lq
+    out = torch.empty(B, Lq, 2 * H, device="cuda")
+    L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(out), B, Lq, H, L.ptr(lens), L.stream()))
+    for b0 in range(0, B, 8):
+        n = min(8, B - b0)
+        xs, ls = xw[b0:b0 + n].contiguous(), lens[b0:b0 + n].contiguous()
+        o = torch.empty(n, Lq, 2 * H, device="cuda")
+        L.check(lib.kk_lstm_bidir_f32(L.ptr(xs), L.ptr(whT), L.ptr(o), n, Lq, H, L.ptr(ls), L.stream()))
+        assert torch.equal(o, out[b0:b0 + n]), b0
+    assert torch.isfinite(out).all()
+
+
+@pytest.mark.timeout(120)
 def test_shared_lstm_ragged_lengths_match_solo(weights):
     """lengths=: every sequence of a padded batch equals running it alone (the backward direction starts at its own last
     step), zeros after its end; the padding holds garbage."""
