@@ -236,14 +236,22 @@ extern "C" int kk_lstm_bidir_f32(const float* xw, const float* whT, float* out, 
   }
   // Sequences per cluster.  A cluster needs 8 SMs of one GPC (one CTA per SM: the weights fill shared memory), and a B200
   // holds 15 such clusters, not 148 / 8 = 18: with 8 sequences per cluster B = 64 is 16 clusters = TWO waves (1.88 ms at
-  // L = 320); with 10 it is 14 clusters, one wave.  Smallest R whose grid is co-resident, else the largest.
+  // L = 320); with 10 it is 14 clusters, one wave (1.11 ms).  Pick the R with the least waves x time per step, the
+  // latter ~ (4 + R) by measurement (5.9 k clocks at R = 8, 6.8 k at R = 10).
   int rc = KK_ERR_UNSUPPORTED;
   const int cand[3] = {8, 10, 12};
-  int pick = 2;
+  int pick = 0;
+  long best = -1;
   for (int i = 0; i < 3; ++i) {
     const int fit = kk::lstm_max_clusters(cand[i], H);
     if (fit < 0) return KK_ERR_CUDA;
-    if (2 * kk::cdiv(B, cand[i]) <= fit) { pick = i; break; }
+    if (fit == 0) continue;
+    const long waves = kk::cdiv(2 * kk::cdiv(B, cand[i]), fit), cost = waves * (4 + cand[i]);
+    if (best < 0 || cost < best) { best = cost; pick = i; }
+  }
+  if (best < 0) {
+    kk::set_error("kk_lstm_bidir_f32: no cluster of %d CTAs fits this device", kk::LSTM_CS);
+    return KK_ERR_UNSUPPORTED;
   }
   switch (cand[pick]) {
     case 8: rc = kk::lstm_launch<8>(xw, whT, out, B, L, H, lens, (cudaStream_t)stream, nullptr); break;
