@@ -780,8 +780,12 @@ static int launch_stft(const StftArgs& a0, const FftPlan& p, int B, cudaStream_t
                   (size_t)2 * ff::GROUPS * ff::BUF * 8 +
                   (MODE == 1 ? (size_t)2 * (a.n_mels + 4) * 4 + (size_t)MEL_ITEMS * (8 + 32) + (size_t)ff::GROUPS * MEL_MAX * 4 + 16 : 0) + 16;
     dim3 grid(cdiv(a.frames, fpb), B);
-    // register-table variant once a thread runs enough frames to amortise its 24 sincospif (A/B knob KK_FFT_RT=0/1)
+    // register-table variant once a thread runs enough frames to amortise its 24 sincospif (A/B knob KK_FFT_RT=0/1 in -DKK_TUNE builds)
+#ifdef KK_TUNE
     static const int rt_env = [] { const char* e = getenv("KK_FFT_RT"); return e ? atoi(e) : -1; }();
+#else
+    constexpr int rt_env = -1;                               // the product library reads no environment
+#endif
     const bool rt = MODE == 0 && (rt_env >= 0 ? rt_env != 0 : fpb >= 64);   // log-mel: measured slower (2.26 -> 2.66 ms)
     if (rt) {
       KK_CUDA(cudaFuncSetAttribute(stft_fast_kernel<MODE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
@@ -880,8 +884,12 @@ extern "C" int kk_istft_f32(const float* spec, const float* window, float* out, 
       return KK_OK;
     };
     // register-table variant: measured slower here (1.35 -> 1.50 ms: the inverse leans on occupancy to cover its
-    // spectrum loads); kept behind KK_IFFT_RT=1 for A/B
+    // spectrum loads); kept behind KK_IFFT_RT=1 (-DKK_TUNE builds) for A/B
+#ifdef KK_TUNE
     static const bool rt = [] { const char* e = getenv("KK_IFFT_RT"); return e && atoi(e) != 0; }();
+#else
+    constexpr bool rt = false;                               // the product library reads no environment
+#endif
     int lrc = sa.R == 4 ? (rt ? launch(kk::istft_stream_kernel<4, true>) : launch(kk::istft_stream_kernel<4, false>))
             : sa.R == 2 ? (rt ? launch(kk::istft_stream_kernel<2, true>) : launch(kk::istft_stream_kernel<2, false>))
                         : (rt ? launch(kk::istft_stream_kernel<1, true>) : launch(kk::istft_stream_kernel<1, false>));
