@@ -4,7 +4,7 @@
 //     z = xw[t] + h Wh^T,   c = sigmoid(z_f) c + sigmoid(z_i) tanh(z_g),   h = sigmoid(z_o) tanh(c).
 // Layout of the work: a thread-block CLUSTER of 8 CTAs owns one direction of 8 sequences.  CTA j of the cluster holds
 // the recurrent weights of hidden units [j H/8, (j+1) H/8) - all four gates, H x 4 (H/8) floats, 128 KB at H = 256 -
-// in shared memory for the whole sequence, so a step moves nothing but h: every CTA stores its slice of h(t) straight
+// in REGISTERS for the whole sequence (64 per thread), so a step moves nothing but h: every CTA stores its slice of h(t) straight
 // into the (double-buffered) h block of all eight CTAs - distributed shared memory, st.async.shared::cluster with
 // mbarrier complete_tx - and every CTA waits on its OWN mbarrier until the R x H floats of the step have arrived: no
 // cluster-wide barrier and no fence in the loop (barrier.cluster's release / acquire compile to MEMBAR.ALL.GPU and an
@@ -43,23 +43,17 @@ constexpr int LSTM_KQ = LSTM_KQ_;   // the k range of the recurrent product is s
 // grid (LSTM_CS, ceil(B / R), 2), cluster (LSTM_CS, 1, 1), block 2 UC LSTM_KQ threads (UC = H / LSTM_CS), the first R UC of
 // them own a cell.  R = sequences per cluster: the result of a sequence does not depend on it (its sums run over k in the
 // same order whoever its neighbours are); the host picks it so that all clusters are co-resident.
-template <int R>
+template <int R, int KPER>
 __global__ void __launch_bounds__(LSTM_KQ * 64, 1) lstm_bidir_cluster_kernel(const float* __restrict__ xw, const float* __restrict__ whT,
                                           float* __restrict__ out, int B, int L, int H, const int* __restrict__ lens) {
   extern __shared__ __align__(16) unsigned char smem_[];
   const int UC = H / LSTM_CS, NCOL = 4 * UC;
-  float* ws = reinterpret_cast<float*>(smem_);          // [H][NCOL]            recurrent weights of this CTA's units
-  float* hs = ws + (size_t)H * NCOL;                    // [2][R][H]       h(t-1) / h(t) of the cluster's sequences
+  float* hs = reinterpret_cast<float*>(smem_);          // [2][R][H]       h(t-1) / h(t) of the cluster's sequences
   float* pre = hs + (size_t)2 * R * H;             // [LSTM_KQ][R][NCOL] partial h Wh^T of this step
   const int j = (int)cluster_ctarank();                 // hidden-unit slice
   const int dir = blockIdx.z, b0 = blockIdx.y * R;
   const int tid = threadIdx.x, nthr = blockDim.x;
 
-  // resident weights: column (g, uu) of this CTA = row g H + j UC + uu of Wh = column of whT[dir]
-  for (int i = tid; i < H * NCOL; i += nthr) {
-    const int k = i / NCOL, c = i - k * NCOL, g = c / UC, uu = c - g * UC;
-    ws[i] = whT[((size_t)dir * H + k) * (4 * H) + g * H + j * UC + uu];
-  }
   for (int i = tid; i < 2 * R * H; i += nthr) hs[i] = 0.f;
   __shared__ __align__(8) uint64_t hbar[2];             // "h buffer [i] is complete" (same offset in every CTA of the cluster)
   if (tid == 0) {
@@ -82,15 +76,25 @@ __global__ void __launch_bounds__(LSTM_KQ * 64, 1) lstm_bidir_cluster_kernel(con
     if (bi < B) lmax = max(lmax, lens ? min(max(lens[bi], 0), L) : L);
   }
   const int cp = tid % (NCOL / 2), kq = tid / (NCOL / 2);
-  const int kper = H / LSTM_KQ;
+  // resident weights, in REGISTERS: this thread's two columns (c = 2 cp, 2 cp + 1; column (g, uu) of this CTA = row
+  // g H + j UC + uu of Wh = column of whT[dir]) over its eighth of k - 2 KPER = 64 registers at H = 256.  The 128 KB slice
+  // of a CTA fills half of the SM's register file instead of its shared memory, and a step reads it at no cost: the
+  // shared-memory data pipe (1024 of ~3300 wavefronts per step were the weights) no longer bounds the matvec.
+  f2 wreg[KPER];
+  {
+    const int c0 = 2 * cp, g0 = c0 / UC, u0 = c0 - g0 * UC;        // UC is even: both columns in the same gate
+    const float* wsrc = whT + ((size_t)dir * H + (size_t)kq * KPER) * (4 * H) + g0 * H + j * UC + u0;
+#pragma unroll
+    for (int k = 0; k < KPER; ++k) {
+      const float2 w2 = *reinterpret_cast<const float2*>(wsrc + (size_t)k * (4 * H));
+      wreg[k] = pack2(w2.x, w2.y);
+    }
+  }
   float cstate = 0.f;
   const size_t xw_row = (size_t)2 * 4 * H;
   // this thread's h goes to the same place of every CTA of the cluster (distributed shared memory)
-  uint32_t peer[LSTM_CS];
   const uint32_t mine = (uint32_t)__cvta_generic_to_shared(hs + (size_t)r * H + j * UC + uu);
   const uint32_t bar_rel = (uint32_t)__cvta_generic_to_shared(&hbar[0]) - mine;   // a peer's window has the same layout
-#pragma unroll
-  for (int c = 0; c < LSTM_CS; ++c) asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(peer[c]) : "r"(mine), "r"(c));
   cluster_sync_acqrel();   // every CTA has cleared its h buffers and set up its mbarriers before a peer writes into them
 #ifdef KK_LSTM_DBG
   const bool dbg = tid == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
@@ -116,21 +120,16 @@ __global__ void __launch_bounds__(LSTM_KQ * 64, 1) lstm_bidir_cluster_kernel(con
     f2 acc[R];
 #pragma unroll
     for (int q = 0; q < R; ++q) acc[q] = 0ull;
-    const f2* wp = reinterpret_cast<const f2*>(ws + (size_t)kq * kper * NCOL) + cp;
-    const float* hp = hs + (size_t)cur * R * H + kq * kper;
-#pragma unroll 2
-    for (int k = 0; k < kper; k += 4) {
-      float4 hv[R];
+    const float* hp = hs + (size_t)cur * R * H + kq * KPER;
 #pragma unroll
-      for (int q = 0; q < R; ++q) hv[q] = *reinterpret_cast<const float4*>(hp + (size_t)q * H + k);
-      const f2 w0 = wp[(size_t)(k + 0) * (NCOL / 2)], w1 = wp[(size_t)(k + 1) * (NCOL / 2)];
-      const f2 w2 = wp[(size_t)(k + 2) * (NCOL / 2)], w3 = wp[(size_t)(k + 3) * (NCOL / 2)];
+    for (int k = 0; k < KPER; k += 4) {
 #pragma unroll
       for (int q = 0; q < R; ++q) {
-        acc[q] = fma2(pack2(hv[q].x, hv[q].x), w0, acc[q]);
-        acc[q] = fma2(pack2(hv[q].y, hv[q].y), w1, acc[q]);
-        acc[q] = fma2(pack2(hv[q].z, hv[q].z), w2, acc[q]);
-        acc[q] = fma2(pack2(hv[q].w, hv[q].w), w3, acc[q]);
+        const float4 hv = *reinterpret_cast<const float4*>(hp + (size_t)q * H + k);
+        acc[q] = fma2(pack2(hv.x, hv.x), wreg[k + 0], acc[q]);
+        acc[q] = fma2(pack2(hv.y, hv.y), wreg[k + 1], acc[q]);
+        acc[q] = fma2(pack2(hv.z, hv.z), wreg[k + 2], acc[q]);
+        acc[q] = fma2(pack2(hv.w, hv.w), wreg[k + 3], acc[q]);
       }
     }
     {
@@ -164,9 +163,12 @@ __global__ void __launch_bounds__(LSTM_KQ * 64, 1) lstm_bidir_cluster_kernel(con
     if (cell && !last) {
       const uint32_t off = (uint32_t)((cur ^ 1) * R * H) * 4u, boff = bar_rel + 8u * (cur ^ 1);
 #pragma unroll
-      for (int c = 0; c < LSTM_CS; ++c)
-        asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(peer[c] + off),
-                     "r"(__float_as_uint(hout)), "r"(peer[c] + boff) : "memory");
+      for (int c = 0; c < LSTM_CS; ++c) {
+        uint32_t pc;                                    // (mapa per send: eight registers are worth more than eight instructions)
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(pc) : "r"(mine), "r"(c));
+        asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(pc + off),
+                     "r"(__float_as_uint(hout)), "r"(pc + boff) : "memory");
+      }
     }
     // (past the sequence's end the state is no longer used - rows are independent - and output row s is zero)
     if (row_ok) out[((size_t)b * L + (active ? t : s)) * (2 * H) + dir * H + j * UC + uu] = hout;
@@ -178,13 +180,12 @@ __global__ void __launch_bounds__(LSTM_KQ * 64, 1) lstm_bidir_cluster_kernel(con
     for (int s = max(lmax, len); s < L; ++s) out[((size_t)b * L + s) * (2 * H) + dir * H + j * UC + uu] = 0.f;
 }
 
-// Launch with R sequences per cluster; with `fit` != nullptr only report how many such clusters are co-resident.
-template <int R>
-static int lstm_launch(const float* xw, const float* whT, float* out, int B, int L, int H, const int* lens, cudaStream_t stream,
-                       int* fit) {
+template <int R, int KPER>
+static int lstm_launch_k(const float* xw, const float* whT, float* out, int B, int L, int H, const int* lens, cudaStream_t stream,
+                         int* fit) {
   const int UC = H / LSTM_CS, NCOL = 4 * UC;
-  const size_t smem = ((size_t)H * NCOL + (size_t)2 * H * R + (size_t)LSTM_KQ * R * NCOL) * sizeof(float);
-  KK_CUDA(cudaFuncSetAttribute(lstm_bidir_cluster_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t smem = ((size_t)2 * H * R + (size_t)LSTM_KQ * R * NCOL) * sizeof(float);   // h (two buffers), partial sums
+  KK_CUDA(cudaFuncSetAttribute(lstm_bidir_cluster_kernel<R, KPER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(LSTM_CS, (unsigned)cdiv(B, R), 2);
   cfg.blockDim = dim3(2 * UC * LSTM_KQ);
@@ -195,11 +196,23 @@ static int lstm_launch(const float* xw, const float* whT, float* out, int B, int
   attr[0].val.clusterDim.x = LSTM_CS; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
   if (fit) {
-    KK_CUDA(cudaOccupancyMaxActiveClusters(fit, lstm_bidir_cluster_kernel<R>, &cfg));
+    KK_CUDA(cudaOccupancyMaxActiveClusters(fit, lstm_bidir_cluster_kernel<R, KPER>, &cfg));
     return KK_OK;
   }
-  KK_CUDA(cudaLaunchKernelEx(&cfg, lstm_bidir_cluster_kernel<R>, xw, whT, out, B, L, H, lens));
+  KK_CUDA(cudaLaunchKernelEx(&cfg, lstm_bidir_cluster_kernel<R, KPER>, xw, whT, out, B, L, H, lens));
   return KK_OK;
+}
+
+// Launch with R sequences per cluster; with `fit` != nullptr only report how many such clusters are co-resident.
+template <int R>
+static int lstm_launch(const float* xw, const float* whT, float* out, int B, int L, int H, const int* lens, cudaStream_t stream,
+                       int* fit) {
+  switch (H / LSTM_KQ) {
+    case 8: return lstm_launch_k<R, 8>(xw, whT, out, B, L, H, lens, stream, fit);
+    case 16: return lstm_launch_k<R, 16>(xw, whT, out, B, L, H, lens, stream, fit);
+    case 24: return lstm_launch_k<R, 24>(xw, whT, out, B, L, H, lens, stream, fit);
+    default: return lstm_launch_k<R, 32>(xw, whT, out, B, L, H, lens, stream, fit);
+  }
 }
 
 // co-resident clusters for (R, H) on the current device, cached (a property of the device and the kernel image)
