@@ -2,13 +2,14 @@
 // i, f, g, o; the `shared` layer of ProsodyPredictor.F0Ntrain :355-358).  The input projection x Wx^T + b_ih + b_hh of
 // all time steps is one GEMM (kk_conv1d_tf32_tc as a 1x1 convolution); this kernel runs the L dependent steps
 //     z = xw[t] + h Wh^T,   c = sigmoid(z_f) c + sigmoid(z_i) tanh(z_g),   h = sigmoid(z_o) tanh(c).
-// Layout of the work: a thread-block CLUSTER of 8 CTAs owns one direction of 8 sequences.  CTA j of the cluster holds
+// Layout of the work: a thread-block CLUSTER of 8 CTAs owns one direction of R = 8, 10 or 12 sequences (the host picks
+// R so that every cluster of the grid is co-resident: a B200 holds 15 of them).  CTA j of the cluster holds
 // the recurrent weights of hidden units [j H/8, (j+1) H/8) - all four gates, H x 4 (H/8) floats, 128 KB at H = 256 -
 // in REGISTERS for the whole sequence (64 per thread), so a step moves nothing but h: every CTA stores its slice of h(t) straight
 // into the (double-buffered) h block of all eight CTAs - distributed shared memory, st.async.shared::cluster with
 // mbarrier complete_tx - and every CTA waits on its OWN mbarrier until the R x H floats of the step have arrived: no
 // cluster-wide barrier and no fence in the loop (barrier.cluster's release / acquire compile to MEMBAR.ALL.GPU and an
-// L1 invalidate, ~1.2 k clocks a step).  16 clusters = 128 CTAs cover B = 64.
+// L1 invalidate, ~1.2 k clocks a step).  14 clusters of 10 sequences = 112 CTAs cover B = 64 in one wave.
 // Ragged batches: `lens` = valid steps per sequence; the backward direction starts at each sequence's own last step,
 // finished sequences stop updating, outputs past a sequence's end are zeros.
 #include "common.cuh"
