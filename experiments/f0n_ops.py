@@ -20,7 +20,16 @@ for dt in ("bf16", "fp32"):
     for _ in range(10):
         pp.F0Ntrain(x, s, borrow=True)
     e1.record(); e1.synchronize()
-    print(f"{dt}: F0Ntrain {e0.elapsed_time(e1) / 10:.3f} ms per call (LSTM included)")
+    print(f"{dt}: F0Ntrain {e0.elapsed_time(e1) / 10:.3f} ms per call (LSTM included, heads on two streams)")
+    pp.parallel_heads = False
+    for _ in range(3):
+        pp.F0Ntrain(x, s, borrow=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        pp.F0Ntrain(x, s, borrow=True)
+    e1.record(); e1.synchronize()
+    print(f"{dt}: F0Ntrain {e0.elapsed_time(e1) / 10:.3f} ms per call (one stream)")
     plan = pp.engine.plans[(B, Lq)]
     recs = plan.run_timed(L.stream()); recs = plan.run_timed(L.stream())
     by = collections.OrderedDict()

@@ -58,7 +58,11 @@ class ProsodyEngine(DecoderEngine):
         h_all = self._buf(plan, "pp.h_all", (B, self.ada_R))
         plan.add(self.lib.kk_style_affine, self._addr(s), self._addr(self.ada_W), self._addr(self.ada_b),
                  self._addr(h_all), B, self.ada_R, self.cfg["style_dim"])
+        # the two heads share nothing but their inputs: N runs as a parallel branch (Plan.run_parallel, like the
+        # decoder's noise branch), forked here and joined after F0's last launch
+        plan.fork_index = len(plan.ops)
         for head in ("F0", "N"):
+            plan.cur_branch = 1 if head == "N" else 0
             y0 = self._buf(plan, f"pp.{head}.y0", (B, L_, d))
             y1 = self._buf(plan, f"pp.{head}.y1", (B, 2 * L_, h2))
             y2 = self._buf(plan, f"pp.{head}.y2", (B, 2 * L_, h2))
@@ -72,6 +76,9 @@ class ProsodyEngine(DecoderEngine):
             self._tap(plan, f"{head}.blocks", y2, lambda t: t.transpose(1, 2))
             self._conv(plan, self.convs[f"{head}_proj"], self._addr(y2), B, 2 * L_, h2, 2 * L_,
                        out_addr=self._addr(out), out_pitch=1, force_f32=True)
+        plan._push((None, ("@done", 0)))
+        plan.cur_branch = 0
+        plan._push((None, ("@join", 0)))
         plan.shape = (B, L_)
         return plan
 
@@ -99,6 +106,8 @@ class ProsodyPredictor:
         self._weights: Dict[str, torch.Tensor] = {}
         self._engine: Optional[ProsodyEngine] = None
         self._lstm = None      # (input-projection GEMM, transposed recurrent weights) once the weights are loaded
+        self.parallel_heads = True          # F0 and N heads on two streams (False: one stream, same launches)
+        self._side: Optional[torch.cuda.Stream] = None
 
     # ------------------------------------------------------------------ weights
     def parameter_shapes(self) -> Dict[str, tuple]:
@@ -246,7 +255,12 @@ class ProsodyPredictor:
         plan.buffers["pp.in.x"].copy_(hidden, non_blocking=True)
         plan.buffers["pp.in.s"].copy_(s, non_blocking=True)
         plan.capture = capture_taps
-        plan.run(L.stream())
+        if self.parallel_heads and not capture_taps:
+            if self._side is None:
+                self._side = torch.cuda.Stream(dev)
+            plan.run_parallel(self._side)
+        else:
+            plan.run(L.stream())
         f0, n = plan.buffers["pp.out.F0"], plan.buffers["pp.out.N"]
         return (f0, n) if borrow else (f0.clone(), n.clone())
 

@@ -246,3 +246,21 @@ def test_model_runs_f0ntrain_when_frontend_returns_en(weights):
     y = build_decoder(dw, dtype="fp32")(din["asr"], F0.clone(), N.clone(), din["s"], seed=3)
     torch.testing.assert_close(out.audio, y[0], rtol=0, atol=1e-6)
     assert out.pred_dur.shape == (10,)
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("dtype", ["fp32", "bf16"])
+def test_f0ntrain_parallel_heads_equal_one_stream(weights, dtype):
+    """The N head runs as a parallel branch on a second stream (forked after the style projection, joined after F0's
+    last launch): the same launches, so the same bits as the one-stream schedule."""
+    B, Lq = 5, 37
+    inp = synth.synth_prosody_inputs(B, Lq, seed=1700)
+    pp = build_prosody_predictor(weights, dtype=dtype)
+    x, s = torch.as_tensor(inp["x"]).cuda(), torch.as_tensor(inp["s"]).cuda()
+    assert pp.parallel_heads
+    f0_p, n_p = pp.F0Ntrain(x, s)
+    f0_p2, n_p2 = pp.F0Ntrain(x, s)
+    pp.parallel_heads = False
+    f0_s, n_s = pp.F0Ntrain(x, s)
+    assert torch.equal(f0_p, f0_s) and torch.equal(n_p, n_s)
+    assert torch.equal(f0_p, f0_p2) and torch.equal(n_p, n_p2)
