@@ -264,3 +264,26 @@ def test_f0ntrain_parallel_heads_equal_one_stream(weights, dtype):
     f0_s, n_s = pp.F0Ntrain(x, s)
     assert torch.equal(f0_p, f0_s) and torch.equal(n_p, n_s)
     assert torch.equal(f0_p, f0_p2) and torch.equal(n_p, n_p2)
+
+
+@pytest.mark.timeout(120)
+def test_lstm_repeated_launches_are_bit_identical():
+    """Stand-in for racecheck on the cluster protocol (st.async into eight CTAs' shared memory, per-CTA mbarriers, two h
+    buffers): 40 launches of the same ragged batch, with other work and fresh allocations in between, give the same bits."""
+    H, B, Lq = 256, 64, 48
+    lib = L.load()
+    g = torch.Generator(device="cuda").manual_seed(77)
+    xw = torch.randn(B, Lq, 2 * 4 * H, device="cuda", generator=g) * 0.7
+    whT = torch.randn(2, H, 4 * H, device="cuda", generator=g) / 16
+    lens = torch.randint(1, Lq + 1, (B,), device="cuda", generator=g, dtype=torch.int32)
+    first = None
+    for i in range(40):
+        out = torch.full((B, Lq, 2 * H), float("nan"), device="cuda")
+        junk = torch.randn(1 << (10 + i % 12), device="cuda")           # shifts the allocator and keeps other kernels in flight
+        junk.mul_(2.0)
+        L.check(lib.kk_lstm_bidir_f32(L.ptr(xw), L.ptr(whT), L.ptr(out), B, Lq, H, L.ptr(lens), L.stream()))
+        if first is None:
+            first = out.clone()
+            assert torch.isfinite(first).all()
+        else:
+            assert torch.equal(out, first), i
